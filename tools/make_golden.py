@@ -1,0 +1,146 @@
+#!/usr/bin/env python
+"""Generate golden input/output vectors by running the UNMODIFIED reference in this container.
+
+The reference (/root/reference) has no tests or fixtures of its own, so parity is
+pinned on outputs of the reference itself: this script imports / loads it by path, runs it on
+seeded synthetic inputs on CPU fp32 and writes small fixtures under tests/golden/.
+It cannot run on the GPU box (no /root/reference there); the fixtures travel instead.
+
+Stubs: albumentations, albumentations.pytorch(ToTensorV2), termcolor and
+torchvision.io.VideoReader are absent from this image and never executed by the hot path
+(SURVEY F11); they are stubbed in sys.modules so `utils.models`, `utils.loss`, `rs` import.
+
+usage: python tools/make_golden.py            (writes tests/golden/*.npz)
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+SEED = 100  # the reference's default seed, train.py:160
+
+
+def install_stubs():
+    alb = types.ModuleType("albumentations")
+    albp = types.ModuleType("albumentations.pytorch")
+    albp.ToTensorV2 = object
+    alb.pytorch = albp
+    for name in ("Compose", "RandomCrop", "Resize", "Normalize", "HorizontalFlip", "VerticalFlip",
+                 "ImageOnlyTransform", "BasicTransform", "DualTransform"):
+        setattr(alb, name, type(name, (), {"__init__": lambda self, *a, **k: None}))
+    sys.modules.setdefault("albumentations", alb)
+    sys.modules.setdefault("albumentations.pytorch", albp)
+    tc = types.ModuleType("termcolor")
+    tc.colored = lambda s, *a, **k: s
+    sys.modules.setdefault("termcolor", tc)
+    import torchvision.io as tvio
+    if not hasattr(tvio, "VideoReader"):
+        tvio.VideoReader = object
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+
+
+def smooth_noise_u8(g, n, h, w, sigma=0.03):
+    """SURVEY §8(d) 'smooth+noise' generator: bicubic-upsampled 1/8-res uniform + N(0,sigma), clamp, x255."""
+    lo = torch.rand(n, 3, max(1, h // 8), max(1, w // 8), generator=g)
+    img = torch.nn.functional.interpolate(lo, size=(h, w), mode="bicubic", align_corners=False)
+    clean = img.clamp(0, 1)
+    noisy = (clean + sigma * torch.randn(n, 3, h, w, generator=g)).clamp(0, 1)
+    return (clean * 255).round().to(torch.uint8), (noisy * 255).round().to(torch.uint8)
+
+
+@torch.no_grad()
+def golden_model_pt():
+    m = torch.jit.load(os.path.join(REF, "model.pt"), "cpu").eval()
+    g = torch.Generator().manual_seed(SEED)
+    cases = {}
+    x = torch.randint(0, 256, (2, 3, 96, 96), dtype=torch.uint8, generator=g)
+    cases["uniform_2x96x96"] = x
+    x = torch.randint(0, 256, (1, 3, 40, 56), dtype=torch.uint8, generator=g)
+    cases["uniform_1x40x56"] = x
+    x = torch.randint(0, 256, (3, 3, 17, 23), dtype=torch.uint8, generator=g)  # ragged: not /8, not /16
+    cases["uniform_3x17x23"] = x
+    x = torch.randint(0, 256, (1, 3, 1, 1), dtype=torch.uint8, generator=g)  # minimum size
+    cases["uniform_1x1x1"] = x
+    _, noisy = smooth_noise_u8(g, 1, 72, 88)
+    cases["smooth_1x72x88"] = noisy
+    cases["zeros_1x32x32"] = torch.zeros(1, 3, 32, 32, dtype=torch.uint8)
+    cases["ones255_1x24x40"] = torch.full((1, 3, 24, 40), 255, dtype=torch.uint8)
+    out = {}
+    net = m.net
+    for name, x in cases.items():
+        y = m(x.clone())
+        assert y.dtype == torch.uint8 and y.shape == x.shape
+        out[name + ".in"] = x.numpy()
+        out[name + ".out"] = y.numpy()
+    # pre-round float (tanh) output of the Denoise sub-module for one case
+    x = cases["uniform_1x40x56"]
+    t = getattr(net, "1")(getattr(net, "0")(x.clone()))
+    out["uniform_1x40x56.tanh"] = t.numpy().astype(np.float32)
+    np.savez_compressed(os.path.join(OUT, "model_pt_golden.npz"), **out)
+    print("model_pt_golden.npz:", {k: v.shape for k, v in out.items()})
+    return m
+
+
+@torch.no_grad()
+def golden_rs_tiling(m):
+    """rs.py:82-111 still-image path executed with the reference's own sliding_window."""
+    import rs as ref_rs
+    g = torch.Generator().manual_seed(SEED + 1)
+    image = torch.randint(0, 256, (3, 136, 200), dtype=torch.uint8, generator=g)
+    result_image = None
+    high = width = 0
+    step_size = 96
+    for step_size, _, _, win in ref_rs.sliding_window(image, step_size):
+        w = m(win.unsqueeze(0).clone())
+        if result_image is None:
+            result_image = torch.zeros_like(image)
+            _, image_high, image_width = result_image.size()
+        for frame in w:
+            c, h, ww = frame.size()
+            result_image[..., high:high + h, width:width + ww] = frame
+            width += ww
+            if width >= image_width:
+                high += h
+                width = 0
+    whole = m(image.unsqueeze(0).clone())[0]
+    np.savez_compressed(os.path.join(OUT, "rs_tiling_golden.npz"), image=image.numpy(),
+                        rs_window96=result_image.numpy(), whole=whole.numpy())
+    diff = (result_image.int() - whole.int()).abs()
+    print("rs_tiling_golden.npz: seam max diff vs whole", int(diff.max()), "frac!=0", float((diff > 0).float().mean()))
+
+
+def golden_l1():
+    from utils.loss import L1Loss
+    g = torch.Generator().manual_seed(SEED + 2)
+    out = {}
+    crit = L1Loss(1.0)
+    for name, shape in (("a", (2, 3, 16, 16)), ("b", (1, 3, 7, 5)), ("c", (4, 3, 128, 128))):
+        p = (torch.rand(shape, generator=g) * 2 - 1).requires_grad_(True)
+        t = torch.rand(shape, generator=g) * 2 - 1
+        if name == "b":
+            with torch.no_grad():
+                p[0, 0, 0, :3] = t[0, 0, 0, :3]  # exact ties: sign(0) = 0
+        loss = crit(p, t)
+        loss.backward()
+        if name != "c":
+            out[name + ".pred"], out[name + ".tgt"] = p.detach().numpy(), t.numpy()
+            out[name + ".grad"] = p.grad.numpy()
+        else:  # large case: keep only seeds' statistics
+            out[name + ".grad_abs_sum"] = np.float64(p.grad.abs().double().sum().item())
+        out[name + ".loss"] = np.float32(loss.item())
+    np.savez_compressed(os.path.join(OUT, "l1_golden.npz"), **out)
+    print("l1_golden.npz:", {k: getattr(v, 'shape', ()) for k, v in out.items()})
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(os.cpu_count() or 1)
+    install_stubs()
+    os.makedirs(OUT, exist_ok=True)
+    m = golden_model_pt()
+    golden_rs_tiling(m)
+    golden_l1()
