@@ -1,0 +1,5 @@
+"""B200-native (sm_100a) hot path of thnak/image_super_resolution: the conv network's forward pass
+and pixel-loss training step behind the reference's own Python surfaces.  See DESIGN.md."""
+from .modelpt import ModelPT, load, RF_RADIUS, FLOP_PER_PX  # noqa: F401
+
+__all__ = ["ModelPT", "load", "RF_RADIUS", "FLOP_PER_PX"]

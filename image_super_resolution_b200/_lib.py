@@ -1,0 +1,99 @@
+"""ctypes binding of libsrb200.so (C ABI in include/srb200.h).
+
+There is NO CPU or PyTorch fallback: if the shared library is missing or a call fails, this module
+raises.  PyTorch is used by the callers only for device memory, streams and torch.distributed.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsrb200.so")
+
+SRB_DT_F16, SRB_DT_BF16, SRB_DT_F32 = 0, 1, 2
+F_LRELU, F_RESIDUAL, F_TANH, F_U8OUT, F_PIXSHUF2, F_F32OUT = 1, 2, 4, 8, 16, 32
+
+_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_fp = C.POINTER(C.c_float)
+
+# name -> (restype, argtypes); every symbol declared in include/srb200.h
+SIGNATURES = {
+    "srb_last_error": (C.c_char_p, []),
+    "srb_version": (_i, []),
+    "srb_create": (_i, [_i, C.POINTER(_vp)]),
+    "srb_destroy": (None, [_vp]),
+    "srb_num_sms": (_i, [_vp]),
+    "srb_debug_set": (_i, [_vp, _i, _i]),
+    "srb_pack_conv": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, C.POINTER(_vp)]),
+    "srb_free_weights": (None, [_vp]),
+    "srb_conv2d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _f, _f, _f, _i, _i, _i, _i, _vp]),
+    "srb_u8nchw_to_c8": (_i, [_vp, _vp, _vp, _fp, _fp, _f, _i, _i, _i, _i, _vp]),
+    "srb_f32nchw_to_c8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "srb_c8_to_f32nchw": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "srb_model_pt_create": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), _fp, _fp, _f, _f, _i, C.POINTER(_vp)]),
+    "srb_model_pt_destroy": (None, [_vp]),
+    "srb_model_pt_workspace_bytes": (_sz, [_i, _i, _i]),
+    "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
+    "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
+    "srb_model_pt_launches": (_i, []),
+    "srb_l1_partials_len": (_i, []),
+    "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
+    "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+def lib():
+    """Load libsrb200.so (once).  Raises if it has not been built — never falls back."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise ImportError(
+                        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(nvcc, sm_100a). There is no CPU fallback.")
+                l = C.CDLL(LIB_PATH)
+                for name, (res, args) in SIGNATURES.items():
+                    fn = getattr(l, name)  # AttributeError if the .so lacks a declared symbol
+                    fn.restype = res
+                    fn.argtypes = args
+                _lib = l
+    return _lib
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = lib().srb_last_error().decode(errors="replace")
+        raise RuntimeError(f"libsrb200 {what} failed ({rc}): {msg}")
+
+
+class Context:
+    """One srb_ctx per CUDA device (per process); owns nothing but staging buffers."""
+    _by_device: dict[int, "Context"] = {}
+
+    def __init__(self, device: int):
+        self.device = int(device)
+        h = _vp()
+        check(lib().srb_create(self.device, C.byref(h)), "srb_create")
+        self.handle = h
+        self.num_sms = lib().srb_num_sms(h)
+
+    @classmethod
+    def get(cls, device: int) -> "Context":
+        device = int(device)
+        if device not in cls._by_device:
+            cls._by_device[device] = Context(device)
+        return cls._by_device[device]
+
+    def debug_set(self, key: int, value: int):
+        check(lib().srb_debug_set(self.handle, key, value), "srb_debug_set")
+
+
+def f32_ptr(arr):
+    """numpy float32 contiguous array -> void* (keeps no reference: caller holds arr)."""
+    return arr.ctypes.data_as(_vp)

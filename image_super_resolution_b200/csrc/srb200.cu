@@ -1,0 +1,486 @@
+// libsrb200.so — C ABI (include/srb200.h) over the sm_100a kernels in srb_conv.cuh / srb_elem.cuh.
+// Host side: context, weight packing into the UMMA B-operand layout (with BN folding),
+// TMA tensor-map construction, kernel dispatch and the model.pt layer schedule.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include <vector>
+#include <map>
+#include <tuple>
+
+#include "../../include/srb200.h"
+#include "srb_conv.cuh"
+#include "srb_elem.cuh"
+
+using namespace srb;
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char t_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof(t_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                            \
+    do {                                                                                          \
+        cudaError_t e__ = (expr);                                                                 \
+        if (e__ != cudaSuccess) return fail(SRB_ECUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char* srb_last_error(void) { return t_err; }
+extern "C" int srb_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------------------
+// objects
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct srb_ctx {
+    int device = 0;
+    int num_sms = 0;
+    PFN_encodeTiled encode = nullptr;
+    int dbg_swap = 0;
+    int dbg_grid = 0;
+    // pinned + device staging for the *_host entry
+    uint8_t* h_pin = nullptr; size_t h_pin_bytes = 0;
+    uint8_t* d_io = nullptr; size_t d_io_bytes = 0;
+    void* d_ws = nullptr; size_t d_ws_bytes = 0;
+    cudaStream_t own_stream = nullptr;
+};
+
+struct srb_weights {
+    int cout = 0, cin = 0, k = 0, dtype = 0;
+    int mode = 0, c8in = 0, nout = 0, ksteps = 0;
+    uint8_t* d_pack = nullptr;
+    float* d_bias = nullptr;
+    size_t pack_bytes = 0;
+};
+
+struct srb_net {
+    srb_weights* conv[20];
+    float mean[3], std_[3], maxv, slope;
+    int dtype;
+};
+
+extern "C" int srb_create(int device, srb_ctx** out) {
+    if (!out) return fail(SRB_EINVAL, "srb_create: out is NULL");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(SRB_EINVAL, "srb_create: device %d of %d", device, ndev);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(SRB_ENOSUP, "srb_create: device %d is sm_%d%d; this library holds sm_100a kernels only", device,
+                    prop.major, prop.minor);
+    srb_ctx* c = new srb_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+        delete c;
+        return fail(SRB_ECUDA, "srb_create: cuTensorMapEncodeTiled not available from the driver");
+    }
+    c->encode = reinterpret_cast<PFN_encodeTiled>(fn);
+    *out = c;
+    return SRB_OK;
+}
+
+extern "C" void srb_destroy(srb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->d_io) cudaFree(c->d_io);
+    if (c->d_ws) cudaFree(c->d_ws);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+extern "C" int srb_num_sms(const srb_ctx* c) { return c ? c->num_sms : 0; }
+extern "C" int srb_debug_set(srb_ctx* c, int key, int value) {
+    if (!c) return fail(SRB_EINVAL, "ctx is NULL");
+    if (key == 0) c->dbg_swap = value;
+    else if (key == 1) c->dbg_grid = value;
+    else return fail(SRB_EINVAL, "srb_debug_set: unknown key %d", key);
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// weight packing: OIHW fp32 (+BN) -> per K-step [2 granules][NOUT rows][8 k] 16-bit (UMMA B, K-major,
+// SWIZZLE_NONE: row n of granule g at byte (g*NOUT + n)*16).  The K-step order must match the MMA
+// issue loops of conv_tc_kernel.
+// ------------------------------------------------------------------------------------------
+static uint16_t f2h(float f, int dtype) {
+    if (dtype == SRB_DT_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(f); return *reinterpret_cast<uint16_t*>(&h); }
+    __half h = __float2half_rn(f);
+    return *reinterpret_cast<uint16_t*>(&h);
+}
+
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, const float* bn4, float bn_eps, int cout,
+                             int cin, int k, int dtype, srb_weights** out) {
+    if (!ctx || !w || !out) return fail(SRB_EINVAL, "srb_pack_conv: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_pack_conv: dtype %d", dtype);
+    int mode, c8in, nout, ksteps;
+    if (k == 9 && cin == 3) { mode = MODE_PAIRDX; c8in = 1; nout = round_up(cout, 32); ksteps = 9 * 5; }
+    else if (k == 9 && cout == 3 && cin % 16 == 0) { mode = MODE_DXN; c8in = cin / 8; nout = 32; ksteps = 9 * (c8in / 2); }
+    else if (k == 3 && cin % 16 == 0) { mode = MODE_STD; c8in = cin / 8; nout = round_up(cout, 32); ksteps = 9 * (c8in / 2); }
+    else return fail(SRB_ENOSUP, "srb_pack_conv: no kernel for cout=%d cin=%d k=%d", cout, cin, k);
+    if (nout > 256) return fail(SRB_ENOSUP, "srb_pack_conv: cout=%d > 256", cout);
+
+    // BN fold (fuse_conv_and_bn): W' = W * gamma/sqrt(var+eps); b' = (b - mean)*gamma/sqrt(var+eps) + beta
+    std::vector<float> scale(cout, 1.f), fb(cout, 0.f);
+    for (int o = 0; o < cout; ++o) {
+        float b0 = bias ? bias[o] : 0.f;
+        if (bn4) {
+            float g = bn4[o], be = bn4[cout + o], mu = bn4[2 * cout + o], var = bn4[3 * cout + o];
+            float s = g / sqrtf(var + bn_eps);
+            scale[o] = s;
+            fb[o] = (b0 - mu) * s + be;
+        } else fb[o] = b0;
+    }
+    auto W = [&](int o, int c, int dy, int dx) -> float { return w[(((size_t)o * cin + c) * k + dy) * k + dx] * scale[o]; };
+
+    const size_t step_elems = (size_t)2 * nout * 8;
+    std::vector<uint16_t> pack((size_t)ksteps * step_elems, 0);
+    std::vector<float> hbias(nout, 0.f);
+    int ks = 0;
+    if (mode == MODE_STD) {
+        for (int dy = 0; dy < 3; ++dy) for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < c8in / 2; ++c2, ++ks)
+            for (int g = 0; g < 2; ++g) for (int n = 0; n < cout; ++n) for (int j = 0; j < 8; ++j)
+                pack[ks * step_elems + ((size_t)g * nout + n) * 8 + j] = f2h(W(n, (2 * c2 + g) * 8 + j, dy, dx), dtype);
+        for (int o = 0; o < cout; ++o) hbias[o] = fb[o];
+    } else if (mode == MODE_PAIRDX) {
+        for (int dy = 0; dy < 9; ++dy) for (int dxp = 0; dxp < 5; ++dxp, ++ks)
+            for (int g = 0; g < 2; ++g) {
+                int dx = 2 * dxp + g;
+                if (dx >= 9) continue;
+                for (int n = 0; n < cout; ++n) for (int j = 0; j < cin; ++j)
+                    pack[ks * step_elems + ((size_t)g * nout + n) * 8 + j] = f2h(W(n, j, dy, dx), dtype);
+            }
+        for (int o = 0; o < cout; ++o) hbias[o] = fb[o];
+    } else {  // MODE_DXN: row n = dx*3 + co
+        for (int dy = 0; dy < 9; ++dy) for (int c2 = 0; c2 < c8in / 2; ++c2, ++ks)
+            for (int g = 0; g < 2; ++g) for (int dx = 0; dx < 9; ++dx) for (int co = 0; co < 3; ++co) for (int j = 0; j < 8; ++j)
+                pack[ks * step_elems + ((size_t)g * nout + dx * 3 + co) * 8 + j] = f2h(W(co, (2 * c2 + g) * 8 + j, dy, dx), dtype);
+        for (int o = 0; o < 3; ++o) hbias[o] = fb[o];
+    }
+
+    srb_weights* sw = new srb_weights();
+    sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
+    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps;
+    sw->pack_bytes = pack.size() * 2;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
+        delete sw;
+        return fail(SRB_ENOMEM, "srb_pack_conv: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemcpy(sw->d_pack, pack.data(), sw->pack_bytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(sw->d_bias, hbias.data(), nout * sizeof(float), cudaMemcpyHostToDevice));
+    *out = sw;
+    return SRB_OK;
+}
+
+extern "C" void srb_free_weights(srb_weights* w) {
+    if (!w) return;
+    if (w->d_pack) cudaFree(w->d_pack);
+    if (w->d_bias) cudaFree(w->d_bias);
+    delete w;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv dispatch
+// ------------------------------------------------------------------------------------------
+template <int C8IN, int NOUT, int KH, int KW, int MODE>
+static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, ConvParams p, cudaStream_t st) {
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE>;
+    if (w->ksteps != G::KSTEPS || (size_t)G::WBYTES != w->pack_bytes)
+        return fail(SRB_EINVAL, "launch_conv: packed weights do not match the kernel geometry");
+    p.tiles_x = (p.W + G::TW - 1) / G::TW;
+    p.tiles_y = (p.H + G::TH - 1) / G::TH;
+    long long nt = (long long)p.tiles_x * p.tiles_y * p.N;
+    if (nt <= 0 || nt > 0x7fffffffLL) return fail(SRB_EINVAL, "launch_conv: %lld tiles", nt);
+    p.num_tiles = (int)nt;
+
+    CUtensorMap tmap;
+    cuuint64_t gdim[4] = {(cuuint64_t)p.W * 8, (cuuint64_t)p.H, (cuuint64_t)x_c8_total, (cuuint64_t)p.N};
+    cuuint64_t gstr[3] = {(cuuint64_t)p.W * 16, (cuuint64_t)p.W * p.H * 16, (cuuint64_t)p.W * p.H * 16 * x_c8_total};
+    cuuint32_t box[4] = {(cuuint32_t)G::HALO_W * 8, (cuuint32_t)G::HALO_H, (cuuint32_t)C8IN, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = ctx->encode(&tmap, w->dtype == SRB_DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                             4, const_cast<void*>(x), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d (W=%d H=%d planes=%d N=%d)", (int)r, p.W, p.H, x_c8_total, p.N);
+
+    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    p.dbg_swap = ctx->dbg_swap;
+    if (w->dtype == SRB_DT_BF16) {
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, true>;
+        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
+    } else {
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, false>;
+        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, int x_c8_off, void* y,
+                              int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
+                              float res_scale, float out_scale, float lrelu_slope, int flags, int N, int H, int W,
+                              srb_stream_t stream) {
+    if (!ctx || !w || !x || !y) return fail(SRB_EINVAL, "srb_conv2d_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv2d_fwd: empty shape %dx%dx%d", N, H, W);
+    if (((uintptr_t)x & 15) || ((uintptr_t)y & 15 && w->mode != MODE_DXN) || ((uintptr_t)residual & 15))
+        return fail(SRB_EINVAL, "srb_conv2d_fwd: buffers must be 16-byte aligned");
+    if (x_c8_off < 0 || x_c8_off + w->c8in > x_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: input plane slice out of range");
+    if ((flags & SRB_F_RESIDUAL) && !residual) return fail(SRB_EINVAL, "srb_conv2d_fwd: SRB_F_RESIDUAL without residual");
+    if ((long long)H * W * 16 * x_c8_total >= (1ll << 40)) return fail(SRB_EINVAL, "srb_conv2d_fwd: image too large");
+    ConvParams p{};
+    p.N = N; p.H = H; p.W = W;
+    p.x_c8_off = x_c8_off;
+    p.wpack = w->d_pack; p.bias = w->d_bias;
+    p.y = y; p.y_c8_total = y_c8_total; p.y_c8_off = y_c8_off;
+    p.res = residual; p.res_c8_total = res_c8_total; p.res_c8_off = res_c8_off;
+    p.res_scale = res_scale; p.out_scale = out_scale; p.slope = lrelu_slope;
+    p.flags = flags; p.cout = w->cout;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (w->mode == MODE_DXN) {
+        if (!(flags & (SRB_F_U8OUT | SRB_F_F32OUT))) return fail(SRB_EINVAL, "srb_conv2d_fwd: tail conv needs SRB_F_U8OUT or SRB_F_F32OUT");
+        if (w->c8in == 8) return launch_conv<8, 32, 9, 9, MODE_DXN>(ctx, w, x, x_c8_total, p, st);
+        return fail(SRB_ENOSUP, "srb_conv2d_fwd: tail conv with cin=%d", w->cin);
+    }
+    if (flags & (SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_TANH)) return fail(SRB_EINVAL, "srb_conv2d_fwd: tanh/u8/f32 output only on the tail conv");
+    int out_planes = (flags & SRB_F_PIXSHUF2) ? w->cout / 32 : (w->cout + 7) / 8;
+    if ((flags & SRB_F_PIXSHUF2) && (w->cout % 32)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PixelShuffle(2) needs cout %% 32 == 0");
+    if ((flags & SRB_F_PIXSHUF2) && (flags & SRB_F_RESIDUAL)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PIXSHUF2 with residual unsupported");
+    if (y_c8_off < 0 || y_c8_off + out_planes > y_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: output plane slice out of range");
+    if (w->cout % 8) return fail(SRB_ENOSUP, "srb_conv2d_fwd: cout=%d not a multiple of 8", w->cout);
+    if (w->mode == MODE_PAIRDX) {
+        if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX>(ctx, w, x, x_c8_total, p, st);
+        return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
+    }
+#define SRB_STD(C8, NO) if (w->c8in == C8 && w->nout == NO) return launch_conv<C8, NO, 3, 3, MODE_STD>(ctx, w, x, x_c8_total, p, st);
+    SRB_STD(8, 32) SRB_STD(4, 64) SRB_STD(8, 64)
+    SRB_STD(12, 32) SRB_STD(16, 32) SRB_STD(20, 32)
+#undef SRB_STD
+    return fail(SRB_ENOSUP, "srb_conv2d_fwd: no 3x3 kernel for cin=%d cout=%d", w->cin, w->cout);
+}
+
+// ------------------------------------------------------------------------------------------
+// elementwise entry points
+// ------------------------------------------------------------------------------------------
+static int ew_grid(srb_ctx* ctx, size_t total, int block) {
+    size_t b = (total + block - 1) / block;
+    size_t cap = (size_t)ctx->num_sms * 8;
+    return (int)(b < cap ? (b ? b : 1) : cap);
+}
+
+extern "C" int srb_u8nchw_to_c8(srb_ctx* ctx, const uint8_t* in, void* out, const float mean[3], const float std_[3],
+                                float maxv, int dtype, int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !in || !out || !mean || !std_) return fail(SRB_EINVAL, "srb_u8nchw_to_c8: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_u8nchw_to_c8: empty shape");
+    size_t HW = (size_t)H * W, total = HW * N;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16)
+        u8nchw_to_c8_kernel<true><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, HW, total);
+    else
+        u8nchw_to_c8_kernel<false><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_f32nchw_to_c8(srb_ctx* ctx, const float* in, void* out, int C, int c8_total, int c8_off, int dtype,
+                                 int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !in || !out) return fail(SRB_EINVAL, "srb_f32nchw_to_c8: NULL argument");
+    int planes = (C + 7) / 8;
+    if (C <= 0 || c8_off < 0 || c8_off + planes > c8_total) return fail(SRB_EINVAL, "srb_f32nchw_to_c8: plane slice out of range");
+    size_t HW = (size_t)H * W, total = HW * N * planes;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) f32nchw_to_c8_kernel<true><<<grid, 256, 0, st>>>(in, (uint4*)out, C, c8_total, c8_off, HW, total);
+    else f32nchw_to_c8_kernel<false><<<grid, 256, 0, st>>>(in, (uint4*)out, C, c8_total, c8_off, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_c8_to_f32nchw(srb_ctx* ctx, const void* in, float* out, int C, int c8_total, int c8_off, int dtype,
+                                 int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !in || !out) return fail(SRB_EINVAL, "srb_c8_to_f32nchw: NULL argument");
+    int planes = (C + 7) / 8;
+    if (C <= 0 || c8_off < 0 || c8_off + planes > c8_total) return fail(SRB_EINVAL, "srb_c8_to_f32nchw: plane slice out of range");
+    size_t HW = (size_t)H * W, total = HW * N * C;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) c8_to_f32nchw_kernel<true><<<grid, 256, 0, st>>>(in, out, C, c8_total, c8_off, HW, total);
+    else c8_to_f32nchw_kernel<false><<<grid, 256, 0, st>>>(in, out, C, c8_total, c8_off, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// L1 loss
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_l1_partials_len(void) { return L1_MAX_BLOCKS; }
+
+extern "C" int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                               float* loss_out, float* partials, srb_stream_t stream) {
+    if (!ctx || !pred || !tgt || !loss_out || !partials) return fail(SRB_EINVAL, "srb_l1_loss_fwd: NULL argument");
+    if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_fwd: empty input (mean of nothing)");
+    if (((uintptr_t)pred & 15) || ((uintptr_t)tgt & 15)) return fail(SRB_EINVAL, "srb_l1_loss_fwd: buffers must be 16-byte aligned");
+    size_t b = (n / 4 + 255) / 256;
+    int grid = (int)(b < (size_t)L1_MAX_BLOCKS ? (b ? b : 1) : L1_MAX_BLOCKS);
+    float scale = (float)((double)w / (double)n);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (pred_dtype) {
+        case 0: l1_fwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
+        case 1: l1_fwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
+        case 2: l1_fwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
+        default: return fail(SRB_EINVAL, "srb_l1_loss_fwd: pred_dtype %d", pred_dtype);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                               float grad_scale, void* dpred, srb_stream_t stream) {
+    if (!ctx || !pred || !tgt || !dpred) return fail(SRB_EINVAL, "srb_l1_loss_bwd: NULL argument");
+    if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_bwd: empty input");
+    size_t b = (n + 255) / 256;
+    size_t cap = (size_t)ctx->num_sms * 8;
+    int grid = (int)(b < cap ? b : cap);
+    float g = (float)((double)w * (double)grad_scale / (double)n);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (pred_dtype) {
+        case 0: l1_bwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
+        case 1: l1_bwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
+        case 2: l1_bwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
+        default: return fail(SRB_EINVAL, "srb_l1_loss_bwd: pred_dtype %d", pred_dtype);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// model.pt graph
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const float* const* b, const float mean[3],
+                                   const float std_[3], float maxv, float slope, int dtype, srb_net** out) {
+    if (!ctx || !w || !b || !mean || !std_ || !out) return fail(SRB_EINVAL, "srb_model_pt_create: NULL argument");
+    srb_net* net = new srb_net();
+    memset(net->conv, 0, sizeof(net->conv));
+    for (int i = 0; i < 3; ++i) { net->mean[i] = mean[i]; net->std_[i] = std_[i]; }
+    net->maxv = maxv; net->slope = slope; net->dtype = dtype;
+    int rc = SRB_OK;
+    for (int i = 0; i < 20 && rc == SRB_OK; ++i) {
+        int cout, cin, k;
+        if (i == 0) { cout = 64; cin = 3; k = 9; }
+        else if (i == 19) { cout = 3; cin = 64; k = 9; }
+        else if (i == 18) { cout = 64; cin = 64; k = 3; }
+        else if (i & 1) { cout = 32; cin = 64; k = 3; }
+        else { cout = 64; cin = 32; k = 3; }
+        if (!w[i] || !b[i]) rc = fail(SRB_EINVAL, "srb_model_pt_create: weight %d is NULL", i);
+        else rc = srb_pack_conv(ctx, w[i], b[i], nullptr, 0.f, cout, cin, k, dtype, &net->conv[i]);
+    }
+    if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
+    *out = net;
+    return SRB_OK;
+}
+
+extern "C" void srb_model_pt_destroy(srb_net* net) {
+    if (!net) return;
+    for (int i = 0; i < 20; ++i) srb_free_weights(net->conv[i]);
+    delete net;
+}
+
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
+    if (N <= 0 || H <= 0 || W <= 0) return 0;
+    size_t P = (size_t)N * H * W;
+    return align256(P * 16) + 3 * align256(P * 128) + align256(P * 64);
+}
+
+extern "C" int srb_model_pt_launches(void) { return 20; }
+
+extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in, uint8_t* out, int N, int H, int W,
+                                    void* ws, size_t ws_bytes, srb_stream_t stream) {
+    if (!ctx || !net || !in || !out || !ws) return fail(SRB_EINVAL, "srb_model_pt_forward: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_model_pt_forward: empty shape %dx%dx%d", N, H, W);
+    size_t need = srb_model_pt_workspace_bytes(N, H, W);
+    if (ws_bytes < need) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace %zu < %zu bytes", ws_bytes, need);
+    if ((uintptr_t)ws & 255) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace must be 256-byte aligned");
+    size_t P = (size_t)N * H * W;
+    uint8_t* base = (uint8_t*)ws;
+    void* in8 = base; base += align256(P * 16);
+    void* x0 = base; base += align256(P * 128);
+    void* ra = base; base += align256(P * 128);
+    void* rb = base; base += align256(P * 128);
+    void* hid = base;
+    const float s = net->slope;
+    int rc;
+    if ((rc = srb_u8nchw_to_c8(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
+    if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+    void* cur = x0;
+    for (int i = 0; i < 8; ++i) {
+        void* nxt = (i & 1) ? rb : ra;
+        if ((rc = srb_conv2d_fwd(ctx, net->conv[1 + 2 * i], cur, 8, 0, hid, 4, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+        if ((rc = srb_conv2d_fwd(ctx, net->conv[2 + 2 * i], hid, 4, 0, nxt, 8, 0, cur, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
+        cur = nxt;
+    }
+    // cur == rb after 8 blocks; long skip adds conv0's (post-activation) output
+    if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
+    if ((rc = srb_conv2d_fwd(ctx, net->conv[19], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+    return SRB_OK;
+}
+
+extern "C" int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N, int H, int W) {
+    if (!ctx || !net || !in_host || !out_host) return fail(SRB_EINVAL, "srb_model_pt_forward_host: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_model_pt_forward_host: empty shape");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    size_t io = (size_t)N * 3 * H * W, io_al = align256(io);
+    size_t ws = srb_model_pt_workspace_bytes(N, H, W);
+    if (!ctx->own_stream) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    if (ctx->h_pin_bytes < 2 * io_al) {
+        if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+        ctx->h_pin = nullptr; ctx->h_pin_bytes = 0;
+        CUDA_TRY(cudaMallocHost((void**)&ctx->h_pin, 2 * io_al));
+        ctx->h_pin_bytes = 2 * io_al;
+    }
+    if (ctx->d_io_bytes < 2 * io_al) {
+        if (ctx->d_io) cudaFree(ctx->d_io);
+        ctx->d_io = nullptr; ctx->d_io_bytes = 0;
+        CUDA_TRY(cudaMalloc((void**)&ctx->d_io, 2 * io_al));
+        ctx->d_io_bytes = 2 * io_al;
+    }
+    if (ctx->d_ws_bytes < ws) {
+        if (ctx->d_ws) cudaFree(ctx->d_ws);
+        ctx->d_ws = nullptr; ctx->d_ws_bytes = 0;
+        CUDA_TRY(cudaMalloc(&ctx->d_ws, ws));
+        ctx->d_ws_bytes = ws;
+    }
+    cudaStream_t st = ctx->own_stream;
+    memcpy(ctx->h_pin, in_host, io);
+    CUDA_TRY(cudaMemcpyAsync(ctx->d_io, ctx->h_pin, io, cudaMemcpyHostToDevice, st));
+    int rc = srb_model_pt_forward(ctx, net, ctx->d_io, ctx->d_io + io_al, N, H, W, ctx->d_ws, ctx->d_ws_bytes, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(ctx->h_pin + io_al, ctx->d_io + io_al, io, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(out_host, ctx->h_pin + io_al, io);
+    return SRB_OK;
+}

@@ -1,0 +1,156 @@
+// HBM-bound helper kernels: input normalisation/packing, layout converters, L1 loss fwd/bwd.
+// All are coalesced, 16-byte vectorised where the layout allows, grid sized in multiples of the SM count.
+#pragma once
+#include "srb_ptx.cuh"
+
+namespace srb {
+
+template <bool BF16>
+__device__ __forceinline__ uint32_t pk2(float a, float b) {
+    if constexpr (BF16) { __nv_bfloat162 h = __floats2bfloat162_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+    else { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+}
+template <bool BF16>
+__device__ __forceinline__ float ld16f(const void* p, size_t i) {
+    if constexpr (BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+    else return __half2float(reinterpret_cast<const __half*>(p)[i]);
+}
+
+// Normalize.forward on uint8 (utils/datasets.py:65-71 as traced): f32(x)/255 - mean, /std — three
+// separately rounded fp32 ops like the reference — then one rounding to the 16-bit operand type.
+// in: [N][3][H][W] u8, out: [N][1][H][W][8] (channels 3..7 = 0).  One thread per pixel.
+template <bool BF16>
+__global__ void u8nchw_to_c8_kernel(const uint8_t* __restrict__ in, uint4* __restrict__ out, float m0, float m1,
+                                    float m2, float s0, float s1, float s2, float maxv, size_t HW, size_t total) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        size_t n = i / HW, px = i - n * HW;
+        const uint8_t* b = in + n * 3 * HW + px;
+        float r = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[0], maxv), m0), s0);
+        float g = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[HW], maxv), m1), s1);
+        float bl = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[2 * HW], maxv), m2), s2);
+        uint4 o;
+        o.x = pk2<BF16>(r, g); o.y = pk2<BF16>(bl, 0.f); o.z = 0u; o.w = 0u;
+        out[i] = o;
+    }
+}
+
+// fp32 NCHW [N][C][H][W] -> planes c8_off.. of a C8 buffer; channels beyond C in the last plane are zero.
+template <bool BF16>
+__global__ void f32nchw_to_c8_kernel(const float* __restrict__ in, uint4* __restrict__ out, int C, int c8_total,
+                                     int c8_off, size_t HW, size_t total /* N * ceil(C/8) * HW */) {
+    const int planes = (C + 7) / 8;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        size_t px = i % HW; size_t t = i / HW; int pl = (int)(t % planes); size_t n = t / planes;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            int c = pl * 8 + j;
+            v[j] = c < C ? in[(n * C + c) * HW + px] : 0.f;
+        }
+        uint4 o;
+        o.x = pk2<BF16>(v[0], v[1]); o.y = pk2<BF16>(v[2], v[3]); o.z = pk2<BF16>(v[4], v[5]); o.w = pk2<BF16>(v[6], v[7]);
+        out[(n * c8_total + c8_off + pl) * HW + px] = o;
+    }
+}
+
+template <bool BF16>
+__global__ void c8_to_f32nchw_kernel(const void* __restrict__ in, float* __restrict__ out, int C, int c8_total,
+                                     int c8_off, size_t HW, size_t total /* N * C * HW */) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        size_t px = i % HW; size_t t = i / HW; int c = (int)(t % C); size_t n = t / C;
+        out[i] = ld16f<BF16>(in, ((n * c8_total + c8_off + (c >> 3)) * HW + px) * 8 + (c & 7));
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// L1 loss (utils/loss.py:38-39).  Forward: per-thread fp32 partial sums over 16-byte loads,
+// warp-shuffle tree, one partial per CTA, and the last CTA to finish adds the partials in index
+// order (deterministic, no float atomics).  Backward: sign(p - t) * scale, sign(0) = 0.
+// ------------------------------------------------------------------------------------------
+constexpr int L1_MAX_BLOCKS = 1184;  // 148 SMs x 8
+__device__ unsigned int g_l1_done_counter;
+
+template <int DT>
+__device__ __forceinline__ float ldp(const void* p, size_t i) {
+    if constexpr (DT == 0) return __half2float(reinterpret_cast<const __half*>(p)[i]);
+    else if constexpr (DT == 1) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+    else return reinterpret_cast<const float*>(p)[i];
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int DT>
+__global__ void __launch_bounds__(256) l1_fwd_kernel(const void* __restrict__ pred, const float* __restrict__ tgt,
+                                                     size_t n, float scale /* w / n */, float* __restrict__ loss,
+                                                     float* __restrict__ partials) {
+    float acc = 0.f;
+    const size_t n4 = n / 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 t = reinterpret_cast<const float4*>(tgt)[i];
+        float p0, p1, p2, p3;
+        if constexpr (DT == 2) {
+            float4 q = reinterpret_cast<const float4*>(pred)[i];
+            p0 = q.x; p1 = q.y; p2 = q.z; p3 = q.w;
+        } else {
+            uint2 q = reinterpret_cast<const uint2*>(pred)[i];
+            if constexpr (DT == 0) {
+                float2 a = __half22float2(*reinterpret_cast<__half2*>(&q.x)), b = __half22float2(*reinterpret_cast<__half2*>(&q.y));
+                p0 = a.x; p1 = a.y; p2 = b.x; p3 = b.y;
+            } else {
+                float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&q.x)), b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&q.y));
+                p0 = a.x; p1 = a.y; p2 = b.x; p3 = b.y;
+            }
+        }
+        acc += fabsf(p0 - t.x) + fabsf(p1 - t.y) + fabsf(p2 - t.z) + fabsf(p3 - t.w);
+    }
+    for (size_t i = n4 * 4 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride)
+        acc += fabsf(ldp<DT>(pred, i) - tgt[i]);
+
+    __shared__ float s_part[8];
+    __shared__ bool s_last;
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < (blockDim.x >> 5) ? s_part[threadIdx.x] : 0.f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) {
+            partials[blockIdx.x] = v;
+            __threadfence();
+            unsigned int done = atomicAdd(&g_l1_done_counter, 1u);
+            s_last = (done == gridDim.x - 1);
+        }
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double tot = 0.0;  // few hundred partials: serial-in-lane then fixed-order lane tree
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += 32) tot += (double)reinterpret_cast<volatile float*>(partials)[b];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        if (threadIdx.x == 0) {
+            *loss = (float)(tot * (double)scale);
+            g_l1_done_counter = 0;
+        }
+    }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(256) l1_bwd_kernel(const void* __restrict__ pred, const float* __restrict__ tgt,
+                                                     size_t n, float g /* w*scale/n */, void* __restrict__ dpred) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride) {
+        float d = ldp<DT>(pred, i) - tgt[i];
+        float s = d > 0.f ? g : (d < 0.f ? -g : 0.f);
+        if constexpr (DT == 0) reinterpret_cast<__half*>(dpred)[i] = __float2half_rn(s);
+        else if constexpr (DT == 1) reinterpret_cast<__nv_bfloat16*>(dpred)[i] = __float2bfloat16_rn(s);
+        else reinterpret_cast<float*>(dpred)[i] = s;
+    }
+}
+
+}  // namespace srb

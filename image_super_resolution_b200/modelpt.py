@@ -1,0 +1,165 @@
+"""Drop-in for the object `torch.jit.load("model.pt")` returns in the reference (rs.py:48-49).
+
+    model = image_super_resolution_b200.load("model.pt")     # or the extracted .npz
+    model.to("cuda").eval()
+    out_u8 = model(window_u8)          # rs.py:94  uint8 [N,3,H,W] -> uint8 [N,3,H,W]
+
+The graph (Normalize -> conv0 -> 8 x ResidualBlock1 -> conv1 + skip -> conv2 + tanh -> uint8;
+SURVEY §8(a) a1-a7) runs entirely inside libsrb200.so on sm_100a; this class only owns the
+packed weights and a workspace tensor.  There is no PyTorch / CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Context, check, lib
+from .ops import dtype_code
+
+# state-dict keys of the 20 convs in graph order (archive __torch__.py, class Denoise)
+CONV_KEYS = (["net.1.conv0.0.conv"] + [f"net.1.residual.{i}.m.{j}.conv" for i in range(8) for j in (0, 1)] +
+             ["net.1.conv1.conv", "net.1.conv2.0.conv"])
+LRELU_SLOPE = 0.2          # leaky_relu_(0.2) in the traced graph
+RF_RADIUS = 25             # receptive-field radius of the graph
+FLOP_PER_PX = 725760       # algorithmic FLOP per pixel
+
+
+def _load_state(path: str) -> "OrderedDict[str, torch.Tensor]":
+    path = str(path)
+    if path.endswith(".npz"):
+        z = np.load(path)
+        return OrderedDict((k, torch.from_numpy(z[k].copy())) for k in z.files)
+    m = torch.jit.load(path, "cpu")  # exactly as rs.py:48 opens it (TorchScript archive)
+    return OrderedDict((k, v.detach().clone()) for k, v in m.state_dict().items() if "store_bn" not in k)
+
+
+class ModelPT:
+    """Callable with the surface rs.py uses: .to(device), .eval(), __call__(uint8 NCHW), .state_dict()."""
+
+    def __init__(self, state: "OrderedDict[str, torch.Tensor]", dtype="fp16"):
+        missing = [k + s for k in CONV_KEYS for s in (".weight", ".bias") if k + s not in state]
+        if missing:
+            raise KeyError(f"not a model.pt state dict, missing {missing[:3]}...")
+        self._state = state
+        self._dtype = dtype_code(dtype)
+        self._device = None
+        self._net = None
+        self._ctx = None
+        self._ws = None
+        self.training = False
+
+    # ---- torch.nn.Module-like surface -------------------------------------------------------
+    def state_dict(self):
+        return OrderedDict(self._state)
+
+    def eval(self):
+        self.training = False
+        return self
+
+    def train(self, mode: bool = True):
+        if mode:
+            raise RuntimeError("model.pt is an inference artefact (TorchScript trace); training uses the class nets")
+        return self
+
+    def to(self, device):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("ModelPT runs on sm_100a only; there is no CPU path (use the reference for CPU)")
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if self._device is not None and self._device.index == idx:
+            return self
+        self._release()
+        self._device = torch.device("cuda", idx)
+        self._ctx = Context.get(idx)
+        ws, bs = [], []
+        for k in CONV_KEYS:
+            ws.append(np.ascontiguousarray(self._state[k + ".weight"].numpy(), dtype=np.float32))
+            bs.append(np.ascontiguousarray(self._state[k + ".bias"].numpy(), dtype=np.float32))
+        wp = (C.c_void_p * 20)(*[w.ctypes.data for w in ws])
+        bp = (C.c_void_p * 20)(*[b.ctypes.data for b in bs])
+        mean = (C.c_float * 3)(*self._state["net.0.mean"].flatten().tolist())
+        std = (C.c_float * 3)(*self._state["net.0.std"].flatten().tolist())
+        maxv = float(self._state["net.0.max_pixel_value"])
+        h = C.c_void_p()
+        with torch.cuda.device(idx):
+            check(lib().srb_model_pt_create(self._ctx.handle, wp, bp, mean, std, maxv, LRELU_SLOPE, self._dtype,
+                                            C.byref(h)), "srb_model_pt_create")
+        self._net = h
+        return self
+
+    def cuda(self, device=None):
+        return self.to(torch.device("cuda", device if device is not None else torch.cuda.current_device()))
+
+    def _release(self):
+        if self._net is not None:
+            lib().srb_model_pt_destroy(self._net)
+            self._net = None
+        self._ws = None
+
+    def __del__(self):
+        try:
+            self._release()
+        except Exception:
+            pass
+
+    # ---- forward ---------------------------------------------------------------------------
+    def _workspace(self, nbytes: int) -> torch.Tensor:
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self._device)
+        return self._ws
+
+    def workspace_bytes(self, N: int, H: int, W: int) -> int:
+        return int(lib().srb_model_pt_workspace_bytes(N, H, W))
+
+    @torch.no_grad()
+    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        if self._net is None:
+            raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
+        if x.dim() != 4 or x.shape[1] != 3:
+            raise RuntimeError(f"expected [N,3,H,W], got {tuple(x.shape)}")
+        if x.dtype != torch.uint8:
+            # The trace baked the uint8 branch of Normalize: a float input is divided by 255
+            # too.  Only integral values in [0,255] are representable on the uint8 kernel path.
+            xr = x.round()
+            if not bool(((xr == x) & (x >= 0) & (x <= 255)).all()):
+                raise RuntimeError("float input with non-integral / out-of-range pixels is not supported by the "
+                                   "uint8 kernel path (model.pt divides by 255 internally)")
+            x = xr.to(torch.uint8)
+        N, _, H, W = x.shape
+        if N == 0 or H == 0 or W == 0:
+            return torch.empty_like(x)
+        if not x.is_cuda:  # host tensors: the C ABI's host entry does H2D / D2H itself
+            x = x.contiguous()
+            y = torch.empty_like(x)
+            with torch.cuda.device(self._device):
+                check(lib().srb_model_pt_forward_host(self._ctx.handle, self._net, x.data_ptr(), y.data_ptr(), N, H, W),
+                      "srb_model_pt_forward_host")
+            return y
+        if x.device != self._device:
+            raise RuntimeError(f"input on {x.device}, model on {self._device}")
+        x = x.contiguous()
+        y = out if out is not None else torch.empty_like(x)
+        nbytes = self.workspace_bytes(N, H, W)
+        ws = self._workspace(nbytes)
+        stream = C.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
+        with torch.cuda.device(self._device):
+            check(lib().srb_model_pt_forward(self._ctx.handle, self._net, x.data_ptr(), y.data_ptr(), N, H, W,
+                                             ws.data_ptr(), ws.numel(), stream), "srb_model_pt_forward")
+        return y
+
+    __call__ = forward
+
+    @staticmethod
+    def launches_per_forward() -> int:
+        return int(lib().srb_model_pt_launches())
+
+
+def load(path, map_location="cpu", dtype="fp16") -> ModelPT:
+    """Same call shape as `torch.jit.load(path, "cpu")` (rs.py:48)."""
+    del map_location  # weights are staged on the host until .to(device), like the reference
+    return ModelPT(_load_state(path), dtype=dtype)

@@ -1,0 +1,136 @@
+"""Thin Python operators over the C ABI (include/srb200.h).  torch supplies device memory and the
+current stream only; all arithmetic runs in libsrb200.so's sm_100a kernels.  No fallbacks."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (Context, check, lib, SRB_DT_F16, SRB_DT_BF16, SRB_DT_F32, F_LRELU, F_RESIDUAL, F_TANH, F_U8OUT,
+                   F_PIXSHUF2, F_F32OUT)
+
+_TORCH_DT = {SRB_DT_F16: torch.float16, SRB_DT_BF16: torch.bfloat16}
+
+
+def dtype_code(dtype) -> int:
+    if dtype in (SRB_DT_F16, "fp16", "float16", torch.float16):
+        return SRB_DT_F16
+    if dtype in (SRB_DT_BF16, "bf16", "bfloat16", torch.bfloat16):
+        return SRB_DT_BF16
+    raise ValueError(f"unsupported operand dtype {dtype!r} (fp16 or bf16)")
+
+
+def _stream_ptr(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _require_cuda(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: the B200 path has no CPU fallback")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+
+
+class PackedConv:
+    """Packed filter of one conv (BN folded, UMMA B-operand layout) living on one device."""
+
+    def __init__(self, ctx: Context, weight, bias=None, bn=None, bn_eps: float = 1e-5, dtype=SRB_DT_F16):
+        w = np.ascontiguousarray(weight.detach().cpu().numpy() if isinstance(weight, torch.Tensor) else weight,
+                                 dtype=np.float32)
+        cout, cin, kh, kw = w.shape
+        if kh != kw:
+            raise ValueError("square filters only")
+        b = None if bias is None else np.ascontiguousarray(
+            bias.detach().cpu().numpy() if isinstance(bias, torch.Tensor) else bias, dtype=np.float32)
+        bn4 = None
+        if bn is not None:  # (gamma, beta, running_mean, running_var)
+            bn4 = np.ascontiguousarray(np.stack([np.asarray(t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t,
+                                                            dtype=np.float32) for t in bn]), dtype=np.float32)
+        self.ctx, self.cout, self.cin, self.k = ctx, cout, cin, kh
+        self.dtype = dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_pack_conv(ctx.handle, _lib.f32_ptr(w), None if b is None else _lib.f32_ptr(b),
+                                  None if bn4 is None else _lib.f32_ptr(bn4), float(bn_eps), cout, cin, kh, self.dtype,
+                                  C.byref(h)), "srb_pack_conv")
+        self.handle = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_free_weights(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+def conv2d_fwd(pc: PackedConv, x: torch.Tensor, x_planes: int, x_off: int, y: torch.Tensor, y_planes: int, y_off: int,
+               N: int, H: int, W: int, residual: torch.Tensor | None = None, res_planes: int = 0, res_off: int = 0,
+               res_scale: float = 1.0, out_scale: float = 1.0, slope: float = 0.0, flags: int = 0):
+    _require_cuda(x, "x")
+    _require_cuda(y, "y")
+    if residual is not None:
+        _require_cuda(residual, "residual")
+        flags |= F_RESIDUAL
+    check(lib().srb_conv2d_fwd(pc.ctx.handle, pc.handle, x.data_ptr(), x_planes, x_off, y.data_ptr(), y_planes, y_off,
+                               None if residual is None else residual.data_ptr(), res_planes, res_off, res_scale,
+                               out_scale, slope, flags, N, H, W, _stream_ptr(x.device)), "srb_conv2d_fwd")
+
+
+def c8_empty(N: int, planes: int, H: int, W: int, dtype, device) -> torch.Tensor:
+    """[N][planes][H][W][8] activation buffer."""
+    return torch.empty((N, planes, H, W, 8), dtype=_TORCH_DT[dtype_code(dtype)], device=device)
+
+
+def nchw_to_c8(x: torch.Tensor, out: torch.Tensor | None = None, planes: int | None = None, off: int = 0,
+               dtype=SRB_DT_F16) -> torch.Tensor:
+    """fp32 NCHW -> C8 planes (zero padded to a multiple of 8 channels) with the library's kernel."""
+    _require_cuda(x, "x")
+    x = x.float().contiguous()
+    N, Cc, H, W = x.shape
+    p = (Cc + 7) // 8
+    planes = planes or p
+    if out is None:
+        out = c8_empty(N, planes, H, W, dtype, x.device)
+    ctx = Context.get(x.device.index or 0)
+    check(lib().srb_f32nchw_to_c8(ctx.handle, x.data_ptr(), out.data_ptr(), Cc, planes, off, dtype_code(dtype), N, H, W,
+                                  _stream_ptr(x.device)), "srb_f32nchw_to_c8")
+    return out
+
+
+def c8_to_nchw(x: torch.Tensor, channels: int, off: int = 0) -> torch.Tensor:
+    _require_cuda(x, "x")
+    N, planes, H, W, _ = x.shape
+    out = torch.empty((N, channels, H, W), dtype=torch.float32, device=x.device)
+    ctx = Context.get(x.device.index or 0)
+    check(lib().srb_c8_to_f32nchw(ctx.handle, x.data_ptr(), out.data_ptr(), channels, planes, off,
+                                  dtype_code(x.dtype), N, H, W, _stream_ptr(x.device)), "srb_c8_to_f32nchw")
+    return out
+
+
+def _pred_code(t: torch.Tensor) -> int:
+    return {torch.float16: SRB_DT_F16, torch.bfloat16: SRB_DT_BF16, torch.float32: SRB_DT_F32}[t.dtype]
+
+
+def l1_loss_fwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0) -> torch.Tensor:
+    _require_cuda(pred, "pred")
+    _require_cuda(tgt, "tgt")
+    if tgt.dtype != torch.float32 or pred.shape != tgt.shape:
+        raise RuntimeError("l1_loss_fwd: target must be fp32 with pred's shape")
+    ctx = Context.get(pred.device.index or 0)
+    out = torch.empty((), dtype=torch.float32, device=pred.device)
+    partials = torch.empty(lib().srb_l1_partials_len(), dtype=torch.float32, device=pred.device)
+    check(lib().srb_l1_loss_fwd(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w),
+                                out.data_ptr(), partials.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_fwd")
+    return out
+
+
+def l1_loss_bwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0, grad_scale: float = 1.0) -> torch.Tensor:
+    _require_cuda(pred, "pred")
+    _require_cuda(tgt, "tgt")
+    ctx = Context.get(pred.device.index or 0)
+    g = torch.empty_like(pred)
+    check(lib().srb_l1_loss_bwd(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w),
+                                float(grad_scale), g.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_bwd")
+    return g

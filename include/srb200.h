@@ -1,0 +1,113 @@
+/* srb200.h — C ABI of libsrb200.so: hand-written sm_100a kernels for the super-resolution hot path.
+ *
+ * The reference (thnak/image_super_resolution) has no FFI of its own: the boundary it exposes is the
+ * Python object protocol of torch.nn.Module / torch.jit.ScriptModule at four call sites
+ * (rs.py:64, rs.py:94, train.py:55, train.py:56 — SURVEY §8(b)).  Each entry point below names the
+ * reference code whose execution it replaces.  All pointers are plain device (or, where stated,
+ * host) pointers, all sizes plain ints; no torch types.  Every function returns 0 on success or a
+ * negative SRB_E* code; srb_last_error() gives the thread-local message.  No call allocates device
+ * memory behind the caller's back except srb_create / srb_pack_conv / srb_model_pt_create (which
+ * own the packed weights) and the *_host convenience entry (which owns pinned staging buffers).
+ * All device work is enqueued on the caller's stream (a cudaStream_t passed as void*).
+ *
+ * Activation layout ("C8 planes"): [N][C/8][H][W][8] 16-bit floats (fp16 or bf16) — a 16-byte granule
+ * holds 8 consecutive channels of one pixel.  A conv may read / write a slice of planes of a wider
+ * buffer (c8_total, c8_off), which makes torch.cat of the dense blocks (utils/models.py:267-270) free.
+ */
+#ifndef SRB200_H
+#define SRB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRB_OK 0
+#define SRB_EINVAL (-1)   /* bad argument: shape, alignment, unsupported channel count ...        */
+#define SRB_ECUDA (-2)    /* a CUDA runtime / driver call failed                                  */
+#define SRB_ENOSUP (-3)   /* no sm_100a kernel for this configuration (never falls back to a CPU) */
+#define SRB_ENOMEM (-4)
+
+#define SRB_DT_F16 0
+#define SRB_DT_BF16 1
+
+/* epilogue flags of srb_conv2d_fwd */
+#define SRB_F_LRELU 1      /* LeakyReLU(slope) after bias (in-place activations of Conv/ConvWithoutBN) */
+#define SRB_F_RESIDUAL 2   /* y = out_scale*act(conv+b) + res_scale*residual                        */
+#define SRB_F_TANH 4       /* tanh (tail conv, utils/models.py:636,691)                              */
+#define SRB_F_U8OUT 8      /* TanhToArrayImage fused: uint8 NCHW output (utils/models.py:448-451)    */
+#define SRB_F_PIXSHUF2 16  /* nn.PixelShuffle(2) folded into the store (utils/models.py:580-583)     */
+#define SRB_F_F32OUT 32    /* tail conv: fp32 NCHW output                                            */
+
+typedef struct srb_ctx srb_ctx;
+typedef struct srb_weights srb_weights;
+typedef struct srb_net srb_net;
+typedef void* srb_stream_t; /* cudaStream_t */
+
+const char* srb_last_error(void);
+int srb_version(void);
+
+/* One context per device and host thread (the reference is single-threaded per process: rs.py, train.py). */
+int srb_create(int device, srb_ctx** out);
+void srb_destroy(srb_ctx* ctx);
+int srb_num_sms(const srb_ctx* ctx);
+/* diagnostics only: key 0 = swap LBO/SBO in UMMA descriptors, key 1 = grid size cap (0 = #SMs) */
+int srb_debug_set(srb_ctx* ctx, int key, int value);
+
+/* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for
+ * none), convert to dtype and lay the filter out as the UMMA B operand.  w is fp32 OIHW on the HOST.
+ * Replaces Conv.fuseforward / ConvWithoutBN._forward_impl weight handling (utils/models.py:97-106,191-196).
+ * Supported: (cin=3,k=9) head; (cin%16==0, k=3); (cout=3, cin%16==0, k=9) tail. */
+int srb_pack_conv(srb_ctx* ctx, const float* w_oihw, const float* bias, const float* bn4, float bn_eps,
+                  int cout, int cin, int k, int dtype, srb_weights** out);
+void srb_free_weights(srb_weights* w);
+
+/* One conv + fused epilogue.  Replaces aten::_convolution + bias + leaky_relu_/tanh + add/mul groups of
+ * Conv/ConvWithoutBN/ResidualBlock1/RDB/RRDB/Scaler forward (utils/models.py:97-98,195-196,208-209,
+ * 265-271,316-317,580-583).  x, y, residual are C8-plane device buffers (see header comment); for the
+ * tail conv (cout=3) y is NCHW uint8 (SRB_F_U8OUT) or fp32 (SRB_F_F32OUT). */
+int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, int x_c8_off, void* y,
+                   int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
+                   float res_scale, float out_scale, float lrelu_slope, int flags, int N, int H, int W,
+                   srb_stream_t stream);
+
+/* Normalize.forward (utils/datasets.py:65-71, uint8 branch baked into model.pt):
+ * uint8 NCHW [N,3,H,W] -> ((x/255)-mean)/std as one C8 plane (channels 3..7 zero). */
+int srb_u8nchw_to_c8(srb_ctx* ctx, const uint8_t* in, void* out_c8, const float mean[3], const float std_[3],
+                     float max_pixel_value, int dtype, int N, int H, int W, srb_stream_t stream);
+/* Layout converters for float callers (class nets take normalised fp32 NCHW, utils/models.py:645). */
+int srb_f32nchw_to_c8(srb_ctx* ctx, const float* in, void* out_c8, int C, int c8_total, int c8_off, int dtype,
+                      int N, int H, int W, srb_stream_t stream);
+int srb_c8_to_f32nchw(srb_ctx* ctx, const void* in_c8, float* out, int C, int c8_total, int c8_off, int dtype,
+                      int N, int H, int W, srb_stream_t stream);
+
+/* The whole model.pt graph (Model.forward, utils/models.py:738-739, on the traced old-revision Denoise):
+ * Normalize -> conv0 9x9+LReLU -> 8 x ResidualBlock1 -> conv1 + long skip -> conv2 9x9 + tanh -> uint8.
+ * weights: the 20 conv filters/biases in graph order (conv0, 8 x (m.0, m.1), conv1, conv2), fp32 host
+ * pointers w[i] = OIHW, b[i]; mean/std/max_pixel_value are net.0.* of the archive. */
+int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const float* const* b, const float mean[3],
+                        const float std_[3], float max_pixel_value, float lrelu_slope, int dtype, srb_net** out);
+void srb_model_pt_destroy(srb_net* net);
+size_t srb_model_pt_workspace_bytes(int N, int H, int W);
+/* device uint8 NCHW -> device uint8 NCHW; replaces `model(window_img)` (rs.py:94) / `model(frames)` (rs.py:64) */
+int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uint8_t* out_nchw, int N, int H,
+                         int W, void* workspace, size_t ws_bytes, srb_stream_t stream);
+/* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
+int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
+                              int H, int W);
+/* number of kernels of this library one srb_model_pt_forward enqueues */
+int srb_model_pt_launches(void);
+
+/* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
+ * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
+int srb_l1_partials_len(void);
+int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                    float* loss_out, float* partials, srb_stream_t stream);
+int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                    float grad_scale, void* dpred, srb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB200_H */

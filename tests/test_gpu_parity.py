@@ -1,0 +1,235 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Every call goes through the C ABI.
+
+Tolerances (fp16 operands, fp32 accumulate):
+  * single conv vs fp32 conv of the SAME fp16-rounded operands: |err| <= 2e-3 * max|ref| + 1e-3 (output rounding to fp16)
+  * model.pt end to end vs the fp32 oracle / reference golden: max-abs <= 2/255 on [0,1] pixels, >= 97 % pixels exact
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WEIGHTS = os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def ctx(dev):
+    from image_super_resolution_b200._lib import Context
+    return Context.get(0)
+
+
+def _conv_case(ctx, dev, cout, cin, k, N, H, W, flags=0, slope=0.2, residual=False, res_scale=1.0, out_scale=1.0,
+               seed=0, dtype="fp16"):
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(cout, cin, k, k, generator=g) / np.sqrt(cin * k * k)
+    b = torch.randn(cout, generator=g) * 0.1
+    x = torch.randn(N, cin, H, W, generator=g)
+    tdt = torch.float16 if dtype == "fp16" else torch.bfloat16
+    xq, wq = x.to(tdt).float(), w.to(tdt).float()
+    ref = F.conv2d(xq, wq, b, padding=k // 2)
+    if flags & ops.F_LRELU:
+        ref = F.leaky_relu(ref, slope)
+    ref = ref * out_scale
+    res = None
+    if residual:
+        res = torch.randn(N, cout, H, W, generator=g)
+        ref = ref + res_scale * res.to(tdt).float()
+    pc = ops.PackedConv(ctx, w, b, dtype=dtype)
+    xc = ops.nchw_to_c8(x.to(dev), dtype=dtype)
+    planes_out = (cout + 7) // 8
+    y = torch.zeros((N, planes_out, H, W, 8), dtype=tdt, device=dev)
+    rc = ops.nchw_to_c8(res.to(dev), dtype=dtype) if residual else None
+    ops.conv2d_fwd(pc, xc, xc.shape[1], 0, y, planes_out, 0, N, H, W, residual=rc, res_planes=planes_out, res_off=0,
+                   res_scale=res_scale, out_scale=out_scale, slope=slope, flags=flags)
+    out = ops.c8_to_nchw(y, cout).cpu()
+    torch.cuda.synchronize()
+    return out, ref
+
+
+def _assert_close(out, ref, what, rel=2e-3, abs_=1e-3, dtype="fp16"):
+    if dtype != "fp16":
+        rel, abs_ = 1e-2, 8e-3
+    err = (out - ref).abs()
+    tol = rel * ref.abs().max().item() + abs_
+    bad = err > tol
+    if bad.any():
+        idx = torch.nonzero(bad)[:8].tolist()
+        raise AssertionError(f"{what}: max err {err.max().item():.4g} > tol {tol:.4g}; {int(bad.sum())}/{bad.numel()} bad; "
+                             f"first bad idx {idx}; out={out[bad][:4].tolist()} ref={ref[bad][:4].tolist()}")
+
+
+@pytest.mark.parametrize("cout,cin", [(32, 64), (64, 32), (64, 64)])
+def test_conv3x3_plain(ctx, dev, cout, cin):
+    out, ref = _conv_case(ctx, dev, cout, cin, 3, 2, 32, 24)
+    _assert_close(out, ref, f"conv3x3 {cin}->{cout}")
+
+
+def test_conv3x3_lrelu_residual_ragged(ctx, dev):
+    from image_super_resolution_b200 import ops
+    out, ref = _conv_case(ctx, dev, 64, 32, 3, 3, 19, 13, flags=ops.F_LRELU, residual=True, res_scale=0.5,
+                          out_scale=0.2, seed=3)
+    _assert_close(out, ref, "conv3x3 lrelu+residual ragged")
+
+
+def test_conv3x3_many_tiles_persistent(ctx, dev):
+    # more tiles than CTAs: exercises stage ring wrap-around and both TMEM accumulators
+    out, ref = _conv_case(ctx, dev, 32, 64, 3, 4, 128, 120, seed=5)
+    _assert_close(out, ref, "conv3x3 many tiles")
+
+
+def test_conv3x3_bf16(ctx, dev):
+    out, ref = _conv_case(ctx, dev, 64, 64, 3, 1, 16, 16, dtype="bf16", seed=6)
+    _assert_close(out, ref, "conv3x3 bf16", dtype="bf16")
+
+
+def test_conv9x9_head(ctx, dev):
+    from image_super_resolution_b200 import ops
+    out, ref = _conv_case(ctx, dev, 64, 3, 9, 2, 33, 21, flags=ops.F_LRELU, seed=7)
+    _assert_close(out, ref, "conv9x9 head 3->64")
+
+
+def test_conv9x9_tail(ctx, dev):
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    N, H, W = 2, 21, 29
+    w = torch.randn(3, 64, 9, 9, generator=g) / 72.0
+    b = torch.randn(3, generator=g) * 0.1
+    x = torch.randn(N, 64, H, W, generator=g)
+    ref = torch.tanh(F.conv2d(x.half().float(), w.half().float(), b, padding=4))
+    pc = ops.PackedConv(ctx, w, b)
+    xc = ops.nchw_to_c8(x.to(dev))
+    y = torch.zeros((N, 3, H, W), dtype=torch.float32, device=dev)
+    ops.conv2d_fwd(pc, xc, 8, 0, y, 0, 0, N, H, W, flags=ops.F_TANH | ops.F_F32OUT)
+    _assert_close(y.cpu(), ref, "conv9x9 tail 64->3 tanh f32", rel=1e-3, abs_=1e-4)
+    yu = torch.zeros((N, 3, H, W), dtype=torch.uint8, device=dev)
+    ops.conv2d_fwd(pc, xc, 8, 0, yu, 0, 0, N, H, W, flags=ops.F_TANH | ops.F_U8OUT)
+    ref_u8 = ((ref + 1) / 2 * 255).round()
+    assert (yu.cpu().float() - ref_u8).abs().max().item() <= 1
+
+
+def test_u8_normalize_pack(ctx, dev):
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200._lib import lib, check
+    import ctypes as C
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 256, (2, 3, 9, 11), dtype=torch.uint8, generator=g)
+    mean, std = [0.485, 0.456, 0.406], [0.229, 0.224, 0.225]
+    out = torch.zeros((2, 1, 9, 11, 8), dtype=torch.float16, device=dev)
+    check(lib().srb_u8nchw_to_c8(ctx.handle, x.to(dev).data_ptr(), out.data_ptr(), (C.c_float * 3)(*mean),
+                                 (C.c_float * 3)(*std), 255.0, 0, 2, 9, 11, None))
+    ref = ((x.float() / 255.0) - torch.tensor(mean).view(1, 3, 1, 1)) / torch.tensor(std).view(1, 3, 1, 1)
+    got = ops.c8_to_nchw(out, 8).cpu()
+    assert torch.equal(got[:, :3], ref.half().float())  # bit-exact: same fp32 ops, one rounding to fp16
+    assert torch.count_nonzero(got[:, 3:]) == 0
+
+
+@pytest.fixture(scope="module")
+def model(dev):
+    import image_super_resolution_b200 as srb
+    return srb.load(WEIGHTS).to(dev).eval()
+
+
+CASES = ["uniform_2x96x96", "uniform_1x40x56", "uniform_3x17x23", "uniform_1x1x1", "smooth_1x72x88", "zeros_1x32x32",
+         "ones255_1x24x40"]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_model_pt_vs_reference_golden(model, dev, case, golden_dir):
+    gold = np.load(os.path.join(golden_dir, "model_pt_golden.npz"))
+    x = torch.from_numpy(gold[case + ".in"])
+    ref = torch.from_numpy(gold[case + ".out"])
+    y = model(x.to(dev)).cpu()
+    d = (y.int() - ref.int()).abs()
+    exact = (d == 0).float().mean().item()
+    assert d.max().item() <= 2, f"{case}: max diff {d.max().item()} LSB (tolerance 2/255)"
+    assert exact >= 0.97 or x.numel() < 200, f"{case}: only {exact:.3f} of pixels exact"
+
+
+def test_model_pt_host_entry_matches_device_entry(model, dev):
+    g = torch.Generator().manual_seed(9)
+    x = torch.randint(0, 256, (2, 3, 50, 70), dtype=torch.uint8, generator=g)
+    a = model(x)                 # host buffers through srb_model_pt_forward_host
+    b = model(x.to(dev)).cpu()   # device buffers through srb_model_pt_forward
+    assert not a.is_cuda and torch.equal(a, b)
+
+
+def test_model_pt_psnr_delta_and_determinism(model, dev):
+    """|dPSNR(out, clean)| <= 0.01 dB vs the fp32 oracle on the denoise task; repeated runs identical."""
+    from oracle import modelpt_oracle as mo
+    g = torch.Generator().manual_seed(100)
+    lo = torch.rand(1, 3, 24, 32, generator=g)
+    clean = F.interpolate(lo, size=(192, 256), mode="bicubic", align_corners=False).clamp(0, 1)
+    for sigma in (0.02, 0.05):
+        noisy = (clean + sigma * torch.randn(clean.shape, generator=g)).clamp(0, 1)
+        xu = (noisy * 255).round().to(torch.uint8)
+        cu = (clean * 255).round().to(torch.uint8)
+        ref = mo.forward_u8(xu)
+        y1 = model(xu.to(dev)).cpu()
+        y2 = model(xu.to(dev)).cpu()
+        assert torch.equal(y1, y2)
+        d = (y1.int() - ref.int()).abs()
+        assert d.max().item() <= 2
+        dp = mo.psnr(y1, cu) - mo.psnr(ref, cu)
+        assert abs(dp) <= 0.01, f"sigma={sigma}: PSNR delta {dp:+.4f} dB"
+
+
+def test_model_pt_tile_independence_large(model, dev):
+    """Size-independent property at bench scale: a [256,3,64,64] batch equals its images run one by one,
+    and halo tiling of a big image equals the whole-image forward."""
+    g = torch.Generator().manual_seed(4)
+    x = torch.randint(0, 256, (256, 3, 64, 64), dtype=torch.uint8, generator=g).to(dev)
+    y = model(x)
+    for i in (0, 77, 255):
+        assert torch.equal(model(x[i:i + 1].contiguous()), y[i:i + 1])
+    img = torch.randint(0, 256, (1, 3, 300, 420), dtype=torch.uint8, generator=g).to(dev)
+    whole = model(img)
+    R = 25
+    y0, y1, x0, x1 = 100, 200, 150, 330
+    tile = img[:, :, y0 - R:y1 + R, x0 - R:x1 + R].contiguous()
+    t = model(tile)[:, :, R:R + (y1 - y0), R:R + (x1 - x0)]
+    assert torch.equal(t, whole[:, :, y0:y1, x0:x1])
+
+
+def test_l1_loss_kernels(dev, golden_dir):
+    from image_super_resolution_b200 import ops
+    from oracle import l1_oracle
+    gold = np.load(os.path.join(golden_dir, "l1_golden.npz"))
+    for name in ("a", "b"):
+        p, t = torch.from_numpy(gold[name + ".pred"]).to(dev), torch.from_numpy(gold[name + ".tgt"]).to(dev)
+        loss = ops.l1_loss_fwd(p, t, 1.0).item()
+        assert abs(loss - float(gold[name + ".loss"])) <= 1e-6 * abs(float(gold[name + ".loss"])) + 1e-9
+        gr = ops.l1_loss_bwd(p, t, 1.0, 1.0).cpu().numpy()
+        assert np.array_equal(gr, gold[name + ".grad"])
+    g = torch.Generator().manual_seed(2)
+    p = (torch.rand(16, 3, 128, 128, generator=g) * 2 - 1)
+    t = (torch.rand(16, 3, 128, 128, generator=g) * 2 - 1)
+    want = float(l1_oracle.l1_loss(p.numpy(), t.numpy()))
+    got = ops.l1_loss_fwd(p.to(dev), t.to(dev)).item()
+    assert abs(got - want) <= 1e-6 * want
+    got16 = ops.l1_loss_fwd(p.half().to(dev), t.to(dev)).item()
+    want16 = float(l1_oracle.l1_loss(p.half().float().numpy(), t.numpy()))
+    assert abs(got16 - want16) <= 1e-6 * want16
+    gr = ops.l1_loss_bwd(p.to(dev), t.to(dev), 1.0, 1024.0).cpu().numpy()
+    assert np.array_equal(gr, l1_oracle.l1_grad(p.numpy(), t.numpy(), 1.0, 1024.0))
+
+
+def test_bad_arguments_raise(model, dev, ctx):
+    from image_super_resolution_b200 import ops
+    with pytest.raises(RuntimeError):
+        model(torch.zeros(1, 4, 8, 8, dtype=torch.uint8, device=dev))
+    with pytest.raises(RuntimeError):
+        ops.PackedConv(ctx, torch.zeros(10, 5, 3, 3))  # cin not a multiple of 16: no kernel, no fallback
+    assert model(torch.zeros(0, 3, 8, 8, dtype=torch.uint8, device=dev)).shape == (0, 3, 8, 8)
