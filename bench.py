@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py — the headline metric of BASELINE.json: output Mpix/s of model.pt inference.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port)
+
+Workload (config.workload): BASELINE.json configs[1] — a [256,3,64,64] uint8 batch through the model.pt
+graph, fp16 operands / fp32 accumulate, on each of N GPUs (frames are independent: weak scaling, no
+collective).  One step = one forward over that batch.  The working set of a step
+(~487 MB of C8-plane activations) is far larger than the 126 MB L2, so no explicit L2 flush is needed.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WEIGHTS = os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")
+BATCH, HH, WW = 256, 64, 64
+FLOP_PER_PX = 725760  # algorithmic FLOP (2*MAC) per pixel of the model.pt graph
+# algorithmic FLOP/px of each launch of one forward, in launch order (pack, conv0, 8x(A,B), conv1, conv2)
+LAUNCH_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
+LAUNCH_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64",
+                                                                                                 "conv9x9_tail_64_3"]
+assert sum(LAUNCH_FLOP_PX) == FLOP_PER_PX
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"bf16_tflops": d.get("bf16_tflops"), "bf16_tflops_sustained": d.get("bf16_tflops_sustained"),
+                "hbm_gbs": d.get("hbm_gbs"), "source": "measured"}
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period: float = 0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+                 nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def dist_setup(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def cpu_port_forward_timer(sample_tiles: int, min_seconds: float, max_iters: int = 1000):
+    """Times the oracle (CPU fp32 port of the reference path, all host threads) on a bounded sample."""
+    from oracle import modelpt_oracle as mo  # the one place bench.py executes oracle/: the CPU baseline
+    torch.set_num_threads(os.cpu_count() or 1)
+    sd = mo.load_weights(WEIGHTS)
+    g = torch.Generator().manual_seed(100)
+    x = torch.randint(0, 256, (sample_tiles, 3, HH, WW), dtype=torch.uint8, generator=g)
+    mo.forward_u8(x, sd)  # warm-up
+    times = []
+    t_all = time.perf_counter()
+    while (time.perf_counter() - t_all < min_seconds or len(times) < 3) and len(times) < max_iters:
+        t0 = time.perf_counter()
+        mo.forward_u8(x, sd)
+        times.append(time.perf_counter() - t0)
+    px = sample_tiles * HH * WW
+    return px, times
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path (fp32, oneDNN through ATen, all host
+    threads), restated by oracle/ from the extracted weights — /root/reference does not exist on the GPU box."""
+    if rank != 0:
+        return
+    sample_tiles = 32  # bounded sample of the [256,3,64,64] workload per step
+    from oracle import modelpt_oracle as mo
+    torch.set_num_threads(os.cpu_count() or 1)
+    sd = mo.load_weights(WEIGHTS)
+    g = torch.Generator().manual_seed(100)
+    x = torch.randint(0, 256, (sample_tiles, 3, HH, WW), dtype=torch.uint8, generator=g)
+    for _ in range(max(args.warmup, 1)):
+        mo.forward_u8(x, sd)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        mo.forward_u8(x, sd)
+    dt = time.perf_counter() - t0
+    px = sample_tiles * HH * WW * args.steps
+    v = px / dt / 1e6
+    sample = f"{sample_tiles} of the 256 64x64 tiles per step, fp32, torch CPU ({torch.get_num_threads()} threads)"
+    line = {"impl": "reference", "metric": "model.pt inference output Mpix/s", "value": v, "unit": "Mpix/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "model.pt batched inference, 64x64 LR tiles x256 batch (BASELINE configs[1]); "
+                                   "reference arm runs a bounded 32-tile sample per step on host cores"},
+            "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local):
+    import torch.distributed as dist
+    import image_super_resolution_b200 as srb
+    from image_super_resolution_b200._lib import lib, check
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    model = srb.load(WEIGHTS).to(dev).eval()
+    g = torch.Generator().manual_seed(100 + rank)
+    x_host = torch.randint(0, 256, (BATCH, 3, HH, WW), dtype=torch.uint8, generator=g).pin_memory()
+    y_host = torch.empty_like(x_host).pin_memory()
+    x = x_host.to(dev)
+    y = torch.empty_like(x)
+    K, Wm = args.steps, max(args.warmup, 3)
+    px_step = BATCH * HH * WW
+
+    for _ in range(Wm):
+        model(x, out=y)
+    # ---- device-resident throughput ("value") ----
+    sampler = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.start()
+    e0.record()
+    for _ in range(K):
+        model(x, out=y)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+
+    # ---- end to end through the public API, host buffers, copies inside the timed region ----
+    xd = torch.empty_like(x)
+    for _ in range(2):
+        xd.copy_(x_host, non_blocking=True)
+        y_host.copy_(model(xd, out=y), non_blocking=True)
+    barrier()
+    e0.record()
+    for _ in range(K):
+        xd.copy_(x_host, non_blocking=True)
+        y_host.copy_(model(xd, out=y), non_blocking=True)
+    e1.record()
+    barrier()
+    ms2 = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    ms_e2e = float(ms2.item())
+
+    # ---- per-launch durations (CUDA events recorded by the library on the launching stream) ----
+    ctxh = model._ctx.handle
+    nl = model.launches_per_forward()
+    acc = [0.0] * nl
+    buf = (C.c_float * 64)()
+    check(lib().srb_profile_enable(ctxh, 1))
+    for _ in range(K):
+        model(x, out=y)
+        n = lib().srb_profile_read(ctxh, buf, 64)
+        assert n == nl, (n, nl)
+        for i in range(nl):
+            acc[i] += buf[i]
+    check(lib().srb_profile_enable(ctxh, 0))
+    per_launch = [a / K for a in acc]
+    groups = {}
+    for name, t, f in zip(LAUNCH_NAMES, per_launch, LAUNCH_FLOP_PX):
+        gsum = groups.setdefault(name, [0, 0.0, 0.0])
+        gsum[0] += 1; gsum[1] += t; gsum[2] += f * px_step
+    pk = peaks()
+    kernels = {k: {"launches": v[0], "ms_per_launch": v[1] / v[0], "tflops": (v[2] / v[0]) / (v[1] / v[0]) / 1e9,
+                   "share": v[1] / sum(per_launch)} for k, v in groups.items()}
+    top = max(groups, key=lambda k: groups[k][1])
+    achieved = kernels[top]["tflops"]
+    roofline = {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                "frac": achieved / pk["bf16_tflops"], "traffic": None,
+                "peak_source": f"{pk['source']} burst bf16 (MEASURED_PEAKS.json)",
+                "whole_step_tflops": px_step * FLOP_PER_PX / (sum(per_launch) / 1e3) / 1e12,
+                "kernels": kernels}
+
+    if rank == 0:
+        value = world * px_step * K / (ms_total / 1e3) / 1e6
+        e2e = world * px_step * K / (ms_e2e / 1e3) / 1e6
+        line = {"metric": "model.pt inference output Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world,
+                "steps": K, "warmup": Wm, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+                "config": {"workload": "model.pt batched inference, 64x64 LR tiles x256 batch per GPU (BASELINE configs[1])",
+                           "per_gpu_batch": BATCH, "tile": [HH, WW], "operands": "fp16 in, fp32 accumulate",
+                           "l2": "working set 487 MB per step > 126 MB L2 (no flush needed)",
+                           "parallelism": f"frames sharded over {world} GPU(s), no collective"},
+                "tflops": value * 1e6 * FLOP_PER_PX / 1e12,
+                "frac_of_bf16_peak": value * 1e6 * FLOP_PER_PX / 1e12 / (pk["bf16_tflops"] * world),
+                "clocks": clocks,
+                "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": x_host.numel(),
+                        "d2h_bytes_per_step": y_host.numel(), "ms_per_step": ms_e2e / K},
+                "gpu_launches": nl * K,
+                "roofline": roofline}
+        if world == 1 and not args.no_cpu:
+            px, times = cpu_port_forward_timer(sample_tiles=32, min_seconds=10.0)
+            best = min(times)
+            line["cpu_baseline"] = {"value": px / best / 1e6, "unit": "Mpix/s", "cores": torch.get_num_threads(),
+                                    "kind": "port",
+                                    "sample": f"32 of the 256 64x64 tiles, fp32 torch CPU oracle, best of {len(times)} runs"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank, world, local = dist_setup(args.gpus)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local)
+
+
+if __name__ == "__main__":
+    main()

@@ -55,6 +55,10 @@ struct srb_ctx {
     uint8_t* d_io = nullptr; size_t d_io_bytes = 0;
     void* d_ws = nullptr; size_t d_ws_bytes = 0;
     cudaStream_t own_stream = nullptr;
+    // optional per-launch timing of srb_model_pt_forward (bench/roofline only)
+    int prof = 0;
+    std::vector<cudaEvent_t> ev;
+    int nev = 0;
 };
 
 struct srb_weights {
@@ -66,7 +70,7 @@ struct srb_weights {
 };
 
 struct srb_net {
-    srb_weights* conv[20];
+    srb_weights* conv[19];
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -104,6 +108,7 @@ extern "C" void srb_destroy(srb_ctx* c) {
     if (c->d_io) cudaFree(c->d_io);
     if (c->d_ws) cudaFree(c->d_ws);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
     delete c;
 }
 extern "C" int srb_num_sms(const srb_ctx* c) { return c ? c->num_sms : 0; }
@@ -387,11 +392,11 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
     for (int i = 0; i < 3; ++i) { net->mean[i] = mean[i]; net->std_[i] = std_[i]; }
     net->maxv = maxv; net->slope = slope; net->dtype = dtype;
     int rc = SRB_OK;
-    for (int i = 0; i < 20 && rc == SRB_OK; ++i) {
+    for (int i = 0; i < 19 && rc == SRB_OK; ++i) {
         int cout, cin, k;
         if (i == 0) { cout = 64; cin = 3; k = 9; }
-        else if (i == 19) { cout = 3; cin = 64; k = 9; }
-        else if (i == 18) { cout = 64; cin = 64; k = 3; }
+        else if (i == 18) { cout = 3; cin = 64; k = 9; }
+        else if (i == 17) { cout = 64; cin = 64; k = 3; }
         else if (i & 1) { cout = 32; cin = 64; k = 3; }
         else { cout = 64; cin = 32; k = 3; }
         if (!w[i] || !b[i]) rc = fail(SRB_EINVAL, "srb_model_pt_create: weight %d is NULL", i);
@@ -404,7 +409,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
 
 extern "C" void srb_model_pt_destroy(srb_net* net) {
     if (!net) return;
-    for (int i = 0; i < 20; ++i) srb_free_weights(net->conv[i]);
+    for (int i = 0; i < 19; ++i) srb_free_weights(net->conv[i]);
     delete net;
 }
 
@@ -417,6 +422,35 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
 }
 
 extern "C" int srb_model_pt_launches(void) { return 20; }
+
+extern "C" int srb_profile_enable(srb_ctx* ctx, int on) {
+    if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
+    ctx->prof = on;
+    ctx->nev = 0;
+    return SRB_OK;
+}
+
+// elapsed ms between consecutive events recorded by the last profiled forward; returns the count written
+extern "C" int srb_profile_read(srb_ctx* ctx, float* ms, int max_n) {
+    if (!ctx || !ms) return fail(SRB_EINVAL, "srb_profile_read: NULL argument");
+    if (ctx->nev < 2) return 0;
+    if (cudaEventSynchronize(ctx->ev[ctx->nev - 1]) != cudaSuccess) return fail(SRB_ECUDA, "srb_profile_read: event sync failed");
+    int n = 0;
+    for (int i = 0; i + 1 < ctx->nev && n < max_n; ++i, ++n)
+        if (cudaEventElapsedTime(&ms[n], ctx->ev[i], ctx->ev[i + 1]) != cudaSuccess) return fail(SRB_ECUDA, "srb_profile_read: elapsed failed");
+    return n;
+}
+
+static void prof_mark(srb_ctx* ctx, cudaStream_t st, bool first = false) {
+    if (!ctx->prof) return;
+    if (first) ctx->nev = 0;
+    if ((int)ctx->ev.size() <= ctx->nev) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        ctx->ev.push_back(e);
+    }
+    cudaEventRecord(ctx->ev[ctx->nev++], st);
+}
 
 extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in, uint8_t* out, int N, int H, int W,
                                     void* ws, size_t ws_bytes, srb_stream_t stream) {
@@ -434,18 +468,26 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     void* hid = base;
     const float s = net->slope;
     int rc;
+    cudaStream_t pst = (cudaStream_t)stream;
+    prof_mark(ctx, pst, true);
     if ((rc = srb_u8nchw_to_c8(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
+    prof_mark(ctx, pst);
     if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+    prof_mark(ctx, pst);
     void* cur = x0;
     for (int i = 0; i < 8; ++i) {
         void* nxt = (i & 1) ? rb : ra;
         if ((rc = srb_conv2d_fwd(ctx, net->conv[1 + 2 * i], cur, 8, 0, hid, 4, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+        prof_mark(ctx, pst);
         if ((rc = srb_conv2d_fwd(ctx, net->conv[2 + 2 * i], hid, 4, 0, nxt, 8, 0, cur, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
+        prof_mark(ctx, pst);
         cur = nxt;
     }
     // cur == rb after 8 blocks; long skip adds conv0's (post-activation) output
     if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
-    if ((rc = srb_conv2d_fwd(ctx, net->conv[19], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+    prof_mark(ctx, pst);
+    if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+    prof_mark(ctx, pst);
     return SRB_OK;
 }
 

@@ -20,7 +20,7 @@ from . import _lib
 from ._lib import Context, check, lib
 from .ops import dtype_code
 
-# state-dict keys of the 20 convs in graph order (archive __torch__.py, class Denoise)
+# state-dict keys of the 19 convs in graph order (archive __torch__.py, class Denoise)
 CONV_KEYS = (["net.1.conv0.0.conv"] + [f"net.1.residual.{i}.m.{j}.conv" for i in range(8) for j in (0, 1)] +
              ["net.1.conv1.conv", "net.1.conv2.0.conv"])
 LRELU_SLOPE = 0.2          # leaky_relu_(0.2) in the traced graph
@@ -79,8 +79,8 @@ class ModelPT:
         for k in CONV_KEYS:
             ws.append(np.ascontiguousarray(self._state[k + ".weight"].numpy(), dtype=np.float32))
             bs.append(np.ascontiguousarray(self._state[k + ".bias"].numpy(), dtype=np.float32))
-        wp = (C.c_void_p * 20)(*[w.ctypes.data for w in ws])
-        bp = (C.c_void_p * 20)(*[b.ctypes.data for b in bs])
+        wp = (C.c_void_p * 19)(*[w.ctypes.data for w in ws])
+        bp = (C.c_void_p * 19)(*[b.ctypes.data for b in bs])
         mean = (C.c_float * 3)(*self._state["net.0.mean"].flatten().tolist())
         std = (C.c_float * 3)(*self._state["net.0.std"].flatten().tolist())
         maxv = float(self._state["net.0.max_pixel_value"])

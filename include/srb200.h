@@ -84,7 +84,7 @@ int srb_c8_to_f32nchw(srb_ctx* ctx, const void* in_c8, float* out, int C, int c8
 
 /* The whole model.pt graph (Model.forward, utils/models.py:738-739, on the traced old-revision Denoise):
  * Normalize -> conv0 9x9+LReLU -> 8 x ResidualBlock1 -> conv1 + long skip -> conv2 9x9 + tanh -> uint8.
- * weights: the 20 conv filters/biases in graph order (conv0, 8 x (m.0, m.1), conv1, conv2), fp32 host
+ * weights: the 19 conv filters/biases in graph order (conv0, 8 x (m.0, m.1), conv1, conv2), fp32 host
  * pointers w[i] = OIHW, b[i]; mean/std/max_pixel_value are net.0.* of the archive. */
 int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const float* const* b, const float mean[3],
                         const float std_[3], float max_pixel_value, float lrelu_slope, int dtype, srb_net** out);
@@ -98,6 +98,10 @@ int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host
                               int H, int W);
 /* number of kernels of this library one srb_model_pt_forward enqueues */
 int srb_model_pt_launches(void);
+/* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
+ * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
+int srb_profile_enable(srb_ctx* ctx, int on);
+int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
 
 /* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
  * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
