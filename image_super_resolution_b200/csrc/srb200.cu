@@ -14,6 +14,7 @@
 #include "../../include/srb200.h"
 #include "srb_conv.cuh"
 #include "srb_elem.cuh"
+#include "srb_ubench.cuh"
 
 using namespace srb;
 
@@ -50,6 +51,7 @@ struct srb_ctx {
     PFN_encodeTiled encode = nullptr;
     int dbg_swap = 0;
     int dbg_grid = 0;
+    int dbg_skip = 0;
     // pinned + device staging for the *_host entry
     uint8_t* h_pin = nullptr; size_t h_pin_bytes = 0;
     uint8_t* d_io = nullptr; size_t d_io_bytes = 0;
@@ -116,6 +118,7 @@ extern "C" int srb_debug_set(srb_ctx* c, int key, int value) {
     if (!c) return fail(SRB_EINVAL, "ctx is NULL");
     if (key == 0) c->dbg_swap = value;
     else if (key == 1) c->dbg_grid = value;
+    else if (key == 2) c->dbg_skip = value;
     else return fail(SRB_EINVAL, "srb_debug_set: unknown key %d", key);
     return SRB_OK;
 }
@@ -231,6 +234,7 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
     if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
     p.dbg_swap = ctx->dbg_swap;
+    p.dbg_skip = ctx->dbg_skip;
     if (w->dtype == SRB_DT_BF16) {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, true>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
@@ -524,5 +528,25 @@ extern "C" int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8
     CUDA_TRY(cudaMemcpyAsync(ctx->h_pin + io_al, ctx->d_io + io_al, io, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     memcpy(out_host, ctx->h_pin + io_al, io);
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// measurement tooling: tcgen05.mma micro-benchmark (see srb_ubench.cuh)
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host) {
+    if (!ctx || !out2_host) return fail(SRB_EINVAL, "srb_ubench_mma: NULL argument");
+    if (racc < 1 || racc * n * (m64 > 0 ? m64 : 1) > 512 || m64 > 4) return fail(SRB_EINVAL, "srb_ubench_mma: racc*n*warps > 512 TMEM columns");
+    long long* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, 16));
+    const int smem = 100 * 1024;
+#define UB(NN) case NN: CUDA_TRY(cudaFuncSetAttribute(ubench_mma_kernel<NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+               ubench_mma_kernel<NN><<<grid, 128, smem>>>(layout, racc, iters, m64, d); break;
+    switch (n) { UB(16) UB(32) UB(64) UB(96) UB(128) UB(192) UB(256) default: cudaFree(d); return fail(SRB_EINVAL, "srb_ubench_mma: n=%d", n); }
+#undef UB
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpy(out2_host, d, 16, cudaMemcpyDeviceToHost));
+    cudaFree(d);
     return SRB_OK;
 }

@@ -47,6 +47,7 @@ struct ConvParams {
     int flags;
     int cout;                // real output channels (DXN: 3)
     int dbg_swap;            // debug: swap LBO/SBO of the A descriptor (diagnostics only)
+    int dbg_skip;            // debug/bottleneck probes: 1 = no TMA tile loads, 2 = no MMAs, 4 = no global I/O in epilogue
 };
 
 template <int C8IN, int NOUT, int KH, int KW, int MODE>
@@ -153,9 +154,12 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                 int r = tile - n * tiles_per_img;
                 int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
                 mbar_wait(&empty[s], ph ^ 1, 1);
-                mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES);
-                tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::TW - G::PADX) * 8,
-                            ty * G::TH - G::PADY, p.x_c8_off, n);
+                if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
+                else {
+                    mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES);
+                    tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::TW - G::PADX) * 8,
+                                ty * G::TH - G::PADY, p.x_c8_off, n);
+                }
                 if (++s == G::STAGES) { s = 0; ph ^= 1; }
             }
         }
@@ -179,7 +183,8 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                 const uint32_t a_addr = smem_u32(s_a + s * G::STAGE_STRIDE);
                 const uint32_t d_tmem = tmem_base + a * NOUT;
                 int ks = 0;
-                if constexpr (MODE == MODE_STD) {
+                if (p.dbg_skip & 2) {
+                } else if constexpr (MODE == MODE_STD) {
 #pragma unroll 1
                     for (int dy = 0; dy < KH; ++dy)
 #pragma unroll 1
@@ -231,7 +236,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             const uint32_t t_addr = tmem_base + a * NOUT + ((uint32_t)(lg * 32) << 16);
             if constexpr (MODE != MODE_DXN) {
                 const int y = tyi * G::TH + (L >> 3), x = txi * G::TW + (L & 7);
-                const bool valid = (y < p.H) && (x < p.W);
+                const bool valid = (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
                 const size_t pix = (size_t)y * p.W + x;
 #pragma unroll 1
                 for (int c0 = 0; c0 < NOUT; c0 += 32) {
@@ -310,7 +315,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
 #pragma unroll
                     for (int co = 0; co < 3; ++co)
                         acc[co] += __shfl_sync(0xffffffffu, __uint_as_float(rr[dx * 3 + co]), (lane + dx - 4) & 31);
-                const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W);
+                const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
                 if (valid) {
 #pragma unroll
                     for (int co = 0; co < 3; ++co) {

@@ -1,0 +1,68 @@
+// Micro-benchmark of tcgen05.mma issue/throughput on this part: cycles per M=128 x N x K=16 MMA as a
+// function of N, the operand layout, and how many independent TMEM accumulators are interleaved.
+// Measurement tooling only (drives kernel design decisions recorded in DESIGN.md); not on the product path.
+#pragma once
+#include "srb_ptx.cuh"
+
+namespace srb {
+
+// layout: 0 = SWIZZLE_NONE with the conv kernel's halo-tile strides (LBO=2880, SBO=160)
+//         1 = SWIZZLE_NONE dense (LBO=2048 [128 rows x 16 B], SBO=128)
+//         2 = SWIZZLE_128B canonical (SBO=1024)
+template <int N>
+__global__ void __launch_bounds__(128, 1) ubench_mma_kernel(int layout, int racc, int iters, int m64, long long* out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    __shared__ uint64_t bar[4];
+    __shared__ uint32_t s_tmem;
+    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) mbar_init(&bar[i], 1); fence_mbar_init(); }
+    if (threadIdx.x < 32) tmem_alloc(&s_tmem, 512);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = s_tmem;
+    const int nwarps = m64 > 0 ? m64 : 1;   // (re-purposed knob) number of issuing warps
+    const int wid = threadIdx.x >> 5;
+    if (wid < nwarps) {   // warp-uniform control flow; one elected lane issues (no divergent-issue waterfall)
+        const uint32_t a_addr = smem_u32(smem), b_addr = smem_u32(smem + 64 * 1024);
+        uint64_t adesc, bdesc;
+        if (layout == 0) { adesc = umma_desc_nosw(a_addr, 2880, 160); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }
+        else if (layout == 1) { adesc = umma_desc_nosw(a_addr, 2048, 128); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }
+        else {
+            adesc = umma_desc_nosw(a_addr, 16, 1024) | (2ull << 61);
+            bdesc = umma_desc_nosw(b_addr, 16, 1024) | (2ull << 61);
+        }
+        const uint32_t idesc = umma_idesc_f16(128, N, 0);
+        const uint32_t tb = tmem_base + wid * racc * N;
+        uint64_t* mybar = &bar[wid];
+        if (elect_one()) {
+            for (int r = 0; r < racc; ++r) umma_f16_ss(tb + r * N, adesc, bdesc, idesc, 0);
+            umma_commit(mybar);
+        }
+        __syncwarp();
+        mbar_wait(mybar, 0, 100);
+        long long t0 = clock64();
+        for (int i = 0; i < iters; i += 4) {
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    for (int r = 0; r < racc; ++r)
+                        umma_f16_ss(tb + r * N, adesc + (uint64_t)(k * 2), bdesc, idesc, 1);
+            }
+            __syncwarp();
+        }
+        long long t1 = clock64();
+        if (elect_one()) umma_commit(mybar);
+        __syncwarp();
+        mbar_wait(mybar, 1, 101);
+        long long t2 = clock64();
+        if (blockIdx.x == 0 && threadIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace srb

@@ -102,6 +102,9 @@ int srb_model_pt_launches(void);
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
 int srb_profile_enable(srb_ctx* ctx, int on);
 int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
+/* measurement only: cycles for `iters` rounds of `racc` interleaved M=128(64) x n x 16 tcgen05.mma;
+ * out2_host[0] = issue cycles, out2_host[1] = cycles until all MMAs completed */
+int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host);
 
 /* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
  * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
