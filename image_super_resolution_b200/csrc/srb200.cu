@@ -210,23 +210,25 @@ extern "C" void srb_free_weights(srb_weights* w) {
 // ------------------------------------------------------------------------------------------
 // conv dispatch
 // ------------------------------------------------------------------------------------------
-template <int C8IN, int NOUT, int KH, int KW, int MODE>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT>
 static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, ConvParams p, cudaStream_t st) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE>;
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT>;
     if (w->ksteps != G::KSTEPS || (size_t)G::WBYTES != w->pack_bytes)
         return fail(SRB_EINVAL, "launch_conv: packed weights do not match the kernel geometry");
-    p.tiles_x = (p.W + G::TW - 1) / G::TW;
-    p.tiles_y = (p.H + G::TH - 1) / G::TH;
+    p.tiles_x = (p.W + G::SUPER_W - 1) / G::SUPER_W;
+    p.tiles_y = (p.H + G::SUPER_H - 1) / G::SUPER_H;
     long long nt = (long long)p.tiles_x * p.tiles_y * p.N;
     if (nt <= 0 || nt > 0x7fffffffLL) return fail(SRB_EINVAL, "launch_conv: %lld tiles", nt);
     p.num_tiles = (int)nt;
 
     CUtensorMap tmap;
-    cuuint64_t gdim[4] = {(cuuint64_t)p.W * 8, (cuuint64_t)p.H, (cuuint64_t)x_c8_total, (cuuint64_t)p.N};
+    cuuint64_t gdim[4] = {(cuuint64_t)p.W * 4, (cuuint64_t)p.H, (cuuint64_t)x_c8_total, (cuuint64_t)p.N};
     cuuint64_t gstr[3] = {(cuuint64_t)p.W * 16, (cuuint64_t)p.W * p.H * 16, (cuuint64_t)p.W * p.H * 16 * x_c8_total};
-    cuuint32_t box[4] = {(cuuint32_t)G::HALO_W * 8, (cuuint32_t)G::HALO_H, (cuuint32_t)C8IN, 1};
+    cuuint32_t box[4] = {(cuuint32_t)G::HALO_W * 4, (cuuint32_t)G::HALO_H, (cuuint32_t)C8IN, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = ctx->encode(&tmap, w->dtype == SRB_DT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+    // typed as 32-bit words (4 per 16-byte granule): only zero fill and byte movement matter, and it lifts the
+    // 256-element box limit to 64 pixels per row
+    CUresult r = ctx->encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32,
                              4, const_cast<void*>(x), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d (W=%d H=%d planes=%d N=%d)", (int)r, p.W, p.H, x_c8_total, p.N);
@@ -236,11 +238,11 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     p.dbg_swap = ctx->dbg_swap;
     p.dbg_skip = ctx->dbg_skip;
     if (w->dtype == SRB_DT_BF16) {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, true>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, true>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
     } else {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, false>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, false>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
     }
@@ -270,22 +272,23 @@ extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x,
     cudaStream_t st = (cudaStream_t)stream;
     if (w->mode == MODE_DXN) {
         if (!(flags & (SRB_F_U8OUT | SRB_F_F32OUT))) return fail(SRB_EINVAL, "srb_conv2d_fwd: tail conv needs SRB_F_U8OUT or SRB_F_F32OUT");
-        if (w->c8in == 8) return launch_conv<8, 32, 9, 9, MODE_DXN>(ctx, w, x, x_c8_total, p, st);
+        if (w->c8in == 8) return launch_conv<8, 32, 9, 9, MODE_DXN, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: tail conv with cin=%d", w->cin);
     }
     if (flags & (SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_TANH)) return fail(SRB_EINVAL, "srb_conv2d_fwd: tanh/u8/f32 output only on the tail conv");
     int out_planes = (flags & SRB_F_PIXSHUF2) ? w->cout / 32 : (w->cout + 7) / 8;
     if ((flags & SRB_F_PIXSHUF2) && (w->cout % 32)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PixelShuffle(2) needs cout %% 32 == 0");
     if ((flags & SRB_F_PIXSHUF2) && (flags & SRB_F_RESIDUAL)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PIXSHUF2 with residual unsupported");
+    if ((flags & SRB_F_RESIDUAL) && w->nout > 64) return fail(SRB_ENOSUP, "srb_conv2d_fwd: residual epilogue needs cout <= 64");
+    if ((flags & SRB_F_RESIDUAL) && (res_c8_off < 0 || res_c8_off + out_planes > res_c8_total)) return fail(SRB_EINVAL, "srb_conv2d_fwd: residual plane slice out of range");
     if (y_c8_off < 0 || y_c8_off + out_planes > y_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: output plane slice out of range");
     if (w->cout % 8) return fail(SRB_ENOSUP, "srb_conv2d_fwd: cout=%d not a multiple of 8", w->cout);
     if (w->mode == MODE_PAIRDX) {
-        if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX>(ctx, w, x, x_c8_total, p, st);
+        if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
     }
-#define SRB_STD(C8, NO) if (w->c8in == C8 && w->nout == NO) return launch_conv<C8, NO, 3, 3, MODE_STD>(ctx, w, x, x_c8_total, p, st);
-    SRB_STD(8, 32) SRB_STD(4, 64) SRB_STD(8, 64)
-    SRB_STD(12, 32) SRB_STD(16, 32) SRB_STD(20, 32)
+#define SRB_STD(C8, NO, NTT) if (w->c8in == C8 && w->nout == NO) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT>(ctx, w, x, x_c8_total, p, st);
+    SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3)
 #undef SRB_STD
     return fail(SRB_ENOSUP, "srb_conv2d_fwd: no 3x3 kernel for cin=%d cout=%d", w->cin, w->cout);
 }

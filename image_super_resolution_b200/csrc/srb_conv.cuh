@@ -11,10 +11,16 @@
 // channel planes are LBO apart.  A filter tap (dy,dx) is then just a different start address into
 // the same halo tile (no swizzle => any 16-byte shift is legal), so one TMA load feeds all taps.
 //
-// GEMM view: M = 128 pixels (8 wide x 16 high tile), N = Cout, K = 16 per tcgen05.mma.
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 = epilogue (TMEM -> regs ->
-// bias / LeakyReLU / scale / residual / pack -> global).  Two TMEM accumulators overlap the
-// epilogue of tile i with the MMAs of tile i+1; a ring of halo-tile stages overlaps TMA with MMA.
+// GEMM view: an M-tile is 128 pixels (8 wide x 16 high; DXN: 16 wide x 8 high), N = Cout, K = 16 per
+// tcgen05.mma.  Measured on B200 (tools/gpu_ubench.py): an SS-mode M=128 MMA costs
+// max(N/2, (4 KB + 32 B*N) / 128 B/clk) cycles and a dependent MMA into the same accumulator cannot
+// start for ~85 cycles, so a pipeline step is a SUPER-TILE of NT M-tiles sharing one TMA box whose
+// MMAs are issued round-robin into NT independent TMEM accumulators.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (warp-uniform loop, one elected lane issues),
+// warps 2..5 = epilogue (TMEM -> regs -> bias / LeakyReLU / scale / residual / pack -> global).
+// Two accumulator sets overlap the epilogue of step i with the MMAs of step i+1; a ring of halo-tile
+// stages overlaps TMA with MMA; residual granules are prefetched into registers before the
+// accumulator is waited for, so the epilogue never sits on a DRAM round trip.
 #pragma once
 #include <cuda.h>
 #include "srb_ptx.cuh"
@@ -35,7 +41,7 @@ enum : int {
 
 struct ConvParams {
     int N, H, W;
-    int tiles_x, tiles_y, num_tiles;
+    int tiles_x, tiles_y, num_tiles;   // super-tiles
     int x_c8_off;            // first input plane
     const uint8_t* wpack;    // packed B operand: ksteps x [2][NOUT][8] halves
     const float* bias;       // NOUT floats (zero padded)
@@ -46,41 +52,47 @@ struct ConvParams {
     float res_scale, out_scale, slope;
     int flags;
     int cout;                // real output channels (DXN: 3)
-    int dbg_swap;            // debug: swap LBO/SBO of the A descriptor (diagnostics only)
-    int dbg_skip;            // debug/bottleneck probes: 1 = no TMA tile loads, 2 = no MMAs, 4 = no global I/O in epilogue
+    int dbg_swap;            // debug: swap LBO/SBO of the descriptors (diagnostics only)
+    int dbg_skip;            // bottleneck probes: 1 = no TMA tile loads, 2 = no MMAs, 4 = no global I/O in epilogue
 };
 
-template <int C8IN, int NOUT, int KH, int KW, int MODE>
+// NT M-tiles per super-tile: STD tiles sit side by side in x; PAIRDX / DXN tiles are stacked in y.
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT>
 struct ConvGeom {
-    static constexpr int TW = (MODE == MODE_DXN) ? 8 : 8;    // output tile width
-    static constexpr int TH = (MODE == MODE_DXN) ? 8 : 16;   // output tile height
+    static constexpr int TW = 8;                                  // output tile width
+    static constexpr int TH = (MODE == MODE_DXN) ? 8 : 16;        // output tile height
+    static constexpr int SUPER_W = (MODE == MODE_STD) ? TW * NT : TW;
+    static constexpr int SUPER_H = (MODE == MODE_STD) ? TH : TH * NT;
     static constexpr int PADX = KW / 2, PADY = KH / 2;
-    static constexpr int HALO_W = (MODE == MODE_DXN) ? 16 : (TW + KW - 1 + ((MODE == MODE_PAIRDX) ? (KW & 1) : 0));
-    static constexpr int HALO_H = TH + KH - 1;
-    static constexpr int ROWP = HALO_W * 16;                 // bytes between tile rows
-    static constexpr int PLANE = HALO_H * ROWP;              // bytes between channel planes
-    static constexpr int STAGE_BYTES = C8IN * PLANE;         // one TMA box
+    static constexpr int HALO_W = (MODE == MODE_DXN) ? 16 : (SUPER_W + KW - 1 + ((MODE == MODE_PAIRDX) ? (KW & 1) : 0));
+    static constexpr int HALO_H = SUPER_H + KH - 1;
+    static constexpr int ROWP = HALO_W * 16;                      // bytes between tile rows
+    static constexpr int PLANE = HALO_H * ROWP;                   // bytes between channel planes
+    static constexpr int TOFF = (MODE == MODE_STD) ? TW * 16 : TH * ROWP;  // A-operand offset of M-tile t
+    static constexpr int STAGE_BYTES = C8IN * PLANE;              // one TMA box
     static constexpr int STAGE_STRIDE = (STAGE_BYTES + 1023) / 1024 * 1024;
     static constexpr int KSTEPS = (MODE == MODE_STD)      ? KH * KW * (C8IN / 2)
                                   : (MODE == MODE_PAIRDX) ? KH * ((KW + 1) / 2)
                                                           : KH * (C8IN / 2);
-    static constexpr int WSTEP_BYTES = 2 * NOUT * 16;        // one K=16 slice of B
+    static constexpr int WSTEP_BYTES = 2 * NOUT * 16;             // one K=16 slice of B
     static constexpr int WBYTES = KSTEPS * WSTEP_BYTES;
-    static constexpr int TMEM_COLS = (2 * NOUT <= 32) ? 32 : (2 * NOUT <= 64) ? 64 : (2 * NOUT <= 128) ? 128
-                                     : (2 * NOUT <= 256) ? 256 : 512;
-    static constexpr int SMEM_FIXED = 1024 /*align slack*/ + WBYTES + NOUT * 4 + 256 /*barriers*/;
+    static constexpr int ACC_COLS = 2 * NT * NOUT;                // two accumulator sets
+    static constexpr int TMEM_COLS = (ACC_COLS <= 32) ? 32 : (ACC_COLS <= 64) ? 64 : (ACC_COLS <= 128) ? 128
+                                     : (ACC_COLS <= 256) ? 256 : 512;
+    static constexpr int SMEM_FIXED = 1024 /*align slack*/ + (WBYTES + 1023) / 1024 * 1024 + NOUT * 4 + 256 /*barriers*/;
     static constexpr int max_stages() {
-        int s = (227 * 1024 - SMEM_FIXED - 1024) / STAGE_STRIDE;
+        int s = (227 * 1024 - SMEM_FIXED) / STAGE_STRIDE;
         return s > 4 ? 4 : s;
     }
     static constexpr int STAGES = max_stages();
-    static constexpr int SMEM_BYTES = SMEM_FIXED + STAGES * STAGE_STRIDE + 1024;
+    static constexpr int SMEM_BYTES = SMEM_FIXED + STAGES * STAGE_STRIDE;
     static_assert(MODE != MODE_PAIRDX || C8IN == 1, "PAIRDX pairs neighbouring pixels of a single plane");
     static_assert(MODE == MODE_PAIRDX || (C8IN % 2) == 0, "K=16 needs two channel planes per MMA");
     static_assert(MODE != MODE_DXN || (KW == 9 && NOUT == 32), "DXN folds 9 dx taps x 3 couts into N=32");
     static_assert(NOUT % 32 == 0 && NOUT <= 256, "epilogue reads TMEM 32 columns at a time");
-    static_assert(HALO_W * 8 <= 256 && HALO_H <= 256, "TMA box limits");
-    static_assert(STAGES >= 1, "does not fit shared memory");
+    static_assert(ACC_COLS <= 512, "TMEM holds 512 columns");
+    static_assert(HALO_W * 4 <= 256 && HALO_H <= 256, "TMA box limits (tensor map is typed as 32-bit words: 4 per granule)");
+    static_assert(STAGES >= 2, "needs two halo stages in shared memory");
 };
 
 __device__ __forceinline__ float lrelu(float v, float s) { return v > 0.f ? v : v * s; }
@@ -103,10 +115,18 @@ __device__ __forceinline__ float2 unpack2(uint32_t u) {
         return __half22float2(*reinterpret_cast<__half2*>(&u));
     }
 }
+__device__ __forceinline__ uint4 ldg_nc16(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 
-template <int C8IN, int NOUT, int KH, int KW, int MODE, bool BF16>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool BF16>
 __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap, const ConvParams p) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE>;
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT>;
+    constexpr int NG = NOUT / 8;                 // output granules per pixel
+    constexpr int NGR = NG <= 8 ? NG : 1;        // residual granules kept in registers (residual needs NOUT <= 64)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_w = smem;                                       // WBYTES
@@ -132,7 +152,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         fence_mbar_init();
         tma_prefetch_desc(&tmap);
     }
-    if (warp == 0) tmem_alloc(s_tmem, G::TMEM_COLS);
+    if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, G::TMEM_COLS); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -141,207 +161,249 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
     const int tiles_per_img = p.tiles_x * p.tiles_y;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (warp-uniform loop, one elected lane issues) =====================
+        if (elect_one()) {
             mbar_arrive_expect_tx(wbar, G::WBYTES);
             for (int off = 0; off < G::WBYTES; off += 16384) {
                 int n = G::WBYTES - off < 16384 ? G::WBYTES - off : 16384;
                 bulk_load_1d(s_w + off, p.wpack + off, n, wbar);
             }
-            int s = 0; uint32_t ph = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                int n = tile / tiles_per_img;
-                int r = tile - n * tiles_per_img;
-                int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-                mbar_wait(&empty[s], ph ^ 1, 1);
+        }
+        __syncwarp();
+        int s = 0; uint32_t ph = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            int n = tile / tiles_per_img;
+            int r = tile - n * tiles_per_img;
+            int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
+            mbar_wait(&empty[s], ph ^ 1, 1);
+            if (elect_one()) {
                 if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
                 else {
                     mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES);
-                    tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::TW - G::PADX) * 8,
-                                ty * G::TH - G::PADY, p.x_c8_off, n);
+                    tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX) * 4,
+                                ty * G::SUPER_H - G::PADY, p.x_c8_off, n);
                 }
-                if (++s == G::STAGES) { s = 0; ph ^= 1; }
             }
+            __syncwarp();
+            if (++s == G::STAGES) { s = 0; ph ^= 1; }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_f16(128, NOUT, BF16 ? 1 : 0);
-            const uint32_t w_addr = smem_u32(s_w);
-            uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (uint32_t)G::PLANE;
-            uint32_t a_sbo = (MODE == MODE_DXN) ? 128u : (uint32_t)G::ROWP;
-            uint32_t b_lbo = NOUT * 16, b_sbo = 128;
-            if (p.dbg_swap) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
-            mbar_wait(wbar, 0, 2);
-            int s = 0; uint32_t ph = 0; int it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-                const int a = it & 1;
-                const uint32_t aph = (it >> 1) & 1;
-                mbar_wait(&tempty[a], aph ^ 1, 3);
-                mbar_wait(&full[s], ph, 4);
-                tc_fence_after();
-                const uint32_t a_addr = smem_u32(s_a + s * G::STAGE_STRIDE);
-                const uint32_t d_tmem = tmem_base + a * NOUT;
-                int ks = 0;
-                if (p.dbg_skip & 2) {
-                } else if constexpr (MODE == MODE_STD) {
+        constexpr uint32_t idesc = umma_idesc_f16(128, NOUT, BF16 ? 1 : 0);
+        uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (uint32_t)G::PLANE;
+        uint32_t a_sbo = (MODE == MODE_DXN) ? 128u : (uint32_t)G::ROWP;
+        uint32_t b_lbo = NOUT * 16, b_sbo = 128;
+        if (p.dbg_swap) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
+        // descriptors with a zero start address; the 14-bit (addr >> 4) field is added per MMA
+        const uint64_t a_desc0 = umma_desc_nosw(0, a_lbo, a_sbo);
+        const uint64_t b_desc0 = umma_desc_nosw(smem_u32(s_w), b_lbo, b_sbo);
+        mbar_wait(wbar, 0, 2);
+        int s = 0; uint32_t ph = 0; int it = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            const int b = it & 1;
+            const uint32_t bph = (it >> 1) & 1;
+            mbar_wait(&tempty[b], bph ^ 1, 3);
+            mbar_wait(&full[s], ph, 4);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint64_t a_desc = a_desc0 + (uint64_t)(smem_u32(s_a + s * G::STAGE_STRIDE) >> 4);
+                const uint32_t d_tmem = tmem_base + b * (NT * NOUT);
+                if (!(p.dbg_skip & 2)) {
+                    int ks = 0;
+                    if constexpr (MODE == MODE_STD) {
 #pragma unroll 1
-                    for (int dy = 0; dy < KH; ++dy)
+                        for (int dy = 0; dy < KH; ++dy)
 #pragma unroll 1
-                        for (int dx = 0; dx < KW; ++dx)
+                            for (int dx = 0; dx < KW; ++dx)
+#pragma unroll
+                                for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
+                                    const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP + dx * 16) >> 4;
+                                    const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+#pragma unroll
+                                    for (int t = 0; t < NT; ++t)
+                                        umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
+                                }
+                    } else if constexpr (MODE == MODE_PAIRDX) {
+#pragma unroll 1
+                        for (int dy = 0; dy < KH; ++dy)
+#pragma unroll
+                            for (int dxp = 0; dxp < (KW + 1) / 2; ++dxp, ++ks) {
+                                const uint32_t ao = (dy * G::ROWP + 2 * dxp * 16) >> 4;
+                                const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+#pragma unroll
+                                for (int t = 0; t < NT; ++t)
+                                    umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
+                            }
+                    } else {
+#pragma unroll 1
+                        for (int dy = 0; dy < KH; ++dy)
 #pragma unroll
                             for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
-                                uint32_t ao = a_addr + 2 * c2 * G::PLANE + dy * G::ROWP + dx * 16;
-                                umma_f16_ss(d_tmem, umma_desc_nosw(ao, a_lbo, a_sbo),
-                                            umma_desc_nosw(w_addr + ks * G::WSTEP_BYTES, b_lbo, b_sbo), idesc, ks > 0);
+                                const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP) >> 4;
+                                const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+#pragma unroll
+                                for (int t = 0; t < NT; ++t)
+                                    umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
                             }
-                } else if constexpr (MODE == MODE_PAIRDX) {
-#pragma unroll 1
-                    for (int dy = 0; dy < KH; ++dy)
-#pragma unroll
-                        for (int dxp = 0; dxp < (KW + 1) / 2; ++dxp, ++ks) {
-                            uint32_t ao = a_addr + dy * G::ROWP + 2 * dxp * 16;
-                            umma_f16_ss(d_tmem, umma_desc_nosw(ao, a_lbo, a_sbo),
-                                        umma_desc_nosw(w_addr + ks * G::WSTEP_BYTES, b_lbo, b_sbo), idesc, ks > 0);
-                        }
-                } else {
-#pragma unroll 1
-                    for (int dy = 0; dy < KH; ++dy)
-#pragma unroll
-                        for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
-                            uint32_t ao = a_addr + 2 * c2 * G::PLANE + dy * G::ROWP;
-                            umma_f16_ss(d_tmem, umma_desc_nosw(ao, a_lbo, a_sbo),
-                                        umma_desc_nosw(w_addr + ks * G::WSTEP_BYTES, b_lbo, b_sbo), idesc, ks > 0);
-                        }
+                    }
                 }
                 umma_commit(&empty[s]);   // halo stage may be refilled once these MMAs have read it
-                umma_commit(&tfull[a]);   // accumulator complete -> epilogue
-                if (++s == G::STAGES) { s = 0; ph ^= 1; }
+                umma_commit(&tfull[b]);   // accumulators complete -> epilogue
             }
+            __syncwarp();
+            if (++s == G::STAGES) { s = 0; ph ^= 1; }
         }
     } else {
         // ===================== epilogue (warps 2..5) =====================
         const int lg = warp & 3;                  // TMEM lane group this warp may access
-        const int L = lg * 32 + lane;             // accumulator row = pixel of the tile
+        const int L = lg * 32 + lane;             // accumulator row = pixel of the M-tile
         const size_t HW = (size_t)p.H * p.W;
+        const bool has_res = (p.flags & F_RESIDUAL) != 0 && !(p.dbg_skip & 4);
         int it = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-            const int a = it & 1;
-            const uint32_t aph = (it >> 1) & 1;
-            int n = tile / tiles_per_img;
-            int r = tile - n * tiles_per_img;
-            int tyi = r / p.tiles_x, txi = r - tyi * p.tiles_x;
-            mbar_wait(&tfull[a], aph, 5);
-            tc_fence_after();
-            const uint32_t t_addr = tmem_base + a * NOUT + ((uint32_t)(lg * 32) << 16);
+            const int b = it & 1;
+            const uint32_t bph = (it >> 1) & 1;
+            const int n = tile / tiles_per_img;
+            const int r = tile - n * tiles_per_img;
+            const int tyi = r / p.tiles_x, txi = r - tyi * p.tiles_x;
+            const uint32_t t_addr0 = tmem_base + b * (NT * NOUT) + ((uint32_t)(lg * 32) << 16);
             if constexpr (MODE != MODE_DXN) {
-                const int y = tyi * G::TH + (L >> 3), x = txi * G::TW + (L & 7);
-                const bool valid = (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
-                const size_t pix = (size_t)y * p.W + x;
-#pragma unroll 1
-                for (int c0 = 0; c0 < NOUT; c0 += 32) {
-                    uint32_t rr[32];
-                    tmem_ld32(t_addr + c0, rr);
-                    tmem_ld_wait();
-                    if (c0 >= p.cout) continue;   // padded output channels
-                    if (!(p.flags & F_PIXSHUF2)) {
+                // pixel of this thread in M-tile t
+                auto pix_y = [&](int t) { return tyi * G::SUPER_H + (MODE == MODE_STD ? 0 : t * G::TH) + (L >> 3); };
+                auto pix_x = [&](int t) { return txi * G::SUPER_W + (MODE == MODE_STD ? t * G::TW : 0) + (L & 7); };
+                uint4 rq[NGR];
+                auto prefetch = [&](int t, uint4* dst) {
+                    const int y = pix_y(t), x = pix_x(t);
+                    if (y < p.H && x < p.W) {
+                        const uint8_t* rp = reinterpret_cast<const uint8_t*>(p.res) +
+                                            (((size_t)n * p.res_c8_total + p.res_c8_off) * HW + (size_t)y * p.W + x) * 16;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int gj = (c0 >> 3) + j;
-                            if (gj * 8 >= p.cout) break;
-                            float v[8];
+                        for (int j = 0; j < NGR; ++j)
+                            if (j * 8 < p.cout) dst[j] = ldg_nc16(rp + (size_t)j * HW * 16);
+                    }
+                };
+                if (has_res) prefetch(0, rq);
+                mbar_wait(&tfull[b], bph, 5);
+                tc_fence_after();
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                float t = __uint_as_float(rr[8 * j + i]) + s_bias[c0 + 8 * j + i];
-                                if (p.flags & F_LRELU) t = lrelu(t, p.slope);
-                                v[i] = t * p.out_scale;
-                            }
-                            if (valid) {
-                                if (p.flags & F_RESIDUAL) {
-                                    const uint4 q = *reinterpret_cast<const uint4*>(
-                                        reinterpret_cast<const uint8_t*>(p.res) +
-                                        (((size_t)n * p.res_c8_total + p.res_c8_off + gj) * HW + pix) * 16);
-                                    const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+                for (int t = 0; t < NT; ++t) {
+                    uint4 rn[NGR];
+                    if (has_res && t + 1 < NT) prefetch(t + 1, rn);
+                    const int y = pix_y(t), x = pix_x(t);
+                    const bool valid = (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
+                    const size_t pix = (size_t)y * p.W + x;
 #pragma unroll
-                                    for (int i = 0; i < 4; ++i) {
-                                        float2 f = unpack2<BF16>(qq[i]);
-                                        v[2 * i] += p.res_scale * f.x;
-                                        v[2 * i + 1] += p.res_scale * f.y;
-                                    }
+                    for (int c0 = 0; c0 < NOUT; c0 += 32) {
+                        uint32_t rr[32];
+                        tmem_ld32(t_addr0 + t * NOUT + c0, rr);
+                        tmem_ld_wait();
+                        if (c0 >= p.cout) continue;   // padded output channels
+                        if (!(p.flags & F_PIXSHUF2)) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int gj = (c0 >> 3) + j;
+                                if (gj * 8 >= p.cout) break;
+                                float v[8];
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    float tt = __uint_as_float(rr[8 * j + i]) + s_bias[c0 + 8 * j + i];
+                                    if (p.flags & F_LRELU) tt = lrelu(tt, p.slope);
+                                    v[i] = tt * p.out_scale;
                                 }
-                                uint4 o;
-                                o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
-                                o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
-                                *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.y) +
-                                    (((size_t)n * p.y_c8_total + p.y_c8_off + gj) * HW + pix) * 16) = o;
+                                if (valid) {
+                                    if (has_res) {
+                                        const uint4 q = rq[gj < NGR ? gj : 0];
+                                        const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                                        for (int i = 0; i < 4; ++i) {
+                                            float2 f = unpack2<BF16>(qq[i]);
+                                            v[2 * i] += p.res_scale * f.x;
+                                            v[2 * i + 1] += p.res_scale * f.y;
+                                        }
+                                    }
+                                    uint4 o;
+                                    o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
+                                    o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
+                                    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.y) +
+                                        (((size_t)n * p.y_c8_total + p.y_c8_off + gj) * HW + pix) * 16) = o;
+                                }
+                            }
+                        } else {
+                            // PixelShuffle(2): conv channel 32k + 4c + 2i + j  ->  out channel 8k + c at (2y+i, 2x+j)
+                            const int k = c0 >> 5;
+                            const size_t W2 = (size_t)p.W * 2, HW4 = HW * 4;
+#pragma unroll
+                            for (int ij = 0; ij < 4; ++ij) {
+                                float v[8];
+#pragma unroll
+                                for (int c = 0; c < 8; ++c) {
+                                    float tt = __uint_as_float(rr[4 * c + ij]) + s_bias[c0 + 4 * c + ij];
+                                    if (p.flags & F_LRELU) tt = lrelu(tt, p.slope);
+                                    v[c] = tt * p.out_scale;
+                                }
+                                if (valid) {
+                                    uint4 o;
+                                    o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
+                                    o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
+                                    const size_t opix = (size_t)(2 * y + (ij >> 1)) * W2 + 2 * x + (ij & 1);
+                                    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.y) +
+                                        (((size_t)n * p.y_c8_total + p.y_c8_off + k) * HW4 + opix) * 16) = o;
+                                }
                             }
                         }
-                    } else {
-                        // PixelShuffle(2): conv channel 32k + 4c + 2i + j  ->  out channel 8k + c at (2y+i, 2x+j)
-                        const int k = c0 >> 5;
-                        const size_t W2 = (size_t)p.W * 2, HW4 = HW * 4;
+                    }
+                    if (has_res && t + 1 < NT) {
 #pragma unroll
-                        for (int ij = 0; ij < 4; ++ij) {
-                            float v[8];
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                float t = __uint_as_float(rr[4 * c + ij]) + s_bias[c0 + 4 * c + ij];
-                                if (p.flags & F_LRELU) t = lrelu(t, p.slope);
-                                v[c] = t * p.out_scale;
-                            }
-                            if (valid) {
-                                uint4 o;
-                                o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
-                                o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
-                                const size_t opix = (size_t)(2 * y + (ij >> 1)) * W2 + 2 * x + (ij & 1);
-                                *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.y) +
-                                    (((size_t)n * p.y_c8_total + p.y_c8_off + k) * HW4 + opix) * 16) = o;
-                            }
-                        }
+                        for (int j = 0; j < NGR; ++j) rq[j] = rn[j];
                     }
                 }
             } else {
                 // DXN: column dx*3+co of row (y, x') is the contribution of input column x' to output
                 // (y, x' - dx + 4); gather the 9 horizontally shifted partials with warp shuffles.
-                uint32_t rr[32];
-                tmem_ld32(t_addr, rr);
-                tmem_ld_wait();
-                const int y = tyi * G::TH + (L >> 4);
-                const int t16 = L & 15;
-                const int x = txi * G::TW - G::PADX + t16;
-                float acc[3] = {s_bias[0], s_bias[1], s_bias[2]};
+                mbar_wait(&tfull[b], bph, 5);
+                tc_fence_after();
 #pragma unroll
-                for (int dx = 0; dx < 9; ++dx)
+                for (int t = 0; t < NT; ++t) {
+                    uint32_t rr[32];
+                    tmem_ld32(t_addr0 + t * NOUT, rr);
+                    tmem_ld_wait();
+                    const int y = tyi * G::SUPER_H + t * G::TH + (L >> 4);
+                    const int t16 = L & 15;
+                    const int x = txi * G::SUPER_W - G::PADX + t16;
+                    float acc[3] = {s_bias[0], s_bias[1], s_bias[2]};
 #pragma unroll
-                    for (int co = 0; co < 3; ++co)
-                        acc[co] += __shfl_sync(0xffffffffu, __uint_as_float(rr[dx * 3 + co]), (lane + dx - 4) & 31);
-                const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
-                if (valid) {
+                    for (int dx = 0; dx < 9; ++dx)
 #pragma unroll
-                    for (int co = 0; co < 3; ++co) {
-                        float t = acc[co];
-                        if (p.flags & F_TANH) t = tanhf(t);
-                        const size_t o = ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
-                        if (p.flags & F_U8OUT) {
-                            float u = (t + 1.0f) * 0.5f;
-                            u = u * 255.0f;
-                            u = fminf(fmaxf(rintf(u), 0.f), 255.f);
-                            reinterpret_cast<uint8_t*>(p.y)[o] = (uint8_t)u;
-                        } else {
-                            reinterpret_cast<float*>(p.y)[o] = t;
+                        for (int co = 0; co < 3; ++co)
+                            acc[co] += __shfl_sync(0xffffffffu, __uint_as_float(rr[dx * 3 + co]), (lane + dx - 4) & 31);
+                    const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
+                    if (valid) {
+#pragma unroll
+                        for (int co = 0; co < 3; ++co) {
+                            float tt = acc[co];
+                            if (p.flags & F_TANH) tt = tanhf(tt);
+                            const size_t o = ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
+                            if (p.flags & F_U8OUT) {
+                                float u = (tt + 1.0f) * 0.5f;
+                                u = u * 255.0f;
+                                u = fminf(fmaxf(rintf(u), 0.f), 255.f);
+                                reinterpret_cast<uint8_t*>(p.y)[o] = (uint8_t)u;
+                            } else {
+                                reinterpret_cast<float*>(p.y)[o] = tt;
+                            }
                         }
                     }
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[a]);
+            if (lane == 0) mbar_arrive(&tempty[b]);
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem_base, G::TMEM_COLS);
+    if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, G::TMEM_COLS); }
 }
 
 }  // namespace srb
