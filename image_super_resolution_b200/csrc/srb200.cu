@@ -210,9 +210,9 @@ extern "C" void srb_free_weights(srb_weights* w) {
 // ------------------------------------------------------------------------------------------
 // conv dispatch
 // ------------------------------------------------------------------------------------------
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false>
 static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, ConvParams p, cudaStream_t st) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT>;
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES>;
     if (w->ksteps != G::KSTEPS || (size_t)G::WBYTES != w->pack_bytes)
         return fail(SRB_EINVAL, "launch_conv: packed weights do not match the kernel geometry");
     p.tiles_x = (p.W + G::SUPER_W - 1) / G::SUPER_W;
@@ -233,18 +233,28 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d (W=%d H=%d planes=%d N=%d)", (int)r, p.W, p.H, x_c8_total, p.N);
 
+    CUtensorMap tmap_res = tmap;
+    if (RES) {
+        cuuint64_t rdim[4] = {(cuuint64_t)p.W * 4, (cuuint64_t)p.H, (cuuint64_t)p.res_c8_total, (cuuint64_t)p.N};
+        cuuint64_t rstr[3] = {(cuuint64_t)p.W * 16, (cuuint64_t)p.W * p.H * 16, (cuuint64_t)p.W * p.H * 16 * p.res_c8_total};
+        cuuint32_t rbox[4] = {(cuuint32_t)G::TW * 4, (cuuint32_t)G::TH, (cuuint32_t)(NOUT / 8), 1};
+        r = ctx->encode(&tmap_res, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(p.res), rdim, rstr, rbox, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled (residual) failed: %d", (int)r);
+    }
     int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
     if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
     p.dbg_swap = ctx->dbg_swap;
     p.dbg_skip = ctx->dbg_skip;
     if (w->dtype == SRB_DT_BF16) {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, true>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, true>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
+        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     } else {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, false>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, false>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, p);
+        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
@@ -287,7 +297,9 @@ extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x,
         if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
     }
-#define SRB_STD(C8, NO, NTT) if (w->c8in == C8 && w->nout == NO) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT>(ctx, w, x, x_c8_total, p, st);
+#define SRB_STD(C8, NO, NTT) if (w->c8in == C8 && w->nout == NO) { \
+        if ((flags & SRB_F_RESIDUAL) && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
+        return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
     SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3)
 #undef SRB_STD
     return fail(SRB_ENOSUP, "srb_conv2d_fwd: no 3x3 kernel for cin=%d cout=%d", w->cin, w->cout);

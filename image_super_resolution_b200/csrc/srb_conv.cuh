@@ -57,7 +57,7 @@ struct ConvParams {
 };
 
 // NT M-tiles per super-tile: STD tiles sit side by side in x; PAIRDX / DXN tiles are stacked in y.
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false>
 struct ConvGeom {
     static constexpr int TW = 8;                                  // output tile width
     static constexpr int TH = (MODE == MODE_DXN) ? 8 : 16;        // output tile height
@@ -84,8 +84,16 @@ struct ConvGeom {
         int s = (227 * 1024 - SMEM_FIXED) / STAGE_STRIDE;
         return s > 4 ? 4 : s;
     }
-    static constexpr int STAGES = max_stages();
-    static constexpr int SMEM_BYTES = SMEM_FIXED + STAGES * STAGE_STRIDE;
+    static constexpr int STAGES = RES ? 2 : max_stages();
+    // RES: the residual M-tiles (8 px x 16 rows x NOUT/8 planes) are TMA-loaded into a ring of smem slots
+    static constexpr int RES_TILE_BYTES = (NOUT / 8) * 128 * 16;
+    static constexpr int max_rslots() {
+        int r = (227 * 1024 - SMEM_FIXED - 2 * STAGE_STRIDE) / RES_TILE_BYTES;
+        return r > 6 ? 6 : r;
+    }
+    static constexpr int RSLOTS = RES ? max_rslots() : 0;
+    static constexpr int SMEM_BYTES = SMEM_FIXED + STAGES * STAGE_STRIDE + RSLOTS * RES_TILE_BYTES;
+    static_assert(!RES || (RSLOTS >= 2 && MODE == MODE_STD), "residual ring needs two slots (STD mode only)");
     static_assert(MODE != MODE_PAIRDX || C8IN == 1, "PAIRDX pairs neighbouring pixels of a single plane");
     static_assert(MODE == MODE_PAIRDX || (C8IN % 2) == 0, "K=16 needs two channel planes per MMA");
     static_assert(MODE != MODE_DXN || (KW == 9 && NOUT == 32), "DXN folds 9 dx taps x 3 couts into N=32");
@@ -122,23 +130,27 @@ __device__ __forceinline__ uint4 ldg_nc16(const void* p) {
     return r;
 }
 
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool BF16>
-__global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap, const ConvParams p) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT>;
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool BF16>
+__global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap,
+                                                         const __grid_constant__ CUtensorMap tmap_res, const ConvParams p) {
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES>;
     constexpr int NG = NOUT / 8;                 // output granules per pixel
     constexpr int NGR = NG <= 8 ? NG : 1;        // residual granules kept in registers (residual needs NOUT <= 64)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_w = smem;                                       // WBYTES
     uint8_t* s_a = smem + (G::WBYTES + 1023) / 1024 * 1024;    // STAGES x STAGE_STRIDE
-    float* s_bias = reinterpret_cast<float*>(s_a + G::STAGES * G::STAGE_STRIDE);
+    uint8_t* s_res = s_a + G::STAGES * G::STAGE_STRIDE;        // RSLOTS x RES_TILE_BYTES
+    float* s_bias = reinterpret_cast<float*>(s_res + G::RSLOTS * G::RES_TILE_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_bias + NOUT);
     uint64_t* full = bars;                   // [STAGES]
     uint64_t* empty = bars + 4;              // [STAGES]
     uint64_t* tfull = bars + 8;              // [2]
     uint64_t* tempty = bars + 10;            // [2]
     uint64_t* wbar = bars + 12;              // [1]
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 14);
+    uint64_t* rfull = bars + 14;             // [RSLOTS <= 6]
+    uint64_t* rempty = bars + 20;            // [RSLOTS <= 6]
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 28);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -149,8 +161,10 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         mbar_init(&tfull[0], 1); mbar_init(&tfull[1], 1);
         mbar_init(&tempty[0], 4); mbar_init(&tempty[1], 4);
         mbar_init(wbar, 1);
+        for (int s = 0; s < G::RSLOTS; ++s) { mbar_init(&rfull[s], 1); mbar_init(&rempty[s], 4); }
         fence_mbar_init();
         tma_prefetch_desc(&tmap);
+        if (RES) tma_prefetch_desc(&tmap_res);
     }
     if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, G::TMEM_COLS); }
     tc_fence_before();
@@ -171,6 +185,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         }
         __syncwarp();
         int s = 0; uint32_t ph = 0;
+        int rs = 0; uint32_t rph = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
             int n = tile / tiles_per_img;
             int r = tile - n * tiles_per_img;
@@ -186,6 +201,22 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
             __syncwarp();
             if (++s == G::STAGES) { s = 0; ph ^= 1; }
+            if constexpr (RES) {
+#pragma unroll 1
+                for (int t = 0; t < NT; ++t) {
+                    mbar_wait(&rempty[rs], rph ^ 1, 6);
+                    if (elect_one()) {
+                        if (p.dbg_skip & 1) { mbar_arrive(&rfull[rs]); }
+                        else {
+                            mbar_arrive_expect_tx(&rfull[rs], G::RES_TILE_BYTES);
+                            tma_load_4d(s_res + rs * G::RES_TILE_BYTES, &tmap_res, &rfull[rs],
+                                        (tx * G::SUPER_W + t * G::TW) * 4, ty * G::SUPER_H, p.res_c8_off, n);
+                        }
+                    }
+                    __syncwarp();
+                    if (++rs == G::RSLOTS) { rs = 0; rph ^= 1; }
+                }
+            }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -258,7 +289,8 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         const int lg = warp & 3;                  // TMEM lane group this warp may access
         const int L = lg * 32 + lane;             // accumulator row = pixel of the M-tile
         const size_t HW = (size_t)p.H * p.W;
-        const bool has_res = (p.flags & F_RESIDUAL) != 0 && !(p.dbg_skip & 4);
+        const bool has_res = !RES && (p.flags & F_RESIDUAL) != 0 && !(p.dbg_skip & 4);   // register-prefetch path
+        int rs = 0; uint32_t rph = 0;                                                    // smem-ring path (RES)
         int it = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int b = it & 1;
@@ -289,6 +321,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                 for (int t = 0; t < NT; ++t) {
                     uint4 rn[NGR];
                     if (has_res && t + 1 < NT) prefetch(t + 1, rn);
+                    if constexpr (RES) mbar_wait(&rfull[rs], rph, 7);
                     const int y = pix_y(t), x = pix_x(t);
                     const bool valid = (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
                     const size_t pix = (size_t)y * p.W + x;
@@ -311,8 +344,10 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                                     v[i] = tt * p.out_scale;
                                 }
                                 if (valid) {
-                                    if (has_res) {
-                                        const uint4 q = rq[gj < NGR ? gj : 0];
+                                    if (RES || has_res) {
+                                        uint4 q;
+                                        if constexpr (RES) q = *reinterpret_cast<const uint4*>(s_res + rs * G::RES_TILE_BYTES + (gj * 128 + L) * 16);
+                                        else q = rq[gj < NGR ? gj : 0];
                                         const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
@@ -355,6 +390,11 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                     if (has_res && t + 1 < NT) {
 #pragma unroll
                         for (int j = 0; j < NGR; ++j) rq[j] = rn[j];
+                    }
+                    if constexpr (RES) {
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&rempty[rs]);
+                        if (++rs == G::RSLOTS) { rs = 0; rph ^= 1; }
                     }
                 }
             } else {
