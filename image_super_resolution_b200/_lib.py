@@ -38,6 +38,8 @@ SIGNATURES = {
     "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
     "srb_model_pt_launches": (_i, []),
+    "srb_check_device": (_i, [_vp]),
+    "srb_debug_trace": (_i, [_vp, _vp]),
     "srb_profile_enable": (_i, [_vp, _i]),
     "srb_profile_read": (_i, [_vp, _fp, _i]),
     "srb_ubench_mma": (_i, [_vp, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_longlong)]),
@@ -92,6 +94,10 @@ class Context:
         if device not in cls._by_device:
             cls._by_device[device] = Context(device)
         return cls._by_device[device]
+
+    def check_device(self):
+        """Synchronise and raise if a kernel reported a pipeline timeout."""
+        check(lib().srb_check_device(self.handle), "srb_check_device")
 
     def debug_set(self, key: int, value: int):
         check(lib().srb_debug_set(self.handle, key, value), "srb_debug_set")

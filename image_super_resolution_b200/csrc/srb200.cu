@@ -52,6 +52,7 @@ struct srb_ctx {
     int dbg_swap = 0;
     int dbg_grid = 0;
     int dbg_skip = 0;
+    long long* dbg_trace = nullptr;
     // pinned + device staging for the *_host entry
     uint8_t* h_pin = nullptr; size_t h_pin_bytes = 0;
     uint8_t* d_io = nullptr; size_t d_io_bytes = 0;
@@ -247,14 +248,15 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
     p.dbg_swap = ctx->dbg_swap;
     p.dbg_skip = ctx->dbg_skip;
+    p.dbg_trace = ctx->dbg_trace;
     if (w->dtype == SRB_DT_BF16) {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, true>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
+        kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     } else {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, false>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, 192, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
+        kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
@@ -441,6 +443,30 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
 }
 
 extern "C" int srb_model_pt_launches(void) { return 20; }
+
+// measurement only: per-step clock trace of CTA 0 of the next conv launches (512 int64 device buffer, or NULL)
+extern "C" int srb_debug_trace(srb_ctx* ctx, void* dev_buf512) {
+    if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
+    ctx->dbg_trace = (long long*)dev_buf512;
+    return SRB_OK;
+}
+
+// Synchronise the device and report a kernel-side protocol timeout (see mbar_wait) as an error.
+extern "C" int srb_check_device(srb_ctx* ctx) {
+    if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    unsigned int flag = 0, info[4] = {0, 0, 0, 0};
+    CUDA_TRY(cudaMemcpyFromSymbol(&flag, g_srb_abort, sizeof(flag)));
+    if (flag) {
+        CUDA_TRY(cudaMemcpyFromSymbol(info, g_srb_timeout_info, sizeof(info)));
+        unsigned int zero = 0;
+        CUDA_TRY(cudaMemcpyToSymbol(g_srb_abort, &zero, sizeof(zero)));
+        return fail(SRB_ECUDA, "kernel pipeline timeout: wait site %u, block %u, thread %u, parity %u", info[0] & 0xffffu,
+                    info[1], info[2], info[3]);
+    }
+    return SRB_OK;
+}
 
 extern "C" int srb_profile_enable(srb_ctx* ctx, int on) {
     if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");

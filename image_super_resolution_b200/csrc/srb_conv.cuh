@@ -53,6 +53,7 @@ struct ConvParams {
     int flags;
     int cout;                // real output channels (DXN: 3)
     int dbg_swap;            // debug: swap LBO/SBO of the descriptors (diagnostics only)
+    long long* dbg_trace;    // optional per-step clock trace of CTA 0 (tools/gpu_trace.py): [64 steps][8 stamps]
     int dbg_skip;            // bottleneck probes: 1 = no TMA tile loads, 2 = no MMAs, 4 = no global I/O in epilogue
 };
 
@@ -104,6 +105,10 @@ struct ConvGeom {
 };
 
 __device__ __forceinline__ float lrelu(float v, float s) { return v > 0.f ? v : v * s; }
+// trace stamp k of step `it` (CTA 0, first 64 steps); costs one predicated store when enabled, a test otherwise
+__device__ __forceinline__ void trace(const ConvParams& p, int it, int k) {
+    if (p.dbg_trace != nullptr && blockIdx.x == 0 && it < 64) p.dbg_trace[it * 8 + k] = clock64();
+}
 
 template <bool BF16>
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
@@ -130,12 +135,25 @@ __device__ __forceinline__ uint4 ldg_nc16(const void* p) {
     return r;
 }
 
+// warps: 0 halo producer, 1 MMA issuer, 2 residual producer, 3 spare, 4.. epilogue (EPI_SETS x 4 warps)
+constexpr int EPI_SETS = 2;
+constexpr int CONV_THREADS = 128 + 128 * EPI_SETS;
+
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint4 lds_u4(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
+
 template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool BF16>
-__global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap,
+__global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap,
                                                          const __grid_constant__ CUtensorMap tmap_res, const ConvParams p) {
     using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES>;
-    constexpr int NG = NOUT / 8;                 // output granules per pixel
-    constexpr int NGR = NG <= 8 ? NG : 1;        // residual granules kept in registers (residual needs NOUT <= 64)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_w = smem;                                       // WBYTES
@@ -159,7 +177,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
     if (threadIdx.x == 0) {
         for (int s = 0; s < G::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(&tfull[0], 1); mbar_init(&tfull[1], 1);
-        mbar_init(&tempty[0], 4); mbar_init(&tempty[1], 4);
+        mbar_init(&tempty[0], 4 * EPI_SETS); mbar_init(&tempty[1], 4 * EPI_SETS);
         mbar_init(wbar, 1);
         for (int s = 0; s < G::RSLOTS; ++s) { mbar_init(&rfull[s], 1); mbar_init(&rempty[s], 4); }
         fence_mbar_init();
@@ -185,12 +203,13 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         }
         __syncwarp();
         int s = 0; uint32_t ph = 0;
-        int rs = 0; uint32_t rph = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int pit = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++pit) {
             int n = tile / tiles_per_img;
             int r = tile - n * tiles_per_img;
             int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
             mbar_wait(&empty[s], ph ^ 1, 1);
+            if (lane == 0) trace(p, pit, 0);     // halo load issued
             if (elect_one()) {
                 if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
                 else {
@@ -201,22 +220,6 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
             __syncwarp();
             if (++s == G::STAGES) { s = 0; ph ^= 1; }
-            if constexpr (RES) {
-#pragma unroll 1
-                for (int t = 0; t < NT; ++t) {
-                    mbar_wait(&rempty[rs], rph ^ 1, 6);
-                    if (elect_one()) {
-                        if (p.dbg_skip & 1) { mbar_arrive(&rfull[rs]); }
-                        else {
-                            mbar_arrive_expect_tx(&rfull[rs], G::RES_TILE_BYTES);
-                            tma_load_4d(s_res + rs * G::RES_TILE_BYTES, &tmap_res, &rfull[rs],
-                                        (tx * G::SUPER_W + t * G::TW) * 4, ty * G::SUPER_H, p.res_c8_off, n);
-                        }
-                    }
-                    __syncwarp();
-                    if (++rs == G::RSLOTS) { rs = 0; rph ^= 1; }
-                }
-            }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -234,7 +237,9 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             const int b = it & 1;
             const uint32_t bph = (it >> 1) & 1;
             mbar_wait(&tempty[b], bph ^ 1, 3);
+            if (lane == 0) trace(p, it, 1);      // accumulator set free
             mbar_wait(&full[s], ph, 4);
+            if (lane == 0) trace(p, it, 2);      // halo landed, MMA issue starts
             tc_fence_after();
             if (elect_one()) {
                 const uint64_t a_desc = a_desc0 + (uint64_t)(smem_u32(s_a + s * G::STAGE_STRIDE) >> 4);
@@ -282,15 +287,45 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                 umma_commit(&tfull[b]);   // accumulators complete -> epilogue
             }
             __syncwarp();
+            if (lane == 0) trace(p, it, 3);      // MMA issue done
             if (++s == G::STAGES) { s = 0; ph ^= 1; }
         }
-    } else {
-        // ===================== epilogue (warps 2..5) =====================
+    } else if (warp == 2) {
+        // ===================== residual producer (RES): one TMA box per M-tile into the smem ring =====================
+        if constexpr (RES) {
+            int rs = 0; uint32_t rph = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                const int n = tile / tiles_per_img;
+                const int r = tile - n * tiles_per_img;
+                const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
+#pragma unroll 1
+                for (int t = 0; t < NT; ++t) {
+                    mbar_wait(&rempty[rs], rph ^ 1, 6);
+                    if (elect_one()) {
+                        if (p.dbg_skip & 1) { mbar_arrive(&rfull[rs]); }
+                        else {
+                            mbar_arrive_expect_tx(&rfull[rs], G::RES_TILE_BYTES);
+                            tma_load_4d(s_res + rs * G::RES_TILE_BYTES, &tmap_res, &rfull[rs],
+                                        (tx * G::SUPER_W + t * G::TW) * 4, ty * G::SUPER_H, p.res_c8_off, n);
+                        }
+                    }
+                    __syncwarp();
+                    if (++rs == G::RSLOTS) { rs = 0; rph ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue: EPI_SETS sets of 4 warps; set e handles M-tiles e, e+EPI_SETS, ... =====================
+        // (one warp per scheduler cannot hide its own ALU latency; two or more per scheduler can)
         const int lg = warp & 3;                  // TMEM lane group this warp may access
+        const int eset = (warp - 4) >> 2;
         const int L = lg * 32 + lane;             // accumulator row = pixel of the M-tile
         const size_t HW = (size_t)p.H * p.W;
-        const bool has_res = !RES && (p.flags & F_RESIDUAL) != 0 && !(p.dbg_skip & 4);   // register-prefetch path
-        int rs = 0; uint32_t rph = 0;                                                    // smem-ring path (RES)
+        const bool io = !(p.dbg_skip & 4);
+        const bool has_res = (p.flags & F_RESIDUAL) != 0;
+        const bool do_lrelu = (p.flags & F_LRELU) != 0;
+        const uint32_t s_bias_u32 = smem_u32(s_bias);
+        const uint32_t s_res_u32 = smem_u32(s_res);
         int it = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int b = it & 1;
@@ -299,33 +334,35 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             const int r = tile - n * tiles_per_img;
             const int tyi = r / p.tiles_x, txi = r - tyi * p.tiles_x;
             const uint32_t t_addr0 = tmem_base + b * (NT * NOUT) + ((uint32_t)(lg * 32) << 16);
+            if (threadIdx.x == 128) trace(p, it, 4);   // epilogue starts waiting
+            mbar_wait(&tfull[b], bph, 5);
+            if (threadIdx.x == 128) trace(p, it, 5);   // accumulators complete
+            tc_fence_after();
             if constexpr (MODE != MODE_DXN) {
-                // pixel of this thread in M-tile t
-                auto pix_y = [&](int t) { return tyi * G::SUPER_H + (MODE == MODE_STD ? 0 : t * G::TH) + (L >> 3); };
-                auto pix_x = [&](int t) { return txi * G::SUPER_W + (MODE == MODE_STD ? t * G::TW : 0) + (L & 7); };
-                uint4 rq[NGR];
-                auto prefetch = [&](int t, uint4* dst) {
-                    const int y = pix_y(t), x = pix_x(t);
-                    if (y < p.H && x < p.W) {
-                        const uint8_t* rp = reinterpret_cast<const uint8_t*>(p.res) +
-                                            (((size_t)n * p.res_c8_total + p.res_c8_off) * HW + (size_t)y * p.W + x) * 16;
-#pragma unroll
-                        for (int j = 0; j < NGR; ++j)
-                            if (j * 8 < p.cout) dst[j] = ldg_nc16(rp + (size_t)j * HW * 16);
-                    }
-                };
-                if (has_res) prefetch(0, rq);
-                mbar_wait(&tfull[b], bph, 5);
-                tc_fence_after();
-#pragma unroll
+#pragma unroll 1
                 for (int t = 0; t < NT; ++t) {
-                    uint4 rn[NGR];
-                    if (has_res && t + 1 < NT) prefetch(t + 1, rn);
-                    if constexpr (RES) mbar_wait(&rfull[rs], rph, 7);
-                    const int y = pix_y(t), x = pix_x(t);
-                    const bool valid = (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
+                    if ((t % EPI_SETS) != eset) {
+                        // not this set's tile — but still observe its residual fill: parity waits are only
+                        // sound if no warp ever falls two phases behind a ring slot
+                        if constexpr (RES) {
+                            const int c = it * NT + t;
+                            mbar_wait(&rfull[c % G::RSLOTS], (uint32_t)((c / G::RSLOTS) & 1), 8);
+                        }
+                        continue;
+                    }
+                    const int y = tyi * G::SUPER_H + (MODE == MODE_STD ? 0 : t * G::TH) + (L >> 3);
+                    const int x = txi * G::SUPER_W + (MODE == MODE_STD ? t * G::TW : 0) + (L & 7);
+                    const bool valid = (y < p.H) && (x < p.W) && io;
                     const size_t pix = (size_t)y * p.W + x;
-#pragma unroll
+                    uint32_t rslot_addr = 0;
+                    int rslot = 0;
+                    if constexpr (RES) {
+                        const int c = it * NT + t;
+                        rslot = c % G::RSLOTS;
+                        mbar_wait(&rfull[rslot], (uint32_t)((c / G::RSLOTS) & 1), 7);
+                        rslot_addr = s_res_u32 + rslot * G::RES_TILE_BYTES + L * 16;
+                    }
+#pragma unroll 1
                     for (int c0 = 0; c0 < NOUT; c0 += 32) {
                         uint32_t rr[32];
                         tmem_ld32(t_addr0 + t * NOUT + c0, rr);
@@ -337,17 +374,21 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                                 const int gj = (c0 >> 3) + j;
                                 if (gj * 8 >= p.cout) break;
                                 float v[8];
+                                const float4 b0 = lds_f4(s_bias_u32 + (c0 + 8 * j) * 4);
+                                const float4 b1 = lds_f4(s_bias_u32 + (c0 + 8 * j + 4) * 4);
+                                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) {
-                                    float tt = __uint_as_float(rr[8 * j + i]) + s_bias[c0 + 8 * j + i];
-                                    if (p.flags & F_LRELU) tt = lrelu(tt, p.slope);
+                                    float tt = __uint_as_float(rr[8 * j + i]) + bb[i];
+                                    if (do_lrelu) tt = fmaxf(tt, tt * p.slope);   // LeakyReLU for 0 <= slope <= 1
                                     v[i] = tt * p.out_scale;
                                 }
                                 if (valid) {
                                     if (RES || has_res) {
                                         uint4 q;
-                                        if constexpr (RES) q = *reinterpret_cast<const uint4*>(s_res + rs * G::RES_TILE_BYTES + (gj * 128 + L) * 16);
-                                        else q = rq[gj < NGR ? gj : 0];
+                                        if constexpr (RES) q = lds_u4(rslot_addr + gj * 2048);
+                                        else q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.res) +
+                                                          (((size_t)n * p.res_c8_total + p.res_c8_off + gj) * HW + pix) * 16);
                                         const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
@@ -373,7 +414,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
 #pragma unroll
                                 for (int c = 0; c < 8; ++c) {
                                     float tt = __uint_as_float(rr[4 * c + ij]) + s_bias[c0 + 4 * c + ij];
-                                    if (p.flags & F_LRELU) tt = lrelu(tt, p.slope);
+                                    if (do_lrelu) tt = fmaxf(tt, tt * p.slope);
                                     v[c] = tt * p.out_scale;
                                 }
                                 if (valid) {
@@ -387,23 +428,16 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
                             }
                         }
                     }
-                    if (has_res && t + 1 < NT) {
-#pragma unroll
-                        for (int j = 0; j < NGR; ++j) rq[j] = rn[j];
-                    }
                     if constexpr (RES) {
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&rempty[rs]);
-                        if (++rs == G::RSLOTS) { rs = 0; rph ^= 1; }
+                        if (lane == 0) mbar_arrive(&rempty[rslot]);
                     }
                 }
             } else {
                 // DXN: column dx*3+co of row (y, x') is the contribution of input column x' to output
                 // (y, x' - dx + 4); gather the 9 horizontally shifted partials with warp shuffles.
-                mbar_wait(&tfull[b], bph, 5);
-                tc_fence_after();
-#pragma unroll
-                for (int t = 0; t < NT; ++t) {
+#pragma unroll 1
+                for (int t = eset; t < NT; t += EPI_SETS) {
                     uint32_t rr[32];
                     tmem_ld32(t_addr0 + t * NOUT, rr);
                     tmem_ld_wait();
@@ -416,7 +450,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
 #pragma unroll
                         for (int co = 0; co < 3; ++co)
                             acc[co] += __shfl_sync(0xffffffffu, __uint_as_float(rr[dx * 3 + co]), (lane + dx - 4) & 31);
-                    const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W) && !(p.dbg_skip & 4);
+                    const bool valid = (t16 >= 4) && (t16 < 12) && (y < p.H) && (x < p.W) && io;
                     if (valid) {
 #pragma unroll
                         for (int co = 0; co < 3; ++co) {
@@ -437,6 +471,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
             tc_fence_before();
             __syncwarp();
+            if (threadIdx.x == 128) trace(p, it, 6);       // epilogue done (set 0, lane group 0)
             if (lane == 0) mbar_arrive(&tempty[b]);
         }
     }

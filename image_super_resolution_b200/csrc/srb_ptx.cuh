@@ -14,6 +14,7 @@ namespace srb {
 // spin budget the kernel records where it was stuck and traps.
 // ------------------------------------------------------------------------------------------
 __device__ unsigned int g_srb_timeout_info[4];
+__device__ volatile unsigned int g_srb_abort;   // set by the first wait that runs out of budget; every later wait bails out
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -46,18 +47,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// tag identifies the wait site in g_srb_timeout_info when the budget runs out
+// tag identifies the wait site.  On a protocol bug the kernel does not hang or trap: the first wait to
+// exceed its budget records where it was, raises g_srb_abort, and every wait returns at once so the
+// launch drains (with garbage results); the host reads the flag (srb_check_device) and reports it.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag) {
     if (mbar_try_wait(bar, parity)) return;
     long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > (1ll << 31)) {  // ~1 s at 2 GHz
-            g_srb_timeout_info[0] = 0xdead0000u | tag;
-            g_srb_timeout_info[1] = blockIdx.x;
-            g_srb_timeout_info[2] = threadIdx.x;
-            g_srb_timeout_info[3] = parity;
-            __threadfence_system();
-            __trap();
+        if (g_srb_abort) return;
+        if (clock64() - t0 > (1ll << 28)) {  // ~0.14 s at 2 GHz
+            if (atomicExch((unsigned int*)&g_srb_abort, 1u) == 0u) {
+                g_srb_timeout_info[0] = 0xdead0000u | tag;
+                g_srb_timeout_info[1] = blockIdx.x;
+                g_srb_timeout_info[2] = threadIdx.x;
+                g_srb_timeout_info[3] = parity;
+            }
+            __threadfence();
+            return;
         }
     }
 }

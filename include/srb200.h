@@ -100,6 +100,9 @@ int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host
 int srb_model_pt_launches(void);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
+/* cudaDeviceSynchronize + report a kernel-side pipeline timeout (kernels never hang: bounded waits) */
+int srb_check_device(srb_ctx* ctx);
+int srb_debug_trace(srb_ctx* ctx, void* dev_buf512_int64);  /* per-step clock stamps of CTA 0, diagnostics */
 int srb_profile_enable(srb_ctx* ctx, int on);
 int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
 /* measurement only: cycles for `iters` rounds of `racc` interleaved M=128(64) x n x 16 tcgen05.mma;

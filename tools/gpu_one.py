@@ -19,7 +19,9 @@ if cout == 3:
 else:
     pout = cout // 8; y = torch.zeros((N, pout, H, W, 8), dtype=torch.float16, device=dev); flags = 0 if residual else ops.F_LRELU
 res = torch.randn((N, pout, H, W, 8), device=dev).half() if residual else None
+ctx.debug_set(2, int(os.environ.get('SRB_SKIP', '0')))
+N = int(os.environ.get('SRB_N', N))
 for _ in range(iters):
     ops.conv2d_fwd(pc, x, pin, 0, y, pout, 0, N, H, W, residual=res, res_planes=pout, flags=flags, slope=0.2)
-torch.cuda.synchronize()
+ctx.check_device()
 print("ok")
