@@ -1,0 +1,53 @@
+"""GPU tests of the rs.py drop-in (tile modes, frame path)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WEIGHTS = os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")
+
+
+@pytest.fixture(scope="module")
+def model():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    import image_super_resolution_b200 as srb
+    return srb.load(WEIGHTS).to("cuda:0").eval()
+
+
+def test_reference_tile_mode_reproduces_rs_py_seams(model, golden_dir):
+    from image_super_resolution_b200 import rs
+    g = np.load(os.path.join(golden_dir, "rs_tiling_golden.npz"))
+    img = torch.from_numpy(g["image"])
+    out = rs.upscale_image(model, img, 96, "reference")
+    d = (out.int() - torch.from_numpy(g["rs_window96"]).int()).abs()
+    assert d.max().item() <= 2 and (d == 0).float().mean().item() >= 0.97
+    # and it is NOT the whole-image result: the seams of the reference are reproduced, not repaired
+    dw = (out.int() - torch.from_numpy(g["whole"]).int()).abs()
+    assert dw.max().item() > 10
+
+
+def test_halo_tile_mode_equals_whole_image(model, golden_dir):
+    from image_super_resolution_b200 import rs
+    g = np.load(os.path.join(golden_dir, "rs_tiling_golden.npz"))
+    img = torch.from_numpy(g["image"])
+    whole = rs.upscale_image(model, img, 96, "whole")
+    halo = rs.upscale_image(model, img, 96, "halo", tile=(64, 80))
+    assert torch.equal(whole, halo)                       # exact, SURVEY F6
+    d = (whole.int() - torch.from_numpy(g["whole"]).int()).abs()
+    assert d.max().item() <= 2
+
+
+def test_sharded_model_and_frame_path(model):
+    from image_super_resolution_b200 import rs
+    sm = rs.ShardedModel(model, devices=[0])
+    g = torch.Generator().manual_seed(3)
+    batches = [torch.randint(0, 256, (2, 3, 40, 48), dtype=torch.uint8, generator=g) for _ in range(3)]
+    sink = rs.ByteSink(keep=True)
+    n = rs.upscale_frames(sm, batches, sink)
+    assert n == 6 and sink.bytes == 6 * 40 * 48 * 3
+    want = model(batches[1].cuda())[1].flip(0).permute(1, 2, 0).cpu().numpy()   # frame 3: BGR, HWC
+    assert np.array_equal(sink.kept[3], want)
