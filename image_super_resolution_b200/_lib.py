@@ -29,6 +29,7 @@ SIGNATURES = {
     "srb_pack_conv": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, C.POINTER(_vp)]),
     "srb_free_weights": (None, [_vp]),
     "srb_conv2d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _f, _f, _f, _i, _i, _i, _i, _vp]),
+    "srb_conv2d_fwd_res2": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _f, _vp, _i, _i, _f, _f, _f, _i, _i, _i, _i, _vp]),
     "srb_u8nchw_to_c8": (_i, [_vp, _vp, _vp, _fp, _fp, _f, _i, _i, _i, _i, _vp]),
     "srb_f32nchw_to_c8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "srb_c8_to_f32nchw": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -67,6 +67,7 @@ struct srb_ctx {
 struct srb_weights {
     int cout = 0, cin = 0, k = 0, dtype = 0;
     int mode = 0, c8in = 0, nout = 0, ksteps = 0;
+    int kblocks = 0;   // > 0: weight-streaming layout, blocks of 4 planes (32 channels)
     uint8_t* d_pack = nullptr;
     float* d_bias = nullptr;
     size_t pack_bytes = 0;
@@ -165,7 +166,15 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
     std::vector<uint16_t> pack((size_t)ksteps * step_elems, 0);
     std::vector<float> hbias(nout, 0.f);
     int ks = 0;
-    if (mode == MODE_STD) {
+    const int kblocks = (mode == MODE_STD && c8in > 8) ? c8in / 4 : 0;
+    if (kblocks && (c8in % 4)) return fail(SRB_ENOSUP, "srb_pack_conv: cin=%d must be a multiple of 32 above 64", cin);
+    if (kblocks) {
+        // weight-streaming order: [K block of 32 channels][dy][dx][2 K-steps]
+        for (int kb = 0; kb < kblocks; ++kb) for (int dy = 0; dy < 3; ++dy) for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < 2; ++c2, ++ks)
+            for (int g = 0; g < 2; ++g) for (int n = 0; n < cout; ++n) for (int j = 0; j < 8; ++j)
+                pack[ks * step_elems + ((size_t)g * nout + n) * 8 + j] = f2h(W(n, (kb * 4 + 2 * c2 + g) * 8 + j, dy, dx), dtype);
+        for (int o = 0; o < cout; ++o) hbias[o] = fb[o];
+    } else if (mode == MODE_STD) {
         for (int dy = 0; dy < 3; ++dy) for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < c8in / 2; ++c2, ++ks)
             for (int g = 0; g < 2; ++g) for (int n = 0; n < cout; ++n) for (int j = 0; j < 8; ++j)
                 pack[ks * step_elems + ((size_t)g * nout + n) * 8 + j] = f2h(W(n, (2 * c2 + g) * 8 + j, dy, dx), dtype);
@@ -188,7 +197,7 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
 
     srb_weights* sw = new srb_weights();
     sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
-    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps;
+    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
     sw->pack_bytes = pack.size() * 2;
     cudaSetDevice(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
@@ -211,10 +220,11 @@ extern "C" void srb_free_weights(srb_weights* w) {
 // ------------------------------------------------------------------------------------------
 // conv dispatch
 // ------------------------------------------------------------------------------------------
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false, bool WS = false>
 static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, ConvParams p, cudaStream_t st) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES>;
-    if (w->ksteps != G::KSTEPS || (size_t)G::WBYTES != w->pack_bytes)
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES, WS>;
+    p.kblocks = WS ? w->kblocks : 1;
+    if (w->ksteps != G::KSTEPS * p.kblocks || (size_t)G::WBLK_BYTES * p.kblocks != w->pack_bytes)
         return fail(SRB_EINVAL, "launch_conv: packed weights do not match the kernel geometry");
     p.tiles_x = (p.W + G::SUPER_W - 1) / G::SUPER_W;
     p.tiles_y = (p.H + G::SUPER_H - 1) / G::SUPER_H;
@@ -250,11 +260,11 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     p.dbg_skip = ctx->dbg_skip;
     p.dbg_trace = ctx->dbg_trace;
     if (w->dtype == SRB_DT_BF16) {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, true>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, true>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     } else {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, false>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, false>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     }
@@ -266,6 +276,14 @@ extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x,
                               int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
                               float res_scale, float out_scale, float lrelu_slope, int flags, int N, int H, int W,
                               srb_stream_t stream) {
+    return srb_conv2d_fwd_res2(ctx, w, x, x_c8_total, x_c8_off, y, y_c8_total, y_c8_off, residual, res_c8_total, res_c8_off,
+                               res_scale, nullptr, 0, 0, 0.f, out_scale, lrelu_slope, flags, N, H, W, stream);
+}
+
+extern "C" int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, int x_c8_off, void* y,
+                                   int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
+                                   float res_scale, const void* res2, int res2_c8_total, int res2_c8_off, float res2_scale,
+                                   float out_scale, float lrelu_slope, int flags, int N, int H, int W, srb_stream_t stream) {
     if (!ctx || !w || !x || !y) return fail(SRB_EINVAL, "srb_conv2d_fwd: NULL argument");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv2d_fwd: empty shape %dx%dx%d", N, H, W);
     if (((uintptr_t)x & 15) || ((uintptr_t)y & 15 && w->mode != MODE_DXN) || ((uintptr_t)residual & 15))
@@ -280,6 +298,8 @@ extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x,
     p.y = y; p.y_c8_total = y_c8_total; p.y_c8_off = y_c8_off;
     p.res = residual; p.res_c8_total = res_c8_total; p.res_c8_off = res_c8_off;
     p.res_scale = res_scale; p.out_scale = out_scale; p.slope = lrelu_slope;
+    p.res2 = res2; p.res2_c8_total = res2_c8_total; p.res2_c8_off = res2_c8_off; p.res2_scale = res2_scale;
+    if (res2 && (((uintptr_t)res2 & 15) || !(flags & SRB_F_RESIDUAL))) return fail(SRB_EINVAL, "srb_conv2d_fwd: res2 needs SRB_F_RESIDUAL and 16-byte alignment");
     p.flags = flags; p.cout = w->cout;
     cudaStream_t st = (cudaStream_t)stream;
     if (w->mode == MODE_DXN) {
@@ -299,10 +319,17 @@ extern "C" int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x,
         if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
     }
-#define SRB_STD(C8, NO, NTT) if (w->c8in == C8 && w->nout == NO) { \
+#define SRB_STD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
     SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3)
+    if (w->kblocks) {   // dense-block convs (Cin = 96..192): K blocks of 32 channels, filter streamed with the halo
+        if (w->nout == 32) return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
+        if (w->nout == 64) {
+            if ((flags & SRB_F_RESIDUAL) && w->cout == 64) return launch_conv<4, 64, 3, 3, MODE_STD, 4, true, true>(ctx, w, x, x_c8_total, p, st);
+            return launch_conv<4, 64, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
+        }
+    }
 #undef SRB_STD
     return fail(SRB_ENOSUP, "srb_conv2d_fwd: no 3x3 kernel for cin=%d cout=%d", w->cin, w->cout);
 }

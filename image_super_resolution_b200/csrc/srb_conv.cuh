@@ -49,7 +49,10 @@ struct ConvParams {
     int y_c8_total, y_c8_off;
     const void* res;         // C8-plane residual, same H, W
     int res_c8_total, res_c8_off;
-    float res_scale, out_scale, slope;
+    const void* res2;        // optional second residual (RRDB outer skip), C8 planes, read with plain loads
+    int res2_c8_total, res2_c8_off;
+    float res_scale, res2_scale, out_scale, slope;
+    int kblocks;             // WS kernels: number of K blocks (C8IN planes each) streamed per super-tile
     int flags;
     int cout;                // real output channels (DXN: 3)
     int dbg_swap;            // debug: swap LBO/SBO of the descriptors (diagnostics only)
@@ -58,7 +61,9 @@ struct ConvParams {
 };
 
 // NT M-tiles per super-tile: STD tiles sit side by side in x; PAIRDX / DXN tiles are stacked in y.
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false>
+// WS (weight streaming): C8IN is the planes of ONE K block; every pipeline stage carries the block's halo box
+// and its slice of the filter, so Cin is unbounded (dense-block convs, 96..192 channels).
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false, bool WS = false>
 struct ConvGeom {
     static constexpr int TW = 8;                                  // output tile width
     static constexpr int TH = (MODE == MODE_DXN) ? 8 : 16;        // output tile height
@@ -71,12 +76,14 @@ struct ConvGeom {
     static constexpr int PLANE = HALO_H * ROWP;                   // bytes between channel planes
     static constexpr int TOFF = (MODE == MODE_STD) ? TW * 16 : TH * ROWP;  // A-operand offset of M-tile t
     static constexpr int STAGE_BYTES = C8IN * PLANE;              // one TMA box
-    static constexpr int STAGE_STRIDE = (STAGE_BYTES + 1023) / 1024 * 1024;
+    static constexpr int A_STRIDE = (STAGE_BYTES + 1023) / 1024 * 1024;
     static constexpr int KSTEPS = (MODE == MODE_STD)      ? KH * KW * (C8IN / 2)
                                   : (MODE == MODE_PAIRDX) ? KH * ((KW + 1) / 2)
                                                           : KH * (C8IN / 2);
     static constexpr int WSTEP_BYTES = 2 * NOUT * 16;             // one K=16 slice of B
-    static constexpr int WBYTES = KSTEPS * WSTEP_BYTES;
+    static constexpr int WBLK_BYTES = KSTEPS * WSTEP_BYTES;      // filter slice of one K block
+    static constexpr int WBYTES = WS ? 0 : WBLK_BYTES;           // resident filter (non-WS)
+    static constexpr int STAGE_STRIDE = A_STRIDE + (WS ? (WBLK_BYTES + 1023) / 1024 * 1024 : 0);
     static constexpr int ACC_COLS = 2 * NT * NOUT;                // two accumulator sets
     static constexpr int TMEM_COLS = (ACC_COLS <= 32) ? 32 : (ACC_COLS <= 64) ? 64 : (ACC_COLS <= 128) ? 128
                                      : (ACC_COLS <= 256) ? 256 : 512;
@@ -102,6 +109,7 @@ struct ConvGeom {
     static_assert(ACC_COLS <= 512, "TMEM holds 512 columns");
     static_assert(HALO_W * 4 <= 256 && HALO_H <= 256, "TMA box limits (tensor map is typed as 32-bit words: 4 per granule)");
     static_assert(STAGES >= 2, "needs two halo stages in shared memory");
+    static_assert(!WS || MODE == MODE_STD, "weight streaming is implemented for the 3x3 STD mode");
 };
 
 __device__ __forceinline__ float lrelu(float v, float s) { return v > 0.f ? v : v * s; }
@@ -150,10 +158,11 @@ __device__ __forceinline__ uint4 lds_u4(uint32_t a) {
     return r;
 }
 
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool BF16>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool WS, bool BF16>
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap,
                                                          const __grid_constant__ CUtensorMap tmap_res, const ConvParams p) {
-    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES>;
+    using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES, WS>;
+    const int kblocks = WS ? p.kblocks : 1;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_w = smem;                                       // WBYTES
@@ -194,7 +203,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 
     if (warp == 0) {
         // ===================== TMA producer (warp-uniform loop, one elected lane issues) =====================
-        if (elect_one()) {
+        if (!WS && elect_one()) {
             mbar_arrive_expect_tx(wbar, G::WBYTES);
             for (int off = 0; off < G::WBYTES; off += 16384) {
                 int n = G::WBYTES - off < 16384 ? G::WBYTES - off : 16384;
@@ -208,18 +217,29 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
             int n = tile / tiles_per_img;
             int r = tile - n * tiles_per_img;
             int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-            mbar_wait(&empty[s], ph ^ 1, 1);
-            if (lane == 0) trace(p, pit, 0);     // halo load issued
-            if (elect_one()) {
-                if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
-                else {
-                    mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES);
-                    tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX) * 4,
-                                ty * G::SUPER_H - G::PADY, p.x_c8_off, n);
+#pragma unroll 1
+            for (int kb = 0; kb < kblocks; ++kb) {
+                mbar_wait(&empty[s], ph ^ 1, 1);
+                if (lane == 0 && kb == 0) trace(p, pit, 0);     // halo load issued
+                if (elect_one()) {
+                    if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
+                    else {
+                        mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES + (WS ? G::WBLK_BYTES : 0));
+                        tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX) * 4,
+                                    ty * G::SUPER_H - G::PADY, p.x_c8_off + kb * C8IN, n);
+                        if constexpr (WS) {
+                            uint8_t* wdst = s_a + s * G::STAGE_STRIDE + G::A_STRIDE;
+                            const uint8_t* wsrc = p.wpack + (size_t)kb * G::WBLK_BYTES;
+                            for (int off = 0; off < G::WBLK_BYTES; off += 16384) {
+                                int nb = G::WBLK_BYTES - off < 16384 ? G::WBLK_BYTES - off : 16384;
+                                bulk_load_1d(wdst + off, wsrc + off, nb, &full[s]);
+                            }
+                        }
+                    }
                 }
+                __syncwarp();
+                if (++s == G::STAGES) { s = 0; ph ^= 1; }
             }
-            __syncwarp();
-            if (++s == G::STAGES) { s = 0; ph ^= 1; }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -231,18 +251,21 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
         // descriptors with a zero start address; the 14-bit (addr >> 4) field is added per MMA
         const uint64_t a_desc0 = umma_desc_nosw(0, a_lbo, a_sbo);
         const uint64_t b_desc0 = umma_desc_nosw(smem_u32(s_w), b_lbo, b_sbo);
-        mbar_wait(wbar, 0, 2);
+        if (!WS) mbar_wait(wbar, 0, 2);
         int s = 0; uint32_t ph = 0; int it = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int b = it & 1;
             const uint32_t bph = (it >> 1) & 1;
             mbar_wait(&tempty[b], bph ^ 1, 3);
             if (lane == 0) trace(p, it, 1);      // accumulator set free
+#pragma unroll 1
+            for (int kb = 0; kb < kblocks; ++kb) {
             mbar_wait(&full[s], ph, 4);
-            if (lane == 0) trace(p, it, 2);      // halo landed, MMA issue starts
+            if (lane == 0 && kb == 0) trace(p, it, 2);      // halo landed, MMA issue starts
             tc_fence_after();
             if (elect_one()) {
                 const uint64_t a_desc = a_desc0 + (uint64_t)(smem_u32(s_a + s * G::STAGE_STRIDE) >> 4);
+                const uint64_t b_desc_s = WS ? umma_desc_nosw(smem_u32(s_a + s * G::STAGE_STRIDE + G::A_STRIDE), b_lbo, b_sbo) : b_desc0;
                 const uint32_t d_tmem = tmem_base + b * (NT * NOUT);
                 if (!(p.dbg_skip & 2)) {
                     int ks = 0;
@@ -254,10 +277,10 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 #pragma unroll
                                 for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
                                     const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP + dx * 16) >> 4;
-                                    const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                    const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
 #pragma unroll
                                     for (int t = 0; t < NT; ++t)
-                                        umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
+                                        umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, (ks | kb) != 0);
                                 }
                     } else if constexpr (MODE == MODE_PAIRDX) {
 #pragma unroll 1
@@ -265,7 +288,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 #pragma unroll
                             for (int dxp = 0; dxp < (KW + 1) / 2; ++dxp, ++ks) {
                                 const uint32_t ao = (dy * G::ROWP + 2 * dxp * 16) >> 4;
-                                const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
@@ -276,19 +299,20 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 #pragma unroll
                             for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
                                 const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP) >> 4;
-                                const uint64_t bd = b_desc0 + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
                             }
                     }
                 }
-                umma_commit(&empty[s]);   // halo stage may be refilled once these MMAs have read it
-                umma_commit(&tfull[b]);   // accumulators complete -> epilogue
+                umma_commit(&empty[s]);                          // stage may be refilled once these MMAs have read it
+                if (kb == kblocks - 1) umma_commit(&tfull[b]);   // accumulators complete -> epilogue
             }
             __syncwarp();
-            if (lane == 0) trace(p, it, 3);      // MMA issue done
             if (++s == G::STAGES) { s = 0; ph ^= 1; }
+            }
+            if (lane == 0) trace(p, it, 3);      // MMA issue done
         }
     } else if (warp == 2) {
         // ===================== residual producer (RES): one TMA box per M-tile into the smem ring =====================
@@ -395,6 +419,17 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                             float2 f = unpack2<BF16>(qq[i]);
                                             v[2 * i] += p.res_scale * f.x;
                                             v[2 * i + 1] += p.res_scale * f.y;
+                                        }
+                                    }
+                                    if (p.res2 != nullptr) {
+                                        const uint4 q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.res2) +
+                                                                 (((size_t)n * p.res2_c8_total + p.res2_c8_off + gj) * HW + pix) * 16);
+                                        const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                                        for (int i = 0; i < 4; ++i) {
+                                            float2 f = unpack2<BF16>(qq[i]);
+                                            v[2 * i] += p.res2_scale * f.x;
+                                            v[2 * i + 1] += p.res2_scale * f.y;
                                         }
                                     }
                                     uint4 o;

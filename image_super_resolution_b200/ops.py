@@ -67,15 +67,19 @@ class PackedConv:
 
 def conv2d_fwd(pc: PackedConv, x: torch.Tensor, x_planes: int, x_off: int, y: torch.Tensor, y_planes: int, y_off: int,
                N: int, H: int, W: int, residual: torch.Tensor | None = None, res_planes: int = 0, res_off: int = 0,
-               res_scale: float = 1.0, out_scale: float = 1.0, slope: float = 0.0, flags: int = 0):
+               res_scale: float = 1.0, out_scale: float = 1.0, slope: float = 0.0, flags: int = 0,
+               res2: torch.Tensor | None = None, res2_planes: int = 0, res2_off: int = 0, res2_scale: float = 1.0):
     _require_cuda(x, "x")
     _require_cuda(y, "y")
     if residual is not None:
         _require_cuda(residual, "residual")
         flags |= F_RESIDUAL
-    check(lib().srb_conv2d_fwd(pc.ctx.handle, pc.handle, x.data_ptr(), x_planes, x_off, y.data_ptr(), y_planes, y_off,
-                               None if residual is None else residual.data_ptr(), res_planes, res_off, res_scale,
-                               out_scale, slope, flags, N, H, W, _stream_ptr(x.device)), "srb_conv2d_fwd")
+    if res2 is not None:
+        _require_cuda(res2, "res2")
+    check(lib().srb_conv2d_fwd_res2(pc.ctx.handle, pc.handle, x.data_ptr(), x_planes, x_off, y.data_ptr(), y_planes, y_off,
+                                    None if residual is None else residual.data_ptr(), res_planes, res_off, res_scale,
+                                    None if res2 is None else res2.data_ptr(), res2_planes, res2_off, res2_scale,
+                                    out_scale, slope, flags, N, H, W, _stream_ptr(x.device)), "srb_conv2d_fwd")
 
 
 def c8_empty(N: int, planes: int, H: int, W: int, dtype, device) -> torch.Tensor:

@@ -58,7 +58,8 @@ int srb_debug_set(srb_ctx* ctx, int key, int value);
 /* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for
  * none), convert to dtype and lay the filter out as the UMMA B operand.  w is fp32 OIHW on the HOST.
  * Replaces Conv.fuseforward / ConvWithoutBN._forward_impl weight handling (utils/models.py:97-106,191-196).
- * Supported: (cin=3,k=9) head; (cin%16==0, k=3); (cout=3, cin%16==0, k=9) tail. */
+ * Supported: (cin=3,k=9) head; k=3 with cin in {32,64} (filter resident in shared memory) or cin%32==0 above 64
+ * (filter streamed in 32-channel K blocks); (cout=3, cin=64, k=9) tail. */
 int srb_pack_conv(srb_ctx* ctx, const float* w_oihw, const float* bias, const float* bn4, float bn_eps,
                   int cout, int cin, int k, int dtype, srb_weights** out);
 void srb_free_weights(srb_weights* w);
@@ -71,6 +72,13 @@ int srb_conv2d_fwd(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_t
                    int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
                    float res_scale, float out_scale, float lrelu_slope, int flags, int N, int H, int W,
                    srb_stream_t stream);
+
+/* Same with a second residual: y = out_scale*act(conv+b) + res_scale*residual + res2_scale*res2 — the last conv of
+ * the third RDB of an RRDB carries both the RDB skip and the RRDB skip (utils/models.py:271 and :317). */
+int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, int x_c8_off, void* y,
+                        int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
+                        float res_scale, const void* res2, int res2_c8_total, int res2_c8_off, float res2_scale,
+                        float out_scale, float lrelu_slope, int flags, int N, int H, int W, srb_stream_t stream);
 
 /* Normalize.forward (utils/datasets.py:65-71, uint8 branch baked into model.pt):
  * uint8 NCHW [N,3,H,W] -> ((x/255)-mean)/std as one C8 plane (channels 3..7 zero). */

@@ -95,6 +95,65 @@ def test_conv3x3_bf16(ctx, dev):
     _assert_close(out, ref, "conv3x3 bf16", dtype="bf16")
 
 
+@pytest.mark.parametrize("cin,cout", [(96, 32), (128, 32), (160, 32), (192, 64)])
+def test_conv3x3_wide_k_weight_streaming(ctx, dev, cin, cout):
+    """Dense-block convs (RDB.forward, utils/models.py:265-271): Cin 96..192 read as a plane slice of a 192-channel
+    buffer, written into another slice (free torch.cat), K streamed in 32-channel blocks."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(cin)
+    N, H, W = 2, 40, 72
+    w = torch.randn(cout, cin, 3, 3, generator=g) / np.sqrt(cin * 9)
+    b = torch.randn(cout, generator=g) * 0.1
+    x = torch.randn(N, 192, H, W, generator=g)
+    ref = F.leaky_relu(F.conv2d(x[:, :cin].half().float(), w.half().float(), b, padding=1), 0.01)
+    pc = ops.PackedConv(ctx, w, b)
+    xc = ops.nchw_to_c8(x.to(dev))                              # 24 planes
+    y = torch.zeros((N, 24, H, W, 8), dtype=torch.float16, device=dev)
+    off = 24 - cout // 8
+    ops.conv2d_fwd(pc, xc, 24, 0, y, 24, off, N, H, W, slope=0.01, flags=ops.F_LRELU)
+    out = ops.c8_to_nchw(y, cout, off=off).cpu()
+    _assert_close(out, ref, f"wide conv {cin}->{cout}")
+    assert torch.count_nonzero(y[:, :off]) == 0               # nothing outside the output slice was touched
+
+
+def test_conv3x3_two_residuals_rrdb_tail(ctx, dev):
+    """Last conv of the 3rd RDB of an RRDB: 0.2*(0.2*conv + rdb_in) + rrdb_in  (utils/models.py:271,317)."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(77)
+    N, H, W = 1, 33, 50
+    w = torch.randn(64, 192, 3, 3, generator=g) / np.sqrt(192 * 9)
+    b = torch.randn(64, generator=g) * 0.1
+    x = torch.randn(N, 192, H, W, generator=g)
+    r2 = torch.randn(N, 64, H, W, generator=g)
+    conv = F.conv2d(x.half().float(), w.half().float(), b, padding=1)
+    ref = 0.04 * conv + 0.2 * x[:, :64].half().float() + r2.half().float()
+    pc = ops.PackedConv(ctx, w, b)
+    xc = ops.nchw_to_c8(x.to(dev))
+    r2c = ops.nchw_to_c8(r2.to(dev))
+    y = torch.zeros((N, 8, H, W, 8), dtype=torch.float16, device=dev)
+    ops.conv2d_fwd(pc, xc, 24, 0, y, 8, 0, N, H, W, residual=xc, res_planes=24, res_off=0, res_scale=0.2, out_scale=0.04,
+                   res2=r2c, res2_planes=8, res2_off=0, res2_scale=1.0)
+    _assert_close(ops.c8_to_nchw(y, 64).cpu(), ref, "rrdb tail conv with two residuals")
+
+
+def test_scaler_conv_pixelshuffle_folded(ctx, dev):
+    """Scaler (utils/models.py:572-589): conv 64->256, PixelShuffle(2), LeakyReLU(0.01) — the shuffle is store
+    addressing; the 256 output channels run as four 64-channel launches writing two output planes each."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    N, H, W = 2, 24, 40
+    w = torch.randn(256, 64, 3, 3, generator=g) / 24.0
+    b = torch.randn(256, generator=g) * 0.1
+    x = torch.randn(N, 64, H, W, generator=g)
+    ref = F.leaky_relu(F.pixel_shuffle(F.conv2d(x.half().float(), w.half().float(), b, padding=1), 2), 0.01)
+    xc = ops.nchw_to_c8(x.to(dev))
+    y = torch.zeros((N, 8, 2 * H, 2 * W, 8), dtype=torch.float16, device=dev)
+    for s in range(4):
+        pc = ops.PackedConv(ctx, w[64 * s:64 * s + 64], b[64 * s:64 * s + 64])
+        ops.conv2d_fwd(pc, xc, 8, 0, y, 8, 2 * s, N, H, W, slope=0.01, flags=ops.F_LRELU | ops.F_PIXSHUF2)
+    _assert_close(ops.c8_to_nchw(y, 64).cpu(), ref, "scaler conv + pixelshuffle")
+
+
 def test_conv9x9_head(ctx, dev):
     from image_super_resolution_b200 import ops
     out, ref = _conv_case(ctx, dev, 64, 3, 9, 2, 33, 21, flags=ops.F_LRELU, seed=7)
