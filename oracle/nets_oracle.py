@@ -1,0 +1,60 @@
+"""ORACLE (test infrastructure) — CPU fp32 functional restatement of the class-defined SR nets.
+
+Restates, from a plain state_dict, the forward of the reference's `EResNet` / `ResNet`
+(utils/models.py:592-650): conv0 9x9 + LeakyReLU -> num_block x RRDB (3 x RDB, utils/models.py:245-271,298-317)
+-> conv1 3x3 + long skip -> (scale//2) x Scaler (conv 64->256, PixelShuffle(2), LeakyReLU(0.01); :572-589)
+-> conv2 9x9 + tanh.  `ResNet` differs by Conv (bias-free conv + BatchNorm, eval mode = running statistics,
+:75-101) inside the RDBs / conv1 and by LeakyReLU(0.2) after conv0 (:596 vs :625).
+Pinned by tests/golden/nets_golden.npz: outputs of the reference classes themselves (tools/make_golden.py).
+"""
+import torch
+import torch.nn.functional as F
+
+
+def _conv(x, sd, prefix, pad):
+    w = sd[prefix + ".conv.weight"]
+    b = sd.get(prefix + ".conv.bias")
+    y = F.conv2d(x, w, b, padding=pad)
+    if prefix + ".bn.weight" in sd:  # Conv with BatchNorm in eval mode (utils/models.py:97-98)
+        y = F.batch_norm(y, sd[prefix + ".bn.running_mean"], sd[prefix + ".bn.running_var"], sd[prefix + ".bn.weight"],
+                         sd[prefix + ".bn.bias"], False, 0.0, 1e-5)
+    return y
+
+
+def rdb(x, sd, prefix, add_rate, slope=0.01):
+    """RDB.forward, utils/models.py:265-271."""
+    feats = [x]
+    for i in range(4):
+        feats.append(F.leaky_relu(_conv(torch.cat(feats, 1), sd, f"{prefix}.conv{i}", 1), slope))
+    return _conv(torch.cat(feats, 1), sd, f"{prefix}.conv", 1) * add_rate + x
+
+
+def rrdb(x, sd, prefix, add_rate):
+    """RRDB.forward, utils/models.py:316-317."""
+    y = x
+    for d in range(3):
+        y = rdb(y, sd, f"{prefix}.net.{d}", add_rate)
+    return y * add_rate + x
+
+
+@torch.no_grad()
+def resnet_forward(x, sd, num_block, add_rate=0.2, scale=2, conv0_slope=0.01):
+    """EResNet.forward (utils/models.py:645-650; conv0_slope=0.01) / ResNet.forward (:613-618; conv0_slope=0.2)."""
+    x0 = F.leaky_relu(_conv(x, sd, "conv0", 4), conv0_slope)
+    r = x0
+    for i in range(num_block):
+        r = rrdb(r, sd, f"residual.{i}", add_rate)
+    y = x0 + _conv(r, sd, "conv1", 1)
+    for k in range(scale // 2):
+        y = F.leaky_relu(F.pixel_shuffle(_conv(y, sd, f"scaler.{k}.net.0", 1), 2), 0.01)
+    return torch.tanh(_conv(y, sd, "conv2", 4))
+
+
+def make_lr_hr(seed: int, n: int, hr: int, scale: int = 2):
+    """Synthetic (hr, lr) pair of SURVEY §8(d) C5: hr uniform[-1,1]; lr = ImageNet-normalised bicubic downsample."""
+    g = torch.Generator().manual_seed(seed)
+    hr_t = torch.rand(n, 3, hr, hr, generator=g) * 2 - 1
+    lr01 = F.interpolate((hr_t + 1) / 2, scale_factor=1.0 / scale, mode="bicubic", align_corners=False).clamp(0, 1)
+    mean = torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
+    std = torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    return hr_t, (lr01 - mean) / std

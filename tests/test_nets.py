@@ -1,0 +1,98 @@
+"""Class nets: CPU tests of the oracle against the reference's own outputs and of the drop-in classes'
+state-dict compatibility; GPU parity of the drop-in forward."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nets_oracle as no
+
+CASES = [("eresnet_2_x2", "EResNet", 2, 2, 0.01), ("eresnet_1_x4", "EResNet", 1, 4, 0.01), ("resnet_1_x2", "ResNet", 1, 2, 0.2)]
+
+
+def _build(cls_name, nb, scale, gold=None, name=None):
+    from image_super_resolution_b200 import models
+    torch.manual_seed(100)   # the reference's default seed (train.py:160): same construction order => same weights
+    net = getattr(models, cls_name)(nb, 0.2, scale).eval()
+    if cls_name == "ResNet":  # the golden run randomised the BatchNorm statistics with this generator
+        g = torch.Generator().manual_seed(107)
+        with torch.no_grad():
+            for m in net.modules():
+                if isinstance(m, torch.nn.BatchNorm2d):
+                    m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+                    m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                    m.weight.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                    m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    return net
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    return np.load(os.path.join(golden_dir, "nets_golden.npz"))
+
+
+@pytest.mark.parametrize("name,cls,nb,scale,s0", CASES)
+def test_dropin_state_dict_matches_reference(gold, name, cls, nb, scale, s0):
+    net = _build(cls, nb, scale)
+    sd = net.state_dict()
+    assert list(sd.keys()) == list(gold[name + ".keys"])                     # key-for-key, in order
+    sums = np.array([float(v.double().sum()) for v in sd.values()])
+    assert np.allclose(sums, gold[name + ".sums"], rtol=0, atol=1e-9)        # same seed => same initial weights
+    abss = np.array([float(v.double().abs().sum()) for v in sd.values()])
+    assert np.allclose(abss, gold[name + ".abssums"], rtol=0, atol=1e-9)
+
+
+@pytest.mark.parametrize("name,cls,nb,scale,s0", CASES)
+def test_oracle_matches_reference_classes(gold, name, cls, nb, scale, s0):
+    net = _build(cls, nb, scale)
+    y = no.resnet_forward(torch.from_numpy(gold[name + ".lr"]), net.state_dict(), nb, 0.2, scale, conv0_slope=s0)
+    assert np.abs(y.numpy() - gold[name + ".out"]).max() <= 2e-6
+
+
+def test_cpu_inputs_and_training_are_refused():
+    from image_super_resolution_b200 import models
+    net = models.EResNet(1, 0.2, 2)
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(1, 3, 8, 8))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,cls,nb,scale,s0", CASES)
+def test_gpu_forward_matches_reference_golden(gold, name, cls, nb, scale, s0):
+    """Tolerance: max-abs <= 4e-3 on the tanh output rescaled to [0,1] (i.e. 8e-3 on [-1,1])."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    net = _build(cls, nb, scale).to("cuda:0")
+    with torch.no_grad():
+        y = net(torch.from_numpy(gold[name + ".lr"]).to("cuda:0")).cpu().numpy()
+    ref = gold[name + ".out"]
+    assert y.shape == ref.shape
+    err = np.abs(y - ref).max()
+    assert err <= 8e-3, f"{name}: max err {err}"
+    # relative check too: EResNet's 0.2-scaled init makes outputs tiny, an absolute bound alone would be vacuous
+    rel = np.abs(y - ref).max() / (np.abs(ref).max() + 1e-12)
+    assert rel <= 2e-2, f"{name}: rel err {rel}"
+
+
+@pytest.mark.gpu
+def test_gpu_model_wrapper_uint8_fuse(gold):
+    """Model(net).init_normalize + fuse(): uint8 in -> uint8 out equals Normalize -> net -> TanhToArrayImage."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from image_super_resolution_b200 import models
+    net = _build("ResNet", 1, 2)
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    m = models.Model(net)
+    m.init_normalize([0.485, 0.456, 0.406], [0.229, 0.224, 0.225])
+    assert list(m.state_dict().keys())[:3] == ["net.0.mean", "net.0.std", "net.0.max_pixel_value"]
+    m.fuse()
+    m = m.to("cuda:0").eval()
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 256, (2, 3, 20, 28), dtype=torch.uint8, generator=g)
+    y = m(x.to("cuda:0")).cpu()
+    xn = ((x.float() / 255.0) - torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)) / torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    t = no.resnet_forward(xn, sd, 1, 0.2, 2, conv0_slope=0.2)
+    ref = ((t + 1) / 2 * 255).round().to(torch.uint8)
+    assert y.dtype == torch.uint8 and y.shape == ref.shape
+    assert (y.int() - ref.int()).abs().max().item() <= 2

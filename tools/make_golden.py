@@ -137,6 +137,37 @@ def golden_l1():
     print("l1_golden.npz:", {k: getattr(v, 'shape', ()) for k, v in out.items()})
 
 
+@torch.no_grad()
+def golden_nets():
+    """Reference EResNet / ResNet (utils/models.py) forward on seeded inputs; weights are NOT stored: the drop-in
+    classes re-create them from the same seed (same construction order), so only checksums + outputs are kept."""
+    from utils.models import EResNet, ResNet
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    from oracle.nets_oracle import make_lr_hr
+    out = {}
+    for name, cls, nb, scale in (("eresnet_2_x2", EResNet, 2, 2), ("eresnet_1_x4", EResNet, 1, 4), ("resnet_1_x2", ResNet, 1, 2)):
+        torch.manual_seed(SEED)
+        net = cls(nb, 0.2, scale).eval()
+        if cls is ResNet:  # give BatchNorm non-trivial running statistics and affine parameters
+            g = torch.Generator().manual_seed(SEED + 7)
+            for m in net.modules():
+                if isinstance(m, torch.nn.BatchNorm2d):
+                    m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+                    m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                    m.weight.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                    m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+        _, lr = make_lr_hr(SEED + 3, 2, 24 * scale, scale)   # LR 24x24
+        y = net(lr.clone())
+        sd = net.state_dict()
+        out[name + ".lr"] = lr.numpy()
+        out[name + ".out"] = y.numpy()
+        out[name + ".keys"] = np.array(list(sd.keys()))
+        out[name + ".sums"] = np.array([float(v.double().sum()) for v in sd.values()])
+        out[name + ".abssums"] = np.array([float(v.double().abs().sum()) for v in sd.values()])
+        print(name, "params", sum(p.numel() for p in net.parameters()), "out", tuple(y.shape), float(y.abs().mean()))
+    np.savez_compressed(os.path.join(OUT, "nets_golden.npz"), **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 1)
     install_stubs()
@@ -144,3 +175,4 @@ if __name__ == "__main__":
     m = golden_model_pt()
     golden_rs_tiling(m)
     golden_l1()
+    golden_nets()
