@@ -44,6 +44,8 @@ SIGNATURES = {
     "srb_profile_enable": (_i, [_vp, _i]),
     "srb_profile_read": (_i, [_vp, _fp, _i]),
     "srb_ubench_mma": (_i, [_vp, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_longlong)]),
+    "srb_conv2d_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _i, _vp]),
+    "srb_bias_grad": (_i, [_vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),

@@ -15,6 +15,7 @@
 #include "srb_conv.cuh"
 #include "srb_elem.cuh"
 #include "srb_ubench.cuh"
+#include "srb_wgrad.cuh"
 
 using namespace srb;
 
@@ -616,5 +617,76 @@ extern "C" int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int ite
     CUDA_TRY(cudaDeviceSynchronize());
     CUDA_TRY(cudaMemcpy(out2_host, d, 16, cudaMemcpyDeviceToHost));
     cudaFree(d);
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// backward: weight / bias gradients (train.py:57 autograd of the convs)
+// ------------------------------------------------------------------------------------------
+static int encode_c8_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N, int H, int W, int planes, int bw, int bh, int bp) {
+    cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, (cuuint64_t)planes, (cuuint64_t)N};
+    cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * planes};
+    cuuint32_t box[4] = {(cuuint32_t)bw * 4, (cuuint32_t)bh, (cuuint32_t)bp, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(base), gdim, gstr, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+    return SRB_OK;
+}
+
+extern "C" int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy,
+                                int dy_c8_total, int dy_c8_off, int cout, float* dw_oihw, float scale, int k, int dtype,
+                                int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !x || !dy || !dw_oihw) return fail(SRB_EINVAL, "srb_conv2d_wgrad: NULL argument");
+    if (k != 3) return fail(SRB_ENOSUP, "srb_conv2d_wgrad: tensor-core path is 3x3 (use srb_conv2d_wgrad_direct for 9x9)");
+    if (cin % 8 || cout % 8) return fail(SRB_ENOSUP, "srb_conv2d_wgrad: cin=%d cout=%d must be multiples of 8", cin, cout);
+    if (((uintptr_t)x & 15) || ((uintptr_t)dy & 15)) return fail(SRB_EINVAL, "srb_conv2d_wgrad: buffers must be 16-byte aligned");
+    if (x_c8_off < 0 || x_c8_off + cin / 8 > x_c8_total || dy_c8_off < 0 || dy_c8_off + cout / 8 > dy_c8_total)
+        return fail(SRB_EINVAL, "srb_conv2d_wgrad: plane slice out of range");
+    using G = WgradGeom;
+    CUtensorMap tx, tdy;
+    int rc;
+    if ((rc = encode_c8_map(ctx, &tx, x, N, H, W, x_c8_total, G::XW, G::XH, G::XPLANES))) return rc;
+    if ((rc = encode_c8_map(ctx, &tdy, dy, N, H, W, dy_c8_total, G::TW, G::TH, G::DYPLANES))) return rc;
+    WgradParams p{};
+    p.N = N; p.H = H; p.W = W;
+    p.tiles_x = (W + G::TW - 1) / G::TW; p.tiles_y = (H + G::TH - 1) / G::TH;
+    long long nt = (long long)p.tiles_x * p.tiles_y * N;
+    if (nt <= 0 || nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_conv2d_wgrad: %lld tiles", nt);
+    p.num_tiles = (int)nt;
+    p.cin_total = cin; p.dw = dw_oihw; p.scale = scale; p.dbg_swap = ctx->dbg_swap;
+    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int ci0 = 0; ci0 < cin; ci0 += 128)
+        for (int co0 = 0; co0 < cout; co0 += 32) {
+            p.cin0 = ci0; p.cout0 = co0;
+            p.cin_blk = cin - ci0 < 128 ? cin - ci0 : 128;
+            p.cout_blk = cout - co0 < 32 ? cout - co0 : 32;
+            p.x_c8_off = x_c8_off + ci0 / 8; p.dy_c8_off = dy_c8_off + co0 / 8;
+            if (dtype == SRB_DT_BF16) {
+                CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+                wgrad_tc_kernel<true><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, p);
+            } else {
+                CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+                wgrad_tc_kernel<false><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, p);
+            }
+            CUDA_TRY(cudaGetLastError());
+        }
+    return SRB_OK;
+}
+
+extern "C" int srb_bias_grad(srb_ctx* ctx, const void* dy, int dy_c8_total, int dy_c8_off, int cout, float* db, float scale,
+                             int dtype, int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !dy || !db) return fail(SRB_EINVAL, "srb_bias_grad: NULL argument");
+    int planes = (cout + 7) / 8;
+    if (dy_c8_off < 0 || dy_c8_off + planes > dy_c8_total) return fail(SRB_EINVAL, "srb_bias_grad: plane slice out of range");
+    size_t HW = (size_t)H * W, total = HW * N;
+    int gx = (int)((total + 255) / 256); if (gx > ctx->num_sms * 2) gx = ctx->num_sms * 2; if (gx < 1) gx = 1;
+    dim3 grid(gx, planes);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) bias_grad_kernel<true><<<grid, 256, 0, st>>>((const uint4*)dy, dy_c8_total, dy_c8_off, planes, HW, N, scale, db, cout);
+    else bias_grad_kernel<false><<<grid, 256, 0, st>>>((const uint4*)dy, dy_c8_total, dy_c8_off, planes, HW, N, scale, db, cout);
+    CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }

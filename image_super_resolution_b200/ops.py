@@ -138,3 +138,23 @@ def l1_loss_bwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0, grad_scal
     check(lib().srb_l1_loss_bwd(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w),
                                 float(grad_scale), g.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_bwd")
     return g
+
+
+def conv2d_wgrad(x: torch.Tensor, x_planes: int, x_off: int, cin: int, dy: torch.Tensor, dy_planes: int, dy_off: int,
+                 cout: int, dw: torch.Tensor, N: int, H: int, W: int, scale: float = 1.0, k: int = 3):
+    """dw (fp32 OIHW, device) += scale * wgrad(x slice, dy slice)."""
+    _require_cuda(x, "x"); _require_cuda(dy, "dy"); _require_cuda(dw, "dw")
+    if dw.dtype != torch.float32 or tuple(dw.shape) != (cout, cin, k, k):
+        raise RuntimeError("conv2d_wgrad: dw must be fp32 [cout, cin, k, k]")
+    ctx = Context.get(x.device.index or 0)
+    check(lib().srb_conv2d_wgrad(ctx.handle, x.data_ptr(), x_planes, x_off, cin, dy.data_ptr(), dy_planes, dy_off, cout,
+                                 dw.data_ptr(), float(scale), k, dtype_code(x.dtype), N, H, W, _stream_ptr(x.device)),
+          "srb_conv2d_wgrad")
+
+
+def bias_grad(dy: torch.Tensor, dy_planes: int, dy_off: int, cout: int, db: torch.Tensor, N: int, H: int, W: int,
+              scale: float = 1.0):
+    _require_cuda(dy, "dy"); _require_cuda(db, "db")
+    ctx = Context.get(dy.device.index or 0)
+    check(lib().srb_bias_grad(ctx.handle, dy.data_ptr(), dy_planes, dy_off, cout, db.data_ptr(), float(scale),
+                              dtype_code(dy.dtype), N, H, W, _stream_ptr(dy.device)), "srb_bias_grad")

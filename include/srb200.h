@@ -117,6 +117,16 @@ int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
  * out2_host[0] = issue cycles, out2_host[1] = cycles until all MMAs completed */
 int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host);
 
+/* Weight gradient of a 3x3 conv (autograd of aten::_convolution, train.py:57):
+ * dw[co][ci][dy][dx] += scale * sum_p dY[p][co] * X[p+(dy-1,dx-1)][ci].  x, dy: C8-plane slices (device);
+ * dw: fp32 OIHW [cout][cin][3][3] on the device, ACCUMULATED into (zero it first).  fp32 atomics: summation order
+ * across CTAs is not fixed.  Bias gradient: db[c] += scale * sum_p dY[p][c]. */
+int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy, int dy_c8_total,
+                     int dy_c8_off, int cout, float* dw_oihw, float scale, int k, int dtype, int N, int H, int W,
+                     srb_stream_t stream);
+int srb_bias_grad(srb_ctx* ctx, const void* dy, int dy_c8_total, int dy_c8_off, int cout, float* db, float scale, int dtype,
+                  int N, int H, int W, srb_stream_t stream);
+
 /* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
  * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
 int srb_l1_partials_len(void);

@@ -154,6 +154,32 @@ def test_scaler_conv_pixelshuffle_folded(ctx, dev):
     _assert_close(ops.c8_to_nchw(y, 64).cpu(), ref, "scaler conv + pixelshuffle")
 
 
+@pytest.mark.parametrize("cin,cout,xoff", [(64, 32, 0), (160, 32, 0), (192, 64, 0), (32, 64, 4)])
+def test_conv3x3_wgrad_and_bias_grad(ctx, dev, cin, cout, xoff):
+    """dW, db of a 3x3 conv vs fp32 autograd on the same fp16-rounded operands (fp32 atomics: rel 2e-3 of max|dW|)."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(cin + cout)
+    N, H, W = 3, 37, 45
+    tot = 24
+    xfull = torch.randn(N, tot * 8, H, W, generator=g)
+    dy = torch.randn(N, cout, H, W, generator=g) * 0.1
+    xs = xfull[:, xoff * 8: xoff * 8 + cin].half().float().requires_grad_(False)
+    wt = torch.zeros(cout, cin, 3, 3, requires_grad=True)
+    bt = torch.zeros(cout, requires_grad=True)
+    y = F.conv2d(xs, wt, bt, padding=1)
+    y.backward(dy.half().float())
+    xc = ops.nchw_to_c8(xfull.to(dev))
+    dyc = ops.nchw_to_c8(dy.to(dev))
+    dw = torch.zeros(cout, cin, 3, 3, device=dev)
+    db = torch.zeros(cout, device=dev)
+    ops.conv2d_wgrad(xc, tot, xoff, cin, dyc, cout // 8, 0, cout, dw, N, H, W, scale=0.5)
+    ops.bias_grad(dyc, cout // 8, 0, cout, db, N, H, W, scale=0.5)
+    from image_super_resolution_b200._lib import Context
+    Context.get(0).check_device()
+    _assert_close(dw.cpu() * 2, wt.grad, f"wgrad {cin}->{cout}", rel=2e-3, abs_=1e-3)
+    _assert_close(db.cpu() * 2, bt.grad, f"bias grad {cout}", rel=2e-3, abs_=1e-3)
+
+
 def test_conv9x9_head(ctx, dev):
     from image_super_resolution_b200 import ops
     out, ref = _conv_case(ctx, dev, 64, 3, 9, 2, 33, 21, flags=ops.F_LRELU, seed=7)
