@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsrb200.so")
 
 SRB_DT_F16, SRB_DT_BF16, SRB_DT_F32 = 0, 1, 2
-F_LRELU, F_RESIDUAL, F_TANH, F_U8OUT, F_PIXSHUF2, F_F32OUT = 1, 2, 4, 8, 16, 32
+F_LRELU, F_RESIDUAL, F_TANH, F_U8OUT, F_PIXSHUF2, F_F32OUT, F_MASK = 1, 2, 4, 8, 16, 32, 64
 
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 _fp = C.POINTER(C.c_float)
@@ -46,9 +46,17 @@ SIGNATURES = {
     "srb_ubench_mma": (_i, [_vp, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_longlong)]),
     "srb_conv2d_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _i, _vp]),
     "srb_bias_grad": (_i, [_vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
+    "srb_conv2d_ex": (_i, [_vp, _vp, _vp, _vp]),
+    "srb_alloc_conv": (_i, [_vp, _i, _i, _i, _i, C.POINTER(_vp)]),
+    "srb_pack_conv_device": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
+    "srb_conv9_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
+    "srb_tanh_bwd_to_c8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
+    "srb_pixunshuffle_mask": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _i, _vp]),
+    "srb_c8_axpby_mask": (_i, [_vp, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
+    "srb_l1_loss_bwd_dev": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp, _vp]),
 }
 
 _lib = None
@@ -104,6 +112,17 @@ class Context:
 
     def debug_set(self, key: int, value: int):
         check(lib().srb_debug_set(self.handle, key, value), "srb_debug_set")
+
+
+class ConvArgs(C.Structure):
+    """srb_conv_args of include/srb200.h."""
+    _fields_ = [("x", _vp), ("x_c8_total", _i), ("x_c8_off", _i),
+                ("y", _vp), ("y_c8_total", _i), ("y_c8_off", _i),
+                ("residual", _vp), ("res_c8_total", _i), ("res_c8_off", _i), ("res_nplanes", _i), ("res_scale", _f),
+                ("res2", _vp), ("res2_c8_total", _i), ("res2_c8_off", _i), ("res2_scale", _f),
+                ("out_scale", _f), ("lrelu_slope", _f), ("flags", _i),
+                ("mask", _vp), ("mask_c8_total", _i), ("mask_c8_off", _i), ("mask_p0", _i), ("mask_p1", _i), ("mask_slope", _f),
+                ("N", _i), ("H", _i), ("W", _i)]
 
 
 def f32_ptr(arr):

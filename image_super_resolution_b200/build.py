@@ -8,7 +8,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "srb200.cu")
 OUT = os.path.join(HERE, "libsrb200.so")
-DEPS = [os.path.join(HERE, "csrc", f) for f in ("srb200.cu", "srb_conv.cuh", "srb_elem.cuh", "srb_ptx.cuh")] + [
+DEPS = sorted(os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc"))) + [
     os.path.join(HERE, "..", "include", "srb200.h")]
 
 

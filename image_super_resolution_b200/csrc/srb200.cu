@@ -16,6 +16,7 @@
 #include "srb_elem.cuh"
 #include "srb_ubench.cuh"
 #include "srb_wgrad.cuh"
+#include "srb_bwd.cuh"
 
 using namespace srb;
 
@@ -139,16 +140,64 @@ static uint16_t f2h(float f, int dtype) {
 
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
+// kernel family + packed-operand geometry of a (cout, cin, k) conv
+static int conv_geometry(int cout, int cin, int k, int* mode, int* c8in, int* nout, int* ksteps, int* kblocks) {
+    if (k == 9 && cin == 3) { *mode = MODE_PAIRDX; *c8in = 1; *nout = round_up(cout, 32); *ksteps = 9 * 5; }
+    else if (k == 9 && cout == 3 && cin % 16 == 0) { *mode = MODE_DXN; *c8in = cin / 8; *nout = 32; *ksteps = 9 * (*c8in / 2); }
+    else if (k == 3 && cin % 16 == 0) { *mode = MODE_STD; *c8in = cin / 8; *nout = round_up(cout, 32); *ksteps = 9 * (*c8in / 2); }
+    else return fail(SRB_ENOSUP, "srb_pack_conv: no kernel for cout=%d cin=%d k=%d", cout, cin, k);
+    if (*nout > 256) return fail(SRB_ENOSUP, "srb_pack_conv: cout=%d > 256", cout);
+    *kblocks = (*mode == MODE_STD && *c8in > 8) ? *c8in / 4 : 0;
+    if (*kblocks && (*c8in % 4)) return fail(SRB_ENOSUP, "srb_pack_conv: cin=%d must be a multiple of 32 above 64", cin);
+    return SRB_OK;
+}
+
+extern "C" int srb_alloc_conv(srb_ctx* ctx, int cout, int cin, int k, int dtype, srb_weights** out) {
+    if (!ctx || !out) return fail(SRB_EINVAL, "srb_alloc_conv: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_alloc_conv: dtype %d", dtype);
+    int mode, c8in, nout, ksteps, kblocks;
+    if (int rc = conv_geometry(cout, cin, k, &mode, &c8in, &nout, &ksteps, &kblocks)) return rc;
+    srb_weights* sw = new srb_weights();
+    sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
+    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
+    sw->pack_bytes = (size_t)ksteps * 2 * nout * 8 * 2;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
+        srb_free_weights(sw);
+        return fail(SRB_ENOMEM, "srb_alloc_conv: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemset(sw->d_pack, 0, sw->pack_bytes));
+    CUDA_TRY(cudaMemset(sw->d_bias, 0, nout * sizeof(float)));
+    *out = sw;
+    return SRB_OK;
+}
+
+extern "C" int srb_pack_conv_device(srb_ctx* ctx, srb_weights* w, const float* w_src, int src_o, int src_i, int o_off,
+                                    int c_off, int transpose, const float* bias_src, srb_stream_t stream) {
+    if (!ctx || !w || !w_src) return fail(SRB_EINVAL, "srb_pack_conv_device: NULL argument");
+    const int so_need = transpose ? c_off + w->cin : o_off + w->cout;
+    const int si_need = transpose ? o_off + w->cout : c_off + w->cin;
+    if (o_off < 0 || c_off < 0 || so_need > src_o || si_need > src_i)
+        return fail(SRB_EINVAL, "srb_pack_conv_device: slice (%d+%d, %d+%d) exceeds the source filter [%d][%d]", o_off, w->cout,
+                    c_off, w->cin, src_o, src_i);
+    PackParams pp;
+    pp.mode = w->mode; pp.c8in = w->c8in; pp.nout = w->nout; pp.kblocks = w->kblocks; pp.cout = w->cout; pp.cin = w->cin;
+    pp.k = w->k; pp.src_i = src_i; pp.o_off = o_off; pp.c_off = c_off; pp.transpose = transpose;
+    pp.total = w->pack_bytes / 2;
+    cudaStream_t st = (cudaStream_t)stream;
+    int grid = (int)((pp.total + 255) / 256);
+    if (w->dtype == SRB_DT_BF16) pack_conv_kernel<true><<<grid, 256, 0, st>>>(w_src, (uint16_t*)w->d_pack, pp, transpose ? nullptr : bias_src, w->d_bias);
+    else pack_conv_kernel<false><<<grid, 256, 0, st>>>(w_src, (uint16_t*)w->d_pack, pp, transpose ? nullptr : bias_src, w->d_bias);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
 extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, const float* bn4, float bn_eps, int cout,
                              int cin, int k, int dtype, srb_weights** out) {
     if (!ctx || !w || !out) return fail(SRB_EINVAL, "srb_pack_conv: NULL argument");
     if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_pack_conv: dtype %d", dtype);
-    int mode, c8in, nout, ksteps;
-    if (k == 9 && cin == 3) { mode = MODE_PAIRDX; c8in = 1; nout = round_up(cout, 32); ksteps = 9 * 5; }
-    else if (k == 9 && cout == 3 && cin % 16 == 0) { mode = MODE_DXN; c8in = cin / 8; nout = 32; ksteps = 9 * (c8in / 2); }
-    else if (k == 3 && cin % 16 == 0) { mode = MODE_STD; c8in = cin / 8; nout = round_up(cout, 32); ksteps = 9 * (c8in / 2); }
-    else return fail(SRB_ENOSUP, "srb_pack_conv: no kernel for cout=%d cin=%d k=%d", cout, cin, k);
-    if (nout > 256) return fail(SRB_ENOSUP, "srb_pack_conv: cout=%d > 256", cout);
+    int mode, c8in, nout, ksteps, kblocks;
+    if (int rc = conv_geometry(cout, cin, k, &mode, &c8in, &nout, &ksteps, &kblocks)) return rc;
 
     // BN fold (fuse_conv_and_bn): W' = W * gamma/sqrt(var+eps); b' = (b - mean)*gamma/sqrt(var+eps) + beta
     std::vector<float> scale(cout, 1.f), fb(cout, 0.f);
@@ -167,8 +216,6 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
     std::vector<uint16_t> pack((size_t)ksteps * step_elems, 0);
     std::vector<float> hbias(nout, 0.f);
     int ks = 0;
-    const int kblocks = (mode == MODE_STD && c8in > 8) ? c8in / 4 : 0;
-    if (kblocks && (c8in % 4)) return fail(SRB_ENOSUP, "srb_pack_conv: cin=%d must be a multiple of 32 above 64", cin);
     if (kblocks) {
         // weight-streaming order: [K block of 32 channels][dy][dx][2 K-steps]
         for (int kb = 0; kb < kblocks; ++kb) for (int dy = 0; dy < 3; ++dy) for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < 2; ++c2, ++ks)
@@ -285,7 +332,22 @@ extern "C" int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const voi
                                    int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
                                    float res_scale, const void* res2, int res2_c8_total, int res2_c8_off, float res2_scale,
                                    float out_scale, float lrelu_slope, int flags, int N, int H, int W, srb_stream_t stream) {
-    if (!ctx || !w || !x || !y) return fail(SRB_EINVAL, "srb_conv2d_fwd: NULL argument");
+    srb_conv_args a;
+    memset(&a, 0, sizeof(a));
+    a.x = x; a.x_c8_total = x_c8_total; a.x_c8_off = x_c8_off;
+    a.y = y; a.y_c8_total = y_c8_total; a.y_c8_off = y_c8_off;
+    a.residual = residual; a.res_c8_total = res_c8_total; a.res_c8_off = res_c8_off; a.res_scale = res_scale;
+    a.res2 = res2; a.res2_c8_total = res2_c8_total; a.res2_c8_off = res2_c8_off; a.res2_scale = res2_scale;
+    a.out_scale = out_scale; a.lrelu_slope = lrelu_slope; a.flags = flags; a.N = N; a.H = H; a.W = W;
+    return srb_conv2d_ex(ctx, w, &a, stream);
+}
+
+extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_args* a, srb_stream_t stream) {
+    if (!ctx || !w || !a || !a->x || !a->y) return fail(SRB_EINVAL, "srb_conv2d: NULL argument");
+    const int N = a->N, H = a->H, W = a->W, flags = a->flags;
+    const void* x = a->x; void* y = a->y; const void* residual = a->residual; const void* res2 = a->res2;
+    const int x_c8_total = a->x_c8_total, x_c8_off = a->x_c8_off, y_c8_total = a->y_c8_total, y_c8_off = a->y_c8_off;
+    const int res_c8_total = a->res_c8_total, res_c8_off = a->res_c8_off;
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv2d_fwd: empty shape %dx%dx%d", N, H, W);
     if (((uintptr_t)x & 15) || ((uintptr_t)y & 15 && w->mode != MODE_DXN) || ((uintptr_t)residual & 15))
         return fail(SRB_EINVAL, "srb_conv2d_fwd: buffers must be 16-byte aligned");
@@ -298,10 +360,20 @@ extern "C" int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const voi
     p.wpack = w->d_pack; p.bias = w->d_bias;
     p.y = y; p.y_c8_total = y_c8_total; p.y_c8_off = y_c8_off;
     p.res = residual; p.res_c8_total = res_c8_total; p.res_c8_off = res_c8_off;
-    p.res_scale = res_scale; p.out_scale = out_scale; p.slope = lrelu_slope;
-    p.res2 = res2; p.res2_c8_total = res2_c8_total; p.res2_c8_off = res2_c8_off; p.res2_scale = res2_scale;
+    p.res_scale = a->res_scale; p.out_scale = a->out_scale; p.slope = a->lrelu_slope;
+    p.res2 = res2; p.res2_c8_total = a->res2_c8_total; p.res2_c8_off = a->res2_c8_off; p.res2_scale = a->res2_scale;
     if (res2 && (((uintptr_t)res2 & 15) || !(flags & SRB_F_RESIDUAL))) return fail(SRB_EINVAL, "srb_conv2d_fwd: res2 needs SRB_F_RESIDUAL and 16-byte alignment");
     p.flags = flags; p.cout = w->cout;
+    p.res_nplanes = a->res_nplanes > 0 ? a->res_nplanes : 1 << 30;
+    p.mask = a->mask; p.mask_c8_total = a->mask_c8_total; p.mask_c8_off = a->mask_c8_off;
+    p.mask_p0 = a->mask_p0; p.mask_p1 = a->mask_p1; p.mask_slope = a->mask_slope;
+    if (flags & SRB_F_MASK) {
+        if (!a->mask || ((uintptr_t)a->mask & 15)) return fail(SRB_EINVAL, "srb_conv2d: SRB_F_MASK needs a 16-byte aligned mask buffer");
+        if (a->mask_p0 < 0 || a->mask_p1 < a->mask_p0 || a->mask_c8_off + a->mask_p1 > a->mask_c8_total)
+            return fail(SRB_EINVAL, "srb_conv2d: mask plane range out of bounds");
+        if (w->mode != MODE_STD || (flags & SRB_F_PIXSHUF2)) return fail(SRB_ENOSUP, "srb_conv2d: SRB_F_MASK is a 3x3 / head-conv epilogue");
+    }
+    const bool partial_res = a->res_nplanes > 0 && a->res_nplanes < (w->cout + 7) / 8;
     cudaStream_t st = (cudaStream_t)stream;
     if (w->mode == MODE_DXN) {
         if (!(flags & (SRB_F_U8OUT | SRB_F_F32OUT))) return fail(SRB_EINVAL, "srb_conv2d_fwd: tail conv needs SRB_F_U8OUT or SRB_F_F32OUT");
@@ -313,21 +385,23 @@ extern "C" int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const voi
     if ((flags & SRB_F_PIXSHUF2) && (w->cout % 32)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PixelShuffle(2) needs cout %% 32 == 0");
     if ((flags & SRB_F_PIXSHUF2) && (flags & SRB_F_RESIDUAL)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PIXSHUF2 with residual unsupported");
     if ((flags & SRB_F_RESIDUAL) && w->nout > 64) return fail(SRB_ENOSUP, "srb_conv2d_fwd: residual epilogue needs cout <= 64");
-    if ((flags & SRB_F_RESIDUAL) && (res_c8_off < 0 || res_c8_off + out_planes > res_c8_total)) return fail(SRB_EINVAL, "srb_conv2d_fwd: residual plane slice out of range");
+    const int res_need = partial_res ? a->res_nplanes : out_planes;
+    if ((flags & SRB_F_RESIDUAL) && (res_c8_off < 0 || res_c8_off + res_need > res_c8_total)) return fail(SRB_EINVAL, "srb_conv2d_fwd: residual plane slice out of range");
     if (y_c8_off < 0 || y_c8_off + out_planes > y_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: output plane slice out of range");
     if (w->cout % 8) return fail(SRB_ENOSUP, "srb_conv2d_fwd: cout=%d not a multiple of 8", w->cout);
     if (w->mode == MODE_PAIRDX) {
         if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
     }
+    // the TMA residual ring needs the residual on every output plane of a full-width (cout == NOUT) conv
 #define SRB_STD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
-        if ((flags & SRB_F_RESIDUAL) && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
+        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
-    SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3)
+    SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3) SRB_STD(4, 32, 4)
     if (w->kblocks) {   // dense-block convs (Cin = 96..192): K blocks of 32 channels, filter streamed with the halo
         if (w->nout == 32) return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
         if (w->nout == 64) {
-            if ((flags & SRB_F_RESIDUAL) && w->cout == 64) return launch_conv<4, 64, 3, 3, MODE_STD, 4, true, true>(ctx, w, x, x_c8_total, p, st);
+            if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == 64) return launch_conv<4, 64, 3, 3, MODE_STD, 4, true, true>(ctx, w, x, x_c8_total, p, st);
             return launch_conv<4, 64, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
         }
     }
@@ -413,6 +487,11 @@ extern "C" int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, c
 
 extern "C" int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
                                float grad_scale, void* dpred, srb_stream_t stream) {
+    return srb_l1_loss_bwd_dev(ctx, pred, pred_dtype, tgt, n, w, grad_scale, nullptr, dpred, stream);
+}
+
+extern "C" int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                                   float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream) {
     if (!ctx || !pred || !tgt || !dpred) return fail(SRB_EINVAL, "srb_l1_loss_bwd: NULL argument");
     if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_bwd: empty input");
     size_t b = (n + 255) / 256;
@@ -421,9 +500,9 @@ extern "C" int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, c
     float g = (float)((double)w * (double)grad_scale / (double)n);
     cudaStream_t st = (cudaStream_t)stream;
     switch (pred_dtype) {
-        case 0: l1_bwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
-        case 1: l1_bwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
-        case 2: l1_bwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred); break;
+        case 0: l1_bwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
+        case 1: l1_bwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
+        case 2: l1_bwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
         default: return fail(SRB_EINVAL, "srb_l1_loss_bwd: pred_dtype %d", pred_dtype);
     }
     CUDA_TRY(cudaGetLastError());
@@ -687,6 +766,90 @@ extern "C" int srb_bias_grad(srb_ctx* ctx, const void* dy, int dy_c8_total, int 
     cudaStream_t st = (cudaStream_t)stream;
     if (dtype == SRB_DT_BF16) bias_grad_kernel<true><<<grid, 256, 0, st>>>((const uint4*)dy, dy_c8_total, dy_c8_off, planes, HW, N, scale, db, cout);
     else bias_grad_kernel<false><<<grid, 256, 0, st>>>((const uint4*)dy, dy_c8_total, dy_c8_off, planes, HW, N, scale, db, cout);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// backward glue + 9x9 weight gradients (srb_bwd.cuh)
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_tanh_bwd_to_c8(srb_ctx* ctx, const float* gout, const float* out, void* g_c8, float scale, int dtype, int N,
+                                  int H, int W, srb_stream_t stream) {
+    if (!ctx || !gout || !out || !g_c8) return fail(SRB_EINVAL, "srb_tanh_bwd_to_c8: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_tanh_bwd_to_c8: empty shape");
+    size_t HW = (size_t)H * W, total = HW * N;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) tanh_bwd_to_c8_kernel<true><<<grid, 256, 0, st>>>(gout, out, (uint4*)g_c8, scale, HW, total);
+    else tanh_bwd_to_c8_kernel<false><<<grid, 256, 0, st>>>(gout, out, (uint4*)g_c8, scale, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_pixunshuffle_mask(srb_ctx* ctx, const void* g_u, const void* u, void* g_s, int c8_u, float slope, int dtype,
+                                     int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !g_u || !u || !g_s) return fail(SRB_EINVAL, "srb_pixunshuffle_mask: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0 || c8_u <= 0) return fail(SRB_EINVAL, "srb_pixunshuffle_mask: empty shape");
+    size_t total = (size_t)N * c8_u * 4 * H * W;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) pixunshuffle_mask_kernel<true><<<grid, 256, 0, st>>>(g_u, u, (uint4*)g_s, c8_u, H, W, slope, total);
+    else pixunshuffle_mask_kernel<false><<<grid, 256, 0, st>>>(g_u, u, (uint4*)g_s, c8_u, H, W, slope, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off, float alpha, const void* b,
+                                 int b_c8_total, int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off,
+                                 float slope, void* out, int out_c8_total, int out_c8_off, int planes, int dtype, int N, int H,
+                                 int W, srb_stream_t stream) {
+    if (!ctx || !a || !out) return fail(SRB_EINVAL, "srb_c8_axpby_mask: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0 || planes <= 0) return fail(SRB_EINVAL, "srb_c8_axpby_mask: empty shape");
+    if (a_c8_off < 0 || a_c8_off + planes > a_c8_total || out_c8_off < 0 || out_c8_off + planes > out_c8_total ||
+        (b && (b_c8_off < 0 || b_c8_off + planes > b_c8_total)) || (act && (act_c8_off < 0 || act_c8_off + planes > act_c8_total)))
+        return fail(SRB_EINVAL, "srb_c8_axpby_mask: plane slice out of range");
+    size_t HW = (size_t)H * W, total = HW * N * planes;
+    int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16)
+        c8_axpby_mask_kernel<true><<<grid, 256, 0, st>>>((const uint4*)a, a_c8_total, a_c8_off, (const uint4*)b, b_c8_total, b_c8_off,
+            (const uint4*)act, act_c8_total, act_c8_off, (uint4*)out, out_c8_total, out_c8_off, planes, alpha, beta, slope, HW, total);
+    else
+        c8_axpby_mask_kernel<false><<<grid, 256, 0, st>>>((const uint4*)a, a_c8_total, a_c8_off, (const uint4*)b, b_c8_total, b_c8_off,
+            (const uint4*)act, act_c8_total, act_c8_off, (uint4*)out, out_c8_total, out_c8_off, planes, alpha, beta, slope, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_conv9_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy, int dy_c8_total,
+                               int dy_c8_off, int cout, float* dw_oihw, float scale, int dtype, int N, int H, int W,
+                               srb_stream_t stream) {
+    if (!ctx || !x || !dy || !dw_oihw) return fail(SRB_EINVAL, "srb_conv9_wgrad: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv9_wgrad: empty shape");
+    Wgrad9Params p{};
+    if (cin == 3 && cout == 64) {          // head: A = dY, S = X
+        p.a = dy; p.a_c8_total = dy_c8_total; p.a_c8_off = dy_c8_off; p.s = x; p.s_c8_total = x_c8_total; p.s_c8_off = x_c8_off;
+        p.sgn = 1; p.a_is_cout = 1;
+        if (dy_c8_off < 0 || dy_c8_off + 8 > dy_c8_total || x_c8_off < 0 || x_c8_off >= x_c8_total) return fail(SRB_EINVAL, "srb_conv9_wgrad: plane slice out of range");
+    } else if (cin == 64 && cout == 3) {   // tail: A = X, S = dY
+        p.a = x; p.a_c8_total = x_c8_total; p.a_c8_off = x_c8_off; p.s = dy; p.s_c8_total = dy_c8_total; p.s_c8_off = dy_c8_off;
+        p.sgn = -1; p.a_is_cout = 0;
+        if (x_c8_off < 0 || x_c8_off + 8 > x_c8_total || dy_c8_off < 0 || dy_c8_off >= dy_c8_total) return fail(SRB_EINVAL, "srb_conv9_wgrad: plane slice out of range");
+    } else return fail(SRB_ENOSUP, "srb_conv9_wgrad: only the 3->64 head and 64->3 tail 9x9 convs (cin=%d cout=%d)", cin, cout);
+    p.dw = dw_oihw; p.scale = scale; p.N = N; p.H = H; p.W = W;
+    p.tiles_x = (W + WG9_T - 1) / WG9_T; p.tiles_y = (H + WG9_T - 1) / WG9_T;
+    long long nt = (long long)p.tiles_x * p.tiles_y * N;
+    if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_conv9_wgrad: %lld tiles", nt);
+    p.num_tiles = (int)nt;
+    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) {
+        CUDA_TRY(cudaFuncSetAttribute(wgrad9_direct_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG9_SMEM));
+        wgrad9_direct_kernel<true><<<grid, 256, WG9_SMEM, st>>>(p);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(wgrad9_direct_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG9_SMEM));
+        wgrad9_direct_kernel<false><<<grid, 256, WG9_SMEM, st>>>(p);
+    }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }

@@ -37,6 +37,7 @@ enum : int {
     F_U8OUT = 8,      // DXN: round((t+1)/2*255) -> uint8 NCHW (TanhToArrayImage, utils/models.py:448-451)
     F_PIXSHUF2 = 16,  // fold nn.PixelShuffle(2) into the store addressing (Scaler, utils/models.py:580-583)
     F_F32OUT = 32,    // DXN: fp32 NCHW output
+    F_MASK = 64,      // backward: multiply output planes [mask_p0, mask_p1) by LeakyReLU'(saved activation)
 };
 
 struct ConvParams {
@@ -52,6 +53,10 @@ struct ConvParams {
     const void* res2;        // optional second residual (RRDB outer skip), C8 planes, read with plain loads
     int res2_c8_total, res2_c8_off;
     float res_scale, res2_scale, out_scale, slope;
+    int res_nplanes;         // residual is added to output planes < res_nplanes only (dgrad into a dense-block gradient)
+    const void* mask;        // F_MASK: saved forward activation (C8 planes, same H, W); sign selects 1 or mask_slope
+    int mask_c8_total, mask_c8_off, mask_p0, mask_p1;
+    float mask_slope;
     int kblocks;             // WS kernels: number of K blocks (C8IN planes each) streamed per super-tile
     int flags;
     int cout;                // real output channels (DXN: 3)
@@ -408,7 +413,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                     v[i] = tt * p.out_scale;
                                 }
                                 if (valid) {
-                                    if (RES || has_res) {
+                                    if ((RES || has_res) && gj < p.res_nplanes) {
                                         uint4 q;
                                         if constexpr (RES) q = lds_u4(rslot_addr + gj * 2048);
                                         else q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.res) +
@@ -430,6 +435,18 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                             float2 f = unpack2<BF16>(qq[i]);
                                             v[2 * i] += p.res2_scale * f.x;
                                             v[2 * i + 1] += p.res2_scale * f.y;
+                                        }
+                                    }
+                                    if ((p.flags & F_MASK) && gj >= p.mask_p0 && gj < p.mask_p1) {
+                                        // LeakyReLU backward: the in-place activation kept its sign (slope > 0)
+                                        const uint4 q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.mask) +
+                                                                 (((size_t)n * p.mask_c8_total + p.mask_c8_off + gj) * HW + pix) * 16);
+                                        const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                                        for (int i = 0; i < 4; ++i) {
+                                            float2 f = unpack2<BF16>(qq[i]);
+                                            if (!(f.x > 0.f)) v[2 * i] *= p.mask_slope;
+                                            if (!(f.y > 0.f)) v[2 * i + 1] *= p.mask_slope;
                                         }
                                     }
                                     uint4 o;

@@ -142,8 +142,10 @@ __global__ void __launch_bounds__(256) l1_fwd_kernel(const void* __restrict__ pr
 
 template <int DT>
 __global__ void __launch_bounds__(256) l1_bwd_kernel(const void* __restrict__ pred, const float* __restrict__ tgt,
-                                                     size_t n, float g /* w*scale/n */, void* __restrict__ dpred) {
+                                                     size_t n, float g /* w*scale/n */, void* __restrict__ dpred,
+                                                     const float* __restrict__ g_dev /* optional device factor */) {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    if (g_dev != nullptr) g *= *g_dev;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride) {
         float d = ldp<DT>(pred, i) - tgt[i];
         float s = d > 0.f ? g : (d < 0.f ? -g : 0.f);

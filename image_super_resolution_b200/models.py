@@ -9,7 +9,8 @@ whole net is issued by `_NetPlan` as a fixed schedule of fused conv launches ove
   * `*add_rate + x` (RDB) and the RRDB skip are epilogue terms (two residuals on the last conv of an RRDB),
   * Scaler: conv 64->256 as four 64-channel launches with nn.PixelShuffle(2) folded into the store,
   * BatchNorm of `ResNet` in eval mode is folded into the packed filter (fuse_conv_and_bn semantics).
-There is no PyTorch fallback: CPU tensors, train-mode BatchNorm and autograd are refused (training step: next).
+Training (autograd) goes through training.TrainPlan; there is no PyTorch fallback: CPU tensors and train-mode
+BatchNorm are refused.
 """
 from __future__ import annotations
 
@@ -228,11 +229,12 @@ class _SRNet(nn.Module):
     def forward(self, inputs: torch.Tensor) -> torch.Tensor:
         if not inputs.is_cuda:
             raise RuntimeError("the B200 path has no CPU fallback: move the model and its inputs to a CUDA device")
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and self.training:
-            raise NotImplementedError("training forward/backward on the sm_100a path is the next §8 row (a17-a19); "
-                                      "use .eval() / torch.no_grad() for inference")
         if inputs.dim() != 4 or inputs.shape[1] != 3:
             raise RuntimeError(f"expected [N,3,h,w], got {tuple(inputs.shape)}")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # train.py:55 — forward with saved activations; backward runs on the same kernels (training.py)
+            from .training import train_forward
+            return train_forward(self, inputs)
         return self._plan(inputs.device).forward(inputs.float().contiguous())
 
     def __deepcopy__(self, memo):  # ModelEMA deep-copies the model (utils/models.py:25): plans are derived caches
@@ -241,7 +243,7 @@ class _SRNet(nn.Module):
         new = cls.__new__(cls)
         memo[id(self)] = new
         for k, v in self.__dict__.items():
-            if k != "_plans":
+            if k not in ("_plans", "_train_plans"):
                 new.__dict__[k] = copy.deepcopy(v, memo)
         return new
 

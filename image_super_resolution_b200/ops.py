@@ -158,3 +158,103 @@ def bias_grad(dy: torch.Tensor, dy_planes: int, dy_off: int, cout: int, db: torc
     ctx = Context.get(dy.device.index or 0)
     check(lib().srb_bias_grad(ctx.handle, dy.data_ptr(), dy_planes, dy_off, cout, db.data_ptr(), float(scale),
                               dtype_code(dy.dtype), N, H, W, _stream_ptr(dy.device)), "srb_bias_grad")
+
+
+# ---------------------------------------------------------------------------------------------
+# training-step operators (device-resident fp32 master weights, backward glue)
+# ---------------------------------------------------------------------------------------------
+class DeviceConv:
+    """Packed operand of a (cout, cin, k) conv that is (re)filled on the device from fp32 master weights."""
+
+    def __init__(self, ctx: Context, cout: int, cin: int, k: int, dtype):
+        self.ctx, self.cout, self.cin, self.k = ctx, cout, cin, k
+        self.dtype = dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_alloc_conv(ctx.handle, cout, cin, k, self.dtype, C.byref(h)), "srb_alloc_conv")
+        self.handle = h
+
+    def fill(self, weight: torch.Tensor, bias: torch.Tensor | None = None, o_off: int = 0, c_off: int = 0,
+             transpose: bool = False):
+        """weight: fp32 [O][I][k][k] on the device.  transpose=True packs the data-gradient operand."""
+        _require_cuda(weight, "weight")
+        if weight.dtype != torch.float32:
+            raise RuntimeError("master weights must be fp32")
+        check(lib().srb_pack_conv_device(self.ctx.handle, self.handle, weight.data_ptr(), weight.shape[0], weight.shape[1],
+                                         o_off, c_off, 1 if transpose else 0,
+                                         None if (bias is None or transpose) else bias.data_ptr(),
+                                         _stream_ptr(weight.device)), "srb_pack_conv_device")
+
+    __del__ = PackedConv.__del__
+
+
+def conv2d_ex(pc, x, x_planes, x_off, y, y_planes, y_off, N, H, W, residual=None, res_planes=0, res_off=0, res_nplanes=0,
+              res_scale=1.0, res2=None, res2_planes=0, res2_off=0, res2_scale=1.0, out_scale=1.0, slope=0.0, flags=0,
+              mask=None, mask_planes=0, mask_off=0, mask_p0=0, mask_p1=0, mask_slope=0.0):
+    """General conv launch (srb_conv2d_ex): forward epilogues plus the backward extras (partial residual, mask)."""
+    a = _lib.ConvArgs()
+    a.x, a.x_c8_total, a.x_c8_off = x.data_ptr(), x_planes, x_off
+    a.y, a.y_c8_total, a.y_c8_off = y.data_ptr(), y_planes, y_off
+    if residual is not None:
+        flags |= F_RESIDUAL
+        a.residual, a.res_c8_total, a.res_c8_off, a.res_nplanes = residual.data_ptr(), res_planes, res_off, res_nplanes
+    a.res_scale = res_scale
+    if res2 is not None:
+        a.res2, a.res2_c8_total, a.res2_c8_off, a.res2_scale = res2.data_ptr(), res2_planes, res2_off, res2_scale
+    a.out_scale, a.lrelu_slope = out_scale, slope
+    if mask is not None:
+        flags |= _lib.F_MASK
+        a.mask, a.mask_c8_total, a.mask_c8_off = mask.data_ptr(), mask_planes, mask_off
+        a.mask_p0, a.mask_p1, a.mask_slope = mask_p0, mask_p1, mask_slope
+    a.flags, a.N, a.H, a.W = flags, N, H, W
+    check(lib().srb_conv2d_ex(pc.ctx.handle, pc.handle, C.byref(a), _stream_ptr(x.device)), "srb_conv2d_ex")
+
+
+def conv9_wgrad(x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, dw, N, H, W, scale=1.0):
+    _require_cuda(x, "x"); _require_cuda(dy, "dy"); _require_cuda(dw, "dw")
+    if dw.dtype != torch.float32 or dw.numel() != cout * cin * 81:
+        raise RuntimeError("conv9_wgrad: dw must be fp32 [cout, cin, 9, 9]")
+    ctx = Context.get(x.device.index or 0)
+    check(lib().srb_conv9_wgrad(ctx.handle, x.data_ptr(), x_planes, x_off, cin, dy.data_ptr(), dy_planes, dy_off, cout,
+                                dw.data_ptr(), float(scale), dtype_code(x.dtype), N, H, W, _stream_ptr(x.device)),
+          "srb_conv9_wgrad")
+
+
+def tanh_bwd_to_c8(gout: torch.Tensor, out: torch.Tensor, dtype, scale: float = 1.0) -> torch.Tensor:
+    _require_cuda(gout, "gout"); _require_cuda(out, "out")
+    N, Cc, H, W = out.shape
+    if Cc != 3 or gout.shape != out.shape or gout.dtype != torch.float32 or out.dtype != torch.float32:
+        raise RuntimeError("tanh_bwd_to_c8: fp32 [N,3,H,W] tensors expected")
+    g8 = c8_empty(N, 1, H, W, dtype, out.device)
+    ctx = Context.get(out.device.index or 0)
+    check(lib().srb_tanh_bwd_to_c8(ctx.handle, gout.data_ptr(), out.data_ptr(), g8.data_ptr(), float(scale), dtype_code(dtype),
+                                   N, H, W, _stream_ptr(out.device)), "srb_tanh_bwd_to_c8")
+    return g8
+
+
+def pixunshuffle_mask(g_u: torch.Tensor, u: torch.Tensor, g_s: torch.Tensor, slope: float):
+    """g_u, u: [N][p][2H][2W][8]; g_s: [N][4p][H][W][8]."""
+    N, p, H2, W2, _ = g_u.shape
+    ctx = Context.get(g_u.device.index or 0)
+    check(lib().srb_pixunshuffle_mask(ctx.handle, g_u.data_ptr(), u.data_ptr(), g_s.data_ptr(), p, float(slope),
+                                      dtype_code(g_u.dtype), N, H2 // 2, W2 // 2, _stream_ptr(g_u.device)), "srb_pixunshuffle_mask")
+
+
+def c8_axpby_mask(a, a_planes, a_off, alpha, b, b_planes, b_off, beta, act, act_planes, act_off, slope, out, out_planes, out_off,
+                  planes, N, H, W):
+    ctx = Context.get(a.device.index or 0)
+    check(lib().srb_c8_axpby_mask(ctx.handle, a.data_ptr(), a_planes, a_off, float(alpha),
+                                  None if b is None else b.data_ptr(), b_planes, b_off, float(beta),
+                                  None if act is None else act.data_ptr(), act_planes, act_off, float(slope),
+                                  out.data_ptr(), out_planes, out_off, planes, dtype_code(a.dtype), N, H, W,
+                                  _stream_ptr(a.device)), "srb_c8_axpby_mask")
+
+
+def l1_loss_bwd_dev(pred: torch.Tensor, tgt: torch.Tensor, grad_out: torch.Tensor, w: float = 1.0) -> torch.Tensor:
+    """dpred = grad_out (device scalar) * w * sign(pred - tgt) / numel."""
+    _require_cuda(pred, "pred"); _require_cuda(tgt, "tgt"); _require_cuda(grad_out, "grad_out")
+    ctx = Context.get(pred.device.index or 0)
+    g = torch.empty_like(pred)
+    go = grad_out.detach().reshape(()).float().contiguous()
+    check(lib().srb_l1_loss_bwd_dev(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w), 1.0,
+                                    go.data_ptr(), g.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_bwd_dev")
+    return g

@@ -1,0 +1,321 @@
+"""Training step of the class nets on the sm_100a kernels: forward with saved activations, backward (data, weight and
+bias gradients), wrapped as one torch.autograd.Function so that the reference's `train()` (train.py:41-67: autocast
+forward, loss, GradScaler backward, clip, Adam, EMA) runs unmodified on the drop-in `EResNet`.
+
+Schedule, all launches through the C ABI:
+  forward   the inference schedule of models._NetPlan, but every RDB owns its 192-channel dense buffer (saved for
+            backward; torch.cat stays free) and the operands are bf16 re-packed on the device from the fp32 masters;
+  backward  per conv: weight gradient (tcgen05, srb_conv2d_wgrad; FP32-pipe srb_conv9_wgrad for the 9x9 head/tail),
+            bias gradient, and the data gradient as a conv of dY with the transposed / rotated filter that
+            ACCUMULATES in place into the dense block's gradient buffer and applies the LeakyReLU mask of the slice
+            that becomes final with that launch (no separate elementwise kernels inside the trunk).
+  DDP       the flat fp32 gradient arena is all-reduced once (NCCL over NVLink) before autograd hands the gradients
+            to the optimizer, i.e. between train.py:57 and :58.
+There is no PyTorch / cuDNN fallback: anything unsupported raises.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from . import ops
+from ._lib import Context
+
+
+def _chunks(c: int) -> list[int]:
+    """Output-channel chunks (64, then a 32 remainder) of a data-gradient conv with c output channels."""
+    return [64] * (c // 64) + ([32] if c % 64 else [])
+
+
+def _slope_of(act) -> float:
+    if isinstance(act, nn.LeakyReLU):
+        return float(act.negative_slope)
+    if isinstance(act, (nn.Identity, nn.Tanh)):
+        return 1.0
+    raise NotImplementedError(f"activation {act.__class__.__name__} has no fused backward")
+
+
+class TrainPlan:
+    """Device-packed operands, saved activations and the fwd/bwd launch schedule of one EResNet on one device."""
+
+    def __init__(self, net, device: torch.device, dtype="bf16", allreduce: bool = True):
+        for m in net.modules():
+            if isinstance(m, nn.BatchNorm2d):
+                raise NotImplementedError("train-mode BatchNorm (ResNet) is not on the sm_100a path (SURVEY §8(f) rank 3); "
+                                          "train EResNet, or run ResNet in eval mode")
+        self.net, self.device, self.dt = net, device, ops.dtype_code(dtype)
+        self.ctx = Context.get(device.index)
+        self.allreduce = allreduce
+        mk = lambda co, ci, k: ops.DeviceConv(self.ctx, co, ci, k, self.dt)  # noqa: E731
+        with torch.cuda.device(device):
+            self.f_conv0 = mk(64, 3, 9)
+            self.rdbs = []
+            for rrdb in net.residual:
+                for rdb in rrdb.net:
+                    fwd = [mk(32, 64 + 32 * i, 3) for i in range(4)] + [mk(64, 192, 3)]
+                    dg = [[mk(co, 32, 3) for co in _chunks(64 + 32 * i)] for i in range(4)] + [[mk(64, 64, 3) for _ in range(3)]]
+                    self.rdbs.append((rrdb, rdb, fwd, dg))
+            self.f_conv1, self.d_conv1 = mk(64, 64, 3), mk(64, 64, 3)
+            self.f_scaler = [[mk(64, 64, 3) for _ in range(4)] for _ in net.scaler]
+            self.d_scaler = [mk(64, 256, 3) for _ in net.scaler]
+            self.f_conv2, self.d_conv2 = mk(3, 64, 9), mk(64, 3, 9)
+        self.params = list(net.parameters())
+        self.numel = sum(p.numel() for p in self.params)
+        self.flat_grad = torch.zeros(self.numel, dtype=torch.float32, device=device)
+        self.grad_views, o = {}, 0
+        for p in self.params:
+            self.grad_views[id(p)] = self.flat_grad[o:o + p.numel()].view_as(p)
+            o += p.numel()
+        self.versions = None
+        self.buf = {}
+        self.saved = None
+        self.launches = 0
+
+    # ---- operands -------------------------------------------------------------------------------------------
+    def _versions(self):
+        return tuple(p._version for p in self.params)
+
+    def repack(self):
+        """fp32 master weights (device) -> bf16 UMMA operands, forward and data-gradient layouts."""
+        n = self.net
+        for p in self.params:
+            if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("training needs contiguous fp32 CUDA parameters (model.to(device) first)")
+        self.f_conv0.fill(n.conv0.conv.weight.data, n.conv0.conv.bias.data)
+        for _, rdb, fwd, dg in self.rdbs:
+            for i in range(5):
+                m = getattr(rdb, f"conv{i}") if i < 4 else rdb.conv
+                w, b = m.conv.weight.data, m.conv.bias.data
+                fwd[i].fill(w, b)
+                o = 0
+                for pk in dg[i]:
+                    pk.fill(w, transpose=True, o_off=o)
+                    o += pk.cout
+        self.f_conv1.fill(n.conv1.conv.weight.data, n.conv1.conv.bias.data)
+        self.d_conv1.fill(n.conv1.conv.weight.data, transpose=True)
+        for s, fq, dq in zip(n.scaler, self.f_scaler, self.d_scaler):
+            w, b = s.net[0].conv.weight.data, s.net[0].conv.bias.data
+            for q in range(4):
+                fq[q].fill(w, b, o_off=64 * q)
+            dq.fill(w, transpose=True)
+        self.f_conv2.fill(n.conv2.conv.weight.data, n.conv2.conv.bias.data)
+        self.d_conv2.fill(n.conv2.conv.weight.data, transpose=True)
+        self.versions = self._versions()
+
+    def _b(self, name, N, planes, H, W):
+        key = (name, N, planes, H, W)
+        t = self.buf.get(name)
+        if t is None or t[0] != key:
+            t = (key, ops.c8_empty(N, planes, H, W, self.dt, self.device))
+            self.buf[name] = t
+        return t[1]
+
+    # ---- forward --------------------------------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        n = self.net
+        if self.versions != self._versions():
+            self.repack()
+        N, _, H, W = x.shape
+        cv = ops.conv2d_ex
+        xin = self._b("xin", N, 1, H, W)
+        ops.nchw_to_c8(x, out=xin, planes=1, dtype=self.dt)
+        nr = len(self.rdbs)
+        dense = [self._b(f"dense{r}", N, 24, H, W) for r in range(nr)]
+        tr = self._b("tr", N, 8, H, W)
+        s0 = _slope_of(n.conv0.act)
+        cv(self.f_conv0, xin, 1, 0, dense[0], 24, 0, N, H, W, slope=s0, flags=ops.F_LRELU)     # x0 = planes 0..7 of dense[0]
+        for r, (rrdb, rdb, fwd, _) in enumerate(self.rdbs):
+            D = dense[r]
+            dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
+            for i in range(4):
+                si = _slope_of(getattr(rdb, f"conv{i}").act)
+                cv(fwd[i], D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=si, flags=ops.F_LRELU)
+            a = float(rdb.add_rate)
+            if r % 3 < 2:    # add_rate*conv + rdb_in  (utils/models.py:271)
+                cv(fwd[4], D, 24, 0, dst, dplanes, 0, N, H, W, residual=D, res_planes=24, res_off=0, res_scale=1.0, out_scale=a)
+            else:            # R*(add_rate*conv + rdb_in) + rrdb_in  (utils/models.py:317)
+                R = float(rrdb.add_rate)
+                cv(fwd[4], D, 24, 0, dst, dplanes, 0, N, H, W, residual=D, res_planes=24, res_off=0, res_scale=R,
+                   out_scale=R * a, res2=dense[r - 2], res2_planes=24, res2_off=0, res2_scale=1.0)
+        t = self._b("t", N, 8, H, W)
+        cv(self.f_conv1, tr, 8, 0, t, 8, 0, N, H, W, residual=dense[0], res_planes=24, res_off=0)   # + long skip x0
+        cur, h, w, ups = t, H, W, []
+        for k, (s, fq) in enumerate(zip(n.scaler, self.f_scaler)):
+            up = self._b(f"up{k}", N, 8, 2 * h, 2 * w)
+            sl = _slope_of(s.net[2])
+            for q in range(4):
+                cv(fq[q], cur, 8, 0, up, 8, 2 * q, N, h, w, slope=sl, flags=ops.F_LRELU | ops.F_PIXSHUF2)
+            ups.append((cur, up, h, w))
+            cur, h, w = up, 2 * h, 2 * w
+        out = torch.empty((N, 3, h, w), dtype=torch.float32, device=self.device)
+        tanh = ops.F_TANH if isinstance(n.conv2.act, nn.Tanh) else 0
+        cv(self.f_conv2, cur, 8, 0, out, 0, 0, N, h, w, flags=tanh | ops.F_F32OUT)
+        self.saved = dict(N=N, H=H, W=W, xin=xin, dense=dense, tr=tr, t=t, ups=ups, out=out, tanh=bool(tanh))
+        return out
+
+    # ---- backward -------------------------------------------------------------------------------------------
+    def _wb(self, m, x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, N, H, W, scale=1.0):
+        """weight + bias gradient of a 3x3 conv module into the flat arena."""
+        ops.conv2d_wgrad(x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, self.grad_views[id(m.conv.weight)], N, H, W,
+                         scale=scale)
+        ops.bias_grad(dy, dy_planes, dy_off, cout, self.grad_views[id(m.conv.bias)], N, H, W, scale=scale)
+
+    def backward(self, gout: torch.Tensor) -> list[torch.Tensor]:
+        sv, n = self.saved, self.net
+        if sv is None:
+            raise RuntimeError("backward without a saved forward")
+        N, H, W = sv["N"], sv["H"], sv["W"]
+        cv = ops.conv2d_ex
+        self.flat_grad.zero_()
+        gout = gout.float().contiguous()
+        h2, w2 = sv["out"].shape[2], sv["out"].shape[3]
+        # ---- tail conv: tanh', 9x9 weight gradient, data gradient = 9x9 conv 3 -> 64 (head kernel, transposed filter)
+        if not sv["tanh"]:
+            raise NotImplementedError("tail conv without tanh")
+        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt)
+        up_last = sv["ups"][-1][1] if sv["ups"] else sv["t"]
+        ops.conv9_wgrad(up_last, 8, 0, 64, g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.weight)], N, h2, w2)
+        ops.bias_grad(g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.bias)], N, h2, w2)
+        g_cur = self._b("g_up_last", N, 8, h2, w2)
+        cv(self.d_conv2, g2, 1, 0, g_cur, 8, 0, N, h2, w2)
+        # ---- scalers, last to first: LeakyReLU' + PixelShuffle inverse, wgrad 64 -> 256, dgrad 256 -> 64
+        for k in range(len(sv["ups"]) - 1, -1, -1):
+            cur_in, up, h, w = sv["ups"][k]
+            s = n.scaler[k]
+            g_s = self._b(f"g_s{k}", N, 32, h, w)
+            ops.pixunshuffle_mask(g_cur, up, g_s, _slope_of(s.net[2]))
+            self._wb(s.net[0], cur_in, 8, 0, 64, g_s, 32, 0, 256, N, h, w)
+            g_in = self._b(f"g_in{k}", N, 8, h, w)
+            cv(self.d_scaler[k], g_s, 32, 0, g_in, 8, 0, N, h, w)
+            g_cur = g_in
+        g_t = g_cur                                         # gradient of t = x0 + conv1(trunk)
+        # ---- conv1
+        self._wb(n.conv1, sv["tr"], 8, 0, 64, g_t, 8, 0, 64, N, H, W)
+        gy, gy_planes = self._b("g_tr", N, 8, H, W), 8     # gradient of the current RRDB's output
+        cv(self.d_conv1, g_t, 8, 0, gy, 8, 0, N, H, W)
+        # ---- RRDBs, last to first
+        pool = [self._b(f"G{j}", N, 24, H, W) for j in range(4)]
+        nr = len(self.rdbs)
+        for r in range(nr - 1, -1, -1):
+            rrdb, rdb, _, dg = self.rdbs[r]
+            D = sv["dense"][r]
+            d = r % 3
+            a, R = float(rdb.add_rate), float(rrdb.add_rate)
+            if d == 2:                                      # start of an RRDB (backward order): three buffers != gy
+                free = [b for b in pool if b is not gy][:3]
+                gsrc, gsrc_planes = gy, gy_planes
+                s_out, s_res = a * R, R
+            else:
+                gsrc, gsrc_planes = G, 24
+                s_out, s_res = a, 1.0
+            G = free[2 - d]
+            sl = [_slope_of(getattr(rdb, f"conv{i}").act) for i in range(4)]
+            # final conv 192 -> 64 (no activation): out = s_out*conv(cat) + s_res*rdb_in
+            self._wb(rdb.conv, D, 24, 0, 192, gsrc, gsrc_planes, 0, 64, N, H, W, scale=s_out)
+            for c in range(3):
+                kw = {}
+                if c == 0:
+                    kw = dict(residual=gsrc, res_planes=gsrc_planes, res_off=0, res_scale=s_res)
+                if c == 2:
+                    kw = dict(mask=D, mask_planes=24, mask_off=16, mask_p0=4, mask_p1=8, mask_slope=sl[3])
+                cv(dg[4][c], gsrc, gsrc_planes, 0, G, 24, 8 * c, N, H, W, out_scale=s_out, **kw)
+            # conv3..conv0: dY = masked slice of G, accumulate the data gradient into planes below it
+            for i in range(3, -1, -1):
+                cin = 64 + 32 * i
+                dy_off = 8 + 4 * i
+                self._wb(getattr(rdb, f"conv{i}"), D, 24, 0, cin, G, 24, dy_off, 32, N, H, W)
+                o = 0
+                for pk in dg[i]:
+                    p0, pl = o // 8, pk.cout // 8
+                    kw = dict(residual=G, res_planes=24, res_off=p0, res_scale=1.0)
+                    if i > 0:
+                        m0, m1 = 8 + 4 * (i - 1), 8 + 4 * i          # planes of o_{i-1}: final after this launch
+                        lo, hi = max(m0, p0), min(m1, p0 + pl)
+                        if lo < hi:
+                            kw.update(mask=D, mask_planes=24, mask_off=p0, mask_p0=lo - p0, mask_p1=hi - p0, mask_slope=sl[i - 1])
+                    elif d == 0:                                      # + the RRDB skip (utils/models.py:317)
+                        kw.update(res2=gy, res2_planes=gy_planes, res2_off=0, res2_scale=1.0)
+                    cv(pk, G, 24, dy_off, G, 24, p0, N, H, W, **kw)
+                    o += pk.cout
+            if d == 0:
+                gy, gy_planes = G, 24
+        # ---- head conv: total gradient of x0 = trunk path + long skip, LeakyReLU', 9x9 weight gradient
+        gx0 = self._b("gx0", N, 8, H, W)
+        ops.c8_axpby_mask(gy, gy_planes, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
+        ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.weight)], N, H, W)
+        ops.bias_grad(gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.bias)], N, H, W)
+        self.saved = None
+        if self.allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            allreduce_mean_(self.flat_grad)
+        return [self.grad_views[id(p)] for p in self.params]
+
+
+def allreduce_mean_(flat: torch.Tensor):
+    """One all-reduce of the flat gradient arena (NCCL over NVLink); mean over ranks like DDP."""
+    ws = dist.get_world_size()
+    if dist.get_backend() == "nccl":
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+    else:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat.div_(ws)
+    return flat
+
+
+class _NetFunction(torch.autograd.Function):
+    """preds = net(lr) with the whole forward / backward on the sm_100a kernels (train.py:55,57)."""
+
+    @staticmethod
+    def forward(ctx, x, plan, *params):
+        ctx.plan = plan
+        return plan.forward(x)
+
+    @staticmethod
+    def backward(ctx, gout):
+        grads = ctx.plan.backward(gout)
+        return (None, None, *grads)
+
+
+def train_forward(net, x: torch.Tensor) -> torch.Tensor:
+    plans = net.__dict__.setdefault("_train_plans", {})
+    plan = plans.get(x.device)
+    if plan is None:
+        plan = plans[x.device] = TrainPlan(net, x.device, getattr(net, "train_operand_dtype", "bf16"))
+    return _NetFunction.apply(x.float().contiguous(), plan, *plan.params)
+
+
+class _L1Function(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, tgt, w):
+        ctx.save_for_backward(pred, tgt)
+        ctx.w = w
+        return ops.l1_loss_fwd(pred, tgt, w)
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, tgt = ctx.saved_tensors
+        return ops.l1_loss_bwd_dev(pred, tgt, g, ctx.w), None, None
+
+
+class L1Loss(nn.Module):
+    """Drop-in for utils/loss.py:32-39 (`sum(loss_weight * mean|x - y|)`) on the library's reduction kernels.
+    The reference's default `L1Loss()` builds an int64 Parameter and raises on current torch; here the
+    default is accepted and stored as float.  `loss_weight` is never given to an optimizer (train.py:265)."""
+
+    def __init__(self, lossweight=1):
+        super().__init__()
+        self.loss_weight = nn.Parameter(torch.tensor([float(lossweight)]), requires_grad=False)
+        self._w = (None, None)
+
+    def _weight(self) -> float:
+        v = self.loss_weight._version
+        if self._w[0] != v:
+            self._w = (v, float(self.loss_weight.detach().sum().item()))
+        return self._w[1]
+
+    def forward(self, inputs: torch.Tensor, ground_truth: torch.Tensor) -> torch.Tensor:
+        if not inputs.is_cuda:
+            raise RuntimeError("the B200 path has no CPU fallback: move predictions and targets to a CUDA device")
+        pred = inputs.contiguous()
+        tgt = ground_truth.float().contiguous()
+        return _L1Function.apply(pred, tgt, self._weight())

@@ -39,6 +39,7 @@ extern "C" {
 #define SRB_F_U8OUT 8      /* TanhToArrayImage fused: uint8 NCHW output (utils/models.py:448-451)    */
 #define SRB_F_PIXSHUF2 16  /* nn.PixelShuffle(2) folded into the store (utils/models.py:580-583)     */
 #define SRB_F_F32OUT 32    /* tail conv: fp32 NCHW output                                            */
+#define SRB_F_MASK 64      /* backward: output planes [mask_p0,mask_p1) *= LeakyReLU'(saved activation) */
 
 typedef struct srb_ctx srb_ctx;
 typedef struct srb_weights srb_weights;
@@ -79,6 +80,34 @@ int srb_conv2d_fwd_res2(srb_ctx* ctx, const srb_weights* w, const void* x, int x
                         int y_c8_total, int y_c8_off, const void* residual, int res_c8_total, int res_c8_off,
                         float res_scale, const void* res2, int res2_c8_total, int res2_c8_off, float res2_scale,
                         float out_scale, float lrelu_slope, int flags, int N, int H, int W, srb_stream_t stream);
+
+/* General form of the conv launch (the two functions above fill this struct).  The extra fields serve the
+ * backward pass of train.py:57 (autograd of RDB.forward, utils/models.py:265-271): the data gradient of a conv
+ * is a conv of dY with the transposed, 180-degree-rotated filter (srb_pack_conv_device, transpose=1) that
+ * ACCUMULATES into a slice of the dense block's gradient buffer (residual == y, res_nplanes limits the planes that
+ * carry a residual) and applies the LeakyReLU backward mask of the slice that becomes final with this launch. */
+typedef struct srb_conv_args {
+    const void* x; int x_c8_total, x_c8_off;
+    void* y; int y_c8_total, y_c8_off;
+    const void* residual; int res_c8_total, res_c8_off; int res_nplanes /* 0 = all output planes */; float res_scale;
+    const void* res2; int res2_c8_total, res2_c8_off; float res2_scale;
+    float out_scale, lrelu_slope;
+    int flags;
+    const void* mask; int mask_c8_total, mask_c8_off /* plane of the mask buffer matching output plane 0 */;
+    int mask_p0, mask_p1 /* output planes [p0,p1) are masked */; float mask_slope;
+    int N, H, W;
+} srb_conv_args;
+int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_args* args, srb_stream_t stream);
+
+/* Training keeps fp32 master weights on the DEVICE (nn.Parameter storage); these re-derive the packed 16-bit
+ * operand from them every step without a host round trip.  srb_alloc_conv creates an empty packed filter for a
+ * (cout, cin, k) conv; srb_pack_conv_device fills it from w_src = fp32 [src_o][src_i][k][k] on the device:
+ *   transpose = 0:  W'[o][c] = w_src[o_off + o][c_off + c]            (forward operand of a cout/cin slice)
+ *   transpose = 1:  W'[o][c][dy][dx] = w_src[c_off + c][o_off + o][k-1-dy][k-1-dx]   (data-gradient operand)
+ * bias_src (device, may be NULL -> zero bias) is read at [o_off + o] when transpose = 0 and ignored otherwise. */
+int srb_alloc_conv(srb_ctx* ctx, int cout, int cin, int k, int dtype, srb_weights** out);
+int srb_pack_conv_device(srb_ctx* ctx, srb_weights* w, const float* w_src, int src_o, int src_i, int o_off, int c_off,
+                         int transpose, const float* bias_src, srb_stream_t stream);
 
 /* Normalize.forward (utils/datasets.py:65-71, uint8 branch baked into model.pt):
  * uint8 NCHW [N,3,H,W] -> ((x/255)-mean)/std as one C8 plane (channels 3..7 zero). */
@@ -127,6 +156,24 @@ int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, 
 int srb_bias_grad(srb_ctx* ctx, const void* dy, int dy_c8_total, int dy_c8_off, int cout, float* db, float scale, int dtype,
                   int N, int H, int W, srb_stream_t stream);
 
+/* 9x9 weight gradients of the head (cin=3,cout=64; utils/models.py:625) and tail (cin=64,cout=3; :636) convs, FP32 pipe.
+ * Same contract as srb_conv2d_wgrad: dw fp32 OIHW [cout][cin][9][9], accumulated into. */
+int srb_conv9_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy, int dy_c8_total,
+                    int dy_c8_off, int cout, float* dw_oihw, float scale, int dtype, int N, int H, int W, srb_stream_t stream);
+
+/* Backward glue that is not a conv epilogue (autograd of EResNet.forward, utils/models.py:645-650):
+ * tanh' of the tail conv: g_c8[n,y,x,0..2] = scale * gout * (1 - out^2), gout/out fp32 NCHW [N,3,H,W], g_c8 one C8 plane. */
+int srb_tanh_bwd_to_c8(srb_ctx* ctx, const float* gout, const float* out, void* g_c8, float scale, int dtype, int N, int H, int W,
+                       srb_stream_t stream);
+/* Scaler backward (utils/models.py:580-583): g_s[n,4c+2i+j,y,x] = g_u[n,c,2y+i,2x+j] * LeakyReLU'(u); g_u, u: c8_u planes at
+ * 2H x 2W; g_s: 4*c8_u planes at H x W. */
+int srb_pixunshuffle_mask(srb_ctx* ctx, const void* g_u, const void* u, void* g_s, int c8_u, float slope, int dtype, int N, int H,
+                          int W, srb_stream_t stream);
+/* out = (alpha*a + beta*b) * LeakyReLU'(act) over C8 plane slices; b and act may be NULL (gradient fan-in at the long skip). */
+int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off, float alpha, const void* b, int b_c8_total,
+                      int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off, float slope, void* out,
+                      int out_c8_total, int out_c8_off, int planes, int dtype, int N, int H, int W, srb_stream_t stream);
+
 /* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
  * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
 int srb_l1_partials_len(void);
@@ -134,6 +181,10 @@ int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float*
                     float* loss_out, float* partials, srb_stream_t stream);
 int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
                     float grad_scale, void* dpred, srb_stream_t stream);
+
+/* same, times a device scalar *grad_out_dev (the upstream gradient of the loss, e.g. GradScaler's scale: train.py:57) */
+int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                        float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream);
 
 #ifdef __cplusplus
 }

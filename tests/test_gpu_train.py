@@ -1,0 +1,223 @@
+"""GPU parity of the training step: every backward kernel against fp32 autograd of the same op,
+then the whole EResNet forward + backward + L1 loss against fp32 autograd of the oracle restatement.
+
+Tolerances (bf16 operands, fp32 accumulate): loss rel-err <= 1e-2, per-tensor gradient cosine >= 0.999
+(>= 0.99 for the deepest nets' smallest bias tensors is NOT accepted: the bar is stated per test)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def ctx(dev):
+    from image_super_resolution_b200._lib import Context
+    return Context.get(0)
+
+
+def _cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a @ b) / (a.norm() * b.norm() + 1e-300))
+
+
+def _q(t):
+    return t.to(torch.bfloat16).float()
+
+
+@pytest.mark.parametrize("cout,cin,k", [(32, 64, 3), (64, 192, 3), (64, 3, 9), (3, 64, 9), (64, 256, 3)])
+def test_device_pack_matches_host_pack(ctx, dev, cout, cin, k):
+    """srb_pack_conv_device (fp32 masters on the device) == srb_pack_conv (host) through the conv they feed."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(1)
+    w = torch.randn(cout, cin, k, k, generator=g) / np.sqrt(cin * k * k)
+    b = torch.randn(cout, generator=g) * 0.1
+    N, H, W = 2, 24, 40
+    x = torch.randn(N, cin, H, W, generator=g)
+    xc = ops.nchw_to_c8(x.to(dev), dtype="bf16")
+    host = ops.PackedConv(ctx, w, b, dtype="bf16")
+    devp = ops.DeviceConv(ctx, cout, cin, k, "bf16")
+    devp.fill(w.to(dev), b.to(dev))
+    outs = []
+    for pc in (host, devp):
+        if cout == 3:
+            y = torch.zeros(N, 3, H, W, device=dev)
+            ops.conv2d_fwd(pc, xc, xc.shape[1], 0, y, 0, 0, N, H, W, flags=ops.F_F32OUT)
+            outs.append(y.cpu())
+        else:
+            y = torch.zeros(N, cout // 8, H, W, 8, dtype=torch.bfloat16, device=dev)
+            ops.conv2d_fwd(pc, xc, xc.shape[1], 0, y, cout // 8, 0, N, H, W)
+            outs.append(y.float().cpu())
+    assert torch.equal(outs[0], outs[1])
+
+
+@pytest.mark.parametrize("cout,cin,k", [(32, 96, 3), (64, 192, 3), (32, 64, 3), (64, 64, 3), (256, 64, 3), (3, 64, 9)])
+def test_data_gradient_is_transposed_conv(ctx, dev, cout, cin, k):
+    """dX of y = conv(x, w): chunks of <= 64 channels of conv(dY, w^T rot180), vs fp32 autograd on bf16-rounded operands."""
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200.training import _chunks
+    g = torch.Generator().manual_seed(2)
+    N, H, W = 2, 20, 28
+    w = _q(torch.randn(cout, cin, k, k, generator=g) / np.sqrt(cin * k * k))
+    dy = _q(torch.randn(N, cout, H, W, generator=g))
+    x = torch.zeros(N, cin, H, W, requires_grad=True)
+    F.conv2d(x, w, padding=k // 2).backward(dy)
+    ref = x.grad
+    dyc = ops.nchw_to_c8(dy.to(dev), dtype="bf16")
+    planes = (cin + 7) // 8
+    G = torch.zeros(N, planes, H, W, 8, dtype=torch.bfloat16, device=dev)
+    wd = w.to(dev)
+    if k == 9 or cin <= 64:
+        pk = ops.DeviceConv(ctx, cin, cout, k, "bf16")
+        pk.fill(wd, transpose=True)
+        ops.conv2d_ex(pk, dyc, dyc.shape[1], 0, G, planes, 0, N, H, W)
+    else:
+        o = 0
+        for co in _chunks(cin):
+            pk = ops.DeviceConv(ctx, co, cout, k, "bf16")
+            pk.fill(wd, transpose=True, o_off=o)
+            ops.conv2d_ex(pk, dyc, dyc.shape[1], 0, G, planes, o // 8, N, H, W)
+            o += co
+    out = ops.c8_to_nchw(G, cin).cpu()
+    err = (out - ref).abs().max().item()
+    assert err <= 8e-3 * ref.abs().max().item() + 1e-3, err
+
+
+def test_dgrad_accumulates_in_place_with_mask(ctx, dev):
+    """G[0:64] += dgrad ; planes 4..7 of the slice are multiplied by LeakyReLU'(saved activation) afterwards."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    N, H, W = 1, 18, 26
+    w = _q(torch.randn(32, 64, 3, 3, generator=g) / 24)
+    dy = _q(torch.randn(N, 32, H, W, generator=g))
+    g0 = _q(torch.randn(N, 64, H, W, generator=g))
+    act = _q(torch.randn(N, 64, H, W, generator=g))
+    x = torch.zeros(N, 64, H, W, requires_grad=True)
+    F.conv2d(x, w, padding=1).backward(dy)
+    ref = x.grad + g0
+    ref[:, 32:] = ref[:, 32:] * torch.where(act[:, 32:] > 0, 1.0, 0.01)
+    Gb = torch.zeros(N, 12, H, W, 8, dtype=torch.bfloat16, device=dev)
+    ops.nchw_to_c8(g0.to(dev), out=Gb, planes=12, off=0, dtype="bf16")
+    ops.nchw_to_c8(dy.to(dev), out=Gb, planes=12, off=8, dtype="bf16")
+    A = ops.nchw_to_c8(act.to(dev), dtype="bf16")
+    pk = ops.DeviceConv(ctx, 64, 32, 3, "bf16")
+    pk.fill(w.to(dev), transpose=True)
+    ops.conv2d_ex(pk, Gb, 12, 8, Gb, 12, 0, N, H, W, residual=Gb, res_planes=12, res_off=0, mask=A, mask_planes=8, mask_off=0,
+                  mask_p0=4, mask_p1=8, mask_slope=0.01)
+    out = ops.c8_to_nchw(Gb, 64).cpu()
+    err = (out - ref).abs().max().item()
+    assert err <= 1e-2 * ref.abs().max().item() + 1e-3, err
+
+
+@pytest.mark.parametrize("which", ["head", "tail"])
+def test_conv9_weight_gradient(ctx, dev, which):
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    cin, cout = (3, 64) if which == "head" else (64, 3)
+    N, H, W = 2, 37, 29
+    x = _q(torch.randn(N, cin, H, W, generator=g))
+    dy = _q(torch.randn(N, cout, H, W, generator=g))
+    w = torch.zeros(cout, cin, 9, 9, requires_grad=True)
+    F.conv2d(x, w, padding=4).backward(dy)
+    xc = ops.nchw_to_c8(x.to(dev), dtype="bf16")
+    dc = ops.nchw_to_c8(dy.to(dev), dtype="bf16")
+    dw = torch.zeros(cout, cin, 9, 9, device=dev)
+    ops.conv9_wgrad(xc, xc.shape[1], 0, cin, dc, dc.shape[1], 0, cout, dw, N, H, W, scale=0.5)
+    err = (dw.cpu() * 2 - w.grad).abs().max().item()
+    assert err <= 1e-4 * w.grad.abs().max().item() + 1e-4, err
+
+
+def test_tanh_bwd_and_pixunshuffle_mask(dev):
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    N, H, W = 2, 10, 14
+    out = torch.tanh(torch.randn(N, 3, H, W, generator=g))
+    go = torch.randn(N, 3, H, W, generator=g)
+    g8 = ops.tanh_bwd_to_c8(go.to(dev), out.to(dev), "bf16")
+    got = ops.c8_to_nchw(g8, 3).cpu()
+    assert torch.equal(got, _q(go * (1 - out * out)))
+    # Scaler backward: s [N,256,H,W] -> u = lrelu(pixel_shuffle(s))
+    s = torch.randn(N, 256, H, W, generator=g)
+    uq = _q(F.leaky_relu(F.pixel_shuffle(s, 2), 0.01))
+    gu = _q(torch.randn(N, 64, 2 * H, 2 * W, generator=g))
+    ref = F.pixel_unshuffle(gu * torch.where(uq > 0, 1.0, 0.01), 2)
+    guc = ops.nchw_to_c8(gu.to(dev), dtype="bf16")
+    uc = ops.nchw_to_c8(uq.to(dev), dtype="bf16")
+    gs = torch.zeros(N, 32, H, W, 8, dtype=torch.bfloat16, device=dev)
+    ops.pixunshuffle_mask(guc, uc, gs, 0.01)
+    assert torch.equal(ops.c8_to_nchw(gs, 256).cpu(), _q(ref))
+
+
+@pytest.mark.parametrize("nb,scale,n,hw", [(1, 2, 2, 24), (2, 4, 1, 16)])
+def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
+    """forward + L1 loss + backward of the drop-in EResNet vs fp32 autograd of the oracle restatement."""
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200.training import L1Loss
+    from oracle import nets_oracle as no  # checker only
+    torch.manual_seed(100)
+    net = models.EResNet(nb, 0.2, scale)
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in net.state_dict().items()}
+    hr, lr = no.make_lr_hr(7, n, hw * scale, scale)
+    ref_out = no.resnet_forward.__wrapped__(lr, sd, nb, 0.2, scale, 0.01)
+    ref_loss = (ref_out - hr).abs().mean()
+    ref_loss.backward()
+    net = net.to(dev).train()
+    loss_fn = L1Loss().to(dev)
+    out = net(lr.to(dev))
+    loss = loss_fn(out, hr.to(dev))
+    (loss * 1024.0).backward()             # GradScaler-style scaled backward
+    torch.cuda.synchronize()
+    from image_super_resolution_b200._lib import Context
+    Context.get(0).check_device()
+    assert (out.detach().cpu() - ref_out.detach()).abs().max().item() <= 2e-2
+    assert abs(loss.item() - ref_loss.item()) <= 1e-2 * ref_loss.item()
+    worst = 1.0
+    for name, p in net.named_parameters():
+        gref = sd[name].grad
+        got = p.grad.detach().cpu() / 1024.0
+        c = _cos(got, gref)
+        worst = min(worst, c)
+        assert c >= 0.995, (name, c)
+        assert abs(float(got.norm()) / float(gref.norm()) - 1) <= 5e-2, (name, float(got.norm()), float(gref.norm()))
+    print("worst per-tensor gradient cosine:", worst)
+
+
+def test_reference_train_loop_runs_on_dropin(dev):
+    """train.py:41-67 restated call for call (zero_grad, autocast fwd, loss, scaled backward, unscale, clip, step, update,
+    schedule) on the drop-in model and loss: the loss goes down on a fixed batch."""
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200.training import L1Loss
+    from oracle import nets_oracle as no
+    torch.manual_seed(100)
+    net = models.EResNet(1, 0.2, 2).to(dev).train()
+    hr, lr = no.make_lr_hr(11, 4, 32, 2)
+    hr, lr = hr.to(dev), lr.to(dev)
+    loss_fn = L1Loss().to(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3, betas=(0.9, 0.999))
+    scaler = torch.amp.GradScaler("cuda")
+    losses = []
+    for _ in range(20):
+        opt.zero_grad()
+        with torch.autocast(device_type="cuda"):
+            preds = net(lr)
+            loss = loss_fn(preds, hr)
+        scaler.scale(loss).backward()
+        scaler.unscale_(opt)
+        torch.nn.utils.clip_grad_norm_(net.parameters(), 10)
+        scaler.step(opt)
+        scaler.update()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0] * 0.95 and all(np.isfinite(losses)), losses
