@@ -53,6 +53,13 @@ SIGNATURES = {
     "srb_tanh_bwd_to_c8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_pixunshuffle_mask": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _i, _vp]),
     "srb_c8_axpby_mask": (_i, [_vp, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "srb_grad_batch_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
+    "srb_grad_batch_units": (_i, [_vp]),
+    "srb_grad_batch_run": (_i, [_vp, _vp, _i, _vp]),
+    "srb_grad_batch_destroy": (None, [_vp]),
+    "srb_pack_batch_create": (_i, [_vp, _vp, _i, C.POINTER(_vp)]),
+    "srb_pack_batch_run": (_i, [_vp, _vp, _vp]),
+    "srb_pack_batch_destroy": (None, [_vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
@@ -123,6 +130,19 @@ class ConvArgs(C.Structure):
                 ("out_scale", _f), ("lrelu_slope", _f), ("flags", _i),
                 ("mask", _vp), ("mask_c8_total", _i), ("mask_c8_off", _i), ("mask_p0", _i), ("mask_p1", _i), ("mask_slope", _f),
                 ("N", _i), ("H", _i), ("W", _i)]
+
+
+class GradJob(C.Structure):
+    """srb_grad_job of include/srb200.h."""
+    _fields_ = [("x", _vp), ("x_c8_total", _i), ("x_c8_off", _i), ("cin", _i),
+                ("dy", _vp), ("dy_c8_total", _i), ("dy_c8_off", _i), ("cout", _i),
+                ("dw", _vp), ("db", _vp), ("scale", _f), ("N", _i), ("H", _i), ("W", _i)]
+
+
+class PackJob(C.Structure):
+    """srb_pack_job of include/srb200.h."""
+    _fields_ = [("w", _vp), ("w_src", _vp), ("src_o", _i), ("src_i", _i), ("o_off", _i), ("c_off", _i), ("transpose", _i),
+                ("bias_src", _vp)]
 
 
 def f32_ptr(arr):

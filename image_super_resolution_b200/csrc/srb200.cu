@@ -853,3 +853,161 @@ extern "C" int srb_conv9_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int 
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// batched weight / bias gradients and batched operand packing (one launch per training step each)
+// ------------------------------------------------------------------------------------------
+struct srb_grad_batch {
+    int dtype = 0, nunits = 0, nbias = 0;
+    CUtensorMap* d_tmaps = nullptr;
+    WgradUnit* d_units = nullptr;
+    BiasUnit* d_bias = nullptr;
+};
+
+extern "C" void srb_grad_batch_destroy(srb_grad_batch* b) {
+    if (!b) return;
+    if (b->d_tmaps) cudaFree(b->d_tmaps);
+    if (b->d_units) cudaFree(b->d_units);
+    if (b->d_bias) cudaFree(b->d_bias);
+    delete b;
+}
+
+extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int n, int dtype, srb_grad_batch** out) {
+    if (!ctx || !jobs || !out || n <= 0) return fail(SRB_EINVAL, "srb_grad_batch_create: NULL / empty argument");
+    using G = WgradGeom;
+    std::vector<CUtensorMap> tmaps;
+    std::vector<WgradUnit> units;
+    std::vector<BiasUnit> bias;
+    for (int j = 0; j < n; ++j) {
+        const srb_grad_job& q = jobs[j];
+        if (!q.dy || q.N <= 0 || q.H <= 0 || q.W <= 0) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: bad dY / shape", j);
+        if ((uintptr_t)q.dy & 15) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: dY must be 16-byte aligned", j);
+        const int dyp = (q.cout + 7) / 8;
+        if (q.dy_c8_off < 0 || q.dy_c8_off + dyp > q.dy_c8_total) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: dY slice out of range", j);
+        if (q.dw) {
+            if (!q.x || ((uintptr_t)q.x & 15)) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: x must be a 16-byte aligned buffer", j);
+            if (q.cin % 8 || q.cout % 8) return fail(SRB_ENOSUP, "srb_grad_batch_create: job %d: cin=%d cout=%d must be multiples of 8", j, q.cin, q.cout);
+            if (q.x_c8_off < 0 || q.x_c8_off + q.cin / 8 > q.x_c8_total) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: x slice out of range", j);
+            CUtensorMap tx, tdy;
+            int rc;
+            if ((rc = encode_c8_map(ctx, &tx, q.x, q.N, q.H, q.W, q.x_c8_total, G::XW, G::XH, G::XPLANES))) return rc;
+            if ((rc = encode_c8_map(ctx, &tdy, q.dy, q.N, q.H, q.W, q.dy_c8_total, G::TW, G::TH, G::DYPLANES))) return rc;
+            const int tm = (int)tmaps.size() / 2;
+            tmaps.push_back(tx); tmaps.push_back(tdy);
+            WgradUnit u{};
+            u.tm = tm; u.N = q.N; u.H = q.H; u.W = q.W;
+            u.tiles_x = (q.W + G::TW - 1) / G::TW; u.tiles_y = (q.H + G::TH - 1) / G::TH;
+            long long nt = (long long)u.tiles_x * u.tiles_y * q.N;
+            if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: %lld tiles", j, nt);
+            u.num_tiles = (int)nt; u.cin_total = q.cin; u.scale = q.scale; u.dw = q.dw;
+            for (int ci0 = 0; ci0 < q.cin; ci0 += 128)
+                for (int co0 = 0; co0 < q.cout; co0 += 32) {
+                    u.cin0 = ci0; u.cout0 = co0;
+                    u.cin_blk = q.cin - ci0 < 128 ? q.cin - ci0 : 128;
+                    u.cout_blk = q.cout - co0 < 32 ? q.cout - co0 : 32;
+                    u.x_c8_off = q.x_c8_off + ci0 / 8; u.dy_c8_off = q.dy_c8_off + co0 / 8;
+                    units.push_back(u);
+                }
+        }
+        if (q.db)
+            for (int pl = 0; pl < dyp; ++pl) {
+                BiasUnit bu{};
+                bu.dy = (const uint4*)q.dy; bu.c8_total = q.dy_c8_total; bu.plane = q.dy_c8_off + pl; bu.N = q.N;
+                bu.HW = (size_t)q.H * q.W; bu.scale = q.scale; bu.db = q.db + pl * 8;
+                bu.nch = q.cout - pl * 8 < 8 ? q.cout - pl * 8 : 8;
+                bias.push_back(bu);
+            }
+    }
+    srb_grad_batch* b = new srb_grad_batch();
+    b->dtype = dtype; b->nunits = (int)units.size(); b->nbias = (int)bias.size();
+    cudaSetDevice(ctx->device);
+    bool ok = true;
+    if (!tmaps.empty()) ok = ok && cudaMalloc(&b->d_tmaps, tmaps.size() * sizeof(CUtensorMap)) == cudaSuccess &&
+        cudaMemcpy(b->d_tmaps, tmaps.data(), tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice) == cudaSuccess;
+    if (!units.empty()) ok = ok && cudaMalloc(&b->d_units, units.size() * sizeof(WgradUnit)) == cudaSuccess &&
+        cudaMemcpy(b->d_units, units.data(), units.size() * sizeof(WgradUnit), cudaMemcpyHostToDevice) == cudaSuccess;
+    if (!bias.empty()) ok = ok && cudaMalloc(&b->d_bias, bias.size() * sizeof(BiasUnit)) == cudaSuccess &&
+        cudaMemcpy(b->d_bias, bias.data(), bias.size() * sizeof(BiasUnit), cudaMemcpyHostToDevice) == cudaSuccess;
+    if (!ok) { srb_grad_batch_destroy(b); return fail(SRB_ENOMEM, "srb_grad_batch_create: device allocation / upload failed"); }
+    *out = b;
+    return SRB_OK;
+}
+
+extern "C" int srb_grad_batch_units(const srb_grad_batch* b) { return b ? b->nunits : 0; }
+
+extern "C" int srb_grad_batch_run(srb_ctx* ctx, srb_grad_batch* b, int splitk, srb_stream_t stream) {
+    if (!ctx || !b) return fail(SRB_EINVAL, "srb_grad_batch_run: NULL argument");
+    if (splitk < 1) splitk = 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    using G = WgradGeom;
+    if (b->nunits) {
+        if (b->dtype == SRB_DT_BF16) {
+            CUDA_TRY(cudaFuncSetAttribute(wgrad_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+            wgrad_batch_kernel<true><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk);
+        } else {
+            CUDA_TRY(cudaFuncSetAttribute(wgrad_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+            wgrad_batch_kernel<false><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk);
+        }
+        CUDA_TRY(cudaGetLastError());
+    }
+    if (b->nbias) {
+        if (b->dtype == SRB_DT_BF16) bias_grad_batch_kernel<true><<<b->nbias, 256, 0, st>>>(b->d_bias);
+        else bias_grad_batch_kernel<false><<<b->nbias, 256, 0, st>>>(b->d_bias);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return SRB_OK;
+}
+
+struct srb_pack_batch {
+    int n = 0; size_t max_total = 0;
+    PackJob* d_jobs = nullptr;
+};
+
+extern "C" void srb_pack_batch_destroy(srb_pack_batch* b) {
+    if (!b) return;
+    if (b->d_jobs) cudaFree(b->d_jobs);
+    delete b;
+}
+
+extern "C" int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int n, srb_pack_batch** out) {
+    if (!ctx || !jobs || !out || n <= 0) return fail(SRB_EINVAL, "srb_pack_batch_create: NULL / empty argument");
+    std::vector<PackJob> v(n);
+    size_t mx = 0;
+    for (int j = 0; j < n; ++j) {
+        const srb_pack_job& q = jobs[j];
+        srb_weights* w = q.w;
+        if (!w || !q.w_src) return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: NULL", j);
+        const int so_need = q.transpose ? q.c_off + w->cin : q.o_off + w->cout;
+        const int si_need = q.transpose ? q.o_off + w->cout : q.c_off + w->cin;
+        if (q.o_off < 0 || q.c_off < 0 || so_need > q.src_o || si_need > q.src_i)
+            return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: slice exceeds the source filter", j);
+        PackJob& pj = v[j];
+        pj.p.mode = w->mode; pj.p.c8in = w->c8in; pj.p.nout = w->nout; pj.p.kblocks = w->kblocks; pj.p.cout = w->cout;
+        pj.p.cin = w->cin; pj.p.k = w->k; pj.p.src_i = q.src_i; pj.p.o_off = q.o_off; pj.p.c_off = q.c_off;
+        pj.p.transpose = q.transpose; pj.p.total = w->pack_bytes / 2;
+        pj.w = q.w_src; pj.pack = (uint16_t*)w->d_pack; pj.bias_src = q.transpose ? nullptr : q.bias_src; pj.bias_dst = w->d_bias;
+        pj.bf16 = w->dtype == SRB_DT_BF16;
+        if (pj.p.total > mx) mx = pj.p.total;
+    }
+    srb_pack_batch* b = new srb_pack_batch();
+    b->n = n; b->max_total = mx;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&b->d_jobs, n * sizeof(PackJob)) != cudaSuccess ||
+        cudaMemcpy(b->d_jobs, v.data(), n * sizeof(PackJob), cudaMemcpyHostToDevice) != cudaSuccess) {
+        srb_pack_batch_destroy(b);
+        return fail(SRB_ENOMEM, "srb_pack_batch_create: device allocation / upload failed");
+    }
+    *out = b;
+    return SRB_OK;
+}
+
+extern "C" int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t stream) {
+    if (!ctx || !b) return fail(SRB_EINVAL, "srb_pack_batch_run: NULL argument");
+    int gx = (int)((b->max_total + 256 * 8 - 1) / (256 * 8));
+    if (gx < 1) gx = 1;
+    if (gx > 64) gx = 64;
+    dim3 grid(gx, b->n);
+    pack_conv_batch_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(b->d_jobs);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}

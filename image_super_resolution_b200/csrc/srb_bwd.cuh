@@ -17,9 +17,8 @@ struct PackParams {
 };
 
 template <bool BF16>
-__global__ void __launch_bounds__(256) pack_conv_kernel(const float* __restrict__ w, uint16_t* __restrict__ pack, PackParams p,
-                                                        const float* __restrict__ bias_src, float* __restrict__ bias_dst) {
-    const size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+__device__ __forceinline__ void pack_conv_element(const float* __restrict__ w, uint16_t* __restrict__ pack, const PackParams& p,
+                                                  const float* __restrict__ bias_src, float* __restrict__ bias_dst, size_t e) {
     if (e < (size_t)p.nout) bias_dst[e] = (bias_src != nullptr && (int)e < p.cout) ? bias_src[p.o_off + e] : 0.f;
     if (e >= p.total) return;
     const int step = 2 * p.nout * 8;
@@ -62,6 +61,26 @@ __global__ void __launch_bounds__(256) pack_conv_kernel(const float* __restrict_
     if constexpr (BF16) { __nv_bfloat16 h = __float2bfloat16_rn(v); r = *reinterpret_cast<uint16_t*>(&h); }
     else { __half h = __float2half_rn(v); r = *reinterpret_cast<uint16_t*>(&h); }
     pack[e] = r;
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(256) pack_conv_kernel(const float* __restrict__ w, uint16_t* __restrict__ pack, PackParams p,
+                                                        const float* __restrict__ bias_src, float* __restrict__ bias_dst) {
+    pack_conv_element<BF16>(w, pack, p, bias_src, bias_dst, blockIdx.x * (size_t)blockDim.x + threadIdx.x);
+}
+
+// all operands of a net in ONE launch (the training step re-derives ~800 packed filters from the fp32 masters)
+struct PackJob {
+    PackParams p;
+    const float* w; uint16_t* pack; const float* bias_src; float* bias_dst;
+    int bf16;
+};
+__global__ void __launch_bounds__(256) pack_conv_batch_kernel(const PackJob* __restrict__ jobs) {
+    const PackJob& j = jobs[blockIdx.y];
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < j.p.total; e += (size_t)gridDim.x * blockDim.x) {
+        if (j.bf16) pack_conv_element<true>(j.w, j.pack, j.p, j.bias_src, j.bias_dst, e);
+        else pack_conv_element<false>(j.w, j.pack, j.p, j.bias_src, j.bias_dst, e);
+    }
 }
 
 // ------------------------------------------------------------------------------------------

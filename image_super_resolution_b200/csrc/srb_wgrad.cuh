@@ -181,4 +181,163 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const uint4* __restrict_
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Batched weight gradients: every (conv, 128-channel cin block, 32-channel cout block) of a whole backward pass is a
+// UNIT of one launch.  The weight gradients are off the critical path of backpropagation (only the data gradients
+// chain), so the training step defers them to the end and runs them as one grid of units x splitk CTAs: with
+// splitk = 1 each dW element is produced by exactly one CTA (no cross-CTA reduction, no contended atomics) and the
+// 148 SMs are kept busy by ~450 independent units instead of 148-way split-K of one small filter at a time.
+// Tensor maps live in a device array (one pair per conv).
+// ------------------------------------------------------------------------------------------
+struct WgradUnit {
+    int tm;                       // index of the conv's tensor-map pair: tmaps[2*tm] = X, tmaps[2*tm+1] = dY
+    int x_c8_off, dy_c8_off;
+    int cin_blk, cout_blk, cin_total, cin0, cout0;
+    int N, H, W, tiles_x, tiles_y, num_tiles;
+    float scale;
+    float* dw;
+};
+
+template <bool BF16>
+__global__ void __launch_bounds__(256, 1) wgrad_batch_kernel(const CUtensorMap* __restrict__ tmaps, const WgradUnit* __restrict__ units,
+                                                             int splitk) {
+    using G = WgradGeom;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* s_st = smem;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::STAGES * G::STAGE_STRIDE);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + 4;
+    uint64_t* done = bars + 8;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 10);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int uidx = blockIdx.x / splitk, part = blockIdx.x - uidx * splitk;
+    const WgradUnit u = units[uidx];
+    const CUtensorMap* tmap_x = tmaps + 2 * u.tm;
+    const CUtensorMap* tmap_dy = tmap_x + 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < G::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(done, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(tmap_x);
+        tma_prefetch_desc(tmap_dy);
+    }
+    if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, 512); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+    const int tiles_per_img = u.tiles_x * u.tiles_y;
+
+    if (warp == 0) {
+        int s = 0; uint32_t ph = 0;
+        for (int tile = part; tile < u.num_tiles; tile += splitk) {
+            const int n = tile / tiles_per_img;
+            const int r = tile - n * tiles_per_img;
+            const int ty = r / u.tiles_x, tx = r - ty * u.tiles_x;
+            mbar_wait(&empty[s], ph ^ 1, 21);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&full[s], G::XBYTES + G::DYBYTES);
+                uint8_t* st = s_st + s * G::STAGE_STRIDE;
+                tma_load_4d(st, tmap_x, &full[s], (tx * G::TW - 1) * 4, ty * G::TH - 1, u.x_c8_off, n);
+                tma_load_4d(st + G::X_STRIDE, tmap_dy, &full[s], tx * G::TW * 4, ty * G::TH, u.dy_c8_off, n);
+            }
+            __syncwarp();
+            if (++s == G::STAGES) { s = 0; ph ^= 1; }
+        }
+    } else if (warp == 1) {
+        constexpr uint32_t idesc = umma_idesc_f16_mn(128, G::NOUT, BF16 ? 1 : 0);
+        const uint64_t a_desc0 = umma_desc_nosw(0, 128, G::XPLANE);
+        const uint64_t b_desc0 = umma_desc_nosw(0, 128, G::DYPLANE);
+        int s = 0; uint32_t ph = 0; int it = 0;
+        for (int tile = part; tile < u.num_tiles; tile += splitk, ++it) {
+            mbar_wait(&full[s], ph, 22);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t xa = smem_u32(s_st + s * G::STAGE_STRIDE);
+                const uint64_t a_desc = a_desc0 + (uint64_t)(xa >> 4);
+                const uint64_t b_desc = b_desc0 + (uint64_t)((xa + G::X_STRIDE) >> 4);
+#pragma unroll 1
+                for (int r = 0; r < G::TH; ++r) {
+                    const uint64_t bd = b_desc + (uint64_t)((r * G::DYROWP) >> 4);
+#pragma unroll
+                    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx)
+                            umma_f16_ss(tmem_base + (dy * 3 + dx) * G::NOUT,
+                                        a_desc + (uint64_t)(((r + dy) * G::XROWP + dx * 16) >> 4), bd, idesc, (it | r) != 0);
+                }
+                umma_commit(&empty[s]);
+            }
+            __syncwarp();
+            if (++s == G::STAGES) { s = 0; ph ^= 1; }
+        }
+        if (elect_one()) umma_commit(done);
+        __syncwarp();
+    } else if (warp >= 4) {
+        const int lg = warp & 3;
+        const int ci = lg * 32 + lane;
+        mbar_wait(done, 0, 23);
+        tc_fence_after();
+        const bool has_tiles = part < u.num_tiles;
+#pragma unroll 1
+        for (int tap = 0; tap < 9; ++tap) {
+            uint32_t rr[32];
+            tmem_ld32(tmem_base + tap * G::NOUT + ((uint32_t)(lg * 32) << 16), rr);
+            tmem_ld_wait();
+            if (has_tiles && ci < u.cin_blk) {
+                float* dst = u.dw + ((size_t)u.cout0 * u.cin_total + u.cin0 + ci) * 9 + tap;
+#pragma unroll
+                for (int co = 0; co < 32; ++co)
+                    if (co < u.cout_blk) atomicAdd(dst + (size_t)co * u.cin_total * 9, __uint_as_float(rr[co]) * u.scale);
+            }
+        }
+        tc_fence_before();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
+}
+
+// batched bias gradients: one CTA per (conv, 8-channel plane); fixed-order in-CTA reduction, plain store (deterministic)
+struct BiasUnit {
+    const uint4* dy; int c8_total, plane; int N; size_t HW;
+    float scale; float* db; int nch;   // db points at the plane's first channel; nch real channels in it
+};
+
+template <bool BF16>
+__global__ void __launch_bounds__(256) bias_grad_batch_kernel(const BiasUnit* __restrict__ units) {
+    const BiasUnit u = units[blockIdx.x];
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int n = 0; n < u.N; ++n) {
+        const uint4* base = u.dy + ((size_t)n * u.c8_total + u.plane) * u.HW;
+        for (size_t px = threadIdx.x; px < u.HW; px += 256) {
+            const uint4 q = base[px];
+            const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float2 f;
+                if constexpr (BF16) f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&qq[k]));
+                else f = __half22float2(*reinterpret_cast<const __half2*>(&qq[k]));
+                acc[2 * k] += f.x; acc[2 * k + 1] += f.y;
+            }
+        }
+    }
+    __shared__ float s_acc[8][8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        float v = acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 8 && (int)threadIdx.x < u.nch) {
+        float v = 0.f;
+        for (int w = 0; w < 8; ++w) v += s_acc[w][threadIdx.x];
+        u.db[threadIdx.x] += v * u.scale;
+    }
+}
+
 }  // namespace srb

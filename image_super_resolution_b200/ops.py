@@ -219,12 +219,13 @@ def conv9_wgrad(x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, dw, N, H, 
           "srb_conv9_wgrad")
 
 
-def tanh_bwd_to_c8(gout: torch.Tensor, out: torch.Tensor, dtype, scale: float = 1.0) -> torch.Tensor:
+def tanh_bwd_to_c8(gout: torch.Tensor, out: torch.Tensor, dtype, scale: float = 1.0, g8: torch.Tensor | None = None) -> torch.Tensor:
     _require_cuda(gout, "gout"); _require_cuda(out, "out")
     N, Cc, H, W = out.shape
     if Cc != 3 or gout.shape != out.shape or gout.dtype != torch.float32 or out.dtype != torch.float32:
         raise RuntimeError("tanh_bwd_to_c8: fp32 [N,3,H,W] tensors expected")
-    g8 = c8_empty(N, 1, H, W, dtype, out.device)
+    if g8 is None:
+        g8 = c8_empty(N, 1, H, W, dtype, out.device)
     ctx = Context.get(out.device.index or 0)
     check(lib().srb_tanh_bwd_to_c8(ctx.handle, gout.data_ptr(), out.data_ptr(), g8.data_ptr(), float(scale), dtype_code(dtype),
                                    N, H, W, _stream_ptr(out.device)), "srb_tanh_bwd_to_c8")
@@ -258,3 +259,65 @@ def l1_loss_bwd_dev(pred: torch.Tensor, tgt: torch.Tensor, grad_out: torch.Tenso
     check(lib().srb_l1_loss_bwd_dev(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w), 1.0,
                                     go.data_ptr(), g.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_bwd_dev")
     return g
+
+
+class GradBatch:
+    """All 3x3 weight gradients + bias gradients of one backward pass: one launch each (srb_grad_batch_*).
+    jobs: dicts with x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, dw, db, scale, N, H, W (x/dw or db may be None)."""
+
+    def __init__(self, ctx: Context, jobs: list[dict], dtype):
+        self.ctx = ctx
+        self._keep = jobs                      # the tensors named by the jobs must outlive the batch
+        arr = (_lib.GradJob * len(jobs))()
+        for a, j in zip(arr, jobs):
+            a.x = None if j.get("x") is None else j["x"].data_ptr()
+            a.x_c8_total, a.x_c8_off, a.cin = j.get("x_planes", 0), j.get("x_off", 0), j.get("cin", 0)
+            a.dy, a.dy_c8_total, a.dy_c8_off, a.cout = j["dy"].data_ptr(), j["dy_planes"], j["dy_off"], j["cout"]
+            a.dw = None if j.get("dw") is None else j["dw"].data_ptr()
+            a.db = None if j.get("db") is None else j["db"].data_ptr()
+            a.scale, a.N, a.H, a.W = float(j.get("scale", 1.0)), j["N"], j["H"], j["W"]
+        h = C.c_void_p()
+        check(lib().srb_grad_batch_create(ctx.handle, arr, len(jobs), dtype_code(dtype), C.byref(h)), "srb_grad_batch_create")
+        self.handle = h
+        self.units = lib().srb_grad_batch_units(h)
+
+    def run(self, device, splitk: int = 1):
+        check(lib().srb_grad_batch_run(self.ctx.handle, self.handle, splitk, _stream_ptr(device)), "srb_grad_batch_run")
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_grad_batch_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+class PackBatch:
+    """All packed operands of a net re-derived from the fp32 master weights in one launch (srb_pack_batch_*).
+    jobs: (DeviceConv, weight, bias_or_None, o_off, c_off, transpose)."""
+
+    def __init__(self, ctx: Context, jobs: list[tuple]):
+        self.ctx = ctx
+        self._keep = jobs
+        arr = (_lib.PackJob * len(jobs))()
+        for a, (pc, w, b, o_off, c_off, tr) in zip(arr, jobs):
+            if w.dtype != torch.float32 or not w.is_cuda or not w.is_contiguous():
+                raise RuntimeError("master weights must be contiguous fp32 CUDA tensors")
+            a.w, a.w_src, a.src_o, a.src_i = pc.handle, w.data_ptr(), w.shape[0], w.shape[1]
+            a.o_off, a.c_off, a.transpose = o_off, c_off, 1 if tr else 0
+            a.bias_src = None if (b is None or tr) else b.data_ptr()
+        h = C.c_void_p()
+        check(lib().srb_pack_batch_create(ctx.handle, arr, len(jobs), C.byref(h)), "srb_pack_batch_create")
+        self.handle = h
+
+    def run(self, device):
+        check(lib().srb_pack_batch_run(self.ctx.handle, self.handle, _stream_ptr(device)), "srb_pack_batch_run")
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_pack_batch_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass

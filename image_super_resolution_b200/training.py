@@ -70,37 +70,48 @@ class TrainPlan:
         self.versions = None
         self.buf = {}
         self.saved = None
-        self.launches = 0
+        self.use_graphs = True
+        self.wgrad_splitk = 1
+        self.graphs = {}
+        self.pack_batch, self.pack_ptrs = None, None
+        self.grad_batch, self.grad_key, self._gjobs = None, None, None
 
     # ---- operands -------------------------------------------------------------------------------------------
     def _versions(self):
         return tuple(p._version for p in self.params)
 
-    def repack(self):
-        """fp32 master weights (device) -> bf16 UMMA operands, forward and data-gradient layouts."""
+    def _pack_jobs(self):
         n = self.net
-        for p in self.params:
-            if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
-                raise RuntimeError("training needs contiguous fp32 CUDA parameters (model.to(device) first)")
-        self.f_conv0.fill(n.conv0.conv.weight.data, n.conv0.conv.bias.data)
+        jobs = [(self.f_conv0, n.conv0.conv.weight.data, n.conv0.conv.bias.data, 0, 0, False)]
         for _, rdb, fwd, dg in self.rdbs:
             for i in range(5):
                 m = getattr(rdb, f"conv{i}") if i < 4 else rdb.conv
                 w, b = m.conv.weight.data, m.conv.bias.data
-                fwd[i].fill(w, b)
+                jobs.append((fwd[i], w, b, 0, 0, False))
                 o = 0
                 for pk in dg[i]:
-                    pk.fill(w, transpose=True, o_off=o)
+                    jobs.append((pk, w, None, o, 0, True))
                     o += pk.cout
-        self.f_conv1.fill(n.conv1.conv.weight.data, n.conv1.conv.bias.data)
-        self.d_conv1.fill(n.conv1.conv.weight.data, transpose=True)
+        jobs.append((self.f_conv1, n.conv1.conv.weight.data, n.conv1.conv.bias.data, 0, 0, False))
+        jobs.append((self.d_conv1, n.conv1.conv.weight.data, None, 0, 0, True))
         for s, fq, dq in zip(n.scaler, self.f_scaler, self.d_scaler):
             w, b = s.net[0].conv.weight.data, s.net[0].conv.bias.data
             for q in range(4):
-                fq[q].fill(w, b, o_off=64 * q)
-            dq.fill(w, transpose=True)
-        self.f_conv2.fill(n.conv2.conv.weight.data, n.conv2.conv.bias.data)
-        self.d_conv2.fill(n.conv2.conv.weight.data, transpose=True)
+                jobs.append((fq[q], w, b, 64 * q, 0, False))
+            jobs.append((dq, w, None, 0, 0, True))
+        jobs.append((self.f_conv2, n.conv2.conv.weight.data, n.conv2.conv.bias.data, 0, 0, False))
+        jobs.append((self.d_conv2, n.conv2.conv.weight.data, None, 0, 0, True))
+        return jobs
+
+    def repack(self):
+        """fp32 master weights (device) -> bf16 UMMA operands, forward and data-gradient layouts: one launch."""
+        ptrs = tuple(p.data_ptr() for p in self.params)
+        if self.pack_batch is None or self.pack_ptrs != ptrs:
+            for p in self.params:
+                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("training needs contiguous fp32 CUDA parameters (model.to(device) first)")
+            self.pack_batch, self.pack_ptrs = ops.PackBatch(self.ctx, self._pack_jobs()), ptrs
+        self.pack_batch.run(self.device)
         self.versions = self._versions()
 
     def _b(self, name, N, planes, H, W):
@@ -111,11 +122,58 @@ class TrainPlan:
             self.buf[name] = t
         return t[1]
 
-    # ---- forward --------------------------------------------------------------------------------------------
+    # ---- CUDA graphs: the step is ~2 000 launches of 5-20 us kernels, host-bound from Python otherwise ------------
+    def _graph_key(self, x):
+        return (tuple(x.shape), tuple(p.data_ptr() for p in self.params))
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        n = self.net
-        if self.versions != self._versions():
+        if not self.use_graphs:
+            if self.versions != self._versions():
+                self.repack()
+            return self._forward_impl(x)
+        key = self._graph_key(x)
+        st = self.graphs.get("key")
+        if st != key:                                        # new shape / re-allocated parameters: capture again
+            self.graphs = {"key": key, "x": x.clone()}
             self.repack()
+            self._forward_impl(self.graphs["x"])             # eager warm-up: allocates buffers, sets kernel attributes
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.repack()
+                self.graphs["out"] = self._forward_impl(self.graphs["x"])
+            self.graphs["fwd"] = g
+            self.graphs["saved"] = self.saved
+        self.graphs["x"].copy_(x)
+        self.graphs["fwd"].replay()
+        self.saved = self.graphs["saved"]
+        return self.graphs["out"]
+
+    def backward(self, gout: torch.Tensor) -> list[torch.Tensor]:
+        if not self.use_graphs:
+            grads = self._backward_impl(gout)
+        else:
+            if self.saved is None:
+                raise RuntimeError("backward without a saved forward")
+            if "bwd" not in self.graphs:
+                self.graphs["gout"] = gout.float().contiguous().clone()
+                self._backward_impl(self.graphs["gout"])
+                torch.cuda.synchronize(self.device)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self.graphs["grads"] = self._backward_impl(self.graphs["gout"])
+                self.graphs["bwd"] = g
+            self.graphs["gout"].copy_(gout)
+            self.graphs["bwd"].replay()
+            grads = self.graphs["grads"]
+        self.saved = None
+        if self.allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            allreduce_mean_(self.flat_grad)
+        return grads
+
+    # ---- forward --------------------------------------------------------------------------------------------
+    def _forward_impl(self, x: torch.Tensor) -> torch.Tensor:
+        n = self.net
         N, _, H, W = x.shape
         cv = ops.conv2d_ex
         xin = self._b("xin", N, 1, H, W)
@@ -156,27 +214,32 @@ class TrainPlan:
 
     # ---- backward -------------------------------------------------------------------------------------------
     def _wb(self, m, x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, N, H, W, scale=1.0):
-        """weight + bias gradient of a 3x3 conv module into the flat arena."""
-        ops.conv2d_wgrad(x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, self.grad_views[id(m.conv.weight)], N, H, W,
-                         scale=scale)
-        ops.bias_grad(dy, dy_planes, dy_off, cout, self.grad_views[id(m.conv.bias)], N, H, W, scale=scale)
+        """weight + bias gradient of a 3x3 conv module: recorded once as a job of the deferred batch (run at the end of
+        backward: weight gradients are off the critical path and every unit is then owned by one CTA)."""
+        if self._gjobs is not None:
+            self._gjobs.append(dict(x=x, x_planes=x_planes, x_off=x_off, cin=cin, dy=dy, dy_planes=dy_planes, dy_off=dy_off,
+                                    cout=cout, dw=self.grad_views[id(m.conv.weight)], db=self.grad_views[id(m.conv.bias)],
+                                    scale=scale, N=N, H=H, W=W))
 
-    def backward(self, gout: torch.Tensor) -> list[torch.Tensor]:
+    def _backward_impl(self, gout: torch.Tensor) -> list[torch.Tensor]:
         sv, n = self.saved, self.net
         if sv is None:
             raise RuntimeError("backward without a saved forward")
         N, H, W = sv["N"], sv["H"], sv["W"]
         cv = ops.conv2d_ex
         self.flat_grad.zero_()
+        gkey = (N, H, W, tuple(sv["out"].shape))
+        self._gjobs = [] if (self.grad_batch is None or self.grad_key != gkey) else None
         gout = gout.float().contiguous()
         h2, w2 = sv["out"].shape[2], sv["out"].shape[3]
         # ---- tail conv: tanh', 9x9 weight gradient, data gradient = 9x9 conv 3 -> 64 (head kernel, transposed filter)
         if not sv["tanh"]:
             raise NotImplementedError("tail conv without tanh")
-        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt)
+        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt, g8=self._b("g2", N, 1, h2, w2))
         up_last = sv["ups"][-1][1] if sv["ups"] else sv["t"]
         ops.conv9_wgrad(up_last, 8, 0, 64, g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.weight)], N, h2, w2)
-        ops.bias_grad(g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.bias)], N, h2, w2)
+        if self._gjobs is not None:
+            self._gjobs.append(dict(dy=g2, dy_planes=1, dy_off=0, cout=3, db=self.grad_views[id(n.conv2.conv.bias)], N=N, H=h2, W=w2))
         g_cur = self._b("g_up_last", N, 8, h2, w2)
         cv(self.d_conv2, g2, 1, 0, g_cur, 8, 0, N, h2, w2)
         # ---- scalers, last to first: LeakyReLU' + PixelShuffle inverse, wgrad 64 -> 256, dgrad 256 -> 64
@@ -195,21 +258,20 @@ class TrainPlan:
         gy, gy_planes = self._b("g_tr", N, 8, H, W), 8     # gradient of the current RRDB's output
         cv(self.d_conv1, g_t, 8, 0, gy, 8, 0, N, H, W)
         # ---- RRDBs, last to first
-        pool = [self._b(f"G{j}", N, 24, H, W) for j in range(4)]
         nr = len(self.rdbs)
+        Gs = [self._b(f"G{j}", N, 24, H, W) for j in range(nr)]    # kept per RDB: the deferred weight gradients read them
         for r in range(nr - 1, -1, -1):
             rrdb, rdb, _, dg = self.rdbs[r]
             D = sv["dense"][r]
             d = r % 3
             a, R = float(rdb.add_rate), float(rrdb.add_rate)
-            if d == 2:                                      # start of an RRDB (backward order): three buffers != gy
-                free = [b for b in pool if b is not gy][:3]
+            if d == 2:                                      # start of an RRDB (backward order)
                 gsrc, gsrc_planes = gy, gy_planes
                 s_out, s_res = a * R, R
             else:
                 gsrc, gsrc_planes = G, 24
                 s_out, s_res = a, 1.0
-            G = free[2 - d]
+            G = Gs[r]
             sl = [_slope_of(getattr(rdb, f"conv{i}").act) for i in range(4)]
             # final conv 192 -> 64 (no activation): out = s_out*conv(cat) + s_res*rdb_in
             self._wb(rdb.conv, D, 24, 0, 192, gsrc, gsrc_planes, 0, 64, N, H, W, scale=s_out)
@@ -244,10 +306,10 @@ class TrainPlan:
         gx0 = self._b("gx0", N, 8, H, W)
         ops.c8_axpby_mask(gy, gy_planes, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
         ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.weight)], N, H, W)
-        ops.bias_grad(gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.bias)], N, H, W)
-        self.saved = None
-        if self.allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            allreduce_mean_(self.flat_grad)
+        if self._gjobs is not None:
+            self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=self.grad_views[id(n.conv0.conv.bias)], N=N, H=H, W=W))
+            self.grad_batch, self.grad_key, self._gjobs = ops.GradBatch(self.ctx, self._gjobs, self.dt), gkey, None
+        self.grad_batch.run(self.device, self.wgrad_splitk)
         return [self.grad_views[id(p)] for p in self.params]
 
 
@@ -268,7 +330,8 @@ class _NetFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, plan, *params):
         ctx.plan = plan
-        return plan.forward(x)
+        out = plan.forward(x)
+        return out.view_as(out)     # fresh tensor object per step over the (graph-static) output buffer
 
     @staticmethod
     def backward(ctx, gout):

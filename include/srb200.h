@@ -174,6 +174,32 @@ int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off,
                       int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off, float slope, void* out,
                       int out_c8_total, int out_c8_off, int planes, int dtype, int N, int H, int W, srb_stream_t stream);
 
+/* Batched gradients: every 3x3 weight gradient and every bias gradient of one backward pass as ONE launch each.
+ * Weight gradients are off backpropagation's critical path, so the step defers them to its end; a unit
+ * (conv, 128-ch cin block, 32-ch cout block) is then owned by one CTA (splitk = 1): no cross-CTA reduction.
+ * Buffers named by the jobs must stay allocated (and keep their addresses) while the batch object lives.
+ * dw / db are ACCUMULATED into; either may be NULL. */
+typedef struct srb_grad_job {
+    const void* x; int x_c8_total, x_c8_off, cin;
+    const void* dy; int dy_c8_total, dy_c8_off, cout;
+    float* dw; float* db; float scale;
+    int N, H, W;
+} srb_grad_job;
+typedef struct srb_grad_batch srb_grad_batch;
+int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int n, int dtype, srb_grad_batch** out);
+int srb_grad_batch_units(const srb_grad_batch* b);
+int srb_grad_batch_run(srb_ctx* ctx, srb_grad_batch* b, int splitk, srb_stream_t stream);
+void srb_grad_batch_destroy(srb_grad_batch* b);
+
+/* Batched srb_pack_conv_device: all packed operands of a net re-derived from the fp32 masters in one launch. */
+typedef struct srb_pack_job {
+    srb_weights* w; const float* w_src; int src_o, src_i, o_off, c_off, transpose; const float* bias_src;
+} srb_pack_job;
+typedef struct srb_pack_batch srb_pack_batch;
+int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int n, srb_pack_batch** out);
+int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t stream);
+void srb_pack_batch_destroy(srb_pack_batch* b);
+
 /* L1Loss.forward / backward (utils/loss.py:38-39): loss = w * mean|pred - tgt| ; dpred = w*scale*sign/numel.
  * pred_dtype: SRB_DT_F16 / SRB_DT_BF16 / 2 = fp32.  tgt fp32.  partials: >= srb_l1_partials_len() floats. */
 int srb_l1_partials_len(void);

@@ -221,3 +221,32 @@ def test_reference_train_loop_runs_on_dropin(dev):
         scaler.update()
         losses.append(loss.item())
     assert losses[-1] < losses[0] * 0.95 and all(np.isfinite(losses)), losses
+
+
+def test_batched_gradients_match_single_launches(ctx, dev):
+    """srb_grad_batch (one CTA per unit, no split-K) == srb_conv2d_wgrad / srb_bias_grad per conv."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(9)
+    N, H, W = 2, 24, 40
+    D = torch.randn(N, 24, H, W, 8, generator=g).to(torch.bfloat16).to(dev)
+    G = torch.randn(N, 24, H, W, 8, generator=g).to(torch.bfloat16).to(dev)
+    specs = [(64, 32, 8), (160, 32, 20), (192, 64, 0)]
+    jobs, refs = [], []
+    for cin, cout, dyo in specs:
+        dw, db = torch.zeros(cout, cin, 3, 3, device=dev), torch.zeros(cout, device=dev)
+        jobs.append(dict(x=D, x_planes=24, x_off=0, cin=cin, dy=G, dy_planes=24, dy_off=dyo, cout=cout, dw=dw, db=db, scale=0.5,
+                         N=N, H=H, W=W))
+        rw, rb = torch.zeros_like(dw), torch.zeros_like(db)
+        ops.conv2d_wgrad(D, 24, 0, cin, G, 24, dyo, cout, rw, N, H, W, scale=0.5)
+        ops.bias_grad(G, 24, dyo, cout, rb, N, H, W, scale=0.5)
+        refs.append((rw, rb))
+    for splitk in (1, 3):
+        for j in jobs:
+            j["dw"].zero_(); j["db"].zero_()
+        gb = ops.GradBatch(ctx, jobs, "bf16")
+        gb.run(dev, splitk)
+        torch.cuda.synchronize()
+        for j, (rw, rb) in zip(jobs, refs):
+            assert (j["dw"] - rw).abs().max().item() <= 1e-3 * rw.abs().max().item() + 1e-4
+            if splitk == 1:
+                assert (j["db"] - rb).abs().max().item() <= 1e-3 * rb.abs().max().item() + 1e-4
