@@ -48,7 +48,7 @@ def peaks():
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
 
-    def __init__(self, index: int, period: float = 0.05):
+    def __init__(self, index: int, period: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -149,6 +149,51 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def bench_train(dev, rank, world, steps, warmup=3):
+    """BASELINE configs[4]: train.py step (EResNet(16,0.2,2), L1 loss, GradScaler, clip, Adam, LinearLR, EMA) on synthetic
+    COCO-shaped 128x128 HR crops, per-GPU batch 16, data parallel with one gradient all-reduce per step.  Runs the
+    drop-in `train()` loop itself; samples/s = global batch x steps / max-over-ranks device time."""
+    import torch.distributed as dist
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200 import train as T
+    from image_super_resolution_b200.training import L1Loss
+    B = 16
+    torch.manual_seed(100)
+    net = models.EResNet(16, 0.2, 2).to(dev)
+    T.broadcast_parameters(net)
+    g = torch.Generator().manual_seed(100 + rank)
+    hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
+    lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
+    loss_fn = L1Loss().to(dev)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
+    sched = torch.optim.lr_scheduler.LinearLR(opt, start_factor=1, end_factor=0.1, total_iters=1000)
+    scaler = torch.amp.GradScaler("cuda")
+    ema = T.ModelEMA(net, tau=1000)
+    T.train(net, ema, [(hr, lr)] * warmup, loss_fn, opt, scaler, sched, 0, None)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    losses = T.train(net, ema, [(hr, lr)] * steps, loss_fn, opt, scaler, sched, 1, None)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item()) / steps
+    flop = 289.0e9 * B          # SURVEY §8(d): fwd + bwd algorithmic FLOP per sample
+    pk = peaks()
+    return {"metric": "train.py step samples/s", "value": world * B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms,
+            "steps": steps, "model": "EResNet(16,0.2,2)", "per_gpu_batch": B, "hr_crop": 128, "operands": "bf16 in, fp32 accumulate",
+            "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), Adam, LinearLR, EMA, loss.item()",
+            "collective": "one all-reduce (mean) of the 11.7M-element fp32 gradient arena per step" if world > 1 else "none",
+            "fwd_bwd_tflops_per_gpu": flop / (ms * 1e-3) / 1e12, "frac_of_bf16_peak": flop / (ms * 1e-3) / 1e12 / pk["bf16_tflops"],
+            "loss_first_last": [losses[0], losses[-1]]}
+
+
 def run_ours(args, rank, world, local):
     import torch.distributed as dist
     import image_super_resolution_b200 as srb
@@ -240,6 +285,13 @@ def run_ours(args, rank, world, local):
                 "whole_step_tflops": px_step * FLOP_PER_PX / (sum(per_launch) / 1e3) / 1e12,
                 "kernels": kernels}
 
+    train_line = None
+    if not args.no_train:
+        try:
+            train_line = bench_train(dev, rank, world, steps=min(K, 10))
+        except Exception as e:  # noqa: BLE001  (the headline line must still print)
+            train_line = {"error": repr(e)[:300]}
+
     if rank == 0:
         value = world * px_step * K / (ms_total / 1e3) / 1e6
         e2e = world * px_step * K / (ms_e2e / 1e3) / 1e6
@@ -257,6 +309,8 @@ def run_ours(args, rank, world, local):
                         "d2h_bytes_per_step": y_host.numel(), "ms_per_step": ms_e2e / K},
                 "gpu_launches": nl * K,
                 "roofline": roofline}
+        if train_line is not None:
+            line["train_step"] = train_line
         if world == 1 and not args.no_cpu:
             px, times = cpu_port_forward_timer(sample_tiles=32, min_seconds=10.0)
             best = min(times)
@@ -275,6 +329,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-train", action="store_true", help="skip the train_step leg (BASELINE configs[4])")
     args = ap.parse_args()
     rank, world, local = dist_setup(args.gpus)
     if args.impl == "reference":

@@ -268,7 +268,7 @@ extern "C" void srb_free_weights(srb_weights* w) {
 // ------------------------------------------------------------------------------------------
 // conv dispatch
 // ------------------------------------------------------------------------------------------
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false, bool WS = false>
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES = false, bool WS = false, bool BWD = false>
 static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_c8_total, ConvParams p, cudaStream_t st) {
     using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES, WS>;
     p.kblocks = WS ? w->kblocks : 1;
@@ -308,11 +308,11 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     p.dbg_skip = ctx->dbg_skip;
     p.dbg_trace = ctx->dbg_trace;
     if (w->dtype == SRB_DT_BF16) {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, true>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, true, BWD>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     } else {
-        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, false>;
+        auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, false, BWD>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
     }
@@ -397,6 +397,15 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
 #define SRB_STD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
+    const bool bwd = (flags & SRB_F_MASK) || partial_res;
+    if (bwd) {   // data-gradient launches of the training step (srb_conv_args: mask / partial residual)
+#define SRB_BWD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
+        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true, false, true>(ctx, w, x, x_c8_total, p, st); \
+        return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false, false, true>(ctx, w, x, x_c8_total, p, st); }
+        SRB_BWD(4, 64, 4) SRB_BWD(8, 64, 3) SRB_BWD(4, 32, 4)
+#undef SRB_BWD
+        return fail(SRB_ENOSUP, "srb_conv2d: no backward-epilogue kernel for cin=%d cout=%d", w->cin, w->cout);
+    }
     SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3) SRB_STD(4, 32, 4)
     if (w->kblocks) {   // dense-block convs (Cin = 96..192): K blocks of 32 channels, filter streamed with the halo
         if (w->nout == 32) return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);

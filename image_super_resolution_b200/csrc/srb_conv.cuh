@@ -163,7 +163,9 @@ __device__ __forceinline__ uint4 lds_u4(uint32_t a) {
     return r;
 }
 
-template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool WS, bool BF16>
+// BWD: compile the backward-only epilogue terms (partial residual, LeakyReLU' mask); the inference kernels are
+// epilogue-bound in places and must not carry them.
+template <int C8IN, int NOUT, int KH, int KW, int MODE, int NT, bool RES, bool WS, bool BF16, bool BWD = false>
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_constant__ CUtensorMap tmap,
                                                          const __grid_constant__ CUtensorMap tmap_res, const ConvParams p) {
     using G = ConvGeom<C8IN, NOUT, KH, KW, MODE, NT, RES, WS>;
@@ -413,7 +415,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                     v[i] = tt * p.out_scale;
                                 }
                                 if (valid) {
-                                    if ((RES || has_res) && gj < p.res_nplanes) {
+                                    if ((RES || has_res) && (!BWD || gj < p.res_nplanes)) {
                                         uint4 q;
                                         if constexpr (RES) q = lds_u4(rslot_addr + gj * 2048);
                                         else q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.res) +
@@ -437,7 +439,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                             v[2 * i + 1] += p.res2_scale * f.y;
                                         }
                                     }
-                                    if ((p.flags & F_MASK) && gj >= p.mask_p0 && gj < p.mask_p1) {
+                                    if (BWD && (p.flags & F_MASK) && gj >= p.mask_p0 && gj < p.mask_p1) {
                                         // LeakyReLU backward: the in-place activation kept its sign (slope > 0)
                                         const uint4 q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.mask) +
                                                                  (((size_t)n * p.mask_c8_total + p.mask_c8_off + gj) * HW + pix) * 16);
