@@ -34,6 +34,10 @@ LAUNCH_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576
 LAUNCH_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64",
                                                                                                  "conv9x9_tail_64_3"]
 assert sum(LAUNCH_FLOP_PX) == FLOP_PER_PX
+# with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 12 launches
+FUSED_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
+FUSED_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
+assert sum(FUSED_FLOP_PX) == FLOP_PER_PX
 
 
 def peaks():
@@ -258,7 +262,8 @@ def run_ours(args, rank, world, local):
 
     # ---- per-launch durations (CUDA events recorded by the library on the launching stream) ----
     ctxh = model._ctx.handle
-    nl = model.launches_per_forward()
+    nl = model.launches_per_forward(HH, WW)
+    names, flops = (FUSED_NAMES, FUSED_FLOP_PX) if nl == len(FUSED_NAMES) else (LAUNCH_NAMES, LAUNCH_FLOP_PX)
     acc = [0.0] * nl
     buf = (C.c_float * 64)()
     check(lib().srb_profile_enable(ctxh, 1))
@@ -271,7 +276,7 @@ def run_ours(args, rank, world, local):
     check(lib().srb_profile_enable(ctxh, 0))
     per_launch = [a / K for a in acc]
     groups = {}
-    for name, t, f in zip(LAUNCH_NAMES, per_launch, LAUNCH_FLOP_PX):
+    for name, t, f in zip(names, per_launch, flops):
         gsum = groups.setdefault(name, [0, 0.0, 0.0])
         gsum[0] += 1; gsum[1] += t; gsum[2] += f * px_step
     pk = peaks()

@@ -38,7 +38,7 @@ SIGNATURES = {
     "srb_model_pt_workspace_bytes": (_sz, [_i, _i, _i]),
     "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
-    "srb_model_pt_launches": (_i, []),
+    "srb_model_pt_launches": (_i, [_i, _i]),
     "srb_check_device": (_i, [_vp]),
     "srb_debug_trace": (_i, [_vp, _vp]),
     "srb_profile_enable": (_i, [_vp, _i]),
@@ -60,6 +60,10 @@ SIGNATURES = {
     "srb_pack_batch_create": (_i, [_vp, _vp, _i, C.POINTER(_vp)]),
     "srb_pack_batch_run": (_i, [_vp, _vp, _vp]),
     "srb_pack_batch_destroy": (None, [_vp]),
+    "srb_resblock_create": (_i, [_vp, _vp, _vp, _vp, _vp, _i, C.POINTER(_vp)]),
+    "srb_resblock_destroy": (None, [_vp]),
+    "srb_resblock_supported": (_i, [_i, _i]),
+    "srb_resblock_fwd": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),

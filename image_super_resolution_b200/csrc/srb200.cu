@@ -17,6 +17,7 @@
 #include "srb_ubench.cuh"
 #include "srb_wgrad.cuh"
 #include "srb_bwd.cuh"
+#include "srb_resblock.cuh"
 
 using namespace srb;
 
@@ -75,8 +76,10 @@ struct srb_weights {
     size_t pack_bytes = 0;
 };
 
+struct srb_resblock;
 struct srb_net {
     srb_weights* conv[19];
+    srb_resblock* rb[8];     // fused ResidualBlock1 operands (used when the shape qualifies)
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -526,6 +529,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
     if (!ctx || !w || !b || !mean || !std_ || !out) return fail(SRB_EINVAL, "srb_model_pt_create: NULL argument");
     srb_net* net = new srb_net();
     memset(net->conv, 0, sizeof(net->conv));
+    memset(net->rb, 0, sizeof(net->rb));
     for (int i = 0; i < 3; ++i) { net->mean[i] = mean[i]; net->std_[i] = std_[i]; }
     net->maxv = maxv; net->slope = slope; net->dtype = dtype;
     int rc = SRB_OK;
@@ -539,6 +543,8 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
         if (!w[i] || !b[i]) rc = fail(SRB_EINVAL, "srb_model_pt_create: weight %d is NULL", i);
         else rc = srb_pack_conv(ctx, w[i], b[i], nullptr, 0.f, cout, cin, k, dtype, &net->conv[i]);
     }
+    for (int i = 0; i < 8 && rc == SRB_OK; ++i)
+        rc = srb_resblock_create(ctx, w[1 + 2 * i], b[1 + 2 * i], w[2 + 2 * i], b[2 + 2 * i], dtype, &net->rb[i]);
     if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
     *out = net;
     return SRB_OK;
@@ -547,6 +553,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
 extern "C" void srb_model_pt_destroy(srb_net* net) {
     if (!net) return;
     for (int i = 0; i < 19; ++i) srb_free_weights(net->conv[i]);
+    for (int i = 0; i < 8; ++i) srb_resblock_destroy(net->rb[i]);
     delete net;
 }
 
@@ -558,7 +565,8 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
     return align256(P * 16) + 3 * align256(P * 128) + align256(P * 64);
 }
 
-extern "C" int srb_model_pt_launches(void) { return 20; }
+// kernels one forward enqueues: pack, head, 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
+extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? 12 : 20; }
 
 // measurement only: per-step clock trace of CTA 0 of the next conv launches (512 int64 device buffer, or NULL)
 extern "C" int srb_debug_trace(srb_ctx* ctx, void* dev_buf512) {
@@ -636,8 +644,15 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
     void* cur = x0;
+    const bool fused = srb_resblock_supported(H, W) && !(ctx->dbg_skip & 8);
     for (int i = 0; i < 8; ++i) {
         void* nxt = (i & 1) ? rb : ra;
+        if (fused) {
+            if ((rc = srb_resblock_fwd(ctx, net->rb[i], cur, nxt, s, N, H, W, stream))) return rc;
+            prof_mark(ctx, pst);
+            cur = nxt;
+            continue;
+        }
         if ((rc = srb_conv2d_fwd(ctx, net->conv[1 + 2 * i], cur, 8, 0, hid, 4, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
         prof_mark(ctx, pst);
         if ((rc = srb_conv2d_fwd(ctx, net->conv[2 + 2 * i], hid, 4, 0, nxt, 8, 0, cur, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
@@ -1017,6 +1032,110 @@ extern "C" int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t 
     if (gx > 64) gx = 64;
     dim3 grid(gx, b->n);
     pack_conv_batch_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(b->d_jobs);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// fused residual block (srb_resblock.cuh)
+// ------------------------------------------------------------------------------------------
+struct srb_resblock {
+    int dtype = 0;
+    uint8_t* d_wA = nullptr; uint8_t* d_wB = nullptr;
+    float* d_bA = nullptr; float* d_bB = nullptr;
+};
+
+extern "C" void srb_resblock_destroy(srb_resblock* rb) {
+    if (!rb) return;
+    if (rb->d_wA) cudaFree(rb->d_wA);
+    if (rb->d_wB) cudaFree(rb->d_wB);
+    if (rb->d_bA) cudaFree(rb->d_bA);
+    if (rb->d_bB) cudaFree(rb->d_bB);
+    delete rb;
+}
+
+// fold packing: K-step ks = dx * (cin/16) + c2 ; [2 granules][3*cout rows: slice s = 2 - dy, then co][8 k]
+static void pack_fold(const float* w, int cout, int cin, int dtype, std::vector<uint16_t>& out) {
+    const int h = cin / 16, rows = 3 * cout;
+    out.assign((size_t)3 * h * 2 * rows * 8, 0);
+    for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < h; ++c2) for (int g = 0; g < 2; ++g)
+        for (int s = 0; s < 3; ++s) for (int co = 0; co < cout; ++co) for (int j = 0; j < 8; ++j) {
+            const int ks = dx * h + c2, c = (2 * c2 + g) * 8 + j, dy = 2 - s;
+            out[(((size_t)ks * 2 + g) * rows + s * cout + co) * 8 + j] = f2h(w[(((size_t)co * cin + c) * 3 + dy) * 3 + dx], dtype);
+        }
+}
+
+extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* bA, const float* wB, const float* bB, int dtype,
+                                   srb_resblock** out) {
+    if (!ctx || !wA || !bA || !wB || !bB || !out) return fail(SRB_EINVAL, "srb_resblock_create: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_resblock_create: dtype %d", dtype);
+    using G = RBGeom;
+    std::vector<uint16_t> pa, pb;
+    pack_fold(wA, G::CH, G::CA, dtype, pa);
+    pack_fold(wB, G::CB, G::CH, dtype, pb);
+    if (pa.size() * 2 != (size_t)G::WA_BYTES || pb.size() * 2 != (size_t)G::WB_BYTES) return fail(SRB_EINVAL, "srb_resblock_create: pack size");
+    srb_resblock* rb = new srb_resblock();
+    rb->dtype = dtype;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&rb->d_wA, G::WA_BYTES) != cudaSuccess || cudaMalloc(&rb->d_wB, G::WB_BYTES) != cudaSuccess ||
+        cudaMalloc(&rb->d_bA, G::CH * 4) != cudaSuccess || cudaMalloc(&rb->d_bB, G::CB * 4) != cudaSuccess) {
+        srb_resblock_destroy(rb);
+        return fail(SRB_ENOMEM, "srb_resblock_create: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemcpy(rb->d_wA, pa.data(), G::WA_BYTES, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(rb->d_wB, pb.data(), G::WB_BYTES, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(rb->d_bA, bA, G::CH * 4, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(rb->d_bB, bB, G::CB * 4, cudaMemcpyHostToDevice));
+    *out = rb;
+    return SRB_OK;
+}
+
+// the fused kernel tiles a row as 16 groups of 8 px whose boundaries must coincide with image edges every 16 groups
+extern "C" int srb_resblock_supported(int H, int W) {
+    if (H <= 0 || W <= 0) return 0;
+    const int gx = (W + 7) / 8;
+    return gx == 1 || gx == 2 || gx == 4 || gx == 8 || gx == 16;
+}
+
+extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void* x, void* y, float slope, int N, int H, int W,
+                                srb_stream_t stream) {
+    if (!ctx || !rb || !x || !y) return fail(SRB_EINVAL, "srb_resblock_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_resblock_fwd: empty shape");
+    if (x == y) return fail(SRB_EINVAL, "srb_resblock_fwd: in-place is not supported (neighbouring CTAs re-read halo rows of x)");
+    if (((uintptr_t)x & 15) || ((uintptr_t)y & 15)) return fail(SRB_EINVAL, "srb_resblock_fwd: buffers must be 16-byte aligned");
+    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_resblock_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
+    using G = RBGeom;
+    CUtensorMap tm;
+    {
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+        cuuint32_t box[4] = {40, 1, 8, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = ctx->encode(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+    }
+    ResblockParams p{};
+    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    const long long groups = (long long)N * p.GX;
+    const long long sets = (groups + 15) / 16;
+    if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_resblock_fwd: too many rows");
+    p.total_rows = (int)(sets * H);
+    p.wA = rb->d_wA; p.wB = rb->d_wB; p.biasA = rb->d_bA; p.biasB = rb->d_bB;
+    p.x = x; p.y = y; p.slope = slope;
+    int grid = p.total_rows / 8;
+    if (grid < 1) grid = 1;
+    if (grid > ctx->num_sms) grid = ctx->num_sms;
+    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rb->dtype == SRB_DT_BF16) {
+        CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        resblock_kernel<true><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, p);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        resblock_kernel<false><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, p);
+    }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }

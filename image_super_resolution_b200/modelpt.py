@@ -155,8 +155,8 @@ class ModelPT:
     __call__ = forward
 
     @staticmethod
-    def launches_per_forward() -> int:
-        return int(lib().srb_model_pt_launches())
+    def launches_per_forward(H: int = 64, W: int = 64) -> int:
+        return int(lib().srb_model_pt_launches(H, W))
 
 
 def load(path, map_location="cpu", dtype="fp16") -> ModelPT:

@@ -321,3 +321,38 @@ class PackBatch:
                 self.handle = None
         except Exception:
             pass
+
+
+class ResBlock:
+    """Fused ResidualBlock1 (utils/models.py:208-209): y = x + convB(LeakyReLU(convA(x))) in one kernel (srb_resblock_*)."""
+
+    def __init__(self, ctx: Context, wA, bA, wB, bB, dtype=SRB_DT_F16):
+        arrs = [np.ascontiguousarray(t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t, dtype=np.float32)
+                for t in (wA, bA, wB, bB)]
+        if arrs[0].shape != (32, 64, 3, 3) or arrs[2].shape != (64, 32, 3, 3):
+            raise ValueError("ResBlock: convA must be 64->32 3x3 and convB 32->64 3x3")
+        self.ctx, self.dtype = ctx, dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_resblock_create(ctx.handle, *[_lib.f32_ptr(a) for a in arrs], self.dtype, C.byref(h)), "srb_resblock_create")
+        self.handle = h
+
+    @staticmethod
+    def supported(H: int, W: int) -> bool:
+        return bool(lib().srb_resblock_supported(H, W))
+
+    def forward(self, x: torch.Tensor, y: torch.Tensor, slope: float):
+        _require_cuda(x, "x"); _require_cuda(y, "y")
+        N, planes, H, W, _ = x.shape
+        if planes != 8 or y.shape != x.shape:
+            raise RuntimeError("ResBlock: x and y must be [N][8][H][W][8]")
+        check(lib().srb_resblock_fwd(self.ctx.handle, self.handle, x.data_ptr(), y.data_ptr(), float(slope), N, H, W,
+                                     _stream_ptr(x.device)), "srb_resblock_fwd")
+        return y
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_resblock_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass

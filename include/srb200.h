@@ -133,8 +133,9 @@ int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uin
 /* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);
-/* number of kernels of this library one srb_model_pt_forward enqueues */
-int srb_model_pt_launches(void);
+/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12 with the fused residual
+ * block kernel, 20 when the width does not qualify for it: srb_resblock_supported) */
+int srb_model_pt_launches(int H, int W);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
 /* cudaDeviceSynchronize + report a kernel-side pipeline timeout (kernels never hang: bounded waits) */
@@ -145,6 +146,18 @@ int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
 /* measurement only: cycles for `iters` rounds of `racc` interleaved M=128(64) x n x 16 tcgen05.mma;
  * out2_host[0] = issue cycles, out2_host[1] = cycles until all MMAs completed */
 int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host);
+
+/* Fused residual block  y = x + convB(LeakyReLU(convA(x)))  — ResidualBlock1.forward (utils/models.py:208-209) with
+ * m = Sequential(Conv(64,32,3,act=LeakyReLU), Conv(32,64,3,act=False)), BN already folded (model.pt state: net.1.residual.{i}.m.{0,1}).
+ * One kernel: the 32-channel hidden activation never leaves shared memory.  wA [32][64][3][3], wB [64][32][3][3] fp32 host.
+ * x, y: 8-plane C8 buffers (distinct).  srb_resblock_supported(H, W): ceil(W/8) must be 1, 2, 4, 8 or 16. */
+typedef struct srb_resblock srb_resblock;
+int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* bA, const float* wB, const float* bB, int dtype,
+                        srb_resblock** out);
+void srb_resblock_destroy(srb_resblock* rb);
+int srb_resblock_supported(int H, int W);
+int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void* x, void* y, float lrelu_slope, int N, int H, int W,
+                     srb_stream_t stream);
 
 /* Weight gradient of a 3x3 conv (autograd of aten::_convolution, train.py:57):
  * dw[co][ci][dy][dx] += scale * sum_p dY[p][co] * X[p+(dy-1,dx-1)][ci].  x, dy: C8-plane slices (device);

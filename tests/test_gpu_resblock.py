@@ -1,0 +1,66 @@
+"""GPU parity of the fused residual-block kernel (srb_resblock.cuh) against fp32 torch on the same fp16-rounded operands
+(hidden activation rounded to fp16 like the unfused layer chain).  Tolerance: |err| <= 4e-3 * max|ref| + 2e-3."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    return torch.device("cuda:0")
+
+
+def _case(dev, N, H, W, seed=0, grid=0):
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200._lib import Context
+    ctx = Context.get(0)
+    g = torch.Generator().manual_seed(seed)
+    wA = torch.randn(32, 64, 3, 3, generator=g) / 24
+    bA = torch.randn(32, generator=g) * 0.1
+    wB = torch.randn(64, 32, 3, 3, generator=g) / 17
+    bB = torch.randn(64, generator=g) * 0.1
+    x = torch.randn(N, 64, H, W, generator=g)
+    q = lambda t: t.half().float()  # noqa: E731
+    hid = q(F.leaky_relu(F.conv2d(q(x), q(wA), bA, padding=1), 0.2))
+    ref = q(x) + F.conv2d(hid, q(wB), bB, padding=1)
+    rb = ops.ResBlock(ctx, wA, bA, wB, bB, "fp16")
+    xc = ops.nchw_to_c8(x.to(dev), dtype="fp16")
+    yc = torch.full_like(xc, float("nan"))
+    if grid:
+        ctx.debug_set(1, grid)
+    try:
+        rb.forward(xc, yc, 0.2)
+        torch.cuda.synchronize()
+        ctx.check_device()
+    finally:
+        ctx.debug_set(1, 0)
+    out = ops.c8_to_nchw(yc, 64).cpu()
+    err = (out - ref).abs().max().item()
+    assert np.isfinite(err) and err <= 4e-3 * ref.abs().max().item() + 2e-3, err
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 12, 64), (3, 20, 64), (1, 5, 8), (5, 9, 16), (2, 33, 128), (3, 17, 60), (2, 1, 64), (7, 2, 28)])
+def test_resblock_matches_fp32_reference(dev, N, H, W):
+    _case(dev, N, H, W, seed=N * 100 + H)
+
+
+def test_resblock_many_rows_per_cta_and_segment_splits(dev):
+    """few CTAs (long marches, ring wrap-arounds) and many CTAs (segments that split images mid-way)"""
+    _case(dev, 6, 64, 64, seed=1, grid=2)
+    _case(dev, 6, 64, 64, seed=2, grid=0)
+    _case(dev, 40, 64, 64, seed=3, grid=0)
+
+
+def test_resblock_rejects_unsupported_widths(dev):
+    from image_super_resolution_b200 import ops
+    assert ops.ResBlock.supported(64, 64) and ops.ResBlock.supported(7, 128) and not ops.ResBlock.supported(64, 96)
