@@ -1118,12 +1118,27 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     }
     ResblockParams p{};
     p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    p.BW = p.GX * 8 < 64 ? p.GX * 8 : 64;
+    CUtensorMap tmy, tmxr;   // residual rows arrive and output rows leave as TMA boxes of BW px x 8 planes
+    {
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+        cuuint32_t box[4] = {(cuuint32_t)p.BW * 4, 1, 8, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = ctx->encode(&tmy, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, y, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = ctx->encode(&tmxr, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled (residual / output) failed: %d", (int)r);
+    }
     const long long groups = (long long)N * p.GX;
     const long long sets = (groups + 15) / 16;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_resblock_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.wA = rb->d_wA; p.wB = rb->d_wB; p.biasA = rb->d_bA; p.biasB = rb->d_bB;
-    p.x = x; p.y = y; p.slope = slope;
+    p.x = x; p.y = y; p.slope = slope; p.dbg_skip = ctx->dbg_skip; p.dbg_trace = ctx->dbg_trace;
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
     if (grid > ctx->num_sms) grid = ctx->num_sms;
@@ -1131,10 +1146,10 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     cudaStream_t st = (cudaStream_t)stream;
     if (rb->dtype == SRB_DT_BF16) {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        resblock_kernel<true><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, p);
+        resblock_kernel<true><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, tmxr, tmy, p);
     } else {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        resblock_kernel<false><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, p);
+        resblock_kernel<false><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, tmxr, tmy, p);
     }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;

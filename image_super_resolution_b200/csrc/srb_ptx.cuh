@@ -50,10 +50,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // tag identifies the wait site.  On a protocol bug the kernel does not hang or trap: the first wait to
 // exceed its budget records where it was, raises g_srb_abort, and every wait returns at once so the
 // launch drains (with garbage results); the host reads the flag (srb_check_device) and reports it.
+// SLEEP_NS > 0: back off between polls — for consumer warps that share a scheduler with a latency-critical issuing
+// warp (a spinning warp steals the issuer's issue slots).
+template <int SLEEP_NS = 0>
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag) {
     if (mbar_try_wait(bar, parity)) return;
     long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
+    for (;;) {
+        // the abort flag lives in global memory (an L2 round trip per look): poll the barrier many times per look, or
+        // every hand-off in the pipeline pays that latency
+#pragma unroll 1
+        for (int i = 0; i < 64; ++i) {
+            if (mbar_try_wait(bar, parity)) return;
+            if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
+        }
         if (g_srb_abort) return;
         if (clock64() - t0 > (1ll << 28)) {  // ~0.14 s at 2 GHz
             if (atomicExch((unsigned int*)&g_srb_abort, 1u) == 0u) {
@@ -89,6 +99,22 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
         ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+
+// 4-D tiled tensor store shared -> global (bulk async group); out-of-bounds parts of the box are clipped
+__device__ __forceinline__ void tma_store_4d(const void* tmap, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+        ::"l"(tmap), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all committed bulk stores of this thread have finished READING shared memory (the source may be overwritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// named barrier among `count` threads (id 1..15; id 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------

@@ -15,8 +15,8 @@
 //     residual and is stored.  HBM traffic per block: read x once, write y once (256 B/px).
 //   * Accumulator rings in TMEM (hidden: RH x 32 columns, output: RY x 64 columns = 512), drained and re-zeroed by the
 //     epilogues, so every MMA accumulates; an MMA whose three rows wrap around the ring is split in two.
-// Warp roles (512 threads): 0 TMA producer, 1 MMA issuer, 4-7 hidden epilogue, 8-15 output epilogue (two sets that
-// alternate rows).  convA and convB MMAs are interleaved (A A B) so consecutive MMAs hit different accumulators.
+// Warp roles (640 threads): 0 TMA producer, 1 convA MMA issuer, 2 convB MMA issuer, 4-11 hidden epilogue, 12-19 output
+// epilogue (each as two sets of 4 warps that alternate rows).  The tensor pipe interleaves the two issuers' independent accumulation chains.
 #pragma once
 #include <cuda.h>
 #include "srb_ptx.cuh"
@@ -26,6 +26,7 @@ namespace srb {
 
 struct ResblockParams {
     int N, H, W, GX;          // GX = groups (8 px) per image row; 16 % GX == 0
+    int BW;                   // pixels per residual / output TMA box: min(GX * 8, 64)
     int total_rows;           // strip-sets x H: the flattened (strip-set, output row) space split evenly over CTAs
     const uint8_t* wA;        // fold-packed 64 -> 32:  12 K-steps x [2][96][8]
     const uint8_t* wB;        // fold-packed 32 -> 64:   6 K-steps x [2][192][8]
@@ -34,7 +35,11 @@ struct ResblockParams {
     const void* x;            // [N][8][H][W][8]
     void* y;                  // [N][8][H][W][8]
     float slope;
+    long long* dbg_trace;     // optional clock stamps of CTA 0: [64 rows][16]
+    int dbg_skip;             // bottleneck probes: 1 = no TMA loads, 2 = no MMAs (16 = no convA, 32 = no convB MMAs), 4 = no global I/O in the output epilogue
 };
+
+constexpr int RB_SLEEP = 40;   // ns between polls of the epilogue warps' waits
 
 struct RBGeom {
     static constexpr int CA = 64, CH = 32, CB = 64;            // channels: in, hidden, out
@@ -50,11 +55,14 @@ struct RBGeom {
     static constexpr int RH = 6, RY = 5;                        // TMEM accumulator rings
     static constexpr int TM_H = 0, TM_Y = RH * CH;              // column bases: 0, 192 (+ 5*64 = 512)
     static constexpr int OFF_WA = 0, OFF_WB = WA_BYTES, OFF_X = OFF_WB + WB_BYTES, OFF_H = OFF_X + XSTAGES * XROW;
-    static constexpr int OFF_BIAS = OFF_H + HSLOTS * HROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
+    static constexpr int YROW = 128 * CB * 2;                   // one output row staged for the TMA store: 16 KB
+    static constexpr int OFF_Y = OFF_H + HSLOTS * HROW;         // two staging slots (one per output-epilogue set)
+    static constexpr int OFF_BIAS = OFF_Y + 2 * YROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
-    static constexpr int THREADS = 512;
+    static constexpr int THREADS = 640;            // 4 control warps + 8 hidden-epilogue warps + 8 output-epilogue warps
     static_assert(RH * CH + RY * CB == 512, "the two accumulator rings fill TMEM");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+    static_assert(XSTAGES <= 8 && RH <= 8 && HSLOTS <= 4 && RY <= 8, "barrier array layout");
 };
 
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
@@ -68,15 +76,34 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
           "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_zero16(uint32_t taddr) {
+    const uint32_t z = 0u;
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};"
+        ::"r"(taddr), "r"(z) : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_zero32(uint32_t taddr) {
-    uint32_t z[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) z[i] = 0u;
-    tmem_st32(taddr, z);
+__device__ __forceinline__ void tmem_zero32(uint32_t taddr) {   // one zero register, named 32 times
+    const uint32_t z = 0u;
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};"
+        ::"r"(taddr), "r"(z) : "memory");
 }
 __device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k) {
+    if (p.dbg_trace != nullptr && blockIdx.x == 0 && row < 64) p.dbg_trace[row * 16 + k] = clock64();
 }
 
 // a segment: output rows [y0, y1) of strip-set ss, with the hidden / input row ranges it needs (clipped to the image)
@@ -95,22 +122,32 @@ __device__ __forceinline__ bool rb_next_seg(const ResblockParams& p, int& g, int
     return true;
 }
 
-// Issue one folded K-step: D slots of rows [c_lo, c_hi] (ring counters, consecutive) += A * B[slice s0 ..], splitting
-// at the ring's wrap-around.  CO = output channels per row slot.
+// Per-row issue plan of the folded MMAs: D slots of rows [c_lo, c_lo + nsl) (ring counters) += A * B[slice s0 ..],
+// split in two at the ring's wrap-around.  Everything that does not depend on the K-step is computed once per row —
+// the issuing thread is a single lane and its instruction latency is on the critical path.
+struct RBPlan { uint32_t d0, d1, idesc0, idesc1, boff0, boff1; bool two; };
 template <int CO, int R, bool BF16>
-__device__ __forceinline__ void rb_mma_fold(uint32_t tm_ring, uint64_t a_desc, uint64_t b_desc, int c_lo, int nsl, int s0) {
-    const int slot = c_lo % R;
-    int n1 = R - slot < nsl ? R - slot : nsl;
-    uint32_t idesc = umma_idesc_f16(128, n1 * CO, BF16 ? 1 : 0);
-    umma_f16_ss(tm_ring + slot * CO, a_desc, b_desc + (uint64_t)((s0 * CO * 16) >> 4), idesc, 1u);
-    if (n1 < nsl) {
-        idesc = umma_idesc_f16(128, (nsl - n1) * CO, BF16 ? 1 : 0);
-        umma_f16_ss(tm_ring, a_desc, b_desc + (uint64_t)(((s0 + n1) * CO * 16) >> 4), idesc, 1u);
-    }
+__device__ __forceinline__ RBPlan rb_plan(uint32_t tm_ring, int slot, int nsl, int s0) {
+    RBPlan q;
+    const int n1 = R - slot < nsl ? R - slot : nsl;
+    q.d0 = tm_ring + slot * CO;
+    q.idesc0 = umma_idesc_f16(128, n1 * CO, BF16 ? 1 : 0);
+    q.boff0 = (uint32_t)((s0 * CO * 16) >> 4);
+    q.two = n1 < nsl;
+    q.d1 = tm_ring;
+    q.idesc1 = umma_idesc_f16(128, (nsl - n1 > 0 ? nsl - n1 : 1) * CO, BF16 ? 1 : 0);
+    q.boff1 = (uint32_t)(((s0 + n1) * CO * 16) >> 4);
+    return q;
+}
+__device__ __forceinline__ void rb_issue(const RBPlan& q, uint64_t a_desc, uint64_t b_desc) {
+    umma_f16_ss(q.d0, a_desc, b_desc + q.boff0, q.idesc0, 1u);
+    if (q.two) umma_f16_ss(q.d1, a_desc, b_desc + q.boff1, q.idesc1, 1u);
 }
 
 template <bool BF16>
 __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __grid_constant__ CUtensorMap tmap_x,
+                                                                      const __grid_constant__ CUtensorMap tmap_xr,
+                                                                      const __grid_constant__ CUtensorMap tmap_y,
                                                                       const ResblockParams p) {
     using G = RBGeom;
     extern __shared__ uint8_t smem_raw[];
@@ -119,18 +156,21 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     uint8_t* s_wB = smem + G::OFF_WB;
     uint8_t* s_x = smem + G::OFF_X;
     uint8_t* s_h = smem + G::OFF_H;
+    uint8_t* s_y = smem + G::OFF_Y;
     float* s_bias = reinterpret_cast<float*>(smem + G::OFF_BIAS);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
-    uint64_t* xfull = bars;            // [4]  TMA -> MMA
-    uint64_t* xempty = bars + 4;       // [4]  MMA -> TMA
-    uint64_t* hafull = bars + 8;       // [RH] hidden accumulator row complete        MMA -> hidden epilogue
-    uint64_t* haempty = bars + 14;     // [RH] drained and re-zeroed                  hidden epilogue -> MMA
-    uint64_t* hsfull = bars + 20;      // [3]  hidden row written to shared memory    hidden epilogue -> MMA
-    uint64_t* hsempty = bars + 23;     // [3]  consumed by convB                      MMA -> hidden epilogue
-    uint64_t* yafull = bars + 26;      // [RY] output accumulator row complete        MMA -> output epilogue
-    uint64_t* yaempty = bars + 31;     // [RY] drained and re-zeroed                  output epilogue -> MMA
-    uint64_t* wbar = bars + 36;
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 40);
+    uint64_t* xfull = bars;            // [XSTAGES]  TMA -> MMA
+    uint64_t* xempty = bars + 8;       // [XSTAGES]  MMA -> TMA
+    uint64_t* hafull = bars + 16;      // [RH] hidden accumulator row complete        MMA -> hidden epilogue
+    uint64_t* haempty = bars + 24;     // [RH] drained and re-zeroed                  hidden epilogue -> MMA
+    uint64_t* hsfull = bars + 32;      // [HSLOTS] hidden row written to shared memory   hidden epilogue -> MMA
+    uint64_t* hsempty = bars + 36;     // [HSLOTS] consumed by convB                     MMA -> hidden epilogue
+    uint64_t* yafull = bars + 40;      // [RY] output accumulator row complete        MMA -> output epilogue
+    uint64_t* yaempty = bars + 48;     // [RY] drained and re-zeroed                  output epilogue -> MMA
+    uint64_t* wbar = bars + 56;
+    uint64_t* rfull = bars + 57;       // [2] staging slot free again and the residual row landed in it    I/O warp -> output epilogue
+    uint64_t* sfull = bars + 59;       // [2] output row staged                                              output epilogue -> I/O warp
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 62);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -142,10 +182,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
         for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], 1); mbar_init(&haempty[i], 4); }
         for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4); mbar_init(&hsempty[i], 1); }
-        for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 4); }
+        for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
         mbar_init(wbar, 1);
+        mbar_init(&rfull[0], 1); mbar_init(&rfull[1], 1);
+        mbar_init(&sfull[0], 8); mbar_init(&sfull[1], 8);
         fence_mbar_init();
         tma_prefetch_desc(&tmap_x);
+        tma_prefetch_desc(&tmap_y);
+        tma_prefetch_desc(&tmap_xr);
     }
     fence_proxy_async_smem();
     if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, 512); }
@@ -184,6 +228,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
                 mbar_wait(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
+                if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)
@@ -192,84 +237,110 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
+        // ===================== convA MMA issuer: one x row per step, N = 3 x 32 into the hidden accumulator ring =====================
+        // (convA and convB are issued by two different warps: a single thread cannot prepare 18 MMAs + 5 commits per row
+        // fast enough, and the tensor pipe interleaves the two warps' independent accumulation chains by itself)
         const uint64_t adescA0 = umma_desc_nosw(0, 160, G::XBOX);           // x row: planes 160 B apart, groups XBOX apart
-        const uint64_t adescB0 = umma_desc_nosw(0, 160, G::HBOX);           // hidden row
         const uint64_t bdescA0 = umma_desc_nosw(smem_u32(s_wA), 3 * G::CH * 16, 128);
-        const uint64_t bdescB0 = umma_desc_nosw(smem_u32(s_wB), 3 * G::CB * 16, 128);
         mbar_wait(wbar, 0, 32);
-        int xc = 0, hbase = 0, ybase = 0, h_acq = 0, y_acq = 0, g = g_begin;
+        // ring positions are tracked incrementally (no divisions on the issue path)
+        int xst = 0; uint32_t xph = 0;                 // x stage / phase of the next x row
+        int hslot0 = 0;                                // ring slot of the segment's first hidden row (hidden counter hbase)
+        int acq_slot = 0; uint32_t acq_ph = 1;         // next hidden slot to acquire, parity to wait for (empty: phase ^ 1)
+        int hbase = 0, h_acq = 0, g = g_begin, xc = 0;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int nx = sg.xhi - sg.xlo + 1, nh = sg.hhi - sg.hlo + 1, ny = sg.y1 - sg.y0;
-            const int lag = sg.hlo - sg.xlo + 3;
 #pragma unroll 1
-            for (int t = 0; t < nx || t - lag < nh; ++t) {
-                const bool doA = t < nx;
-                const bool doB = t - lag >= 0 && t - lag < nh;
-                const int r = sg.xlo + t, h = sg.hlo + t - lag;
-                int a_lo = 0, a_n = 0, a_s0 = 0, b_lo = 0, b_n = 0, b_s0 = 0, st = 0, hs = 0;
-                if (doA) {
-                    st = xc % G::XSTAGES;
-                    mbar_wait(&xfull[st], (uint32_t)((xc / G::XSTAGES) & 1), 33);
-                    const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
-                    a_lo = hbase + lo - sg.hlo; a_n = hi - lo + 1; a_s0 = lo - (r - 1);
-                    for (; h_acq < a_lo + a_n; ++h_acq)
-                        mbar_wait(&haempty[h_acq % G::RH], (uint32_t)(((h_acq / G::RH) & 1) ^ 1), 34);
+            for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
+                mbar_wait(&xfull[xst], xph, 33);
+                const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
+                const int a_lo = hbase + lo - sg.hlo, a_n = hi - lo + 1, a_s0 = lo - (r - 1);
+                for (; h_acq < a_lo + a_n; ++h_acq) {
+                    mbar_wait(&haempty[acq_slot], acq_ph, 34);
+                    if (++acq_slot == G::RH) { acq_slot = 0; acq_ph ^= 1; }
                 }
-                if (doB) {
-                    const int hc = hbase + h - sg.hlo;
-                    hs = hc % G::HSLOTS;
-                    mbar_wait(&hsfull[hs], (uint32_t)((hc / G::HSLOTS) & 1), 35);
-                    const int lo = h - 1 > sg.y0 ? h - 1 : sg.y0, hi = h + 1 < sg.y1 - 1 ? h + 1 : sg.y1 - 1;
-                    b_lo = ybase + lo - sg.y0; b_n = hi - lo + 1; b_s0 = lo - (h - 1);
-                    for (; y_acq < b_lo + b_n; ++y_acq)
-                        mbar_wait(&yaempty[y_acq % G::RY], (uint32_t)(((y_acq / G::RY) & 1) ^ 1), 36);
-                }
+                const int slot_lo = (hslot0 + (lo - sg.hlo)) % G::RH;
                 tc_fence_after();
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
                 if (elect_one()) {
-                    const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + st * G::XROW) >> 4);
-                    const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
+                    const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
+                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, slot_lo, a_n, a_s0);
+                    if (!(p.dbg_skip & (2 | 16))) {
 #pragma unroll
-                    for (int k = 0; k < G::KB; ++k) {
-#pragma unroll
-                        for (int kk = 2 * k; kk < 2 * k + 2; ++kk)
-                            if (doA) {
-                                const int dx = kk >> 2, c2 = kk & 3;
-                                rb_mma_fold<G::CH, G::RH, BF16>(tmem_base + G::TM_H, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4),
-                                                                bdescA0 + (uint64_t)((kk * G::WA_STEP) >> 4), a_lo, a_n, a_s0);
-                            }
-                        if (doB) {
-                            const int dx = k >> 1, c2 = k & 1;
-                            rb_mma_fold<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, adB + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4),
-                                                            bdescB0 + (uint64_t)((k * G::WB_STEP) >> 4), b_lo, b_n, b_s0);
+                        for (int kk = 0; kk < G::KA; ++kk) {
+                            const int dx = kk >> 2, c2 = kk & 3;
+                            rb_issue(q, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), bdescA0 + (uint64_t)((kk * G::WA_STEP) >> 4));
                         }
                     }
-                    if (doA) {
-                        umma_commit(&xempty[st]);
-                        if (r - 1 >= sg.hlo) umma_commit(&hafull[(hbase + r - 1 - sg.hlo) % G::RH]);
-                        if (r == sg.xhi && r <= sg.hhi) umma_commit(&hafull[(hbase + r - sg.hlo) % G::RH]);
-                    }
-                    if (doB) {
-                        umma_commit(&hsempty[hs]);
-                        if (h - 1 >= sg.y0) umma_commit(&yafull[(ybase + h - 1 - sg.y0) % G::RY]);
-                        if (h == sg.hhi && h <= sg.y1 - 1) umma_commit(&yafull[(ybase + h - sg.y0) % G::RY]);
-                    }
+                    umma_commit(&xempty[xst]);
+                    // hidden row r-1 is complete (all three input rows seen); at the last x row also row r itself
+                    if (r - 1 >= sg.hlo) umma_commit(&hafull[(hslot0 + (r - 1 - sg.hlo)) % G::RH]);
+                    if (r == sg.xhi && r <= sg.hhi) umma_commit(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
                 }
                 __syncwarp();
-                if (doA) ++xc;
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
+                if (++xst == G::XSTAGES) { xst = 0; xph ^= 1; }
             }
-            hbase += nh; ybase += ny;
+            const int nh = sg.hhi - sg.hlo + 1;
+            hbase += nh;
+            hslot0 = (hslot0 + nh) % G::RH;
+        }
+    } else if (warp == 2) {
+        // ===================== convB MMA issuer: one hidden row per step, N = 3 x 64 into the output accumulator ring =====================
+        const uint64_t adescB0 = umma_desc_nosw(0, 160, G::HBOX);
+        const uint64_t bdescB0 = umma_desc_nosw(smem_u32(s_wB), 3 * G::CB * 16, 128);
+        mbar_wait(wbar, 0, 37);
+        int hs = 0; uint32_t hph = 0;                  // hidden smem slot / phase of the next hidden row
+        int yslot0 = 0;                                // ring slot of the segment's first output row
+        int acq_slot = 0; uint32_t acq_ph = 1;
+        int ybase = 0, y_acq = 0, g = g_begin;
+        RBSeg sg;
+        while (rb_next_seg(p, g, g_end, sg)) {
+#pragma unroll 1
+            for (int h = sg.hlo; h <= sg.hhi; ++h) {
+                mbar_wait(&hsfull[hs], hph, 35);
+                const int lo = h - 1 > sg.y0 ? h - 1 : sg.y0, hi = h + 1 < sg.y1 - 1 ? h + 1 : sg.y1 - 1;
+                const int b_lo = ybase + lo - sg.y0, b_n = hi - lo + 1, b_s0 = lo - (h - 1);
+                for (; y_acq < b_lo + b_n; ++y_acq) {
+                    mbar_wait(&yaempty[acq_slot], acq_ph, 36);
+                    if (++acq_slot == G::RY) { acq_slot = 0; acq_ph ^= 1; }
+                }
+                const int slot_lo = (yslot0 + (lo - sg.y0)) % G::RY;
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
+                    const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, slot_lo, b_n, b_s0);
+                    if (!(p.dbg_skip & (2 | 32))) {
+#pragma unroll
+                        for (int k = 0; k < G::KB; ++k) {
+                            const int dx = k >> 1, c2 = k & 1;
+                            rb_issue(q, adB + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), bdescB0 + (uint64_t)((k * G::WB_STEP) >> 4));
+                        }
+                    }
+                    umma_commit(&hsempty[hs]);
+                    if (h - 1 >= sg.y0) umma_commit(&yafull[(yslot0 + (h - 1 - sg.y0)) % G::RY]);
+                    if (h == sg.hhi && h <= sg.y1 - 1) umma_commit(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
+                }
+                __syncwarp();
+                if (++hs == G::HSLOTS) { hs = 0; hph ^= 1; }
+            }
+            const int ny = sg.y1 - sg.y0;
+            ybase += ny;
+            yslot0 = (yslot0 + ny) % G::RY;
         }
     }
-    else if (warp >= 4 && warp < 8) {
+    else if (warp >= 4 && warp < 12) {
         // ===================== hidden epilogue: TMEM -> bias, LeakyReLU -> 16-bit -> shared memory (convB's A operand) =====================
+        // Two sets of 4 warps alternate rows: a row's hand-off time is dominated by fixed latencies (TMEM load, shared
+        // stores, fences, barrier round trips), so rows are overlapped rather than split.
         const int lg = warp & 3;
+        const int set = (warp - 4) >> 2;
         const int L = lg * 32 + lane;              // accumulator lane = pixel of the row
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + G::TM_H + ((uint32_t)(lg * 32) << 16);
         const uint32_t s_h_u32 = smem_u32(s_h);
-        const uint32_t s_bias_u32 = smem_u32(s_bias);
+        const float4* sb4 = reinterpret_cast<const float4*>(s_bias);
+        const bool tr = p.dbg_trace != nullptr && lane == 0 && lg == 0;
         int hbase = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
@@ -280,18 +351,22 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int c = hbase + h - sg.hlo;
+                if ((c & 1) != set) continue;
                 const int slot = c % G::RH, hs = c % G::HSLOTS;
-                mbar_wait(&hafull[slot], (uint32_t)((c / G::RH) & 1), 41);
+                if (tr) rb_trace(p, c, 2);        // hidden epilogue starts waiting
+                mbar_wait<RB_SLEEP>(&hafull[slot], (uint32_t)((c / G::RH) & 1), 41);
+                if (tr) rb_trace(p, c, 3);        // hidden accumulator complete
                 tc_fence_after();
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CH, rr);
                 tmem_ld_wait();
-                tmem_zero32(t_lane + slot * G::CH);
-                mbar_wait(&hsempty[hs], (uint32_t)(((c / G::HSLOTS) & 1) ^ 1), 42);
-                const uint32_t box = s_h_u32 + hs * G::HROW + grp * G::HBOX;
+                if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
+                if (tr) rb_trace(p, c, 11);
+                // all arithmetic first (plain shared loads: the compiler may overlap the four planes), then the stores
+                uint4 o[4];
 #pragma unroll
                 for (int pl = 0; pl < 4; ++pl) {
-                    const float4 b0 = lds_f4(s_bias_u32 + (8 * pl) * 4), b1 = lds_f4(s_bias_u32 + (8 * pl + 4) * 4);
+                    const float4 b0 = sb4[2 * pl], b1 = sb4[2 * pl + 1];
                     const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
                     float v[8];
 #pragma unroll
@@ -300,81 +375,139 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                         tt = fmaxf(tt, tt * p.slope);
                         v[k] = valid ? tt : 0.f;     // outside the image the hidden activation is convB's zero padding
                     }
-                    uint4 o;
-                    o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
-                    o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
-                    sts_u4(box + pl * 160 + (i + 1) * 16, o);
-                    if (left) sts_u4(box - G::HBOX + pl * 160 + 9 * 16, o);      // right halo slot of the group to the left
-                    if (right) sts_u4(box + G::HBOX + pl * 160, o);              // left halo slot of the group to the right
+                    o[pl].x = pack2<BF16>(v[0], v[1]); o[pl].y = pack2<BF16>(v[2], v[3]);
+                    o[pl].z = pack2<BF16>(v[4], v[5]); o[pl].w = pack2<BF16>(v[6], v[7]);
                 }
+                mbar_wait<RB_SLEEP>(&hsempty[hs], (uint32_t)(((c / G::HSLOTS) & 1) ^ 1), 42);
+                if (tr) rb_trace(p, c, 12);
+                const uint32_t box = s_h_u32 + hs * G::HROW + grp * G::HBOX;
+#pragma unroll
+                for (int pl = 0; pl < 4; ++pl) {
+                    sts_u4(box + pl * 160 + (i + 1) * 16, o[pl]);
+                    if (left) sts_u4(box - G::HBOX + pl * 160 + 9 * 16, o[pl]);      // right halo slot of the group to the left
+                    if (right) sts_u4(box + G::HBOX + pl * 160, o[pl]);              // left halo slot of the group to the right
+                }
+                if (tr) rb_trace(p, c, 13);
                 tmem_st_wait();
                 tc_fence_before();
+                if (tr) rb_trace(p, c, 14);
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) { mbar_arrive(&haempty[slot]); mbar_arrive(&hsfull[hs]); }
+                if (tr) rb_trace(p, c, 4);        // hidden row published
             }
             hbase += sg.hhi - sg.hlo + 1;
         }
-    } else if (warp >= 8) {
-        // ===================== output epilogue: two sets of 4 warps alternate rows; + bias + x (residual) -> y =====================
-        const int lg = warp & 3;
-        const int set = (warp - 8) >> 2;
-        const int L = lg * 32 + lane;
-        const int grp = L >> 3, i = L & 7;
-        const uint32_t t_lane = tmem_base + G::TM_Y + ((uint32_t)(lg * 32) << 16);
-        const uint32_t s_bias_u32 = smem_u32(s_bias) + G::CH * 4;
-        int ybase = 0, g = g_begin;
+    } else if (warp == 3) {
+        // ===================== output I/O warp: residual rows in, finished rows out — all by TMA =====================
+        // Two 16 KB staging slots alternate by row ([box][plane][pixel] granules).  Per row: wait until the epilogue has
+        // staged it, TMA-store the slot, wait until the store has read it, then TMA-load the residual (x) row that will
+        // use the slot next (two rows ahead; an L2 hit).  Keeping this off the epilogue warps matters: a thread that
+        // issues a bulk store and waits for its read blocks for ~1000 clk.
+        const int gpb = p.BW >> 3, nbox = 16 / gpb, box_bytes = 8 * p.BW * 16;
+        const bool io = !(p.dbg_skip & 4);
+        auto load_residual = [&](int sl, int ss, int yy) {      // one elected lane
+            if (!io || (p.dbg_skip & 128)) { mbar_arrive(&rfull[sl]); return; }
+            mbar_arrive_expect_tx(&rfull[sl], G::YROW);
+            for (int b = 0; b < nbox; ++b) {
+                const int q = ss * 16 + b * gpb;
+                const int n = q / p.GX, gx = q - n * p.GX;
+                tma_load_4d(s_y + sl * G::YROW + b * box_bytes, &tmap_xr, &rfull[sl], gx * 8 * 4, yy, 0, n);
+            }
+        };
+        // load cursor (runs two rows ahead of the store cursor over the same row sequence)
+        int gl = g_begin; RBSeg sl_seg; bool l_have = rb_next_seg(p, gl, g_end, sl_seg); int ly = l_have ? sl_seg.y0 : 0; int lc = 0;
+        auto load_next = [&]() {
+            if (!l_have) return;
+            if (lane == 0) load_residual(lc & 1, sl_seg.ss, ly);
+            ++lc;
+            if (++ly >= sl_seg.y1) { l_have = rb_next_seg(p, gl, g_end, sl_seg); ly = l_have ? sl_seg.y0 : 0; }
+        };
+        load_next(); load_next();
+        int c = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + grp;
-            const int n = q / p.GX, gx = q - n * p.GX;
-            const int xx = gx * 8 + i;
-            const bool valid = n < p.N && xx < p.W;
 #pragma unroll 1
-            for (int y = sg.y0; y < sg.y1; ++y) {
-                const int c = ybase + y - sg.y0;
-                if ((c & 1) != set) continue;
-                const int slot = c % G::RY;
-                const size_t pix = valid ? ((size_t)n * 8 * HW + (size_t)y * p.W + xx) : 0;
-                uint4 res[8];
-#pragma unroll
-                for (int pl = 0; pl < 8; ++pl)
-                    res[pl] = valid ? ldg_nc16(reinterpret_cast<const uint8_t*>(p.x) + (pix + pl * HW) * 16) : make_uint4(0, 0, 0, 0);
-                mbar_wait(&yafull[slot], (uint32_t)((c / G::RY) & 1), 43);
-                tc_fence_after();
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t rr[32];
-                    tmem_ld32(t_lane + slot * G::CB + half * 32, rr);
-                    tmem_ld_wait();
-                    tmem_zero32(t_lane + slot * G::CB + half * 32);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int pl = half * 4 + j;
-                        const float4 b0 = lds_f4(s_bias_u32 + (8 * pl) * 4), b1 = lds_f4(s_bias_u32 + (8 * pl + 4) * 4);
-                        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                        const uint32_t qq[4] = {res[pl].x, res[pl].y, res[pl].z, res[pl].w};
-                        float v[8];
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float2 f = unpack2<BF16>(qq[k]);
-                            v[2 * k] = __uint_as_float(rr[8 * j + 2 * k]) + bb[2 * k] + f.x;
-                            v[2 * k + 1] = __uint_as_float(rr[8 * j + 2 * k + 1]) + bb[2 * k + 1] + f.y;
+            for (int y = sg.y0; y < sg.y1; ++y, ++c) {
+                const int sl = c & 1;
+                mbar_wait(&sfull[sl], (uint32_t)((c >> 1) & 1), 45);
+                if (lane == 0) {
+                    if (io && !(p.dbg_skip & 256)) {
+                        for (int b = 0; b < nbox; ++b) {
+                            const int q = sg.ss * 16 + b * gpb;
+                            const int n = q / p.GX, gx = q - n * p.GX;
+                            if (n < p.N) tma_store_4d(&tmap_y, s_y + sl * G::YROW + b * box_bytes, gx * 8 * 4, y, 0, n);
                         }
-                        if (valid) {
-                            uint4 o;
-                            o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
-                            o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
-                            *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.y) + (pix + pl * HW) * 16) = o;
-                        }
+                        tma_store_commit();
+                        tma_store_wait_read();
                     }
+                }
+                __syncwarp();
+                load_next();                     // row c+2 takes the slot
+            }
+        }
+        if (lane == 0) tma_store_wait_all();
+        __syncwarp();
+    } else if (warp >= 12) {
+        // ===================== output epilogue: 8 warps per row (two channel halves); + bias + x (residual) -> y =====================
+        // The residual row is already in the row's staging slot (I/O warp); every thread adds accumulator + bias to its
+        // own pixel in place and the slot is handed back to the I/O warp for the TMA store.  (Per-thread global loads /
+        // stores cost an epilogue thread ~70 clk each here; measured.)
+        const int lg = warp & 3;
+        const int half = (warp - 12) >> 2;         // channels 32*half .. : planes 4*half .. 4*half+3
+        const int L = lg * 32 + lane;
+        const int grp = L >> 3, i = L & 7;
+        const uint32_t t_lane = tmem_base + G::TM_Y + half * 32 + ((uint32_t)(lg * 32) << 16);
+        const float4* sb4 = reinterpret_cast<const float4*>(s_bias + G::CH + half * 32);
+        const bool tr = p.dbg_trace != nullptr && threadIdx.x == 384;
+        const int gpb = p.BW >> 3;                                  // groups per box
+        const int box_bytes = 8 * p.BW * 16, plane_bytes = p.BW * 16;
+        const uint32_t s_px0 = smem_u32(s_y) + (grp / gpb) * box_bytes + ((grp % gpb) * 8 + i) * 16 + 4 * half * plane_bytes;
+        int c = 0, g = g_begin;                    // c: running output-row counter (staging slot c & 1, accumulator slot c % RY)
+        int slot = 0; uint32_t yph = 0;
+        RBSeg sg;
+        while (rb_next_seg(p, g, g_end, sg)) {
+#pragma unroll 1
+            for (int y = sg.y0; y < sg.y1; ++y, ++c) {
+                const int sl = c & 1;
+                if (tr) rb_trace(p, c, 5);      // output epilogue starts waiting
+                mbar_wait<RB_SLEEP>(&yafull[slot], yph, 43);
+                if (tr) rb_trace(p, c, 6);      // output accumulator complete
+                tc_fence_after();
+                uint32_t rr[32];
+                tmem_ld32(t_lane + slot * G::CB, rr);
+                tmem_ld_wait();
+                if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CB);
+                mbar_wait<RB_SLEEP>(&rfull[sl], (uint32_t)((c >> 1) & 1), 44);
+                if (tr) rb_trace(p, c, 8);
+                const uint32_t s_px = s_px0 + sl * G::YROW;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 b0 = sb4[2 * j], b1 = sb4[2 * j + 1];
+                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                    const uint4 rq = lds_u4(s_px + j * plane_bytes);
+                    const uint32_t qq[4] = {rq.x, rq.y, rq.z, rq.w};
+                    float v[8];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float2 f = unpack2<BF16>(qq[k]);
+                        v[2 * k] = __uint_as_float(rr[8 * j + 2 * k]) + bb[2 * k] + f.x;
+                        v[2 * k + 1] = __uint_as_float(rr[8 * j + 2 * k + 1]) + bb[2 * k + 1] + f.y;
+                    }
+                    uint4 o;
+                    o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
+                    o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
+                    sts_u4(s_px + j * plane_bytes, o);
                 }
                 tmem_st_wait();
                 tc_fence_before();
+                if (tr) rb_trace(p, c, 9);
+                fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&yaempty[slot]);
+                if (lane == 0) { mbar_arrive(&yaempty[slot]); mbar_arrive(&sfull[sl]); }
+                if (tr) rb_trace(p, c, 7);      // output row handed to the I/O warp
+                if (++slot == G::RY) { slot = 0; yph ^= 1; }
             }
-            ybase += sg.y1 - sg.y0;
         }
     }
 

@@ -30,6 +30,9 @@ __global__ void __launch_bounds__(128, 1) ubench_mma_kernel(int layout, int racc
         uint64_t adesc, bdesc;
         if (layout == 0) { adesc = umma_desc_nosw(a_addr, 2880, 160); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }
         else if (layout == 1) { adesc = umma_desc_nosw(a_addr, 2048, 128); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }
+        else if (layout == 3) { adesc = umma_desc_nosw(a_addr, 160, 1280); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }   // resblock x row
+        else if (layout == 4) { adesc = umma_desc_nosw(a_addr, 160, 640); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }    // resblock hidden row
+        else if (layout == 5) { adesc = umma_desc_nosw(a_addr, 176, 1408); bdesc = umma_desc_nosw(b_addr, N * 16, 128); }   // 11-px boxes (odd 16-B pitch)
         else {
             adesc = umma_desc_nosw(a_addr, 16, 1024) | (2ull << 61);
             bdesc = umma_desc_nosw(b_addr, 16, 1024) | (2ull << 61);
