@@ -55,6 +55,8 @@ struct srb_ctx {
     int dbg_swap = 0;
     int dbg_grid = 0;
     int dbg_skip = 0;
+    int dbg_repeat = 0;       // probes: launch the fused block this many extra times per call
+    int dbg_threads = 0, dbg_smem = -1;
     long long* dbg_trace = nullptr;
     // pinned + device staging for the *_host entry
     uint8_t* h_pin = nullptr; size_t h_pin_bytes = 0;
@@ -126,6 +128,9 @@ extern "C" int srb_debug_set(srb_ctx* c, int key, int value) {
     if (key == 0) c->dbg_swap = value;
     else if (key == 1) c->dbg_grid = value;
     else if (key == 2) c->dbg_skip = value;
+    else if (key == 3) c->dbg_repeat = value;
+    else if (key == 4) c->dbg_threads = value;
+    else if (key == 5) c->dbg_smem = value;
     else return fail(SRB_EINVAL, "srb_debug_set: unknown key %d", key);
     return SRB_OK;
 }
@@ -1039,10 +1044,14 @@ extern "C" int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t 
 // ------------------------------------------------------------------------------------------
 // fused residual block (srb_resblock.cuh)
 // ------------------------------------------------------------------------------------------
+struct RBMaps { const void* x = nullptr; void* y = nullptr; int N = 0, H = 0, W = 0; CUtensorMap tm, tmxr, tmy; };
 struct srb_resblock {
     int dtype = 0;
     uint8_t* d_wA = nullptr; uint8_t* d_wB = nullptr;
     float* d_bA = nullptr; float* d_bB = nullptr;
+    mutable RBMaps maps[2];          // tensor maps of the last two (x, y, shape) pairs: a trunk ping-pongs two buffers
+    mutable int next_map = 0;
+    mutable bool attr_set = false;
 };
 
 extern "C" void srb_resblock_destroy(srb_resblock* rb) {
@@ -1105,33 +1114,33 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     if (((uintptr_t)x & 15) || ((uintptr_t)y & 15)) return fail(SRB_EINVAL, "srb_resblock_fwd: buffers must be 16-byte aligned");
     if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_resblock_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
     using G = RBGeom;
-    CUtensorMap tm;
-    {
-        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
-        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
-        cuuint32_t box[4] = {40, 1, 8, 1};
-        cuuint32_t estr[4] = {1, 1, 1, 1};
-        CUresult r = ctx->encode(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
-                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
-    }
     ResblockParams p{};
     p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
     p.BW = p.GX * 8 < 64 ? p.GX * 8 : 64;
-    CUtensorMap tmy, tmxr;   // residual rows arrive and output rows leave as TMA boxes of BW px x 8 planes
-    {
+    RBMaps* m = nullptr;
+    for (RBMaps& c : rb->maps)
+        if (c.x == x && c.y == y && c.N == N && c.H == H && c.W == W) m = &c;
+    if (!m) {
+        m = &rb->maps[rb->next_map];
+        rb->next_map ^= 1;
+        m->x = nullptr;
         cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
         cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
-        cuuint32_t box[4] = {(cuuint32_t)p.BW * 4, 1, 8, 1};
         cuuint32_t estr[4] = {1, 1, 1, 1};
-        CUresult r = ctx->encode(&tmy, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, y, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        cuuint32_t box[4] = {40, 1, 8, 1};                              // convA operand: one group with its halo
+        cuuint32_t boxr[4] = {(cuuint32_t)p.BW * 4, 1, 8, 1};            // residual rows in / output rows out: BW px x 8 planes
+        CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r == CUDA_SUCCESS)
-            r = ctx->encode(&tmxr, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+            r = ctx->encode(&m->tmy, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, y, gdim, gstr, boxr, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r == CUDA_SUCCESS)
+            r = ctx->encode(&m->tmxr, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, boxr, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled (residual / output) failed: %d", (int)r);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+        m->x = x; m->y = y; m->N = N; m->H = H; m->W = W;
     }
     const long long groups = (long long)N * p.GX;
     const long long sets = (groups + 15) / 16;
@@ -1143,14 +1152,24 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     if (grid < 1) grid = 1;
     if (grid > ctx->num_sms) grid = ctx->num_sms;
     if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
-    cudaStream_t st = (cudaStream_t)stream;
-    if (rb->dtype == SRB_DT_BF16) {
+    if (!rb->attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        resblock_kernel<true><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, tmxr, tmy, p);
-    } else {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        resblock_kernel<false><<<grid, G::THREADS, G::SMEM_BYTES, st>>>(tm, tmxr, tmy, p);
+        rb->attr_set = true;
     }
-    CUDA_TRY(cudaGetLastError());
+    // programmatic dependent launch: this launch's prologue (barriers, TMEM, filters) overlaps the previous launch's tail
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if ((ctx->dbg_skip & 4096) && ctx->dbg_threads > 0) cfg.blockDim = dim3(ctx->dbg_threads);     // launch-overhead probes only
+    if ((ctx->dbg_skip & 4096) && ctx->dbg_smem >= 0) cfg.dynamicSmemBytes = ctx->dbg_smem;
+    for (int rep = 0; rep <= ctx->dbg_repeat; ++rep) {
+        if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, m->tmxr, m->tmy, p));
+        else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, m->tmxr, m->tmy, p));
+    }
     return SRB_OK;
 }

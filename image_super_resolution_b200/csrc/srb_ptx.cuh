@@ -112,6 +112,11 @@ __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk
 // all committed bulk stores of this thread have finished READING shared memory (the source may be overwritten)
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// Programmatic dependent launch: a kernel launched with programmaticStreamSerialization may start while its predecessor
+// in the stream is still running; pdl_wait() blocks until the predecessor has completed and its writes are visible (a
+// no-op for a normal launch), pdl_launch_dependents() lets the successor's CTAs take the SMs this grid's CTAs vacate.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 // named barrier among `count` threads (id 1..15; id 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");

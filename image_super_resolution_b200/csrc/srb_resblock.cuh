@@ -45,7 +45,7 @@ struct RBGeom {
     static constexpr int CA = 64, CH = 32, CB = 64;            // channels: in, hidden, out
     static constexpr int XBOX = 8 * 10 * 16;                    // one group box of x: [8 planes][10 px][16 B]
     static constexpr int XROW = 16 * XBOX;                      // 20480 B per x row
-    static constexpr int XSTAGES = 4;
+    static constexpr int XSTAGES = 3;
     static constexpr int HBOX = 4 * 10 * 16;                    // hidden group box: [4 planes][10 px][16 B]
     static constexpr int HROW = 16 * HBOX;                      // 10240 B
     static constexpr int HSLOTS = 3;
@@ -56,10 +56,11 @@ struct RBGeom {
     static constexpr int TM_H = 0, TM_Y = RH * CH;              // column bases: 0, 192 (+ 5*64 = 512)
     static constexpr int OFF_WA = 0, OFF_WB = WA_BYTES, OFF_X = OFF_WB + WB_BYTES, OFF_H = OFF_X + XSTAGES * XROW;
     static constexpr int YROW = 128 * CB * 2;                   // one output row staged for the TMA store: 16 KB
-    static constexpr int OFF_Y = OFF_H + HSLOTS * HROW;         // two staging slots (one per output-epilogue set)
-    static constexpr int OFF_BIAS = OFF_Y + 2 * YROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
+    static constexpr int YSLOTS = 3;                            // staging slots: residual row in, finished row out
+    static constexpr int OFF_Y = OFF_H + HSLOTS * HROW;
+    static constexpr int OFF_BIAS = OFF_Y + YSLOTS * YROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
-    static constexpr int THREADS = 640;            // 4 control warps + 8 hidden-epilogue warps + 8 output-epilogue warps
+    static constexpr int THREADS = 672;            // 4 control warps + 8 hidden-epilogue + 8 output-epilogue warps + second I/O warp
     static_assert(RH * CH + RY * CB == 512, "the two accumulator rings fill TMEM");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
     static_assert(XSTAGES <= 8 && RH <= 8 && HSLOTS <= 4 && RY <= 8, "barrier array layout");
@@ -151,7 +152,9 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                                                                       const ResblockParams p) {
     using G = RBGeom;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // (offset arithmetic on the __shared__ array, not an integer round trip: the compiler keeps the shared address space
+    // and the epilogues' plain loads / stores become LDS / STS instead of generic accesses)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* s_wA = smem + G::OFF_WA;
     uint8_t* s_wB = smem + G::OFF_WB;
     uint8_t* s_x = smem + G::OFF_X;
@@ -168,12 +171,37 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     uint64_t* yafull = bars + 40;      // [RY] output accumulator row complete        MMA -> output epilogue
     uint64_t* yaempty = bars + 48;     // [RY] drained and re-zeroed                  output epilogue -> MMA
     uint64_t* wbar = bars + 56;
-    uint64_t* rfull = bars + 57;       // [2] staging slot free again and the residual row landed in it    I/O warp -> output epilogue
-    uint64_t* sfull = bars + 59;       // [2] output row staged                                              output epilogue -> I/O warp
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 62);
+    uint64_t* rfull = bars + 57;       // [YSLOTS] staging slot free again and the residual row landed in it    I/O warp -> output epilogue
+    uint64_t* sfull = bars + 60;       // [YSLOTS] output row staged                                              output epilogue -> I/O warp
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 63);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (p.dbg_trace != nullptr && threadIdx.x == 0) {           // per-CTA timing: [1024 + 8 * cta + k]
+        long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        p.dbg_trace[1024 + 8 * blockIdx.x] = gt;
+        p.dbg_trace[1024 + 8 * blockIdx.x + 1] = clock64();
+        // per-launch records [2304 + 4 * launch]: earliest CTA start, latest CTA start, earliest end, latest end (ns)
+        const long long old = (long long)atomicAdd((unsigned long long*)&p.dbg_trace[2300], 1ull);
+        const int launch = (int)(old / gridDim.x);
+        if (launch < 400) {
+            atomicMin(&p.dbg_trace[2304 + 4 * launch], gt);
+            atomicMax(&p.dbg_trace[2304 + 4 * launch + 1], gt);
+        }
+        p.dbg_trace[1024 + 8 * blockIdx.x + 6] = launch;
+    }
 
+    if (p.dbg_skip & 4096) {        // launch-overhead probe: nothing but the stamps
+        if (p.dbg_trace != nullptr && threadIdx.x == 0) {
+            long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+            p.dbg_trace[1024 + 8 * blockIdx.x + 5] = gt;
+            const int launch = (int)p.dbg_trace[1024 + 8 * blockIdx.x + 6];
+            if (launch < 400) {
+                atomicMin(&p.dbg_trace[2304 + 4 * launch + 2], gt);
+                atomicMax(&p.dbg_trace[2304 + 4 * launch + 3], gt);
+            }
+        }
+        return;
+    }
     // zero the hidden ring once: halo slots at image borders are never written and must read as zero padding
     for (int i = threadIdx.x; i < G::HSLOTS * G::HROW / 16; i += G::THREADS)
         reinterpret_cast<uint4*>(s_h)[i] = make_uint4(0, 0, 0, 0);
@@ -184,8 +212,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4); mbar_init(&hsempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
         mbar_init(wbar, 1);
-        mbar_init(&rfull[0], 1); mbar_init(&rfull[1], 1);
-        mbar_init(&sfull[0], 8); mbar_init(&sfull[1], 8);
+        for (int i = 0; i < G::YSLOTS; ++i) { mbar_init(&rfull[i], 1); mbar_init(&sfull[i], 8); }
         fence_mbar_init();
         tma_prefetch_desc(&tmap_x);
         tma_prefetch_desc(&tmap_y);
@@ -197,18 +224,30 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
-    if (warp >= 4 && warp < 8) {       // all accumulators start at zero: every MMA of this kernel accumulates
+    if (warp >= 4 && warp < 8) {
+        // every MMA of this kernel accumulates, and an accumulator row starts at its bias (so the epilogues do not add
+        // it): the rings are armed here once and re-armed by the epilogue that drains a row
         const uint32_t lg = (uint32_t)((warp & 3) * 32) << 16;
 #pragma unroll 1
-        for (int c = 0; c < 512; c += 32) tmem_zero32(tmem_base + lg + c);
+        for (int c = 0; c < 512; c += 32) {
+            const int b0 = c < G::TM_Y ? 0 : G::CH + ((c - G::TM_Y) & 32);
+            uint32_t bv[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[b0 + k]);
+            tmem_st32(tmem_base + lg + c, bv);
+        }
         tmem_st_wait();
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
 
+    if (p.dbg_trace != nullptr && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 2] = clock64();
+    // Everything above touched only this launch's constants.  The next launch in the stream may now start its own
+    // prologue on every SM this grid vacates; the warps below that touch activations first wait for the previous launch.
+    pdl_launch_dependents();
     const int g_begin = (int)((long long)blockIdx.x * p.total_rows / gridDim.x);
-    const int g_end = (int)((long long)(blockIdx.x + 1) * p.total_rows / gridDim.x);
+    const int g_end = (p.dbg_skip & 2048) ? g_begin : (int)((long long)(blockIdx.x + 1) * p.total_rows / gridDim.x);   // 2048: prologue-only probe
     const size_t HW = (size_t)p.H * p.W;
 
     if (warp == 0) {
@@ -219,6 +258,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             for (int off = 0; off < G::WB_BYTES; off += 12288) bulk_load_1d(s_wB + off, p.wB + off, 12288, wbar);
         }
         __syncwarp();
+        pdl_wait();                          // x is the previous launch's output
         int xc = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
@@ -264,7 +304,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
                 if (elect_one()) {
                     const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
-                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, slot_lo, a_n, a_s0);
+                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, (p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
                     if (!(p.dbg_skip & (2 | 16))) {
 #pragma unroll
                         for (int kk = 0; kk < G::KA; ++kk) {
@@ -309,7 +349,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tc_fence_after();
                 if (elect_one()) {
                     const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
-                    const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, slot_lo, b_n, b_s0);
+                    const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, (p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
                     if (!(p.dbg_skip & (2 | 32))) {
 #pragma unroll
                         for (int k = 0; k < G::KB; ++k) {
@@ -360,23 +400,29 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CH, rr);
                 tmem_ld_wait();
-                if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
+                if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
+                    uint32_t bv[32];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float4 b = sb4[k];
+                        bv[4 * k] = __float_as_uint(b.x); bv[4 * k + 1] = __float_as_uint(b.y);
+                        bv[4 * k + 2] = __float_as_uint(b.z); bv[4 * k + 3] = __float_as_uint(b.w);
+                    }
+                    tmem_st32(t_lane + slot * G::CH, bv);
+                }
                 if (tr) rb_trace(p, c, 11);
-                // all arithmetic first (plain shared loads: the compiler may overlap the four planes), then the stores
                 uint4 o[4];
 #pragma unroll
                 for (int pl = 0; pl < 4; ++pl) {
-                    const float4 b0 = sb4[2 * pl], b1 = sb4[2 * pl + 1];
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
                     float v[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        float tt = __uint_as_float(rr[8 * pl + k]) + bb[k];
-                        tt = fmaxf(tt, tt * p.slope);
-                        v[k] = valid ? tt : 0.f;     // outside the image the hidden activation is convB's zero padding
+                        const float tt = __uint_as_float(rr[8 * pl + k]);
+                        v[k] = fmaxf(tt, tt * p.slope);
                     }
                     o[pl].x = pack2<BF16>(v[0], v[1]); o[pl].y = pack2<BF16>(v[2], v[3]);
                     o[pl].z = pack2<BF16>(v[4], v[5]); o[pl].w = pack2<BF16>(v[6], v[7]);
+                    if (!valid) o[pl] = make_uint4(0, 0, 0, 0);   // outside the image the hidden activation is convB's zero padding
                 }
                 mbar_wait<RB_SLEEP>(&hsempty[hs], (uint32_t)(((c / G::HSLOTS) & 1) ^ 1), 42);
                 if (tr) rb_trace(p, c, 12);
@@ -398,12 +444,16 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             }
             hbase += sg.hhi - sg.hlo + 1;
         }
-    } else if (warp == 3) {
-        // ===================== output I/O warp: residual rows in, finished rows out — all by TMA =====================
-        // Two 16 KB staging slots alternate by row ([box][plane][pixel] granules).  Per row: wait until the epilogue has
-        // staged it, TMA-store the slot, wait until the store has read it, then TMA-load the residual (x) row that will
-        // use the slot next (two rows ahead; an L2 hit).  Keeping this off the epilogue warps matters: a thread that
-        // issues a bulk store and waits for its read blocks for ~1000 clk.
+    } else if (warp == 3 || warp == 20) {
+        // ===================== output I/O warps: residual rows in, finished rows out — all by TMA =====================
+        // Three 16 KB staging slots rotate by row ([box][plane][pixel] granules); the two I/O warps alternate rows.  Per
+        // row: wait until the epilogue has staged it, TMA-store the slot, wait until the store has read it, then TMA-load
+        // the residual (x) row that will use the slot next (three rows ahead; an L2 hit).  A slot's round trip — store
+        // read-out ~1000 clk, residual load ~1500 clk under load, epilogue ~1000 clk — must fit in YSLOTS row periods:
+        // with two slots it set the row period (2100-2200 clk measured).  Keeping this off the epilogue warps matters
+        // too: a thread that issues a bulk store and waits for its read blocks for ~1000 clk.
+        const int my = warp == 3 ? 0 : 1;
+        pdl_wait();                          // residual rows are the previous launch's output; y may still be read by it
         const int gpb = p.BW >> 3, nbox = 16 / gpb, box_bytes = 8 * p.BW * 16;
         const bool io = !(p.dbg_skip & 4);
         auto load_residual = [&](int sl, int ss, int yy) {      // one elected lane
@@ -415,24 +465,28 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tma_load_4d(s_y + sl * G::YROW + b * box_bytes, &tmap_xr, &rfull[sl], gx * 8 * 4, yy, 0, n);
             }
         };
-        // load cursor (runs two rows ahead of the store cursor over the same row sequence)
-        int gl = g_begin; RBSeg sl_seg; bool l_have = rb_next_seg(p, gl, g_end, sl_seg); int ly = l_have ? sl_seg.y0 : 0; int lc = 0;
+        // load cursor: runs YSLOTS rows ahead of the store cursor over the same row sequence.  Row lc's residual goes
+        // into the slot row lc - YSLOTS just left, so it is loaded by the warp that stored that row (the first YSLOTS
+        // rows by warp 3).
+        int gl = g_begin; RBSeg sl_seg; bool l_have = rb_next_seg(p, gl, g_end, sl_seg); int ly = l_have ? sl_seg.y0 : 0;
+        int lc = 0, lslot = 0;
         auto load_next = [&]() {
             if (!l_have) return;
-            if (lane == 0) load_residual(lc & 1, sl_seg.ss, ly);
+            const bool mine = lc < G::YSLOTS ? my == 0 : ((lc - G::YSLOTS) & 1) == my;
+            if (lane == 0 && mine) load_residual(lslot, sl_seg.ss, ly);
             ++lc;
+            if (++lslot == G::YSLOTS) lslot = 0;
             if (++ly >= sl_seg.y1) { l_have = rb_next_seg(p, gl, g_end, sl_seg); ly = l_have ? sl_seg.y0 : 0; }
         };
-        load_next(); load_next();
-        int c = 0, g = g_begin;
+        for (int i = 0; i < G::YSLOTS; ++i) load_next();
+        int c = 0, g = g_begin, sl = 0; uint32_t sph = 0;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
-                const int sl = c & 1;
-                mbar_wait(&sfull[sl], (uint32_t)((c >> 1) & 1), 45);
-                if (lane == 0) {
-                    if (io && !(p.dbg_skip & 256)) {
+                if ((c & 1) == my) {
+                    mbar_wait(&sfull[sl], sph, 45);
+                    if (lane == 0 && io && !(p.dbg_skip & 256)) {
                         for (int b = 0; b < nbox; ++b) {
                             const int q = sg.ss * 16 + b * gpb;
                             const int n = q / p.GX, gx = q - n * p.GX;
@@ -441,14 +495,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                         tma_store_commit();
                         tma_store_wait_read();
                     }
+                    __syncwarp();
                 }
-                __syncwarp();
-                load_next();                     // row c+2 takes the slot
+                load_next();                     // row c + YSLOTS takes the slot
+                if (++sl == G::YSLOTS) { sl = 0; sph ^= 1; }
             }
         }
         if (lane == 0) tma_store_wait_all();
         __syncwarp();
-    } else if (warp >= 12) {
+    } else if (warp >= 12 && warp < 20) {
         // ===================== output epilogue: 8 warps per row (two channel halves); + bias + x (residual) -> y =====================
         // The residual row is already in the row's staging slot (I/O warp); every thread adds accumulator + bias to its
         // own pixel in place and the slot is handed back to the I/O warp for the TMA store.  (Per-thread global loads /
@@ -462,14 +517,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         const bool tr = p.dbg_trace != nullptr && threadIdx.x == 384;
         const int gpb = p.BW >> 3;                                  // groups per box
         const int box_bytes = 8 * p.BW * 16, plane_bytes = p.BW * 16;
-        const uint32_t s_px0 = smem_u32(s_y) + (grp / gpb) * box_bytes + ((grp % gpb) * 8 + i) * 16 + 4 * half * plane_bytes;
-        int c = 0, g = g_begin;                    // c: running output-row counter (staging slot c & 1, accumulator slot c % RY)
-        int slot = 0; uint32_t yph = 0;
+        uint8_t* const s_px0 = s_y + (grp / gpb) * box_bytes + ((grp % gpb) * 8 + i) * 16 + 4 * half * plane_bytes;
+        int c = 0, g = g_begin;                    // c: running output-row counter
+        int slot = 0; uint32_t yph = 0;            // accumulator ring slot / phase
+        int sl = 0; uint32_t sph = 0;              // staging slot / phase
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
-                const int sl = c & 1;
                 if (tr) rb_trace(p, c, 5);      // output epilogue starts waiting
                 mbar_wait<RB_SLEEP>(&yafull[slot], yph, 43);
                 if (tr) rb_trace(p, c, 6);      // output accumulator complete
@@ -477,28 +532,36 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CB, rr);
                 tmem_ld_wait();
-                if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CB);
-                mbar_wait<RB_SLEEP>(&rfull[sl], (uint32_t)((c >> 1) & 1), 44);
+                if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
+                    uint32_t bv[32];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float4 b = sb4[k];
+                        bv[4 * k] = __float_as_uint(b.x); bv[4 * k + 1] = __float_as_uint(b.y);
+                        bv[4 * k + 2] = __float_as_uint(b.z); bv[4 * k + 3] = __float_as_uint(b.w);
+                    }
+                    tmem_st32(t_lane + slot * G::CB, bv);
+                }
+                if (tr) rb_trace(p, c, 10);
+                mbar_wait<RB_SLEEP>(&rfull[sl], sph, 44);
                 if (tr) rb_trace(p, c, 8);
-                const uint32_t s_px = s_px0 + sl * G::YROW;
+                // plain shared loads / stores: the four planes' loads are issued together, the stores after the math
+                uint8_t* const s_px = s_px0 + sl * G::YROW;
+                uint4 rq[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) rq[j] = *reinterpret_cast<const uint4*>(s_px + j * plane_bytes);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const float4 b0 = sb4[2 * j], b1 = sb4[2 * j + 1];
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                    const uint4 rq = lds_u4(s_px + j * plane_bytes);
-                    const uint32_t qq[4] = {rq.x, rq.y, rq.z, rq.w};
-                    float v[8];
+                    const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
+                    uint32_t ov[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         const float2 f = unpack2<BF16>(qq[k]);
-                        v[2 * k] = __uint_as_float(rr[8 * j + 2 * k]) + bb[2 * k] + f.x;
-                        v[2 * k + 1] = __uint_as_float(rr[8 * j + 2 * k + 1]) + bb[2 * k + 1] + f.y;
+                        ov[k] = pack2<BF16>(__uint_as_float(rr[8 * j + 2 * k]) + f.x, __uint_as_float(rr[8 * j + 2 * k + 1]) + f.y);
                     }
-                    uint4 o;
-                    o.x = pack2<BF16>(v[0], v[1]); o.y = pack2<BF16>(v[2], v[3]);
-                    o.z = pack2<BF16>(v[4], v[5]); o.w = pack2<BF16>(v[6], v[7]);
-                    sts_u4(s_px + j * plane_bytes, o);
+                    *reinterpret_cast<uint4*>(s_px + j * plane_bytes) = make_uint4(ov[0], ov[1], ov[2], ov[3]);
                 }
+                if (tr) rb_trace(p, c, 15);
                 tmem_st_wait();
                 tc_fence_before();
                 if (tr) rb_trace(p, c, 9);
@@ -507,12 +570,24 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (lane == 0) { mbar_arrive(&yaempty[slot]); mbar_arrive(&sfull[sl]); }
                 if (tr) rb_trace(p, c, 7);      // output row handed to the I/O warp
                 if (++slot == G::RY) { slot = 0; yph ^= 1; }
+                if (++sl == G::YSLOTS) { sl = 0; sph ^= 1; }
             }
         }
     }
 
+    if (p.dbg_trace != nullptr && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 3] = clock64();   // producer done
     tc_fence_before();
     __syncthreads();
+    if (p.dbg_trace != nullptr && threadIdx.x == 0) {
+        long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        p.dbg_trace[1024 + 8 * blockIdx.x + 4] = clock64();
+        p.dbg_trace[1024 + 8 * blockIdx.x + 5] = gt;
+        const int launch = (int)p.dbg_trace[1024 + 8 * blockIdx.x + 6];
+        if (launch < 400) {
+            atomicMin(&p.dbg_trace[2304 + 4 * launch + 2], gt);
+            atomicMax(&p.dbg_trace[2304 + 4 * launch + 3], gt);
+        }
+    }
     if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
 }
 

@@ -20,8 +20,8 @@ def timed(n=20):
     for _ in range(n): rb.forward(x, y, 0.2)
     b.record(); torch.cuda.synchronize()
     return a.elapsed_time(b) / n * 1e3
-for skip, name in [(0, "full"), (1, "no TMA"), (2, "no MMA"), (4, "no global I/O in out-epilogue"), (3, "no TMA, no MMA"),
-                   (64, "no TMEM re-zeroing (wrong results)"), (128, "no residual prefetch loads"), (256, "no output stores"), (130, "no MMA, no residual loads"), (258, "no MMA, no stores"), (16, "no convA MMAs"), (32, "no convB MMAs"), (6, "no MMA, no I/O"), (5, "no TMA, no I/O"), (7, "nothing but the barrier protocol + epilogue ALU")]:
+for skip, name in [(0, "full"), (1024, "normal launches (no programmatic dependent launch)"), (1, "no TMA"), (2, "no MMA"), (4, "no global I/O in out-epilogue"), (3, "no TMA, no MMA"),
+                   (64, "no TMEM re-zeroing (wrong results)"), (128, "no residual prefetch loads"), (256, "no output stores"), (130, "no MMA, no residual loads"), (258, "no MMA, no stores"), (512, "no MMA split at the ring wrap (wrong results)"), (16, "no convA MMAs"), (32, "no convB MMAs"), (6, "no MMA, no I/O"), (5, "no TMA, no I/O"), (7, "nothing but the barrier protocol + epilogue ALU")]:
     ctx.debug_set(2, skip)
     print(f"skip={skip} ({name}): {timed():7.1f} us")
 ctx.debug_set(2, 0)
