@@ -10,7 +10,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsrb200.so")
+LIB_PATH = os.environ.get("SRB200_LIB") or os.path.join(_HERE, "libsrb200.so")   # override: kernel-variant sweeps (tools/)
 
 SRB_DT_F16, SRB_DT_BF16, SRB_DT_F32 = 0, 1, 2
 F_LRELU, F_RESIDUAL, F_TANH, F_U8OUT, F_PIXSHUF2, F_F32OUT, F_MASK = 1, 2, 4, 8, 16, 32, 64

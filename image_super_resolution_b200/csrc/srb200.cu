@@ -55,6 +55,7 @@ struct srb_ctx {
     int dbg_swap = 0;
     int dbg_grid = 0;
     int dbg_skip = 0;
+    bool pdl = false;         // launch the conv kernels with programmatic stream serialization (set by srb_model_pt_forward)
     int dbg_repeat = 0;       // probes: launch the fused block this many extra times per call
     int dbg_threads = 0, dbg_smem = -1;
     long long* dbg_trace = nullptr;
@@ -315,16 +316,21 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     p.dbg_swap = ctx->dbg_swap;
     p.dbg_skip = ctx->dbg_skip;
     p.dbg_trace = ctx->dbg_trace;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(CONV_THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = ctx->pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
     if (w->dtype == SRB_DT_BF16) {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, true, BWD>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tmap, tmap_res, p));
     } else {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, false, BWD>;
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-        kern<<<grid, CONV_THREADS, G::SMEM_BYTES, st>>>(tmap, tmap_res, p);
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tmap, tmap_res, p));
     }
-    CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
 
@@ -643,6 +649,8 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     const float s = net->slope;
     int rc;
     cudaStream_t pst = (cudaStream_t)stream;
+    struct PdlScope { srb_ctx* c; ~PdlScope() { c->pdl = false; } } pdl_scope{ctx};
+    ctx->pdl = !(ctx->dbg_skip & 1024);
     prof_mark(ctx, pst, true);
     if ((rc = srb_u8nchw_to_c8(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
@@ -1044,11 +1052,12 @@ extern "C" int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t 
 // ------------------------------------------------------------------------------------------
 // fused residual block (srb_resblock.cuh)
 // ------------------------------------------------------------------------------------------
-struct RBMaps { const void* x = nullptr; void* y = nullptr; int N = 0, H = 0, W = 0; CUtensorMap tm, tmxr, tmy; };
+struct RBMaps { const void* x = nullptr; int N = 0, H = 0, W = 0; CUtensorMap tm; };
 struct srb_resblock {
     int dtype = 0;
     uint8_t* d_wA = nullptr; uint8_t* d_wB = nullptr;
     float* d_bA = nullptr; float* d_bB = nullptr;
+    float h_bias[32 + 64] = {};      // the kernel takes the biases by value (constant bank)
     mutable RBMaps maps[2];          // tensor maps of the last two (x, y, shape) pairs: a trunk ping-pongs two buffers
     mutable int next_map = 0;
     mutable bool attr_set = false;
@@ -1095,6 +1104,8 @@ extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* b
     CUDA_TRY(cudaMemcpy(rb->d_wB, pb.data(), G::WB_BYTES, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(rb->d_bA, bA, G::CH * 4, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(rb->d_bB, bB, G::CB * 4, cudaMemcpyHostToDevice));
+    memcpy(rb->h_bias, bA, G::CH * 4);
+    memcpy(rb->h_bias + G::CH, bB, G::CB * 4);
     *out = rb;
     return SRB_OK;
 }
@@ -1119,7 +1130,7 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     p.BW = p.GX * 8 < 64 ? p.GX * 8 : 64;
     RBMaps* m = nullptr;
     for (RBMaps& c : rb->maps)
-        if (c.x == x && c.y == y && c.N == N && c.H == H && c.W == W) m = &c;
+        if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
     if (!m) {
         m = &rb->maps[rb->next_map];
         rb->next_map ^= 1;
@@ -1128,25 +1139,18 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
         cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
         cuuint32_t estr[4] = {1, 1, 1, 1};
         cuuint32_t box[4] = {40, 1, 8, 1};                              // convA operand: one group with its halo
-        cuuint32_t boxr[4] = {(cuuint32_t)p.BW * 4, 1, 8, 1};            // residual rows in / output rows out: BW px x 8 planes
         CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r == CUDA_SUCCESS)
-            r = ctx->encode(&m->tmy, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, y, gdim, gstr, boxr, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r == CUDA_SUCCESS)
-            r = ctx->encode(&m->tmxr, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, boxr, estr,
-                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
-        m->x = x; m->y = y; m->N = N; m->H = H; m->W = W;
+        m->x = x; m->N = N; m->H = H; m->W = W;
     }
     const long long groups = (long long)N * p.GX;
     const long long sets = (groups + 15) / 16;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_resblock_fwd: too many rows");
     p.total_rows = (int)(sets * H);
-    p.wA = rb->d_wA; p.wB = rb->d_wB; p.biasA = rb->d_bA; p.biasB = rb->d_bB;
+    p.wA = rb->d_wA; p.wB = rb->d_wB;
+    memcpy(p.bias, rb->h_bias, sizeof(p.bias));
     p.x = x; p.y = y; p.slope = slope; p.dbg_skip = ctx->dbg_skip; p.dbg_trace = ctx->dbg_trace;
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
@@ -1168,8 +1172,8 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     if ((ctx->dbg_skip & 4096) && ctx->dbg_threads > 0) cfg.blockDim = dim3(ctx->dbg_threads);     // launch-overhead probes only
     if ((ctx->dbg_skip & 4096) && ctx->dbg_smem >= 0) cfg.dynamicSmemBytes = ctx->dbg_smem;
     for (int rep = 0; rep <= ctx->dbg_repeat; ++rep) {
-        if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, m->tmxr, m->tmy, p));
-        else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, m->tmxr, m->tmy, p));
+        if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, p));
+        else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, p));
     }
     return SRB_OK;
 }

@@ -205,6 +205,10 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
+    // programmatic dependent launch (srb_model_pt_forward chains its launches this way): the prologue above touched only
+    // this launch's constants; the next launch may start its own on the SMs this grid vacates, and every warp below that
+    // touches activations first waits for the previous launch to complete (a no-op for a normal launch)
+    pdl_launch_dependents();
 
     const int tiles_per_img = p.tiles_x * p.tiles_y;
 
@@ -218,6 +222,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
             }
         }
         __syncwarp();
+        pdl_wait();
         int s = 0; uint32_t ph = 0;
         int pit = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++pit) {
@@ -324,6 +329,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     } else if (warp == 2) {
         // ===================== residual producer (RES): one TMA box per M-tile into the smem ring =====================
         if constexpr (RES) {
+            pdl_wait();
             int rs = 0; uint32_t rph = 0;
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
                 const int n = tile / tiles_per_img;
@@ -350,6 +356,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
         // (one warp per scheduler cannot hide its own ALU latency; two or more per scheduler can)
         const int lg = warp & 3;                  // TMEM lane group this warp may access
         const int eset = (warp - 4) >> 2;
+        pdl_wait();                               // outputs may still be read, residual / mask written, by the previous launch
         const int L = lg * 32 + lane;             // accumulator row = pixel of the M-tile
         const size_t HW = (size_t)p.H * p.W;
         const bool io = !(p.dbg_skip & 4);

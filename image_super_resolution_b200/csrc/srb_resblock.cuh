@@ -30,8 +30,7 @@ struct ResblockParams {
     int total_rows;           // strip-sets x H: the flattened (strip-set, output row) space split evenly over CTAs
     const uint8_t* wA;        // fold-packed 64 -> 32:  12 K-steps x [2][96][8]
     const uint8_t* wB;        // fold-packed 32 -> 64:   6 K-steps x [2][192][8]
-    const float* biasA;       // 32
-    const float* biasB;       // 64
+    float bias[32 + 64];      // convA, convB biases, by value (copied to shared memory in the prologue)
     const void* x;            // [N][8][H][W][8]
     void* y;                  // [N][8][H][W][8]
     float slope;
@@ -39,28 +38,32 @@ struct ResblockParams {
     int dbg_skip;             // bottleneck probes: 1 = no TMA loads, 2 = no MMAs (16 = no convA, 32 = no convB MMAs), 4 = no global I/O in the output epilogue
 };
 
+#ifndef RB_RH
+#define RB_RH 6
+#define RB_RY 5
+#define RB_HSLOTS 3
+#define RB_XSTAGES 4
+#endif
 constexpr int RB_SLEEP = 40;   // ns between polls of the epilogue warps' waits
 
 struct RBGeom {
     static constexpr int CA = 64, CH = 32, CB = 64;            // channels: in, hidden, out
     static constexpr int XBOX = 8 * 10 * 16;                    // one group box of x: [8 planes][10 px][16 B]
     static constexpr int XROW = 16 * XBOX;                      // 20480 B per x row
-    static constexpr int XSTAGES = 3;
-    static constexpr int HBOX = 4 * 10 * 16;                    // hidden group box: [4 planes][10 px][16 B]
+    static constexpr int XSTAGES = RB_XSTAGES;
+    static constexpr int HPLANE = 10 * 16;
+    static constexpr int HBOX = 4 * HPLANE;                     // hidden group box: [4 planes][10 px][16 B]
     static constexpr int HROW = 16 * HBOX;                      // 10240 B
-    static constexpr int HSLOTS = 3;
+    static constexpr int HSLOTS = RB_HSLOTS;
     static constexpr int KA = 3 * (CA / 16), KB = 3 * (CH / 16);           // 12, 6 K-steps per row
     static constexpr int WA_STEP = 2 * 3 * CH * 16, WB_STEP = 2 * 3 * CB * 16;   // 3072, 6144
     static constexpr int WA_BYTES = KA * WA_STEP, WB_BYTES = KB * WB_STEP;       // 36864 each
-    static constexpr int RH = 6, RY = 5;                        // TMEM accumulator rings
+    static constexpr int RH = RB_RH, RY = RB_RY;                        // TMEM accumulator rings
     static constexpr int TM_H = 0, TM_Y = RH * CH;              // column bases: 0, 192 (+ 5*64 = 512)
     static constexpr int OFF_WA = 0, OFF_WB = WA_BYTES, OFF_X = OFF_WB + WB_BYTES, OFF_H = OFF_X + XSTAGES * XROW;
-    static constexpr int YROW = 128 * CB * 2;                   // one output row staged for the TMA store: 16 KB
-    static constexpr int YSLOTS = 3;                            // staging slots: residual row in, finished row out
-    static constexpr int OFF_Y = OFF_H + HSLOTS * HROW;
-    static constexpr int OFF_BIAS = OFF_Y + YSLOTS * YROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
+    static constexpr int OFF_BIAS = OFF_H + HSLOTS * HROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
-    static constexpr int THREADS = 672;            // 4 control warps + 8 hidden-epilogue + 8 output-epilogue warps + second I/O warp
+    static constexpr int THREADS = 640;            // 4 control warps (one spare) + 8 hidden-epilogue + 8 output-epilogue warps
     static_assert(RH * CH + RY * CB == 512, "the two accumulator rings fill TMEM");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
     static_assert(XSTAGES <= 8 && RH <= 8 && HSLOTS <= 4 && RY <= 8, "barrier array layout");
@@ -147,8 +150,6 @@ __device__ __forceinline__ void rb_issue(const RBPlan& q, uint64_t a_desc, uint6
 
 template <bool BF16>
 __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __grid_constant__ CUtensorMap tmap_x,
-                                                                      const __grid_constant__ CUtensorMap tmap_xr,
-                                                                      const __grid_constant__ CUtensorMap tmap_y,
                                                                       const ResblockParams p) {
     using G = RBGeom;
     extern __shared__ uint8_t smem_raw[];
@@ -159,7 +160,6 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     uint8_t* s_wB = smem + G::OFF_WB;
     uint8_t* s_x = smem + G::OFF_X;
     uint8_t* s_h = smem + G::OFF_H;
-    uint8_t* s_y = smem + G::OFF_Y;
     float* s_bias = reinterpret_cast<float*>(smem + G::OFF_BIAS);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
     uint64_t* xfull = bars;            // [XSTAGES]  TMA -> MMA
@@ -171,9 +171,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     uint64_t* yafull = bars + 40;      // [RY] output accumulator row complete        MMA -> output epilogue
     uint64_t* yaempty = bars + 48;     // [RY] drained and re-zeroed                  output epilogue -> MMA
     uint64_t* wbar = bars + 56;
-    uint64_t* rfull = bars + 57;       // [YSLOTS] staging slot free again and the residual row landed in it    I/O warp -> output epilogue
-    uint64_t* sfull = bars + 60;       // [YSLOTS] output row staged                                              output epilogue -> I/O warp
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 63);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 57);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (p.dbg_trace != nullptr && threadIdx.x == 0) {           // per-CTA timing: [1024 + 8 * cta + k]
@@ -205,18 +203,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     // zero the hidden ring once: halo slots at image borders are never written and must read as zero padding
     for (int i = threadIdx.x; i < G::HSLOTS * G::HROW / 16; i += G::THREADS)
         reinterpret_cast<uint4*>(s_h)[i] = make_uint4(0, 0, 0, 0);
-    for (int i = threadIdx.x; i < G::CH + G::CB; i += G::THREADS) s_bias[i] = i < G::CH ? p.biasA[i] : p.biasB[i - G::CH];
+    for (int i = threadIdx.x; i < G::CH + G::CB; i += G::THREADS) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
         for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
         for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], 1); mbar_init(&haempty[i], 4); }
         for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4); mbar_init(&hsempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
         mbar_init(wbar, 1);
-        for (int i = 0; i < G::YSLOTS; ++i) { mbar_init(&rfull[i], 1); mbar_init(&sfull[i], 8); }
         fence_mbar_init();
         tma_prefetch_desc(&tmap_x);
-        tma_prefetch_desc(&tmap_y);
-        tma_prefetch_desc(&tmap_xr);
     }
     fence_proxy_async_smem();
     if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, 512); }
@@ -233,7 +228,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             const int b0 = c < G::TM_Y ? 0 : G::CH + ((c - G::TM_Y) & 32);
             uint32_t bv[32];
 #pragma unroll
-            for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[b0 + k]);
+            for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(p.bias[b0 + k]);
             tmem_st32(tmem_base + lg + c, bv);
         }
         tmem_st_wait();
@@ -379,7 +374,6 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + G::TM_H + ((uint32_t)(lg * 32) << 16);
         const uint32_t s_h_u32 = smem_u32(s_h);
-        const float4* sb4 = reinterpret_cast<const float4*>(s_bias);
         const bool tr = p.dbg_trace != nullptr && lane == 0 && lg == 0;
         int hbase = 0, g = g_begin;
         RBSeg sg;
@@ -403,11 +397,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const float4 b = sb4[k];
-                        bv[4 * k] = __float_as_uint(b.x); bv[4 * k + 1] = __float_as_uint(b.y);
-                        bv[4 * k + 2] = __float_as_uint(b.z); bv[4 * k + 3] = __float_as_uint(b.w);
-                    }
+                    for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[k]);
                     tmem_st32(t_lane + slot * G::CH, bv);
                 }
                 if (tr) rb_trace(p, c, 11);
@@ -444,87 +434,42 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             }
             hbase += sg.hhi - sg.hlo + 1;
         }
-    } else if (warp == 3 || warp == 20) {
-        // ===================== output I/O warps: residual rows in, finished rows out — all by TMA =====================
-        // Three 16 KB staging slots rotate by row ([box][plane][pixel] granules); the two I/O warps alternate rows.  Per
-        // row: wait until the epilogue has staged it, TMA-store the slot, wait until the store has read it, then TMA-load
-        // the residual (x) row that will use the slot next (three rows ahead; an L2 hit).  A slot's round trip — store
-        // read-out ~1000 clk, residual load ~1500 clk under load, epilogue ~1000 clk — must fit in YSLOTS row periods:
-        // with two slots it set the row period (2100-2200 clk measured).  Keeping this off the epilogue warps matters
-        // too: a thread that issues a bulk store and waits for its read blocks for ~1000 clk.
-        const int my = warp == 3 ? 0 : 1;
-        pdl_wait();                          // residual rows are the previous launch's output; y may still be read by it
-        const int gpb = p.BW >> 3, nbox = 16 / gpb, box_bytes = 8 * p.BW * 16;
-        const bool io = !(p.dbg_skip & 4);
-        auto load_residual = [&](int sl, int ss, int yy) {      // one elected lane
-            if (!io || (p.dbg_skip & 128)) { mbar_arrive(&rfull[sl]); return; }
-            mbar_arrive_expect_tx(&rfull[sl], G::YROW);
-            for (int b = 0; b < nbox; ++b) {
-                const int q = ss * 16 + b * gpb;
-                const int n = q / p.GX, gx = q - n * p.GX;
-                tma_load_4d(s_y + sl * G::YROW + b * box_bytes, &tmap_xr, &rfull[sl], gx * 8 * 4, yy, 0, n);
-            }
-        };
-        // load cursor: runs YSLOTS rows ahead of the store cursor over the same row sequence.  Row lc's residual goes
-        // into the slot row lc - YSLOTS just left, so it is loaded by the warp that stored that row (the first YSLOTS
-        // rows by warp 3).
-        int gl = g_begin; RBSeg sl_seg; bool l_have = rb_next_seg(p, gl, g_end, sl_seg); int ly = l_have ? sl_seg.y0 : 0;
-        int lc = 0, lslot = 0;
-        auto load_next = [&]() {
-            if (!l_have) return;
-            const bool mine = lc < G::YSLOTS ? my == 0 : ((lc - G::YSLOTS) & 1) == my;
-            if (lane == 0 && mine) load_residual(lslot, sl_seg.ss, ly);
-            ++lc;
-            if (++lslot == G::YSLOTS) lslot = 0;
-            if (++ly >= sl_seg.y1) { l_have = rb_next_seg(p, gl, g_end, sl_seg); ly = l_have ? sl_seg.y0 : 0; }
-        };
-        for (int i = 0; i < G::YSLOTS; ++i) load_next();
-        int c = 0, g = g_begin, sl = 0; uint32_t sph = 0;
-        RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
-#pragma unroll 1
-            for (int y = sg.y0; y < sg.y1; ++y, ++c) {
-                if ((c & 1) == my) {
-                    mbar_wait(&sfull[sl], sph, 45);
-                    if (lane == 0 && io && !(p.dbg_skip & 256)) {
-                        for (int b = 0; b < nbox; ++b) {
-                            const int q = sg.ss * 16 + b * gpb;
-                            const int n = q / p.GX, gx = q - n * p.GX;
-                            if (n < p.N) tma_store_4d(&tmap_y, s_y + sl * G::YROW + b * box_bytes, gx * 8 * 4, y, 0, n);
-                        }
-                        tma_store_commit();
-                        tma_store_wait_read();
-                    }
-                    __syncwarp();
-                }
-                load_next();                     // row c + YSLOTS takes the slot
-                if (++sl == G::YSLOTS) { sl = 0; sph ^= 1; }
-            }
-        }
-        if (lane == 0) tma_store_wait_all();
-        __syncwarp();
-    } else if (warp >= 12 && warp < 20) {
-        // ===================== output epilogue: 8 warps per row (two channel halves); + bias + x (residual) -> y =====================
-        // The residual row is already in the row's staging slot (I/O warp); every thread adds accumulator + bias to its
-        // own pixel in place and the slot is handed back to the I/O warp for the TMA store.  (Per-thread global loads /
-        // stores cost an epilogue thread ~70 clk each here; measured.)
+    } else if (warp >= 12) {
+        // ===================== output epilogue: 8 warps per row (two channel halves); + x (residual) -> y =====================
+        // Residual in and result out go straight between global memory and registers: a warp's 32 lanes are 32
+        // consecutive pixels, so each of a thread's four 16-byte plane granules is part of a 512-byte contiguous run.
+        // (Staging the row in shared memory for TMA costs 64 KB of shared-memory traffic per row — residual in, read,
+        // result written, store read-out — and this kernel is bound by the 128 B/clk shared-memory port: the MMAs alone
+        // read 147 KB of operands per row.)  The residual of the next row is requested before this row's math.
         const int lg = warp & 3;
         const int half = (warp - 12) >> 2;         // channels 32*half .. : planes 4*half .. 4*half+3
         const int L = lg * 32 + lane;
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + G::TM_Y + half * 32 + ((uint32_t)(lg * 32) << 16);
-        const float4* sb4 = reinterpret_cast<const float4*>(s_bias + G::CH + half * 32);
         const bool tr = p.dbg_trace != nullptr && threadIdx.x == 384;
-        const int gpb = p.BW >> 3;                                  // groups per box
-        const int box_bytes = 8 * p.BW * 16, plane_bytes = p.BW * 16;
-        uint8_t* const s_px0 = s_y + (grp / gpb) * box_bytes + ((grp % gpb) * 8 + i) * 16 + 4 * half * plane_bytes;
+        const bool no_ld = (p.dbg_skip & (4 | 128)) != 0, no_st = (p.dbg_skip & (4 | 256)) != 0;
+        const size_t plane = HW;                   // granules per plane
+        pdl_wait();                                // x is the previous launch's output; y may still be read by it
         int c = 0, g = g_begin;                    // c: running output-row counter
         int slot = 0; uint32_t yph = 0;            // accumulator ring slot / phase
-        int sl = 0; uint32_t sph = 0;              // staging slot / phase
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
+            const int q = sg.ss * 16 + grp;
+            const int n = q / p.GX, gx = q - n * p.GX;
+            const bool valid = n < p.N && gx * 8 + i < p.W;
+            // granule index of (n, plane 4*half, row 0, this pixel)
+            const size_t px0 = valid ? ((size_t)n * 8 + 4 * half) * plane + (size_t)(gx * 8 + i) : 0;
+            const uint4* xg = reinterpret_cast<const uint4*>(p.x) + px0;
+            uint4* yg = reinterpret_cast<uint4*>(p.y) + px0;
+            uint4 nxt[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                nxt[j] = valid && !no_ld ? __ldg(xg + j * plane + (size_t)sg.y0 * p.W) : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
+                uint4 rq[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) rq[j] = nxt[j];
                 if (tr) rb_trace(p, c, 5);      // output epilogue starts waiting
                 mbar_wait<RB_SLEEP>(&yafull[slot], yph, 43);
                 if (tr) rb_trace(p, c, 6);      // output accumulator complete
@@ -535,21 +480,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const float4 b = sb4[k];
-                        bv[4 * k] = __float_as_uint(b.x); bv[4 * k + 1] = __float_as_uint(b.y);
-                        bv[4 * k + 2] = __float_as_uint(b.z); bv[4 * k + 3] = __float_as_uint(b.w);
-                    }
+                    for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[G::CH + half * 32 + k]);
                     tmem_st32(t_lane + slot * G::CB, bv);
                 }
                 if (tr) rb_trace(p, c, 10);
-                mbar_wait<RB_SLEEP>(&rfull[sl], sph, 44);
-                if (tr) rb_trace(p, c, 8);
-                // plain shared loads / stores: the four planes' loads are issued together, the stores after the math
-                uint8_t* const s_px = s_px0 + sl * G::YROW;
-                uint4 rq[4];
+                if (y + 1 < sg.y1 && valid && !no_ld) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) rq[j] = *reinterpret_cast<const uint4*>(s_px + j * plane_bytes);
+                    for (int j = 0; j < 4; ++j) nxt[j] = __ldg(xg + j * plane + (size_t)(y + 1) * p.W);
+                }
+                if (tr) rb_trace(p, c, 8);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
@@ -559,18 +498,16 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                         const float2 f = unpack2<BF16>(qq[k]);
                         ov[k] = pack2<BF16>(__uint_as_float(rr[8 * j + 2 * k]) + f.x, __uint_as_float(rr[8 * j + 2 * k + 1]) + f.y);
                     }
-                    *reinterpret_cast<uint4*>(s_px + j * plane_bytes) = make_uint4(ov[0], ov[1], ov[2], ov[3]);
+                    if (valid && !no_st) yg[j * plane + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
                 }
                 if (tr) rb_trace(p, c, 15);
                 tmem_st_wait();
                 tc_fence_before();
                 if (tr) rb_trace(p, c, 9);
-                fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) { mbar_arrive(&yaempty[slot]); mbar_arrive(&sfull[sl]); }
-                if (tr) rb_trace(p, c, 7);      // output row handed to the I/O warp
+                if (lane == 0) mbar_arrive(&yaempty[slot]);
+                if (tr) rb_trace(p, c, 7);      // output row done
                 if (++slot == G::RY) { slot = 0; yph ^= 1; }
-                if (++sl == G::YSLOTS) { sl = 0; sph ^= 1; }
             }
         }
     }
