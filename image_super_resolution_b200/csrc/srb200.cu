@@ -18,6 +18,7 @@
 #include "srb_wgrad.cuh"
 #include "srb_bwd.cuh"
 #include "srb_resblock.cuh"
+#include "srb_rowconv.cuh"
 
 using namespace srb;
 
@@ -80,9 +81,11 @@ struct srb_weights {
 };
 
 struct srb_resblock;
+struct srb_rowconv;
 struct srb_net {
     srb_weights* conv[19];
     srb_resblock* rb[8];     // fused ResidualBlock1 operands (used when the shape qualifies)
+    srb_rowconv* rc1 = nullptr;   // conv1 (+ long skip) on the row-fold kernel
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -556,6 +559,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
     }
     for (int i = 0; i < 8 && rc == SRB_OK; ++i)
         rc = srb_resblock_create(ctx, w[1 + 2 * i], b[1 + 2 * i], w[2 + 2 * i], b[2 + 2 * i], dtype, &net->rb[i]);
+    if (rc == SRB_OK) rc = srb_rowconv_create(ctx, w[17], b[17], dtype, &net->rc1);
     if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
     *out = net;
     return SRB_OK;
@@ -565,6 +569,7 @@ extern "C" void srb_model_pt_destroy(srb_net* net) {
     if (!net) return;
     for (int i = 0; i < 19; ++i) srb_free_weights(net->conv[i]);
     for (int i = 0; i < 8; ++i) srb_resblock_destroy(net->rb[i]);
+    srb_rowconv_destroy(net->rc1);
     delete net;
 }
 
@@ -673,7 +678,9 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
         cur = nxt;
     }
     // cur == rb after 8 blocks; long skip adds conv0's (post-activation) output
-    if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
+    if (fused && !(ctx->dbg_skip & 8192)) {
+        if ((rc = srb_rowconv_fwd(ctx, net->rc1, cur, x0, ra, 0.f, 0, N, H, W, stream))) return rc;
+    } else if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
     if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
@@ -1175,5 +1182,99 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
         if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, p));
         else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, p));
     }
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// row-fold 3x3 conv 64 -> 64 (conv1 of the model.pt graph)
+// ------------------------------------------------------------------------------------------
+struct srb_rowconv {
+    int dtype = 0;
+    uint8_t* d_w = nullptr;
+    float h_bias[64] = {};
+    mutable RBMaps maps[2];
+    mutable int next_map = 0;
+    mutable bool attr_set = false;
+};
+
+extern "C" void srb_rowconv_destroy(srb_rowconv* rc) {
+    if (!rc) return;
+    if (rc->d_w) cudaFree(rc->d_w);
+    delete rc;
+}
+
+extern "C" int srb_rowconv_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_rowconv** out) {
+    if (!ctx || !w || !bias || !out) return fail(SRB_EINVAL, "srb_rowconv_create: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_rowconv_create: dtype %d", dtype);
+    using G = RCGeom;
+    std::vector<uint16_t> pk;
+    pack_fold(w, G::C, G::C, dtype, pk);
+    if (pk.size() * 2 != (size_t)G::W_BYTES) return fail(SRB_EINVAL, "srb_rowconv_create: pack size");
+    srb_rowconv* rc = new srb_rowconv();
+    rc->dtype = dtype;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&rc->d_w, G::W_BYTES) != cudaSuccess) {
+        srb_rowconv_destroy(rc);
+        return fail(SRB_ENOMEM, "srb_rowconv_create: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemcpy(rc->d_w, pk.data(), G::W_BYTES, cudaMemcpyHostToDevice));
+    memcpy(rc->h_bias, bias, G::C * 4);
+    *out = rc;
+    return SRB_OK;
+}
+
+extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* x, const void* res, void* y, float slope, int flags,
+                               int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !rc || !x || !y) return fail(SRB_EINVAL, "srb_rowconv_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_rowconv_fwd: empty shape");
+    if (x == y) return fail(SRB_EINVAL, "srb_rowconv_fwd: in-place is not supported (neighbouring CTAs re-read halo rows of x)");
+    if (((uintptr_t)x & 15) || ((uintptr_t)y & 15) || ((uintptr_t)res & 15)) return fail(SRB_EINVAL, "srb_rowconv_fwd: buffers must be 16-byte aligned");
+    if (flags & ~SRB_F_LRELU) return fail(SRB_ENOSUP, "srb_rowconv_fwd: flags 0x%x (only SRB_F_LRELU)", flags);
+    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_rowconv_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
+    using G = RCGeom;
+    RowconvParams p{};
+    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    RBMaps* m = nullptr;
+    for (RBMaps& c : rc->maps)
+        if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
+    if (!m) {
+        m = &rc->maps[rc->next_map];
+        rc->next_map ^= 1;
+        m->x = nullptr;
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        cuuint32_t box[4] = {40, 1, 8, 1};
+        CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+        m->x = x; m->N = N; m->H = H; m->W = W;
+    }
+    const long long groups = (long long)N * p.GX;
+    const long long sets = (groups + 15) / 16;
+    if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_rowconv_fwd: too many rows");
+    p.total_rows = (int)(sets * H);
+    p.w = rc->d_w;
+    memcpy(p.bias, rc->h_bias, sizeof(p.bias));
+    p.res = res; p.y = y; p.slope = slope; p.lrelu = (flags & SRB_F_LRELU) ? 1 : 0; p.dbg_skip = ctx->dbg_skip;
+    int grid = p.total_rows / 8;
+    if (grid < 1) grid = 1;
+    if (grid > ctx->num_sms) grid = ctx->num_sms;
+    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (!rc->attr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(rowconv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(rowconv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        rc->attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (rc->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<true>, m->tm, p));
+    else CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<false>, m->tm, p));
     return SRB_OK;
 }

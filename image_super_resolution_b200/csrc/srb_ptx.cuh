@@ -47,6 +47,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// try_wait that lets the hardware park the thread for up to `ns` nanoseconds (woken when the phase completes) instead
+// of returning at once: a parked warp issues nothing, a polling one burns issue slots, shared-memory reads and power
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+    return ok != 0;
+}
 // tag identifies the wait site.  On a protocol bug the kernel does not hang or trap: the first wait to
 // exceed its budget records where it was, raises g_srb_abort, and every wait returns at once so the
 // launch drains (with garbage results); the host reads the flag (srb_check_device) and reports it.
@@ -61,8 +74,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
         // every hand-off in the pipeline pays that latency
 #pragma unroll 1
         for (int i = 0; i < 64; ++i) {
-            if (mbar_try_wait(bar, parity)) return;
-            if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
+            if constexpr (SLEEP_NS < 0) {            // parked by the hardware for up to -SLEEP_NS ns per try
+                if (mbar_try_wait_hint(bar, parity, (uint32_t)(-SLEEP_NS))) return;
+            } else {
+                if (mbar_try_wait(bar, parity)) return;
+                if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
+            }
         }
         if (g_srb_abort) return;
         if (clock64() - t0 > (1ll << 28)) {  // ~0.14 s at 2 GHz

@@ -44,7 +44,14 @@ struct ResblockParams {
 #define RB_HSLOTS 3
 #define RB_XSTAGES 4
 #endif
-constexpr int RB_SLEEP = 40;   // ns between polls of the epilogue warps' waits
+#ifndef RB_SLEEP_NS
+#define RB_SLEEP_NS 40
+#endif
+#ifndef RB_CTRL_NS
+#define RB_CTRL_NS 0
+#endif
+constexpr int RB_SLEEP = RB_SLEEP_NS;   // epilogue warps' waits: > 0 ns between polls, < 0 parked by the hardware up to that long
+constexpr int RB_CTRL = RB_CTRL_NS;     // producer / issuer warps' waits
 
 struct RBGeom {
     static constexpr int CA = 64, CH = 32, CB = 64;            // channels: in, hidden, out
@@ -80,6 +87,13 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
           "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
         : "memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -112,7 +126,8 @@ __device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k
 
 // a segment: output rows [y0, y1) of strip-set ss, with the hidden / input row ranges it needs (clipped to the image)
 struct RBSeg { int ss, y0, y1, hlo, hhi, xlo, xhi; };
-__device__ __forceinline__ bool rb_next_seg(const ResblockParams& p, int& g, int g1, RBSeg& s) {
+template <class Params>
+__device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBSeg& s) {
     if (g >= g1) return false;
     s.ss = g / p.H;
     s.y0 = g - s.ss * p.H;
@@ -262,7 +277,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
-                mbar_wait(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
+                mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
                 if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
@@ -287,11 +302,11 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         while (rb_next_seg(p, g, g_end, sg)) {
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
-                mbar_wait(&xfull[xst], xph, 33);
+                mbar_wait<RB_CTRL>(&xfull[xst], xph, 33);
                 const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
                 const int a_lo = hbase + lo - sg.hlo, a_n = hi - lo + 1, a_s0 = lo - (r - 1);
                 for (; h_acq < a_lo + a_n; ++h_acq) {
-                    mbar_wait(&haempty[acq_slot], acq_ph, 34);
+                    mbar_wait<RB_CTRL>(&haempty[acq_slot], acq_ph, 34);
                     if (++acq_slot == G::RH) { acq_slot = 0; acq_ph ^= 1; }
                 }
                 const int slot_lo = (hslot0 + (lo - sg.hlo)) % G::RH;
@@ -333,11 +348,11 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         while (rb_next_seg(p, g, g_end, sg)) {
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
-                mbar_wait(&hsfull[hs], hph, 35);
+                mbar_wait<RB_CTRL>(&hsfull[hs], hph, 35);
                 const int lo = h - 1 > sg.y0 ? h - 1 : sg.y0, hi = h + 1 < sg.y1 - 1 ? h + 1 : sg.y1 - 1;
                 const int b_lo = ybase + lo - sg.y0, b_n = hi - lo + 1, b_s0 = lo - (h - 1);
                 for (; y_acq < b_lo + b_n; ++y_acq) {
-                    mbar_wait(&yaempty[acq_slot], acq_ph, 36);
+                    mbar_wait<RB_CTRL>(&yaempty[acq_slot], acq_ph, 36);
                     if (++acq_slot == G::RY) { acq_slot = 0; acq_ph ^= 1; }
                 }
                 const int slot_lo = (yslot0 + (lo - sg.y0)) % G::RY;

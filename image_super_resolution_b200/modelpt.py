@@ -154,6 +154,57 @@ class ModelPT:
 
     __call__ = forward
 
+    @torch.no_grad()
+    def stream(self, batches, depth: int = 2):
+        """Pipelined host-to-host inference over a sequence of uint8 host batches — the shape of rs.py's video loop
+        (rs.py:58-76: frames from the reader -> model -> writer).  Yields one pinned uint8 host tensor per input batch, in
+        order.  H2D of batch i+1 and D2H of batch i-1 run on copy streams while the kernels of batch i run on the compute
+        stream; `depth` batches are in flight.  A yielded tensor is valid until `depth` more batches have been consumed
+        (its buffer is then reused): write it out or copy it before asking for more, as a frame writer does."""
+        if self._net is None:
+            raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
+        depth = max(1, int(depth))
+        dev = self._device
+        s_in, s_c, s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        nbuf = depth + 1
+        slots = [None] * nbuf          # per slot: (x_dev, y_dev, y_host, ev_in, ev_c, ev_out, shape)
+        pending = []                   # slot indices submitted and not yet yielded
+        i = 0
+        for xb in batches:
+            if xb.dtype != torch.uint8 or xb.dim() != 4 or xb.shape[1] != 3 or xb.is_cuda:
+                raise RuntimeError("stream() takes uint8 host tensors [N,3,H,W]")
+            xb = xb.contiguous()
+            k = i % nbuf
+            if len(pending) == nbuf:                       # the slot about to be reused must have been consumed
+                raise RuntimeError("internal: ring overrun")
+            sl = slots[k]
+            if sl is None or sl[6] != tuple(xb.shape):
+                sl = (torch.empty(xb.shape, dtype=torch.uint8, device=dev), torch.empty(xb.shape, dtype=torch.uint8, device=dev),
+                      torch.empty(xb.shape, dtype=torch.uint8).pin_memory(), torch.cuda.Event(), torch.cuda.Event(),
+                      torch.cuda.Event(), tuple(xb.shape))
+                slots[k] = sl
+            x_dev, y_dev, y_host, ev_in, ev_c, ev_out, _ = sl
+            with torch.cuda.stream(s_in):
+                x_dev.copy_(xb, non_blocking=True)
+                ev_in.record(s_in)
+            with torch.cuda.stream(s_c):
+                s_c.wait_event(ev_in)
+                self.forward(x_dev, out=y_dev)
+                ev_c.record(s_c)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_c)
+                y_host.copy_(y_dev, non_blocking=True)
+                ev_out.record(s_out)
+            pending.append(k)
+            i += 1
+            if len(pending) > depth:
+                j = pending.pop(0)
+                slots[j][5].synchronize()
+                yield slots[j][2]
+        for j in pending:
+            slots[j][5].synchronize()
+            yield slots[j][2]
+
     @staticmethod
     def launches_per_forward(H: int = 64, W: int = 64) -> int:
         return int(lib().srb_model_pt_launches(H, W))

@@ -323,6 +323,41 @@ class PackBatch:
             pass
 
 
+class RowConv:
+    """Row-fold 3x3 conv 64 -> 64 (+ bias, optional LeakyReLU, optional residual) in one launch (srb_rowconv_*):
+    `Conv(64,64,3,act=False)` + long skip of the model.pt graph (utils/models.py:690, :704)."""
+
+    def __init__(self, ctx: Context, w, b, dtype=SRB_DT_F16):
+        arrs = [np.ascontiguousarray(t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t, dtype=np.float32)
+                for t in (w, b)]
+        if arrs[0].shape != (64, 64, 3, 3) or arrs[1].shape != (64,):
+            raise ValueError("RowConv: weight must be [64][64][3][3], bias [64]")
+        self.ctx, self.dtype = ctx, dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_rowconv_create(ctx.handle, *[_lib.f32_ptr(a) for a in arrs], self.dtype, C.byref(h)), "srb_rowconv_create")
+        self.handle = h
+
+    def forward(self, x: torch.Tensor, y: torch.Tensor, res: torch.Tensor | None = None, slope: float = 0.0, lrelu: bool = False):
+        _require_cuda(x, "x"); _require_cuda(y, "y")
+        N, planes, H, W, _ = x.shape
+        if planes != 8 or y.shape != x.shape or (res is not None and res.shape != x.shape):
+            raise RuntimeError("RowConv: x, y (and res) must be [N][8][H][W][8]")
+        if res is not None:
+            _require_cuda(res, "res")
+        check(lib().srb_rowconv_fwd(self.ctx.handle, self.handle, x.data_ptr(), res.data_ptr() if res is not None else None,
+                                    y.data_ptr(), float(slope), F_LRELU if lrelu else 0, N, H, W, _stream_ptr(x.device)),
+              "srb_rowconv_fwd")
+        return y
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_rowconv_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
 class ResBlock:
     """Fused ResidualBlock1 (utils/models.py:208-209): y = x + convB(LeakyReLU(convA(x))) in one kernel (srb_resblock_*)."""
 

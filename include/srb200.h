@@ -134,7 +134,7 @@ int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uin
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);
 /* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12 with the fused residual
- * block kernel, 20 when the width does not qualify for it: srb_resblock_supported) */
+ * block / row-fold kernels, 20 when the width does not qualify for it: srb_resblock_supported) */
 int srb_model_pt_launches(int H, int W);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
@@ -158,6 +158,16 @@ void srb_resblock_destroy(srb_resblock* rb);
 int srb_resblock_supported(int H, int W);
 int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void* x, void* y, float lrelu_slope, int N, int H, int W,
                      srb_stream_t stream);
+
+/* Row-fold 3x3 conv 64 -> 64: y = act(conv(x) + b) + res — `Conv(64,64,3,act=False)` utils/models.py:690 with the long
+ * skip `inputs + self.conv1(residual)` :704 (model.pt: net.1.conv1), the same GEMM mapping as the fused residual block
+ * (dy taps folded into N = 192, accumulation over adjacent TMEM rows).  w [64][64][3][3] fp32 host (BN folded),
+ * res: 8-plane C8 buffer or NULL, lrelu_slope applied when flags has SRB_F_LRELU.  Shapes as srb_resblock_supported. */
+typedef struct srb_rowconv srb_rowconv;
+int srb_rowconv_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_rowconv** out);
+void srb_rowconv_destroy(srb_rowconv* rc);
+int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* x, const void* res, void* y, float lrelu_slope, int flags,
+                    int N, int H, int W, srb_stream_t stream);
 
 /* Weight gradient of a 3x3 conv (autograd of aten::_convolution, train.py:57):
  * dw[co][ci][dy][dx] += scale * sum_p dY[p][co] * X[p+(dy-1,dx-1)][ci].  x, dy: C8-plane slices (device);

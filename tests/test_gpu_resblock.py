@@ -64,3 +64,49 @@ def test_resblock_many_rows_per_cta_and_segment_splits(dev):
 def test_resblock_rejects_unsupported_widths(dev):
     from image_super_resolution_b200 import ops
     assert ops.ResBlock.supported(64, 64) and ops.ResBlock.supported(7, 128) and not ops.ResBlock.supported(64, 96)
+
+
+# ---- row-fold single conv (srb_rowconv.cuh): conv1 + long skip of the model.pt graph ----
+def _rowconv_case(dev, N, H, W, seed=0, grid=0, res=True, lrelu=False):
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200._lib import Context
+    ctx = Context.get(0)
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(64, 64, 3, 3, generator=g) / 24
+    b = torch.randn(64, generator=g) * 0.1
+    x = torch.randn(N, 64, H, W, generator=g)
+    r = torch.randn(N, 64, H, W, generator=g)
+    q = lambda t: t.half().float()  # noqa: E731
+    ref = F.conv2d(q(x), q(w), b, padding=1)
+    if lrelu:
+        ref = F.leaky_relu(ref, 0.2)
+    if res:
+        ref = ref + q(r)
+    rc = ops.RowConv(ctx, w, b, "fp16")
+    xc = ops.nchw_to_c8(x.to(dev), dtype="fp16")
+    rcc = ops.nchw_to_c8(r.to(dev), dtype="fp16") if res else None
+    yc = torch.full_like(xc, float("nan"))
+    if grid:
+        ctx.debug_set(1, grid)
+    try:
+        rc.forward(xc, yc, rcc, slope=0.2, lrelu=lrelu)
+        torch.cuda.synchronize()
+        ctx.check_device()
+    finally:
+        ctx.debug_set(1, 0)
+    out = ops.c8_to_nchw(yc, 64).cpu()
+    err = (out - ref).abs().max().item()
+    assert np.isfinite(err) and err <= 4e-3 * ref.abs().max().item() + 2e-3, err
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 12, 64), (3, 20, 64), (1, 5, 8), (5, 9, 16), (2, 33, 128), (3, 17, 60), (2, 1, 64), (7, 2, 28)])
+def test_rowconv_matches_fp32_reference(dev, N, H, W):
+    _rowconv_case(dev, N, H, W, seed=N * 100 + H)
+
+
+def test_rowconv_variants_and_segment_splits(dev):
+    _rowconv_case(dev, 6, 64, 64, seed=1, grid=2)
+    _rowconv_case(dev, 6, 64, 64, seed=2, grid=0)
+    _rowconv_case(dev, 3, 19, 32, seed=3, res=False)
+    _rowconv_case(dev, 3, 19, 32, seed=4, res=True, lrelu=True)
+    _rowconv_case(dev, 9, 40, 64, seed=5, grid=37)

@@ -51,3 +51,17 @@ def test_sharded_model_and_frame_path(model):
     assert n == 6 and sink.bytes == 6 * 40 * 48 * 3
     want = model(batches[1].cuda())[1].flip(0).permute(1, 2, 0).cpu().numpy()   # frame 3: BGR, HWC
     assert np.array_equal(sink.kept[3], want)
+
+
+def test_stream_pipelined_host_batches_match_forward(model):
+    """ModelPT.stream (copy / compute overlap, ring of device buffers) returns, in order, what forward() returns."""
+    g = torch.Generator().manual_seed(7)
+    batches = [torch.randint(0, 256, (3, 3, 40, 64), dtype=torch.uint8, generator=g) for _ in range(7)]
+    batches.insert(3, torch.randint(0, 256, (2, 3, 24, 32), dtype=torch.uint8, generator=g))   # a shape change mid-stream
+    want = [model(b.cuda()).cpu() for b in batches]
+    got = [y.clone() for y in model.stream(iter(batches), depth=2)]
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+    with pytest.raises(RuntimeError):
+        list(model.stream([torch.zeros(1, 3, 8, 8)]))
