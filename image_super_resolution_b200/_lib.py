@@ -67,6 +67,9 @@ SIGNATURES = {
     "srb_rowconv_create": (_i, [_vp, _vp, _vp, _i, C.POINTER(_vp)]),
     "srb_rowconv_destroy": (None, [_vp]),
     "srb_rowconv_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
+    "srb_tail9_create": (_i, [_vp, _vp, _vp, _i, C.POINTER(_vp)]),
+    "srb_tail9_destroy": (None, [_vp]),
+    "srb_tail9_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),

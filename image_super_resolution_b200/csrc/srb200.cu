@@ -19,6 +19,7 @@
 #include "srb_bwd.cuh"
 #include "srb_resblock.cuh"
 #include "srb_rowconv.cuh"
+#include "srb_tail.cuh"
 
 using namespace srb;
 
@@ -82,10 +83,12 @@ struct srb_weights {
 
 struct srb_resblock;
 struct srb_rowconv;
+struct srb_tail9;
 struct srb_net {
     srb_weights* conv[19];
     srb_resblock* rb[8];     // fused ResidualBlock1 operands (used when the shape qualifies)
     srb_rowconv* rc1 = nullptr;   // conv1 (+ long skip) on the row-fold kernel
+    srb_tail9* tail = nullptr;    // conv2 + tanh -> uint8 on the row-fold kernel
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -560,6 +563,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
     for (int i = 0; i < 8 && rc == SRB_OK; ++i)
         rc = srb_resblock_create(ctx, w[1 + 2 * i], b[1 + 2 * i], w[2 + 2 * i], b[2 + 2 * i], dtype, &net->rb[i]);
     if (rc == SRB_OK) rc = srb_rowconv_create(ctx, w[17], b[17], dtype, &net->rc1);
+    if (rc == SRB_OK) rc = srb_tail9_create(ctx, w[18], b[18], dtype, &net->tail);
     if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
     *out = net;
     return SRB_OK;
@@ -570,6 +574,7 @@ extern "C" void srb_model_pt_destroy(srb_net* net) {
     for (int i = 0; i < 19; ++i) srb_free_weights(net->conv[i]);
     for (int i = 0; i < 8; ++i) srb_resblock_destroy(net->rb[i]);
     srb_rowconv_destroy(net->rc1);
+    srb_tail9_destroy(net->tail);
     delete net;
 }
 
@@ -682,7 +687,9 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
         if ((rc = srb_rowconv_fwd(ctx, net->rc1, cur, x0, ra, 0.f, 0, N, H, W, stream))) return rc;
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
-    if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+    if (fused && !(ctx->dbg_skip & 16384)) {
+        if ((rc = srb_tail9_fwd(ctx, net->tail, ra, out, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+    } else if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
     return SRB_OK;
 }
@@ -1276,5 +1283,103 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (rc->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<true>, m->tm, p));
     else CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<false>, m->tm, p));
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// row-fold 9x9 conv 64 -> 3 + tanh -> uint8 (conv2 + TanhToArrayImage of the model.pt graph)
+// ------------------------------------------------------------------------------------------
+struct srb_tail9 {
+    int dtype = 0;
+    uint8_t* d_w = nullptr;
+    float h_bias[3] = {};
+    mutable RBMaps maps[2];
+    mutable int next_map = 0;
+    mutable bool attr_set = false;
+};
+
+extern "C" void srb_tail9_destroy(srb_tail9* t) {
+    if (!t) return;
+    if (t->d_w) cudaFree(t->d_w);
+    delete t;
+}
+
+extern "C" int srb_tail9_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_tail9** out) {
+    if (!ctx || !w || !bias || !out) return fail(SRB_EINVAL, "srb_tail9_create: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_tail9_create: dtype %d", dtype);
+    using G = TLGeom;
+    // K-step kk = 16 input channels; [2 granules][288 rows: slice s = 8 - dy, then dx * 3 + co (27 of 32)][8 k]
+    std::vector<uint16_t> pk((size_t)G::W_BYTES / 2, 0);
+    for (int kk = 0; kk < G::KS; ++kk) for (int g = 0; g < 2; ++g) for (int s = 0; s < 9; ++s) for (int dx = 0; dx < 9; ++dx)
+        for (int co = 0; co < 3; ++co) for (int j = 0; j < 8; ++j) {
+            const int c = (2 * kk + g) * 8 + j, dy = 8 - s;
+            pk[(((size_t)kk * 2 + g) * G::BROWS + s * G::NS + dx * 3 + co) * 8 + j] = f2h(w[(((size_t)co * 64 + c) * 9 + dy) * 9 + dx], dtype);
+        }
+    srb_tail9* t = new srb_tail9();
+    t->dtype = dtype;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&t->d_w, G::W_BYTES) != cudaSuccess) {
+        srb_tail9_destroy(t);
+        return fail(SRB_ENOMEM, "srb_tail9_create: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemcpy(t->d_w, pk.data(), G::W_BYTES, cudaMemcpyHostToDevice));
+    memcpy(t->h_bias, bias, 3 * 4);
+    *out = t;
+    return SRB_OK;
+}
+
+extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, void* y, int flags, int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !t || !x || !y) return fail(SRB_EINVAL, "srb_tail9_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_tail9_fwd: empty shape");
+    if ((uintptr_t)x & 15) return fail(SRB_EINVAL, "srb_tail9_fwd: x must be 16-byte aligned");
+    const int fmt = flags & (SRB_F_U8OUT | SRB_F_F32OUT);
+    if ((flags & ~(SRB_F_TANH | SRB_F_U8OUT | SRB_F_F32OUT)) || (fmt != SRB_F_U8OUT && fmt != SRB_F_F32OUT))
+        return fail(SRB_ENOSUP, "srb_tail9_fwd: flags 0x%x (SRB_F_TANH and exactly one of SRB_F_U8OUT / SRB_F_F32OUT)", flags);
+    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_tail9_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
+    using G = TLGeom;
+    TailParams p{};
+    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    RBMaps* m = nullptr;
+    for (RBMaps& c : t->maps)
+        if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
+    if (!m) {
+        m = &t->maps[t->next_map];
+        t->next_map ^= 1;
+        m->x = nullptr;
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        cuuint32_t box[4] = {32, 1, 8, 1};                              // one group of 8 px, no halo
+        CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+        m->x = x; m->N = N; m->H = H; m->W = W;
+    }
+    const long long groups = (long long)N * p.GX;
+    const long long sets = (groups + 15) / 16;
+    if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_tail9_fwd: too many rows");
+    p.total_rows = (int)(sets * H);
+    p.w = t->d_w;
+    memcpy(p.bias, t->h_bias, sizeof(p.bias));
+    p.y = y; p.flags = flags; p.dbg_skip = ctx->dbg_skip;
+    int grid = p.total_rows / 8;
+    if (grid < 1) grid = 1;
+    if (grid > ctx->num_sms) grid = ctx->num_sms;
+    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (!t->attr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(tail9_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(tail9_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        t->attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (t->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<true>, m->tm, p));
+    else CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<false>, m->tm, p));
     return SRB_OK;
 }

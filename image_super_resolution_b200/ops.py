@@ -358,6 +358,40 @@ class RowConv:
             pass
 
 
+class Tail9:
+    """Row-fold 9x9 conv 64 -> 3 + bias (+ tanh) -> NCHW uint8 / fp32 in one launch (srb_tail9_*): conv2 + TanhToArrayImage
+    of the model.pt graph (utils/models.py:691, :448-451)."""
+
+    def __init__(self, ctx: Context, w, b, dtype=SRB_DT_F16):
+        arrs = [np.ascontiguousarray(t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t, dtype=np.float32)
+                for t in (w, b)]
+        if arrs[0].shape != (3, 64, 9, 9) or arrs[1].shape != (3,):
+            raise ValueError("Tail9: weight must be [3][64][9][9], bias [3]")
+        self.ctx, self.dtype = ctx, dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_tail9_create(ctx.handle, *[_lib.f32_ptr(a) for a in arrs], self.dtype, C.byref(h)), "srb_tail9_create")
+        self.handle = h
+
+    def forward(self, x: torch.Tensor, tanh: bool = True, u8: bool = True) -> torch.Tensor:
+        _require_cuda(x, "x")
+        N, planes, H, W, _ = x.shape
+        if planes != 8:
+            raise RuntimeError("Tail9: x must be [N][8][H][W][8]")
+        y = torch.empty(N, 3, H, W, dtype=torch.uint8 if u8 else torch.float32, device=x.device)
+        flags = (F_TANH if tanh else 0) | (F_U8OUT if u8 else F_F32OUT)
+        check(lib().srb_tail9_fwd(self.ctx.handle, self.handle, x.data_ptr(), y.data_ptr(), flags, N, H, W, _stream_ptr(x.device)),
+              "srb_tail9_fwd")
+        return y
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_tail9_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
 class ResBlock:
     """Fused ResidualBlock1 (utils/models.py:208-209): y = x + convB(LeakyReLU(convA(x))) in one kernel (srb_resblock_*)."""
 

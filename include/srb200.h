@@ -169,6 +169,15 @@ void srb_rowconv_destroy(srb_rowconv* rc);
 int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* x, const void* res, void* y, float lrelu_slope, int flags,
                     int N, int H, int W, srb_stream_t stream);
 
+/* Row-fold 9x9 conv 64 -> 3 + bias (+ tanh) -> NCHW uint8 / fp32: `ConvWithoutBN(64,3,9,act=Tanh)` utils/models.py:691 and
+ * `TanhToArrayImage.forward` :448-451 (model.pt: net.1.conv2, net.2) — both tap directions folded into N, accumulation over
+ * 9 adjacent TMEM rows.  w [3][64][9][9] fp32 host; x: 8-plane C8 buffer; y: NCHW uint8 (SRB_F_U8OUT) or fp32 (SRB_F_F32OUT);
+ * flags: SRB_F_TANH | one of the output formats.  Shapes as srb_resblock_supported. */
+typedef struct srb_tail9 srb_tail9;
+int srb_tail9_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_tail9** out);
+void srb_tail9_destroy(srb_tail9* t);
+int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, void* y, int flags, int N, int H, int W, srb_stream_t stream);
+
 /* Weight gradient of a 3x3 conv (autograd of aten::_convolution, train.py:57):
  * dw[co][ci][dy][dx] += scale * sum_p dY[p][co] * X[p+(dy-1,dx-1)][ci].  x, dy: C8-plane slices (device);
  * dw: fp32 OIHW [cout][cin][3][3] on the device, ACCUMULATED into (zero it first).  fp32 atomics: summation order

@@ -110,3 +110,43 @@ def test_rowconv_variants_and_segment_splits(dev):
     _rowconv_case(dev, 3, 19, 32, seed=3, res=False)
     _rowconv_case(dev, 3, 19, 32, seed=4, res=True, lrelu=True)
     _rowconv_case(dev, 9, 40, 64, seed=5, grid=37)
+
+
+# ---- row-fold 9x9 tail conv (srb_tail.cuh): conv2 + tanh -> uint8 of the model.pt graph ----
+def _tail_case(dev, N, H, W, seed=0, grid=0):
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200._lib import Context
+    ctx = Context.get(0)
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(3, 64, 9, 9, generator=g) / 72
+    b = torch.randn(3, generator=g) * 0.1
+    x = torch.randn(N, 64, H, W, generator=g)
+    q = lambda t: t.half().float()  # noqa: E731
+    pre = F.conv2d(q(x), q(w), b, padding=4)
+    t = ops.Tail9(ctx, w, b, "fp16")
+    xc = ops.nchw_to_c8(x.to(dev), dtype="fp16")
+    if grid:
+        ctx.debug_set(1, grid)
+    try:
+        yf = t.forward(xc, tanh=False, u8=False)
+        yu = t.forward(xc, tanh=True, u8=True)
+        torch.cuda.synchronize()
+        ctx.check_device()
+    finally:
+        ctx.debug_set(1, 0)
+    err = (yf.cpu() - pre).abs().max().item()
+    assert np.isfinite(err) and err <= 2e-3 * pre.abs().max().item() + 1e-3, err
+    want = torch.round((torch.tanh(pre) + 1) / 2 * 255).to(torch.int16)
+    d = (yu.cpu().to(torch.int16) - want).abs()
+    assert d.max().item() <= 1 and (d == 0).float().mean().item() > 0.98, (d.max().item(), (d == 0).float().mean().item())
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 12, 64), (3, 20, 64), (1, 5, 8), (5, 9, 16), (2, 33, 128), (3, 17, 60), (2, 1, 64), (7, 2, 28), (1, 3, 32)])
+def test_tail9_matches_fp32_reference(dev, N, H, W):
+    _tail_case(dev, N, H, W, seed=N * 100 + H)
+
+
+def test_tail9_long_marches_and_segment_splits(dev):
+    _tail_case(dev, 6, 64, 64, seed=1, grid=2)
+    _tail_case(dev, 6, 64, 64, seed=2, grid=0)
+    _tail_case(dev, 9, 40, 64, seed=5, grid=37)
