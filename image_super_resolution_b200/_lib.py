@@ -60,6 +60,7 @@ SIGNATURES = {
     "srb_pack_batch_create": (_i, [_vp, _vp, _i, C.POINTER(_vp)]),
     "srb_pack_batch_run": (_i, [_vp, _vp, _vp]),
     "srb_pack_batch_destroy": (None, [_vp]),
+    "srb_set_programmatic_launch": (_i, [_vp, _i]),
     "srb_resblock_create": (_i, [_vp, _vp, _vp, _vp, _vp, _i, C.POINTER(_vp)]),
     "srb_resblock_destroy": (None, [_vp]),
     "srb_resblock_supported": (_i, [_i, _i]),

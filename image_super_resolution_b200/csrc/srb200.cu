@@ -58,6 +58,7 @@ struct srb_ctx {
     int dbg_grid = 0;
     int dbg_skip = 0;
     bool pdl = false;         // launch the conv kernels with programmatic stream serialization (set by srb_model_pt_forward)
+    bool pdl_all = false;     // ... for every conv launch of this context (srb_set_programmatic_launch)
     int dbg_repeat = 0;       // probes: launch the fused block this many extra times per call
     int dbg_threads = 0, dbg_smem = -1;
     long long* dbg_trace = nullptr;
@@ -130,6 +131,11 @@ extern "C" void srb_destroy(srb_ctx* c) {
     delete c;
 }
 extern "C" int srb_num_sms(const srb_ctx* c) { return c ? c->num_sms : 0; }
+extern "C" int srb_set_programmatic_launch(srb_ctx* c, int on) {
+    if (!c) return fail(SRB_EINVAL, "ctx is NULL");
+    c->pdl_all = on != 0;
+    return SRB_OK;
+}
 extern "C" int srb_debug_set(srb_ctx* c, int key, int value) {
     if (!c) return fail(SRB_EINVAL, "ctx is NULL");
     if (key == 0) c->dbg_swap = value;
@@ -326,7 +332,7 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(CONV_THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = ctx->pdl ? 1 : 0;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->pdl || ctx->pdl_all) ? 1 : 0;
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (w->dtype == SRB_DT_BF16) {
         auto kern = conv_tc_kernel<C8IN, NOUT, KH, KW, MODE, NT, RES, WS, true, BWD>;

@@ -19,7 +19,7 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
-from . import ops
+from . import ops, _lib
 from ._lib import Context
 
 
@@ -71,6 +71,7 @@ class TrainPlan:
         self.buf = {}
         self.saved = None
         self.use_graphs = True
+        self.use_pdl = True          # programmatic edges between the conv nodes of the captured graphs
         self.wgrad_splitk = 1
         self.graphs = {}
         self.pack_batch, self.pack_ptrs = None, None
@@ -122,6 +123,10 @@ class TrainPlan:
             self.buf[name] = t
         return t[1]
 
+    def _pdl(self, on: bool):
+        if self.use_pdl:
+            _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 1 if on else 0), "srb_set_programmatic_launch")
+
     # ---- CUDA graphs: the step is ~2 000 launches of 5-20 us kernels, host-bound from Python otherwise ------------
     def _graph_key(self, x):
         return (tuple(x.shape), tuple(p.data_ptr() for p in self.params))
@@ -138,12 +143,18 @@ class TrainPlan:
             self.repack()
             self._forward_impl(self.graphs["x"])             # eager warm-up: allocates buffers, sets kernel attributes
             torch.cuda.synchronize(self.device)
+            # The operand re-pack stays outside the graph: inside it the packed weights are then constants, and the conv
+            # nodes can be linked by programmatic edges (each conv's prologue overlaps its predecessor's tail).
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self.repack()
-                self.graphs["out"] = self._forward_impl(self.graphs["x"])
+            self._pdl(True)
+            try:
+                with torch.cuda.graph(g):
+                    self.graphs["out"] = self._forward_impl(self.graphs["x"])
+            finally:
+                self._pdl(False)
             self.graphs["fwd"] = g
             self.graphs["saved"] = self.saved
+        self.repack()
         self.graphs["x"].copy_(x)
         self.graphs["fwd"].replay()
         self.saved = self.graphs["saved"]
@@ -160,8 +171,12 @@ class TrainPlan:
                 self._backward_impl(self.graphs["gout"])
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    self.graphs["grads"] = self._backward_impl(self.graphs["gout"])
+                self._pdl(True)
+                try:
+                    with torch.cuda.graph(g):
+                        self.graphs["grads"] = self._backward_impl(self.graphs["gout"])
+                finally:
+                    self._pdl(False)
                 self.graphs["bwd"] = g
             self.graphs["gout"].copy_(gout)
             self.graphs["bwd"].replay()

@@ -140,6 +140,12 @@ int srb_model_pt_launches(int H, int W);
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
 /* cudaDeviceSynchronize + report a kernel-side pipeline timeout (kernels never hang: bounded waits) */
 int srb_check_device(srb_ctx* ctx);
+/* on != 0: every conv launch of this context carries cudaLaunchAttributeProgrammaticStreamSerialization, so its prologue
+ * (barriers, TMEM, filters, bias) overlaps the tail of the previous launch in the stream (also as programmatic edges of a
+ * captured CUDA graph).  The kernels wait for the previous launch before touching activations, but they read packed weights
+ * and biases in the prologue: only enable this where those are not written by the immediately preceding launches of the
+ * same stream.  srb_model_pt_forward / srb_resblock_fwd / srb_rowconv_fwd / srb_tail9_fwd always launch this way. */
+int srb_set_programmatic_launch(srb_ctx* ctx, int on);
 int srb_debug_trace(srb_ctx* ctx, void* dev_buf512_int64);  /* per-step clock stamps of CTA 0, diagnostics */
 int srb_profile_enable(srb_ctx* ctx, int on);
 int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
