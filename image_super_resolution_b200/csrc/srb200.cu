@@ -458,8 +458,19 @@ extern "C" int srb_u8nchw_to_c8(srb_ctx* ctx, const uint8_t* in, void* out, cons
     if (!ctx || !in || !out || !mean || !std_) return fail(SRB_EINVAL, "srb_u8nchw_to_c8: NULL argument");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_u8nchw_to_c8: empty shape");
     size_t HW = (size_t)H * W, total = HW * N;
-    int grid = ew_grid(ctx, total, 256);
     cudaStream_t st = (cudaStream_t)stream;
+    if (HW % 4 == 0 && ((uintptr_t)in & 3) == 0 && HW / 4 < 0x40000000ull) {
+        const size_t total4 = total / 4;
+        size_t nb = (total4 + 255) / 256, cap = (size_t)ctx->num_sms * 16;
+        const int g4 = (int)(nb < cap ? (nb ? nb : 1) : cap);
+        if (dtype == SRB_DT_BF16)
+            u8nchw_to_c8_x4_kernel<true><<<g4, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, (unsigned)(HW / 4), total4);
+        else
+            u8nchw_to_c8_x4_kernel<false><<<g4, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, (unsigned)(HW / 4), total4);
+        CUDA_TRY(cudaGetLastError());
+        return SRB_OK;
+    }
+    int grid = ew_grid(ctx, total, 256);
     if (dtype == SRB_DT_BF16)
         u8nchw_to_c8_kernel<true><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, HW, total);
     else

@@ -34,6 +34,28 @@ __global__ void u8nchw_to_c8_kernel(const uint8_t* __restrict__ in, uint4* __res
     }
 }
 
+// four pixels per thread (H*W % 4 == 0 and a 4-byte aligned input): one 32-bit load per colour plane, four 16-byte stores
+template <bool BF16>
+__global__ void u8nchw_to_c8_x4_kernel(const uint8_t* __restrict__ in, uint4* __restrict__ out, float m0, float m1,
+                                       float m2, float s0, float s1, float s2, float maxv, unsigned HW4, size_t total4) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t n = i / HW4;
+        const unsigned q = (unsigned)(i - n * HW4);
+        const uint32_t* b = reinterpret_cast<const uint32_t*>(in + n * 3 * (size_t)HW4 * 4) + q;
+        const uint32_t r4 = __ldg(b), g4 = __ldg(b + HW4), b4 = __ldg(b + 2 * (size_t)HW4);
+        uint4* o = out + i * 4;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float r = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((r4 >> (8 * k)) & 255u), maxv), m0), s0);
+            const float g = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((g4 >> (8 * k)) & 255u), maxv), m1), s1);
+            const float bl = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((b4 >> (8 * k)) & 255u), maxv), m2), s2);
+            uint4 v;
+            v.x = pk2<BF16>(r, g); v.y = pk2<BF16>(bl, 0.f); v.z = 0u; v.w = 0u;
+            o[k] = v;
+        }
+    }
+}
+
 // fp32 NCHW [N][C][H][W] -> planes c8_off.. of a C8 buffer; channels beyond C in the last plane are zero.
 template <bool BF16>
 __global__ void f32nchw_to_c8_kernel(const float* __restrict__ in, uint4* __restrict__ out, int C, int c8_total,
