@@ -61,6 +61,8 @@ SIGNATURES = {
     "srb_pack_batch_run": (_i, [_vp, _vp, _vp]),
     "srb_pack_batch_destroy": (None, [_vp]),
     "srb_set_programmatic_launch": (_i, [_vp, _i]),
+    "srb_u8nchw_to_pair4": (_i, [_vp, _vp, _vp, _fp, _fp, _f, _i, _i, _i, _i, _vp]),
+    "srb_pack_conv_pair4": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(_vp)]),
     "srb_resblock_create": (_i, [_vp, _vp, _vp, _vp, _vp, _i, C.POINTER(_vp)]),
     "srb_resblock_destroy": (None, [_vp]),
     "srb_resblock_supported": (_i, [_i, _i]),

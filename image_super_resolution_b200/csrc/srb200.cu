@@ -90,6 +90,7 @@ struct srb_net {
     srb_resblock* rb[8];     // fused ResidualBlock1 operands (used when the shape qualifies)
     srb_rowconv* rc1 = nullptr;   // conv1 (+ long skip) on the row-fold kernel
     srb_tail9* tail = nullptr;    // conv2 + tanh -> uint8 on the row-fold kernel
+    srb_weights* head4 = nullptr; // conv0 packed for pixel-pair input granules (MODE_PAIR4)
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -279,6 +280,38 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
     return SRB_OK;
 }
 
+// 9x9 head conv, Cin = 3, for pixel-pair input granules (MODE_PAIR4, srb_conv.cuh): K-step ks = dy * 3 + dxq; K granule g
+// holds taps dx = 4*dxq + 2*g + {0, 1}, 4 k-slots each (3 channels + 0)
+extern "C" int srb_pack_conv_pair4(srb_ctx* ctx, const float* w, const float* bias, int cout, int dtype, srb_weights** out) {
+    if (!ctx || !w || !out) return fail(SRB_EINVAL, "srb_pack_conv_pair4: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_pack_conv_pair4: dtype %d", dtype);
+    if (cout != 64) return fail(SRB_ENOSUP, "srb_pack_conv_pair4: cout=%d (64 only)", cout);
+    const int nout = 64, ksteps = 27;
+    const size_t step_elems = (size_t)2 * nout * 8;
+    std::vector<uint16_t> pack((size_t)ksteps * step_elems, 0);
+    for (int dy = 0; dy < 9; ++dy) for (int dxq = 0; dxq < 3; ++dxq) for (int g = 0; g < 2; ++g) for (int n = 0; n < cout; ++n)
+        for (int j = 0; j < 8; ++j) {
+            const int dx = 4 * dxq + 2 * g + (j >> 2), c = j & 3;
+            if (dx >= 9 || c >= 3) continue;
+            pack[(size_t)(dy * 3 + dxq) * step_elems + ((size_t)g * nout + n) * 8 + j] = f2h(w[(((size_t)n * 3 + c) * 9 + dy) * 9 + dx], dtype);
+        }
+    srb_weights* sw = new srb_weights();
+    sw->cout = cout; sw->cin = 3; sw->k = 9; sw->dtype = dtype;
+    sw->mode = MODE_PAIR4; sw->c8in = 1; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = 0;
+    sw->pack_bytes = pack.size() * 2;
+    cudaSetDevice(ctx->device);
+    if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
+        srb_free_weights(sw);
+        return fail(SRB_ENOMEM, "srb_pack_conv_pair4: cudaMalloc failed");
+    }
+    std::vector<float> hb(nout, 0.f);
+    for (int o = 0; o < cout; ++o) hb[o] = bias ? bias[o] : 0.f;
+    CUDA_TRY(cudaMemcpy(sw->d_pack, pack.data(), sw->pack_bytes, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(sw->d_bias, hb.data(), nout * sizeof(float), cudaMemcpyHostToDevice));
+    *out = sw;
+    return SRB_OK;
+}
+
 extern "C" void srb_free_weights(srb_weights* w) {
     if (!w) return;
     if (w->d_pack) cudaFree(w->d_pack);
@@ -302,8 +335,9 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
     p.num_tiles = (int)nt;
 
     CUtensorMap tmap;
-    cuuint64_t gdim[4] = {(cuuint64_t)p.W * 4, (cuuint64_t)p.H, (cuuint64_t)x_c8_total, (cuuint64_t)p.N};
-    cuuint64_t gstr[3] = {(cuuint64_t)p.W * 16, (cuuint64_t)p.W * p.H * 16, (cuuint64_t)p.W * p.H * 16 * x_c8_total};
+    const cuuint64_t WX = (cuuint64_t)p.W + (MODE == MODE_PAIR4 ? 1 : 0);       // PAIR4: granules -1 .. W-1 are stored
+    cuuint64_t gdim[4] = {WX * 4, (cuuint64_t)p.H, (cuuint64_t)x_c8_total, (cuuint64_t)p.N};
+    cuuint64_t gstr[3] = {WX * 16, WX * p.H * 16, WX * p.H * 16 * x_c8_total};
     cuuint32_t box[4] = {(cuuint32_t)G::HALO_W * 4, (cuuint32_t)G::HALO_H, (cuuint32_t)C8IN, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     // typed as 32-bit words (4 per 16-byte granule): only zero fill and byte movement matter, and it lifts the
@@ -415,6 +449,10 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     if ((flags & SRB_F_RESIDUAL) && (res_c8_off < 0 || res_c8_off + res_need > res_c8_total)) return fail(SRB_EINVAL, "srb_conv2d_fwd: residual plane slice out of range");
     if (y_c8_off < 0 || y_c8_off + out_planes > y_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: output plane slice out of range");
     if (w->cout % 8) return fail(SRB_ENOSUP, "srb_conv2d_fwd: cout=%d not a multiple of 8", w->cout);
+    if (w->mode == MODE_PAIR4) {
+        if (x_c8_total != 1 || x_c8_off != 0) return fail(SRB_EINVAL, "srb_conv2d: the pixel-pair head conv reads a single pair-granule plane");
+        return launch_conv<1, 64, 9, 9, MODE_PAIR4, 4>(ctx, w, x, x_c8_total, p, st);
+    }
     if (w->mode == MODE_PAIRDX) {
         if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
@@ -475,6 +513,32 @@ extern "C" int srb_u8nchw_to_c8(srb_ctx* ctx, const uint8_t* in, void* out, cons
         u8nchw_to_c8_kernel<true><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, HW, total);
     else
         u8nchw_to_c8_kernel<false><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_u8nchw_to_pair4(srb_ctx* ctx, const uint8_t* in, void* out, const float mean[3], const float std_[3],
+                                   float maxv, int dtype, int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !in || !out || !mean || !std_) return fail(SRB_EINVAL, "srb_u8nchw_to_pair4: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_u8nchw_to_pair4: empty shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (W % 4 == 0 && ((uintptr_t)in & 3) == 0) {
+        const size_t total4 = (size_t)N * H * (W / 4);
+        size_t nb = (total4 + 255) / 256, cap = (size_t)ctx->num_sms * 16;
+        const int g4 = (int)(nb < cap ? (nb ? nb : 1) : cap);
+        if (dtype == SRB_DT_BF16)
+            u8nchw_to_pair4_x4_kernel<true><<<g4, 256, 0, st>>>(in, (uint2*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
+        else
+            u8nchw_to_pair4_x4_kernel<false><<<g4, 256, 0, st>>>(in, (uint2*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
+        CUDA_TRY(cudaGetLastError());
+        return SRB_OK;
+    }
+    const size_t total = (size_t)N * H * ((size_t)W + 1);
+    const int grid = ew_grid(ctx, total, 256);
+    if (dtype == SRB_DT_BF16)
+        u8nchw_to_pair4_kernel<true><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total);
+    else
+        u8nchw_to_pair4_kernel<false><<<grid, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total);
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
@@ -581,6 +645,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
         rc = srb_resblock_create(ctx, w[1 + 2 * i], b[1 + 2 * i], w[2 + 2 * i], b[2 + 2 * i], dtype, &net->rb[i]);
     if (rc == SRB_OK) rc = srb_rowconv_create(ctx, w[17], b[17], dtype, &net->rc1);
     if (rc == SRB_OK) rc = srb_tail9_create(ctx, w[18], b[18], dtype, &net->tail);
+    if (rc == SRB_OK) rc = srb_pack_conv_pair4(ctx, w[0], b[0], 64, dtype, &net->head4);
     if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
     *out = net;
     return SRB_OK;
@@ -592,6 +657,7 @@ extern "C" void srb_model_pt_destroy(srb_net* net) {
     for (int i = 0; i < 8; ++i) srb_resblock_destroy(net->rb[i]);
     srb_rowconv_destroy(net->rc1);
     srb_tail9_destroy(net->tail);
+    srb_free_weights(net->head4);
     delete net;
 }
 
@@ -600,7 +666,7 @@ static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
     if (N <= 0 || H <= 0 || W <= 0) return 0;
     size_t P = (size_t)N * H * W;
-    return align256(P * 16) + 3 * align256(P * 128) + align256(P * 64);
+    return align256((size_t)N * H * (W + 1) * 16) + 3 * align256(P * 128) + align256(P * 64);
 }
 
 // kernels one forward enqueues: pack, head, 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
@@ -668,7 +734,7 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     if ((uintptr_t)ws & 255) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace must be 256-byte aligned");
     size_t P = (size_t)N * H * W;
     uint8_t* base = (uint8_t*)ws;
-    void* in8 = base; base += align256(P * 16);
+    void* in8 = base; base += align256((size_t)N * H * (W + 1) * 16);   // one input plane (pixel-pair granules: W + 1 per row)
     void* x0 = base; base += align256(P * 128);
     void* ra = base; base += align256(P * 128);
     void* rb = base; base += align256(P * 128);
@@ -679,9 +745,15 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     struct PdlScope { srb_ctx* c; ~PdlScope() { c->pdl = false; } } pdl_scope{ctx};
     ctx->pdl = !(ctx->dbg_skip & 1024);
     prof_mark(ctx, pst, true);
-    if ((rc = srb_u8nchw_to_c8(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
-    prof_mark(ctx, pst);
-    if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+    if (!(ctx->dbg_skip & 32768)) {      // head conv on pixel-pair granules: 27 MMAs per M-tile instead of 45
+        if ((rc = srb_u8nchw_to_pair4(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
+        prof_mark(ctx, pst);
+        if ((rc = srb_conv2d_fwd(ctx, net->head4, in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+    } else {
+        if ((rc = srb_u8nchw_to_c8(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
+        prof_mark(ctx, pst);
+        if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
+    }
     prof_mark(ctx, pst);
     void* cur = x0;
     const bool fused = srb_resblock_supported(H, W) && !(ctx->dbg_skip & 8);

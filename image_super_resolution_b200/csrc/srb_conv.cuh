@@ -27,7 +27,11 @@
 
 namespace srb {
 
-enum : int { MODE_STD = 0, MODE_PAIRDX = 1, MODE_DXN = 2 };
+enum : int { MODE_STD = 0, MODE_PAIRDX = 1, MODE_DXN = 2, MODE_PAIR4 = 3 };
+// MODE_PAIR4 (9x9 head, Cin = 3): the input plane holds PIXEL-PAIR granules — granule g of a row = [pixel g: c0 c1 c2 0 |
+// pixel g+1: c0 c1 c2 0], stored for g = -1 .. W-1 (row pitch W+1 granules; u8nchw_to_pair4_kernel) — so one 16-byte
+// granule carries two dx taps and the two K granules of an MMA (g and g+2, LBO = 32 B) carry four: 9 dy x 3 K-steps = 27
+// MMAs per M-tile instead of PAIRDX's 45.
 
 // epilogue flags (mirrored in include/srb200.h)
 enum : int {
@@ -75,7 +79,8 @@ struct ConvGeom {
     static constexpr int SUPER_W = (MODE == MODE_STD) ? TW * NT : TW;
     static constexpr int SUPER_H = (MODE == MODE_STD) ? TH : TH * NT;
     static constexpr int PADX = KW / 2, PADY = KH / 2;
-    static constexpr int HALO_W = (MODE == MODE_DXN) ? 16 : (SUPER_W + KW - 1 + ((MODE == MODE_PAIRDX) ? (KW & 1) : 0));
+    static constexpr int HALO_W = (MODE == MODE_DXN) ? 16 : (MODE == MODE_PAIR4) ? (SUPER_W + KW - 1 + 2)
+                                                         : (SUPER_W + KW - 1 + ((MODE == MODE_PAIRDX) ? (KW & 1) : 0));
     static constexpr int HALO_H = SUPER_H + KH - 1;
     static constexpr int ROWP = HALO_W * 16;                      // bytes between tile rows
     static constexpr int PLANE = HALO_H * ROWP;                   // bytes between channel planes
@@ -84,6 +89,7 @@ struct ConvGeom {
     static constexpr int A_STRIDE = (STAGE_BYTES + 1023) / 1024 * 1024;
     static constexpr int KSTEPS = (MODE == MODE_STD)      ? KH * KW * (C8IN / 2)
                                   : (MODE == MODE_PAIRDX) ? KH * ((KW + 1) / 2)
+                                  : (MODE == MODE_PAIR4)  ? KH * ((KW + 3) / 4)
                                                           : KH * (C8IN / 2);
     static constexpr int WSTEP_BYTES = 2 * NOUT * 16;             // one K=16 slice of B
     static constexpr int WBLK_BYTES = KSTEPS * WSTEP_BYTES;      // filter slice of one K block
@@ -107,8 +113,8 @@ struct ConvGeom {
     static constexpr int RSLOTS = RES ? max_rslots() : 0;
     static constexpr int SMEM_BYTES = SMEM_FIXED + STAGES * STAGE_STRIDE + RSLOTS * RES_TILE_BYTES;
     static_assert(!RES || (RSLOTS >= 2 && MODE == MODE_STD), "residual ring needs two slots (STD mode only)");
-    static_assert(MODE != MODE_PAIRDX || C8IN == 1, "PAIRDX pairs neighbouring pixels of a single plane");
-    static_assert(MODE == MODE_PAIRDX || (C8IN % 2) == 0, "K=16 needs two channel planes per MMA");
+    static_assert((MODE != MODE_PAIRDX && MODE != MODE_PAIR4) || C8IN == 1, "PAIRDX / PAIR4 pair neighbouring pixels of a single plane");
+    static_assert(MODE == MODE_PAIRDX || MODE == MODE_PAIR4 || (C8IN % 2) == 0, "K=16 needs two channel planes per MMA");
     static_assert(MODE != MODE_DXN || (KW == 9 && NOUT == 32), "DXN folds 9 dx taps x 3 couts into N=32");
     static_assert(NOUT % 32 == 0 && NOUT <= 256, "epilogue reads TMEM 32 columns at a time");
     static_assert(ACC_COLS <= 512, "TMEM holds 512 columns");
@@ -237,7 +243,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                     if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
                     else {
                         mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES + (WS ? G::WBLK_BYTES : 0));
-                        tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX) * 4,
+                        tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX + (MODE == MODE_PAIR4 ? 1 : 0)) * 4,
                                     ty * G::SUPER_H - G::PADY, p.x_c8_off + kb * C8IN, n);
                         if constexpr (WS) {
                             uint8_t* wdst = s_a + s * G::STAGE_STRIDE + G::A_STRIDE;
@@ -256,7 +262,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         constexpr uint32_t idesc = umma_idesc_f16(128, NOUT, BF16 ? 1 : 0);
-        uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (uint32_t)G::PLANE;
+        uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (MODE == MODE_PAIR4) ? 32u : (uint32_t)G::PLANE;
         uint32_t a_sbo = (MODE == MODE_DXN) ? 128u : (uint32_t)G::ROWP;
         uint32_t b_lbo = NOUT * 16, b_sbo = 128;
         if (p.dbg_swap) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
@@ -300,6 +306,17 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 #pragma unroll
                             for (int dxp = 0; dxp < (KW + 1) / 2; ++dxp, ++ks) {
                                 const uint32_t ao = (dy * G::ROWP + 2 * dxp * 16) >> 4;
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+#pragma unroll
+                                for (int t = 0; t < NT; ++t)
+                                    umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
+                            }
+                    } else if constexpr (MODE == MODE_PAIR4) {
+#pragma unroll 1
+                        for (int dy = 0; dy < KH; ++dy)
+#pragma unroll
+                            for (int dxq = 0; dxq < (KW + 3) / 4; ++dxq, ++ks) {
+                                const uint32_t ao = (dy * G::ROWP + 4 * dxq * 16) >> 4;
                                 const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)

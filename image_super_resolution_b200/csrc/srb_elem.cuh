@@ -56,6 +56,62 @@ __global__ void u8nchw_to_c8_x4_kernel(const uint8_t* __restrict__ in, uint4* __
     }
 }
 
+// Normalize into PIXEL-PAIR granules for the MODE_PAIR4 head conv: out[n][y][xs], xs = 0 .. W, = [pixel xs-1 | pixel xs]
+// (4 x 16-bit each: c0 c1 c2 0; pixels -1 and W are zero).  One thread per granule.
+template <bool BF16>
+__global__ void u8nchw_to_pair4_kernel(const uint8_t* __restrict__ in, uint4* __restrict__ out, float m0, float m1,
+                                       float m2, float s0, float s1, float s2, float maxv, int H, int W, size_t total) {
+    const size_t HW = (size_t)H * W;
+    const unsigned W1 = (unsigned)W + 1u;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t row = i / W1;                       // n * H + y
+        const int xs = (int)(i - row * W1);
+        const size_t n = row / (size_t)H, y = row - n * (size_t)H;
+        const uint8_t* b = in + n * 3 * HW + y * (size_t)W;
+        uint32_t h[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int x = xs - 1 + k;
+            if (x >= 0 && x < W) {
+                const float r = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[x], maxv), m0), s0);
+                const float g = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[HW + x], maxv), m1), s1);
+                const float bl = __fdiv_rn(__fsub_rn(__fdiv_rn((float)b[2 * HW + x], maxv), m2), s2);
+                h[2 * k] = pk2<BF16>(r, g); h[2 * k + 1] = pk2<BF16>(bl, 0.f);
+            }
+        }
+        out[i] = make_uint4(h[0], h[1], h[2], h[3]);
+    }
+}
+
+// four pixels per thread (W % 4 == 0, 4-byte aligned input): every pixel's 8-byte half is normalised once and stored twice
+// (second half of granule x, first half of granule x + 1); the row's two zero halves come from its first / last thread
+template <bool BF16>
+__global__ void u8nchw_to_pair4_x4_kernel(const uint8_t* __restrict__ in, uint2* __restrict__ out8, float m0, float m1,
+                                          float m2, float s0, float s1, float s2, float maxv, int H, int W, size_t total4) {
+    const size_t HW = (size_t)H * W;
+    const unsigned W4 = (unsigned)W / 4u;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t row = i / W4;                       // n * H + y
+        const unsigned x0 = (unsigned)(i - row * W4) * 4u;
+        const size_t n = row / (size_t)H, y = row - n * (size_t)H;
+        const uint8_t* b = in + n * 3 * HW + y * (size_t)W + x0;
+        const uint32_t r4 = __ldg(reinterpret_cast<const uint32_t*>(b)), g4 = __ldg(reinterpret_cast<const uint32_t*>(b + HW)),
+                       b4 = __ldg(reinterpret_cast<const uint32_t*>(b + 2 * HW));
+        uint2* o = out8 + (row * ((size_t)W + 1) + x0) * 2;          // half 0 of granule x0
+        if (x0 == 0) o[0] = make_uint2(0u, 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float r = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((r4 >> (8 * k)) & 255u), maxv), m0), s0);
+            const float g = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((g4 >> (8 * k)) & 255u), maxv), m1), s1);
+            const float bl = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((b4 >> (8 * k)) & 255u), maxv), m2), s2);
+            const uint2 h = make_uint2(pk2<BF16>(r, g), pk2<BF16>(bl, 0.f));
+            o[2 * k + 1] = h;                // second half of granule x0 + k      = [pixel x-1 | pixel x]
+            o[2 * k + 2] = h;                // first half of granule x0 + k + 1
+        }
+        if (x0 + 4 == (unsigned)W) o[9] = make_uint2(0u, 0u);        // second half of granule W
+    }
+}
+
 // fp32 NCHW [N][C][H][W] -> planes c8_off.. of a C8 buffer; channels beyond C in the last plane are zero.
 template <bool BF16>
 __global__ void f32nchw_to_c8_kernel(const float* __restrict__ in, uint4* __restrict__ out, int C, int c8_total,

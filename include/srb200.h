@@ -165,6 +165,15 @@ int srb_resblock_supported(int H, int W);
 int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void* x, void* y, float lrelu_slope, int N, int H, int W,
                      srb_stream_t stream);
 
+/* Head conv on pixel-pair granules (model.pt: Normalize + net.1.conv0, utils/datasets.py:65-71, utils/models.py:97-98).
+ * srb_u8nchw_to_pair4 writes, per image row, W + 1 granules [pixel g | pixel g+1] (4 x 16-bit each: 3 normalised channels + 0;
+ * g = -1 .. W-1, out-of-image pixels zero) — `out` holds N*H*(W+1) granules.  srb_pack_conv_pair4 packs the [64][3][9][9]
+ * filter so that one K=16 MMA step covers four dx taps (27 steps instead of 45); the result is used with srb_conv2d_fwd
+ * (x_c8_total = 1) exactly like the srb_pack_conv head conv, and gives the same values. */
+int srb_u8nchw_to_pair4(srb_ctx* ctx, const uint8_t* in_nchw, void* out_pairs, const float mean[3], const float std_[3],
+                        float max_pixel_value, int dtype, int N, int H, int W, srb_stream_t stream);
+int srb_pack_conv_pair4(srb_ctx* ctx, const float* w_oihw, const float* bias, int cout, int dtype, srb_weights** out);
+
 /* Row-fold 3x3 conv 64 -> 64: y = act(conv(x) + b) + res — `Conv(64,64,3,act=False)` utils/models.py:690 with the long
  * skip `inputs + self.conv1(residual)` :704 (model.pt: net.1.conv1), the same GEMM mapping as the fused residual block
  * (dy taps folded into N = 192, accumulation over adjacent TMEM rows).  w [64][64][3][3] fp32 host (BN folded),
