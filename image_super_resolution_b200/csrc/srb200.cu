@@ -527,9 +527,9 @@ extern "C" int srb_u8nchw_to_pair4(srb_ctx* ctx, const uint8_t* in, void* out, c
         size_t nb = (total4 + 255) / 256, cap = (size_t)ctx->num_sms * 16;
         const int g4 = (int)(nb < cap ? (nb ? nb : 1) : cap);
         if (dtype == SRB_DT_BF16)
-            u8nchw_to_pair4_x4_kernel<true><<<g4, 256, 0, st>>>(in, (uint2*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
+            u8nchw_to_pair4_x4_kernel<true><<<g4, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
         else
-            u8nchw_to_pair4_x4_kernel<false><<<g4, 256, 0, st>>>(in, (uint2*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
+            u8nchw_to_pair4_x4_kernel<false><<<g4, 256, 0, st>>>(in, (uint4*)out, mean[0], mean[1], mean[2], std_[0], std_[1], std_[2], maxv, H, W, total4);
         CUDA_TRY(cudaGetLastError());
         return SRB_OK;
     }

@@ -83,32 +83,46 @@ __global__ void u8nchw_to_pair4_kernel(const uint8_t* __restrict__ in, uint4* __
     }
 }
 
-// four pixels per thread (W % 4 == 0, 4-byte aligned input): every pixel's 8-byte half is normalised once and stored twice
-// (second half of granule x, first half of granule x + 1); the row's two zero halves come from its first / last thread
+// four pixels per thread (W % 4 == 0, 4-byte aligned input, blockDim a multiple of 32): every pixel's 8-byte half is
+// normalised once; a granule needs the half of the pixel to its left, which comes from the neighbouring lane (lane 0 and
+// the first thread of a row compute / zero it themselves).  Four 16-byte stores per thread, five at the end of a row.
 template <bool BF16>
-__global__ void u8nchw_to_pair4_x4_kernel(const uint8_t* __restrict__ in, uint2* __restrict__ out8, float m0, float m1,
+__global__ void u8nchw_to_pair4_x4_kernel(const uint8_t* __restrict__ in, uint4* __restrict__ out, float m0, float m1,
                                           float m2, float s0, float s1, float s2, float maxv, int H, int W, size_t total4) {
     const size_t HW = (size_t)H * W;
     const unsigned W4 = (unsigned)W / 4u;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t row = i / W4;                       // n * H + y
-        const unsigned x0 = (unsigned)(i - row * W4) * 4u;
+    const int lane = threadIdx.x & 31;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i0 = blockIdx.x * (size_t)blockDim.x + (threadIdx.x & ~31u); i0 < total4; i0 += stride) {   // warp-uniform trip count
+        const size_t i = i0 + lane;
+        const bool act = i < total4;
+        const size_t ii = act ? i : total4 - 1;
+        const size_t row = ii / W4;                       // n * H + y
+        const unsigned x0 = (unsigned)(ii - row * W4) * 4u;
         const size_t n = row / (size_t)H, y = row - n * (size_t)H;
         const uint8_t* b = in + n * 3 * HW + y * (size_t)W + x0;
         const uint32_t r4 = __ldg(reinterpret_cast<const uint32_t*>(b)), g4 = __ldg(reinterpret_cast<const uint32_t*>(b + HW)),
                        b4 = __ldg(reinterpret_cast<const uint32_t*>(b + 2 * HW));
-        uint2* o = out8 + (row * ((size_t)W + 1) + x0) * 2;          // half 0 of granule x0
-        if (x0 == 0) o[0] = make_uint2(0u, 0u);
+        auto norm = [&](uint32_t r, uint32_t g, uint32_t bl) {
+            const float fr = __fdiv_rn(__fsub_rn(__fdiv_rn((float)r, maxv), m0), s0);
+            const float fg = __fdiv_rn(__fsub_rn(__fdiv_rn((float)g, maxv), m1), s1);
+            const float fb = __fdiv_rn(__fsub_rn(__fdiv_rn((float)bl, maxv), m2), s2);
+            return make_uint2(pk2<BF16>(fr, fg), pk2<BF16>(fb, 0.f));
+        };
+        uint2 h[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float r = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((r4 >> (8 * k)) & 255u), maxv), m0), s0);
-            const float g = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((g4 >> (8 * k)) & 255u), maxv), m1), s1);
-            const float bl = __fdiv_rn(__fsub_rn(__fdiv_rn((float)((b4 >> (8 * k)) & 255u), maxv), m2), s2);
-            const uint2 h = make_uint2(pk2<BF16>(r, g), pk2<BF16>(bl, 0.f));
-            o[2 * k + 1] = h;                // second half of granule x0 + k      = [pixel x-1 | pixel x]
-            o[2 * k + 2] = h;                // first half of granule x0 + k + 1
-        }
-        if (x0 + 4 == (unsigned)W) o[9] = make_uint2(0u, 0u);        // second half of granule W
+        for (int k = 0; k < 4; ++k) h[k] = norm((r4 >> (8 * k)) & 255u, (g4 >> (8 * k)) & 255u, (b4 >> (8 * k)) & 255u);
+        uint2 left;
+        left.x = __shfl_up_sync(0xffffffffu, h[3].x, 1);
+        left.y = __shfl_up_sync(0xffffffffu, h[3].y, 1);
+        if (x0 == 0) left = make_uint2(0u, 0u);
+        else if (lane == 0) left = norm(b[-1], b[HW - 1], b[2 * HW - 1]);
+        if (!act) continue;
+        uint4* o = out + row * ((size_t)W + 1) + x0;       // granule x0 = [pixel x0-1 | pixel x0]
+        o[0] = make_uint4(left.x, left.y, h[0].x, h[0].y);
+#pragma unroll
+        for (int k = 1; k < 4; ++k) o[k] = make_uint4(h[k - 1].x, h[k - 1].y, h[k].x, h[k].y);
+        if (x0 + 4 == (unsigned)W) o[4] = make_uint4(h[3].x, h[3].y, 0u, 0u);
     }
 }
 
