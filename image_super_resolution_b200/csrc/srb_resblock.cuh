@@ -18,6 +18,7 @@
 // Warp roles (640 threads): 0 TMA producer, 1 convA MMA issuer, 2 convB MMA issuer, 4-11 hidden epilogue, 12-19 output
 // epilogue (each as two sets of 4 warps that alternate rows).  The tensor pipe interleaves the two issuers' independent accumulation chains.
 #pragma once
+#include <type_traits>
 #include <cuda.h>
 #include "srb_ptx.cuh"
 #include "srb_conv.cuh"
@@ -44,6 +45,9 @@ struct ResblockParams {
 #define RB_HSLOTS 3
 #define RB_XSTAGES 4
 #endif
+#ifndef RB_BIAS_MODE
+#define RB_BIAS_MODE 1       // 0: accumulator rows armed with the bias (re-armed from shared memory); 1: rows armed with zero,
+#endif                       //    the epilogues add the bias as a constant-bank operand (no shared-memory reads, no registers)
 #ifndef RB_SLEEP_NS
 #define RB_SLEEP_NS 40
 #endif
@@ -243,7 +247,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             const int b0 = c < G::TM_Y ? 0 : G::CH + ((c - G::TM_Y) & 32);
             uint32_t bv[32];
 #pragma unroll
-            for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(p.bias[b0 + k]);
+            for (int k = 0; k < 32; ++k) bv[k] = RB_BIAS_MODE == 0 ? __float_as_uint(p.bias[b0 + k]) : 0u;
             tmem_st32(tmem_base + lg + c, bv);
         }
         tmem_st_wait();
@@ -409,7 +413,9 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CH, rr);
                 tmem_ld_wait();
-                if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
+                if (RB_BIAS_MODE == 1) {
+                    if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
+                } else if (!(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[k]);
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     float v[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        const float tt = __uint_as_float(rr[8 * pl + k]);
+                        const float tt = __uint_as_float(rr[8 * pl + k]) + (RB_BIAS_MODE == 1 ? p.bias[8 * pl + k] : 0.f);
                         v[k] = fmaxf(tt, tt * p.slope);
                     }
                     o[pl].x = pack2<BF16>(v[0], v[1]); o[pl].y = pack2<BF16>(v[2], v[3]);
@@ -492,7 +498,9 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CB, rr);
                 tmem_ld_wait();
-                if (!(p.dbg_skip & 64)) {           // re-arm the accumulator row with the bias
+                if (RB_BIAS_MODE == 1) {
+                    if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CB);
+                } else if (!(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[G::CH + half * 32 + k]);
@@ -504,17 +512,25 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     for (int j = 0; j < 4; ++j) nxt[j] = __ldg(xg + j * plane + (size_t)(y + 1) * p.W);
                 }
                 if (tr) rb_trace(p, c, 8);
+                // (the bias index must be a compile-time constant to become a constant-bank operand: one copy per channel half)
+                auto finish = [&](auto off) {
+                    constexpr int OFF = decltype(off)::value;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
-                    uint32_t ov[4];
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
+                        uint32_t ov[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float2 f = unpack2<BF16>(qq[k]);
-                        ov[k] = pack2<BF16>(__uint_as_float(rr[8 * j + 2 * k]) + f.x, __uint_as_float(rr[8 * j + 2 * k + 1]) + f.y);
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = unpack2<BF16>(qq[k]);
+                            float a = __uint_as_float(rr[8 * j + 2 * k]), b = __uint_as_float(rr[8 * j + 2 * k + 1]);
+                            if (RB_BIAS_MODE == 1) { a += p.bias[OFF + 8 * j + 2 * k]; b += p.bias[OFF + 8 * j + 2 * k + 1]; }
+                            ov[k] = pack2<BF16>(a + f.x, b + f.y);
+                        }
+                        if (valid && !no_st) yg[j * plane + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
                     }
-                    if (valid && !no_st) yg[j * plane + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
-                }
+                };
+                if (half == 0) finish(std::integral_constant<int, G::CH>{});
+                else finish(std::integral_constant<int, G::CH + 32>{});
                 if (tr) rb_trace(p, c, 15);
                 tmem_st_wait();
                 tc_fence_before();

@@ -7,7 +7,7 @@
 // output rows r-1, r, r+1), K-steps = 3 dx x 4 channel pairs.  Against the tiled kernel (36 N=64 MMAs per 128 px, each
 // re-reading its 4 KB A tile: 216 KB of operand reads) this is 12 N=192 MMAs, 120 KB — compute-bound instead of
 // shared-memory-bound.  A CTA marches down a contiguous run of rows; accumulator rows live in a ring of 8 x 64 TMEM
-// columns and are re-armed with the bias by the epilogue that drains them.
+// columns and are re-zeroed by the epilogue that drains them (the bias is a constant-bank operand of the epilogue's adds).
 #pragma once
 #include "srb_resblock.cuh"
 
@@ -46,7 +46,6 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);     // keeps the shared address space
     uint8_t* s_w = smem + G::OFF_W;
     uint8_t* s_x = smem + G::OFF_X;
-    float* s_bias = reinterpret_cast<float*>(smem + G::OFF_BIAS);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
     uint64_t* xfull = bars;            // [XSTAGES] TMA -> MMA
     uint64_t* xempty = bars + 4;       // [XSTAGES] MMA -> TMA
@@ -56,7 +55,6 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 25);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < G::C; i += G::THREADS) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
         for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
@@ -70,14 +68,11 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
-    if (warp >= 4 && warp < 8) {       // every MMA accumulates: arm all rows with the bias once
+    if (warp >= 4 && warp < 8) {       // every MMA accumulates: all rows start at zero (the epilogue adds the bias)
         const uint32_t lg = (uint32_t)((warp & 3) * 32) << 16;
 #pragma unroll 1
         for (int c = 0; c < 512; c += 32) {
-            uint32_t bv[32];
-#pragma unroll
-            for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[(c & 32) + k]);
-            tmem_st32(tmem_base + lg + c, bv);
+            tmem_zero32(tmem_base + lg + c);
         }
         tmem_st_wait();
     }
@@ -194,26 +189,27 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::C, rr);
                 tmem_ld_wait();
+                tmem_zero32(t_lane + slot * G::C);
+                // (the bias index must be a compile-time constant to become a constant-bank operand: one copy per channel half)
+                auto finish = [&](auto off) {
+                    constexpr int OFF = decltype(off)::value;
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {    // re-arm the accumulator row with the bias (two halves: register budget)
-                    uint32_t bv[16];
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
+                        uint32_t ov[4];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) bv[k] = __float_as_uint(s_bias[half * 32 + hh * 16 + k]);
-                    tmem_st16(t_lane + slot * G::C + hh * 16, bv);
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t qq[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
-                    uint32_t ov[4];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float2 f = unpack2<BF16>(qq[k]);
-                        float a = __uint_as_float(rr[8 * j + 2 * k]), b = __uint_as_float(rr[8 * j + 2 * k + 1]);
-                        if (p.lrelu) { a = fmaxf(a, a * p.slope); b = fmaxf(b, b * p.slope); }
-                        ov[k] = pack2<BF16>(a + f.x, b + f.y);
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = unpack2<BF16>(qq[k]);
+                            float a = __uint_as_float(rr[8 * j + 2 * k]) + p.bias[OFF + 8 * j + 2 * k];
+                            float b = __uint_as_float(rr[8 * j + 2 * k + 1]) + p.bias[OFF + 8 * j + 2 * k + 1];
+                            if (p.lrelu) { a = fmaxf(a, a * p.slope); b = fmaxf(b, b * p.slope); }
+                            ov[k] = pack2<BF16>(a + f.x, b + f.y);
+                        }
+                        if (valid && !no_st) yg[j * HW + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
                     }
-                    if (valid && !no_st) yg[j * HW + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
-                }
+                };
+                if (half == 0) finish(std::integral_constant<int, 0>{});
+                else finish(std::integral_constant<int, 32>{});
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
