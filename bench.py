@@ -39,9 +39,10 @@ FUSED_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576
 FUSED_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
 assert sum(FUSED_FLOP_PX) == FLOP_PER_PX
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the dominant kernel at the bench shape, from the
-# one `ncu --set full` capture summarised in profiles/ncu_resblock_r1_full.txt (144.0 MB read + 92.0 MB written; the
-# algorithmic traffic is 2 x 134.2 MB, part of the output is still in the 126 MB L2 when the launch ends).
-NCU_TRAFFIC_BYTES = {"resblock_64_32_64_fused": 236.07e6}
+# one `ncu --set full` capture of a whole forward summarised in profiles/ncu_fwd_r1_full.txt (mean of the 8 launches:
+# 143.8 MB read + 92.85 MB written; the algorithmic traffic is 2 x 134.2 MB, part of the output is still in the 126 MB
+# L2 when the launch ends).
+NCU_TRAFFIC_BYTES = {"resblock_64_32_64_fused": 236.65e6}
 NCU_TRAFFIC_SHAPE = (256, 64, 64)
 
 
