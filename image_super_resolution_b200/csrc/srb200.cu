@@ -1213,11 +1213,22 @@ extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* b
     return SRB_OK;
 }
 
-// the fused kernel tiles a row as 16 groups of 8 px whose boundaries must coincide with image edges every 16 groups
-extern "C" int srb_resblock_supported(int H, int W) {
-    if (H <= 0 || W <= 0) return 0;
-    const int gx = (W + 7) / 8;
-    return gx == 1 || gx == 2 || gx == 4 || gx == 8 || gx == 16;
+// The row-fold kernels (fused block, conv1, tail) tile a row as 16 slots of 8 px: several whole image rows of narrow
+// images, or overlapping 16-group strips of a wide one (rb_slot in srb_resblock.cuh) — every width is covered.
+extern "C" int srb_resblock_supported(int H, int W) { return H > 0 && W > 0; }
+
+// Tile geometry of the row-fold kernels; returns the number of strip-sets.  ov = 1: a wide image's strips overlap by one
+// group on each side (the result of a strip's edge groups needs data of groups outside the tile).
+template <class P>
+static long long set_tile_geom(P& p, int N, int H, int W, int ov) {
+    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8; p.OV = ov;
+    if (p.GX <= 16) {
+        p.TR = 16 / p.GX; p.TS = 0;
+        return ((long long)N + p.TR - 1) / p.TR;
+    }
+    const int step = 16 - 2 * ov;
+    p.TR = 0; p.TS = (p.GX - 2 * ov + step - 1) / step;
+    return (long long)N * p.TS;
 }
 
 extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void* x, void* y, float slope, int N, int H, int W,
@@ -1226,11 +1237,9 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_resblock_fwd: empty shape");
     if (x == y) return fail(SRB_EINVAL, "srb_resblock_fwd: in-place is not supported (neighbouring CTAs re-read halo rows of x)");
     if (((uintptr_t)x & 15) || ((uintptr_t)y & 15)) return fail(SRB_EINVAL, "srb_resblock_fwd: buffers must be 16-byte aligned");
-    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_resblock_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
     using G = RBGeom;
     ResblockParams p{};
-    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
-    p.BW = p.GX * 8 < 64 ? p.GX * 8 : 64;
+    const long long sets = set_tile_geom(p, N, H, W, 1);
     RBMaps* m = nullptr;
     for (RBMaps& c : rb->maps)
         if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
@@ -1248,8 +1257,6 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
-    const long long groups = (long long)N * p.GX;
-    const long long sets = (groups + 15) / 16;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_resblock_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.wA = rb->d_wA; p.wB = rb->d_wB;
@@ -1326,10 +1333,9 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
     if (x == y) return fail(SRB_EINVAL, "srb_rowconv_fwd: in-place is not supported (neighbouring CTAs re-read halo rows of x)");
     if (((uintptr_t)x & 15) || ((uintptr_t)y & 15) || ((uintptr_t)res & 15)) return fail(SRB_EINVAL, "srb_rowconv_fwd: buffers must be 16-byte aligned");
     if (flags & ~SRB_F_LRELU) return fail(SRB_ENOSUP, "srb_rowconv_fwd: flags 0x%x (only SRB_F_LRELU)", flags);
-    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_rowconv_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
     using G = RCGeom;
     RowconvParams p{};
-    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    const long long sets = set_tile_geom(p, N, H, W, 0);
     RBMaps* m = nullptr;
     for (RBMaps& c : rc->maps)
         if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
@@ -1347,8 +1353,6 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
-    const long long groups = (long long)N * p.GX;
-    const long long sets = (groups + 15) / 16;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_rowconv_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.w = rc->d_w;
@@ -1424,10 +1428,9 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     const int fmt = flags & (SRB_F_U8OUT | SRB_F_F32OUT);
     if ((flags & ~(SRB_F_TANH | SRB_F_U8OUT | SRB_F_F32OUT)) || (fmt != SRB_F_U8OUT && fmt != SRB_F_F32OUT))
         return fail(SRB_ENOSUP, "srb_tail9_fwd: flags 0x%x (SRB_F_TANH and exactly one of SRB_F_U8OUT / SRB_F_F32OUT)", flags);
-    if (!srb_resblock_supported(H, W)) return fail(SRB_ENOSUP, "srb_tail9_fwd: ceil(W/8) = %d must be 1, 2, 4, 8 or 16", (W + 7) / 8);
     using G = TLGeom;
     TailParams p{};
-    p.N = N; p.H = H; p.W = W; p.GX = (W + 7) / 8;
+    const long long sets = set_tile_geom(p, N, H, W, 1);
     RBMaps* m = nullptr;
     for (RBMaps& c : t->maps)
         if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
@@ -1445,8 +1448,6 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
-    const long long groups = (long long)N * p.GX;
-    const long long sets = (groups + 15) / 16;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_tail9_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.w = t->d_w;

@@ -26,8 +26,8 @@
 namespace srb {
 
 struct ResblockParams {
-    int N, H, W, GX;          // GX = groups (8 px) per image row; 16 % GX == 0
-    int BW;                   // pixels per residual / output TMA box: min(GX * 8, 64)
+    int N, H, W, GX;          // GX = groups (8 px) per image row
+    int TR, TS, OV;           // tile geometry (rb_slot): image rows per tile (narrow), strips per image row (wide), overlap
     int total_rows;           // strip-sets x H: the flattened (strip-set, output row) space split evenly over CTAs
     const uint8_t* wA;        // fold-packed 64 -> 32:  12 K-steps x [2][96][8]
     const uint8_t* wB;        // fold-packed 32 -> 64:   6 K-steps x [2][192][8]
@@ -143,6 +143,33 @@ __device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBS
     s.xhi = s.hhi + 1 < p.H ? s.hhi + 1 : p.H - 1;
     g += s.y1 - s.y0;
     return true;
+}
+
+// Which 8-pixel group each of the 16 slots of strip-set ss is.
+//   TS == 0 (GX <= 16): a tile holds TR = 16 / GX image rows, the same row of TR consecutive images; slots past TR * GX idle.
+//   TS  > 0 (GX  > 16): a tile is 16 consecutive groups of one image row, an image row is TS strips advancing by 16 - 2 * OV
+//   groups.  With OV = 1 (kernels whose result needs the neighbouring groups' data: the fused block's hidden halo, the
+//   tail's dx exchange) the first / last slot of a strip only feeds its neighbour — its own result comes from the adjacent
+//   strip — unless it is the image's edge group.
+// `in`: the slot is a group of the image (else its operand rows are zero), `out`: this tile produces the group's result.
+struct RBSlot { int n, gx; bool in, out; };
+template <class Params>
+__device__ __forceinline__ RBSlot rb_slot(const Params& p, int ss, int j) {
+    RBSlot s;
+    if (p.TS == 0) {
+        const int r = j / p.GX;
+        s.n = ss * p.TR + r;
+        s.gx = j - r * p.GX;
+        s.in = r < p.TR && s.n < p.N;
+        s.out = s.in;
+    } else {
+        s.n = ss / p.TS;
+        s.gx = (ss - s.n * p.TS) * (16 - 2 * p.OV) + j;
+        s.in = s.gx < p.GX;
+        s.out = s.in && (p.OV == 0 || ((j > 0 || s.gx == 0) && (j < 15 || s.gx == p.GX - 1)));
+    }
+    if (!s.in) { s.n = p.N; s.gx = 0; }        // as TMA coordinates: outside the tensor, the box is zero-filled
+    return s;
 }
 
 // Per-row issue plan of the folded MMAs: D slots of rows [c_lo, c_lo + nsl) (ring counters) += A * B[slice s0 ..],
@@ -276,8 +303,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int xc = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + (lane & 15);
-            const int n = q / p.GX, gx = q - n * p.GX;
+            const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const int n = sl.n, gx = sl.gx;
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
@@ -397,10 +424,12 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int hbase = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + grp;
-            const int n = q / p.GX, gx = q - n * p.GX;
-            const bool valid = n < p.N && gx * 8 + i < p.W;
-            const bool left = i == 0 && gx > 0, right = i == 7 && gx < p.GX - 1;
+            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const bool valid = sl.in && sl.gx * 8 + i < p.W;
+            // halo pixels go to the neighbouring slot when that is the neighbouring group of the same image row (an idle or
+            // out-of-image slot of a wide tile writes the zeros its neighbour needs as padding)
+            const bool left = i == 0 && grp > 0 && (p.TS > 0 || sl.gx > 0);
+            const bool right = i == 7 && grp < 15 && (p.TS > 0 || sl.gx < p.GX - 1);
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int c = hbase + h - sg.hlo;
@@ -475,9 +504,9 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int slot = 0; uint32_t yph = 0;            // accumulator ring slot / phase
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + grp;
-            const int n = q / p.GX, gx = q - n * p.GX;
-            const bool valid = n < p.N && gx * 8 + i < p.W;
+            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const int n = sl.n, gx = sl.gx;
+            const bool valid = sl.out && gx * 8 + i < p.W;
             // granule index of (n, plane 4*half, row 0, this pixel)
             const size_t px0 = valid ? ((size_t)n * 8 + 4 * half) * plane + (size_t)(gx * 8 + i) : 0;
             const uint4* xg = reinterpret_cast<const uint4*>(p.x) + px0;

@@ -15,6 +15,7 @@ namespace srb {
 
 struct RowconvParams {
     int N, H, W, GX;
+    int TR, TS, OV;           // tile geometry (rb_slot); OV = 0: every group carries its own halo
     int total_rows;
     const uint8_t* w;         // packed [12 K-steps][2 granules][192 rows][8 k] 16-bit
     float bias[64];
@@ -96,8 +97,8 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
         int xc = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + (lane & 15);
-            const int n = q / p.GX, gx = q - n * p.GX;
+            const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const int n = sl.n, gx = sl.gx;
 #pragma unroll 1
             for (int r = sg.hlo; r <= sg.hhi; ++r, ++xc) {          // x rows y0-1 .. y1 (clipped): RBSeg's hidden-row range
                 const int st = xc % G::XSTAGES;
@@ -169,9 +170,9 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
         int c = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + grp;
-            const int n = q / p.GX, gx = q - n * p.GX;
-            const bool valid = n < p.N && gx * 8 + i < p.W;
+            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const int n = sl.n, gx = sl.gx;
+            const bool valid = sl.out && gx * 8 + i < p.W;
             const size_t px0 = valid ? ((size_t)n * 8 + 4 * half) * HW + (size_t)(gx * 8 + i) : 0;
             const uint4* rg = reinterpret_cast<const uint4*>(p.res) + px0;
             uint4* yg = reinterpret_cast<uint4*>(p.y) + px0;

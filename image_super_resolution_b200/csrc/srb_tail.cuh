@@ -17,6 +17,7 @@ namespace srb {
 
 struct TailParams {
     int N, H, W, GX;
+    int TR, TS, OV;           // tile geometry (rb_slot); OV = 1: the dx exchange needs the neighbouring groups' partial sums
     int total_rows;
     const uint8_t* w;         // packed [4 K-steps][2 granules][288 rows = 9 dy-slices x 32][8 k] 16-bit
     float bias[3];
@@ -112,8 +113,8 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
         int xc = 0, g = g_begin;
         TLSeg sg;
         while (tl_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + (lane & 15);
-            const int n = q / p.GX, gx = q - n * p.GX;
+            const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const int n = sl.n, gx = sl.gx;
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
@@ -189,17 +190,17 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + ((uint32_t)(lg * 32) << 16);
         float* const P = s_p + set * (G::PCOLS * G::PLEN);
-        const int gxw = p.GX * 8;                                   // pixels of one image row in the tile
+        const int gxw = p.TS > 0 ? 128 : p.GX * 8;                  // pixels of one image row in the tile
         const int pidx = (L / gxw) * (gxw + 8) + (L % gxw);         // padded position of this lane's pixel (its own column at +4)
         const bool no_st = (p.dbg_skip & 4) != 0;
         pdl_wait();
         int c = 0, g = g_begin;
         TLSeg sg;
         while (tl_next_seg(p, g, g_end, sg)) {
-            const int q = sg.ss * 16 + grp;
-            const int n = q / p.GX, gx = q - n * p.GX;
+            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const int n = sl.n, gx = sl.gx;
             const int x = gx * 8 + i;
-            const bool valid = n < p.N && x < p.W;
+            const bool inside = sl.in && x < p.W, valid = sl.out && x < p.W;
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
                 if ((c & 1) != set) continue;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
                 tmem_ld_wait();
                 tmem_zero32(t_lane + slot * G::NS);
 #pragma unroll
-                for (int k = 0; k < G::PCOLS; ++k) P[k * G::PLEN + pidx + 4] = valid ? __uint_as_float(rr[k]) : 0.f;
+                for (int k = 0; k < G::PCOLS; ++k) P[k * G::PLEN + pidx + 4] = inside ? __uint_as_float(rr[k]) : 0.f;
                 tmem_st_wait();
                 tc_fence_before();
                 named_bar_sync(1 + set, 128);

@@ -372,12 +372,17 @@ class Tail9:
         check(lib().srb_tail9_create(ctx.handle, *[_lib.f32_ptr(a) for a in arrs], self.dtype, C.byref(h)), "srb_tail9_create")
         self.handle = h
 
-    def forward(self, x: torch.Tensor, tanh: bool = True, u8: bool = True) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, tanh: bool = True, u8: bool = True, out: torch.Tensor = None) -> torch.Tensor:
         _require_cuda(x, "x")
         N, planes, H, W, _ = x.shape
         if planes != 8:
             raise RuntimeError("Tail9: x must be [N][8][H][W][8]")
-        y = torch.empty(N, 3, H, W, dtype=torch.uint8 if u8 else torch.float32, device=x.device)
+        dt = torch.uint8 if u8 else torch.float32
+        if out is None:
+            out = torch.empty(N, 3, H, W, dtype=dt, device=x.device)
+        elif out.dtype != dt or tuple(out.shape) != (N, 3, H, W) or not out.is_contiguous() or out.device != x.device:
+            raise RuntimeError("Tail9: out must be a contiguous [N,3,H,W] tensor of the output type on x's device")
+        y = out
         flags = (F_TANH if tanh else 0) | (F_U8OUT if u8 else F_F32OUT)
         check(lib().srb_tail9_fwd(self.ctx.handle, self.handle, x.data_ptr(), y.data_ptr(), flags, N, H, W, _stream_ptr(x.device)),
               "srb_tail9_fwd")

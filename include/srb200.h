@@ -133,8 +133,8 @@ int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uin
 /* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);
-/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12 with the fused residual
- * block / row-fold kernels, 20 when the width does not qualify for it: srb_resblock_supported) */
+/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12: normalise, head, 8 fused
+ * residual blocks, conv1, tail) */
 int srb_model_pt_launches(int H, int W);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
@@ -156,7 +156,8 @@ int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64
 /* Fused residual block  y = x + convB(LeakyReLU(convA(x)))  — ResidualBlock1.forward (utils/models.py:208-209) with
  * m = Sequential(Conv(64,32,3,act=LeakyReLU), Conv(32,64,3,act=False)), BN already folded (model.pt state: net.1.residual.{i}.m.{0,1}).
  * One kernel: the 32-channel hidden activation never leaves shared memory.  wA [32][64][3][3], wB [64][32][3][3] fp32 host.
- * x, y: 8-plane C8 buffers (distinct).  srb_resblock_supported(H, W): ceil(W/8) must be 1, 2, 4, 8 or 16. */
+ * x, y: 8-plane C8 buffers (distinct).  Every H, W > 0 is covered (srb_resblock_supported is kept for callers that asked
+ * before every width was): rows up to 128 px are tiled several images to an M-tile, wider rows as overlapping strips. */
 typedef struct srb_resblock srb_resblock;
 int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* bA, const float* wB, const float* bB, int dtype,
                         srb_resblock** out);
@@ -177,7 +178,7 @@ int srb_pack_conv_pair4(srb_ctx* ctx, const float* w_oihw, const float* bias, in
 /* Row-fold 3x3 conv 64 -> 64: y = act(conv(x) + b) + res — `Conv(64,64,3,act=False)` utils/models.py:690 with the long
  * skip `inputs + self.conv1(residual)` :704 (model.pt: net.1.conv1), the same GEMM mapping as the fused residual block
  * (dy taps folded into N = 192, accumulation over adjacent TMEM rows).  w [64][64][3][3] fp32 host (BN folded),
- * res: 8-plane C8 buffer or NULL, lrelu_slope applied when flags has SRB_F_LRELU.  Shapes as srb_resblock_supported. */
+ * res: 8-plane C8 buffer or NULL, lrelu_slope applied when flags has SRB_F_LRELU.  Any H, W > 0. */
 typedef struct srb_rowconv srb_rowconv;
 int srb_rowconv_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_rowconv** out);
 void srb_rowconv_destroy(srb_rowconv* rc);
@@ -187,7 +188,7 @@ int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* x, const vo
 /* Row-fold 9x9 conv 64 -> 3 + bias (+ tanh) -> NCHW uint8 / fp32: `ConvWithoutBN(64,3,9,act=Tanh)` utils/models.py:691 and
  * `TanhToArrayImage.forward` :448-451 (model.pt: net.1.conv2, net.2) — both tap directions folded into N, accumulation over
  * 9 adjacent TMEM rows.  w [3][64][9][9] fp32 host; x: 8-plane C8 buffer; y: NCHW uint8 (SRB_F_U8OUT) or fp32 (SRB_F_F32OUT);
- * flags: SRB_F_TANH | one of the output formats.  Shapes as srb_resblock_supported. */
+ * flags: SRB_F_TANH | one of the output formats.  Any H, W > 0. */
 typedef struct srb_tail9 srb_tail9;
 int srb_tail9_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_tail9** out);
 void srb_tail9_destroy(srb_tail9* t);

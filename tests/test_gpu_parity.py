@@ -290,6 +290,26 @@ def test_model_pt_tile_independence_large(model, dev):
     assert torch.equal(t, whole[:, :, y0:y1, x0:x1])
 
 
+@pytest.mark.parametrize("shape", [(1, 3, 90, 300), (2, 3, 33, 56), (1, 3, 20, 1000)])
+def test_model_pt_rowfold_kernels_vs_tiled_kernels_and_oracle(model, dev, shape):
+    """Widths that tile the row-fold kernels with idle slots / overlapping strips: the forward agrees with the fp32 oracle
+    (<= 2 LSB) and with the library's own layer-by-layer tiled kernels (debug switch 8: <= 1 LSB, >= 97 % identical)."""
+    from oracle import modelpt_oracle as mo
+    g = torch.Generator().manual_seed(shape[2] + shape[3])
+    x = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g)
+    y = model(x.to(dev)).cpu()
+    model._ctx.debug_set(2, 8)
+    try:
+        t = model(x.to(dev)).cpu()
+    finally:
+        model._ctx.debug_set(2, 0)
+    d = (y.int() - t.int()).abs()
+    assert d.max().item() <= 1 and (d == 0).float().mean().item() >= 0.97
+    ref = mo.forward_u8(x)
+    d = (y.int() - ref.int()).abs()
+    assert d.max().item() <= 2 and (d == 0).float().mean().item() >= 0.97
+
+
 def test_l1_loss_kernels(dev, golden_dir):
     from image_super_resolution_b200 import ops
     from oracle import l1_oracle

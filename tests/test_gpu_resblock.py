@@ -61,9 +61,25 @@ def test_resblock_many_rows_per_cta_and_segment_splits(dev):
     _case(dev, 40, 64, 64, seed=3, grid=0)
 
 
-def test_resblock_rejects_unsupported_widths(dev):
+# widths that do not divide a 128-pixel tile (idle slots), and rows wider than a tile (overlapping strips: the result of a
+# strip's edge groups comes from the neighbouring strip), ragged ends included
+ANY_WIDTH = [(2, 9, 56), (3, 7, 24), (1, 7, 96), (2, 6, 100), (1, 6, 136), (2, 5, 250), (1, 4, 360), (1, 3, 129), (2, 4, 240)]
+
+
+@pytest.mark.parametrize("N,H,W", ANY_WIDTH)
+def test_resblock_any_width(dev, N, H, W):
+    _case(dev, N, H, W, seed=N * 100 + H + W)
+
+
+def test_resblock_wide_rows_long_marches(dev):
+    _case(dev, 1, 70, 300, seed=11, grid=3)
+    _case(dev, 2, 40, 200, seed=12, grid=0)
+
+
+def test_resblock_supported_every_width(dev):
     from image_super_resolution_b200 import ops
-    assert ops.ResBlock.supported(64, 64) and ops.ResBlock.supported(7, 128) and not ops.ResBlock.supported(64, 96)
+    assert ops.ResBlock.supported(64, 64) and ops.ResBlock.supported(7, 128) and ops.ResBlock.supported(64, 96)
+    assert ops.ResBlock.supported(1080, 1920) and not ops.ResBlock.supported(0, 64)
 
 
 # ---- row-fold single conv (srb_rowconv.cuh): conv1 + long skip of the model.pt graph ----
@@ -104,6 +120,11 @@ def test_rowconv_matches_fp32_reference(dev, N, H, W):
     _rowconv_case(dev, N, H, W, seed=N * 100 + H)
 
 
+@pytest.mark.parametrize("N,H,W", ANY_WIDTH)
+def test_rowconv_any_width(dev, N, H, W):
+    _rowconv_case(dev, N, H, W, seed=N * 100 + H + W)
+
+
 def test_rowconv_variants_and_segment_splits(dev):
     _rowconv_case(dev, 6, 64, 64, seed=1, grid=2)
     _rowconv_case(dev, 6, 64, 64, seed=2, grid=0)
@@ -128,8 +149,8 @@ def _tail_case(dev, N, H, W, seed=0, grid=0):
     if grid:
         ctx.debug_set(1, grid)
     try:
-        yf = t.forward(xc, tanh=False, u8=False)
-        yu = t.forward(xc, tanh=True, u8=True)
+        yf = t.forward(xc, tanh=False, u8=False, out=torch.full((N, 3, H, W), float("nan"), device=dev))
+        yu = t.forward(xc, tanh=True, u8=True, out=torch.full((N, 3, H, W), 77, dtype=torch.uint8, device=dev))
         torch.cuda.synchronize()
         ctx.check_device()
     finally:
@@ -144,6 +165,16 @@ def _tail_case(dev, N, H, W, seed=0, grid=0):
 @pytest.mark.parametrize("N,H,W", [(2, 12, 64), (3, 20, 64), (1, 5, 8), (5, 9, 16), (2, 33, 128), (3, 17, 60), (2, 1, 64), (7, 2, 28), (1, 3, 32)])
 def test_tail9_matches_fp32_reference(dev, N, H, W):
     _tail_case(dev, N, H, W, seed=N * 100 + H)
+
+
+@pytest.mark.parametrize("N,H,W", ANY_WIDTH)
+def test_tail9_any_width(dev, N, H, W):
+    _tail_case(dev, N, H, W, seed=N * 100 + H + W)
+
+
+def test_tail9_wide_rows_long_marches(dev):
+    _tail_case(dev, 1, 70, 300, seed=11, grid=3)
+    _tail_case(dev, 2, 40, 200, seed=12, grid=0)
 
 
 def test_tail9_long_marches_and_segment_splits(dev):
