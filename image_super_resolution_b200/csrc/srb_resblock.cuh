@@ -35,7 +35,7 @@ struct ResblockParams {
     const void* x;            // [N][8][H][W][8]
     void* y;                  // [N][8][H][W][8]
     float slope;
-    long long* dbg_trace;     // optional clock stamps of CTA 0: [64 rows][16]
+    long long* dbg_trace;     // optional clock stamps of CTA 0: [32 rows][32]
     int dbg_skip;             // bottleneck probes: 1 = no TMA loads, 2 = no MMAs (16 = no convA, 32 = no convB MMAs), 4 = no global I/O in the output epilogue
 };
 
@@ -125,7 +125,7 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
 }
 
 __device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k) {
-    if (p.dbg_trace != nullptr && blockIdx.x == 0 && row < 64) p.dbg_trace[row * 16 + k] = clock64();
+    if (p.dbg_trace != nullptr && blockIdx.x == 0 && row < 32) p.dbg_trace[row * 32 + k] = clock64();
 }
 
 // a segment: output rows [y0, y1) of strip-set ss, with the hidden / input row ranges it needs (clipped to the image)
@@ -309,12 +309,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 19);         // x stage free
                 if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)
                     tma_load_4d(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, &xfull[st], (gx * 8 - 1) * 4, r, 0, n);
                 __syncwarp();
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 20);         // x row requested
             }
         }
     } else if (warp == 1) {
@@ -334,6 +336,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 mbar_wait<RB_CTRL>(&xfull[xst], xph, 33);
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 21);         // x row arrived
                 const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
                 const int a_lo = hbase + lo - sg.hlo, a_n = hi - lo + 1, a_s0 = lo - (r - 1);
                 for (; h_acq < a_lo + a_n; ++h_acq) {
@@ -374,12 +377,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int hs = 0; uint32_t hph = 0;                  // hidden smem slot / phase of the next hidden row
         int yslot0 = 0;                                // ring slot of the segment's first output row
         int acq_slot = 0; uint32_t acq_ph = 1;
-        int ybase = 0, y_acq = 0, g = g_begin;
+        int ybase = 0, ybase_h = 0, y_acq = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
+                const int hc = ybase_h + h - sg.hlo;               // running hidden-row counter (trace only)
                 mbar_wait<RB_CTRL>(&hsfull[hs], hph, 35);
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 16);         // hidden row in shared memory
                 const int lo = h - 1 > sg.y0 ? h - 1 : sg.y0, hi = h + 1 < sg.y1 - 1 ? h + 1 : sg.y1 - 1;
                 const int b_lo = ybase + lo - sg.y0, b_n = hi - lo + 1, b_s0 = lo - (h - 1);
                 for (; y_acq < b_lo + b_n; ++y_acq) {
@@ -388,6 +393,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 }
                 const int slot_lo = (yslot0 + (lo - sg.y0)) % G::RY;
                 tc_fence_after();
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 17);         // output accumulator rows acquired
                 if (elect_one()) {
                     const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
                     const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, (p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
@@ -403,8 +409,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     if (h == sg.hhi && h <= sg.y1 - 1) umma_commit(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
                 }
                 __syncwarp();
+                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 18);         // convB MMAs + commits issued
                 if (++hs == G::HSLOTS) { hs = 0; hph ^= 1; }
             }
+            ybase_h += sg.hhi - sg.hlo + 1;
             const int ny = sg.y1 - sg.y0;
             ybase += ny;
             yslot0 = (yslot0 + ny) % G::RY;
