@@ -444,7 +444,6 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     int out_planes = (flags & SRB_F_PIXSHUF2) ? w->cout / 32 : (w->cout + 7) / 8;
     if ((flags & SRB_F_PIXSHUF2) && (w->cout % 32)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PixelShuffle(2) needs cout %% 32 == 0");
     if ((flags & SRB_F_PIXSHUF2) && (flags & SRB_F_RESIDUAL)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PIXSHUF2 with residual unsupported");
-    if ((flags & SRB_F_RESIDUAL) && w->nout > 64) return fail(SRB_ENOSUP, "srb_conv2d_fwd: residual epilogue needs cout <= 64");
     const int res_need = partial_res ? a->res_nplanes : out_planes;
     if ((flags & SRB_F_RESIDUAL) && (res_c8_off < 0 || res_c8_off + res_need > res_c8_total)) return fail(SRB_EINVAL, "srb_conv2d_fwd: residual plane slice out of range");
     if (y_c8_off < 0 || y_c8_off + out_planes > y_c8_total) return fail(SRB_EINVAL, "srb_conv2d_fwd: output plane slice out of range");
@@ -461,12 +460,16 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
 #define SRB_STD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
-    const bool bwd = (flags & SRB_F_MASK) || partial_res;
+    // wide outputs (96..160 channels) exist only as whole-conv data gradients of the dense blocks (32 -> Cin, 64 -> 2 x 96)
+    const bool bwd = (flags & SRB_F_MASK) || partial_res || (w->nout > 64 && !w->kblocks && !(flags & SRB_F_PIXSHUF2));
     if (bwd) {   // data-gradient launches of the training step (srb_conv_args: mask / partial residual)
 #define SRB_BWD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true, false, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false, false, true>(ctx, w, x, x_c8_total, p, st); }
         SRB_BWD(4, 64, 4) SRB_BWD(8, 64, 3) SRB_BWD(4, 32, 4)
+        SRB_BWD(4, 96, 2) SRB_BWD(4, 128, 2) SRB_BWD(4, 160, 1)
+        // 64 -> 96: the 108 KB filter leaves no room for a TMA residual ring; residual granules come through plain loads
+        if (!w->kblocks && w->c8in == 8 && w->nout == 96) return launch_conv<8, 96, 3, 3, MODE_STD, 2, false, false, true>(ctx, w, x, x_c8_total, p, st);
 #undef SRB_BWD
         return fail(SRB_ENOSUP, "srb_conv2d: no backward-epilogue kernel for cin=%d cout=%d", w->cin, w->cout);
     }

@@ -201,7 +201,8 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
         mbar_init(&tfull[0], 1); mbar_init(&tfull[1], 1);
         mbar_init(&tempty[0], 4 * EPI_SETS); mbar_init(&tempty[1], 4 * EPI_SETS);
         mbar_init(wbar, 1);
-        for (int s = 0; s < G::RSLOTS; ++s) { mbar_init(&rfull[s], 1); mbar_init(&rempty[s], 4); }
+        // NT == 1: both epilogue sets work on the same M-tile (alternate 32-column chunks) and both release its residual slot
+        for (int s = 0; s < G::RSLOTS; ++s) { mbar_init(&rfull[s], 1); mbar_init(&rempty[s], NT == 1 ? 4 * EPI_SETS : 4); }
         fence_mbar_init();
         tma_prefetch_desc(&tmap);
         if (RES) tma_prefetch_desc(&tmap_res);
@@ -396,7 +397,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
             if constexpr (MODE != MODE_DXN) {
 #pragma unroll 1
                 for (int t = 0; t < NT; ++t) {
-                    if ((t % EPI_SETS) != eset) {
+                    if (NT > 1 && (t % EPI_SETS) != eset) {
                         // not this set's tile — but still observe its residual fill: parity waits are only
                         // sound if no warp ever falls two phases behind a ring slot
                         if constexpr (RES) {
@@ -419,6 +420,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                     }
 #pragma unroll 1
                     for (int c0 = 0; c0 < NOUT; c0 += 32) {
+                        if (NT == 1 && ((c0 >> 5) % EPI_SETS) != eset) continue;   // one M-tile per step: the sets split its columns
                         uint32_t rr[32];
                         tmem_ld32(t_addr0 + t * NOUT + c0, rr);
                         tmem_ld_wait();

@@ -24,8 +24,10 @@ from ._lib import Context
 
 
 def _chunks(c: int) -> list[int]:
-    """Output-channel chunks (64, then a 32 remainder) of a data-gradient conv with c output channels."""
-    return [64] * (c // 64) + ([32] if c % 64 else [])
+    """Output-channel chunks of a data-gradient conv with c output channels: one launch up to 160 channels (N = 96 .. 160
+    MMAs run at the full tensor rate, N <= 64 ones at 40-67 %), two 96-channel halves for the 192-channel gradient of an
+    RDB's last conv (its 64 -> 192 filter does not fit in shared memory in one piece)."""
+    return [c] if c <= 160 else [96] * (c // 96) + ([c % 96] if c % 96 else [])
 
 
 def _slope_of(act) -> float:
@@ -54,7 +56,7 @@ class TrainPlan:
             for rrdb in net.residual:
                 for rdb in rrdb.net:
                     fwd = [mk(32, 64 + 32 * i, 3) for i in range(4)] + [mk(64, 192, 3)]
-                    dg = [[mk(co, 32, 3) for co in _chunks(64 + 32 * i)] for i in range(4)] + [[mk(64, 64, 3) for _ in range(3)]]
+                    dg = [[mk(co, 32, 3) for co in _chunks(64 + 32 * i)] for i in range(4)] + [[mk(co, 64, 3) for co in _chunks(192)]]
                     self.rdbs.append((rrdb, rdb, fwd, dg))
             self.f_conv1, self.d_conv1 = mk(64, 64, 3), mk(64, 64, 3)
             self.f_scaler = [[mk(64, 64, 3) for _ in range(4)] for _ in net.scaler]
@@ -290,13 +292,16 @@ class TrainPlan:
             sl = [_slope_of(getattr(rdb, f"conv{i}").act) for i in range(4)]
             # final conv 192 -> 64 (no activation): out = s_out*conv(cat) + s_res*rdb_in
             self._wb(rdb.conv, D, 24, 0, 192, gsrc, gsrc_planes, 0, 64, N, H, W, scale=s_out)
-            for c in range(3):
+            o = 0
+            for pk in dg[4]:
+                p0, pl = o // 8, pk.cout // 8
                 kw = {}
-                if c == 0:
-                    kw = dict(residual=gsrc, res_planes=gsrc_planes, res_off=0, res_scale=s_res)
-                if c == 2:
-                    kw = dict(mask=D, mask_planes=24, mask_off=16, mask_p0=4, mask_p1=8, mask_slope=sl[3])
-                cv(dg[4][c], gsrc, gsrc_planes, 0, G, 24, 8 * c, N, H, W, out_scale=s_out, **kw)
+                if p0 == 0:                                 # + s_res * (gradient of the RDB output) on the rdb_in planes
+                    kw = dict(residual=gsrc, res_planes=gsrc_planes, res_off=0, res_nplanes=8, res_scale=s_res)
+                if p0 + pl > 20:                            # planes 20..23 = o_3: final after this launch
+                    kw.update(mask=D, mask_planes=24, mask_off=p0, mask_p0=20 - p0, mask_p1=24 - p0, mask_slope=sl[3])
+                cv(pk, gsrc, gsrc_planes, 0, G, 24, p0, N, H, W, out_scale=s_out, **kw)
+                o += pk.cout
             # conv3..conv0: dY = masked slice of G, accumulate the data gradient into planes below it
             for i in range(3, -1, -1):
                 cin = 64 + 32 * i

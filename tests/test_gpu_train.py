@@ -96,28 +96,68 @@ def test_data_gradient_is_transposed_conv(ctx, dev, cout, cin, k):
     assert err <= 8e-3 * ref.abs().max().item() + 1e-3, err
 
 
-def test_dgrad_accumulates_in_place_with_mask(ctx, dev):
-    """G[0:64] += dgrad ; planes 4..7 of the slice are multiplied by LeakyReLU'(saved activation) afterwards."""
+@pytest.mark.parametrize("cin", [64, 96, 128, 160])
+def test_dgrad_accumulates_in_place_with_mask(ctx, dev, cin):
+    """G[0:cin] += dgrad (one launch for the whole 32 -> cin transposed conv); the last four planes of the slice are
+    multiplied by LeakyReLU'(saved activation) afterwards."""
     from image_super_resolution_b200 import ops
     g = torch.Generator().manual_seed(3)
-    N, H, W = 1, 18, 26
-    w = _q(torch.randn(32, 64, 3, 3, generator=g) / 24)
+    N, H, W = 2, 18, 26
+    w = _q(torch.randn(32, cin, 3, 3, generator=g) / 24)
     dy = _q(torch.randn(N, 32, H, W, generator=g))
-    g0 = _q(torch.randn(N, 64, H, W, generator=g))
-    act = _q(torch.randn(N, 64, H, W, generator=g))
-    x = torch.zeros(N, 64, H, W, requires_grad=True)
+    g0 = _q(torch.randn(N, cin, H, W, generator=g))
+    act = _q(torch.randn(N, cin, H, W, generator=g))
+    x = torch.zeros(N, cin, H, W, requires_grad=True)
     F.conv2d(x, w, padding=1).backward(dy)
     ref = x.grad + g0
-    ref[:, 32:] = ref[:, 32:] * torch.where(act[:, 32:] > 0, 1.0, 0.01)
-    Gb = torch.zeros(N, 12, H, W, 8, dtype=torch.bfloat16, device=dev)
-    ops.nchw_to_c8(g0.to(dev), out=Gb, planes=12, off=0, dtype="bf16")
-    ops.nchw_to_c8(dy.to(dev), out=Gb, planes=12, off=8, dtype="bf16")
+    ref[:, cin - 32:] = ref[:, cin - 32:] * torch.where(act[:, cin - 32:] > 0, 1.0, 0.01)
+    P = cin // 8
+    Gb = torch.zeros(N, P + 4, H, W, 8, dtype=torch.bfloat16, device=dev)
+    ops.nchw_to_c8(g0.to(dev), out=Gb, planes=P + 4, off=0, dtype="bf16")
+    ops.nchw_to_c8(dy.to(dev), out=Gb, planes=P + 4, off=P, dtype="bf16")
     A = ops.nchw_to_c8(act.to(dev), dtype="bf16")
-    pk = ops.DeviceConv(ctx, 64, 32, 3, "bf16")
+    pk = ops.DeviceConv(ctx, cin, 32, 3, "bf16")
     pk.fill(w.to(dev), transpose=True)
-    ops.conv2d_ex(pk, Gb, 12, 8, Gb, 12, 0, N, H, W, residual=Gb, res_planes=12, res_off=0, mask=A, mask_planes=8, mask_off=0,
-                  mask_p0=4, mask_p1=8, mask_slope=0.01)
-    out = ops.c8_to_nchw(Gb, 64).cpu()
+    ops.conv2d_ex(pk, Gb, P + 4, P, Gb, P + 4, 0, N, H, W, residual=Gb, res_planes=P + 4, res_off=0, mask=A, mask_planes=P,
+                  mask_off=0, mask_p0=P - 4, mask_p1=P, mask_slope=0.01)
+    out = ops.c8_to_nchw(Gb, cin).cpu()
+    err = (out - ref).abs().max().item()
+    assert err <= 1e-2 * ref.abs().max().item() + 1e-3, err
+    assert torch.equal(ops.c8_to_nchw(Gb, 32, off=P).cpu(), dy)      # the dY planes are left alone
+
+
+def test_dgrad_wide_halves_partial_residual(ctx, dev):
+    """The 64 -> 192 gradient of an RDB's last conv as two 96-channel launches: out_scale, the residual on the first
+    8 planes only (res_nplanes), the mask on planes 20..23."""
+    from image_super_resolution_b200 import ops
+    from image_super_resolution_b200.training import _chunks
+    g = torch.Generator().manual_seed(5)
+    N, H, W = 2, 21, 30
+    w = _q(torch.randn(64, 192, 3, 3, generator=g) / 40)
+    dy = _q(torch.randn(N, 64, H, W, generator=g))
+    act = _q(torch.randn(N, 192, H, W, generator=g))
+    x = torch.zeros(N, 192, H, W, requires_grad=True)
+    F.conv2d(x, w, padding=1).backward(dy)
+    ref = 0.2 * x.grad
+    ref[:, :64] += 0.5 * dy
+    ref[:, 160:] = ref[:, 160:] * torch.where(act[:, 160:] > 0, 1.0, 0.01)
+    dyc = ops.nchw_to_c8(dy.to(dev), dtype="bf16")
+    A = ops.nchw_to_c8(act.to(dev), dtype="bf16")
+    G = torch.zeros(N, 24, H, W, 8, dtype=torch.bfloat16, device=dev)
+    assert _chunks(192) == [96, 96]
+    o = 0
+    for co in _chunks(192):
+        pk = ops.DeviceConv(ctx, co, 64, 3, "bf16")
+        pk.fill(w.to(dev), transpose=True, o_off=o)
+        p0, pl = o // 8, co // 8
+        kw = {}
+        if p0 == 0:
+            kw = dict(residual=dyc, res_planes=8, res_off=0, res_nplanes=8, res_scale=0.5)
+        if p0 + pl > 20:
+            kw.update(mask=A, mask_planes=24, mask_off=p0, mask_p0=20 - p0, mask_p1=24 - p0, mask_slope=0.01)
+        ops.conv2d_ex(pk, dyc, 8, 0, G, 24, p0, N, H, W, out_scale=0.2, **kw)
+        o += co
+    out = ops.c8_to_nchw(G, 192).cpu()
     err = (out - ref).abs().max().item()
     assert err <= 1e-2 * ref.abs().max().item() + 1e-3, err
 
