@@ -8,6 +8,7 @@
 #include <string.h>
 #include <math.h>
 #include <vector>
+#include <algorithm>
 #include <map>
 #include <tuple>
 
@@ -857,6 +858,49 @@ static int encode_c8_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N,
     return SRB_OK;
 }
 
+// dY tensor map with the dimensions ordered (pixel, plane, row, image): a box lands in shared memory as [row][plane][px],
+// which makes the (row shift, plane) channel groups of the folded weight-gradient GEMM equidistant (srb_wgrad.cuh)
+static int encode_dy_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N, int H, int W, int planes) {
+    using G = WgradGeom;
+    cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)planes, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t gstr[3] = {(cuuint64_t)W * H * 16, (cuuint64_t)W * 16, (cuuint64_t)W * H * 16 * planes};
+    cuuint32_t box[4] = {(cuuint32_t)G::TW * 4, (cuuint32_t)G::DYPLANES, (cuuint32_t)G::DYH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(base), gdim, gstr, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled (dY, plane-minor rows) failed: %d", (int)r);
+    return SRB_OK;
+}
+
+// input-channel blocks of a weight-gradient GEMM: N = block width, at most 160 (three fp32 accumulators in 512 TMEM columns)
+static void wgrad_blocks(int cin, int* nblk, int* blk) {
+    *nblk = (cin + 159) / 160;
+    *blk = round_up((cin + *nblk - 1) / *nblk, 16);
+}
+
+// units of one conv appended to `units`; tm = index of its tensor-map pair
+static int wgrad_units(const srb_grad_job& q, int tm, std::vector<WgradUnit>& units) {
+    using G = WgradGeom;
+    int nblk, blk;
+    wgrad_blocks(q.cin, &nblk, &blk);
+    WgradUnit u{};
+    u.tm = tm; u.N = q.N; u.H = q.H; u.W = q.W;
+    u.tiles_x = (q.W + G::TW - 1) / G::TW; u.tiles_y = (q.H + G::TH - 1) / G::TH;
+    long long nt = (long long)u.tiles_x * u.tiles_y * q.N;
+    if (nt <= 0 || nt > 0x7fffffffLL) return fail(SRB_EINVAL, "weight gradient: %lld tiles", nt);
+    u.num_tiles = (int)nt; u.cin_total = q.cin; u.scale = q.scale; u.dw = q.dw; u.xplanes = blk / 8;
+    for (int ci0 = 0; ci0 < q.cin; ci0 += blk)
+        for (int co0 = 0; co0 < q.cout; co0 += 32) {
+            u.cin0 = ci0; u.cout0 = co0;
+            u.cin_blk = q.cin - ci0 < blk ? q.cin - ci0 : blk;
+            u.cout_blk = q.cout - co0 < 32 ? q.cout - co0 : 32;
+            u.x_c8_off = q.x_c8_off + ci0 / 8; u.dy_c8_off = q.dy_c8_off + co0 / 8;
+            units.push_back(u);
+        }
+    return SRB_OK;
+}
+
 extern "C" int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy,
                                 int dy_c8_total, int dy_c8_off, int cout, float* dw_oihw, float scale, int k, int dtype,
                                 int N, int H, int W, srb_stream_t stream) {
@@ -866,35 +910,32 @@ extern "C" int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int
     if (((uintptr_t)x & 15) || ((uintptr_t)dy & 15)) return fail(SRB_EINVAL, "srb_conv2d_wgrad: buffers must be 16-byte aligned");
     if (x_c8_off < 0 || x_c8_off + cin / 8 > x_c8_total || dy_c8_off < 0 || dy_c8_off + cout / 8 > dy_c8_total)
         return fail(SRB_EINVAL, "srb_conv2d_wgrad: plane slice out of range");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv2d_wgrad: empty shape");
     using G = WgradGeom;
-    CUtensorMap tx, tdy;
+    srb_grad_job q{};
+    q.x = x; q.x_c8_total = x_c8_total; q.x_c8_off = x_c8_off; q.cin = cin; q.dy = dy; q.dy_c8_total = dy_c8_total;
+    q.dy_c8_off = dy_c8_off; q.cout = cout; q.dw = dw_oihw; q.scale = scale; q.N = N; q.H = H; q.W = W;
+    std::vector<WgradUnit> units;
     int rc;
-    if ((rc = encode_c8_map(ctx, &tx, x, N, H, W, x_c8_total, G::XW, G::XH, G::XPLANES))) return rc;
-    if ((rc = encode_c8_map(ctx, &tdy, dy, N, H, W, dy_c8_total, G::TW, G::TH, G::DYPLANES))) return rc;
-    WgradParams p{};
-    p.N = N; p.H = H; p.W = W;
-    p.tiles_x = (W + G::TW - 1) / G::TW; p.tiles_y = (H + G::TH - 1) / G::TH;
-    long long nt = (long long)p.tiles_x * p.tiles_y * N;
-    if (nt <= 0 || nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_conv2d_wgrad: %lld tiles", nt);
-    p.num_tiles = (int)nt;
-    p.cin_total = cin; p.dw = dw_oihw; p.scale = scale; p.dbg_swap = ctx->dbg_swap;
-    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    if ((rc = wgrad_units(q, 0, units))) return rc;
+    CUtensorMap tx, tdy;
+    if ((rc = encode_c8_map(ctx, &tx, x, N, H, W, x_c8_total, G::XW, G::TH, units[0].xplanes))) return rc;
+    if ((rc = encode_dy_map(ctx, &tdy, dy, N, H, W, dy_c8_total))) return rc;
+    // one launch per unit, its pixel tiles spread over the SMs left per unit (split-K with red.global.add)
+    int grid = ctx->num_sms / (int)units.size();
+    if (grid < 1) grid = 1;
+    if (grid > units[0].num_tiles) grid = units[0].num_tiles;
     cudaStream_t st = (cudaStream_t)stream;
-    for (int ci0 = 0; ci0 < cin; ci0 += 128)
-        for (int co0 = 0; co0 < cout; co0 += 32) {
-            p.cin0 = ci0; p.cout0 = co0;
-            p.cin_blk = cin - ci0 < 128 ? cin - ci0 : 128;
-            p.cout_blk = cout - co0 < 32 ? cout - co0 : 32;
-            p.x_c8_off = x_c8_off + ci0 / 8; p.dy_c8_off = dy_c8_off + co0 / 8;
-            if (dtype == SRB_DT_BF16) {
-                CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-                wgrad_tc_kernel<true><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, p);
-            } else {
-                CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-                wgrad_tc_kernel<false><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, p);
-            }
-            CUDA_TRY(cudaGetLastError());
+    for (const WgradUnit& u : units) {
+        if (dtype == SRB_DT_BF16) {
+            CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+            wgrad_tc_kernel<true><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, ctx->dbg_skip);
+        } else {
+            CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+            wgrad_tc_kernel<false><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, ctx->dbg_skip);
         }
+        CUDA_TRY(cudaGetLastError());
+    }
     return SRB_OK;
 }
 
@@ -1032,25 +1073,13 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
             if (q.cin % 8 || q.cout % 8) return fail(SRB_ENOSUP, "srb_grad_batch_create: job %d: cin=%d cout=%d must be multiples of 8", j, q.cin, q.cout);
             if (q.x_c8_off < 0 || q.x_c8_off + q.cin / 8 > q.x_c8_total) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: x slice out of range", j);
             CUtensorMap tx, tdy;
-            int rc;
-            if ((rc = encode_c8_map(ctx, &tx, q.x, q.N, q.H, q.W, q.x_c8_total, G::XW, G::XH, G::XPLANES))) return rc;
-            if ((rc = encode_c8_map(ctx, &tdy, q.dy, q.N, q.H, q.W, q.dy_c8_total, G::TW, G::TH, G::DYPLANES))) return rc;
+            int rc, nblk, blk;
+            wgrad_blocks(q.cin, &nblk, &blk);
+            if ((rc = encode_c8_map(ctx, &tx, q.x, q.N, q.H, q.W, q.x_c8_total, G::XW, G::TH, blk / 8))) return rc;
+            if ((rc = encode_dy_map(ctx, &tdy, q.dy, q.N, q.H, q.W, q.dy_c8_total))) return rc;
             const int tm = (int)tmaps.size() / 2;
             tmaps.push_back(tx); tmaps.push_back(tdy);
-            WgradUnit u{};
-            u.tm = tm; u.N = q.N; u.H = q.H; u.W = q.W;
-            u.tiles_x = (q.W + G::TW - 1) / G::TW; u.tiles_y = (q.H + G::TH - 1) / G::TH;
-            long long nt = (long long)u.tiles_x * u.tiles_y * q.N;
-            if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_grad_batch_create: job %d: %lld tiles", j, nt);
-            u.num_tiles = (int)nt; u.cin_total = q.cin; u.scale = q.scale; u.dw = q.dw;
-            for (int ci0 = 0; ci0 < q.cin; ci0 += 128)
-                for (int co0 = 0; co0 < q.cout; co0 += 32) {
-                    u.cin0 = ci0; u.cout0 = co0;
-                    u.cin_blk = q.cin - ci0 < 128 ? q.cin - ci0 : 128;
-                    u.cout_blk = q.cout - co0 < 32 ? q.cout - co0 : 32;
-                    u.x_c8_off = q.x_c8_off + ci0 / 8; u.dy_c8_off = q.dy_c8_off + co0 / 8;
-                    units.push_back(u);
-                }
+            if ((rc = wgrad_units(q, tm, units))) return rc;
         }
         if (q.db)
             for (int pl = 0; pl < dyp; ++pl) {
@@ -1061,6 +1090,9 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
                 bias.push_back(bu);
             }
     }
+    // longest units first: the block scheduler hands CTAs to SMs in index order as they free up
+    auto unit_cost = [](const WgradUnit& u) { const int n = u.xplanes * 8; return (long long)u.num_tiles * (n / 2 > 32 + n / 4 ? n / 2 : 32 + n / 4); };
+    std::stable_sort(units.begin(), units.end(), [&](const WgradUnit& a, const WgradUnit& c) { return unit_cost(a) > unit_cost(c); });
     srb_grad_batch* b = new srb_grad_batch();
     b->dtype = dtype; b->nunits = (int)units.size(); b->nbias = (int)bias.size();
     cudaSetDevice(ctx->device);
@@ -1086,10 +1118,10 @@ extern "C" int srb_grad_batch_run(srb_ctx* ctx, srb_grad_batch* b, int splitk, s
     if (b->nunits) {
         if (b->dtype == SRB_DT_BF16) {
             CUDA_TRY(cudaFuncSetAttribute(wgrad_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-            wgrad_batch_kernel<true><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk);
+            wgrad_batch_kernel<true><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk, ctx->dbg_skip);
         } else {
             CUDA_TRY(cudaFuncSetAttribute(wgrad_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-            wgrad_batch_kernel<false><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk);
+            wgrad_batch_kernel<false><<<b->nunits * splitk, 256, G::SMEM_BYTES, st>>>(b->d_tmaps, b->d_units, splitk, ctx->dbg_skip);
         }
         CUDA_TRY(cudaGetLastError());
     }
