@@ -458,27 +458,43 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
     }
     // the TMA residual ring needs the residual on every output plane of a full-width (cout == NOUT) conv
-#define SRB_STD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
-        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); \
+    // Small problems (a training batch: 16 x 64 x 64 px = 512 M-tiles for 148 SMs): with NT = 4 a CTA gets ONE super-tile and
+    // its load, MMAs and epilogue run back to back; two-tile super-tiles give every CTA two pipeline steps that overlap.
+    const long long mtiles = (long long)((W + 7) / 8) * ((H + 15) / 16) * N;
+    const bool small = mtiles < (long long)ctx->num_sms * 6 && !(ctx->dbg_skip & 65536);   // (debug bit 65536: always the large-problem tiling)
+#define SRB_STD(C8, NO, NTT, NTS) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
+        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) { \
+            if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, true>(ctx, w, x, x_c8_total, p, st); \
+            return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true>(ctx, w, x, x_c8_total, p, st); } \
+        if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, false>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false>(ctx, w, x, x_c8_total, p, st); }
-    // wide outputs (96..160 channels) exist only as whole-conv data gradients of the dense blocks (32 -> Cin, 64 -> 2 x 96)
     const bool bwd = (flags & SRB_F_MASK) || partial_res || (w->nout > 64 && !w->kblocks && !(flags & SRB_F_PIXSHUF2));
     if (bwd) {   // data-gradient launches of the training step (srb_conv_args: mask / partial residual)
-#define SRB_BWD(C8, NO, NTT) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
-        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true, false, true>(ctx, w, x, x_c8_total, p, st); \
+#define SRB_BWD(C8, NO, NTT, NTS) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
+        if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) { \
+            if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, true, false, true>(ctx, w, x, x_c8_total, p, st); \
+            return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true, false, true>(ctx, w, x, x_c8_total, p, st); } \
+        if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, false, false, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false, false, true>(ctx, w, x, x_c8_total, p, st); }
-        SRB_BWD(4, 64, 4) SRB_BWD(8, 64, 3) SRB_BWD(4, 32, 4)
-        SRB_BWD(4, 96, 2) SRB_BWD(4, 128, 2) SRB_BWD(4, 160, 1)
+        SRB_BWD(4, 64, 4, 2) SRB_BWD(8, 64, 3, 2) SRB_BWD(4, 32, 4, 2)
+        SRB_BWD(4, 96, 2, 2) SRB_BWD(4, 128, 2, 2) SRB_BWD(4, 160, 1, 1)
         // 64 -> 96: the 108 KB filter leaves no room for a TMA residual ring; residual granules come through plain loads
         if (!w->kblocks && w->c8in == 8 && w->nout == 96) return launch_conv<8, 96, 3, 3, MODE_STD, 2, false, false, true>(ctx, w, x, x_c8_total, p, st);
 #undef SRB_BWD
         return fail(SRB_ENOSUP, "srb_conv2d: no backward-epilogue kernel for cin=%d cout=%d", w->cin, w->cout);
     }
-    SRB_STD(8, 32, 4) SRB_STD(4, 64, 4) SRB_STD(8, 64, 3) SRB_STD(4, 32, 4)
+    SRB_STD(8, 32, 4, 2) SRB_STD(4, 64, 4, 2) SRB_STD(8, 64, 3, 2) SRB_STD(4, 32, 4, 2)
     if (w->kblocks) {   // dense-block convs (Cin = 96..192): K blocks of 32 channels, filter streamed with the halo
-        if (w->nout == 32) return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
+        if (w->nout == 32) {
+            if (small) return launch_conv<4, 32, 3, 3, MODE_STD, 2, false, true>(ctx, w, x, x_c8_total, p, st);
+            return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
+        }
         if (w->nout == 64) {
-            if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == 64) return launch_conv<4, 64, 3, 3, MODE_STD, 4, true, true>(ctx, w, x, x_c8_total, p, st);
+            if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == 64) {
+                if (small) return launch_conv<4, 64, 3, 3, MODE_STD, 2, true, true>(ctx, w, x, x_c8_total, p, st);
+                return launch_conv<4, 64, 3, 3, MODE_STD, 4, true, true>(ctx, w, x, x_c8_total, p, st);
+            }
+            if (small) return launch_conv<4, 64, 3, 3, MODE_STD, 2, false, true>(ctx, w, x, x_c8_total, p, st);
             return launch_conv<4, 64, 3, 3, MODE_STD, 4, false, true>(ctx, w, x, x_c8_total, p, st);
         }
     }
@@ -896,6 +912,7 @@ static int wgrad_units(const srb_grad_job& q, int tm, std::vector<WgradUnit>& un
             u.cin_blk = q.cin - ci0 < blk ? q.cin - ci0 : blk;
             u.cout_blk = q.cout - co0 < 32 ? q.cout - co0 : 32;
             u.x_c8_off = q.x_c8_off + ci0 / 8; u.dy_c8_off = q.dy_c8_off + co0 / 8;
+            u.db = (q.db && ci0 == 0) ? q.db + co0 : nullptr;     // the bias gradient rides on the first input-channel block
             units.push_back(u);
         }
     return SRB_OK;
@@ -914,7 +931,7 @@ extern "C" int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int
     using G = WgradGeom;
     srb_grad_job q{};
     q.x = x; q.x_c8_total = x_c8_total; q.x_c8_off = x_c8_off; q.cin = cin; q.dy = dy; q.dy_c8_total = dy_c8_total;
-    q.dy_c8_off = dy_c8_off; q.cout = cout; q.dw = dw_oihw; q.scale = scale; q.N = N; q.H = H; q.W = W;
+    q.dy_c8_off = dy_c8_off; q.cout = cout; q.dw = dw_oihw; q.db = nullptr; q.scale = scale; q.N = N; q.H = H; q.W = W;
     std::vector<WgradUnit> units;
     int rc;
     if ((rc = wgrad_units(q, 0, units))) return rc;
@@ -1081,7 +1098,7 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
             tmaps.push_back(tx); tmaps.push_back(tdy);
             if ((rc = wgrad_units(q, tm, units))) return rc;
         }
-        if (q.db)
+        if (q.db && !q.dw)      // bias gradients without a 3x3 weight gradient (9x9 head / tail): the reduction kernel
             for (int pl = 0; pl < dyp; ++pl) {
                 BiasUnit bu{};
                 bu.dy = (const uint4*)q.dy; bu.c8_total = q.dy_c8_total; bu.plane = q.dy_c8_off + pl; bu.N = q.N;
@@ -1092,7 +1109,8 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
     }
     // longest units first: the block scheduler hands CTAs to SMs in index order as they free up
     auto unit_cost = [](const WgradUnit& u) { const int n = u.xplanes * 8; return (long long)u.num_tiles * (n / 2 > 32 + n / 4 ? n / 2 : 32 + n / 4); };
-    std::stable_sort(units.begin(), units.end(), [&](const WgradUnit& a, const WgradUnit& c) { return unit_cost(a) > unit_cost(c); });
+    if (!(ctx->dbg_skip & 131072))
+        std::stable_sort(units.begin(), units.end(), [&](const WgradUnit& a, const WgradUnit& c) { return unit_cost(a) > unit_cost(c); });
     srb_grad_batch* b = new srb_grad_batch();
     b->dtype = dtype; b->nunits = (int)units.size(); b->nbias = (int)bias.size();
     cudaSetDevice(ctx->device);

@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[7] = clock64();    // kernel entry
 
     for (int i = threadIdx.x; i < NOUT; i += blockDim.x) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
@@ -212,6 +213,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
+    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[15] = clock64();   // prologue done
     // programmatic dependent launch (srb_model_pt_forward chains its launches this way): the prologue above touched only
     // this launch's constants; the next launch may start its own on the SMs this grid vacates, and every warp below that
     // touches activations first waits for the previous launch to complete (a no-op for a normal launch)
@@ -559,6 +561,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     tc_fence_before();
     __syncthreads();
     if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, G::TMEM_COLS); }
+    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[23] = clock64();   // exit
 }
 
 }  // namespace srb

@@ -27,6 +27,7 @@ struct WgradUnit {
     int N, H, W, tiles_x, tiles_y, num_tiles;
     float scale;
     float* dw;
+    float* db;                    // bias gradient of the cout block (this unit sums the dY tiles it loads anyway), or nullptr
 };
 
 struct WgradGeom {
@@ -63,7 +64,8 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < G::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        // a stage is released by the MMA commit and, when the unit also owns a bias gradient, by the two summing warps
+        for (int s = 0; s < G::STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], u.db != nullptr ? 3 : 1); }
         mbar_init(done, 1);
         fence_mbar_init();
         tma_prefetch_desc(tmap_x);
@@ -125,7 +127,41 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
         }
         if (elect_one()) umma_commit(done);
         __syncwarp();
-    } else if (warp >= 4) {
+    } else if (warp < 4) {
+        // ===== bias gradient db[co] = sum_p dY[p][co]: warps 2, 3 sum the (non-halo rows of the) dY tiles from shared memory
+        if (u.db != nullptr) {
+            const int t = (warp - 2) * 32 + lane, plane = t >> 4, px = t & 15;
+            float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            int s = 0; uint32_t ph = 0;
+            for (int tile = part; tile < u.num_tiles; tile += splitk) {
+                mbar_wait(&full[s], ph, 24);
+                const uint32_t base = smem_u32(s_st + s * G::STAGE_STRIDE + G::X_STRIDE) + plane * G::DYGRP + px * 16;
+#pragma unroll
+                for (int r = 1; r <= G::TH; ++r) {
+                    uint32_t q0, q1, q2, q3;
+                    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q0), "=r"(q1), "=r"(q2), "=r"(q3) : "r"(base + r * G::DYROWP));
+                    const uint32_t qq[4] = {q0, q1, q2, q3};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float2 f;
+                        if constexpr (BF16) f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&qq[k]));
+                        else f = __half22float2(*reinterpret_cast<const __half2*>(&qq[k]));
+                        acc[2 * k] += f.x; acc[2 * k + 1] += f.y;
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[s]);
+                if (++s == G::STAGES) { s = 0; ph ^= 1; }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float v = acc[k];
+#pragma unroll
+                for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (px == 0 && plane * 8 + k < u.cout_blk && part < u.num_tiles && !(dbg_skip & 1)) atomicAdd(u.db + plane * 8 + k, v * u.scale);
+            }
+        }
+    } else {
         // epilogue: once, after every tile of this CTA has been accumulated.  TMEM lane = s*32 + co (dy = 2 - s), column = ci
         const int lg = warp & 3;
         mbar_wait(done, 0, 23);

@@ -7,7 +7,8 @@ sys.path.insert(0, ROOT)
 from image_super_resolution_b200 import ops
 from image_super_resolution_b200._lib import Context, lib, check
 dev = torch.device("cuda:0"); ctx = Context.get(0)
-N, H, W = 256, 64, 64
+N, H, W = (int(sys.argv[1]) if len(sys.argv) > 1 else 256), 64, 64
+GHZ = 1.9
 for cout, cin, k, residual in ((32, 64, 3, 0), (64, 32, 3, 1), (64, 64, 3, 1), (64, 3, 9, 0), (3, 64, 9, 0)):
     g = torch.Generator().manual_seed(0)
     pc = ops.PackedConv(ctx, torch.randn(cout, cin, k, k, generator=g) * 0.05, torch.zeros(cout))
@@ -25,8 +26,15 @@ for cout, cin, k, residual in ((32, 64, 3, 0), (64, 32, 3, 1), (64, 64, 3, 1), (
         ops.conv2d_fwd(pc, x, pin, 0, y, pout, 0, N, H, W, residual=res, res_planes=pout, flags=flags, slope=0.2)
     torch.cuda.synchronize()
     check(lib().srb_debug_trace(ctx.handle, None))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(20):
+        ops.conv2d_fwd(pc, x, pin, 0, y, pout, 0, N, H, W, residual=res, res_planes=pout, flags=flags, slope=0.2)
+    e1.record(); torch.cuda.synchronize()
+    print(f"   back-to-back launch period {e0.elapsed_time(e1) / 20 * 1e3:.1f} us")
     t = tr.cpu().view(64, 8)
     t0 = int(t[0, 0])
+    print(f"   CTA 0: entry -> prologue done {int(t[1, 7]) - int(t[0, 7])} clk, prologue done -> first TMA issue {t0 - int(t[1, 7])} clk, entry -> exit {int(t[2, 7]) - int(t[0, 7])} clk")
     print(f"== conv k{k} {cin}->{cout} res={residual}: stamps relative to first TMA issue (cycles)")
     print("step  tma_issue  acc_free  halo_ok  mma_issued  epi_wait  acc_done  epi_done | mma_issue_len  epi_len  step_period")
     prev = None

@@ -32,4 +32,8 @@ def timed(fn, n=10):
 for skip in (0, 1, 2, 3):
     ctx.debug_set(2, skip)
     print(f"skip={skip}:", "  ".join(f"splitk {k}: {timed(lambda: gb.run(dev, k)):7.1f} us" for k in (1, 2, 3, 4, 8)))
+ctx.debug_set(2, 131072)            # units in job order (RDB-major: siblings share their X / dY planes through L2)
+from image_super_resolution_b200 import ops
+gb2 = ops.GradBatch(ctx, gb._keep, "bf16")
 ctx.debug_set(2, 0)
+print("job order:", "  ".join(f"splitk {k}: {timed(lambda: gb2.run(dev, k)):7.1f} us" for k in (1, 2, 3)))
