@@ -175,13 +175,16 @@ def bench_train(dev, rank, world, steps, warmup=3):
     hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
     lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
     loss_fn = L1Loss().to(dev)
-    # the reference's optimizer (train.py:265: Adam, lr 1e-4, betas (0.9, 0.999), no weight decay) in PyTorch's fused
-    # implementation: one multi-tensor kernel instead of ~10 foreach launches over 488 tensors (same arithmetic; the
-    # foreach path costs the host 20 ms per step here, tools/gpu_train_phases.py)
-    opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999), fused=True)
+    # the reference's optimizer (train.py:265: Adam, lr 1e-4, betas (0.9, 0.999), no weight decay), GradScaler, gradient
+    # clipping and EMA as the library's fused tail (optim.py: two launches over flat arenas, same arithmetic and call order;
+    # parity vs the torch objects in tests/test_gpu_optim.py).  SRB_TORCH_TAIL=1 runs torch's own objects instead.
+    if os.environ.get("SRB_TORCH_TAIL") == "1":
+        opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999), fused=True)
+        scaler, ema, tail = torch.amp.GradScaler("cuda"), T.ModelEMA(net, tau=1000), "torch GradScaler / clip_grad_norm_ / Adam(fused=True) / per-tensor EMA"
+    else:
+        opt = T.FlatAdam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
+        scaler, ema, tail = T.GradScaler("cuda"), T.ModelEMA(net, tau=1000).attach(opt), "fused tail (FlatAdam + GradScaler + clip + EMA: 2 launches)"
     sched = torch.optim.lr_scheduler.LinearLR(opt, start_factor=1, end_factor=0.1, total_iters=1000)
-    scaler = torch.amp.GradScaler("cuda")
-    ema = T.ModelEMA(net, tau=1000)
     T.train(net, ema, [(hr, lr)] * warmup, loss_fn, opt, scaler, sched, 0, None)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if world > 1:
@@ -201,7 +204,7 @@ def bench_train(dev, rank, world, steps, warmup=3):
     pk = peaks()
     return {"metric": "train.py step samples/s", "value": world * B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms,
             "steps": steps, "model": "EResNet(16,0.2,2)", "per_gpu_batch": B, "hr_crop": 128, "operands": "bf16 in, fp32 accumulate",
-            "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), torch Adam(fused=True), LinearLR, EMA, loss.item()",
+            "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), Adam, LinearLR, EMA, loss.item(); " + tail,
             "collective": "one all-reduce (mean) of the 11.7M-element fp32 gradient arena per step" if world > 1 else "none",
             "fwd_bwd_tflops_per_gpu": flop / (ms * 1e-3) / 1e12, "frac_of_bf16_peak": flop / (ms * 1e-3) / 1e12 / pk["bf16_tflops"],
             "loss_first_last": [losses[0], losses[-1]]}

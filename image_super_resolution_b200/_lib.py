@@ -73,6 +73,9 @@ SIGNATURES = {
     "srb_tail9_create": (_i, [_vp, _vp, _vp, _i, C.POINTER(_vp)]),
     "srb_tail9_destroy": (None, [_vp]),
     "srb_tail9_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "srb_optim_workspace_floats": (_i, []),
+    "srb_grad_stats": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
+    "srb_adam_ema_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _f, _f, _f, _f, _f, _f, _f, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),

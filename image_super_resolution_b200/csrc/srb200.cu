@@ -21,6 +21,7 @@
 #include "srb_resblock.cuh"
 #include "srb_rowconv.cuh"
 #include "srb_tail.cuh"
+#include "srb_optim.cuh"
 
 using namespace srb;
 
@@ -587,6 +588,48 @@ extern "C" int srb_c8_to_f32nchw(srb_ctx* ctx, const void* in, float* out, int C
     cudaStream_t st = (cudaStream_t)stream;
     if (dtype == SRB_DT_BF16) c8_to_f32nchw_kernel<true><<<grid, 256, 0, st>>>(in, out, C, c8_total, c8_off, HW, total);
     else c8_to_f32nchw_kernel<false><<<grid, 256, 0, st>>>(in, out, C, c8_total, c8_off, HW, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// fused optimizer tail over flat fp32 arenas (train.py:58-63)
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_optim_workspace_floats(void) { return 2 * GSTAT_MAX_BLOCKS + 8; }
+
+extern "C" int srb_grad_stats(srb_ctx* ctx, const float* grads, size_t n, const float* scale_dev, float* stats, float* workspace,
+                              srb_stream_t stream) {
+    if (!ctx || !grads || !stats || !workspace) return fail(SRB_EINVAL, "srb_grad_stats: NULL argument");
+    if (n == 0 || (n & 3)) return fail(SRB_EINVAL, "srb_grad_stats: the arena length must be a positive multiple of 4 floats (pad with zeros)");
+    if (((uintptr_t)grads & 15) || ((uintptr_t)workspace & 15)) return fail(SRB_EINVAL, "srb_grad_stats: buffers must be 16-byte aligned");
+    const size_t n4 = n / 4;
+    size_t b = (n4 + 255) / 256;
+    const size_t cap = (size_t)ctx->num_sms * 4 < (size_t)GSTAT_MAX_BLOCKS ? (size_t)ctx->num_sms * 4 : (size_t)GSTAT_MAX_BLOCKS;
+    const int grid = (int)(b < cap ? b : cap);
+    // workspace: [2 * GSTAT_MAX_BLOCKS] per-block partials, then the arrival counter (zero before the first call; the
+    // kernel leaves it at zero)
+    unsigned int* counter = reinterpret_cast<unsigned int*>(workspace + 2 * GSTAT_MAX_BLOCKS);
+    grad_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(grads), n4, scale_dev, stats, workspace, counter);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float* ema,
+                                 size_t n, const float* scale_dev, const float* stats, float max_norm, float lr, float beta1,
+                                 float beta2, float eps, float weight_decay, float ema_decay, srb_stream_t stream) {
+    if (!ctx || !params || !grads || !exp_avg || !exp_avg_sq || !stats) return fail(SRB_EINVAL, "srb_adam_ema_step: NULL argument");
+    if (n == 0 || (n & 3)) return fail(SRB_EINVAL, "srb_adam_ema_step: the arena length must be a positive multiple of 4 floats (pad with zeros)");
+    if (((uintptr_t)params | (uintptr_t)grads | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq | (uintptr_t)ema) & 15)
+        return fail(SRB_EINVAL, "srb_adam_ema_step: arenas must be 16-byte aligned");
+    if (!(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f && eps >= 0.f && lr >= 0.f))
+        return fail(SRB_EINVAL, "srb_adam_ema_step: lr=%g betas=(%g, %g) eps=%g", lr, beta1, beta2, eps);
+    AdamArgs a{};
+    a.p = reinterpret_cast<float4*>(params); a.g = reinterpret_cast<const float4*>(grads);
+    a.m = reinterpret_cast<float4*>(exp_avg); a.v = reinterpret_cast<float4*>(exp_avg_sq); a.ema = reinterpret_cast<float4*>(ema);
+    a.n4 = n / 4; a.scale = scale_dev; a.stats = stats; a.max_norm = max_norm;
+    a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.ema_decay = ema_decay;
+    const int grid = ew_grid(ctx, a.n4, 256);
+    adam_ema_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }

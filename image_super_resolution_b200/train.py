@@ -18,7 +18,8 @@ from copy import deepcopy
 
 import torch
 import torch.distributed as dist
-from torch.nn.utils import clip_grad_norm_
+
+from .optim import clip_grad_norm_, FlatAdam, GradScaler  # noqa: F401  (torch's own for anything but a FlatAdam)
 
 
 class ModelEMA:
@@ -31,6 +32,20 @@ class ModelEMA:
         self.decay = lambda x: decay * (1 - math.exp(-x / tau))
         for p in self.ema.parameters():
             p.requires_grad = False
+        self._opt = None
+
+    def attach(self, optimizer):
+        """Let `optimizer` (optim.FlatAdam over this model's parameters) blend the EMA parameters in its own pass over the
+        parameter arena; `update()` then only advances the counter (and blends floating-point buffers, if any)."""
+        ps = [p for p in self.ema.parameters()]
+        if any(not p.is_cuda for p in ps):
+            raise RuntimeError("ModelEMA.attach: move the EMA model to the optimizer's device first (ema.ema.to(device))")
+        from .optim import flatten_
+        with torch.no_grad():
+            arena = flatten_(ps)
+        optimizer.attach_ema(self, arena)
+        self._opt = optimizer
+        return self
 
     @torch.no_grad()
     def update(self, model):
@@ -39,7 +54,11 @@ class ModelEMA:
         # the floating-point entries of the two state_dicts, paired in module order (parameters, then buffers) — the same
         # tensors `state_dict()` would return, without building 2 x 488 prefixed keys every step (4 ms of host time)
         dst, src = [], []
-        for v, m in zip(list(self.ema.parameters()) + list(self.ema.buffers()), list(model.parameters()) + list(model.buffers())):
+        if self._opt is not None and self._opt.ema_applied_for == self.updates:      # parameters: done by the optimizer's pass
+            pairs = zip(list(self.ema.buffers()), list(model.buffers()))
+        else:
+            pairs = zip(list(self.ema.parameters()) + list(self.ema.buffers()), list(model.parameters()) + list(model.buffers()))
+        for v, m in pairs:
             if v.dtype.is_floating_point:
                 dst.append(v)
                 src.append(m.detach())

@@ -23,6 +23,9 @@ from . import ops, _lib
 from ._lib import Context
 
 
+PARAM_EPOCH = [0]      # bumped by optimizers that update the parameters behind autograd's version counters (optim.FlatAdam)
+
+
 def _chunks(c: int) -> list[int]:
     """Output-channel chunks of a data-gradient conv with c output channels: one launch up to 160 channels (N = 96 .. 160
     MMAs run at the full tensor rate, N <= 64 ones at 40-67 %), two 96-channel halves for the 192-channel gradient of an
@@ -64,7 +67,8 @@ class TrainPlan:
             self.f_conv2, self.d_conv2 = mk(3, 64, 9), mk(64, 3, 9)
         self.params = list(net.parameters())
         self.numel = sum(p.numel() for p in self.params)
-        self.flat_grad = torch.zeros(self.numel, dtype=torch.float32, device=device)
+        # one flat arena (zero-padded to whole 16-byte granules): the all-reduce, clip_grad_norm_ and optim.FlatAdam see it whole
+        self.flat_grad = torch.zeros((self.numel + 3) // 4 * 4, dtype=torch.float32, device=device)
         self.grad_views, o = {}, 0
         for p in self.params:
             self.grad_views[id(p)] = self.flat_grad[o:o + p.numel()].view_as(p)
@@ -81,7 +85,10 @@ class TrainPlan:
 
     # ---- operands -------------------------------------------------------------------------------------------
     def _versions(self):
-        return tuple(p._version for p in self.params)
+        return tuple(p._version for p in self.params) + (PARAM_EPOCH[0],)
+
+    def __deepcopy__(self, memo):
+        return None            # deepcopy(model) (ModelEMA, utils/models.py:25) must not clone device handles; a copy re-plans
 
     def _pack_jobs(self):
         n = self.net
@@ -356,13 +363,15 @@ class _NetFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gout):
         grads = ctx.plan.backward(gout)
-        return (None, None, *grads)
+        # fresh tensor objects over the arena: autograd then adopts them as .grad (a tensor it does not own alone is cloned —
+        # 488 device copies per step), and .grad stays a view of the flat arena for the optimizer
+        return (None, None, *[g.detach() for g in grads])
 
 
 def train_forward(net, x: torch.Tensor) -> torch.Tensor:
     plans = net.__dict__.setdefault("_train_plans", {})
     plan = plans.get(x.device)
-    if plan is None:
+    if plan is None:           # (also after deepcopy(model): see TrainPlan.__deepcopy__)
         plan = plans[x.device] = TrainPlan(net, x.device, getattr(net, "train_operand_dtype", "bf16"))
     return _NetFunction.apply(x.float().contiguous(), plan, *plan.params)
 

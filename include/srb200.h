@@ -222,6 +222,23 @@ int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off,
                       int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off, float slope, void* out,
                       int out_c8_total, int out_c8_off, int planes, int dtype, int N, int H, int W, srb_stream_t stream);
 
+/* Fused optimizer tail over FLAT fp32 arenas (the parameters / gradients / Adam moments / EMA weights of the whole net as
+ * one zero-padded buffer each, length n a multiple of 4) — SURVEY §8(f) rank 1.
+ * srb_grad_stats replaces the per-tensor loops of gradscaler.unscale_ (train.py:58: inf/nan check of g/scale) and of
+ * clip_grad_norm_ (train.py:59: global 2-norm): stats[0] = sum (g/scale)^2, stats[1] = 1 if any g/scale is non-finite,
+ * stats[2] += 1 when finite (the optimizer step number; zero it once).  scale_dev = GradScaler's device scalar or NULL.
+ * workspace: srb_optim_workspace_floats() floats, zeroed once.  Deterministic (fixed-order partial sums).
+ * srb_adam_ema_step replaces gradscaler.step(Adam) (train.py:60; torch.optim.Adam arithmetic, no amsgrad; skipped on the
+ * device when stats[1] != 0) and ema.update (train.py:63 -> utils/models.py:31-40: ema = d*ema + (1-d)*p, ema may be
+ * NULL) in one pass; g is read as g / scale * min(1, max_norm / (sqrt(stats[0]) + 1e-6)) (max_norm <= 0: no clipping)
+ * and never rewritten. */
+int srb_optim_workspace_floats(void);
+int srb_grad_stats(srb_ctx* ctx, const float* grads, size_t n, const float* scale_dev, float* stats, float* workspace,
+                   srb_stream_t stream);
+int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float* ema, size_t n,
+                      const float* scale_dev, const float* stats, float max_norm, float lr, float beta1, float beta2, float eps,
+                      float weight_decay, float ema_decay, srb_stream_t stream);
+
 /* Batched gradients: every 3x3 weight gradient and every bias gradient of one backward pass as ONE launch each.
  * Weight gradients are off backpropagation's critical path, so the step defers them to its end; a unit
  * (conv, 128-ch cin block, 32-ch cout block) is then owned by one CTA (splitk = 1): no cross-CTA reduction.

@@ -109,3 +109,22 @@ def test_data_parallel_gradient_allreduce_world2_gloo_equals_global_batch():
     (model(x) - y).abs().mean().backward()
     want = torch.cat([p.grad.flatten() for p in model.parameters()])
     assert torch.allclose(torch.from_numpy(flat), want, rtol=1e-5, atol=1e-7)
+
+
+def test_fused_tail_objects_refuse_cpu_and_fall_through():
+    """optim.FlatAdam has no CPU path; clip_grad_norm_ / GradScaler hand anything that is not a FlatAdam to torch's own."""
+    import pytest
+    import torch
+    from image_super_resolution_b200.optim import FlatAdam, GradScaler, clip_grad_norm_
+    lin = torch.nn.Linear(4, 3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        FlatAdam(lin.parameters(), lr=1e-3)
+    lin(torch.ones(2, 4)).sum().backward()
+    ref = torch.sqrt(sum(p.grad.pow(2).sum() for p in lin.parameters())).item()
+    n = clip_grad_norm_(lin.parameters(), 0.5)
+    assert abs(n.item() - ref) < 1e-5
+    now = torch.sqrt(sum(p.grad.pow(2).sum() for p in lin.parameters())).item()
+    assert abs(now - min(ref, 0.5)) < 1e-4
+    sc = GradScaler("cpu", enabled=False)
+    opt = torch.optim.SGD(lin.parameters(), lr=0.1)
+    sc.unscale_(opt); sc.step(opt); sc.update()

@@ -16,11 +16,18 @@ g = torch.Generator().manual_seed(100)
 hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
 lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
 loss_fn = L1Loss().to(dev)
-fused = len(sys.argv) > 1 and sys.argv[1] == "fused"
-opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999), fused=fused)
+mode = sys.argv[1] if len(sys.argv) > 1 else "foreach"      # foreach | fused (torch Adam fused=True) | flat (optim.FlatAdam tail)
+fused = mode
+if mode == "flat":
+    opt = T.FlatAdam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
+    scaler = T.GradScaler("cuda")
+    ema = T.ModelEMA(net, tau=1000).attach(opt)
+    clip_grad_norm_ = T.clip_grad_norm_
+else:
+    opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999), fused=mode == "fused")
+    scaler = torch.amp.GradScaler("cuda")
+    ema = T.ModelEMA(net, tau=1000)
 sched = torch.optim.lr_scheduler.LinearLR(opt, start_factor=1, end_factor=0.1, total_iters=1000)
-scaler = torch.amp.GradScaler("cuda")
-ema = T.ModelEMA(net, tau=1000)
 T.train(net, ema, [(hr, lr)] * 3, loss_fn, opt, scaler, sched, 0, None)
 acc = {}
 def phase(name, fn):
