@@ -919,11 +919,12 @@ static int encode_c8_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N,
 
 // dY tensor map with the dimensions ordered (pixel, plane, row, image): a box lands in shared memory as [row][plane][px],
 // which makes the (row shift, plane) channel groups of the folded weight-gradient GEMM equidistant (srb_wgrad.cuh)
-static int encode_dy_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N, int H, int W, int planes) {
+static int encode_dy_map(srb_ctx* ctx, CUtensorMap* tm, const void* base, int N, int H, int W, int planes, int box_planes = WgradGeom::DYPLANES,
+                         int box_rows = WgradGeom::DYH) {
     using G = WgradGeom;
     cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)planes, (cuuint64_t)H, (cuuint64_t)N};
     cuuint64_t gstr[3] = {(cuuint64_t)W * H * 16, (cuuint64_t)W * 16, (cuuint64_t)W * H * 16 * planes};
-    cuuint32_t box[4] = {(cuuint32_t)G::TW * 4, (cuuint32_t)G::DYPLANES, (cuuint32_t)G::DYH, 1};
+    cuuint32_t box[4] = {(cuuint32_t)G::TW * 4, (cuuint32_t)box_planes, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(base), gdim, gstr, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -981,21 +982,22 @@ extern "C" int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int
     CUtensorMap tx, tdy;
     if ((rc = encode_c8_map(ctx, &tx, x, N, H, W, x_c8_total, G::XW, G::TH, units[0].xplanes))) return rc;
     if ((rc = encode_dy_map(ctx, &tdy, dy, N, H, W, dy_c8_total))) return rc;
-    // one launch per unit, its pixel tiles spread over the SMs left per unit (split-K with red.global.add)
+    // one launch: units x split-K parts of their pixel tiles (red.global.add), about one CTA per SM
     int grid = ctx->num_sms / (int)units.size();
     if (grid < 1) grid = 1;
     if (grid > units[0].num_tiles) grid = units[0].num_tiles;
+    WgradUnit u0 = units[0];
+    u0.x_c8_off = x_c8_off; u0.dy_c8_off = dy_c8_off;
+    const dim3 g2(grid, (unsigned)units.size());
     cudaStream_t st = (cudaStream_t)stream;
-    for (const WgradUnit& u : units) {
-        if (dtype == SRB_DT_BF16) {
-            CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-            wgrad_tc_kernel<true><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, ctx->dbg_skip);
-        } else {
-            CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
-            wgrad_tc_kernel<false><<<grid, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, ctx->dbg_skip);
-        }
-        CUDA_TRY(cudaGetLastError());
+    if (dtype == SRB_DT_BF16) {
+        CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        wgrad_tc_kernel<true, 3><<<g2, 256, G::SMEM_BYTES, st>>>(tx, tdy, u0, cin, cout, u0.xplanes * 8, ctx->dbg_skip);
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        wgrad_tc_kernel<false, 3><<<g2, 256, G::SMEM_BYTES, st>>>(tx, tdy, u0, cin, cout, u0.xplanes * 8, ctx->dbg_skip);
     }
+    CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
 
@@ -1068,31 +1070,40 @@ extern "C" int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, in
 extern "C" int srb_conv9_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy, int dy_c8_total,
                                int dy_c8_off, int cout, float* dw_oihw, float scale, int dtype, int N, int H, int W,
                                srb_stream_t stream) {
+    // the folded tensor-core weight-gradient GEMM (srb_wgrad.cuh, KS = 9): units of (8 output channels = one dY plane,
+    // <= 32 input channels), every unit's pixel tiles split over the SMs left per unit
     if (!ctx || !x || !dy || !dw_oihw) return fail(SRB_EINVAL, "srb_conv9_wgrad: NULL argument");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv9_wgrad: empty shape");
-    Wgrad9Params p{};
-    if (cin == 3 && cout == 64) {          // head: A = dY, S = X
-        p.a = dy; p.a_c8_total = dy_c8_total; p.a_c8_off = dy_c8_off; p.s = x; p.s_c8_total = x_c8_total; p.s_c8_off = x_c8_off;
-        p.sgn = 1; p.a_is_cout = 1;
-        if (dy_c8_off < 0 || dy_c8_off + 8 > dy_c8_total || x_c8_off < 0 || x_c8_off >= x_c8_total) return fail(SRB_EINVAL, "srb_conv9_wgrad: plane slice out of range");
-    } else if (cin == 64 && cout == 3) {   // tail: A = X, S = dY
-        p.a = x; p.a_c8_total = x_c8_total; p.a_c8_off = x_c8_off; p.s = dy; p.s_c8_total = dy_c8_total; p.s_c8_off = dy_c8_off;
-        p.sgn = -1; p.a_is_cout = 0;
-        if (x_c8_off < 0 || x_c8_off + 8 > x_c8_total || dy_c8_off < 0 || dy_c8_off >= dy_c8_total) return fail(SRB_EINVAL, "srb_conv9_wgrad: plane slice out of range");
-    } else return fail(SRB_ENOSUP, "srb_conv9_wgrad: only the 3->64 head and 64->3 tail 9x9 convs (cin=%d cout=%d)", cin, cout);
-    p.dw = dw_oihw; p.scale = scale; p.N = N; p.H = H; p.W = W;
-    p.tiles_x = (W + WG9_T - 1) / WG9_T; p.tiles_y = (H + WG9_T - 1) / WG9_T;
-    long long nt = (long long)p.tiles_x * p.tiles_y * N;
+    if (cin <= 0 || cout <= 0) return fail(SRB_EINVAL, "srb_conv9_wgrad: cin=%d cout=%d", cin, cout);
+    if (((uintptr_t)x & 15) || ((uintptr_t)dy & 15)) return fail(SRB_EINVAL, "srb_conv9_wgrad: buffers must be 16-byte aligned");
+    const int xp = (cin + 7) / 8, dyp = (cout + 7) / 8;
+    if (x_c8_off < 0 || x_c8_off + xp > x_c8_total || dy_c8_off < 0 || dy_c8_off + dyp > dy_c8_total)
+        return fail(SRB_EINVAL, "srb_conv9_wgrad: plane slice out of range");
+    using G = WgradGeomT<9>;
+    const int blk = cin < 32 ? round_up(cin, 16) : 32;          // MMA N: 16 for the head's 3 input channels, else 32
+    CUtensorMap tx, tdy;
+    int rc;
+    if ((rc = encode_c8_map(ctx, &tx, x, N, H, W, x_c8_total, G::XW, G::TH, blk / 8))) return rc;
+    if ((rc = encode_dy_map(ctx, &tdy, dy, N, H, W, dy_c8_total, G::DYPLANES, G::DYH))) return rc;
+    WgradUnit u{};
+    u.N = N; u.H = H; u.W = W;
+    u.tiles_x = (W + G::TW - 1) / G::TW; u.tiles_y = (H + G::TH - 1) / G::TH;
+    long long nt = (long long)u.tiles_x * u.tiles_y * N;
     if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_conv9_wgrad: %lld tiles", nt);
-    p.num_tiles = (int)nt;
-    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    u.num_tiles = (int)nt; u.cin_total = cin; u.scale = scale; u.dw = dw_oihw; u.db = nullptr; u.xplanes = blk / 8;
+    const int nunits = ((cin + blk - 1) / blk) * dyp;
+    int grid = ctx->num_sms / nunits;
+    if (grid < 1) grid = 1;
+    if (grid > u.num_tiles) grid = u.num_tiles;
     cudaStream_t st = (cudaStream_t)stream;
+    u.x_c8_off = x_c8_off; u.dy_c8_off = dy_c8_off;
+    const dim3 g2(grid, (unsigned)nunits);
     if (dtype == SRB_DT_BF16) {
-        CUDA_TRY(cudaFuncSetAttribute(wgrad9_direct_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG9_SMEM));
-        wgrad9_direct_kernel<true><<<grid, 256, WG9_SMEM, st>>>(p);
+        CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<true, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        wgrad_tc_kernel<true, 9><<<g2, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, cin, cout, blk, ctx->dbg_skip);
     } else {
-        CUDA_TRY(cudaFuncSetAttribute(wgrad9_direct_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG9_SMEM));
-        wgrad9_direct_kernel<false><<<grid, 256, WG9_SMEM, st>>>(p);
+        CUDA_TRY(cudaFuncSetAttribute(wgrad_tc_kernel<false, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        wgrad_tc_kernel<false, 9><<<g2, 256, G::SMEM_BYTES, st>>>(tx, tdy, u, cin, cout, blk, ctx->dbg_skip);
     }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;

@@ -170,115 +170,6 @@ __global__ void c8_axpby_mask_kernel(const uint4* __restrict__ a, int a_tot, int
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// Weight gradient of the 9x9 head (3->64) and tail (64->3) convs — 4 % of the FLOPs each, K = 3 is no tensor-core
-// shape, so this one runs on the FP32 pipe:   T[c64][c3][tap] = sum_p A[p][c64] * S[p + sgn*(tap - centre)][c3]
-//   head (utils/models.py:625): A = dY (64 ch), S = X (3 ch),  sgn = +1,  dW[c64][c3][tap]
-//   tail (utils/models.py:636): A = X (64 ch),  S = dY (3 ch), sgn = -1,  dW[c3][c64][tap]
-// A is a C8 8-plane slice, S a single C8 plane (channels 0..2).  Persistent CTAs walk 16x16 pixel tiles; thread
-// (c64, tap group tg) keeps 21 taps x 3 channels in registers; the S reads are warp-uniform (broadcast).
-// ------------------------------------------------------------------------------------------
-struct Wgrad9Params {
-    const void* a; int a_c8_total, a_c8_off;
-    const void* s; int s_c8_total, s_c8_off;
-    float* dw; float scale;
-    int sgn, a_is_cout;
-    int N, H, W, tiles_x, tiles_y, num_tiles;
-};
-constexpr int WG9_T = 16, WG9_SW = WG9_T + 8;
-constexpr int WG9_SMEM = 256 * 64 * 4 + WG9_SW * WG9_SW * 16;
-
-template <bool BF16>
-__global__ void __launch_bounds__(256, 1) wgrad9_direct_kernel(const Wgrad9Params p) {
-    extern __shared__ __align__(16) uint8_t wg9_smem[];
-    float* s_a = reinterpret_cast<float*>(wg9_smem);                       // [256 px][64 ch]
-    float4* s_s = reinterpret_cast<float4*>(wg9_smem + 256 * 64 * 4);      // [24][24] (3 ch + pad)
-    const int tid = threadIdx.x;
-    const int c64 = tid & 63, tg = tid >> 6;
-    int off[21];
-#pragma unroll
-    for (int m = 0; m < 21; ++m) {
-        const int tap = tg + 4 * m;
-        const int dy = tap / 9, dx = tap - dy * 9;
-        off[m] = tap < 81 ? p.sgn * ((dy - 4) * WG9_SW + (dx - 4)) : 0;
-    }
-    float acc[21][3];
-#pragma unroll
-    for (int m = 0; m < 21; ++m) { acc[m][0] = 0.f; acc[m][1] = 0.f; acc[m][2] = 0.f; }
-    const size_t HW = (size_t)p.H * p.W;
-    const int tiles_per_img = p.tiles_x * p.tiles_y;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int n = tile / tiles_per_img;
-        const int r = tile - n * tiles_per_img;
-        const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-        __syncthreads();
-        // A tile: 256 px x 8 planes, plane fastest across threads (conflict-free shared stores)
-        for (int i = tid; i < 256 * 8; i += 256) {
-            const int pl = i & 7, px = i >> 3;
-            const int y = ty * WG9_T + (px >> 4), x = tx * WG9_T + (px & 15);
-            float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            if (y < p.H && x < p.W) {
-                const uint4 q = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.a) +
-                    (((size_t)n * p.a_c8_total + p.a_c8_off + pl) * HW + (size_t)y * p.W + x) * 16);
-                const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    float2 f;
-                    if constexpr (BF16) f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&qq[k]));
-                    else f = __half22float2(*reinterpret_cast<const __half2*>(&qq[k]));
-                    v[2 * k] = f.x; v[2 * k + 1] = f.y;
-                }
-            }
-            float4* dst = reinterpret_cast<float4*>(s_a + px * 64 + pl * 8);
-            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-        }
-        for (int i = tid; i < WG9_SW * WG9_SW; i += 256) {
-            const int sy = i / WG9_SW, sx = i - sy * WG9_SW;
-            const int y = ty * WG9_T + sy - 4, x = tx * WG9_T + sx - 4;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (y >= 0 && y < p.H && x >= 0 && x < p.W) {
-                const uint2 q = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(p.s) +
-                    (((size_t)n * p.s_c8_total + p.s_c8_off) * HW + (size_t)y * p.W + x) * 16);
-                float2 f0, f1;
-                if constexpr (BF16) {
-                    f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.x));
-                    f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&q.y));
-                } else {
-                    f0 = __half22float2(*reinterpret_cast<const __half2*>(&q.x));
-                    f1 = __half22float2(*reinterpret_cast<const __half2*>(&q.y));
-                }
-                v = make_float4(f0.x, f0.y, f1.x, 0.f);
-            }
-            s_s[i] = v;
-        }
-        __syncthreads();
-#pragma unroll 1
-        for (int px = 0; px < 256; ++px) {
-            const float a = s_a[px * 64 + c64];
-            const int base = ((px >> 4) + 4) * WG9_SW + (px & 15) + 4;
-#pragma unroll
-            for (int m = 0; m < 21; ++m) {
-                const float4 sv = s_s[base + off[m]];
-                acc[m][0] = fmaf(a, sv.x, acc[m][0]);
-                acc[m][1] = fmaf(a, sv.y, acc[m][1]);
-                acc[m][2] = fmaf(a, sv.z, acc[m][2]);
-            }
-        }
-    }
-    if (blockIdx.x < p.num_tiles) {
-#pragma unroll
-        for (int m = 0; m < 21; ++m) {
-            const int tap = tg + 4 * m;
-            if (tap < 81) {
-#pragma unroll
-                for (int c3 = 0; c3 < 3; ++c3) {
-                    const size_t idx = p.a_is_cout ? ((size_t)c64 * 3 + c3) * 81 + tap : ((size_t)c3 * 64 + c64) * 81 + tap;
-                    atomicAdd(p.dw + idx, acc[m][c3] * p.scale);
-                }
-            }
-        }
-    }
-}
+// (the 9x9 head / tail weight gradients run on the folded tensor-core GEMM of srb_wgrad.cuh, KS = 9)
 
 }  // namespace srb

@@ -30,29 +30,38 @@ struct WgradUnit {
     float* db;                    // bias gradient of the cout block (this unit sums the dY tiles it loads anyway), or nullptr
 };
 
-struct WgradGeom {
-    static constexpr int TW = 16, TH = 8;
-    static constexpr int XW = TW + 2, MAXPLANES = 20, DYPLANES = 4, DYH = TH + 2;
-    static constexpr int XROWP = XW * 16, XPLANE = TH * XROWP;                // 288, 2304
-    static constexpr int X_STRIDE = MAXPLANES * XPLANE;                       // 46080
-    static constexpr int DYGRP = TW * 16, DYROWP = DYPLANES * DYGRP, DYBYTES = DYH * DYROWP;   // 256, 1024, 10240
-    static constexpr int STAGE_STRIDE = X_STRIDE + DYBYTES;                   // 56320
+// KS = 3: the 3x3 convs (4 dY planes = 32 output channels per unit, N up to 160 input channels).
+// KS = 9: the 9x9 head / tail convs (utils/models.py:625, :636) in the same mapping — one dY plane (8 output channels, the
+// tail's 3 + zeros) x 9 row shifts = 9 of the 16 M groups, 9 dx accumulators of N <= 32 input channels (the head's 3 + zeros).
+template <int KS>
+struct WgradGeomT {
+    static constexpr int TW = 16, TH = 8, PAD = KS / 2;
+    static constexpr int XW = TW + 2 * PAD, DYPLANES = (KS == 3) ? 4 : 1, DYH = TH + 2 * PAD;
+    static constexpr int MAXPLANES = (KS == 3) ? 20 : 4;                      // KS accumulators x 8 * MAXPLANES columns <= 512
+    static constexpr int XROWP = XW * 16, XPLANE = TH * XROWP;                // 3x3: 288, 2304;  9x9: 384, 3072
+    static constexpr int X_STRIDE = 46080;                                    // = 20 planes of the 3x3 geometry
+    static constexpr int DYGRP = TW * 16, DYROWP = DYPLANES * DYGRP, DYBYTES = DYH * DYROWP;   // 3x3: 256, 1024, 10240;  9x9: 256, 256, 4096
+    static constexpr int DY_STRIDE = 10240;
+    static constexpr int STAGE_STRIDE = X_STRIDE + DY_STRIDE;                 // 56320
     static constexpr int STAGES = 4;
-    static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_STRIDE + 1024 + 256;   // the idle M lanes read 1 KB past a dY tile
-    static constexpr int NOUT = 32;
+    static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_STRIDE + 1024 + 256;   // the idle M lanes read past a dY tile (<= 1 KB past the stage)
+    static constexpr int NOUT = 8 * DYPLANES;
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
-    static_assert(X_STRIDE % 1024 == 0 && STAGE_STRIDE % 1024 == 0, "stage alignment");
+    static_assert(MAXPLANES * XPLANE <= X_STRIDE && DYBYTES <= DY_STRIDE, "stage layout");
+    static_assert((TH - 1) * DYROWP + 16 * DYGRP <= DY_STRIDE + 1024, "A operand over-read stays inside the allocation");
+    static_assert(KS * MAXPLANES * 8 <= 512, "TMEM columns");
 };
+using WgradGeom = WgradGeomT<3>;
 
 // kind::f16 instruction descriptor with both operands MN-major
 __host__ __device__ constexpr uint32_t umma_idesc_f16_mn(int M, int N, int fmt) {
     return umma_idesc_f16(M, N, fmt) | (1u << 15) | (1u << 16);
 }
 
-template <bool BF16>
+template <bool BF16, int KS>
 __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUtensorMap* tmap_dy, const WgradUnit& u, int part,
                                            int splitk, int dbg_skip) {
-    using G = WgradGeom;
+    using G = WgradGeomT<KS>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* s_st = smem;
@@ -92,8 +101,8 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
                 else {
                     mbar_arrive_expect_tx(&full[s], bytes);
                     uint8_t* st = s_st + s * G::STAGE_STRIDE;
-                    tma_load_4d(st, tmap_x, &full[s], (tx * G::TW - 1) * 4, ty * G::TH, u.x_c8_off, n);
-                    tma_load_4d(st + G::X_STRIDE, tmap_dy, &full[s], tx * G::TW * 4, u.dy_c8_off, ty * G::TH - 1, n);
+                    tma_load_4d(st, tmap_x, &full[s], (tx * G::TW - G::PAD) * 4, ty * G::TH, u.x_c8_off, n);
+                    tma_load_4d(st + G::X_STRIDE, tmap_dy, &full[s], tx * G::TW * 4, u.dy_c8_off, ty * G::TH - G::PAD, n);
                 }
             }
             __syncwarp();
@@ -116,7 +125,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
                     for (int r = 0; r < G::TH; ++r) {
                         const uint64_t ad = a_desc + (uint64_t)((r * G::DYROWP) >> 4);
 #pragma unroll
-                        for (int dx = 0; dx < 3; ++dx)
+                        for (int dx = 0; dx < KS; ++dx)
                             umma_f16_ss(tmem_base + dx * NN, ad, b_desc + (uint64_t)((r * G::XROWP + dx * 16) >> 4), idesc, (it | r) != 0);
                     }
                 }
@@ -129,7 +138,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
         __syncwarp();
     } else if (warp < 4) {
         // ===== bias gradient db[co] = sum_p dY[p][co]: warps 2, 3 sum the (non-halo rows of the) dY tiles from shared memory
-        if (u.db != nullptr) {
+        if (KS == 3 && u.db != nullptr) {
             const int t = (warp - 2) * 32 + lane, plane = t >> 4, px = t & 15;
             float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             int s = 0; uint32_t ph = 0;
@@ -162,24 +171,26 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
             }
         }
     } else {
-        // epilogue: once, after every tile of this CTA has been accumulated.  TMEM lane = s*32 + co (dy = 2 - s), column = ci
+        // epilogue: once, after every tile of this CTA has been accumulated.  TMEM lane = s * NOUT + co (dy = KS-1 - s), column = ci
         const int lg = warp & 3;
         mbar_wait(done, 0, 23);
         tc_fence_after();
         const bool has_tiles = part < u.num_tiles && !(dbg_skip & 2);
-        if (lg < 3) {
-            float* dst0 = u.dw + ((size_t)(u.cout0 + lane) * u.cin_total + u.cin0) * 9 + (2 - lg) * 3;
+        const int L = lg * 32 + lane, sft = L / G::NOUT, co = L % G::NOUT;
+        if (lg * 32 < KS * G::NOUT) {
+            const bool lane_ok = has_tiles && sft < KS && co < u.cout_blk;
+            float* dst0 = u.dw + ((size_t)(u.cout0 + co) * u.cin_total + u.cin0) * (KS * KS) + (KS - 1 - sft) * KS;
 #pragma unroll 1
-            for (int dx = 0; dx < 3; ++dx)
+            for (int dx = 0; dx < KS; ++dx)
 #pragma unroll 1
                 for (int c0 = 0; c0 < u.cin_blk; c0 += 32) {
                     uint32_t rr[32];
                     tmem_ld32(tmem_base + dx * NN + c0 + ((uint32_t)(lg * 32) << 16), rr);
                     tmem_ld_wait();
-                    if (has_tiles && lane < u.cout_blk) {
+                    if (lane_ok) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
-                            if (c0 + j < u.cin_blk) atomicAdd(dst0 + (size_t)(c0 + j) * 9 + dx, __uint_as_float(rr[j]) * u.scale);
+                            if (c0 + j < u.cin_blk) atomicAdd(dst0 + (size_t)(c0 + j) * (KS * KS) + dx, __uint_as_float(rr[j]) * u.scale);
                     }
                 }
         }
@@ -190,11 +201,21 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
     if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
 }
 
-// one unit, passed by value (srb_conv2d_wgrad: a single conv, its pixel tiles spread over gridDim.x CTAs)
-template <bool BF16>
+// one conv, its template unit passed by value (srb_conv2d_wgrad, srb_conv9_wgrad): blockIdx.y enumerates the conv's
+// (input-channel block, output-channel block) units, blockIdx.x the split-K parts of a unit's pixel tiles
+template <bool BF16, int KS>
 __global__ void __launch_bounds__(256, 1) wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap_x,
-                                                          const __grid_constant__ CUtensorMap tmap_dy, const WgradUnit u, int dbg_skip) {
-    wgrad_body<BF16>(&tmap_x, &tmap_dy, u, (int)blockIdx.x, (int)gridDim.x, dbg_skip);
+                                                          const __grid_constant__ CUtensorMap tmap_dy, const WgradUnit u0, int cin,
+                                                          int cout, int blk, int dbg_skip) {
+    using G = WgradGeomT<KS>;
+    const int ncb = (cout + G::NOUT - 1) / G::NOUT;
+    const int cib = (int)blockIdx.y / ncb, cob = (int)blockIdx.y - cib * ncb;
+    WgradUnit u = u0;
+    u.cin0 = cib * blk; u.cout0 = cob * G::NOUT;
+    u.cin_blk = cin - u.cin0 < blk ? cin - u.cin0 : blk;
+    u.cout_blk = cout - u.cout0 < G::NOUT ? cout - u.cout0 : G::NOUT;
+    u.x_c8_off += u.cin0 / 8; u.dy_c8_off += u.cout0 / 8;
+    wgrad_body<BF16, KS>(&tmap_x, &tmap_dy, u, (int)blockIdx.x, (int)gridDim.x, dbg_skip);
 }
 
 // bias gradient: db[c] += scale * sum_p dY[p][c] over a C8 plane slice (HBM-bound, one pass, 16-byte loads)
@@ -246,7 +267,7 @@ __global__ void __launch_bounds__(256, 1) wgrad_batch_kernel(const CUtensorMap* 
                                                              int splitk, int dbg_skip) {
     const int uidx = blockIdx.x / splitk, part = blockIdx.x - uidx * splitk;
     const WgradUnit u = units[uidx];
-    wgrad_body<BF16>(tmaps + 2 * u.tm, tmaps + 2 * u.tm + 1, u, part, splitk, dbg_skip);
+    wgrad_body<BF16, 3>(tmaps + 2 * u.tm, tmaps + 2 * u.tm + 1, u, part, splitk, dbg_skip);
 }
 
 // batched bias gradients: one CTA per (conv, 8-channel plane); fixed-order in-CTA reduction, plain store (deterministic)

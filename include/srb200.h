@@ -204,7 +204,8 @@ int srb_conv2d_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, 
 int srb_bias_grad(srb_ctx* ctx, const void* dy, int dy_c8_total, int dy_c8_off, int cout, float* db, float scale, int dtype,
                   int N, int H, int W, srb_stream_t stream);
 
-/* 9x9 weight gradients of the head (cin=3,cout=64; utils/models.py:625) and tail (cin=64,cout=3; :636) convs, FP32 pipe.
+/* 9x9 weight gradients of the head (cin=3,cout=64; utils/models.py:625) and tail (cin=64,cout=3; :636) convs on the same
+ * tensor-core GEMM (9 row shifts of one dY plane folded into M, 9 dx accumulators; any cin, cout).
  * Same contract as srb_conv2d_wgrad: dw fp32 OIHW [cout][cin][9][9], accumulated into. */
 int srb_conv9_wgrad(srb_ctx* ctx, const void* x, int x_c8_total, int x_c8_off, int cin, const void* dy, int dy_c8_total,
                     int dy_c8_off, int cout, float* dw_oihw, float scale, int dtype, int N, int H, int W, srb_stream_t stream);
@@ -241,7 +242,8 @@ int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads, float* ex
 
 /* Batched gradients: every 3x3 weight gradient and every bias gradient of one backward pass as ONE launch each.
  * Weight gradients are off backpropagation's critical path, so the step defers them to its end; a unit
- * (conv, 128-ch cin block, 32-ch cout block) is then owned by one CTA (splitk = 1): no cross-CTA reduction.
+ * (conv, <= 160-ch cin block, 32-ch cout block) is then owned by one CTA (splitk = 1): no cross-CTA reduction.  The bias
+ * gradient of a conv that also has a weight gradient rides on its first cin block (the dY tiles are in shared memory).
  * Buffers named by the jobs must stay allocated (and keep their addresses) while the batch object lives.
  * dw / db are ACCUMULATED into; either may be NULL. */
 typedef struct srb_grad_job {
