@@ -37,6 +37,7 @@ SIGNATURES = {
     "srb_model_pt_destroy": (None, [_vp]),
     "srb_model_pt_workspace_bytes": (_sz, [_i, _i, _i]),
     "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
+    "srb_model_pt_forward_frames": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
     "srb_model_pt_launches": (_i, [_i, _i]),
     "srb_check_device": (_i, [_vp]),

@@ -439,10 +439,11 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     cudaStream_t st = (cudaStream_t)stream;
     if (w->mode == MODE_DXN) {
         if (!(flags & (SRB_F_U8OUT | SRB_F_F32OUT))) return fail(SRB_EINVAL, "srb_conv2d_fwd: tail conv needs SRB_F_U8OUT or SRB_F_F32OUT");
+        if ((flags & SRB_F_HWC_BGR) && !(flags & SRB_F_U8OUT)) return fail(SRB_EINVAL, "srb_conv2d_fwd: SRB_F_HWC_BGR is a uint8 store");
         if (w->c8in == 8) return launch_conv<8, 32, 9, 9, MODE_DXN, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: tail conv with cin=%d", w->cin);
     }
-    if (flags & (SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_TANH)) return fail(SRB_EINVAL, "srb_conv2d_fwd: tanh/u8/f32 output only on the tail conv");
+    if (flags & (SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_TANH | SRB_F_HWC_BGR)) return fail(SRB_EINVAL, "srb_conv2d_fwd: tanh/u8/f32/HWC output only on the tail conv");
     int out_planes = (flags & SRB_F_PIXSHUF2) ? w->cout / 32 : (w->cout + 7) / 8;
     if ((flags & SRB_F_PIXSHUF2) && (w->cout % 32)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PixelShuffle(2) needs cout %% 32 == 0");
     if ((flags & SRB_F_PIXSHUF2) && (flags & SRB_F_RESIDUAL)) return fail(SRB_EINVAL, "srb_conv2d_fwd: PIXSHUF2 with residual unsupported");
@@ -790,11 +791,18 @@ static void prof_mark(srb_ctx* ctx, cudaStream_t st, bool first = false) {
 
 extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in, uint8_t* out, int N, int H, int W,
                                     void* ws, size_t ws_bytes, srb_stream_t stream) {
+    return srb_model_pt_forward_frames(ctx, net, in, out, SRB_LAYOUT_NCHW_RGB, N, H, W, ws, ws_bytes, stream);
+}
+
+extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uint8_t* in, uint8_t* out, int out_layout, int N, int H, int W,
+                                    void* ws, size_t ws_bytes, srb_stream_t stream) {
     if (!ctx || !net || !in || !out || !ws) return fail(SRB_EINVAL, "srb_model_pt_forward: NULL argument");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_model_pt_forward: empty shape %dx%dx%d", N, H, W);
     size_t need = srb_model_pt_workspace_bytes(N, H, W);
     if (ws_bytes < need) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace %zu < %zu bytes", ws_bytes, need);
     if ((uintptr_t)ws & 255) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace must be 256-byte aligned");
+    if (out_layout != SRB_LAYOUT_NCHW_RGB && out_layout != SRB_LAYOUT_NHWC_BGR) return fail(SRB_EINVAL, "srb_model_pt_forward_frames: out_layout %d", out_layout);
+    const int oflags = SRB_F_TANH | SRB_F_U8OUT | (out_layout == SRB_LAYOUT_NHWC_BGR ? SRB_F_HWC_BGR : 0);
     size_t P = (size_t)N * H * W;
     uint8_t* base = (uint8_t*)ws;
     void* in8 = base; base += align256((size_t)N * H * (W + 1) * 16);   // one input plane (pixel-pair granules: W + 1 per row)
@@ -840,8 +848,8 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
     if (fused && !(ctx->dbg_skip & 16384)) {
-        if ((rc = srb_tail9_fwd(ctx, net->tail, ra, out, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
-    } else if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, SRB_F_TANH | SRB_F_U8OUT, N, H, W, stream))) return rc;
+        if ((rc = srb_tail9_fwd(ctx, net->tail, ra, out, oflags, N, H, W, stream))) return rc;
+    } else if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, oflags, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
     return SRB_OK;
 }
@@ -1533,8 +1541,9 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_tail9_fwd: empty shape");
     if ((uintptr_t)x & 15) return fail(SRB_EINVAL, "srb_tail9_fwd: x must be 16-byte aligned");
     const int fmt = flags & (SRB_F_U8OUT | SRB_F_F32OUT);
-    if ((flags & ~(SRB_F_TANH | SRB_F_U8OUT | SRB_F_F32OUT)) || (fmt != SRB_F_U8OUT && fmt != SRB_F_F32OUT))
-        return fail(SRB_ENOSUP, "srb_tail9_fwd: flags 0x%x (SRB_F_TANH and exactly one of SRB_F_U8OUT / SRB_F_F32OUT)", flags);
+    if ((flags & ~(SRB_F_TANH | SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_HWC_BGR)) || (fmt != SRB_F_U8OUT && fmt != SRB_F_F32OUT) ||
+        ((flags & SRB_F_HWC_BGR) && fmt != SRB_F_U8OUT))
+        return fail(SRB_ENOSUP, "srb_tail9_fwd: flags 0x%x (SRB_F_TANH, exactly one of SRB_F_U8OUT / SRB_F_F32OUT, SRB_F_HWC_BGR only with U8OUT)", flags);
     using G = TLGeom;
     TailParams p{};
     const long long sets = set_tile_geom(p, N, H, W, 1);

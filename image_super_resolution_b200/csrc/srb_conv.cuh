@@ -42,6 +42,7 @@ enum : int {
     F_PIXSHUF2 = 16,  // fold nn.PixelShuffle(2) into the store addressing (Scaler, utils/models.py:580-583)
     F_F32OUT = 32,    // DXN: fp32 NCHW output
     F_MASK = 64,      // backward: multiply output planes [mask_p0, mask_p1) by LeakyReLU'(saved activation)
+    F_HWC_BGR = 128,  // with F_U8OUT: store NHWC with the channels reversed (RGB2BGR + permute of rs.py:65-74, utils/datasets.py:113-124)
 };
 
 struct ConvParams {
@@ -538,7 +539,8 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                         for (int co = 0; co < 3; ++co) {
                             float tt = acc[co];
                             if (p.flags & F_TANH) tt = tanhf(tt);
-                            const size_t o = ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
+                            const size_t o = (p.flags & F_HWC_BGR) ? ((size_t)n * HW + (size_t)y * p.W + x) * 3 + (2 - co)
+                                                                   : ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
                             if (p.flags & F_U8OUT) {
                                 float u = (tt + 1.0f) * 0.5f;
                                 u = u * 255.0f;

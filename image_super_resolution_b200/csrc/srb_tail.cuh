@@ -22,7 +22,7 @@ struct TailParams {
     const uint8_t* w;         // packed [4 K-steps][2 granules][288 rows = 9 dy-slices x 32][8 k] 16-bit
     float bias[3];
     void* y;                  // NCHW uint8 (F_U8OUT) or fp32 (F_F32OUT)
-    int flags;                // F_TANH, F_U8OUT, F_F32OUT
+    int flags;                // F_TANH, F_U8OUT (+ F_HWC_BGR), F_F32OUT
     int dbg_skip;
 };
 
@@ -228,7 +228,8 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
                     for (int co = 0; co < 3; ++co) {
                         float tt = acc[co];
                         if (p.flags & F_TANH) tt = tanhf(tt);
-                        const size_t o = ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
+                        const size_t o = (p.flags & F_HWC_BGR) ? ((size_t)n * HW + (size_t)y * p.W + x) * 3 + (2 - co)
+                                                               : ((size_t)n * 3 + co) * HW + (size_t)y * p.W + x;
                         if (p.flags & F_U8OUT) {
                             float u = (tt + 1.0f) * 0.5f;
                             u = u * 255.0f;

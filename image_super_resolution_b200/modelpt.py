@@ -117,7 +117,12 @@ class ModelPT:
         return int(lib().srb_model_pt_workspace_bytes(N, H, W))
 
     @torch.no_grad()
-    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None, layout: str = "nchw") -> torch.Tensor:
+        """uint8 [N,3,H,W] -> uint8 [N,3,H,W] (rs.py:64 / :94).  layout="hwc_bgr" (device inputs): the result is written as
+        [N,H,W,3] with the channels reversed — the frame the video writer takes (rs.py:65-74: RGB2BGR + permute), produced
+        by the tail conv's store instead of two elementwise kernels."""
+        if layout not in ("nchw", "hwc_bgr"):
+            raise ValueError(f"layout {layout!r}")
         if self._net is None:
             raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
         if x.dim() != 4 or x.shape[1] != 3:
@@ -132,7 +137,9 @@ class ModelPT:
             x = xr.to(torch.uint8)
         N, _, H, W = x.shape
         if N == 0 or H == 0 or W == 0:
-            return torch.empty_like(x)
+            return torch.empty_like(x) if layout == "nchw" else x.new_empty((N, H, W, 3))
+        if not x.is_cuda and layout != "nchw":
+            raise RuntimeError("layout='hwc_bgr' takes device inputs (use stream(..., layout='hwc_bgr') for host batches)")
         if not x.is_cuda:  # host tensors: the C ABI's host entry does H2D / D2H itself
             x = x.contiguous()
             y = torch.empty_like(x)
@@ -143,19 +150,22 @@ class ModelPT:
         if x.device != self._device:
             raise RuntimeError(f"input on {x.device}, model on {self._device}")
         x = x.contiguous()
-        y = out if out is not None else torch.empty_like(x)
+        y = out if out is not None else (torch.empty_like(x) if layout == "nchw" else x.new_empty((N, H, W, 3)))
+        if y.numel() != x.numel() or y.dtype != torch.uint8 or not y.is_contiguous() or y.device != x.device:
+            raise RuntimeError("out must be a contiguous uint8 tensor of the input's size on the input's device")
         nbytes = self.workspace_bytes(N, H, W)
         ws = self._workspace(nbytes)
         stream = C.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
         with torch.cuda.device(self._device):
-            check(lib().srb_model_pt_forward(self._ctx.handle, self._net, x.data_ptr(), y.data_ptr(), N, H, W,
-                                             ws.data_ptr(), ws.numel(), stream), "srb_model_pt_forward")
+            check(lib().srb_model_pt_forward_frames(self._ctx.handle, self._net, x.data_ptr(), y.data_ptr(),
+                                                    1 if layout == "hwc_bgr" else 0, N, H, W, ws.data_ptr(), ws.numel(), stream),
+                  "srb_model_pt_forward_frames")
         return y
 
     __call__ = forward
 
     @torch.no_grad()
-    def stream(self, batches, depth: int = 2):
+    def stream(self, batches, depth: int = 2, layout: str = "nchw"):
         """Pipelined host-to-host inference over a sequence of uint8 host batches — the shape of rs.py's video loop
         (rs.py:58-76: frames from the reader -> model -> writer).  Yields one pinned uint8 host tensor per input batch, in
         order.  H2D of batch i+1 and D2H of batch i-1 run on copy streams while the kernels of batch i run on the compute
@@ -179,8 +189,9 @@ class ModelPT:
                 raise RuntimeError("internal: ring overrun")
             sl = slots[k]
             if sl is None or sl[6] != tuple(xb.shape):
-                sl = (torch.empty(xb.shape, dtype=torch.uint8, device=dev), torch.empty(xb.shape, dtype=torch.uint8, device=dev),
-                      torch.empty(xb.shape, dtype=torch.uint8).pin_memory(), torch.cuda.Event(), torch.cuda.Event(),
+                oshape = tuple(xb.shape) if layout == "nchw" else (xb.shape[0], xb.shape[2], xb.shape[3], 3)
+                sl = (torch.empty(xb.shape, dtype=torch.uint8, device=dev), torch.empty(oshape, dtype=torch.uint8, device=dev),
+                      torch.empty(oshape, dtype=torch.uint8).pin_memory(), torch.cuda.Event(), torch.cuda.Event(),
                       torch.cuda.Event(), tuple(xb.shape))
                 slots[k] = sl
             x_dev, y_dev, y_host, ev_in, ev_c, ev_out, _ = sl
@@ -189,7 +200,7 @@ class ModelPT:
                 ev_in.record(s_in)
             with torch.cuda.stream(s_c):
                 s_c.wait_event(ev_in)
-                self.forward(x_dev, out=y_dev)
+                self.forward(x_dev, out=y_dev, layout=layout)
                 ev_c.record(s_c)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_c)

@@ -78,11 +78,11 @@ class ShardedModel:
     def __len__(self):
         return len(self.devices)
 
-    def forward_on(self, slot: int, x: torch.Tensor) -> torch.Tensor:
+    def forward_on(self, slot: int, x: torch.Tensor, layout: str = "nchw") -> torch.Tensor:
         d = self.devices[slot % len(self.devices)]
         m = self.replicas[slot % len(self.devices)]
         with torch.cuda.device(d):
-            return m(x.to(torch.device("cuda", d), non_blocking=True))
+            return m.forward(x.to(torch.device("cuda", d), non_blocking=True), layout=layout)
 
 
 @torch.no_grad()
@@ -145,16 +145,17 @@ def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor
     inflight: list[torch.Tensor] = []
     n = 0
 
+    layout = "hwc_bgr" if bgr else "nchw"               # BGR frames: the tail conv stores HWC / BGR itself (no glue kernels)
+
     def drain(out: torch.Tensor):
         nonlocal n
-        o = out.flip(1) if bgr else out                 # RGB -> BGR on the device
-        o = o.permute(0, 2, 3, 1).contiguous().cpu().numpy()
+        o = (out if bgr else out.permute(0, 2, 3, 1).contiguous()).cpu().numpy()
         for f in o:
             sink.writeFrame(f)
             n += 1
 
     for i, frames in enumerate(batches):
-        out = sm.forward_on(i, frames) if sm else model(frames.to(model._device, non_blocking=True))
+        out = sm.forward_on(i, frames, layout) if sm else model.forward(frames.to(model._device, non_blocking=True), layout=layout)
         inflight.append(out)
         if len(inflight) >= G:                          # keep one unit in flight per device
             drain(inflight.pop(0))

@@ -40,6 +40,7 @@ extern "C" {
 #define SRB_F_PIXSHUF2 16  /* nn.PixelShuffle(2) folded into the store (utils/models.py:580-583)     */
 #define SRB_F_F32OUT 32    /* tail conv: fp32 NCHW output                                            */
 #define SRB_F_MASK 64      /* backward: output planes [mask_p0,mask_p1) *= LeakyReLU'(saved activation) */
+#define SRB_F_HWC_BGR 128  /* tail conv with SRB_F_U8OUT: store NHWC, channels reversed (rs.py:65-74 glue folded into the store) */
 
 typedef struct srb_ctx srb_ctx;
 typedef struct srb_weights srb_weights;
@@ -130,6 +131,13 @@ size_t srb_model_pt_workspace_bytes(int N, int H, int W);
 /* device uint8 NCHW -> device uint8 NCHW; replaces `model(window_img)` (rs.py:94) / `model(frames)` (rs.py:64) */
 int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uint8_t* out_nchw, int N, int H,
                          int W, void* workspace, size_t ws_bytes, srb_stream_t stream);
+/* The video path's output glue folded into the tail conv's store: out_layout SRB_LAYOUT_NHWC_BGR
+ * writes [N][H][W][3] with the channels reversed — what rs.py:65-74 builds from model(frames) with RGB2BGR
+ * (utils/datasets.py:113-124) + permute + contiguous before FFMPEG_recorder.writeFrame (utils/ffmpeg.py:69-76). */
+#define SRB_LAYOUT_NCHW_RGB 0
+#define SRB_LAYOUT_NHWC_BGR 1
+int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uint8_t* out, int out_layout, int N, int H,
+                                int W, void* workspace, size_t ws_bytes, srb_stream_t stream);
 /* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);

@@ -65,3 +65,26 @@ def test_stream_pipelined_host_batches_match_forward(model):
         assert torch.equal(a, b)
     with pytest.raises(RuntimeError):
         list(model.stream([torch.zeros(1, 3, 8, 8)]))
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 40, 48), (1, 3, 24, 200), (3, 3, 64, 64), (1, 3, 37, 61)])
+def test_hwc_bgr_store_equals_flip_permute_of_the_nchw_result(model, shape):
+    """RGB2BGR + NCHW->HWC (rs.py:65-74, utils/datasets.py:113-124) folded into the tail conv's store is
+    bit-identical to the glue applied to the NCHW result — direct call, pipelined host stream, and the tiled tail kernel."""
+    from image_super_resolution_b200._lib import Context
+    g = torch.Generator().manual_seed(13)
+    x = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g)
+    want = model(x.cuda()).flip(1).permute(0, 2, 3, 1).contiguous().cpu()
+    got = model.forward(x.cuda(), layout="hwc_bgr").cpu()
+    assert got.shape == (shape[0], shape[2], shape[3], 3) and torch.equal(got, want)
+    got_s = [y.clone() for y in model.stream(iter([x, x]), depth=2, layout="hwc_bgr")]
+    assert all(torch.equal(y, want) for y in got_s)
+    ctx = Context.get(0)
+    ctx.debug_set(2, 16384)                   # the tiled 9x9 tail kernel (fallback path) stores the same bytes
+    try:
+        got_t = model.forward(x.cuda(), layout="hwc_bgr").cpu()
+    finally:
+        ctx.debug_set(2, 0)
+    assert torch.equal(got_t, want)
+    with pytest.raises(RuntimeError):
+        model.forward(x, layout="hwc_bgr")    # host tensors go through stream()
