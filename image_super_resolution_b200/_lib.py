@@ -159,7 +159,7 @@ class GradJob(C.Structure):
 class PackJob(C.Structure):
     """srb_pack_job of include/srb200.h."""
     _fields_ = [("w", _vp), ("w_src", _vp), ("src_o", _i), ("src_i", _i), ("o_off", _i), ("c_off", _i), ("transpose", _i),
-                ("bias_src", _vp)]
+                ("bias_src", _vp), ("c_lo", _i), ("c_n", _i), ("scale", _f)]
 
 
 def f32_ptr(arr):

@@ -207,6 +207,7 @@ extern "C" int srb_pack_conv_device(srb_ctx* ctx, srb_weights* w, const float* w
     PackParams pp;
     pp.mode = w->mode; pp.c8in = w->c8in; pp.nout = w->nout; pp.kblocks = w->kblocks; pp.cout = w->cout; pp.cin = w->cin;
     pp.k = w->k; pp.src_i = src_i; pp.o_off = o_off; pp.c_off = c_off; pp.transpose = transpose;
+    pp.c_lo = 0; pp.c_n = 0; pp.scale = 1.f;
     pp.total = w->pack_bytes / 2;
     cudaStream_t st = (cudaStream_t)stream;
     int grid = (int)((pp.total + 255) / 256);
@@ -478,7 +479,13 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
             return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, true, false, true>(ctx, w, x, x_c8_total, p, st); } \
         if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, false, false, true>(ctx, w, x, x_c8_total, p, st); \
         return launch_conv<C8, NO, 3, 3, MODE_STD, NTT, false, false, true>(ctx, w, x, x_c8_total, p, st); }
-        SRB_BWD(4, 64, 4, 2) SRB_BWD(8, 64, 3, 2) SRB_BWD(4, 32, 4, 2)
+        SRB_BWD(4, 64, 4, 2) SRB_BWD(8, 64, 3, 2) SRB_BWD(4, 32, 4, 2) SRB_BWD(8, 32, 4, 2)
+        // gathered data gradients of a dense block (training.py): the transposed convs of ALL later layers as one conv over
+        // their concatenated output gradients -> the 32 channels of one earlier activation, masked by its LeakyReLU'
+        if (w->kblocks && w->nout == 32 && !(flags & SRB_F_RESIDUAL)) {
+            if (small) return launch_conv<4, 32, 3, 3, MODE_STD, 2, false, true, true>(ctx, w, x, x_c8_total, p, st);
+            return launch_conv<4, 32, 3, 3, MODE_STD, 4, false, true, true>(ctx, w, x, x_c8_total, p, st);
+        }
         SRB_BWD(4, 96, 2, 2) SRB_BWD(4, 128, 2, 2) SRB_BWD(4, 160, 1, 1)
         // 64 -> 96: the 108 KB filter leaves no room for a TMA residual ring; residual granules come through plain loads
         if (!w->kblocks && w->c8in == 8 && w->nout == 96) return launch_conv<8, 96, 3, 3, MODE_STD, 2, false, false, true>(ctx, w, x, x_c8_total, p, st);
@@ -1232,14 +1239,18 @@ extern "C" int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int
         const srb_pack_job& q = jobs[j];
         srb_weights* w = q.w;
         if (!w || !q.w_src) return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: NULL", j);
-        const int so_need = q.transpose ? q.c_off + w->cin : q.o_off + w->cout;
-        const int si_need = q.transpose ? q.o_off + w->cout : q.c_off + w->cin;
+        if (q.c_n < 0 || q.c_lo < 0 || (q.c_n > 0 && (q.c_lo + q.c_n > w->cin || w->mode != MODE_STD)))
+            return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: channel range [%d, +%d) of a %d-channel 3x3 operand", j, q.c_lo, q.c_n, w->cin);
+        const int ncin = q.c_n > 0 ? q.c_n : w->cin;
+        const int so_need = q.transpose ? q.c_off + ncin : q.o_off + w->cout;
+        const int si_need = q.transpose ? q.o_off + w->cout : q.c_off + ncin;
         if (q.o_off < 0 || q.c_off < 0 || so_need > q.src_o || si_need > q.src_i)
             return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: slice exceeds the source filter", j);
         PackJob& pj = v[j];
         pj.p.mode = w->mode; pj.p.c8in = w->c8in; pj.p.nout = w->nout; pj.p.kblocks = w->kblocks; pj.p.cout = w->cout;
         pj.p.cin = w->cin; pj.p.k = w->k; pj.p.src_i = q.src_i; pj.p.o_off = q.o_off; pj.p.c_off = q.c_off;
         pj.p.transpose = q.transpose; pj.p.total = w->pack_bytes / 2;
+        pj.p.c_lo = q.c_lo; pj.p.c_n = q.c_n; pj.p.scale = q.scale == 0.f ? 1.f : q.scale;
         pj.w = q.w_src; pj.pack = (uint16_t*)w->d_pack; pj.bias_src = q.transpose ? nullptr : q.bias_src; pj.bias_dst = w->d_bias;
         pj.bf16 = w->dtype == SRB_DT_BF16;
         if (pj.p.total > mx) mx = pj.p.total;

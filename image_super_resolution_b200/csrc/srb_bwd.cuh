@@ -13,6 +13,9 @@ namespace srb {
 struct PackParams {
     int mode, c8in, nout, kblocks, cout, cin, k;
     int src_i, o_off, c_off, transpose;
+    int c_lo, c_n;  // c_n > 0: this job fills only the packed input channels [c_lo, c_lo + c_n) (source channel = c - c_lo + c_off):
+                    // an operand whose input channels are gathered from several source filters (one job per source)
+    float scale;    // multiplies the source weights (a constant factor of the layer folded into the operand)
     size_t total;   // 16-bit elements of the packed operand
 };
 
@@ -51,11 +54,16 @@ __device__ __forceinline__ void pack_conv_element(const float* __restrict__ w, u
         c = (2 * c2 + g) * 8 + j;
         valid = n < 27;
     }
+    if (p.c_n > 0) {
+        if (c < p.c_lo || c >= p.c_lo + p.c_n) return;     // another job's channels
+        c -= p.c_lo;
+    }
     float v = 0.f;
     if (valid) {
         const int kk = p.k * p.k;
         if (p.transpose) v = w[((size_t)(p.c_off + c) * p.src_i + p.o_off + o) * kk + (p.k - 1 - dy) * p.k + (p.k - 1 - dx)];
         else v = w[((size_t)(p.o_off + o) * p.src_i + p.c_off + c) * kk + dy * p.k + dx];
+        v *= p.scale;
     }
     uint16_t r;
     if constexpr (BF16) { __nv_bfloat16 h = __float2bfloat16_rn(v); r = *reinterpret_cast<uint16_t*>(&h); }

@@ -295,13 +295,16 @@ class GradBatch:
 
 class PackBatch:
     """All packed operands of a net re-derived from the fp32 master weights in one launch (srb_pack_batch_*).
-    jobs: (DeviceConv, weight, bias_or_None, o_off, c_off, transpose)."""
+    jobs: (DeviceConv, weight, bias_or_None, o_off, c_off, transpose[, c_lo, c_n, scale]) — the optional tail fills only the
+    operand's input channels [c_lo, c_lo + c_n) (gathered operands: one job per source filter) with scaled weights."""
 
     def __init__(self, ctx: Context, jobs: list[tuple]):
         self.ctx = ctx
         self._keep = jobs
         arr = (_lib.PackJob * len(jobs))()
-        for a, (pc, w, b, o_off, c_off, tr) in zip(arr, jobs):
+        for a, job in zip(arr, jobs):
+            pc, w, b, o_off, c_off, tr = job[:6]
+            a.c_lo, a.c_n, a.scale = (job[6], job[7], float(job[8])) if len(job) > 6 else (0, 0, 1.0)
             if w.dtype != torch.float32 or not w.is_cuda or not w.is_contiguous():
                 raise RuntimeError("master weights must be contiguous fp32 CUDA tensors")
             a.w, a.w_src, a.src_o, a.src_i = pc.handle, w.data_ptr(), w.shape[0], w.shape[1]

@@ -59,8 +59,11 @@ class TrainPlan:
             for rrdb in net.residual:
                 for rdb in rrdb.net:
                     fwd = [mk(32, 64 + 32 * i, 3) for i in range(4)] + [mk(64, 192, 3)]
-                    dg = [[mk(co, 32, 3) for co in _chunks(64 + 32 * i)] for i in range(4)] + [[mk(co, 64, 3) for co in _chunks(192)]]
-                    self.rdbs.append((rrdb, rdb, fwd, dg))
+                    # data gradients, gathered: stage k = ONE conv over the concatenated output gradients of all later convs
+                    # [dY4 (64) | dY3 | .. | dY_{k+1}] -> the 32 channels of o_k; fin = all five -> the 64 input channels
+                    stage = [mk(32, 64 + 32 * (3 - k), 3) for k in range(4)]
+                    fin = mk(64, 192, 3)
+                    self.rdbs.append((rrdb, rdb, fwd, stage, fin))
             self.f_conv1, self.d_conv1 = mk(64, 64, 3), mk(64, 64, 3)
             self.f_scaler = [[mk(64, 64, 3) for _ in range(4)] for _ in net.scaler]
             self.d_scaler = [mk(64, 256, 3) for _ in net.scaler]
@@ -93,15 +96,24 @@ class TrainPlan:
     def _pack_jobs(self):
         n = self.net
         jobs = [(self.f_conv0, n.conv0.conv.weight.data, n.conv0.conv.bias.data, 0, 0, False)]
-        for _, rdb, fwd, dg in self.rdbs:
+        for r, (rrdb, rdb, fwd, stage, fin) in enumerate(self.rdbs):
+            Wt = []
             for i in range(5):
                 m = getattr(rdb, f"conv{i}") if i < 4 else rdb.conv
                 w, b = m.conv.weight.data, m.conv.bias.data
                 jobs.append((fwd[i], w, b, 0, 0, False))
-                o = 0
-                for pk in dg[i]:
-                    jobs.append((pk, w, None, o, 0, True))
-                    o += pk.cout
+                Wt.append(w)
+            # transposed / rotated filters of the gathered data-gradient convs: input channels [0,64) come from conv4 (times
+            # the block's output scale), [64 + 32(3-j), +32) from conv_j; output channels = source input channels o_off..
+            s_out = float(rdb.add_rate) * (float(rrdb.add_rate) if r % 3 == 2 else 1.0)
+            for k in range(4):
+                o_off = 64 + 32 * k
+                jobs.append((stage[k], Wt[4], None, o_off, 0, True, 0, 64, s_out))
+                for j in range(3, k, -1):
+                    jobs.append((stage[k], Wt[j], None, o_off, 0, True, 64 + 32 * (3 - j), 32, 1.0))
+            jobs.append((fin, Wt[4], None, 0, 0, True, 0, 64, s_out))
+            for j in range(3, -1, -1):
+                jobs.append((fin, Wt[j], None, 0, 0, True, 64 + 32 * (3 - j), 32, 1.0))
         jobs.append((self.f_conv1, n.conv1.conv.weight.data, n.conv1.conv.bias.data, 0, 0, False))
         jobs.append((self.d_conv1, n.conv1.conv.weight.data, None, 0, 0, True))
         for s, fq, dq in zip(n.scaler, self.f_scaler, self.d_scaler):
@@ -207,7 +219,7 @@ class TrainPlan:
         tr = self._b("tr", N, 8, H, W)
         s0 = _slope_of(n.conv0.act)
         cv(self.f_conv0, xin, 1, 0, dense[0], 24, 0, N, H, W, slope=s0, flags=ops.F_LRELU)     # x0 = planes 0..7 of dense[0]
-        for r, (rrdb, rdb, fwd, _) in enumerate(self.rdbs):
+        for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
             D = dense[r]
             dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
             for i in range(4):
@@ -279,59 +291,35 @@ class TrainPlan:
         g_t = g_cur                                         # gradient of t = x0 + conv1(trunk)
         # ---- conv1
         self._wb(n.conv1, sv["tr"], 8, 0, 64, g_t, 8, 0, 64, N, H, W)
-        gy, gy_planes = self._b("g_tr", N, 8, H, W), 8     # gradient of the current RRDB's output
-        cv(self.d_conv1, g_t, 8, 0, gy, 8, 0, N, H, W)
-        # ---- RRDBs, last to first
+        # ---- RRDBs, last to first.  Every RDB owns a dense GRADIENT buffer G (24 planes, kept: the deferred weight gradients
+        # read it) that mirrors the forward's dense activation buffer: planes 0..7 = gy (gradient of the RDB's output, written
+        # by the block behind it), then dY3, dY2, dY1, dY0 (gradients of the pre-activations of o3 .. o0), each produced by
+        # one conv over everything to its left — no read-modify-write passes, fp32 accumulation over all sources.
         nr = len(self.rdbs)
-        Gs = [self._b(f"G{j}", N, 24, H, W) for j in range(nr)]    # kept per RDB: the deferred weight gradients read them
+        Gd = [self._b(f"G{j}", N, 24, H, W) for j in range(nr)]
+        gxf = self._b("g_x0t", N, 8, H, W)                  # gradient of x0 through the trunk
+        cv(self.d_conv1, g_t, 8, 0, Gd[nr - 1], 24, 0, N, H, W)
         for r in range(nr - 1, -1, -1):
-            rrdb, rdb, _, dg = self.rdbs[r]
-            D = sv["dense"][r]
+            rrdb, rdb, _, stage, fin = self.rdbs[r]
+            D, G = sv["dense"][r], Gd[r]
             d = r % 3
             a, R = float(rdb.add_rate), float(rrdb.add_rate)
-            if d == 2:                                      # start of an RRDB (backward order)
-                gsrc, gsrc_planes = gy, gy_planes
-                s_out, s_res = a * R, R
-            else:
-                gsrc, gsrc_planes = G, 24
-                s_out, s_res = a, 1.0
-            G = Gs[r]
+            s_out, s_res = (a * R, R) if d == 2 else (a, 1.0)          # utils/models.py:271 / :317
             sl = [_slope_of(getattr(rdb, f"conv{i}").act) for i in range(4)]
-            # final conv 192 -> 64 (no activation): out = s_out*conv(cat) + s_res*rdb_in
-            self._wb(rdb.conv, D, 24, 0, 192, gsrc, gsrc_planes, 0, 64, N, H, W, scale=s_out)
-            o = 0
-            for pk in dg[4]:
-                p0, pl = o // 8, pk.cout // 8
-                kw = {}
-                if p0 == 0:                                 # + s_res * (gradient of the RDB output) on the rdb_in planes
-                    kw = dict(residual=gsrc, res_planes=gsrc_planes, res_off=0, res_nplanes=8, res_scale=s_res)
-                if p0 + pl > 20:                            # planes 20..23 = o_3: final after this launch
-                    kw.update(mask=D, mask_planes=24, mask_off=p0, mask_p0=20 - p0, mask_p1=24 - p0, mask_slope=sl[3])
-                cv(pk, gsrc, gsrc_planes, 0, G, 24, p0, N, H, W, out_scale=s_out, **kw)
-                o += pk.cout
-            # conv3..conv0: dY = masked slice of G, accumulate the data gradient into planes below it
-            for i in range(3, -1, -1):
-                cin = 64 + 32 * i
-                dy_off = 8 + 4 * i
-                self._wb(getattr(rdb, f"conv{i}"), D, 24, 0, cin, G, 24, dy_off, 32, N, H, W)
-                o = 0
-                for pk in dg[i]:
-                    p0, pl = o // 8, pk.cout // 8
-                    kw = dict(residual=G, res_planes=24, res_off=p0, res_scale=1.0)
-                    if i > 0:
-                        m0, m1 = 8 + 4 * (i - 1), 8 + 4 * i          # planes of o_{i-1}: final after this launch
-                        lo, hi = max(m0, p0), min(m1, p0 + pl)
-                        if lo < hi:
-                            kw.update(mask=D, mask_planes=24, mask_off=p0, mask_p0=lo - p0, mask_p1=hi - p0, mask_slope=sl[i - 1])
-                    elif d == 0:                                      # + the RRDB skip (utils/models.py:317)
-                        kw.update(res2=gy, res2_planes=gy_planes, res2_off=0, res2_scale=1.0)
-                    cv(pk, G, 24, dy_off, G, 24, p0, N, H, W, **kw)
-                    o += pk.cout
-            if d == 0:
-                gy, gy_planes = G, 24
+            self._wb(rdb.conv, D, 24, 0, 192, G, 24, 0, 64, N, H, W, scale=s_out)
+            for k in range(3, -1, -1):
+                nin = 8 + 4 * (3 - k)                                   # gy + dY3 .. dY_{k+1}
+                cv(stage[k], G, 24, 0, G, 24, nin, N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k, mask_p0=0, mask_p1=4,
+                   mask_slope=sl[k])
+                self._wb(getattr(rdb, f"conv{k}"), D, 24, 0, 64 + 32 * k, G, 24, nin, 32, N, H, W)
+            dst, dplanes = (Gd[r - 1], 24) if r > 0 else (gxf, 8)
+            kw = dict(residual=G, res_planes=24, res_off=0, res_scale=s_res)
+            if d == 0:                                                  # + the RRDB skip (utils/models.py:317)
+                kw.update(res2=Gd[r + 2], res2_planes=24, res2_off=0, res2_scale=1.0)
+            cv(fin, G, 24, 0, dst, dplanes, 0, N, H, W, **kw)
         # ---- head conv: total gradient of x0 = trunk path + long skip, LeakyReLU', 9x9 weight gradient
         gx0 = self._b("gx0", N, 8, H, W)
-        ops.c8_axpby_mask(gy, gy_planes, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
+        ops.c8_axpby_mask(gxf, 8, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
         ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.weight)], N, H, W)
         if self._gjobs is not None:
             self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=self.grad_views[id(n.conv0.conv.bias)], N=N, H=H, W=W))

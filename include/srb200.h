@@ -266,9 +266,14 @@ int srb_grad_batch_units(const srb_grad_batch* b);
 int srb_grad_batch_run(srb_ctx* ctx, srb_grad_batch* b, int splitk, srb_stream_t stream);
 void srb_grad_batch_destroy(srb_grad_batch* b);
 
-/* Batched srb_pack_conv_device: all packed operands of a net re-derived from the fp32 masters in one launch. */
+/* Batched srb_pack_conv_device: all packed operands of a net re-derived from the fp32 masters in one launch.
+ * c_n > 0: the job fills only the operand's input channels [c_lo, c_lo + c_n) from source channels c_off .. (3x3 operands):
+ * an operand whose input channels are gathered from several source filters takes one job per source — the data-gradient
+ * convs of a dense block read the concatenated output gradients of all later convs (training.py).  scale (0 = 1) multiplies
+ * the source weights. */
 typedef struct srb_pack_job {
     srb_weights* w; const float* w_src; int src_o, src_i, o_off, c_off, transpose; const float* bias_src;
+    int c_lo, c_n; float scale;
 } srb_pack_job;
 typedef struct srb_pack_batch srb_pack_batch;
 int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int n, srb_pack_batch** out);
