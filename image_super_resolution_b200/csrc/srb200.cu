@@ -1213,8 +1213,9 @@ extern "C" int srb_grad_batch_run(srb_ctx* ctx, srb_grad_batch* b, int splitk, s
         CUDA_TRY(cudaGetLastError());
     }
     if (b->nbias) {
-        if (b->dtype == SRB_DT_BF16) bias_grad_batch_kernel<true><<<b->nbias, 256, 0, st>>>(b->d_bias);
-        else bias_grad_batch_kernel<false><<<b->nbias, 256, 0, st>>>(b->d_bias);
+        const dim3 bg(b->nbias, 64);
+        if (b->dtype == SRB_DT_BF16) bias_grad_batch_kernel<true><<<bg, 256, 0, st>>>(b->d_bias);
+        else bias_grad_batch_kernel<false><<<bg, 256, 0, st>>>(b->d_bias);
         CUDA_TRY(cudaGetLastError());
     }
     return SRB_OK;
