@@ -464,7 +464,8 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     // Small problems (a training batch: 16 x 64 x 64 px = 512 M-tiles for 148 SMs): with NT = 4 a CTA gets ONE super-tile and
     // its load, MMAs and epilogue run back to back; two-tile super-tiles give every CTA two pipeline steps that overlap.
     const long long mtiles = (long long)((W + 7) / 8) * ((H + 15) / 16) * N;
-    const bool small = mtiles < (long long)ctx->num_sms * 6 && !(ctx->dbg_skip & 65536);   // (debug bit 65536: always the large-problem tiling)
+    const bool small0 = mtiles < (long long)ctx->num_sms * 6 && !(ctx->dbg_skip & 65536);   // (debug bit 65536: always the large-problem tiling)
+    const bool small = small0 && !((ctx->dbg_skip & 262144) && w->kblocks);               // (debug bit 262144: large tiling for the weight-streaming kernels)
 #define SRB_STD(C8, NO, NTT, NTS) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) { \
             if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, true>(ctx, w, x, x_c8_total, p, st); \
