@@ -153,7 +153,11 @@ class FlatAdam(torch.optim.Optimizer):
 
     def zero_grad(self, set_to_none: bool = True):
         self._stats_valid, self._scale, self._max_norm = False, None, 0.0
-        super().zero_grad(set_to_none=set_to_none)
+        if set_to_none:                # the gradients are views of the arena backward rewrites: dropping them is all there is to do
+            for p in self.param_groups[0]["params"]:
+                p.grad = None
+        else:
+            super().zero_grad(set_to_none=False)
 
     def load_state_dict(self, state_dict):
         """torch's format; the loaded moments are copied INTO the flat arenas (the views must stay views)."""

@@ -125,16 +125,18 @@ class TrainPlan:
         jobs.append((self.d_conv2, n.conv2.conv.weight.data, None, 0, 0, True))
         return jobs
 
-    def repack(self):
+    def repack(self, ptrs=None, track_versions=True):
         """fp32 master weights (device) -> bf16 UMMA operands, forward and data-gradient layouts: one launch."""
-        ptrs = tuple(p.data_ptr() for p in self.params)
+        if ptrs is None:
+            ptrs = tuple(p.data_ptr() for p in self.params)
         if self.pack_batch is None or self.pack_ptrs != ptrs:
             for p in self.params:
                 if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
                     raise RuntimeError("training needs contiguous fp32 CUDA parameters (model.to(device) first)")
             self.pack_batch, self.pack_ptrs = ops.PackBatch(self.ctx, self._pack_jobs()), ptrs
         self.pack_batch.run(self.device)
-        self.versions = self._versions()
+        if track_versions:             # (eager mode re-packs only when a parameter changed; graph mode re-packs every forward)
+            self.versions = self._versions()
 
     def _b(self, name, N, planes, H, W):
         key = (name, N, planes, H, W)
@@ -150,7 +152,7 @@ class TrainPlan:
 
     # ---- CUDA graphs: the step is ~2 000 launches of 5-20 us kernels, host-bound from Python otherwise ------------
     def _graph_key(self, x):
-        return (tuple(x.shape), tuple(p.data_ptr() for p in self.params))
+        return (tuple(x.shape), tuple(p.data_ptr() for p in self.params))      # one pass over the parameters per forward
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not self.use_graphs:
@@ -175,7 +177,7 @@ class TrainPlan:
                 self._pdl(False)
             self.graphs["fwd"] = g
             self.graphs["saved"] = self.saved
-        self.repack()
+        self.repack(key[1], track_versions=False)     # the host path between two steps is GPU idle time (loss.item() syncs)
         self.graphs["x"].copy_(x)
         self.graphs["fwd"].replay()
         self.saved = self.graphs["saved"]
