@@ -177,3 +177,37 @@ def test_train_loop_with_fused_tail_matches_torch_tail(dev):
         cos = float((d0 @ d1) / (d0.norm() * d1.norm()))
         assert cos >= 0.995, cos
         assert abs(float(d0.norm() / d1.norm()) - 1.0) <= 0.02
+
+
+def test_flat_adam_state_dict_interchanges_with_torch_adam(dev):
+    """train.py:277-300 saves / restores `optimizer.state_dict()`: a torch.optim.Adam checkpoint loads into FlatAdam (the
+    moments land in the flat arenas, the views stay views) and the next step matches torch's; FlatAdam's own state_dict
+    loads back into torch.optim.Adam."""
+    from image_super_resolution_b200.optim import FlatAdam
+    torch.manual_seed(4)
+    ref, ours = _Toy().to(dev), _Toy().to(dev)
+    ours.load_state_dict(ref.state_dict())
+    pr, po = list(ref.parameters()), list(ours.parameters())
+    opt_r = torch.optim.Adam(pr, lr=1e-3)
+    for _ in range(3):
+        for p in pr:
+            p.grad = torch.randn_like(p)
+        opt_r.step()
+    ours.load_state_dict(ref.state_dict())
+    opt_o = FlatAdam(po, lr=5e-4)
+    opt_o.load_state_dict(opt_r.state_dict())
+    assert opt_o.param_groups[0]["lr"] == 1e-3
+    assert float(opt_o.state[po[0]]["step"]) == 3.0
+    assert opt_o.state[po[0]]["exp_avg"].data_ptr() == opt_o.m_arena.data_ptr()          # still a view of the arena
+    gs = [torch.randn_like(p) for p in pr]
+    for p, g in zip(pr, gs):
+        p.grad = g.clone()
+    _set_flat_grads(po, gs)
+    opt_r.step(); opt_o.step()
+    for a, b in zip(po, pr):
+        assert _close(a.data, b.data)
+    back = torch.optim.Adam([torch.nn.Parameter(p.detach().clone()) for p in po], lr=1.0)
+    back.load_state_dict(opt_o.state_dict())
+    for q, b in zip(back.param_groups[0]["params"], pr):
+        assert _close(back.state[q]["exp_avg"], opt_r.state[b]["exp_avg"])
+        assert float(back.state[q]["step"]) == 4.0
