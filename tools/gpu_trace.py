@@ -9,7 +9,10 @@ from image_super_resolution_b200._lib import Context, lib, check
 dev = torch.device("cuda:0"); ctx = Context.get(0)
 N, H, W = (int(sys.argv[1]) if len(sys.argv) > 1 else 256), 64, 64
 GHZ = 1.9
-for cout, cin, k, residual in ((32, 64, 3, 0), (64, 32, 3, 1), (64, 64, 3, 1), (64, 3, 9, 0), (3, 64, 9, 0)):
+CASES = ((32, 64, 3, 0), (64, 32, 3, 1), (64, 64, 3, 1), (64, 3, 9, 0), (3, 64, 9, 0))
+if len(sys.argv) > 2 and sys.argv[2] == "dense":      # the dense blocks' weight-streaming convs
+    CASES = ((32, 128, 3, 0), (32, 160, 3, 0), (64, 192, 3, 1))
+for cout, cin, k, residual in CASES:
     g = torch.Generator().manual_seed(0)
     pc = ops.PackedConv(ctx, torch.randn(cout, cin, k, k, generator=g) * 0.05, torch.zeros(cout))
     pin = max(1, cin // 8)
