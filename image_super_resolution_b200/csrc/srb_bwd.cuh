@@ -1,6 +1,7 @@
 // Backward-pass helpers of the training step (train.py:57 autograd through utils/models.py:645-650):
-// device-side operand packing from fp32 master weights, the elementwise backward glue that cannot be an
-// epilogue (tanh', PixelShuffle inverse, gradient fan-in) and the 9x9 weight gradients of the head / tail convs.
+// device-side operand packing from fp32 master weights (also operands gathered from several source filters: the
+// data-gradient convs of a dense block) and the elementwise backward glue that cannot be an epilogue (tanh',
+// PixelShuffle inverse, gradient fan-in).  Weight / bias gradients: srb_wgrad.cuh.
 #pragma once
 #include "srb_ptx.cuh"
 #include "srb_elem.cuh"
