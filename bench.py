@@ -274,12 +274,13 @@ def run_ours(args, rank, world, local):
     def host_batches(n):
         for _ in range(n):
             yield x_host
-    for yh in model.stream(host_batches(3)):
+    depth = int(os.environ.get("SRB_STREAM_DEPTH", "2"))
+    for yh in model.stream(host_batches(3 + depth), depth=depth):
         pass
     barrier()
     e0.record()
     n_out = 0
-    for yh in model.stream(host_batches(K)):
+    for yh in model.stream(host_batches(K), depth=depth):
         n_out += 1
     y_host.copy_(yh)
     e1.record()
@@ -343,7 +344,7 @@ def run_ours(args, rank, world, local):
                 "clocks": clocks,
                 "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": x_host.numel(),
                         "d2h_bytes_per_step": y_host.numel(), "ms_per_step": ms_e2e / K,
-                        "api": "ModelPT.stream(host batches): pinned H2D + forward + D2H per step, two batches in flight"},
+                        "api": f"ModelPT.stream(host batches): pinned H2D + forward + D2H per step, {depth} batches in flight"},
                 "gpu_launches": nl * K,
                 "roofline": roofline}
         if train_line is not None:

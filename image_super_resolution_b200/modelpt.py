@@ -165,56 +165,82 @@ class ModelPT:
     __call__ = forward
 
     @torch.no_grad()
-    def stream(self, batches, depth: int = 2, layout: str = "nchw"):
+    def stream(self, batches, depth: int = 2, layout: str = "nchw", graphs: bool = True):
         """Pipelined host-to-host inference over a sequence of uint8 host batches — the shape of rs.py's video loop
         (rs.py:58-76: frames from the reader -> model -> writer).  Yields one pinned uint8 host tensor per input batch, in
         order.  H2D of batch i+1 and D2H of batch i-1 run on copy streams while the kernels of batch i run on the compute
         stream; `depth` batches are in flight.  A yielded tensor is valid until `depth` more batches have been consumed
-        (its buffer is then reused): write it out or copy it before asking for more, as a frame writer does."""
+        (its buffer is then reused): write it out or copy it before asking for more, as a frame writer does.
+        The ring of device / pinned buffers is kept on the model between calls, and (graphs=True) the 12 launches of a slot's
+        forward are captured once per (slot, shape) as a CUDA graph: a step costs the host three enqueues, which is what
+        keeps eight ranks sharing one host at the single-GPU rate."""
         if self._net is None:
             raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
+        if layout not in ("nchw", "hwc_bgr"):
+            raise ValueError(f"layout {layout!r}")
         depth = max(1, int(depth))
         dev = self._device
-        s_in, s_c, s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        st = self.__dict__.get("_stream_state")
+        if st is None or st["net"] is not self._net or st["dev"] != dev:
+            st = self.__dict__["_stream_state"] = dict(net=self._net, dev=dev, slots={},
+                                                       streams=tuple(torch.cuda.Stream(dev) for _ in range(3)))
+        s_in, s_c, s_out = st["streams"]
         nbuf = depth + 1
-        slots = [None] * nbuf          # per slot: (x_dev, y_dev, y_host, ev_in, ev_c, ev_out, shape)
-        pending = []                   # slot indices submitted and not yet yielded
+        pending = []                   # slots submitted and not yet yielded
         i = 0
+
+        def make_slot(shape):
+            oshape = shape if layout == "nchw" else (shape[0], shape[2], shape[3], 3)
+            x_dev = torch.empty(shape, dtype=torch.uint8, device=dev)
+            y_dev = torch.empty(oshape, dtype=torch.uint8, device=dev)
+            y_host = torch.empty(oshape, dtype=torch.uint8).pin_memory()
+            g = None
+            if graphs:
+                with torch.cuda.stream(s_c):               # eager once: workspace, tensor-map caches, kernel attributes
+                    self.forward(x_dev, out=y_dev, layout=layout)
+                torch.cuda.synchronize(dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=s_c):
+                    self.forward(x_dev, out=y_dev, layout=layout)
+            # (the captured launches hold the address of the workspace they were recorded with: the slot keeps it alive)
+            return (x_dev, y_dev, y_host, torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event(), g, self._ws)
+
         for xb in batches:
             if xb.dtype != torch.uint8 or xb.dim() != 4 or xb.shape[1] != 3 or xb.is_cuda:
                 raise RuntimeError("stream() takes uint8 host tensors [N,3,H,W]")
             xb = xb.contiguous()
-            k = i % nbuf
             if len(pending) == nbuf:                       # the slot about to be reused must have been consumed
                 raise RuntimeError("internal: ring overrun")
-            sl = slots[k]
-            if sl is None or sl[6] != tuple(xb.shape):
-                oshape = tuple(xb.shape) if layout == "nchw" else (xb.shape[0], xb.shape[2], xb.shape[3], 3)
-                sl = (torch.empty(xb.shape, dtype=torch.uint8, device=dev), torch.empty(oshape, dtype=torch.uint8, device=dev),
-                      torch.empty(oshape, dtype=torch.uint8).pin_memory(), torch.cuda.Event(), torch.cuda.Event(),
-                      torch.cuda.Event(), tuple(xb.shape))
-                slots[k] = sl
-            x_dev, y_dev, y_host, ev_in, ev_c, ev_out, _ = sl
+            key = (i % nbuf, nbuf, layout, tuple(xb.shape), bool(graphs))
+            sl = st["slots"].get(key)
+            if sl is None:
+                for j in pending:                          # (capturing synchronises: nothing may be in flight on a slot)
+                    j[5].synchronize()
+                sl = st["slots"][key] = make_slot(tuple(xb.shape))
+            x_dev, y_dev, y_host, ev_in, ev_c, ev_out, g, _ = sl
             with torch.cuda.stream(s_in):
                 x_dev.copy_(xb, non_blocking=True)
                 ev_in.record(s_in)
             with torch.cuda.stream(s_c):
                 s_c.wait_event(ev_in)
-                self.forward(x_dev, out=y_dev, layout=layout)
+                if g is not None:
+                    g.replay()
+                else:
+                    self.forward(x_dev, out=y_dev, layout=layout)
                 ev_c.record(s_c)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_c)
                 y_host.copy_(y_dev, non_blocking=True)
                 ev_out.record(s_out)
-            pending.append(k)
+            pending.append(sl)
             i += 1
             if len(pending) > depth:
                 j = pending.pop(0)
-                slots[j][5].synchronize()
-                yield slots[j][2]
+                j[5].synchronize()
+                yield j[2]
         for j in pending:
-            slots[j][5].synchronize()
-            yield slots[j][2]
+            j[5].synchronize()
+            yield j[2]
 
     @staticmethod
     def launches_per_forward(H: int = 64, W: int = 64) -> int:
