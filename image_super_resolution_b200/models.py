@@ -17,7 +17,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
-from . import ops
+from . import ops, _lib
 from ._lib import Context
 
 
@@ -122,6 +122,8 @@ class _NetPlan:
         self.versions = None
         self.net = net
         self.buffers = {}
+        self.use_graphs = True      # the ~260 launches of a forward are captured once per input shape (host-bound otherwise)
+        self.graphs = {}
         self.repack()
 
     def _pack(self, m, cout_slice=None):
@@ -155,21 +157,47 @@ class _NetPlan:
             self.scalers = [[self._pack(s.net[0], slice(64 * q, 64 * q + 64)) for q in range(4)] for s in n.scaler]
             self.conv2 = self._pack(n.conv2)
         self.versions = self._param_versions()
+        self.graphs = {}            # captured launches hold the addresses of the previous packed filters
 
     def _buf(self, name, N, planes, H, W):
         key = (name, N, planes, H, W)
         if key not in self.buffers:
-            self.buffers = {k: v for k, v in self.buffers.items() if k[0] != name}
+            if not self.graphs:     # (captured graphs of other shapes still use their buffers)
+                self.buffers = {k: v for k, v in self.buffers.items() if k[0] != name}
             self.buffers[key] = ops.c8_empty(N, planes, H, W, self.dtype, self.device)
         return self.buffers[key]
 
     @torch.no_grad()
     def forward(self, x: torch.Tensor, u8_out: bool = False, x_is_c8: torch.Tensor | None = None) -> torch.Tensor:
-        n = self.net
         if self.versions != self._param_versions():
             self.repack()   # parameters changed (optimizer step / load_state_dict): derived caches are re-derived
         N, _, H, W = x.shape
         xin = x_is_c8 if x_is_c8 is not None else ops.nchw_to_c8(x, dtype=self.dtype)          # 1 plane (3 ch + zeros)
+        if not self.use_graphs:
+            return self._run(xin, N, H, W, u8_out)
+        key = (N, H, W, bool(u8_out))
+        st = self.graphs.get(key)
+        if st is None:
+            if len(self.graphs) >= 8:                     # many different shapes (ragged tiles): start over
+                self.graphs, self.buffers = {}, {}
+            xs = xin.clone()
+            self._run(xs, N, H, W, u8_out)                # eager once: buffers, kernel attributes
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 1), "srb_set_programmatic_launch")
+            try:                                          # the filters are constants of the graph: its conv nodes are chained
+                with torch.cuda.graph(g):                 # by programmatic dependent launch edges
+                    out = self._run(xs, N, H, W, u8_out)
+            finally:
+                _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 0), "srb_set_programmatic_launch")
+            st = self.graphs[key] = (g, xs, out)
+        g, xs, out = st
+        xs.copy_(xin)
+        g.replay()
+        return out.clone()
+
+    def _run(self, xin: torch.Tensor, N: int, H: int, W: int, u8_out: bool) -> torch.Tensor:
+        n = self.net
         dense = [self._buf(f"dense{i}", N, 24, H, W) for i in range(3)]
         x0 = self._buf("x0", N, 8, H, W)
         s0, f0 = _slope(n.conv0.act)

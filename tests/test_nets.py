@@ -96,3 +96,36 @@ def test_gpu_model_wrapper_uint8_fuse(gold):
     ref = ((t + 1) / 2 * 255).round().to(torch.uint8)
     assert y.dtype == torch.uint8 and y.shape == ref.shape
     assert (y.int() - ref.int()).abs().max().item() <= 2
+
+
+@pytest.mark.gpu
+def test_gpu_captured_forward_replays_correctly():
+    """models._NetPlan captures the forward's launches per input shape (CUDA graph with programmatic edges): replays on new
+    inputs, other shapes in between and a parameter change (re-pack => re-capture) give what eager launches give, bit for bit."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from image_super_resolution_b200 import models
+    dev = torch.device("cuda:0")
+    torch.manual_seed(100)
+    net = models.EResNet(1, 0.2, 2).to(dev).eval()
+    g = torch.Generator().manual_seed(5)
+    xs = [torch.randn(2, 3, 24, 40, generator=g).to(dev), torch.randn(2, 3, 24, 40, generator=g).to(dev),
+          torch.randn(1, 3, 33, 17, generator=g).to(dev)]
+    plan = net._plan(dev)
+
+    def eager(x):
+        plan.use_graphs = False
+        try:
+            return net(x)
+        finally:
+            plan.use_graphs = True
+
+    with torch.no_grad():
+        want = [eager(x) for x in xs]
+        for i in (0, 1, 2, 0, 2, 1):
+            assert torch.equal(net(xs[i]), want[i]), i
+        assert len(plan.graphs) == 2
+        net.conv1.conv.weight.mul_(1.5)                      # parameters changed: packed filters and graphs are re-derived
+        w2 = eager(xs[0])
+        assert not torch.equal(w2, want[0])
+        assert torch.equal(net(xs[0]), w2)
