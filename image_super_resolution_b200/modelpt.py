@@ -200,7 +200,7 @@ class ModelPT:
                     self.forward(x_dev, out=y_dev, layout=layout)
                 torch.cuda.synchronize(dev)
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=s_c):
+                with torch.cuda.graph(g, stream=s_c, capture_error_mode="thread_local"):   # (NCCL watchdog / sampler threads may call CUDA)
                     self.forward(x_dev, out=y_dev, layout=layout)
             # (the captured launches hold the address of the workspace they were recorded with: the slot keeps it alive)
             return (x_dev, y_dev, y_host, torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event(), g, self._ws)

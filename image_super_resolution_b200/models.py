@@ -186,7 +186,7 @@ class _NetPlan:
             g = torch.cuda.CUDAGraph()
             _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 1), "srb_set_programmatic_launch")
             try:                                          # the filters are constants of the graph: its conv nodes are chained
-                with torch.cuda.graph(g):                 # by programmatic dependent launch edges
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):     # by programmatic dependent launch edges
                     out = self._run(xs, N, H, W, u8_out)
             finally:
                 _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 0), "srb_set_programmatic_launch")

@@ -171,7 +171,7 @@ class TrainPlan:
             g = torch.cuda.CUDAGraph()
             self._pdl(True)
             try:
-                with torch.cuda.graph(g):
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
                     self.graphs["out"] = self._forward_impl(self.graphs["x"])
             finally:
                 self._pdl(False)
@@ -196,7 +196,7 @@ class TrainPlan:
                 g = torch.cuda.CUDAGraph()
                 self._pdl(True)
                 try:
-                    with torch.cuda.graph(g):
+                    with torch.cuda.graph(g, capture_error_mode="thread_local"):
                         self.graphs["grads"] = self._backward_impl(self.graphs["gout"])
                 finally:
                     self._pdl(False)
