@@ -97,12 +97,22 @@ struct srb_net {
     int dtype;
 };
 
+// The library works on the context's device and leaves the caller's current device as it found it (PyTorch tracks the
+// runtime's current device: a replica created for cuda:1 must not redirect the caller's later .cuda() calls).
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int d) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; if (prev != d) cudaSetDevice(d); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 extern "C" int srb_create(int device, srb_ctx** out) {
     if (!out) return fail(SRB_EINVAL, "srb_create: out is NULL");
     int ndev = 0;
     CUDA_TRY(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(SRB_EINVAL, "srb_create: device %d of %d", device, ndev);
-    CUDA_TRY(cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10)
@@ -125,7 +135,7 @@ extern "C" int srb_create(int device, srb_ctx** out) {
 
 extern "C" void srb_destroy(srb_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->device);
+    DeviceGuard dev_guard(c->device);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     if (c->d_io) cudaFree(c->d_io);
     if (c->d_ws) cudaFree(c->d_ws);
@@ -185,7 +195,7 @@ extern "C" int srb_alloc_conv(srb_ctx* ctx, int cout, int cin, int k, int dtype,
     sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
     sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
     sw->pack_bytes = (size_t)ksteps * 2 * nout * 8 * 2;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
         srb_free_weights(sw);
         return fail(SRB_ENOMEM, "srb_alloc_conv: cudaMalloc failed");
@@ -272,7 +282,7 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
     sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
     sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
     sw->pack_bytes = pack.size() * 2;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
         delete sw;
         return fail(SRB_ENOMEM, "srb_pack_conv: cudaMalloc failed");
@@ -302,7 +312,7 @@ extern "C" int srb_pack_conv_pair4(srb_ctx* ctx, const float* w, const float* bi
     sw->cout = cout; sw->cin = 3; sw->k = 9; sw->dtype = dtype;
     sw->mode = MODE_PAIR4; sw->c8in = 1; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = 0;
     sw->pack_bytes = pack.size() * 2;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
         srb_free_weights(sw);
         return fail(SRB_ENOMEM, "srb_pack_conv_pair4: cudaMalloc failed");
@@ -754,7 +764,7 @@ extern "C" int srb_debug_trace(srb_ctx* ctx, void* dev_buf512) {
 // Synchronise the device and report a kernel-side protocol timeout (see mbar_wait) as an error.
 extern "C" int srb_check_device(srb_ctx* ctx) {
     if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
-    CUDA_TRY(cudaSetDevice(ctx->device));
+    DeviceGuard dev_guard(ctx->device);
     CUDA_TRY(cudaDeviceSynchronize());
     unsigned int flag = 0, info[4] = {0, 0, 0, 0};
     CUDA_TRY(cudaMemcpyFromSymbol(&flag, g_srb_abort, sizeof(flag)));
@@ -865,7 +875,7 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
 extern "C" int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N, int H, int W) {
     if (!ctx || !net || !in_host || !out_host) return fail(SRB_EINVAL, "srb_model_pt_forward_host: NULL argument");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_model_pt_forward_host: empty shape");
-    CUDA_TRY(cudaSetDevice(ctx->device));
+    DeviceGuard dev_guard(ctx->device);
     size_t io = (size_t)N * 3 * H * W, io_al = align256(io);
     size_t ws = srb_model_pt_workspace_bytes(N, H, W);
     if (!ctx->own_stream) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
@@ -1183,7 +1193,7 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
         std::stable_sort(units.begin(), units.end(), [&](const WgradUnit& a, const WgradUnit& c) { return unit_cost(a) > unit_cost(c); });
     srb_grad_batch* b = new srb_grad_batch();
     b->dtype = dtype; b->nunits = (int)units.size(); b->nbias = (int)bias.size();
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     bool ok = true;
     if (!tmaps.empty()) ok = ok && cudaMalloc(&b->d_tmaps, tmaps.size() * sizeof(CUtensorMap)) == cudaSuccess &&
         cudaMemcpy(b->d_tmaps, tmaps.data(), tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice) == cudaSuccess;
@@ -1259,7 +1269,7 @@ extern "C" int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int
     }
     srb_pack_batch* b = new srb_pack_batch();
     b->n = n; b->max_total = mx;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&b->d_jobs, n * sizeof(PackJob)) != cudaSuccess ||
         cudaMemcpy(b->d_jobs, v.data(), n * sizeof(PackJob), cudaMemcpyHostToDevice) != cudaSuccess) {
         srb_pack_batch_destroy(b);
@@ -1325,7 +1335,7 @@ extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* b
     if (pa.size() * 2 != (size_t)G::WA_BYTES || pb.size() * 2 != (size_t)G::WB_BYTES) return fail(SRB_EINVAL, "srb_resblock_create: pack size");
     srb_resblock* rb = new srb_resblock();
     rb->dtype = dtype;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&rb->d_wA, G::WA_BYTES) != cudaSuccess || cudaMalloc(&rb->d_wB, G::WB_BYTES) != cudaSuccess ||
         cudaMalloc(&rb->d_bA, G::CH * 4) != cudaSuccess || cudaMalloc(&rb->d_bB, G::CB * 4) != cudaSuccess) {
         srb_resblock_destroy(rb);
@@ -1443,7 +1453,7 @@ extern "C" int srb_rowconv_create(srb_ctx* ctx, const float* w, const float* bia
     if (pk.size() * 2 != (size_t)G::W_BYTES) return fail(SRB_EINVAL, "srb_rowconv_create: pack size");
     srb_rowconv* rc = new srb_rowconv();
     rc->dtype = dtype;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&rc->d_w, G::W_BYTES) != cudaSuccess) {
         srb_rowconv_destroy(rc);
         return fail(SRB_ENOMEM, "srb_rowconv_create: cudaMalloc failed");
@@ -1538,7 +1548,7 @@ extern "C" int srb_tail9_create(srb_ctx* ctx, const float* w, const float* bias,
         }
     srb_tail9* t = new srb_tail9();
     t->dtype = dtype;
-    cudaSetDevice(ctx->device);
+    DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&t->d_w, G::W_BYTES) != cudaSuccess) {
         srb_tail9_destroy(t);
         return fail(SRB_ENOMEM, "srb_tail9_create: cudaMalloc failed");

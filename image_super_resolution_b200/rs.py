@@ -13,6 +13,7 @@ File decode/encode stays the caller's (torchvision) business; the video writer i
 """
 from __future__ import annotations
 
+import collections
 from pathlib import Path
 from typing import Iterable, Iterator, Sequence
 
@@ -142,25 +143,48 @@ def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor
     devices; results leave in frame order as HWC (BGR like RGB2BGR, utils/datasets.py:113-124) into sink.writeFrame."""
     sm = model if isinstance(model, ShardedModel) else None
     G = len(sm) if sm else 1
-    inflight: list[torch.Tensor] = []
+    layout = "hwc_bgr" if bgr else "nchw"               # BGR frames: the tail conv stores HWC / BGR itself (no glue kernels)
     n = 0
 
-    layout = "hwc_bgr" if bgr else "nchw"               # BGR frames: the tail conv stores HWC / BGR itself (no glue kernels)
-
-    def drain(out: torch.Tensor):
+    def emit(o):
         nonlocal n
-        o = (out if bgr else out.permute(0, 2, 3, 1).contiguous()).cpu().numpy()
         for f in o:
             sink.writeFrame(f)
             n += 1
 
-    for i, frames in enumerate(batches):
-        out = sm.forward_on(i, frames, layout) if sm else model.forward(frames.to(model._device, non_blocking=True), layout=layout)
-        inflight.append(out)
-        if len(inflight) >= G:                          # keep one unit in flight per device
-            drain(inflight.pop(0))
-    for out in inflight:
-        drain(out)
+    # Every device runs the pipelined host-to-host stream of its replica (H2D of the next batch and D2H of the previous one
+    # overlap the kernels; the forward is a captured graph); batch i goes to device i mod G and the results are taken in
+    # frame order, so the writer gets each pinned result while the following batches compute.
+    reps = sm.replicas if sm else [model]
+    src = iter(batches)
+    queues = [collections.deque() for _ in range(G)]
+    state = {"next": 0, "done": False}
+
+    def feeder(d):
+        """Batches d, d + G, ... of the shared source (pulled lazily, in order)."""
+        while True:
+            while not queues[d] and not state["done"]:
+                try:
+                    b = next(src)
+                except StopIteration:
+                    state["done"] = True
+                    break
+                queues[state["next"] % G].append(b if not b.is_cuda else b.cpu())
+                state["next"] += 1
+            if not queues[d]:
+                return
+            yield queues[d].popleft()
+
+    gens = [m.stream(feeder(d), depth=2, layout=layout) for d, m in enumerate(reps)]
+    i = 0
+    while True:
+        m = reps[i % G]
+        with torch.cuda.device(m._device):
+            y = next(gens[i % G], None)
+        if y is None:
+            break
+        emit((y if bgr else y.permute(0, 2, 3, 1).contiguous()).numpy())
+        i += 1
     return n
 
 

@@ -41,16 +41,25 @@ def test_halo_tile_mode_equals_whole_image(model, golden_dir):
     assert d.max().item() <= 2
 
 
-def test_sharded_model_and_frame_path(model):
+@pytest.mark.parametrize("ndev,nb", [(1, 3), (2, 5), (2, 4)])
+def test_sharded_model_and_frame_path(model, ndev, nb):
+    """rs.upscale_frames: batch i on device i mod G through that replica's pipelined stream, frames leave in order as BGR HWC."""
     from image_super_resolution_b200 import rs
-    sm = rs.ShardedModel(model, devices=[0])
+    if torch.cuda.device_count() < ndev:
+        pytest.skip(f"needs {ndev} GPUs")
+    sm = rs.ShardedModel(model, devices=list(range(ndev)))
     g = torch.Generator().manual_seed(3)
-    batches = [torch.randint(0, 256, (2, 3, 40, 48), dtype=torch.uint8, generator=g) for _ in range(3)]
+    batches = [torch.randint(0, 256, (2, 3, 40, 48), dtype=torch.uint8, generator=g) for _ in range(nb)]
     sink = rs.ByteSink(keep=True)
     n = rs.upscale_frames(sm, batches, sink)
-    assert n == 6 and sink.bytes == 6 * 40 * 48 * 3
-    want = model(batches[1].cuda())[1].flip(0).permute(1, 2, 0).cpu().numpy()   # frame 3: BGR, HWC
-    assert np.array_equal(sink.kept[3], want)
+    assert n == 2 * nb and sink.bytes == 2 * nb * 40 * 48 * 3
+    for i in range(nb):
+        want = model(batches[i].cuda())
+        for j in range(2):
+            assert np.array_equal(sink.kept[2 * i + j], want[j].flip(0).permute(1, 2, 0).cpu().numpy()), (i, j)
+    sink_rgb = rs.ByteSink(keep=True)
+    rs.upscale_frames(sm, batches[:2], sink_rgb, bgr=False)
+    assert np.array_equal(sink_rgb.kept[3], model(batches[1].cuda())[1].permute(1, 2, 0).cpu().numpy())
 
 
 def test_stream_pipelined_host_batches_match_forward(model):
