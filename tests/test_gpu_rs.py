@@ -97,3 +97,27 @@ def test_hwc_bgr_store_equals_flip_permute_of_the_nchw_result(model, shape):
     assert torch.equal(got_t, want)
     with pytest.raises(RuntimeError):
         model.forward(x, layout="hwc_bgr")    # host tensors go through stream()
+
+
+@pytest.mark.parametrize("ndev", [1, 2])
+def test_upscale_image_modes_agree_with_per_window_forwards(model, ndev):
+    """rs.upscale_image with the device-resident canvas: "reference" (windows of equal shape batched) == one forward per
+    rs.sliding_window window, pasted like rs.py:105-111; "halo" == "whole"; a ragged image, on one and on two devices."""
+    from image_super_resolution_b200 import rs
+    if torch.cuda.device_count() < ndev:
+        pytest.skip(f"needs {ndev} GPUs")
+    m = model if ndev == 1 else rs.ShardedModel(model, devices=list(range(ndev)))
+    g = torch.Generator().manual_seed(21)
+    img = torch.randint(0, 256, (3, 150, 221), dtype=torch.uint8, generator=g)
+    want = torch.zeros_like(img)
+    for _, x, y, win in rs.sliding_window(img, 64):
+        o = model(win.unsqueeze(0).contiguous().cuda())[0].cpu()
+        want[:, y:y + o.shape[-2], x:x + o.shape[-1]] = o
+    assert torch.equal(rs.upscale_image(m, img, 64, "reference"), want)
+    assert torch.equal(rs.upscale_image(m, img, 64, "reference", batch=3), want)
+    whole = model(img.unsqueeze(0).cuda())[0].cpu()
+    assert torch.equal(rs.upscale_image(m, img, 64, "whole"), whole)
+    assert torch.equal(rs.upscale_image(m, img, 64, "halo", tile=(64, 96)), whole)
+    assert torch.equal(rs.upscale_image(m, img, 64, "halo"), whole)
+    small = img[:, :40, :50].contiguous()                       # smaller than the window: one window = the image (rs.py:20-21)
+    assert torch.equal(rs.upscale_image(m, small, 64, "reference"), model(small.unsqueeze(0).cuda())[0].cpu())
