@@ -394,6 +394,23 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
             const int tyi = r / p.tiles_x, txi = r - tyi * p.tiles_x;
             const uint32_t t_addr0 = tmem_base + b * (NT * NOUT) + ((uint32_t)(lg * 32) << 16);
             if (threadIdx.x == 128) trace(p, it, 4);   // epilogue starts waiting
+            // backward of a 32-channel layer: the saved activation granules of this set's first M-tile are requested before
+            // the wait for the accumulators (the mask read was an exposed DRAM / L2 round trip per tile)
+            constexpr bool MASK_PF = BWD && NOUT == 32 && MODE == MODE_STD;
+            uint4 mpf[MASK_PF ? 4 : 1];
+            bool mpf_ok = false;
+            if constexpr (MASK_PF) {
+                if ((p.flags & F_MASK) && p.mask_p0 == 0 && p.mask_p1 == 4 && eset < NT) {
+                    const int y = tyi * G::SUPER_H + (L >> 3), x = txi * G::SUPER_W + eset * G::TW + (L & 7);
+                    if (y < p.H && x < p.W) {
+                        mpf_ok = true;
+                        const uint8_t* mb = reinterpret_cast<const uint8_t*>(p.mask) +
+                                            (((size_t)n * p.mask_c8_total + p.mask_c8_off) * HW + (size_t)y * p.W + x) * 16;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) mpf[j] = ldg_nc16(mb + (size_t)j * HW * 16);
+                    }
+                }
+            }
             mbar_wait(&tfull[b], bph, 5);
             if (threadIdx.x == 128) trace(p, it, 5);   // accumulators complete
             tc_fence_after();
@@ -470,8 +487,10 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                                     }
                                     if (BWD && (p.flags & F_MASK) && gj >= p.mask_p0 && gj < p.mask_p1) {
                                         // LeakyReLU backward: the in-place activation kept its sign (slope > 0)
-                                        const uint4 q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.mask) +
-                                                                 (((size_t)n * p.mask_c8_total + p.mask_c8_off + gj) * HW + pix) * 16);
+                                        uint4 q;
+                                        if (MASK_PF && mpf_ok && t == eset) q = mpf[MASK_PF ? j : 0];
+                                        else q = ldg_nc16(reinterpret_cast<const uint8_t*>(p.mask) +
+                                                          (((size_t)n * p.mask_c8_total + p.mask_c8_off + gj) * HW + pix) * 16);
                                         const uint32_t qq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
