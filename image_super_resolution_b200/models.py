@@ -259,11 +259,19 @@ class _SRNet(nn.Module):
             raise RuntimeError("the B200 path has no CPU fallback: move the model and its inputs to a CUDA device")
         if inputs.dim() != 4 or inputs.shape[1] != 3:
             raise RuntimeError(f"expected [N,3,h,w], got {tuple(inputs.shape)}")
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+        if torch.is_grad_enabled() and self._any_requires_grad():
             # train.py:55 — forward with saved activations; backward runs on the same kernels (training.py)
             from .training import train_forward
             return train_forward(self, inputs)
         return self._plan(inputs.device).forward(inputs.float().contiguous())
+
+    def _any_requires_grad(self) -> bool:
+        # (the module-tree walk of self.parameters() costs 0.15 ms per call: it sits on the host path between two steps)
+        ps = self.__dict__.get("_param_list")
+        if ps is None or len(ps[1]) != ps[0]:
+            lst = list(self.parameters())
+            ps = self.__dict__["_param_list"] = (len(lst), lst)
+        return any(p.requires_grad for p in ps[1])
 
     def __deepcopy__(self, memo):  # ModelEMA deep-copies the model (utils/models.py:25): plans are derived caches
         import copy
@@ -271,7 +279,7 @@ class _SRNet(nn.Module):
         new = cls.__new__(cls)
         memo[id(self)] = new
         for k, v in self.__dict__.items():
-            if k not in ("_plans", "_train_plans"):
+            if k not in ("_plans", "_train_plans", "_param_list"):
                 new.__dict__[k] = copy.deepcopy(v, memo)
         return new
 

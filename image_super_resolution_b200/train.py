@@ -117,6 +117,7 @@ def train(model, ema, dataloader, compute_loss, optimizer, gradscaler, schedule,
     rank0 = not (dist.is_available() and dist.is_initialized()) or dist.get_rank() == 0
     board = tensorBoard if (tensorBoard is not None and rank0) else _NullBoard()
     total = len(dataloader)
+    deferred = [] if (isinstance(board, _NullBoard) and device.type == "cuda") else None
     for idx, (hr_images, lr_images) in enumerate(dataloader):
         hr_images, lr_images = hr_images.to(device, non_blocking=True), lr_images.to(device, non_blocking=True)
         optimizer.zero_grad()
@@ -132,7 +133,15 @@ def train(model, ema, dataloader, compute_loss, optimizer, gradscaler, schedule,
             schedule.step()
         if ema is not None:
             ema.update(model)
-        value = loss.item()                        # the reference reads it back every step (train.py:64-65)
-        losses.append(value)
-        board.add_scalar("loss", value, epoch * total + idx + 1)
+        if deferred is None:
+            value = loss.item()                    # the reference reads it back every step (train.py:64-65) for its logger
+            losses.append(value)
+            board.add_scalar("loss", value, epoch * total + idx + 1)
+        else:
+            deferred.append(loss.detach().clone())
+    if deferred:
+        # nobody watches the per-step value (no tensorBoard): the read-backs are taken together at the end of the epoch, so
+        # the host keeps enqueueing the next step while the device finishes this one (a .item() per step leaves the GPU idle
+        # for the host's whole launch path: 0.7 of 9.7 ms).  Same return value: the list of per-step losses.
+        losses = torch.stack(deferred).float().cpu().tolist()
     return losses
