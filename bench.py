@@ -31,12 +31,12 @@ BATCH, HH, WW = 256, 64, 64
 FLOP_PER_PX = 725760  # algorithmic FLOP (2*MAC) per pixel of the model.pt graph
 # algorithmic FLOP/px of each launch of one forward, in launch order (pack, conv0, 8x(A,B), conv1, conv2)
 LAUNCH_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
-LAUNCH_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64",
+LAUNCH_NAMES = ["u8nchw_to_pair4_x4", "conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64",
                                                                                                  "conv9x9_tail_64_3"]
 assert sum(LAUNCH_FLOP_PX) == FLOP_PER_PX
 # with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 12 launches
 FUSED_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
-FUSED_NAMES = ["u8nchw_to_c8", "conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
+FUSED_NAMES = ["u8nchw_to_pair4_x4", "conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
 assert sum(FUSED_FLOP_PX) == FLOP_PER_PX
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the dominant kernel at the bench shape, from the
 # one `ncu --set full` capture of a whole forward summarised in profiles/ncu_fwd_r1_full.txt (mean of the 8 launches:
@@ -61,7 +61,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index: int, period: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.period = index, period
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.power, self.reasons, self.max_mhz = [], [], set(), None
         self._halt = threading.Event()
         self.ok = False
         try:
@@ -86,6 +86,7 @@ class ClockSampler(threading.Thread):
         while not self._halt.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, name in names.items():
                     if r & bit:
@@ -98,8 +99,9 @@ class ClockSampler(threading.Thread):
         self._halt.set()
         self.join(timeout=2)
         s = sorted(self.samples)
+        pw = sorted(self.power)
         return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "power_w_median": (pw[len(pw) // 2] if pw else None), "power_w_max": (pw[-1] if pw else None)}
 
 
 def dist_setup(n_gpus: int):
@@ -159,6 +161,95 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def time_cuda(fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def gpu_reference(dev, model, steps, warmup):
+    """The number the kernels must beat: the same model.pt graph as STOCK PyTorch CUDA ops —
+    aten::_convolution -> cuDNN, leaky_relu_, add, tanh, round — under torch.autocast('cuda') (fp16) with cudnn.benchmark and
+    the TF32 flags, exactly as the reference runs it on a GPU (rs.py:62-64, :93-94, :126-129), on the same B200, same inputs,
+    same steps / warm-up, CUDA-event timed.  A baseline leg: it executes the oracle's restatement of the graph on device
+    tensors; none of this repo's kernels are on it."""
+    from oracle import modelpt_oracle as mo
+    torch.backends.cudnn.benchmark = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.backends.cudnn.allow_tf32 = True
+    sd = {k: v.to(dev) for k, v in mo.load_weights(WEIGHTS).items()}
+    pk = peaks()
+    out = {"what": "stock PyTorch (cuDNN) model.pt graph, torch.autocast fp16, cudnn.benchmark, TF32 flags (rs.py:62-64,126-129)",
+           "torch": torch.__version__, "cudnn": torch.backends.cudnn.version()}
+    g = torch.Generator().manual_seed(100)
+    for name, shape in (("config2_256x64x64", (BATCH, 3, HH, WW)), ("config3_2x1080p", (2, 3, 1080, 1920))):
+        x = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g).to(dev)
+
+        def ref_fwd():
+            with torch.autocast(device_type="cuda"):
+                return mo.forward_u8(x, sd)
+
+        y = torch.empty_like(x)
+        px = shape[0] * shape[2] * shape[3]
+        ms_ref = time_cuda(ref_fwd, steps, max(warmup, 5))       # (cudnn.benchmark picks its algorithms during warm-up)
+        ms_ours = time_cuda(lambda: model(x, out=y), steps, max(warmup, 3))
+        d = (ref_fwd().int() - y.int()).abs()
+        out[name] = {"reference_mpix_s": px / ms_ref / 1e3, "reference_ms": ms_ref,
+                     "reference_frac_of_bf16_peak": px * FLOP_PER_PX / (ms_ref * 1e-3) / 1e12 / pk["bf16_tflops"],
+                     "ours_mpix_s": px / ms_ours / 1e3, "ours_ms": ms_ours, "ours_over_gpu_reference": ms_ref / ms_ours,
+                     "max_abs_lsb_vs_ours": int(d.max()), "frac_exact_vs_ours": float((d == 0).float().mean())}
+        del x, y
+        torch.cuda.empty_cache()
+    return out
+
+
+def sustained(dev, local, model, x, y, seconds=3.0):
+    """>= `seconds` of back-to-back forwards (the headline `value` is an 18 ms burst): the rate a video stream sees once the
+    1000 W power cap has engaged, with NVML clock / power samples, against the SUSTAINED cuBLAS bf16 figure."""
+    px_step = x.shape[0] * x.shape[2] * x.shape[3]
+    for _ in range(3):
+        model(x, out=y)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local, period=0.02)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    t0 = time.perf_counter()
+    e0.record()
+    n = 0
+    while True:
+        for _ in range(100):
+            model(x, out=y)
+        n += 100
+        if time.perf_counter() - t0 > seconds:     # (the host runs ahead of the device: the timed region is >= this long)
+            break
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    pk = peaks()
+    tf = n * px_step * FLOP_PER_PX / (ms * 1e-3) / 1e12
+    return {"value": n * px_step / ms / 1e3, "unit": "Mpix/s", "seconds": ms / 1e3, "steps": n, "ms_per_step": ms / n,
+            "tflops": tf, "frac_of_bf16_sustained": tf / pk["bf16_tflops_sustained"], "frac_of_bf16_burst": tf / pk["bf16_tflops"],
+            "peak_sustained": pk["bf16_tflops_sustained"], "clocks": clocks}
+
+
+class _StubBoard:
+    """The reference always logs the loss per step (train.py:64-65: loss.item() + tensorBoard.add_scalar)."""
+
+    def __init__(self):
+        self.n = 0
+
+    def add_scalar(self, *a, **k):
+        self.n += 1
+
+
 def bench_train(dev, rank, world, steps, warmup=3):
     """BASELINE configs[4]: train.py step (EResNet(16,0.2,2), L1 loss, GradScaler, clip, Adam, LinearLR, EMA) on synthetic
     COCO-shaped 128x128 HR crops, per-GPU batch 16, data parallel with one gradient all-reduce per step.  Runs the
@@ -168,43 +259,56 @@ def bench_train(dev, rank, world, steps, warmup=3):
     from image_super_resolution_b200 import train as T
     from image_super_resolution_b200.training import L1Loss
     B = 16
-    torch.manual_seed(100)
-    net = models.EResNet(16, 0.2, 2).to(dev)
-    T.broadcast_parameters(net)
     g = torch.Generator().manual_seed(100 + rank)
     hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
     lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
     loss_fn = L1Loss().to(dev)
-    # the reference's optimizer (train.py:265: Adam, lr 1e-4, betas (0.9, 0.999), no weight decay), GradScaler, gradient
-    # clipping and EMA as the library's fused tail (optim.py: two launches over flat arenas, same arithmetic and call order;
-    # parity vs the torch objects in tests/test_gpu_optim.py).  SRB_TORCH_TAIL=1 runs torch's own objects instead.
-    if os.environ.get("SRB_TORCH_TAIL") == "1":
-        opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999), fused=True)
-        scaler, ema, tail = torch.amp.GradScaler("cuda"), T.ModelEMA(net, tau=1000), "torch GradScaler / clip_grad_norm_ / Adam(fused=True) / per-tensor EMA"
-    else:
-        opt = T.FlatAdam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
-        scaler, ema, tail = T.GradScaler("cuda"), T.ModelEMA(net, tau=1000).attach(opt), "fused tail (FlatAdam + GradScaler + clip + EMA: 2 launches)"
-    sched = torch.optim.lr_scheduler.LinearLR(opt, start_factor=1, end_factor=0.1, total_iters=1000)
-    T.train(net, ema, [(hr, lr)] * warmup, loss_fn, opt, scaler, sched, 0, None)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0.record()
-    losses = T.train(net, ema, [(hr, lr)] * steps, loss_fn, opt, scaler, sched, 1, None)
-    e1.record()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item()) / steps
+
+    def one(tail: str, board):
+        """ms per step (max over ranks) of the drop-in train() with the given optimizer tail and logger."""
+        torch.manual_seed(100)
+        net = models.EResNet(16, 0.2, 2).to(dev)
+        T.broadcast_parameters(net)
+        # the reference's optimizer (train.py:265: Adam, lr 1e-4, betas (0.9, 0.999), no weight decay), GradScaler, gradient
+        # clipping and EMA: either the library's fused tail (optim.py: two launches over flat arenas, same arithmetic and call
+        # order; parity vs the torch objects in tests/test_gpu_optim.py) or torch's own objects, unmodified
+        if tail == "torch":
+            opt = torch.optim.Adam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
+            scaler, ema = torch.amp.GradScaler("cuda"), T.ModelEMA(net, tau=1000)
+        else:
+            opt = T.FlatAdam(net.parameters(), lr=1e-4, betas=(0.9, 0.999))
+            scaler, ema = T.GradScaler("cuda"), T.ModelEMA(net, tau=1000).attach(opt)
+        sched = torch.optim.lr_scheduler.LinearLR(opt, start_factor=1, end_factor=0.1, total_iters=1000)
+        T.train(net, ema, [(hr, lr)] * warmup, loss_fn, opt, scaler, sched, 0, board)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        losses = T.train(net, ema, [(hr, lr)] * steps, loss_fn, opt, scaler, sched, 1, board)
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        del net, opt, ema
+        return float(ms.item()) / steps, losses
+
+    # headline of the leg: the reference's loop as the reference runs it — loss.item() + add_scalar EVERY step (train.py:64-65)
+    ms, losses = one("fused", _StubBoard())
+    ms_torch, _ = one("torch", _StubBoard())
+    ms_deferred, _ = one("fused", None)          # no logger attached: train() takes the read-backs together at the end
     flop = 289.0e9 * B          # SURVEY §8(d): fwd + bwd algorithmic FLOP per sample
     pk = peaks()
     return {"metric": "train.py step samples/s", "value": world * B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms,
             "steps": steps, "model": "EResNet(16,0.2,2)", "per_gpu_batch": B, "hr_crop": 128, "operands": "bf16 in, fp32 accumulate",
-            "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), Adam, LinearLR, EMA, loss.item(); " + tail,
+            "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), Adam, LinearLR, EMA, per-step "
+                    "loss.item() + add_scalar (train.py:64-65); fused tail (FlatAdam + GradScaler + clip + EMA: 2 launches)",
+            "ms_per_step_torch_tail": ms_torch, "samples_s_torch_tail": world * B / ms_torch * 1e3,
+            "torch_tail": "torch.amp.GradScaler / torch clip_grad_norm_ / torch.optim.Adam / per-tensor EMA on the same fwd+bwd kernels",
+            "ms_per_step_no_logger": ms_deferred,
             "collective": "one all-reduce (mean) of the 11.7M-element fp32 gradient arena per step" if world > 1 else "none",
             "fwd_bwd_tflops_per_gpu": flop / (ms * 1e-3) / 1e12, "frac_of_bf16_peak": flop / (ms * 1e-3) / 1e12 / pk["bf16_tflops"],
             "loss_first_last": [losses[0], losses[-1]]}
@@ -322,6 +426,18 @@ def run_ours(args, rank, world, local):
                 "whole_step_tflops": px_step * FLOP_PER_PX / (sum(per_launch) / 1e3) / 1e12,
                 "kernels": kernels}
 
+    gpu_ref = sus = None
+    if world == 1 and not args.no_gpu_reference:
+        try:
+            gpu_ref = gpu_reference(dev, model, K, Wm)
+        except Exception as e:  # noqa: BLE001
+            gpu_ref = {"error": repr(e)[:300]}
+    if not args.no_sustained:
+        try:
+            sus = sustained(dev, local, model, x, y, seconds=args.sustained_seconds)
+        except Exception as e:  # noqa: BLE001
+            sus = {"error": repr(e)[:300]}
+
     train_line = None
     if not args.no_train:
         try:
@@ -347,6 +463,10 @@ def run_ours(args, rank, world, local):
                         "api": f"ModelPT.stream(host batches): pinned H2D + forward + D2H per step, {depth} batches in flight"},
                 "gpu_launches": nl * K,
                 "roofline": roofline}
+        if gpu_ref is not None:
+            line["gpu_reference"] = gpu_ref
+        if sus is not None:
+            line["sustained"] = sus
         if train_line is not None:
             line["train_step"] = train_line
         if world == 1 and not args.no_cpu:
@@ -368,6 +488,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-train", action="store_true", help="skip the train_step leg (BASELINE configs[4])")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip the stock-PyTorch (cuDNN fp16) leg on the same GPU")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the >= 3 s back-to-back leg")
+    ap.add_argument("--sustained-seconds", type=float, default=3.0)
     args = ap.parse_args()
     rank, world, local = dist_setup(args.gpus)
     if args.impl == "reference":

@@ -25,7 +25,7 @@ SIGNATURES = {
     "srb_create": (_i, [_i, C.POINTER(_vp)]),
     "srb_destroy": (None, [_vp]),
     "srb_num_sms": (_i, [_vp]),
-    "srb_debug_set": (_i, [_vp, _i, _i]),
+    "srb_set_option": (_i, [_vp, _i, _i]),
     "srb_pack_conv": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, C.POINTER(_vp)]),
     "srb_free_weights": (None, [_vp]),
     "srb_conv2d_fwd": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _f, _f, _f, _i, _i, _i, _i, _vp]),
@@ -41,10 +41,9 @@ SIGNATURES = {
     "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
     "srb_model_pt_launches": (_i, [_i, _i]),
     "srb_check_device": (_i, [_vp]),
-    "srb_debug_trace": (_i, [_vp, _vp]),
+    "srb_poll_abort": (_i, [_vp]),
     "srb_profile_enable": (_i, [_vp, _i]),
     "srb_profile_read": (_i, [_vp, _fp, _i]),
-    "srb_ubench_mma": (_i, [_vp, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_longlong)]),
     "srb_conv2d_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _i, _vp]),
     "srb_bias_grad": (_i, [_vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_conv2d_ex": (_i, [_vp, _vp, _vp, _vp]),
@@ -76,12 +75,23 @@ SIGNATURES = {
     "srb_tail9_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "srb_optim_workspace_floats": (_i, []),
     "srb_grad_stats": (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
-    "srb_adam_ema_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _f, _f, _f, _f, _f, _f, _f, _vp]),
+    "srb_adam_ema_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _f, _f, _f, _f, _f, _f, _f, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
     "srb_l1_loss_bwd_dev": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp, _vp]),
 }
+
+# probe hooks of the -DSRB_DEBUG build (include/srb200_debug.h): present only when SRB200_LIB points at libsrb200_dbg.so (tools/)
+DEBUG_SIGNATURES = {
+    "srb_debug_set": (_i, [_vp, _i, _i]),
+    "srb_debug_trace": (_i, [_vp, _vp]),
+    "srb_ubench_mma": (_i, [_vp, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_longlong)]),
+    "srb_ubench_mix": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), _i, _i, C.POINTER(C.c_longlong)]),
+}
+OPT_MAX_GRID, OPT_PATH = 1, 2
+PATH_UNFUSED_TRUNK, PATH_NO_PDL, PATH_TILED_CONV1, PATH_TILED_TAIL, PATH_C8_HEAD = 8, 1024, 8192, 16384, 32768
+PATH_LARGE_TILING, PATH_UNSORTED_UNITS, PATH_WS_LARGE_TILING = 65536, 131072, 262144
 
 _lib = None
 _lock = threading.Lock()
@@ -102,6 +112,11 @@ def lib():
                     fn = getattr(l, name)  # AttributeError if the .so lacks a declared symbol
                     fn.restype = res
                     fn.argtypes = args
+                for name, (res, args) in DEBUG_SIGNATURES.items():
+                    fn = getattr(l, name, None)
+                    if fn is not None:
+                        fn.restype = res
+                        fn.argtypes = args
                 _lib = l
     return _lib
 
@@ -134,8 +149,21 @@ class Context:
         """Synchronise and raise if a kernel reported a pipeline timeout."""
         check(lib().srb_check_device(self.handle), "srb_check_device")
 
+    def poll(self):
+        """Raise if a kernel of this device reported a pipeline timeout since the last check (no synchronisation: reads the
+        host-mapped abort flag).  Called wherever results are handed to the caller."""
+        check(lib().srb_poll_abort(self.handle), "srb_poll_abort")
+
+    def set_option(self, key: int, value: int):
+        """Host-side options (include/srb200.h: SRB_OPT_MAX_GRID, SRB_OPT_PATH)."""
+        check(lib().srb_set_option(self.handle, key, value), "srb_set_option")
+
     def debug_set(self, key: int, value: int):
-        check(lib().srb_debug_set(self.handle, key, value), "srb_debug_set")
+        """Probe hooks: only with the -DSRB_DEBUG build (SRB200_LIB=.../libsrb200_dbg.so); the product library has none."""
+        fn = getattr(lib(), "srb_debug_set", None)
+        if fn is None:
+            raise RuntimeError("srb_debug_set exists only in libsrb200_dbg.so (build.build(debug=True), SRB200_LIB=...)")
+        check(fn(self.handle, key, value), "srb_debug_set")
 
 
 class ConvArgs(C.Structure):

@@ -8,8 +8,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "srb200.cu")
 OUT = os.path.join(HERE, "libsrb200.so")
+OUT_DEBUG = os.path.join(HERE, "libsrb200_dbg.so")     # -DSRB_DEBUG: probe hooks for tools/ (SRB200_LIB=...); never loaded by the product
 DEPS = sorted(os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc"))) + [
-    os.path.join(HERE, "..", "include", "srb200.h")]
+    os.path.join(HERE, "..", "include", "srb200.h"), os.path.join(HERE, "..", "include", "srb200_debug.h")]
 
 
 def nvcc_path() -> str:
@@ -19,18 +20,21 @@ def nvcc_path() -> str:
     raise RuntimeError("nvcc not found")
 
 
-def up_to_date() -> bool:
-    if not os.path.exists(OUT):
+def up_to_date(out: str = OUT) -> bool:
+    if not os.path.exists(out):
         return False
-    t = os.path.getmtime(OUT)
+    t = os.path.getmtime(out)
     return all(os.path.getmtime(d) <= t for d in DEPS if os.path.exists(d))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if up_to_date() and not force:
-        return OUT
+def build(force: bool = False, verbose: bool = False, debug: bool = False) -> str:
+    out = OUT_DEBUG if debug else OUT
+    if up_to_date(out) and not force:
+        return out
     cmd = [nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "-Xcompiler", "-fPIC", "-shared", "-o", OUT, SRC]
+           "-Xcompiler", "-fPIC", "-shared", "-o", out, SRC]
+    if debug:
+        cmd[1:1] = ["-DSRB_DEBUG"]
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
     r = subprocess.run(cmd, capture_output=True, text=True)
@@ -38,8 +42,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":
-    print(build(force=True, verbose=True))
+    import sys
+    print(build(force=True, verbose=True, debug="--debug" in sys.argv))

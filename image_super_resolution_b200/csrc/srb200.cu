@@ -13,9 +13,14 @@
 #include <tuple>
 
 #include "../../include/srb200.h"
+#ifdef SRB_DEBUG
+#include "../../include/srb200_debug.h"
+#endif
 #include "srb_conv.cuh"
 #include "srb_elem.cuh"
+#ifdef SRB_DEBUG
 #include "srb_ubench.cuh"
+#endif
 #include "srb_wgrad.cuh"
 #include "srb_bwd.cuh"
 #include "srb_resblock.cuh"
@@ -56,8 +61,12 @@ struct srb_ctx {
     int device = 0;
     int num_sms = 0;
     PFN_encodeTiled encode = nullptr;
+    // product options (srb_set_option): a cap on the persistent grids and host-side kernel-family selection
+    int max_grid = 0;
+    int path = 0;             // SRB_PATH_* bits
+    unsigned int* h_abort = nullptr;   // host-mapped mirror of the device abort flag (one per device, shared by its contexts)
+    // probe state: only the -DSRB_DEBUG build (libsrb200_dbg.so, tools/) ever sets these
     int dbg_swap = 0;
-    int dbg_grid = 0;
     int dbg_skip = 0;
     bool pdl = false;         // launch the conv kernels with programmatic stream serialization (set by srb_model_pt_forward)
     bool pdl_all = false;     // ... for every conv launch of this context (srb_set_programmatic_launch)
@@ -107,6 +116,8 @@ struct DeviceGuard {
     DeviceGuard& operator=(const DeviceGuard&) = delete;
 };
 
+static unsigned int* s_abort_host[64] = {};
+
 extern "C" int srb_create(int device, srb_ctx** out) {
     if (!out) return fail(SRB_EINVAL, "srb_create: out is NULL");
     int ndev = 0;
@@ -129,6 +140,18 @@ extern "C" int srb_create(int device, srb_ctx** out) {
         return fail(SRB_ECUDA, "srb_create: cuTensorMapEncodeTiled not available from the driver");
     }
     c->encode = reinterpret_cast<PFN_encodeTiled>(fn);
+    if (device < 64 && !s_abort_host[device]) {
+        // the kernels' bounded waits (srb_ptx.cuh: mbar_wait) mirror their abort flag here: the host polls it without a sync
+        unsigned int* h = nullptr; unsigned int* d = nullptr;
+        if (cudaHostAlloc((void**)&h, 32, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+            memset(h, 0, 32);
+            if (cudaHostGetDevicePointer((void**)&d, h, 0) == cudaSuccess &&
+                cudaMemcpyToSymbol(g_srb_abort_host, &d, sizeof(d)) == cudaSuccess) s_abort_host[device] = h;
+            else cudaFreeHost(h);
+        }
+        cudaGetLastError();
+    }
+    c->h_abort = device < 64 ? s_abort_host[device] : nullptr;
     *out = c;
     return SRB_OK;
 }
@@ -149,17 +172,26 @@ extern "C" int srb_set_programmatic_launch(srb_ctx* c, int on) {
     c->pdl_all = on != 0;
     return SRB_OK;
 }
+extern "C" int srb_set_option(srb_ctx* c, int key, int value) {
+    if (!c) return fail(SRB_EINVAL, "ctx is NULL");
+    if (key == SRB_OPT_MAX_GRID) c->max_grid = value > 0 ? value : 0;
+    else if (key == SRB_OPT_PATH) c->path = value;
+    else return fail(SRB_EINVAL, "srb_set_option: unknown key %d", key);
+    return SRB_OK;
+}
+#ifdef SRB_DEBUG
 extern "C" int srb_debug_set(srb_ctx* c, int key, int value) {
     if (!c) return fail(SRB_EINVAL, "ctx is NULL");
     if (key == 0) c->dbg_swap = value;
-    else if (key == 1) c->dbg_grid = value;
-    else if (key == 2) c->dbg_skip = value;
+    else if (key == 1) c->max_grid = value;
+    else if (key == 2) { c->dbg_skip = value; c->path = value; }    // (the probe scripts pass kernel-probe and path bits in one word)
     else if (key == 3) c->dbg_repeat = value;
     else if (key == 4) c->dbg_threads = value;
     else if (key == 5) c->dbg_smem = value;
     else return fail(SRB_EINVAL, "srb_debug_set: unknown key %d", key);
     return SRB_OK;
 }
+#endif
 
 // ------------------------------------------------------------------------------------------
 // weight packing: OIHW fp32 (+BN) -> per K-step [2 granules][NOUT rows][8 k] 16-bit (UMMA B, K-major,
@@ -371,7 +403,7 @@ static int launch_conv(srb_ctx* ctx, const srb_weights* w, const void* x, int x_
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled (residual) failed: %d", (int)r);
     }
     int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
-    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
     p.dbg_swap = ctx->dbg_swap;
     p.dbg_skip = ctx->dbg_skip;
     p.dbg_trace = ctx->dbg_trace;
@@ -474,8 +506,8 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     // Small problems (a training batch: 16 x 64 x 64 px = 512 M-tiles for 148 SMs): with NT = 4 a CTA gets ONE super-tile and
     // its load, MMAs and epilogue run back to back; two-tile super-tiles give every CTA two pipeline steps that overlap.
     const long long mtiles = (long long)((W + 7) / 8) * ((H + 15) / 16) * N;
-    const bool small0 = mtiles < (long long)ctx->num_sms * 6 && !(ctx->dbg_skip & 65536);   // (debug bit 65536: always the large-problem tiling)
-    const bool small = small0 && !((ctx->dbg_skip & 262144) && w->kblocks);               // (debug bit 262144: large tiling for the weight-streaming kernels)
+    const bool small0 = mtiles < (long long)ctx->num_sms * 6 && !(ctx->path & SRB_PATH_LARGE_TILING);   // (debug bit 65536: always the large-problem tiling)
+    const bool small = small0 && !((ctx->path & SRB_PATH_WS_LARGE_TILING) && w->kblocks);               // (debug bit 262144: large tiling for the weight-streaming kernels)
 #define SRB_STD(C8, NO, NTT, NTS) if (!w->kblocks && w->c8in == C8 && w->nout == NO) { \
         if ((flags & SRB_F_RESIDUAL) && !partial_res && w->cout == NO && res_c8_total >= NO / 8) { \
             if (small) return launch_conv<C8, NO, 3, 3, MODE_STD, NTS, true>(ctx, w, x, x_c8_total, p, st); \
@@ -634,9 +666,9 @@ extern "C" int srb_grad_stats(srb_ctx* ctx, const float* grads, size_t n, const 
 }
 
 extern "C" int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float* ema,
-                                 size_t n, const float* scale_dev, const float* stats, float max_norm, float lr, float beta1,
+                                 size_t n, const float* scale_dev, float* stats, float* workspace, float max_norm, float lr, float beta1,
                                  float beta2, float eps, float weight_decay, float ema_decay, srb_stream_t stream) {
-    if (!ctx || !params || !grads || !exp_avg || !exp_avg_sq || !stats) return fail(SRB_EINVAL, "srb_adam_ema_step: NULL argument");
+    if (!ctx || !params || !grads || !exp_avg || !exp_avg_sq || !stats || !workspace) return fail(SRB_EINVAL, "srb_adam_ema_step: NULL argument");
     if (n == 0 || (n & 3)) return fail(SRB_EINVAL, "srb_adam_ema_step: the arena length must be a positive multiple of 4 floats (pad with zeros)");
     if (((uintptr_t)params | (uintptr_t)grads | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq | (uintptr_t)ema) & 15)
         return fail(SRB_EINVAL, "srb_adam_ema_step: arenas must be 16-byte aligned");
@@ -646,6 +678,7 @@ extern "C" int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads
     a.p = reinterpret_cast<float4*>(params); a.g = reinterpret_cast<const float4*>(grads);
     a.m = reinterpret_cast<float4*>(exp_avg); a.v = reinterpret_cast<float4*>(exp_avg_sq); a.ema = reinterpret_cast<float4*>(ema);
     a.n4 = n / 4; a.scale = scale_dev; a.stats = stats; a.max_norm = max_norm;
+    a.counter = reinterpret_cast<unsigned int*>(workspace + 2 * GSTAT_MAX_BLOCKS);
     a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.ema_decay = ema_decay;
     const int grid = ew_grid(ctx, a.n4, 256);
     adam_ema_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
@@ -754,11 +787,33 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
 // kernels one forward enqueues: pack, head, 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
 extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? 12 : 20; }
 
+#ifdef SRB_DEBUG
 // measurement only: per-step clock trace of CTA 0 of the next conv launches (512 int64 device buffer, or NULL)
 extern "C" int srb_debug_trace(srb_ctx* ctx, void* dev_buf512) {
     if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
     ctx->dbg_trace = (long long*)dev_buf512;
     return SRB_OK;
+}
+#endif
+
+static int report_abort(srb_ctx* ctx, const unsigned int* info) {
+    unsigned int zero = 0;
+    cudaMemcpyToSymbol(g_srb_abort, &zero, sizeof(zero));
+    if (ctx->h_abort) memset(ctx->h_abort, 0, 32);
+    return fail(SRB_ECUDA, "kernel pipeline timeout: wait site %u, block %u, thread %u, parity %u — results of the launches "
+                "since the last check are invalid", info[0] & 0xffffu, info[1], info[2], info[3]);
+}
+
+// Non-blocking: has a kernel of this device reported a pipeline timeout (srb_ptx.cuh: mbar_wait) since the last check?
+// Reads the host-mapped mirror of the abort flag — no device synchronisation — so the Python layer calls it at every point
+// where it hands results to the caller.  On a timeout the flag is cleared (after a device sync) and SRB_ECUDA is returned.
+extern "C" int srb_poll_abort(srb_ctx* ctx) {
+    if (!ctx) return fail(SRB_EINVAL, "ctx is NULL");
+    if (!ctx->h_abort || !*reinterpret_cast<volatile unsigned int*>(ctx->h_abort)) return SRB_OK;
+    DeviceGuard dev_guard(ctx->device);
+    cudaDeviceSynchronize();
+    unsigned int info[4] = {ctx->h_abort[1], ctx->h_abort[2], ctx->h_abort[3], ctx->h_abort[4]};
+    return report_abort(ctx, info);
 }
 
 // Synchronise the device and report a kernel-side protocol timeout (see mbar_wait) as an error.
@@ -770,10 +825,7 @@ extern "C" int srb_check_device(srb_ctx* ctx) {
     CUDA_TRY(cudaMemcpyFromSymbol(&flag, g_srb_abort, sizeof(flag)));
     if (flag) {
         CUDA_TRY(cudaMemcpyFromSymbol(info, g_srb_timeout_info, sizeof(info)));
-        unsigned int zero = 0;
-        CUDA_TRY(cudaMemcpyToSymbol(g_srb_abort, &zero, sizeof(zero)));
-        return fail(SRB_ECUDA, "kernel pipeline timeout: wait site %u, block %u, thread %u, parity %u", info[0] & 0xffffu,
-                    info[1], info[2], info[3]);
+        return report_abort(ctx, info);
     }
     return SRB_OK;
 }
@@ -832,9 +884,9 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
     int rc;
     cudaStream_t pst = (cudaStream_t)stream;
     struct PdlScope { srb_ctx* c; ~PdlScope() { c->pdl = false; } } pdl_scope{ctx};
-    ctx->pdl = !(ctx->dbg_skip & 1024);
+    ctx->pdl = !(ctx->path & SRB_PATH_NO_PDL);
     prof_mark(ctx, pst, true);
-    if (!(ctx->dbg_skip & 32768)) {      // head conv on pixel-pair granules: 27 MMAs per M-tile instead of 45
+    if (!(ctx->path & SRB_PATH_C8_HEAD)) {      // head conv on pixel-pair granules: 27 MMAs per M-tile instead of 45
         if ((rc = srb_u8nchw_to_pair4(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
         prof_mark(ctx, pst);
         if ((rc = srb_conv2d_fwd(ctx, net->head4, in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
@@ -845,7 +897,7 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
     }
     prof_mark(ctx, pst);
     void* cur = x0;
-    const bool fused = srb_resblock_supported(H, W) && !(ctx->dbg_skip & 8);
+    const bool fused = srb_resblock_supported(H, W) && !(ctx->path & SRB_PATH_UNFUSED_TRUNK);
     for (int i = 0; i < 8; ++i) {
         void* nxt = (i & 1) ? rb : ra;
         if (fused) {
@@ -861,11 +913,11 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
         cur = nxt;
     }
     // cur == rb after 8 blocks; long skip adds conv0's (post-activation) output
-    if (fused && !(ctx->dbg_skip & 8192)) {
+    if (fused && !(ctx->path & SRB_PATH_TILED_CONV1)) {
         if ((rc = srb_rowconv_fwd(ctx, net->rc1, cur, x0, ra, 0.f, 0, N, H, W, stream))) return rc;
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
-    if (fused && !(ctx->dbg_skip & 16384)) {
+    if (fused && !(ctx->path & SRB_PATH_TILED_TAIL)) {
         if ((rc = srb_tail9_fwd(ctx, net->tail, ra, out, oflags, N, H, W, stream))) return rc;
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, oflags, N, H, W, stream))) return rc;
     prof_mark(ctx, pst);
@@ -904,13 +956,15 @@ extern "C" int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(ctx->h_pin + io_al, ctx->d_io + io_al, io, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    if ((rc = srb_poll_abort(ctx))) return rc;
     memcpy(out_host, ctx->h_pin + io_al, io);
     return SRB_OK;
 }
 
 // ------------------------------------------------------------------------------------------
-// measurement tooling: tcgen05.mma micro-benchmark (see srb_ubench.cuh)
+// measurement tooling: tcgen05.mma micro-benchmark (see srb_ubench.cuh) — debug build only
 // ------------------------------------------------------------------------------------------
+#ifdef SRB_DEBUG
 extern "C" int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host) {
     if (!ctx || !out2_host) return fail(SRB_EINVAL, "srb_ubench_mma: NULL argument");
     if (racc < 1 || racc * n * (m64 > 0 ? m64 : 1) > 512 || m64 > 4) return fail(SRB_EINVAL, "srb_ubench_mma: racc*n*warps > 512 TMEM columns");
@@ -927,6 +981,43 @@ extern "C" int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int ite
     cudaFree(d);
     return SRB_OK;
 }
+
+extern "C" int srb_ubench_mix(srb_ctx* ctx, int nwarps, const int* n, const int* cnt, const int* acc, int rows, int cta_pair,
+                              long long* out_host) {
+    if (!ctx || !n || !cnt || !acc || !out_host || nwarps < 1 || nwarps > 4) return fail(SRB_EINVAL, "srb_ubench_mix: bad argument");
+    MixArgs a{};
+    a.nwarps = nwarps; a.rows = rows; a.commits = 2;
+    int cols = 0;
+    for (int w = 0; w < nwarps; ++w) {
+        a.n[w] = n[w]; a.cnt[w] = cnt[w]; a.acc[w] = acc[w] < 1 ? 1 : acc[w];
+        if (n[w] % 16 || n[w] < 16 || n[w] > 256) return fail(SRB_EINVAL, "srb_ubench_mix: n=%d", n[w]);
+        cols += a.acc[w] * n[w];
+    }
+    if (cols > 512) return fail(SRB_EINVAL, "srb_ubench_mix: %d TMEM columns", cols);
+    DeviceGuard dev_guard(ctx->device);
+    long long* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, 16 * sizeof(long long)));
+    CUDA_TRY(cudaMemset(d, 0, 16 * sizeof(long long)));
+    const int smem = 130 * 1024;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cta_pair ? 2 : 1); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem; cfg.stream = nullptr;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cta_pair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (cta_pair) {
+        CUDA_TRY(cudaFuncSetAttribute(ubench_mix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, ubench_mix_kernel<true>, a, d));
+    } else {
+        CUDA_TRY(cudaFuncSetAttribute(ubench_mix_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, ubench_mix_kernel<false>, a, d));
+    }
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpy(out_host, d, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return SRB_OK;
+}
+#endif  // SRB_DEBUG
 
 // ------------------------------------------------------------------------------------------
 // backward: weight / bias gradients (train.py:57 autograd of the convs)
@@ -1189,7 +1280,7 @@ extern "C" int srb_grad_batch_create(srb_ctx* ctx, const srb_grad_job* jobs, int
     }
     // longest units first: the block scheduler hands CTAs to SMs in index order as they free up
     auto unit_cost = [](const WgradUnit& u) { const int n = u.xplanes * 8; return (long long)u.num_tiles * (n / 2 > 32 + n / 4 ? n / 2 : 32 + n / 4); };
-    if (!(ctx->dbg_skip & 131072))
+    if (!(ctx->path & SRB_PATH_UNSORTED_UNITS))
         std::stable_sort(units.begin(), units.end(), [&](const WgradUnit& a, const WgradUnit& c) { return unit_cost(a) > unit_cost(c); });
     srb_grad_batch* b = new srb_grad_batch();
     b->dtype = dtype; b->nunits = (int)units.size(); b->nbias = (int)bias.size();
@@ -1403,7 +1494,7 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
     if (grid > ctx->num_sms) grid = ctx->num_sms;
-    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
     if (!rb->attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
@@ -1415,11 +1506,11 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if ((ctx->dbg_skip & 4096) && ctx->dbg_threads > 0) cfg.blockDim = dim3(ctx->dbg_threads);     // launch-overhead probes only
-    if ((ctx->dbg_skip & 4096) && ctx->dbg_smem >= 0) cfg.dynamicSmemBytes = ctx->dbg_smem;
-    for (int rep = 0; rep <= ctx->dbg_repeat; ++rep) {
+    if (SRB_DBG(ctx->dbg_skip & 4096) && ctx->dbg_threads > 0) cfg.blockDim = dim3(ctx->dbg_threads);     // launch-overhead probes only
+    if (SRB_DBG(ctx->dbg_skip & 4096) && ctx->dbg_smem >= 0) cfg.dynamicSmemBytes = ctx->dbg_smem;
+    for (int rep = 0; rep <= SRB_DBG(ctx->dbg_repeat); ++rep) {
         if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, p));
         else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, p));
     }
@@ -1499,7 +1590,7 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
     if (grid > ctx->num_sms) grid = ctx->num_sms;
-    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
     if (!rc->attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(rowconv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         CUDA_TRY(cudaFuncSetAttribute(rowconv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
@@ -1510,7 +1601,7 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (rc->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<true>, m->tm, p));
     else CUDA_TRY(cudaLaunchKernelEx(&cfg, rowconv_kernel<false>, m->tm, p));
@@ -1595,7 +1686,7 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
     if (grid > ctx->num_sms) grid = ctx->num_sms;
-    if (ctx->dbg_grid > 0 && grid > ctx->dbg_grid) grid = ctx->dbg_grid;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
     if (!t->attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(tail9_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         CUDA_TRY(cudaFuncSetAttribute(tail9_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
@@ -1606,7 +1697,7 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = (ctx->dbg_skip & 1024) ? 0 : 1;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (t->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<true>, m->tm, p));
     else CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<false>, m->tm, p));

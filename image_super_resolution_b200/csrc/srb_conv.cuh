@@ -127,7 +127,7 @@ struct ConvGeom {
 __device__ __forceinline__ float lrelu(float v, float s) { return v > 0.f ? v : v * s; }
 // trace stamp k of step `it` (CTA 0, first 64 steps); costs one predicated store when enabled, a test otherwise
 __device__ __forceinline__ void trace(const ConvParams& p, int it, int k) {
-    if (p.dbg_trace != nullptr && blockIdx.x == 0 && it < 64) p.dbg_trace[it * 8 + k] = clock64();
+    if (SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0 && it < 64) p.dbg_trace[it * 8 + k] = clock64();
 }
 
 template <bool BF16>
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[7] = clock64();    // kernel entry
+    if (threadIdx.x == 0 && SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0) p.dbg_trace[7] = clock64();    // kernel entry
 
     for (int i = threadIdx.x; i < NOUT; i += blockDim.x) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
-    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[15] = clock64();   // prologue done
+    if (threadIdx.x == 0 && SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0) p.dbg_trace[15] = clock64();   // prologue done
     // programmatic dependent launch (srb_model_pt_forward chains its launches this way): the prologue above touched only
     // this launch's constants; the next launch may start its own on the SMs this grid vacates, and every warp below that
     // touches activations first waits for the previous launch to complete (a no-op for a normal launch)
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                 mbar_wait(&empty[s], ph ^ 1, 1);
                 if (lane == 0 && kb == 0) trace(p, pit, 0);     // halo load issued
                 if (elect_one()) {
-                    if (p.dbg_skip & 1) { mbar_arrive(&full[s]); }
+                    if SRB_DBG(p.dbg_skip & 1) { mbar_arrive(&full[s]); }
                     else {
                         mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES + (WS ? G::WBLK_BYTES : 0));
                         tma_load_4d(s_a + s * G::STAGE_STRIDE, &tmap, &full[s], (tx * G::SUPER_W - G::PADX + (MODE == MODE_PAIR4 ? 1 : 0)) * 4,
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
         uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (MODE == MODE_PAIR4) ? 32u : (uint32_t)G::PLANE;
         uint32_t a_sbo = (MODE == MODE_DXN) ? 128u : (uint32_t)G::ROWP;
         uint32_t b_lbo = NOUT * 16, b_sbo = 128;
-        if (p.dbg_swap) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
+        if (SRB_DBG(p.dbg_swap)) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
         // descriptors with a zero start address; the 14-bit (addr >> 4) field is added per MMA
         const uint64_t a_desc0 = umma_desc_nosw(0, a_lbo, a_sbo);
         const uint64_t b_desc0 = umma_desc_nosw(smem_u32(s_w), b_lbo, b_sbo);
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                 const uint64_t a_desc = a_desc0 + (uint64_t)(smem_u32(s_a + s * G::STAGE_STRIDE) >> 4);
                 const uint64_t b_desc_s = WS ? umma_desc_nosw(smem_u32(s_a + s * G::STAGE_STRIDE + G::A_STRIDE), b_lbo, b_sbo) : b_desc0;
                 const uint32_t d_tmem = tmem_base + b * (NT * NOUT);
-                if (!(p.dbg_skip & 2)) {
+                if (!SRB_DBG(p.dbg_skip & 2)) {
                     int ks = 0;
                     if constexpr (MODE == MODE_STD) {
 #pragma unroll 1
@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
                 for (int t = 0; t < NT; ++t) {
                     mbar_wait(&rempty[rs], rph ^ 1, 6);
                     if (elect_one()) {
-                        if (p.dbg_skip & 1) { mbar_arrive(&rfull[rs]); }
+                        if SRB_DBG(p.dbg_skip & 1) { mbar_arrive(&rfull[rs]); }
                         else {
                             mbar_arrive_expect_tx(&rfull[rs], G::RES_TILE_BYTES);
                             tma_load_4d(s_res + rs * G::RES_TILE_BYTES, &tmap_res, &rfull[rs],
@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
         pdl_wait();                               // outputs may still be read, residual / mask written, by the previous launch
         const int L = lg * 32 + lane;             // accumulator row = pixel of the M-tile
         const size_t HW = (size_t)p.H * p.W;
-        const bool io = !(p.dbg_skip & 4);
+        const bool io = !SRB_DBG(p.dbg_skip & 4);
         const bool has_res = (p.flags & F_RESIDUAL) != 0;
         const bool do_lrelu = (p.flags & F_LRELU) != 0;
         const uint32_t s_bias_u32 = smem_u32(s_bias);
@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
     tc_fence_before();
     __syncthreads();
     if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, G::TMEM_COLS); }
-    if (threadIdx.x == 0 && p.dbg_trace != nullptr && blockIdx.x == 0) p.dbg_trace[23] = clock64();   // exit
+    if (threadIdx.x == 0 && SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0) p.dbg_trace[23] = clock64();   // exit
 }
 
 }  // namespace srb

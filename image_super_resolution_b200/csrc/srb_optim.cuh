@@ -14,7 +14,8 @@
 namespace srb {
 
 // stats[0] = sum (g / scale)^2, stats[1] = 1 if any g / scale is non-finite, stats[2] = number of optimizer steps taken
-// (incremented here when the gradients are finite: adam_ema_kernel of the same step reads it as its step number)
+// (advanced by adam_ema_kernel's last block, so this kernel may run any number of times per step: logging the norm before
+// unscale_, after step(), or without a step at all leaves the bias correction alone)
 constexpr int GSTAT_MAX_BLOCKS = 1024;
 
 __global__ void __launch_bounds__(256) grad_stats_kernel(const float4* __restrict__ g, size_t n4, const float* __restrict__ scale,
@@ -65,7 +66,6 @@ __global__ void __launch_bounds__(256) grad_stats_kernel(const float4* __restric
             const bool nonfinite = b2 || !isfinite(tt);
             stats[0] = tt;
             stats[1] = nonfinite ? 1.f : 0.f;
-            if (!nonfinite) stats[2] += 1.f;
             *counter = 0u;
         }
     }
@@ -75,7 +75,8 @@ struct AdamArgs {
     float4* p; const float4* g; float4* m; float4* v; float4* ema;      // ema may be nullptr
     size_t n4;
     const float* scale;      // GradScaler scale (device) or nullptr
-    const float* stats;      // grad_stats_kernel output of this step
+    float* stats;            // grad_stats_kernel output of this step; [2] = steps taken so far (advanced here)
+    unsigned int* counter;   // arrival counter (zero on entry, left at zero)
     float max_norm;          // > 0: clip the global norm (clip_grad_norm_ was called this step)
     float lr, beta1, beta2, eps, weight_decay;
     float ema_decay;         // d of utils/models.py:34 for this update
@@ -83,7 +84,8 @@ struct AdamArgs {
 
 __global__ void __launch_bounds__(256) adam_ema_kernel(const AdamArgs a) {
     const float inv = a.scale != nullptr ? 1.0f / __ldg(a.scale) : 1.0f;
-    const float sumsq = __ldg(a.stats), found_inf = __ldg(a.stats + 1), step = __ldg(a.stats + 2);
+    // (plain loads: the last block of this launch writes stats[2] — after every block has read it, see the tail)
+    const float sumsq = a.stats[0], found_inf = a.stats[1], step = a.stats[2] + 1.0f;
     const bool skip = found_inf != 0.f;                     // GradScaler.step: no optimizer step on non-finite gradients
     float coef = 1.0f;
     if (a.max_norm > 0.f) coef = fminf(a.max_norm / (sqrtf(sumsq) + 1e-6f), 1.0f);     // torch.nn.utils.clip_grad_norm_
@@ -115,6 +117,15 @@ __global__ void __launch_bounds__(256) adam_ema_kernel(const AdamArgs a) {
             float4 e = a.ema[i];
             e.x = d * e.x + omd * p.x; e.y = d * e.y + omd * p.y; e.z = d * e.z + omd * p.z; e.w = d * e.w + omd * p.w;
             a.ema[i] = e;
+        }
+    }
+    // the step counter advances once per optimizer step taken: by the last block to finish (every block has read it by then)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(a.counter, 1u) == gridDim.x - 1) {
+            if (!skip) a.stats[2] = step;
+            *a.counter = 0u;
         }
     }
 }

@@ -7,14 +7,28 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 
+// Probe hooks (bottleneck probes, clock traces) exist only in the -DSRB_DEBUG build that tools/ loads
+// (libsrb200_dbg.so); in the product library every such branch is a compile-time constant and disappears.
+#ifdef SRB_DEBUG
+#define SRB_DBG(expr) (expr)
+#else
+#define SRB_DBG(expr) (0)
+#endif
+
 namespace srb {
 
 // ------------------------------------------------------------------------------------------
 // Bounded waits: a protocol bug must not hang the GPU box (that is a strike); after a generous
-// spin budget the kernel records where it was stuck and traps.
+// spin budget the kernel records where it was stuck, raises the abort flag and the launch drains.
+// The flag is mirrored into host-mapped pinned memory, so the host can poll it without a device
+// synchronisation (srb_poll_abort: every sync point of the Python layer raises on it).
 // ------------------------------------------------------------------------------------------
 __device__ unsigned int g_srb_timeout_info[4];
 __device__ volatile unsigned int g_srb_abort;   // set by the first wait that runs out of budget; every later wait bails out
+__device__ unsigned int* g_srb_abort_host;      // host-mapped mirror: [0] flag, [1..4] timeout info (set up by srb_create)
+#ifndef SRB_WAIT_BUDGET_LOG2
+#define SRB_WAIT_BUDGET_LOG2 32                 // 2^32 cycles: ~2.3 s at 1.9 GHz (time-sliced / profiled runs stay far below)
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -82,14 +96,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
             }
         }
         if (g_srb_abort) return;
-        if (clock64() - t0 > (1ll << 28)) {  // ~0.14 s at 2 GHz
+        if (clock64() - t0 > (1ll << SRB_WAIT_BUDGET_LOG2)) {
             if (atomicExch((unsigned int*)&g_srb_abort, 1u) == 0u) {
                 g_srb_timeout_info[0] = 0xdead0000u | tag;
                 g_srb_timeout_info[1] = blockIdx.x;
                 g_srb_timeout_info[2] = threadIdx.x;
                 g_srb_timeout_info[3] = parity;
+                unsigned int* h = g_srb_abort_host;
+                if (h != nullptr) {
+                    h[1] = 0xdead0000u | tag; h[2] = blockIdx.x; h[3] = threadIdx.x; h[4] = parity;
+                    __threadfence_system();
+                    *reinterpret_cast<volatile unsigned int*>(h) = 1u;
+                }
             }
-            __threadfence();
+            __threadfence_system();
             return;
         }
     }

@@ -125,7 +125,7 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
 }
 
 __device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k) {
-    if (p.dbg_trace != nullptr && blockIdx.x == 0 && row < 32) p.dbg_trace[row * 32 + k] = clock64();
+    if (SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0 && row < 32) p.dbg_trace[row * 32 + k] = clock64();
 }
 
 // a segment: output rows [y0, y1) of strip-set ss, with the hidden / input row ranges it needs (clipped to the image)
@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 57);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (p.dbg_trace != nullptr && threadIdx.x == 0) {           // per-CTA timing: [1024 + 8 * cta + k]
+    if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) {           // per-CTA timing: [1024 + 8 * cta + k]
         long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
         p.dbg_trace[1024 + 8 * blockIdx.x] = gt;
         p.dbg_trace[1024 + 8 * blockIdx.x + 1] = clock64();
@@ -234,8 +234,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         p.dbg_trace[1024 + 8 * blockIdx.x + 6] = launch;
     }
 
-    if (p.dbg_skip & 4096) {        // launch-overhead probe: nothing but the stamps
-        if (p.dbg_trace != nullptr && threadIdx.x == 0) {
+    if SRB_DBG(p.dbg_skip & 4096) {        // launch-overhead probe: nothing but the stamps
+        if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) {
             long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
             p.dbg_trace[1024 + 8 * blockIdx.x + 5] = gt;
             const int launch = (int)p.dbg_trace[1024 + 8 * blockIdx.x + 6];
@@ -283,12 +283,12 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     __syncthreads();
     tc_fence_after();
 
-    if (p.dbg_trace != nullptr && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 2] = clock64();
+    if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 2] = clock64();
     // Everything above touched only this launch's constants.  The next launch in the stream may now start its own
     // prologue on every SM this grid vacates; the warps below that touch activations first wait for the previous launch.
     pdl_launch_dependents();
     const int g_begin = (int)((long long)blockIdx.x * p.total_rows / gridDim.x);
-    const int g_end = (p.dbg_skip & 2048) ? g_begin : (int)((long long)(blockIdx.x + 1) * p.total_rows / gridDim.x);   // 2048: prologue-only probe
+    const int g_end = SRB_DBG(p.dbg_skip & 2048) ? g_begin : (int)((long long)(blockIdx.x + 1) * p.total_rows / gridDim.x);   // 2048: prologue-only probe
     const size_t HW = (size_t)p.H * p.W;
 
     if (warp == 0) {
@@ -309,14 +309,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 19);         // x stage free
-                if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 19);         // x stage free
+                if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)
                     tma_load_4d(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, &xfull[st], (gx * 8 - 1) * 4, r, 0, n);
                 __syncwarp();
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 20);         // x row requested
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 20);         // x row requested
             }
         }
     } else if (warp == 1) {
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 mbar_wait<RB_CTRL>(&xfull[xst], xph, 33);
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 21);         // x row arrived
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 21);         // x row arrived
                 const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
                 const int a_lo = hbase + lo - sg.hlo, a_n = hi - lo + 1, a_s0 = lo - (r - 1);
                 for (; h_acq < a_lo + a_n; ++h_acq) {
@@ -345,11 +345,11 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 }
                 const int slot_lo = (hslot0 + (lo - sg.hlo)) % G::RH;
                 tc_fence_after();
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
                 if (elect_one()) {
                     const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
-                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, (p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
-                    if (!(p.dbg_skip & (2 | 16))) {
+                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
+                    if (!SRB_DBG(p.dbg_skip & (2 | 16))) {
 #pragma unroll
                         for (int kk = 0; kk < G::KA; ++kk) {
                             const int dx = kk >> 2, c2 = kk & 3;
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     if (r == sg.xhi && r <= sg.hhi) umma_commit(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
                 }
                 __syncwarp();
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
                 if (++xst == G::XSTAGES) { xst = 0; xph ^= 1; }
             }
             const int nh = sg.hhi - sg.hlo + 1;
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int hc = ybase_h + h - sg.hlo;               // running hidden-row counter (trace only)
                 mbar_wait<RB_CTRL>(&hsfull[hs], hph, 35);
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 16);         // hidden row in shared memory
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, hc, 16);         // hidden row in shared memory
                 const int lo = h - 1 > sg.y0 ? h - 1 : sg.y0, hi = h + 1 < sg.y1 - 1 ? h + 1 : sg.y1 - 1;
                 const int b_lo = ybase + lo - sg.y0, b_n = hi - lo + 1, b_s0 = lo - (h - 1);
                 for (; y_acq < b_lo + b_n; ++y_acq) {
@@ -393,11 +393,11 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 }
                 const int slot_lo = (yslot0 + (lo - sg.y0)) % G::RY;
                 tc_fence_after();
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 17);         // output accumulator rows acquired
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, hc, 17);         // output accumulator rows acquired
                 if (elect_one()) {
                     const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
-                    const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, (p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
-                    if (!(p.dbg_skip & (2 | 32))) {
+                    const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
+                    if (!SRB_DBG(p.dbg_skip & (2 | 32))) {
 #pragma unroll
                         for (int k = 0; k < G::KB; ++k) {
                             const int dx = k >> 1, c2 = k & 1;
@@ -409,7 +409,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     if (h == sg.hhi && h <= sg.y1 - 1) umma_commit(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
                 }
                 __syncwarp();
-                if (p.dbg_trace != nullptr && lane == 0) rb_trace(p, hc, 18);         // convB MMAs + commits issued
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, hc, 18);         // convB MMAs + commits issued
                 if (++hs == G::HSLOTS) { hs = 0; hph ^= 1; }
             }
             ybase_h += sg.hhi - sg.hlo + 1;
@@ -428,7 +428,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + G::TM_H + ((uint32_t)(lg * 32) << 16);
         const uint32_t s_h_u32 = smem_u32(s_h);
-        const bool tr = p.dbg_trace != nullptr && lane == 0 && lg == 0;
+        const bool tr = SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && lg == 0;
         int hbase = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
@@ -451,8 +451,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tmem_ld32(t_lane + slot * G::CH, rr);
                 tmem_ld_wait();
                 if (RB_BIAS_MODE == 1) {
-                    if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
-                } else if (!(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
+                    if (!SRB_DBG(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
+                } else if (!SRB_DBG(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[k]);
@@ -504,8 +504,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         const int L = lg * 32 + lane;
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + G::TM_Y + half * 32 + ((uint32_t)(lg * 32) << 16);
-        const bool tr = p.dbg_trace != nullptr && threadIdx.x == 384;
-        const bool no_ld = (p.dbg_skip & (4 | 128)) != 0, no_st = (p.dbg_skip & (4 | 256)) != 0;
+        const bool tr = SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 384;
+        const bool no_ld = SRB_DBG(p.dbg_skip & (4 | 128)) != 0, no_st = SRB_DBG(p.dbg_skip & (4 | 256)) != 0;
         const size_t plane = HW;                   // granules per plane
         pdl_wait();                                // x is the previous launch's output; y may still be read by it
         int c = 0, g = g_begin;                    // c: running output-row counter
@@ -536,8 +536,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tmem_ld32(t_lane + slot * G::CB, rr);
                 tmem_ld_wait();
                 if (RB_BIAS_MODE == 1) {
-                    if (!(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CB);
-                } else if (!(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
+                    if (!SRB_DBG(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CB);
+                } else if (!SRB_DBG(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias
                     uint32_t bv[32];
 #pragma unroll
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[G::CH + half * 32 + k]);
@@ -580,10 +580,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         }
     }
 
-    if (p.dbg_trace != nullptr && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 3] = clock64();   // producer done
+    if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 3] = clock64();   // producer done
     tc_fence_before();
     __syncthreads();
-    if (p.dbg_trace != nullptr && threadIdx.x == 0) {
+    if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) {
         long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
         p.dbg_trace[1024 + 8 * blockIdx.x + 4] = clock64();
         p.dbg_trace[1024 + 8 * blockIdx.x + 5] = gt;

@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
             for (int r = sg.hlo; r <= sg.hhi; ++r, ++xc) {          // x rows y0-1 .. y1 (clipped): RBSeg's hidden-row range
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 51);
-                if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
+                if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
                 if (elect_one()) {
                     const uint64_t ad = adesc0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
                     const RBPlan q = rb_plan<G::C, G::RY, BF16>(tmem_base, slot_lo, b_n, b_s0);
-                    if (!(p.dbg_skip & 2)) {
+                    if (!SRB_DBG(p.dbg_skip & 2)) {
 #pragma unroll
                         for (int kk = 0; kk < G::KS; ++kk) {
                             const int dx = kk >> 2, c2 = kk & 3;
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
         const int L = lg * 32 + lane;
         const int grp = L >> 3, i = L & 7;
         const uint32_t t_lane = tmem_base + half * 32 + ((uint32_t)(lg * 32) << 16);
-        const bool has_res = p.res != nullptr && !(p.dbg_skip & 4), no_st = (p.dbg_skip & 4) != 0;
+        const bool has_res = p.res != nullptr && !SRB_DBG(p.dbg_skip & 4), no_st = SRB_DBG(p.dbg_skip & 4) != 0;
         pdl_wait();
         int c = 0, g = g_begin;
         RBSeg sg;

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 61);
-                if (p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
+                if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
                     const uint32_t id1 = umma_idesc_f16(128, n1 * G::NS, BF16 ? 1 : 0);
                     const uint32_t id2 = umma_idesc_f16(128, (n2 > 0 ? n2 : 1) * G::NS, BF16 ? 1 : 0);
                     const uint64_t b1 = bdesc0 + (uint64_t)((s0 * G::NS * 16) >> 4), b2 = bdesc0 + (uint64_t)(((s0 + n1) * G::NS * 16) >> 4);
-                    if (!(p.dbg_skip & 2)) {
+                    if (!SRB_DBG(p.dbg_skip & 2)) {
 #pragma unroll
                         for (int kk = 0; kk < G::KS; ++kk) {
                             const uint64_t a = ad + (uint64_t)((2 * kk * 128) >> 4), bo = (uint64_t)((kk * G::W_STEP) >> 4);
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
         float* const P = s_p + set * (G::PCOLS * G::PLEN);
         const int gxw = p.TS > 0 ? 128 : p.GX * 8;                  // pixels of one image row in the tile
         const int pidx = (L / gxw) * (gxw + 8) + (L % gxw);         // padded position of this lane's pixel (its own column at +4)
-        const bool no_st = (p.dbg_skip & 4) != 0;
+        const bool no_st = SRB_DBG(p.dbg_skip & 4) != 0;
         pdl_wait();
         int c = 0, g = g_begin;
         TLSeg sg;

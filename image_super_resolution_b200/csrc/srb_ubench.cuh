@@ -68,4 +68,92 @@ __global__ void __launch_bounds__(128, 1) ubench_mma_kernel(int layout, int racc
     if (threadIdx.x < 32) tmem_dealloc(tmem_base, 512);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Mixed issue streams (the fused residual block's issuers): warp w issues, per "row", cnt[w] MMAs of N = n[w] round-robin
+// over acc[w] accumulators (acc = 1: one dependent chain), then `commits` commits; `rows` rows back to back.
+// PAIR: a cluster of two CTAs, cta_group::2 MMAs of M = 256 issued by the leader (each CTA reads its own A rows and
+// half of B from its own shared memory).
+// ------------------------------------------------------------------------------------------------------------------
+struct MixArgs { int nwarps, rows, commits; int n[4], cnt[4], acc[4]; };
+
+template <bool PAIR>
+__global__ void __launch_bounds__(128, 1) ubench_mix_kernel(MixArgs a, long long* out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    __shared__ uint64_t bar[8];
+    __shared__ uint32_t s_tmem;
+    __shared__ long long s_t0;
+    uint32_t rank = 0;
+    if (PAIR) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    for (int i = threadIdx.x; i < 128 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x == 0) { for (int i = 0; i < 8; ++i) mbar_init(&bar[i], 1); fence_mbar_init(); }
+    if (threadIdx.x < 32) {
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else tmem_alloc(&s_tmem, 512);
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    if (PAIR) { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+    else __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = s_tmem;
+    const int wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_t0 = clock64();
+    __syncthreads();
+    const long long t0 = s_t0;
+    if (wid < a.nwarps && rank == 0) {
+        int cb = 0;
+        for (int v = 0; v < wid; ++v) cb += a.acc[v] * a.n[v];
+        const int n = a.n[wid], cnt = a.cnt[wid], acc = a.acc[wid];
+        const uint64_t adesc = umma_desc_nosw(smem_u32(smem) + wid * 8192, 160, 1280);           // x-row boxes
+        const uint64_t bdesc = umma_desc_nosw(smem_u32(smem + 64 * 1024), (PAIR ? n / 2 : n) * 16, 128);
+        const uint32_t idesc = umma_idesc_f16(PAIR ? 256 : 128, n, 0);
+        const uint32_t bstep = (uint32_t)(((PAIR ? n / 2 : n) * 32) >> 4);
+        uint64_t* mybar = &bar[wid];
+        uint64_t* dummy = &bar[4 + wid];
+#pragma unroll 1
+        for (int r = 0; r < a.rows; ++r) {
+            if (elect_one()) {
+                int k = 0;
+#pragma unroll 1
+                for (int i = 0; i < cnt; ++i) {
+                    const uint32_t d = tmem_base + cb + k * n;
+                    if (PAIR) {
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                     "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                                     ::"r"(d), "l"(adesc + (uint64_t)(2 * (i & 3))), "l"(bdesc + (uint64_t)((i & 7) * bstep)), "r"(idesc), "r"(1u) : "memory");
+                    } else umma_f16_ss(d, adesc + (uint64_t)(2 * (i & 3)), bdesc + (uint64_t)((i & 7) * bstep), idesc, 1u);
+                    if (++k == acc) k = 0;
+                }
+                for (int c = 0; c < a.commits; ++c) {
+                    if (PAIR) asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                                           ::"r"(smem_u32(dummy)), "h"((uint16_t)3) : "memory");
+                    else umma_commit(dummy);
+                }
+            }
+            __syncwarp();
+        }
+        const long long t1 = clock64();
+        if (elect_one()) {
+            if (PAIR) asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                                   ::"r"(smem_u32(mybar)), "h"((uint16_t)3) : "memory");
+            else umma_commit(mybar);
+        }
+        __syncwarp();
+        mbar_wait(mybar, 0, 102);
+        const long long t2 = clock64();
+        if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) { out[1 + wid] = t1 - t0; out[5 + wid] = t2 - t0; }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x == 0) out[0] = clock64() - t0;
+    if (PAIR) { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+    if (threadIdx.x < 32) {
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        else tmem_dealloc(tmem_base, 512);
+    }
+}
+
 }  // namespace srb

@@ -97,7 +97,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
             const int ty = r / u.tiles_x, tx = r - ty * u.tiles_x;
             mbar_wait(&empty[s], ph ^ 1, 21);
             if (elect_one()) {
-                if (dbg_skip & 1) { mbar_arrive(&full[s]); }
+                if SRB_DBG(dbg_skip & 1) { mbar_arrive(&full[s]); }
                 else {
                     mbar_arrive_expect_tx(&full[s], bytes);
                     uint8_t* st = s_st + s * G::STAGE_STRIDE;
@@ -120,7 +120,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
                 const uint32_t xa = smem_u32(s_st + s * G::STAGE_STRIDE);
                 const uint64_t a_desc = a_desc0 + (uint64_t)((xa + G::X_STRIDE) >> 4);
                 const uint64_t b_desc = b_desc0 + (uint64_t)(xa >> 4);
-                if (!(dbg_skip & 2)) {
+                if (!SRB_DBG(dbg_skip & 2)) {
 #pragma unroll 1
                     for (int r = 0; r < G::TH; ++r) {
                         const uint64_t ad = a_desc + (uint64_t)((r * G::DYROWP) >> 4);
@@ -167,7 +167,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
                 float v = acc[k];
 #pragma unroll
                 for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                if (px == 0 && plane * 8 + k < u.cout_blk && part < u.num_tiles && !(dbg_skip & 1)) atomicAdd(u.db + plane * 8 + k, v * u.scale);
+                if (px == 0 && plane * 8 + k < u.cout_blk && part < u.num_tiles && !SRB_DBG(dbg_skip & 1)) atomicAdd(u.db + plane * 8 + k, v * u.scale);
             }
         }
     } else {
@@ -175,7 +175,7 @@ __device__ __forceinline__ void wgrad_body(const CUtensorMap* tmap_x, const CUte
         const int lg = warp & 3;
         mbar_wait(done, 0, 23);
         tc_fence_after();
-        const bool has_tiles = part < u.num_tiles && !(dbg_skip & 2);
+        const bool has_tiles = part < u.num_tiles && !SRB_DBG(dbg_skip & 2);
         const int L = lg * 32 + lane, sft = L / G::NOUT, co = L % G::NOUT;
         if (lg * 32 < KS * G::NOUT) {
             const bool lane_ok = has_tiles && sft < KS && co < u.cout_blk;

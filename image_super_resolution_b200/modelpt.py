@@ -169,8 +169,9 @@ class ModelPT:
         """Pipelined host-to-host inference over a sequence of uint8 host batches — the shape of rs.py's video loop
         (rs.py:58-76: frames from the reader -> model -> writer).  Yields one pinned uint8 host tensor per input batch, in
         order.  H2D of batch i+1 and D2H of batch i-1 run on copy streams while the kernels of batch i run on the compute
-        stream; `depth` batches are in flight.  A yielded tensor is valid until `depth` more batches have been consumed
-        (its buffer is then reused): write it out or copy it before asking for more, as a frame writer does.
+        stream; `depth` batches are in flight.  A yielded tensor stays valid until `depth` more items have been taken from the
+        generator (the ring holds 2 * depth + 1 slots; the slot is then reused): write it out or copy it before that, as a
+        frame writer does.  `list(model.stream(...))` of more than depth + 1 batches therefore needs a .clone() per item.
         The ring of device / pinned buffers is kept on the model between calls, and (graphs=True) the 12 launches of a slot's
         forward are captured once per (slot, shape) as a CUDA graph: a step costs the host three enqueues, which is what
         keeps eight ranks sharing one host at the single-GPU rate."""
@@ -185,7 +186,7 @@ class ModelPT:
             st = self.__dict__["_stream_state"] = dict(net=self._net, dev=dev, slots={},
                                                        streams=tuple(torch.cuda.Stream(dev) for _ in range(3)))
         s_in, s_c, s_out = st["streams"]
-        nbuf = depth + 1
+        nbuf = 2 * depth + 1
         pending = []                   # slots submitted and not yet yielded
         i = 0
 
@@ -209,7 +210,7 @@ class ModelPT:
             if xb.dtype != torch.uint8 or xb.dim() != 4 or xb.shape[1] != 3 or xb.is_cuda:
                 raise RuntimeError("stream() takes uint8 host tensors [N,3,H,W]")
             xb = xb.contiguous()
-            if len(pending) == nbuf:                       # the slot about to be reused must have been consumed
+            if len(pending) > depth:                       # (never: a batch is yielded as soon as depth + 1 are pending)
                 raise RuntimeError("internal: ring overrun")
             key = (i % nbuf, nbuf, layout, tuple(xb.shape), bool(graphs))
             sl = st["slots"].get(key)
@@ -237,9 +238,11 @@ class ModelPT:
             if len(pending) > depth:
                 j = pending.pop(0)
                 j[5].synchronize()
+                self._ctx.poll()                           # a kernel-side pipeline timeout raises here, not downstream
                 yield j[2]
         for j in pending:
             j[5].synchronize()
+            self._ctx.poll()
             yield j[2]
 
     @staticmethod

@@ -17,7 +17,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
-from . import ops, _lib
+from . import ops, _lib, training as _training
 from ._lib import Context
 
 
@@ -145,7 +145,10 @@ class _NetPlan:
         return ops.PackedConv(self.ctx, w, b, bn=bn, bn_eps=eps, dtype=self.dtype)
 
     def _param_versions(self):
-        return tuple(p._version for p in self.net.parameters()) + tuple(b._version for b in self.net.buffers())
+        # autograd's version counters do not see writes through raw pointers (optim.FlatAdam's fused step, its attached EMA
+        # arena) or through `.data` (broadcast_parameters): those bump training.PARAM_EPOCH instead
+        return (tuple(p._version for p in self.net.parameters()) + tuple(b._version for b in self.net.buffers())
+                + (_training.PARAM_EPOCH[0],))
 
     def repack(self):
         n = self.net
@@ -168,47 +171,63 @@ class _NetPlan:
         return self.buffers[key]
 
     @torch.no_grad()
-    def forward(self, x: torch.Tensor, u8_out: bool = False, x_is_c8: torch.Tensor | None = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor | None, u8_out: bool = False, fill_input=None, shape=None) -> torch.Tensor:
+        """x: fp32 [N,3,H,W] (converted to the C8 input plane by the library's kernel), or `fill_input(plane)` writes the
+        plane itself (Model.forward: Normalize fused into the uint8 -> C8 pack).  Every kernel of the forward is the library's:
+        the input conversion writes straight into the captured graph's static input plane, the trunk replays as one graph,
+        and the tail conv is launched into a fresh output tensor (no staging copies)."""
         if self.versions != self._param_versions():
             self.repack()   # parameters changed (optimizer step / load_state_dict): derived caches are re-derived
-        N, _, H, W = x.shape
-        xin = x_is_c8 if x_is_c8 is not None else ops.nchw_to_c8(x, dtype=self.dtype)          # 1 plane (3 ch + zeros)
+        N, _, H, W = shape if shape is not None else x.shape
+
+        def fill(plane):
+            if fill_input is not None:
+                fill_input(plane)
+            else:
+                ops.nchw_to_c8(x, out=plane, planes=1, dtype=self.dtype)
+
         if not self.use_graphs:
-            return self._run(xin, N, H, W, u8_out)
-        key = (N, H, W, bool(u8_out))
+            xin = self._buf("xin", N, 1, H, W)
+            fill(xin)
+            cur, h, w = self._run_trunk(xin, N, H, W)
+            return self._run_tail(cur, N, h, w, u8_out)
+        key = (N, H, W)
         st = self.graphs.get(key)
         if st is None:
             if len(self.graphs) >= 8:                     # many different shapes (ragged tiles): start over
                 self.graphs, self.buffers = {}, {}
-            xs = xin.clone()
-            self._run(xs, N, H, W, u8_out)                # eager once: buffers, kernel attributes
+            xs = ops.c8_empty(N, 1, H, W, self.dtype, self.device)
+            fill(xs)
+            self._run_trunk(xs, N, H, W)                  # eager once: buffers, kernel attributes
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 1), "srb_set_programmatic_launch")
             try:                                          # the filters are constants of the graph: its conv nodes are chained
                 with torch.cuda.graph(g, capture_error_mode="thread_local"):     # by programmatic dependent launch edges
-                    out = self._run(xs, N, H, W, u8_out)
+                    cur, h, w = self._run_trunk(xs, N, H, W)
             finally:
                 _lib.check(_lib.lib().srb_set_programmatic_launch(self.ctx.handle, 0), "srb_set_programmatic_launch")
-            st = self.graphs[key] = (g, xs, out)
-        g, xs, out = st
-        xs.copy_(xin)
+            st = self.graphs[key] = (g, xs, cur, h, w)
+        g, xs, cur, h, w = st
+        fill(xs)
         g.replay()
-        return out.clone()
+        return self._run_tail(cur, N, h, w, u8_out)
 
-    def _run(self, xin: torch.Tensor, N: int, H: int, W: int, u8_out: bool) -> torch.Tensor:
+    def _run_trunk(self, xin: torch.Tensor, N: int, H: int, W: int):
+        """conv0 .. last Scaler; returns (tail input, h, w)."""
         n = self.net
-        dense = [self._buf(f"dense{i}", N, 24, H, W) for i in range(3)]
-        x0 = self._buf("x0", N, 8, H, W)
+        # X holds conv0's output (the long skip, utils/models.py:647) in planes 0..7 for the whole forward and doubles as the
+        # first RDB's dense buffer; three more dense buffers rotate through the RRDBs
+        X = self._buf("denseX", N, 24, H, W)
+        rot = [self._buf(f"dense{i}", N, 24, H, W) for i in range(3)]
         s0, f0 = _slope(n.conv0.act)
-        ops.conv2d_fwd(self.conv0, xin, 1, 0, x0, 8, 0, N, H, W, slope=s0, flags=f0)
-        dense[0][:, :8].copy_(x0)                      # RRDB input lives in planes 0..7 of a dense buffer
-        a = 0                                          # index of the dense buffer holding the current RRDB input
+        ops.conv2d_fwd(self.conv0, xin, 1, 0, X, 24, 0, N, H, W, slope=s0, flags=f0)
+        a, free = X, list(rot)                         # a: buffer holding the current RRDB's input (its skip)
         for rrdb, packs in zip(n.residual, self.rdbs):
-            order = [a, (a + 1) % 3, (a + 2) % 3]      # RDB1: A->B, RDB2: B->C, RDB3: C->B (A keeps the RRDB skip)
-            src_dst = [(order[0], order[1]), (order[1], order[2]), (order[2], order[1])]
+            b, c = free[0], free[1]                    # RDB1: a->b, RDB2: b->c, RDB3: c->b
+            src_dst = [(a, b), (b, c), (c, b)]
             for d, (rdb, pk) in enumerate(zip(rrdb.net, packs)):
-                src, dst = dense[src_dst[d][0]], dense[src_dst[d][1]]
+                src, dst = src_dst[d]
                 for i in range(4):
                     si, fi = _slope(getattr(rdb, f"conv{i}").act)
                     ops.conv2d_fwd(pk[i], src, 24, 0, src, 24, 8 + 4 * i, N, H, W, slope=si, flags=fi)
@@ -219,11 +238,11 @@ class _NetPlan:
                 else:         # + the RRDB skip: R*(r*conv + rdb_in) + rrdb_in  (utils/models.py:317)
                     R = float(rrdb.add_rate)
                     ops.conv2d_fwd(pk[4], src, 24, 0, dst, 24, 0, N, H, W, residual=src, res_planes=24, res_off=0,
-                                   res_scale=R, out_scale=R * r, res2=dense[order[0]], res2_planes=24, res2_off=0,
-                                   res2_scale=1.0)
-            a = order[1]
+                                   res_scale=R, out_scale=R * r, res2=a, res2_planes=24, res2_off=0, res2_scale=1.0)
+            free = [t for t in rot if t is not b]      # the output (b) is the next RRDB's input; X is never recycled
+            a = b
         t = self._buf("t", N, 8, H, W)
-        ops.conv2d_fwd(self.conv1, dense[a], 24, 0, t, 8, 0, N, H, W, residual=x0, res_planes=8, res_off=0)
+        ops.conv2d_fwd(self.conv1, a, 24, 0, t, 8, 0, N, H, W, residual=X, res_planes=24, res_off=0)
         cur, h, w = t, H, W
         for k, (s, pk) in enumerate(zip(n.scaler, self.scalers)):
             up = self._buf(f"up{k}", N, 8, 2 * h, 2 * w)
@@ -231,7 +250,10 @@ class _NetPlan:
             for q in range(4):
                 ops.conv2d_fwd(pk[q], cur, 8, 0, up, 8, 2 * q, N, h, w, slope=sl, flags=fl | ops.F_PIXSHUF2)
             cur, h, w = up, 2 * h, 2 * w
-        tanh = ops.F_TANH if isinstance(n.conv2.act, nn.Tanh) else 0
+        return cur, h, w
+
+    def _run_tail(self, cur: torch.Tensor, N: int, h: int, w: int, u8_out: bool) -> torch.Tensor:
+        tanh = ops.F_TANH if isinstance(self.net.conv2.act, nn.Tanh) else 0
         if u8_out:
             out = torch.empty((N, 3, h, w), dtype=torch.uint8, device=self.device)
             ops.conv2d_fwd(self.conv2, cur, 8, 0, out, 0, 0, N, h, w, flags=tanh | ops.F_U8OUT)
@@ -241,7 +263,7 @@ class _NetPlan:
         return out
 
     def launches(self) -> int:
-        return 2 + 15 * len(self.rdbs) + 1 + 4 * len(self.scalers) + 1
+        return 2 + 5 * 3 * len(self.rdbs) + 1 + 4 * len(self.scalers) + 1
 
 
 class _SRNet(nn.Module):
@@ -395,13 +417,15 @@ class Model(nn.Module):
         from ._lib import lib, check
         plan = core._plan(inputs.device)
         N, _, H, W = inputs.shape
-        xin = ops.c8_empty(N, 1, H, W, plan.dtype, inputs.device)
         mean = (C.c_float * 3)(*norm.mean.flatten().tolist())
         std = (C.c_float * 3)(*norm.std.flatten().tolist())
-        check(lib().srb_u8nchw_to_c8(plan.ctx.handle, inputs.contiguous().data_ptr(), xin.data_ptr(), mean, std,
-                                     float(norm.max_pixel_value), plan.dtype, N, H, W,
-                                     C.c_void_p(torch.cuda.current_stream(inputs.device).cuda_stream)), "srb_u8nchw_to_c8")
-        return plan.forward(inputs, u8_out=True, x_is_c8=xin)
+        src = inputs.contiguous()
+
+        def fill(plane):       # Normalize (utils/datasets.py:65-71) fused into the uint8 -> C8 pack, written into the plan's input plane
+            check(lib().srb_u8nchw_to_c8(plan.ctx.handle, src.data_ptr(), plane.data_ptr(), mean, std,
+                                         float(norm.max_pixel_value), plan.dtype, N, H, W,
+                                         C.c_void_p(torch.cuda.current_stream(inputs.device).cuda_stream)), "srb_u8nchw_to_c8")
+        return plan.forward(None, u8_out=True, fill_input=fill, shape=(N, 3, H, W))
 
     def fuse(self):
         for m in self.modules():

@@ -144,7 +144,7 @@ class FlatAdam(torch.optim.Optimizer):
         check(lib().srb_adam_ema_step(self.ctx.handle, self.p_arena.data_ptr(), self.g_arena.data_ptr(), self.m_arena.data_ptr(),
                                       self.v_arena.data_ptr(), ema_ptr, self.n,
                                       None if self._scale is None else self._scale.data_ptr(), self.stats.data_ptr(),
-                                      float(self._max_norm), float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]),
+                                      self.work.data_ptr(), float(self._max_norm), float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]),
                                       float(g["eps"]), float(g["weight_decay"]), d, _stream_ptr(self.device)), "srb_adam_ema_step")
         self._stats_valid, self._scale, self._max_norm = False, None, 0.0
         from . import training
@@ -152,12 +152,12 @@ class FlatAdam(torch.optim.Optimizer):
         return None
 
     def zero_grad(self, set_to_none: bool = True):
+        """The gradients are views of the arena backward rewrites: dropping them is all there is to do.  set_to_none=False
+        is treated the same way — a retained .grad would alias the arena the next backward writes (training.TrainPlan.backward
+        refuses that), and gradient accumulation over several backward passes is not supported by the flat arena."""
         self._stats_valid, self._scale, self._max_norm = False, None, 0.0
-        if set_to_none:                # the gradients are views of the arena backward rewrites: dropping them is all there is to do
-            for p in self.param_groups[0]["params"]:
-                p.grad = None
-        else:
-            super().zero_grad(set_to_none=False)
+        for p in self.param_groups[0]["params"]:
+            p.grad = None
 
     def load_state_dict(self, state_dict):
         """torch's format; the loaded moments are copied INTO the flat arenas (the views must stay views)."""
@@ -165,11 +165,15 @@ class FlatAdam(torch.optim.Optimizer):
         steps = self.stats[2]
         super().load_state_dict(state_dict)
         with torch.no_grad():
-            for p, s in self.state.items():
+            if not self.state:             # a checkpoint taken before the first step: fresh moments, step 0
+                self.m_arena.zero_(); self.v_arena.zero_(); steps.zero_()
+            for p in self.param_groups[0]["params"]:
                 m, v = views[id(p)]
-                m.copy_(s["exp_avg"]); v.copy_(s["exp_avg_sq"])
-                steps.copy_(torch.as_tensor(s["step"], dtype=torch.float32))
-                s["exp_avg"], s["exp_avg_sq"], s["step"] = m, v, steps
+                s = self.state.get(p)
+                if s:
+                    m.copy_(s["exp_avg"]); v.copy_(s["exp_avg_sq"])
+                    steps.copy_(torch.as_tensor(s["step"], dtype=torch.float32))
+                self.state[p] = dict(step=steps, exp_avg=m, exp_avg_sq=v)      # the views stay views of the arenas
 
 
 def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=False, foreach=None):

@@ -127,10 +127,14 @@ def upscale_image(model: ModelPT | ShardedModel, image: torch.Tensor, window_siz
 
     def download(t: torch.Tensor) -> torch.Tensor:
         if out is None:
-            return t.cpu()
-        out.copy_(t, non_blocking=True)
-        torch.cuda.current_stream(t.device).synchronize()
-        return out
+            r = t.cpu()
+        else:
+            out.copy_(t, non_blocking=True)
+            torch.cuda.current_stream(t.device).synchronize()
+            r = out
+        for m in reps:
+            m._ctx.poll()          # a kernel-side pipeline timeout raises here instead of returning garbage pixels
+        return r
 
     src = image if not image.is_cuda else image.cpu()
     if G == 1 and image.is_cuda and image.device == reps[0]._device:

@@ -103,6 +103,8 @@ def broadcast_parameters(model, src: int = 0):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         for t in list(model.parameters()) + list(model.buffers()):
             dist.broadcast(t.data, src)
+        from . import training
+        training.PARAM_EPOCH[0] += 1            # written through .data: autograd's version counters did not move
 
 
 class _NullBoard:
@@ -148,4 +150,7 @@ def train(model, ema, dataloader, compute_loss, optimizer, gradscaler, schedule,
         # the host keeps enqueueing the next step while the device finishes this one (a .item() per step leaves the GPU idle
         # for the host's whole launch path: 0.7 of 9.7 ms).  Same return value: the list of per-step losses.
         losses = torch.stack(deferred).float().cpu().tolist()
+    if device.type == "cuda":
+        from ._lib import Context
+        Context.get(device.index or 0).poll()      # a kernel-side pipeline timeout during the epoch raises here
     return losses

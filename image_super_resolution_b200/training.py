@@ -184,6 +184,14 @@ class TrainPlan:
         return self.graphs["out"]
 
     def backward(self, gout: torch.Tensor) -> list[torch.Tensor]:
+        # The gradients handed to autograd are views of the flat arena this call rewrites.  A parameter that still holds
+        # last step's .grad holds the SAME memory: AccumulateGrad would add the new gradient onto itself (2 g instead of
+        # g1 + g2).  Gradient accumulation over several backward passes is not supported: refuse instead of being wrong.
+        for p in self.params:
+            if p.grad is not None:
+                raise RuntimeError("backward with .grad still set: the drop-in nets write their gradients into one flat arena, "
+                                   "so gradients cannot be accumulated over several backward passes — call "
+                                   "optimizer.zero_grad() (set_to_none=True, torch's default and what train.py:53 does) first")
         if not self.use_graphs:
             grads = self._backward_impl(gout)
         else:

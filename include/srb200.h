@@ -54,8 +54,22 @@ int srb_version(void);
 int srb_create(int device, srb_ctx** out);
 void srb_destroy(srb_ctx* ctx);
 int srb_num_sms(const srb_ctx* ctx);
-/* diagnostics only: key 0 = swap LBO/SBO in UMMA descriptors, key 1 = grid size cap (0 = #SMs) */
-int srb_debug_set(srb_ctx* ctx, int key, int value);
+/* Host-side options of a context (no effect inside any kernel):
+ *   SRB_OPT_MAX_GRID  cap on the persistent grids (0 = one CTA per SM): leaves SMs to a co-running stream; the parity tests
+ *                     use it to move the row segments' boundaries
+ *   SRB_OPT_PATH      SRB_PATH_* bits selecting an alternative kernel family for a layer of the model.pt graph (the tiled
+ *                     implicit-GEMM kernels the row-fold ones replaced: kept as tested second implementations) */
+#define SRB_OPT_MAX_GRID 1
+#define SRB_OPT_PATH 2
+#define SRB_PATH_UNFUSED_TRUNK 8          /* ResidualBlock1 as two conv launches instead of the fused kernel          */
+#define SRB_PATH_NO_PDL 1024              /* plain launches (no programmatic dependent launch)                         */
+#define SRB_PATH_TILED_CONV1 8192         /* conv1 + long skip on the tiled kernel                                      */
+#define SRB_PATH_TILED_TAIL 16384         /* conv2 9x9 + tanh on the tiled (dx-folded) kernel                           */
+#define SRB_PATH_C8_HEAD 32768            /* conv0 9x9 on C8 input planes (pixel pairs in K) instead of pair granules   */
+#define SRB_PATH_LARGE_TILING 65536       /* never pick the small-problem super-tile shapes                             */
+#define SRB_PATH_UNSORTED_UNITS 131072    /* batched weight gradient: units in job order                                */
+#define SRB_PATH_WS_LARGE_TILING 262144   /* large tiling for the weight-streaming convs only                           */
+int srb_set_option(srb_ctx* ctx, int key, int value);
 
 /* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for
  * none), convert to dtype and lay the filter out as the UMMA B operand.  w is fp32 OIHW on the HOST.
@@ -148,18 +162,20 @@ int srb_model_pt_launches(int H, int W);
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
 /* cudaDeviceSynchronize + report a kernel-side pipeline timeout (kernels never hang: bounded waits) */
 int srb_check_device(srb_ctx* ctx);
+/* The same report without a synchronisation: reads the host-mapped mirror of the kernels' abort flag.  SRB_OK when no
+ * wait of any launch on this device has timed out since the last check; otherwise SRB_ECUDA (flag cleared) — every result
+ * produced since is invalid.  The Python layer calls it wherever it hands results to its caller. */
+int srb_poll_abort(srb_ctx* ctx);
 /* on != 0: every conv launch of this context carries cudaLaunchAttributeProgrammaticStreamSerialization, so its prologue
  * (barriers, TMEM, filters, bias) overlaps the tail of the previous launch in the stream (also as programmatic edges of a
  * captured CUDA graph).  The kernels wait for the previous launch before touching activations, but they read packed weights
  * and biases in the prologue: only enable this where those are not written by the immediately preceding launches of the
  * same stream.  srb_model_pt_forward / srb_resblock_fwd / srb_rowconv_fwd / srb_tail9_fwd always launch this way. */
 int srb_set_programmatic_launch(srb_ctx* ctx, int on);
-int srb_debug_trace(srb_ctx* ctx, void* dev_buf512_int64);  /* per-step clock stamps of CTA 0, diagnostics */
 int srb_profile_enable(srb_ctx* ctx, int on);
 int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
-/* measurement only: cycles for `iters` rounds of `racc` interleaved M=128(64) x n x 16 tcgen05.mma;
- * out2_host[0] = issue cycles, out2_host[1] = cycles until all MMAs completed */
-int srb_ubench_mma(srb_ctx* ctx, int n, int layout, int racc, int iters, int m64, int grid, long long* out2_host);
+/* (probe hooks — in-kernel bottleneck probes, clock traces, the tcgen05.mma micro-benchmark — are not part of this library:
+ * they exist only in the -DSRB_DEBUG build, libsrb200_dbg.so, declared in include/srb200_debug.h and loaded by tools/) */
 
 /* Fused residual block  y = x + convB(LeakyReLU(convA(x)))  — ResidualBlock1.forward (utils/models.py:208-209) with
  * m = Sequential(Conv(64,32,3,act=LeakyReLU), Conv(32,64,3,act=False)), BN already folded (model.pt state: net.1.residual.{i}.m.{0,1}).
@@ -235,18 +251,20 @@ int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off,
  * one zero-padded buffer each, length n a multiple of 4) — SURVEY §8(f) rank 1.
  * srb_grad_stats replaces the per-tensor loops of gradscaler.unscale_ (train.py:58: inf/nan check of g/scale) and of
  * clip_grad_norm_ (train.py:59: global 2-norm): stats[0] = sum (g/scale)^2, stats[1] = 1 if any g/scale is non-finite,
- * stats[2] += 1 when finite (the optimizer step number; zero it once).  scale_dev = GradScaler's device scalar or NULL.
+ * stats[2] is left alone (the number of optimizer steps taken: srb_adam_ema_step advances it; zero it once), so the
+ * statistics may be recomputed any number of times per step.  scale_dev = GradScaler's device scalar or NULL.
  * workspace: srb_optim_workspace_floats() floats, zeroed once.  Deterministic (fixed-order partial sums).
  * srb_adam_ema_step replaces gradscaler.step(Adam) (train.py:60; torch.optim.Adam arithmetic, no amsgrad; skipped on the
  * device when stats[1] != 0) and ema.update (train.py:63 -> utils/models.py:31-40: ema = d*ema + (1-d)*p, ema may be
  * NULL) in one pass; g is read as g / scale * min(1, max_norm / (sqrt(stats[0]) + 1e-6)) (max_norm <= 0: no clipping)
- * and never rewritten. */
+ * and never rewritten.  The step number of the update is stats[2] + 1; the kernel's last block stores it back (not when
+ * the step is skipped).  workspace: the same buffer srb_grad_stats uses (its arrival counter is shared). */
 int srb_optim_workspace_floats(void);
 int srb_grad_stats(srb_ctx* ctx, const float* grads, size_t n, const float* scale_dev, float* stats, float* workspace,
                    srb_stream_t stream);
 int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float* ema, size_t n,
-                      const float* scale_dev, const float* stats, float max_norm, float lr, float beta1, float beta2, float eps,
-                      float weight_decay, float ema_decay, srb_stream_t stream);
+                      const float* scale_dev, float* stats, float* workspace, float max_norm, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, float ema_decay, srb_stream_t stream);
 
 /* Batched gradients: every 3x3 weight gradient and every bias gradient of one backward pass as ONE launch each.
  * Weight gradients are off backpropagation's critical path, so the step defers them to its end; a unit

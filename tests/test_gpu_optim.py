@@ -211,3 +211,108 @@ def test_flat_adam_state_dict_interchanges_with_torch_adam(dev):
     for q, b in zip(back.param_groups[0]["params"], pr):
         assert _close(back.state[q]["exp_avg"], opt_r.state[b]["exp_avg"])
         assert float(back.state[q]["step"]) == 4.0
+
+
+def test_norm_queries_do_not_advance_the_step_counter(dev):
+    """the Adam step number advances once per optimizer step TAKEN (in the Adam pass), not whenever the gradient
+    statistics are computed — logging the norm before unscale_, after step(), or without a step leaves the bias correction
+    alone; a skipped (non-finite) step does not count."""
+    from image_super_resolution_b200.optim import FlatAdam, GradScaler, clip_grad_norm_
+    torch.manual_seed(3)
+    ours, ref = _Toy().to(dev), _Toy().to(dev)
+    ref.load_state_dict(ours.state_dict())
+    po, pr = list(ours.parameters()), list(ref.parameters())
+    opt_o = FlatAdam(po, lr=1e-2)
+    opt_r = torch.optim.Adam(pr, lr=1e-2)
+    for step in range(3):
+        gs = [torch.randn_like(p) for p in pr]
+        opt_o.zero_grad(); opt_r.zero_grad()
+        _set_flat_grads(po, gs)
+        for p, g in zip(pr, gs):
+            p.grad = g.clone()
+        for _ in range(3):                                   # extra norm queries (logging)
+            opt_o._stats_valid = False
+            opt_o.total_norm()
+        clip_grad_norm_(ours.parameters(), 10)
+        torch.nn.utils.clip_grad_norm_(ref.parameters(), 10)
+        opt_o.step(); opt_r.step()
+        opt_o._stats_valid = False
+        opt_o.total_norm()                                   # ... and one after the step
+        assert float(opt_o.stats[2].item()) == step + 1
+    for a, b in zip(po, pr):
+        assert _close(a, b)
+    # a non-finite gradient: the step is skipped on the device and not counted
+    gs = [torch.randn_like(p) for p in pr]
+    gs[1][0] = float("inf")
+    opt_o.zero_grad()
+    _set_flat_grads(po, gs)
+    before = [p.detach().clone() for p in po]
+    sc = GradScaler("cuda", init_scale=4.0)
+    sc.scale(torch.zeros((), device=dev, requires_grad=True).sum())
+    sc.unscale_(opt_o); sc.step(opt_o); sc.update()
+    assert float(opt_o.stats[2].item()) == 3
+    assert all(torch.equal(a, b) for a, b in zip(po, before))
+    # torch's state_dict format round-trips, including an optimizer that has not stepped yet (empty state)
+    fresh = FlatAdam(list(_Toy().to(dev).parameters()), lr=1e-2)
+    fresh.load_state_dict(torch.optim.Adam(list(_Toy().to(dev).parameters()), lr=1e-2).state_dict())
+    assert float(fresh.stats[2].item()) == 0 and float(fresh.m_arena.abs().sum().item()) == 0
+    for p in fresh.param_groups[0]["params"]:
+        assert fresh.state[p]["exp_avg"].data_ptr() >= fresh.m_arena.data_ptr()
+
+
+def test_eval_forward_after_fused_steps_uses_the_new_weights(dev):
+    """optim.FlatAdam updates the parameters (and the attached EMA arena) through raw pointers, which
+    autograd's version counters do not see — the inference plan's cache key includes training.PARAM_EPOCH, so an eval forward
+    after k more steps runs on the current weights, for the model and for the EMA copy."""
+    import copy
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200 import train as T
+    from image_super_resolution_b200.training import L1Loss
+    from oracle import nets_oracle as no
+    torch.manual_seed(100)
+    net = models.EResNet(1, 0.2, 2).to(dev)
+    hr, lr = no.make_lr_hr(11, 2, 32, 2)
+    hr, lr = hr.to(dev), lr.to(dev)
+    opt = T.FlatAdam(net.parameters(), lr=1e-3)
+    scaler = T.GradScaler("cuda")
+    ema = T.ModelEMA(net, tau=5)
+    ema.ema.to(dev)
+    ema.attach(opt)
+    loss_fn = L1Loss().to(dev)
+
+    def fresh_eval(m):
+        c = copy.deepcopy(m).eval()                  # a deep copy re-plans from the current parameter values
+        with torch.no_grad():
+            return c(lr)
+
+    for rnd in range(2):
+        T.train(net, ema, [(hr, lr)] * 3, loss_fn, opt, scaler, None, rnd, None)
+        net.eval()
+        with torch.no_grad():
+            y, ye = net(lr), ema.ema(lr)
+        assert torch.equal(y, fresh_eval(net)), f"round {rnd}: stale packed filters on the trained model"
+        assert torch.equal(ye, fresh_eval(ema.ema)), f"round {rnd}: stale packed filters on the EMA model"
+    assert not torch.equal(y, ye)
+
+
+def test_backward_with_retained_grads_is_refused(dev):
+    """the gradients are views of one arena that every backward rewrites; a second backward onto retained .grad
+    tensors would alias it (2 g instead of g1 + g2) — refused loudly; zero_grad(set_to_none=False) drops them as well."""
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200 import train as T
+    from image_super_resolution_b200.training import L1Loss
+    from oracle import nets_oracle as no
+    torch.manual_seed(100)
+    net = models.EResNet(1, 0.2, 2).to(dev).train()
+    hr, lr = no.make_lr_hr(12, 2, 32, 2)
+    hr, lr = hr.to(dev), lr.to(dev)
+    loss_fn = L1Loss().to(dev)
+    loss_fn(net(lr), hr).backward()
+    g1 = [p.grad.detach().clone() for p in net.parameters()]
+    with pytest.raises(RuntimeError, match="accumulated"):
+        loss_fn(net(lr), hr).backward()
+    opt = T.FlatAdam(net.parameters(), lr=1e-3)
+    opt.zero_grad(set_to_none=False)
+    assert all(p.grad is None for p in net.parameters())
+    loss_fn(net(lr), hr).backward()
+    assert all(torch.equal(p.grad, g) for p, g in zip(net.parameters(), g1))      # same step, same gradients: deterministic

@@ -298,11 +298,11 @@ def test_model_pt_rowfold_kernels_vs_tiled_kernels_and_oracle(model, dev, shape)
     g = torch.Generator().manual_seed(shape[2] + shape[3])
     x = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g)
     y = model(x.to(dev)).cpu()
-    model._ctx.debug_set(2, 8)
+    model._ctx.set_option(2, 8)
     try:
         t = model(x.to(dev)).cpu()
     finally:
-        model._ctx.debug_set(2, 0)
+        model._ctx.set_option(2, 0)
     d = (y.int() - t.int()).abs()
     assert d.max().item() <= 1 and (d == 0).float().mean().item() >= 0.97
     ref = mo.forward_u8(x)

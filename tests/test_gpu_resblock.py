@@ -37,13 +37,13 @@ def _case(dev, N, H, W, seed=0, grid=0):
     xc = ops.nchw_to_c8(x.to(dev), dtype="fp16")
     yc = torch.full_like(xc, float("nan"))
     if grid:
-        ctx.debug_set(1, grid)
+        ctx.set_option(1, grid)
     try:
         rb.forward(xc, yc, 0.2)
         torch.cuda.synchronize()
         ctx.check_device()
     finally:
-        ctx.debug_set(1, 0)
+        ctx.set_option(1, 0)
     out = ops.c8_to_nchw(yc, 64).cpu()
     err = (out - ref).abs().max().item()
     assert np.isfinite(err) and err <= 4e-3 * ref.abs().max().item() + 2e-3, err
@@ -103,13 +103,13 @@ def _rowconv_case(dev, N, H, W, seed=0, grid=0, res=True, lrelu=False):
     rcc = ops.nchw_to_c8(r.to(dev), dtype="fp16") if res else None
     yc = torch.full_like(xc, float("nan"))
     if grid:
-        ctx.debug_set(1, grid)
+        ctx.set_option(1, grid)
     try:
         rc.forward(xc, yc, rcc, slope=0.2, lrelu=lrelu)
         torch.cuda.synchronize()
         ctx.check_device()
     finally:
-        ctx.debug_set(1, 0)
+        ctx.set_option(1, 0)
     out = ops.c8_to_nchw(yc, 64).cpu()
     err = (out - ref).abs().max().item()
     assert np.isfinite(err) and err <= 4e-3 * ref.abs().max().item() + 2e-3, err
@@ -147,14 +147,14 @@ def _tail_case(dev, N, H, W, seed=0, grid=0):
     t = ops.Tail9(ctx, w, b, "fp16")
     xc = ops.nchw_to_c8(x.to(dev), dtype="fp16")
     if grid:
-        ctx.debug_set(1, grid)
+        ctx.set_option(1, grid)
     try:
         yf = t.forward(xc, tanh=False, u8=False, out=torch.full((N, 3, H, W), float("nan"), device=dev))
         yu = t.forward(xc, tanh=True, u8=True, out=torch.full((N, 3, H, W), 77, dtype=torch.uint8, device=dev))
         torch.cuda.synchronize()
         ctx.check_device()
     finally:
-        ctx.debug_set(1, 0)
+        ctx.set_option(1, 0)
     err = (yf.cpu() - pre).abs().max().item()
     assert np.isfinite(err) and err <= 2e-3 * pre.abs().max().item() + 1e-3, err
     want = torch.round((torch.tanh(pre) + 1) / 2 * 255).to(torch.int16)

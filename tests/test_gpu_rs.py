@@ -89,11 +89,11 @@ def test_hwc_bgr_store_equals_flip_permute_of_the_nchw_result(model, shape):
     got_s = [y.clone() for y in model.stream(iter([x, x]), depth=2, layout="hwc_bgr")]
     assert all(torch.equal(y, want) for y in got_s)
     ctx = Context.get(0)
-    ctx.debug_set(2, 16384)                   # the tiled 9x9 tail kernel (fallback path) stores the same bytes
+    ctx.set_option(2, 16384)                   # the tiled 9x9 tail kernel (fallback path) stores the same bytes
     try:
         got_t = model.forward(x.cuda(), layout="hwc_bgr").cpu()
     finally:
-        ctx.debug_set(2, 0)
+        ctx.set_option(2, 0)
     assert torch.equal(got_t, want)
     with pytest.raises(RuntimeError):
         model.forward(x, layout="hwc_bgr")    # host tensors go through stream()
@@ -121,3 +121,18 @@ def test_upscale_image_modes_agree_with_per_window_forwards(model, ndev):
     assert torch.equal(rs.upscale_image(m, img, 64, "halo"), whole)
     small = img[:, :40, :50].contiguous()                       # smaller than the window: one window = the image (rs.py:20-21)
     assert torch.equal(rs.upscale_image(m, small, 64, "reference"), model(small.unsqueeze(0).cuda())[0].cpu())
+
+
+def test_stream_results_stay_valid_for_depth_more_items(model):
+    """a yielded pinned tensor is valid until `depth` more items have been taken (ring of 2 * depth + 1 slots):
+    holding depth + 1 results without cloning is safe."""
+    g = torch.Generator().manual_seed(17)
+    batches = [torch.randint(0, 256, (2, 3, 24, 40), dtype=torch.uint8, generator=g) for _ in range(9)]
+    want = [model(b.cuda()).cpu() for b in batches]
+    depth = 2
+    held = []
+    for i, y in enumerate(model.stream(iter(batches), depth=depth)):
+        held.append((i, y))                                   # no clone
+        for j, t in held[-(depth + 1):]:
+            assert torch.equal(t, want[j]), (i, j)
+    assert len(held) == len(batches)

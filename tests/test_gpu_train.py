@@ -1,8 +1,9 @@
 """GPU parity of the training step: every backward kernel against fp32 autograd of the same op,
 then the whole EResNet forward + backward + L1 loss against fp32 autograd of the oracle restatement.
 
-Tolerances (bf16 operands, fp32 accumulate): loss rel-err <= 1e-2, per-tensor gradient cosine >= 0.999
-(>= 0.99 for the deepest nets' smallest bias tensors is NOT accepted: the bar is stated per test)."""
+Tolerances (bf16 operands, fp32 accumulate): loss rel-err <= 1e-2, per-tensor gradient cosine >= 0.999 vs
+fp32 autograd — asserted on every parameter tensor of every net below, including BASELINE configs[4]'s EResNet(16, 0.2, 2)
+at LR 64 x 64; the measured distribution is printed with the test."""
 import os
 import sys
 
@@ -201,9 +202,14 @@ def test_tanh_bwd_and_pixunshuffle_mask(dev):
     assert torch.equal(ops.c8_to_nchw(gs, 256).cpu(), _q(ref))
 
 
-@pytest.mark.parametrize("nb,scale,n,hw", [(1, 2, 2, 24), (2, 4, 1, 16)])
+COS_MIN = 0.999
+NORM_TOL = 2e-2          # |g| / |g_ref| - 1
+
+
+@pytest.mark.parametrize("nb,scale,n,hw", [(1, 2, 2, 24), (2, 4, 1, 16), (16, 2, 2, 64)])
 def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
-    """forward + L1 loss + backward of the drop-in EResNet vs fp32 autograd of the oracle restatement."""
+    """forward + L1 loss + backward of the drop-in EResNet vs fp32 autograd of the oracle restatement (CPU); the last case
+    is BASELINE configs[4]'s net and LR shape: EResNet(16, 0.2, 2), 64 x 64 (B = 2 keeps the CPU autograd to seconds)."""
     from image_super_resolution_b200 import models
     from image_super_resolution_b200.training import L1Loss
     from oracle import nets_oracle as no  # checker only
@@ -224,15 +230,18 @@ def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
     Context.get(0).check_device()
     assert (out.detach().cpu() - ref_out.detach()).abs().max().item() <= 2e-2
     assert abs(loss.item() - ref_loss.item()) <= 1e-2 * ref_loss.item()
-    worst = 1.0
+    rows = []
     for name, p in net.named_parameters():
         gref = sd[name].grad
         got = p.grad.detach().cpu() / 1024.0
-        c = _cos(got, gref)
-        worst = min(worst, c)
-        assert c >= 0.995, (name, c)
-        assert abs(float(got.norm()) / float(gref.norm()) - 1) <= 5e-2, (name, float(got.norm()), float(gref.norm()))
-    print("worst per-tensor gradient cosine:", worst)
+        rows.append((_cos(got, gref), abs(float(got.norm()) / float(gref.norm()) - 1), name))
+    cs = np.array([r[0] for r in rows])
+    ns = np.array([r[1] for r in rows])
+    print(f"EResNet({nb}) x{scale} {n}x{hw}x{hw}: {len(rows)} tensors; gradient cosine min {cs.min():.5f} / 1% {np.quantile(cs, 0.01):.5f} / "
+          f"median {np.median(cs):.5f}; |norm ratio - 1| max {ns.max():.4f}; worst: " +
+          ", ".join(f"{nm} {c:.5f}" for c, _, nm in sorted(rows)[:4]))
+    bad = [(nm, round(c, 5), round(d, 4)) for c, d, nm in rows if c < COS_MIN or d > NORM_TOL]
+    assert not bad, bad[:10]
 
 
 def test_reference_train_loop_runs_on_dropin(dev):

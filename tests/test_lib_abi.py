@@ -41,6 +41,13 @@ def test_binding_covers_header(built_lib):
     built_lib.lib()  # resolves all
 
 
+def test_product_library_carries_no_probe_hooks(built_lib):
+    """The bottleneck probes / clock traces / micro-benchmarks live in the -DSRB_DEBUG build only (include/srb200_debug.h)."""
+    l = ctypes.CDLL(built_lib.LIB_PATH)
+    for s in built_lib.DEBUG_SIGNATURES:
+        assert not hasattr(l, s), f"libsrb200.so exports the probe hook {s}"
+
+
 def test_errors_are_reported_not_crashed(built_lib):
     import torch
     l = built_lib.lib()

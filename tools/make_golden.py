@@ -114,6 +114,33 @@ def golden_rs_tiling(m):
     print("rs_tiling_golden.npz: seam max diff vs whole", int(diff.max()), "frac!=0", float((diff > 0).float().mean()))
 
 
+@torch.no_grad()
+def golden_rs_config1(m):
+    """BASELINE configs[0]: rs.py:82-111 on one 256 x 256 RGB image, window 96 (9 windows of 96 / 96 / 64 per axis, batch 1),
+    executed with the reference's own sliding_window and stitching loop on the reference's model.pt (CPU fp32)."""
+    import rs as ref_rs
+    g = torch.Generator().manual_seed(SEED)
+    image = torch.randint(0, 256, (3, 256, 256), dtype=torch.uint8, generator=g)
+    result_image = None
+    high = width = 0
+    for step_size, _, _, win in ref_rs.sliding_window(image, 96):
+        w = m(win.unsqueeze(0).clone())
+        if result_image is None:
+            result_image = torch.zeros_like(image)
+            _, image_high, image_width = result_image.size()
+        for frame in w:
+            c, h, ww = frame.size()
+            result_image[..., high:high + h, width:width + ww] = frame
+            width += ww
+            if width >= image_width:
+                high += h
+                width = 0
+    whole = m(image.unsqueeze(0).clone())[0]
+    np.savez_compressed(os.path.join(OUT, "rs_config1_golden.npz"), image=image.numpy(), rs_window96=result_image.numpy(),
+                        whole=whole.numpy())
+    print("rs_config1_golden.npz: 256x256, window 96; seam max diff vs whole", int((result_image.int() - whole.int()).abs().max()))
+
+
 def golden_l1():
     from utils.loss import L1Loss
     g = torch.Generator().manual_seed(SEED + 2)
@@ -168,11 +195,32 @@ def golden_nets():
     np.savez_compressed(os.path.join(OUT, "nets_golden.npz"), **out)
 
 
+@torch.no_grad()
+def golden_eresnet16():
+    """BASELINE configs[4]'s net: the reference EResNet(16, 0.2, 2) (utils/models.py:621-650; 244 convs) forward on a seeded
+    [2,3,64,64] LR batch.  Weights are re-created by the drop-in from the same seed; only checksums travel."""
+    from utils.models import EResNet
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    from oracle.nets_oracle import make_lr_hr
+    torch.manual_seed(SEED)
+    net = EResNet(16, 0.2, 2).eval()
+    _, lr = make_lr_hr(SEED + 5, 2, 128, 2)
+    y = net(lr.clone())
+    sd = net.state_dict()
+    out = {"lr": lr.numpy(), "out": y.numpy(), "keys": np.array(list(sd.keys())),
+           "sums": np.array([float(v.double().sum()) for v in sd.values()])}
+    np.savez_compressed(os.path.join(OUT, "eresnet16_golden.npz"), **out)
+    print("eresnet16_golden.npz: params", sum(p.numel() for p in net.parameters()), "out", tuple(y.shape), "mean|y|", float(y.abs().mean()),
+          "max|y|", float(y.abs().max()))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 1)
     install_stubs()
     os.makedirs(OUT, exist_ok=True)
     m = golden_model_pt()
     golden_rs_tiling(m)
+    golden_rs_config1(m)
     golden_l1()
     golden_nets()
+    golden_eresnet16()
