@@ -303,7 +303,7 @@ def bench_train(dev, rank, world, steps, warmup=3):
     flop = 289.0e9 * B          # fwd + bwd algorithmic FLOP per sample
     pk = peaks()
     return {"metric": "train.py step samples/s", "value": world * B / ms * 1e3, "unit": "samples/s", "ms_per_step": ms,
-            "steps": steps, "model": "EResNet(16,0.2,2)", "per_gpu_batch": B, "hr_crop": 128, "operands": "bf16 in, fp32 accumulate",
+            "steps": steps, "model": "EResNet(16,0.2,2)", "per_gpu_batch": B, "hr_crop": 128, "operands": "fp16 in + GradScaler loss scaling (the reference's autocast precision), fp32 accumulate",
             "loop": "drop-in train(): autocast fwd, L1, GradScaler backward, unscale, clip(10), Adam, LinearLR, EMA, per-step "
                     "loss.item() + add_scalar (train.py:64-65); fused tail (FlatAdam + GradScaler + clip + EMA: 2 launches)",
             "ms_per_step_torch_tail": ms_torch, "samples_s_torch_tail": world * B / ms_torch * 1e3,

@@ -39,9 +39,26 @@ struct ResblockParams {
     int dbg_skip;             // bottleneck probes: 1 = no TMA loads, 2 = no MMAs (16 = no convA, 32 = no convB MMAs), 4 = no global I/O in the output epilogue
 };
 
+// RB_KSPLIT: convA is issued by TWO warps, each owning half of the input channels (K) and its own hidden accumulator ring;
+// the hidden epilogue adds the two partial sums.  Why (profiles/ubench_mix_r2.log): a chain of N = 96 MMAs into one
+// accumulator runs at 73 clk per MMA (48 clk of math) whatever the number of accumulators one thread alternates between,
+// while two issuers with a chain each reach 67 clk — and in the kernel the issuing thread's per-row bookkeeping is exposed
+// because the tensor pipe's queue is only a few MMAs deep: with two issuers the pipe stays fed while either thread waits.
+// The two rings double the hidden TMEM columns, so all rings are 4 rows deep (2*4*32 + 4*64 = 512 columns).
+// Measured: fused block 89.1 -> 83.1 us per launch in the bench, forward 1180 -> 1210 Mpix/s.
+#ifndef RB_KSPLIT
+#define RB_KSPLIT 1
+#endif
 #ifndef RB_RH
+#if RB_KSPLIT
+#define RB_RH 4
+#define RB_RY 4
+#else
 #define RB_RH 6
 #define RB_RY 5
+#endif
+#endif
+#ifndef RB_HSLOTS
 #define RB_HSLOTS 3
 #define RB_XSTAGES 4
 #endif
@@ -70,12 +87,15 @@ struct RBGeom {
     static constexpr int WA_STEP = 2 * 3 * CH * 16, WB_STEP = 2 * 3 * CB * 16;   // 3072, 6144
     static constexpr int WA_BYTES = KA * WA_STEP, WB_BYTES = KB * WB_STEP;       // 36864 each
     static constexpr int RH = RB_RH, RY = RB_RY;                        // TMEM accumulator rings
-    static constexpr int TM_H = 0, TM_Y = RH * CH;              // column bases: 0, 192 (+ 5*64 = 512)
+    static constexpr int KSPLIT = RB_KSPLIT ? 2 : 1;                   // convA issuers = partial hidden accumulator rings
+    static constexpr int TM_H = 0, TM_H1 = RH * CH, TM_Y = KSPLIT * RH * CH;   // column bases
     static constexpr int OFF_WA = 0, OFF_WB = WA_BYTES, OFF_X = OFF_WB + WB_BYTES, OFF_H = OFF_X + XSTAGES * XROW;
     static constexpr int OFF_BIAS = OFF_H + HSLOTS * HROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
     static constexpr int THREADS = 640;            // 4 control warps (one spare) + 8 hidden-epilogue + 8 output-epilogue warps
-    static_assert(RH * CH + RY * CB == 512, "the two accumulator rings fill TMEM");
+    static_assert(KSPLIT * RH * CH + RY * CB == 512, "the accumulator rings fill TMEM");
+    static_assert(KSPLIT == 1 || RB_BIAS_MODE == 1, "the K-split hidden rings are armed with zero");
+    static_assert(RH >= 4 && RY >= 4, "a ring holds three accumulating rows and one draining");
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
     static_assert(XSTAGES <= 8 && RH <= 8 && HSLOTS <= 4 && RY <= 8, "barrier array layout");
 };
@@ -251,8 +271,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         reinterpret_cast<uint4*>(s_h)[i] = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < G::CH + G::CB; i += G::THREADS) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
-        for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
-        for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], 1); mbar_init(&haempty[i], 4); }
+        for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], G::KSPLIT); }
+        for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], G::KSPLIT); mbar_init(&haempty[i], 4); }
         for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4); mbar_init(&hsempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
         mbar_init(wbar, 1);
@@ -319,8 +339,11 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 20);         // x row requested
             }
         }
-    } else if (warp == 1) {
-        // ===================== convA MMA issuer: one x row per step, N = 3 x 32 into the hidden accumulator ring =====================
+    } else if (warp == 1 || (G::KSPLIT == 2 && warp == 3)) {
+        // ===================== convA MMA issuer(s): one x row per step, N = 3 x 32 into the hidden accumulator ring =====================
+        // K split: warp 1 owns input channels 0..31 (K-steps c2 = 0, 1 of every dx) and ring H0, warp 3 channels 32..63 and H1
+        const int kh = warp == 3 ? 1 : 0;
+        const uint32_t tm_ring_a = tmem_base + (kh ? G::TM_H1 : G::TM_H);
         // (convA and convB are issued by two different warps: a single thread cannot prepare 18 MMAs + 5 commits per row
         // fast enough, and the tensor pipe interleaves the two warps' independent accumulation chains by itself)
         const uint64_t adescA0 = umma_desc_nosw(0, 160, G::XBOX);           // x row: planes 160 B apart, groups XBOX apart
@@ -336,7 +359,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 mbar_wait<RB_CTRL>(&xfull[xst], xph, 33);
-                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 21);         // x row arrived
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && kh == 0) rb_trace(p, xc, 21);         // x row arrived
                 const int lo = r - 1 > sg.hlo ? r - 1 : sg.hlo, hi = r + 1 < sg.hhi ? r + 1 : sg.hhi;
                 const int a_lo = hbase + lo - sg.hlo, a_n = hi - lo + 1, a_s0 = lo - (r - 1);
                 for (; h_acq < a_lo + a_n; ++h_acq) {
@@ -345,15 +368,25 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 }
                 const int slot_lo = (hslot0 + (lo - sg.hlo)) % G::RH;
                 tc_fence_after();
-                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && kh == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
                 if (elect_one()) {
                     const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
-                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tmem_base + G::TM_H, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
+                    const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tm_ring_a, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
                     if (!SRB_DBG(p.dbg_skip & (2 | 16))) {
+                        if constexpr (G::KSPLIT == 2) {
 #pragma unroll
-                        for (int kk = 0; kk < G::KA; ++kk) {
-                            const int dx = kk >> 2, c2 = kk & 3;
-                            rb_issue(q, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), bdescA0 + (uint64_t)((kk * G::WA_STEP) >> 4));
+                            for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                                for (int cc = 0; cc < 2; ++cc) {
+                                    const int c2 = 2 * kh + cc, kk = dx * 4 + c2;
+                                    rb_issue(q, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), bdescA0 + (uint64_t)((kk * G::WA_STEP) >> 4));
+                                }
+                        } else {
+#pragma unroll
+                            for (int kk = 0; kk < G::KA; ++kk) {
+                                const int dx = kk >> 2, c2 = kk & 3;
+                                rb_issue(q, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), bdescA0 + (uint64_t)((kk * G::WA_STEP) >> 4));
+                            }
                         }
                     }
                     umma_commit(&xempty[xst]);
@@ -362,7 +395,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     if (r == sg.xhi && r <= sg.hhi) umma_commit(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
                 }
                 __syncwarp();
-                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
+                if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && kh == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
                 if (++xst == G::XSTAGES) { xst = 0; xph ^= 1; }
             }
             const int nh = sg.hhi - sg.hlo + 1;
@@ -449,7 +482,14 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tc_fence_after();
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::CH, rr);
-                tmem_ld_wait();
+                if constexpr (G::KSPLIT == 2) {             // second partial sum (input channels 32..63)
+                    uint32_t r1[32];
+                    tmem_ld32(t_lane + G::TM_H1 + slot * G::CH, r1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) rr[k] = __float_as_uint(__uint_as_float(rr[k]) + __uint_as_float(r1[k]));
+                    if (!SRB_DBG(p.dbg_skip & 64)) tmem_zero32(t_lane + G::TM_H1 + slot * G::CH);
+                } else tmem_ld_wait();
                 if (RB_BIAS_MODE == 1) {
                     if (!SRB_DBG(p.dbg_skip & 64)) tmem_zero32(t_lane + slot * G::CH);
                 } else if (!SRB_DBG(p.dbg_skip & 64)) {    // re-arm the accumulator row with the bias

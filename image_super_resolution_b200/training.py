@@ -4,7 +4,11 @@ forward, loss, GradScaler backward, clip, Adam, EMA) runs unmodified on the drop
 
 Schedule, all launches through the C ABI:
   forward   the inference schedule of models._NetPlan, but every RDB owns its 192-channel dense buffer (saved for
-            backward; torch.cat stays free) and the operands are bf16 re-packed on the device from the fp32 masters;
+            backward; torch.cat stays free) and the operands are 16-bit re-packed on the device from the fp32 masters.
+            Operand type: fp16 — the reference's own training precision (train.py:54 autocast + GradScaler).
+            Measured on EResNet(16) (tools/gpu_train_parity.py): with GradScaler's loss scale (65536) every one of the
+            488 gradient tensors has cosine >= 0.9991 vs fp32 autograd; bf16 operands reach only 0.9958 (242 tensors
+            below the 0.999 contract), fp16 WITHOUT loss scaling underflows.  `net.train_operand_dtype = "bf16"` selects bf16;
   backward  per conv: weight gradient (tcgen05, srb_conv2d_wgrad; FP32-pipe srb_conv9_wgrad for the 9x9 head/tail),
             bias gradient, and the data gradient as a conv of dY with the transposed / rotated filter that
             ACCUMULATES in place into the dense block's gradient buffer and applies the LeakyReLU mask of the slice
@@ -44,7 +48,7 @@ def _slope_of(act) -> float:
 class TrainPlan:
     """Device-packed operands, saved activations and the fwd/bwd launch schedule of one EResNet on one device."""
 
-    def __init__(self, net, device: torch.device, dtype="bf16", allreduce: bool = True):
+    def __init__(self, net, device: torch.device, dtype="fp16", allreduce: bool = True):
         for m in net.modules():
             if isinstance(m, nn.BatchNorm2d):
                 raise NotImplementedError("train-mode BatchNorm (ResNet) is not on the sm_100a path (SURVEY §8(f) rank 3); "
@@ -82,6 +86,12 @@ class TrainPlan:
         self.use_graphs = True
         self.use_pdl = True          # programmatic edges between the conv nodes of the captured graphs
         self.wgrad_splitk = 1
+        # Internal gradient shift: the data-gradient chain runs on 16-bit tensors whose magnitudes span the tail conv (~1 with
+        # GradScaler's 65536) down to the dense blocks of a x4 net at initialisation (~4e-5: fp16 subnormals).  The chain is
+        # linear, so the upstream gradient is multiplied by 2^8 where it enters (tanh backward) and every weight / bias
+        # gradient by 2^-8 where it leaves (exact: powers of two).  An overflow shows up as inf in the fp32 gradients, which
+        # GradScaler answers by skipping the step and halving its scale, exactly as for its own scale.
+        self.grad_shift = 256.0
         self.graphs = {}
         self.pack_batch, self.pack_ptrs = None, None
         self.grad_batch, self.grad_key, self._gjobs = None, None, None
@@ -126,7 +136,7 @@ class TrainPlan:
         return jobs
 
     def repack(self, ptrs=None, track_versions=True):
-        """fp32 master weights (device) -> bf16 UMMA operands, forward and data-gradient layouts: one launch."""
+        """fp32 master weights (device) -> 16-bit UMMA operands, forward and data-gradient layouts: one launch."""
         if ptrs is None:
             ptrs = tuple(p.data_ptr() for p in self.params)
         if self.pack_batch is None or self.pack_ptrs != ptrs:
@@ -265,7 +275,7 @@ class TrainPlan:
         if self._gjobs is not None:
             self._gjobs.append(dict(x=x, x_planes=x_planes, x_off=x_off, cin=cin, dy=dy, dy_planes=dy_planes, dy_off=dy_off,
                                     cout=cout, dw=self.grad_views[id(m.conv.weight)], db=self.grad_views[id(m.conv.bias)],
-                                    scale=scale, N=N, H=H, W=W))
+                                    scale=scale / float(self.grad_shift), N=N, H=H, W=W))
 
     def _backward_impl(self, gout: torch.Tensor) -> list[torch.Tensor]:
         sv, n = self.saved, self.net
@@ -281,11 +291,13 @@ class TrainPlan:
         # ---- tail conv: tanh', 9x9 weight gradient, data gradient = 9x9 conv 3 -> 64 (head kernel, transposed filter)
         if not sv["tanh"]:
             raise NotImplementedError("tail conv without tanh")
-        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt, g8=self._b("g2", N, 1, h2, w2))
+        sh, ish = float(self.grad_shift), 1.0 / float(self.grad_shift)
+        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt, scale=sh, g8=self._b("g2", N, 1, h2, w2))
         up_last = sv["ups"][-1][1] if sv["ups"] else sv["t"]
-        ops.conv9_wgrad(up_last, 8, 0, 64, g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.weight)], N, h2, w2)
+        ops.conv9_wgrad(up_last, 8, 0, 64, g2, 1, 0, 3, self.grad_views[id(n.conv2.conv.weight)], N, h2, w2, scale=ish)
         if self._gjobs is not None:
-            self._gjobs.append(dict(dy=g2, dy_planes=1, dy_off=0, cout=3, db=self.grad_views[id(n.conv2.conv.bias)], N=N, H=h2, W=w2))
+            self._gjobs.append(dict(dy=g2, dy_planes=1, dy_off=0, cout=3, db=self.grad_views[id(n.conv2.conv.bias)], N=N, H=h2, W=w2,
+                                    scale=ish))
         g_cur = self._b("g_up_last", N, 8, h2, w2)
         cv(self.d_conv2, g2, 1, 0, g_cur, 8, 0, N, h2, w2)
         # ---- scalers, last to first: LeakyReLU' + PixelShuffle inverse, wgrad 64 -> 256, dgrad 256 -> 64
@@ -330,9 +342,10 @@ class TrainPlan:
         # ---- head conv: total gradient of x0 = trunk path + long skip, LeakyReLU', 9x9 weight gradient
         gx0 = self._b("gx0", N, 8, H, W)
         ops.c8_axpby_mask(gxf, 8, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
-        ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.weight)], N, H, W)
+        ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, self.grad_views[id(n.conv0.conv.weight)], N, H, W, scale=ish)
         if self._gjobs is not None:
-            self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=self.grad_views[id(n.conv0.conv.bias)], N=N, H=H, W=W))
+            self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=self.grad_views[id(n.conv0.conv.bias)], N=N, H=H, W=W,
+                                    scale=ish))
             self.grad_batch, self.grad_key, self._gjobs = ops.GradBatch(self.ctx, self._gjobs, self.dt), gkey, None
         self.grad_batch.run(self.device, self.wgrad_splitk)
         return [self.grad_views[id(p)] for p in self.params]
@@ -370,7 +383,7 @@ def train_forward(net, x: torch.Tensor) -> torch.Tensor:
     plans = net.__dict__.setdefault("_train_plans", {})
     plan = plans.get(x.device)
     if plan is None:           # (also after deepcopy(model): see TrainPlan.__deepcopy__)
-        plan = plans[x.device] = TrainPlan(net, x.device, getattr(net, "train_operand_dtype", "bf16"))
+        plan = plans[x.device] = TrainPlan(net, x.device, getattr(net, "train_operand_dtype", "fp16"))
     return _NetFunction.apply(x.float().contiguous(), plan, *plan.params)
 
 

@@ -315,4 +315,15 @@ def test_backward_with_retained_grads_is_refused(dev):
     opt.zero_grad(set_to_none=False)
     assert all(p.grad is None for p in net.parameters())
     loss_fn(net(lr), hr).backward()
-    assert all(torch.equal(p.grad, g) for p, g in zip(net.parameters(), g1))      # same step, same gradients: deterministic
+    # Same step, same gradients.  Bit-reproducible: every data gradient and every 3x3 weight / bias gradient (one CTA owns a
+    # unit, fixed summation order).  NOT bit-reproducible: the 9x9 head / tail weight gradients and their bias gradients, whose
+    # pixel tiles are split over CTAs that finish with fp32 red.global.add in arrival order (include/srb200.h: srb_conv9_wgrad)
+    # — equal up to fp32 rounding of a different summation order.
+    atomics = {"conv0.conv.weight", "conv0.conv.bias", "conv2.conv.weight", "conv2.conv.bias"}
+    diffs = []
+    for (name, p), g in zip(net.named_parameters(), g1):
+        if name in atomics:
+            assert (p.grad - g).abs().max().item() <= 1e-5 * g.abs().max().item() + 1e-9, name
+        elif not torch.equal(p.grad, g):
+            diffs.append((name, float((p.grad - g).abs().max()), float(g.abs().max())))
+    assert not diffs, diffs[:8]

@@ -1,7 +1,7 @@
 """GPU parity of the training step: every backward kernel against fp32 autograd of the same op,
 then the whole EResNet forward + backward + L1 loss against fp32 autograd of the oracle restatement.
 
-Tolerances (bf16 operands, fp32 accumulate): loss rel-err <= 1e-2, per-tensor gradient cosine >= 0.999 vs
+Tolerances (fp16 operands + loss scaling — the reference's own training precision — fp32 accumulate): loss rel-err <= 1e-2, per-tensor gradient cosine >= 0.999 vs
 fp32 autograd — asserted on every parameter tensor of every net below, including BASELINE configs[4]'s EResNet(16, 0.2, 2)
 at LR 64 x 64; the measured distribution is printed with the test."""
 import os
@@ -203,10 +203,11 @@ def test_tanh_bwd_and_pixunshuffle_mask(dev):
 
 
 COS_MIN = 0.999
+SCALE = 65536.0          # fp16 operands need the loss scaling the reference trains with (train.py:57, GradScaler)
 NORM_TOL = 2e-2          # |g| / |g_ref| - 1
 
 
-@pytest.mark.parametrize("nb,scale,n,hw", [(1, 2, 2, 24), (2, 4, 1, 16), (16, 2, 2, 64)])
+@pytest.mark.parametrize("nb,scale,n,hw", [(1, 2, 2, 24), (2, 4, 2, 24), (16, 2, 2, 64)])
 def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
     """forward + L1 loss + backward of the drop-in EResNet vs fp32 autograd of the oracle restatement (CPU); the last case
     is BASELINE configs[4]'s net and LR shape: EResNet(16, 0.2, 2), 64 x 64 (B = 2 keeps the CPU autograd to seconds)."""
@@ -224,7 +225,7 @@ def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
     loss_fn = L1Loss().to(dev)
     out = net(lr.to(dev))
     loss = loss_fn(out, hr.to(dev))
-    (loss * 1024.0).backward()             # GradScaler-style scaled backward
+    (loss * SCALE).backward()              # GradScaler-style scaled backward (torch.amp.GradScaler init_scale = 65536)
     torch.cuda.synchronize()
     from image_super_resolution_b200._lib import Context
     Context.get(0).check_device()
@@ -233,7 +234,7 @@ def test_eresnet_training_step_matches_fp32_autograd(dev, nb, scale, n, hw):
     rows = []
     for name, p in net.named_parameters():
         gref = sd[name].grad
-        got = p.grad.detach().cpu() / 1024.0
+        got = p.grad.detach().cpu() / SCALE
         rows.append((_cos(got, gref), abs(float(got.norm()) / float(gref.norm()) - 1), name))
     cs = np.array([r[0] for r in rows])
     ns = np.array([r[1] for r in rows])

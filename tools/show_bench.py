@@ -7,3 +7,7 @@ for k, v in d.get("roofline", {}).get("kernels", {}).items():
     print(f"  {k:22s} x{v['launches']}  {v['ms_per_launch']*1e3:7.1f} us  {v['tflops']:7.1f} TF  share {v['share']:.3f}")
 if "cpu_baseline" in d:
     print("  cpu_baseline", d["cpu_baseline"])
+for k in ("sustained", "gpu_reference", "train_step"):
+    if k in d:
+        print(f"  {k}: " + json.dumps(d[k])[:900])
+print("  roofline frac", d.get("roofline", {}).get("frac"))
