@@ -78,6 +78,7 @@ SIGNATURES = {
     "srb_adam_ema_step": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _f, _f, _f, _f, _f, _f, _f, _vp]),
     "srb_l1_partials_len": (_i, []),
     "srb_l1_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
+    "srb_l1_loss_fwd_noalloc": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
     "srb_l1_loss_bwd_dev": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp, _vp]),
 }

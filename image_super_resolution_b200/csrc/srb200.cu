@@ -1703,3 +1703,99 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     else CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<false>, m->tm, p));
     return SRB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free L1 loss (srb_l1_loss_fwd_noalloc).  No counterpart in the reference: added
+// for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// srb_l1_loss_fwd takes its reduction scratch (`partials`) from the caller; this variant keeps it in a file-scope device
+// array, so the caller passes only inputs and outputs and the call performs no cudaMalloc / cudaFree / allocating routine.
+//   * every GPU that loads the library holds the array (16.6 KB) until exit;
+//   * one partial sum per 16 384-element chunk (one CTA each, summed in index order by the last CTA to finish:
+//     deterministic) => at most SRB_L1_NOALLOC_MAX_ELEMS = 4096 x 16384 elements per call, larger inputs are refused;
+//   * ALL calls on a device share the array, which keeps the last call's contents: the arrival counter is cleared on the
+//     stream before every launch and the partials are fully rewritten, but two calls that overlap on the GPU (different
+//     streams) race — serialise them.
+// In host code `g_srb_noalloc_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, taken once per device with that device current.
+// ------------------------------------------------------------------------------------------
+constexpr int L1NA_MAX_PARTIALS = 4096;
+constexpr int L1NA_CHUNK = 16384;                       // elements per CTA: 256 threads x 16 float4
+static_assert((size_t)L1NA_MAX_PARTIALS * L1NA_CHUNK == SRB_L1_NOALLOC_MAX_ELEMS, "header constant");
+static __device__ __align__(256) float g_srb_noalloc_scratch[L1NA_MAX_PARTIALS + 64];   // [0, 4096) partials, [4096] arrival counter
+
+template <int DT>
+__global__ void __launch_bounds__(256) l1_fwd_noalloc_kernel(const void* __restrict__ pred, const float* __restrict__ tgt, size_t n,
+                                                             float scale /* w / n */, float* __restrict__ loss, float* __restrict__ scratch) {
+    const size_t lo = (size_t)blockIdx.x * L1NA_CHUNK;
+    const size_t hi = lo + L1NA_CHUNK < n ? lo + L1NA_CHUNK : n;
+    float acc = 0.f;
+    const bool vec = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(tgt)) & 15) == 0;
+    size_t i0 = lo;
+    if (vec) {                                          // whole float4 groups of the chunk (lo is a multiple of 4)
+        const size_t g_end = lo / 4 + (hi - lo) / 4;
+        for (size_t g = lo / 4 + threadIdx.x; g < g_end; g += 256) {
+            const float4 t = reinterpret_cast<const float4*>(tgt)[g];
+            acc += fabsf(ldp<DT>(pred, 4 * g) - t.x) + fabsf(ldp<DT>(pred, 4 * g + 1) - t.y) + fabsf(ldp<DT>(pred, 4 * g + 2) - t.z) +
+                   fabsf(ldp<DT>(pred, 4 * g + 3) - t.w);
+        }
+        i0 = g_end * 4;
+    }
+    for (size_t i = i0 + threadIdx.x; i < hi; i += 256) acc += fabsf(ldp<DT>(pred, i) - tgt[i]);
+    __shared__ float s_part[8];
+    __shared__ bool s_last;
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch + L1NA_MAX_PARTIALS);
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < 8 ? s_part[threadIdx.x] : 0.f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) {
+            scratch[blockIdx.x] = v;
+            __threadfence();
+            s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+        }
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double tot = 0.0;
+        for (unsigned int b = threadIdx.x; b < gridDim.x; b += 32) tot += (double)reinterpret_cast<volatile float*>(scratch)[b];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        if (threadIdx.x == 0) { *loss = (float)(tot * (double)scale); *counter = 0u; }
+    }
+}
+
+static float* s_noalloc_scratch_dev[64] = {};           // device address of g_srb_noalloc_scratch, per device
+
+extern "C" int srb_l1_loss_fwd_noalloc(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                                       float* loss_out, srb_stream_t stream) {
+    if (!ctx || !pred || !tgt || !loss_out) return fail(SRB_EINVAL, "srb_l1_loss_fwd_noalloc: NULL argument");
+    if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_fwd_noalloc: empty input (mean of nothing)");
+    if (n > (size_t)SRB_L1_NOALLOC_MAX_ELEMS)
+        return fail(SRB_EINVAL, "srb_l1_loss_fwd_noalloc: %zu elements exceed the built-in scratch (at most %zu = %d partial sums x %d "
+                    "elements); use srb_l1_loss_fwd with caller-provided partials", n, (size_t)SRB_L1_NOALLOC_MAX_ELEMS, L1NA_MAX_PARTIALS, L1NA_CHUNK);
+    if (pred_dtype < 0 || pred_dtype > 2) return fail(SRB_EINVAL, "srb_l1_loss_fwd_noalloc: pred_dtype %d", pred_dtype);
+    if (ctx->device < 0 || ctx->device >= 64) return fail(SRB_ENOSUP, "srb_l1_loss_fwd_noalloc: device index %d", ctx->device);
+    DeviceGuard dev_guard(ctx->device);
+    float* scratch = s_noalloc_scratch_dev[ctx->device];
+    if (!scratch) {                                     // set-up, once per device, with that device current
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_srb_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(SRB_ECUDA, "srb_l1_loss_fwd_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        scratch = s_noalloc_scratch_dev[ctx->device] = static_cast<float*>(p);
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the previous call's contents: the arrival counter must start at zero (an aborted launch could leave it set)
+    CUDA_TRY(cudaMemsetAsync(scratch + L1NA_MAX_PARTIALS, 0, 64 * sizeof(float), st));
+    const int grid = (int)((n + L1NA_CHUNK - 1) / L1NA_CHUNK);
+    const float scale = (float)((double)w / (double)n);
+    switch (pred_dtype) {
+        case 0: l1_fwd_noalloc_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, scratch); break;
+        case 1: l1_fwd_noalloc_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, scratch); break;
+        default: l1_fwd_noalloc_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, scratch); break;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}

@@ -306,6 +306,18 @@ int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float*
 int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
                     float grad_scale, void* dpred, srb_stream_t stream);
 
+/* Allocation-free variant of srb_l1_loss_fwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The reduction scratch that srb_l1_loss_fwd takes from the caller (`partials`) lives in a file-scope
+ * `static __device__ __align__(256)` array of the library (16.6 KB, held by every GPU that loads the library until exit);
+ * the call performs no cudaMalloc / cudaFree / allocating routine.  Limit: n <= SRB_L1_NOALLOC_MAX_ELEMS (4096 partial sums
+ * x 16 384 elements each) — larger inputs return SRB_EINVAL.  All calls on a device share that array: calls that overlap
+ * on the GPU (different streams) race; calls on one stream are safe (the arrival counter is cleared on the stream before
+ * every launch, the partial sums are rewritten).  Same value as srb_l1_loss_fwd up to the summation order (rel 1e-6). */
+#define SRB_L1_NOALLOC_MAX_ELEMS 67108864
+int srb_l1_loss_fwd_noalloc(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                            float* loss_out, srb_stream_t stream);
+
 /* same, times a device scalar *grad_out_dev (the upstream gradient of the loss, e.g. GradScaler's scale: train.py:57) */
 int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
                         float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream);
