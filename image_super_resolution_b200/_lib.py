@@ -39,6 +39,7 @@ SIGNATURES = {
     "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_frames": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i]),
+    "srb_copy_rect_u8": (_i, [_vp, _vp, _sz, _sz, _vp, _sz, _sz, _i, _sz, _sz, _i, _vp]),
     "srb_model_pt_launches": (_i, [_i, _i]),
     "srb_check_device": (_i, [_vp]),
     "srb_poll_abort": (_i, [_vp]),

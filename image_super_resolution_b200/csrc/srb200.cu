@@ -1799,3 +1799,27 @@ extern "C" int srb_l1_loss_fwd_noalloc(srb_ctx* ctx, const void* pred, int pred_
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Rectangle copies between a host image and a device tile (rs.py:92 `window_img.to(device)`, :107 `frame.cpu()`): `planes`
+// 2-D copies of width x height bytes, one cudaMemcpy2DAsync per plane, enqueued on the caller's stream.  With pinned host
+// memory the tile (+ halo) goes straight from the image to the device and the interior of the result straight into the stitched
+// host image — no host-side crop / paste copies and no whole-image transfers (single-image sharding).
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_t dst_plane, const void* src, size_t src_pitch,
+                                size_t src_plane, int planes, size_t width, size_t height, int kind, srb_stream_t stream) {
+    if (!ctx || !dst || !src) return fail(SRB_EINVAL, "srb_copy_rect_u8: NULL argument");
+    if (planes <= 0 || width == 0 || height == 0) return fail(SRB_EINVAL, "srb_copy_rect_u8: empty rectangle");
+    if (width > dst_pitch || width > src_pitch) return fail(SRB_EINVAL, "srb_copy_rect_u8: width %zu exceeds a pitch (%zu, %zu)", width, dst_pitch, src_pitch);
+    cudaMemcpyKind k;
+    if (kind == SRB_COPY_H2D) k = cudaMemcpyHostToDevice;
+    else if (kind == SRB_COPY_D2H) k = cudaMemcpyDeviceToHost;
+    else if (kind == SRB_COPY_D2D) k = cudaMemcpyDeviceToDevice;
+    else return fail(SRB_EINVAL, "srb_copy_rect_u8: kind %d", kind);
+    DeviceGuard dev_guard(ctx->device);
+    for (int p = 0; p < planes; ++p)
+        CUDA_TRY(cudaMemcpy2DAsync(static_cast<uint8_t*>(dst) + (size_t)p * dst_plane, dst_pitch,
+                                   static_cast<const uint8_t*>(src) + (size_t)p * src_plane, src_pitch, width, height, k,
+                                   (cudaStream_t)stream));
+    return SRB_OK;
+}

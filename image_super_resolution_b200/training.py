@@ -95,6 +95,15 @@ class TrainPlan:
         self.graphs = {}
         self.pack_batch, self.pack_ptrs = None, None
         self.grad_batch, self.grad_key, self._gjobs = None, None, None
+        # Data parallel, optional (ddp_parts > 1): the deferred weight-gradient batch runs as `ddp_parts` launches over contiguous
+        # slices of the gradient arena (last slice first: backpropagation finishes the net's tail first), and the all-reduce
+        # of a finished slice is handed to NCCL (async, its own stream) while the next launch runs.  MEASURED on 8 B200
+        # (profiles/ddp_overlap_r2.log): 2 parts 10.62 ms per step against 9.84 ms with ONE all-reduce after the whole backward
+        # (9.55 ms on one GPU) — the NCCL kernel and the persistent weight-gradient CTAs (one per SM, 226 KB of shared memory)
+        # slow each other down by more than the 0.23 ms the all-reduce costs on its own, and two one-wave launches pack the
+        # SMs worse than one 2.7-wave launch.  Default: one all-reduce.
+        self.ddp_parts = 1
+        self.grad_parts = None          # [(GradBatch, arena lo, arena hi)] in launch order
 
     # ---- operands -------------------------------------------------------------------------------------------
     def _versions(self):
@@ -209,21 +218,23 @@ class TrainPlan:
                 raise RuntimeError("backward without a saved forward")
             if "bwd" not in self.graphs:
                 self.graphs["gout"] = gout.float().contiguous().clone()
-                self._backward_impl(self.graphs["gout"])
+                self._backward_impl(self.graphs["gout"], run_batch=False)     # (also builds the gradient batch / its parts)
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
                 self._pdl(True)
                 try:
                     with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                        self.graphs["grads"] = self._backward_impl(self.graphs["gout"])
+                        self.graphs["grads"] = self._backward_impl(self.graphs["gout"], run_batch=False)
                 finally:
                     self._pdl(False)
                 self.graphs["bwd"] = g
             self.graphs["gout"].copy_(gout)
             self.graphs["bwd"].replay()
             grads = self.graphs["grads"]
+            if self.grad_parts is not None:      # data parallel: weight-gradient launches outside the graph, all-reduce overlapped
+                self._run_parts()
         self.saved = None
-        if self.allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        if self.grad_parts is None and self._ddp():
             allreduce_mean_(self.flat_grad)
         return grads
 
@@ -277,7 +288,7 @@ class TrainPlan:
                                     cout=cout, dw=self.grad_views[id(m.conv.weight)], db=self.grad_views[id(m.conv.bias)],
                                     scale=scale / float(self.grad_shift), N=N, H=H, W=W))
 
-    def _backward_impl(self, gout: torch.Tensor) -> list[torch.Tensor]:
+    def _backward_impl(self, gout: torch.Tensor, run_batch: bool = True) -> list[torch.Tensor]:
         sv, n = self.saved, self.net
         if sv is None:
             raise RuntimeError("backward without a saved forward")
@@ -346,19 +357,70 @@ class TrainPlan:
         if self._gjobs is not None:
             self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=self.grad_views[id(n.conv0.conv.bias)], N=N, H=H, W=W,
                                     scale=ish))
-            self.grad_batch, self.grad_key, self._gjobs = ops.GradBatch(self.ctx, self._gjobs, self.dt), gkey, None
-        self.grad_batch.run(self.device, self.wgrad_splitk)
+            self.grad_batch, self.grad_key = ops.GradBatch(self.ctx, self._gjobs, self.dt), gkey
+            self.grad_parts = self._split_jobs(self._gjobs) if self._ddp() and self.ddp_parts > 1 else None
+            self._gjobs = None
+        if self.grad_parts is None:
+            self.grad_batch.run(self.device, self.wgrad_splitk)
+        elif run_batch:
+            self._run_parts()
         return [self.grad_views[id(p)] for p in self.params]
 
+    def _ddp(self) -> bool:
+        return self.allreduce and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
-def allreduce_mean_(flat: torch.Tensor):
-    """One all-reduce of the flat gradient arena (NCCL over NVLink); mean over ranks like DDP."""
+    def _split_jobs(self, jobs):
+        """Partition the weight / bias gradient jobs by the arena offset of their targets into `ddp_parts` contiguous slices of
+        about equal work (FLOPs of the weight-gradient GEMMs); returned in launch order = highest arena slice first."""
+        base, esz = self.flat_grad.data_ptr(), 4
+
+        def off(j):
+            t = j.get("dw") if j.get("dw") is not None else j.get("db")
+            return (t.data_ptr() - base) // esz
+
+        def cost(j):
+            return j["N"] * j["H"] * j["W"] * j.get("cin", 0) * j["cout"] + 1
+
+        js = sorted(jobs, key=off)
+        total, parts, cur, acc = sum(cost(j) for j in js), [], [], 0
+        for j in js:
+            cur.append(j)
+            acc += cost(j)
+            if len(parts) < self.ddp_parts - 1 and acc >= total * (len(parts) + 1) / self.ddp_parts:
+                parts.append(cur)
+                cur = []
+        if cur:
+            parts.append(cur)
+        # slice boundaries: a slice ends where the next part's first target begins (parameters without a deferred job — the 9x9
+        # filters, computed inside the captured chain — fall into the slice that surrounds them)
+        bounds = [0] + [off(p[0]) for p in parts[1:]] + [self.flat_grad.numel()]
+        out = [(ops.GradBatch(self.ctx, p, self.dt), bounds[i], bounds[i + 1]) for i, p in enumerate(parts)]
+        return out[::-1]
+
+    def _run_parts(self):
+        """The weight-gradient launches with the all-reduce of every finished arena slice overlapping the next launch."""
+        works = []
+        for gb, lo, hi in self.grad_parts:
+            gb.run(self.device, self.wgrad_splitk)
+            works.append(allreduce_mean_(self.flat_grad[lo:hi], async_op=True))
+        for w in works:
+            if w is not None:
+                w.wait()
+        if dist.get_backend() != "nccl":
+            self.flat_grad.div_(dist.get_world_size())
+
+
+def allreduce_mean_(flat: torch.Tensor, async_op: bool = False):
+    """All-reduce of (a slice of) the flat gradient arena (NCCL over NVLink); mean over ranks like DDP.
+    async_op: returns the work handle (NCCL: AVG, overlaps the caller's stream; gloo: SUM — the caller divides afterwards)."""
     ws = dist.get_world_size()
     if dist.get_backend() == "nccl":
-        dist.all_reduce(flat, op=dist.ReduceOp.AVG)
-    else:
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
-        flat.div_(ws)
+        w = dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=async_op)
+        return w if async_op else flat
+    w = dist.all_reduce(flat, op=dist.ReduceOp.SUM, async_op=async_op)
+    if async_op:
+        return w
+    flat.div_(ws)
     return flat
 
 

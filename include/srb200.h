@@ -155,6 +155,14 @@ int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uint8_t* in_nc
 /* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);
+/* Tile transfer of the still-image path (rs.py:92 `window_img.unsqueeze(0).to(device)`, rs.py:105-111 `result_image[...] =
+ * frame.cpu()`): `planes` 2-D copies (cudaMemcpy2DAsync) of width x height bytes between a pitched host image and a device
+ * tile, on the caller's stream.  kind: SRB_COPY_H2D / SRB_COPY_D2H / SRB_COPY_D2D.  Pin the host image for asynchronous copies. */
+#define SRB_COPY_H2D 0
+#define SRB_COPY_D2H 1
+#define SRB_COPY_D2D 2
+int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_t dst_plane, const void* src, size_t src_pitch,
+                     size_t src_plane, int planes, size_t width, size_t height, int kind, srb_stream_t stream);
 /* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12: normalise, head, 8 fused
  * residual blocks, conv1, tail) */
 int srb_model_pt_launches(int H, int W);
