@@ -93,7 +93,7 @@ DEBUG_SIGNATURES = {
 }
 OPT_MAX_GRID, OPT_PATH = 1, 2
 PATH_UNFUSED_TRUNK, PATH_NO_PDL, PATH_TILED_CONV1, PATH_TILED_TAIL, PATH_C8_HEAD = 8, 1024, 8192, 16384, 32768
-PATH_LARGE_TILING, PATH_UNSORTED_UNITS, PATH_WS_LARGE_TILING = 65536, 131072, 262144
+PATH_LARGE_TILING, PATH_UNSORTED_UNITS, PATH_WS_LARGE_TILING, PATH_NO_PAIR = 65536, 131072, 262144, 1048576
 
 _lib = None
 _lock = threading.Lock()

@@ -1388,6 +1388,7 @@ struct RBMaps { const void* x = nullptr; int N = 0, H = 0, W = 0; CUtensorMap tm
 struct srb_resblock {
     int dtype = 0;
     uint8_t* d_wA = nullptr; uint8_t* d_wB = nullptr;
+    uint8_t* d_wA2 = nullptr; uint8_t* d_wB2 = nullptr;       // CTA-pair packing: [rank][4 arrangements]
     float* d_bA = nullptr; float* d_bB = nullptr;
     float h_bias[32 + 64] = {};      // the kernel takes the biases by value (constant bank)
     mutable RBMaps maps[2];          // tensor maps of the last two (x, y, shape) pairs: a trunk ping-pongs two buffers
@@ -1399,6 +1400,8 @@ extern "C" void srb_resblock_destroy(srb_resblock* rb) {
     if (!rb) return;
     if (rb->d_wA) cudaFree(rb->d_wA);
     if (rb->d_wB) cudaFree(rb->d_wB);
+    if (rb->d_wA2) cudaFree(rb->d_wA2);
+    if (rb->d_wB2) cudaFree(rb->d_wB2);
     if (rb->d_bA) cudaFree(rb->d_bA);
     if (rb->d_bB) cudaFree(rb->d_bB);
     delete rb;
@@ -1413,6 +1416,31 @@ static void pack_fold(const float* w, int cout, int cin, int dtype, std::vector<
             const int ks = dx * h + c2, c = (2 * c2 + g) * 8 + j, dy = 2 - s;
             out[(((size_t)ks * 2 + g) * rows + s * cout + co) * 8 + j] = f2h(w[(((size_t)co * cin + c) * 3 + dy) * 3 + dx], dtype);
         }
+}
+
+// CTA-pair fold packing (RBGeom in srb_resblock.cuh): for rank v of the pair and each arrangement, [K-step][2 granules][rows][8]
+// where the rows are this CTA's half of every piece (s0, n) of B = [W(dy=2) | W(dy=1) | W(dy=0)] (global row = s * cout + co):
+// piece (s0, n) -> rows s0 * cout + v * n * cout / 2 + [0, n * cout / 2).
+static void pack_fold_pair(const float* w, int cout, int cin, int dtype, std::vector<uint16_t>& out) {
+    const int h = cin / 16, ksteps = 3 * h, rowsF = 3 * cout / 2, rows3 = cout / 2;
+    const size_t arrF = (size_t)ksteps * 2 * rowsF * 8, arr3 = (size_t)ksteps * 2 * rows3 * 8, per_rank = 3 * arrF + arr3;
+    out.assign(2 * per_rank, 0);
+    struct Piece { int s0, n; };
+    const Piece arrs[4][2] = {{{0, 3}, {0, 0}}, {{0, 1}, {1, 2}}, {{0, 2}, {2, 1}}, {{1, 1}, {0, 0}}};
+    for (int v = 0; v < 2; ++v) for (int a = 0; a < 4; ++a) {
+        const int rows = a == 3 ? rows3 : rowsF;
+        uint16_t* base = out.data() + v * per_rank + (a < 3 ? a * arrF : 3 * arrF);
+        std::vector<int> grow;                       // global B row of each of this CTA's rows
+        for (int pc = 0; pc < 2; ++pc) {
+            const Piece& q = arrs[a][pc];
+            for (int i = 0; i < q.n * cout / 2; ++i) grow.push_back(q.s0 * cout + v * q.n * cout / 2 + i);
+        }
+        for (int dx = 0; dx < 3; ++dx) for (int c2 = 0; c2 < h; ++c2) for (int g = 0; g < 2; ++g)
+            for (int r = 0; r < rows && r < (int)grow.size(); ++r) for (int j = 0; j < 8; ++j) {
+                const int ks = dx * h + c2, c = (2 * c2 + g) * 8 + j, sl = grow[r] / cout, co = grow[r] % cout, dy = 2 - sl;
+                base[(((size_t)ks * 2 + g) * rows + r) * 8 + j] = f2h(w[(((size_t)co * cin + c) * 3 + dy) * 3 + dx], dtype);
+            }
+    }
 }
 
 extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* bA, const float* wB, const float* bB, int dtype,
@@ -1436,6 +1464,18 @@ extern "C" int srb_resblock_create(srb_ctx* ctx, const float* wA, const float* b
     CUDA_TRY(cudaMemcpy(rb->d_wB, pb.data(), G::WB_BYTES, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(rb->d_bA, bA, G::CH * 4, cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpy(rb->d_bB, bB, G::CB * 4, cudaMemcpyHostToDevice));
+    {
+        std::vector<uint16_t> pa2, pb2;
+        pack_fold_pair(wA, G::CH, G::CA, dtype, pa2);
+        pack_fold_pair(wB, G::CB, G::CH, dtype, pb2);
+        if (pa2.size() * 2 != (size_t)2 * G::W2_BYTES || pb2.size() * 2 != (size_t)2 * G::W2_BYTES) { srb_resblock_destroy(rb); return fail(SRB_EINVAL, "srb_resblock_create: pair pack size"); }
+        if (cudaMalloc(&rb->d_wA2, 2 * G::W2_BYTES) != cudaSuccess || cudaMalloc(&rb->d_wB2, 2 * G::W2_BYTES) != cudaSuccess) {
+            srb_resblock_destroy(rb);
+            return fail(SRB_ENOMEM, "srb_resblock_create: cudaMalloc failed");
+        }
+        CUDA_TRY(cudaMemcpy(rb->d_wA2, pa2.data(), 2 * G::W2_BYTES, cudaMemcpyHostToDevice));
+        CUDA_TRY(cudaMemcpy(rb->d_wB2, pb2.data(), 2 * G::W2_BYTES, cudaMemcpyHostToDevice));
+    }
     memcpy(rb->h_bias, bA, G::CH * 4);
     memcpy(rb->h_bias + G::CH, bB, G::CB * 4);
     *out = rb;
@@ -1487,31 +1527,48 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_resblock_fwd: too many rows");
-    p.total_rows = (int)(sets * H);
-    p.wA = rb->d_wA; p.wB = rb->d_wB;
+    // CTA pairs (cta_group::2): two strip-sets march in lock-step on the two SMs of a TPC, every M = 256 MMA reads half of B from
+    // each.  Needs at least two strip-sets; the leftover of an odd count runs against an empty (zero-filled, not stored) partner.
+    const bool pair = sets >= 2 && !(ctx->path & SRB_PATH_NO_PAIR) && (ctx->num_sms % 2) == 0;
+    p.total_rows = pair ? (int)((sets + 1) / 2 * H) : (int)(sets * H);
+    p.wA = rb->d_wA; p.wB = rb->d_wB; p.wA2 = rb->d_wA2; p.wB2 = rb->d_wB2;
     memcpy(p.bias, rb->h_bias, sizeof(p.bias));
     p.x = x; p.y = y; p.slope = slope; p.dbg_skip = ctx->dbg_skip; p.dbg_trace = ctx->dbg_trace;
     int grid = p.total_rows / 8;
     if (grid < 1) grid = 1;
-    if (grid > ctx->num_sms) grid = ctx->num_sms;
-    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
+    if (pair) {                                   // grid counts CTAs: clusters of two
+        if (grid > ctx->num_sms / 2) grid = ctx->num_sms / 2;
+        if (ctx->max_grid > 0 && grid > (ctx->max_grid + 1) / 2) grid = (ctx->max_grid + 1) / 2;
+        grid *= 2;
+    } else {
+        if (grid > ctx->num_sms) grid = ctx->num_sms;
+        if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
+    }
     if (!rb->attr_set) {
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
         CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM2_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(resblock_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM2_BYTES));
         rb->attr_set = true;
     }
     // programmatic dependent launch: this launch's prologue (barriers, TMEM, filters) overlaps the previous launch's tail
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
     cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = pair ? 2 : 1;
+    if (pair) cfg.dynamicSmemBytes = G::SMEM2_BYTES;
     if (SRB_DBG(ctx->dbg_skip & 4096) && ctx->dbg_threads > 0) cfg.blockDim = dim3(ctx->dbg_threads);     // launch-overhead probes only
     if (SRB_DBG(ctx->dbg_skip & 4096) && ctx->dbg_smem >= 0) cfg.dynamicSmemBytes = ctx->dbg_smem;
     for (int rep = 0; rep <= SRB_DBG(ctx->dbg_repeat); ++rep) {
-        if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, p));
+        if (pair) {
+            if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true, true>, m->tm, p));
+            else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false, true>, m->tm, p));
+        } else if (rb->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<true>, m->tm, p));
         else CUDA_TRY(cudaLaunchKernelEx(&cfg, resblock_kernel<false>, m->tm, p));
     }
     return SRB_OK;

@@ -240,3 +240,105 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 }  // namespace srb
+
+// ------------------------------------------------------------------------------------------
+// CTA pairs (thread-block cluster of two CTAs on one TPC, tcgen05 cta_group::2): one M = 256 MMA issued by the leader CTA
+// works on both CTAs' A rows / TMEM accumulators and reads HALF of B from each CTA's shared memory.
+// ------------------------------------------------------------------------------------------
+namespace srb {
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {       // every thread of every CTA of the cluster
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+    return r;
+}
+// arrive on a barrier given by a shared::cluster address (this CTA's or the peer's).  Default semantics (release at CTA
+// scope): what is handed over lives in the ARRIVING CTA's own shared memory / TMEM and is consumed by that SM's tensor core;
+// the leader only observes the barrier and issues the MMA.  (Measured: `.release.cluster` makes every arrival a cluster-scope
+// memory barrier — 1 500 to 3 000 clk per hand-off in the epilogues, profiles/rb_trace_pair_r2.log.)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {   // acquire at cluster scope
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// bounded wait like mbar_wait, observing arrivals from the peer CTA
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, uint32_t tag) {
+    if (mbar_try_wait_cluster(bar, parity)) return;
+    long long t0 = clock64();
+    for (;;) {
+#pragma unroll 1
+        for (int i = 0; i < 64; ++i)
+            if (mbar_try_wait_cluster(bar, parity)) return;
+        if (g_srb_abort) return;
+        if (clock64() - t0 > (1ll << SRB_WAIT_BUDGET_LOG2)) {
+            if (atomicExch((unsigned int*)&g_srb_abort, 1u) == 0u) {
+                g_srb_timeout_info[0] = 0xdead0000u | tag;
+                g_srb_timeout_info[1] = blockIdx.x;
+                g_srb_timeout_info[2] = threadIdx.x;
+                g_srb_timeout_info[3] = parity;
+                unsigned int* h = g_srb_abort_host;
+                if (h != nullptr) {
+                    h[1] = 0xdead0000u | tag; h[2] = blockIdx.x; h[3] = threadIdx.x; h[4] = parity;
+                    __threadfence_system();
+                    *reinterpret_cast<volatile unsigned int*>(h) = 1u;
+                }
+            }
+            __threadfence_system();
+            return;
+        }
+    }
+}
+// 4-D tiled tensor load into THIS CTA's shared memory whose completion is signalled on a barrier of either CTA of the pair
+// (`bar_cluster_addr`: shared::cluster address, e.g. the leader's barrier from mapa_u32)
+__device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const void* tmap, uint32_t bar_cluster_addr, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_result, uint32_t ncols) {  // whole warp, in both CTAs
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem of both CTAs] += A[each CTA's 128 rows] * B[N/2 rows from each CTA]^T, M = 256; issued by one thread of the leader CTA
+__device__ __forceinline__ void umma_f16_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs once all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+
+}  // namespace srb

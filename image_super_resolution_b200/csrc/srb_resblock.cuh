@@ -31,6 +31,8 @@ struct ResblockParams {
     int total_rows;           // strip-sets x H: the flattened (strip-set, output row) space split evenly over CTAs
     const uint8_t* wA;        // fold-packed 64 -> 32:  12 K-steps x [2][96][8]
     const uint8_t* wB;        // fold-packed 32 -> 64:   6 K-steps x [2][192][8]
+    const uint8_t* wA2;       // CTA-pair packing (pack_fold_pair): [rank][4 arrangements] of each CTA's half of the B rows
+    const uint8_t* wB2;
     float bias[32 + 64];      // convA, convB biases, by value (copied to shared memory in the prologue)
     const void* x;            // [N][8][H][W][8]
     void* y;                  // [N][8][H][W][8]
@@ -92,6 +94,23 @@ struct RBGeom {
     static constexpr int OFF_WA = 0, OFF_WB = WA_BYTES, OFF_X = OFF_WB + WB_BYTES, OFF_H = OFF_X + XSTAGES * XROW;
     static constexpr int OFF_BIAS = OFF_H + HSLOTS * HROW, OFF_BAR = OFF_BIAS + (CH + CB) * 4;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
+    // ---- CTA-pair variant (cta_group::2): every CTA holds HALF of each B piece.  A folded MMA covers slices [s0, s0 + n) of
+    // B = [W(dy=2) | W(dy=1) | W(dy=0)]; the hardware takes the first N/2 rows of a piece from the leader CTA and the second
+    // N/2 from its peer, both at the SAME shared-memory address, so every piece that is ever issued needs its own placement:
+    //   arrangement 0: piece (0,3)                  the common case: a whole three-row window
+    //   arrangement 1: pieces (0,1) then (1,2)      a window split after its first row by the ring's wrap-around / a top edge
+    //   arrangement 2: pieces (0,2) then (2,1)      ... split after its second row / a bottom edge
+    //   arrangement 3: piece (1,1)                  one-row segments
+    // rows per CTA and arrangement: 3*CO/2 (arrangement 3: CO/2); bytes: K-steps x 2 granules x rows x 16.
+    static constexpr int XSTAGES2 = 3;
+    static constexpr int W2_ARR = KA * 2 * (3 * CH / 2) * 16;                        // 18432 (convB: KB * 2 * (3*CB/2) * 16 = the same)
+    static constexpr int W2_P3 = KA * 2 * (CH / 2) * 16;                             // 6144
+    static constexpr int W2_BYTES = 3 * W2_ARR + W2_P3;                              // 61440 per conv and CTA
+    static_assert(KB * 2 * (3 * CB / 2) * 16 == W2_ARR && KB * 2 * (CB / 2) * 16 == W2_P3, "convA / convB pair packs have one size");
+    static constexpr int OFF2_WA = 0, OFF2_WB = W2_BYTES, OFF2_X = 2 * W2_BYTES, OFF2_H = OFF2_X + XSTAGES2 * XROW;
+    static constexpr int OFF2_BIAS = OFF2_H + HSLOTS * HROW, OFF2_BAR = OFF2_BIAS + (CH + CB) * 4;
+    static constexpr int SMEM2_BYTES = 1024 + OFF2_BAR + 512;
+    static_assert(SMEM2_BYTES <= 227 * 1024, "shared memory budget (pair)");
     static constexpr int THREADS = 640;            // 4 control warps (one spare) + 8 hidden-epilogue + 8 output-epilogue warps
     static_assert(KSPLIT * RH * CH + RY * CB == 512, "the accumulator rings fill TMEM");
     static_assert(KSPLIT == 1 || RB_BIAS_MODE == 1, "the K-split hidden rings are armed with zero");
@@ -150,11 +169,13 @@ __device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k
 
 // a segment: output rows [y0, y1) of strip-set ss, with the hidden / input row ranges it needs (clipped to the image)
 struct RBSeg { int ss, y0, y1, hlo, hhi, xlo, xhi; };
+// (ss_mul, ss_add: a CTA pair marches over PAIRS of strip-sets in lock-step — rank r of the pair owns strip-set 2 * q + r)
 template <class Params>
-__device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBSeg& s) {
+__device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBSeg& s, int ss_mul = 1, int ss_add = 0) {
     if (g >= g1) return false;
-    s.ss = g / p.H;
-    s.y0 = g - s.ss * p.H;
+    const int q = g / p.H;
+    s.ss = q * ss_mul + ss_add;
+    s.y0 = g - q * p.H;
     int n = g1 - g;
     s.y1 = s.y0 + n < p.H ? s.y0 + n : p.H;
     s.hlo = s.y0 > 0 ? s.y0 - 1 : 0;
@@ -185,7 +206,7 @@ __device__ __forceinline__ RBSlot rb_slot(const Params& p, int ss, int j) {
     } else {
         s.n = ss / p.TS;
         s.gx = (ss - s.n * p.TS) * (16 - 2 * p.OV) + j;
-        s.in = s.gx < p.GX;
+        s.in = s.gx < p.GX && s.n < p.N;          // (n >= N: the phantom strip-set of a CTA pair when the count is odd)
         s.out = s.in && (p.OV == 0 || ((j > 0 || s.gx == 0) && (j < 15 || s.gx == p.GX - 1)));
     }
     if (!s.in) { s.n = p.N; s.gx = 0; }        // as TMA coordinates: outside the tensor, the box is zero-filled
@@ -214,7 +235,38 @@ __device__ __forceinline__ void rb_issue(const RBPlan& q, uint64_t a_desc, uint6
     if (q.two) umma_f16_ss(q.d1, a_desc, b_desc + q.boff1, q.idesc1, 1u);
 }
 
-template <bool BF16>
+// CTA-pair issue plan: the same window as RBPlan, every piece with its own B placement (see RBGeom) and M = 256
+struct RBPlan2 { uint32_t d0, d1, idesc0, idesc1, ks0, ks1; uint64_t b0, b1; bool two; };
+template <int CO, int KST, bool BF16>
+__device__ __forceinline__ void rb_piece2(uint32_t w_addr, int s0, int n, uint64_t& b, uint32_t& ks, uint32_t& idesc) {
+    constexpr int ROWS = 3 * CO / 2, ARR = KST * 2 * ROWS * 16;
+    int arr, off;
+    if (n == 3) { arr = 0; off = 0; }
+    else if (n == 2) { arr = s0 == 1 ? 1 : 2; off = s0 == 1 ? CO / 2 : 0; }
+    else { arr = s0 == 0 ? 1 : (s0 == 2 ? 2 : 3); off = s0 == 2 ? CO : 0; }
+    const int rows = arr == 3 ? CO / 2 : ROWS;
+    b = umma_desc_nosw(w_addr + arr * ARR + off * 16, rows * 16, 128);
+    ks = (uint32_t)((2 * rows * 16) >> 4);
+    idesc = umma_idesc_f16(256, n * CO, BF16 ? 1 : 0);
+}
+template <int CO, int R, int KST, bool BF16>
+__device__ __forceinline__ RBPlan2 rb_plan2(uint32_t tm_ring, uint32_t w_addr, int slot, int nsl, int s0) {
+    RBPlan2 q;
+    const int n1 = R - slot < nsl ? R - slot : nsl;
+    q.d0 = tm_ring + slot * CO;
+    rb_piece2<CO, KST, BF16>(w_addr, s0, n1, q.b0, q.ks0, q.idesc0);
+    q.two = n1 < nsl;
+    q.d1 = tm_ring;
+    q.b1 = q.b0; q.ks1 = q.ks0; q.idesc1 = q.idesc0;
+    if (q.two) rb_piece2<CO, KST, BF16>(w_addr, s0 + n1, nsl - n1, q.b1, q.ks1, q.idesc1);
+    return q;
+}
+__device__ __forceinline__ void rb_issue2(const RBPlan2& q, uint64_t a_desc, int kk) {
+    umma_f16_ss_pair(q.d0, a_desc, q.b0 + (uint64_t)(kk * q.ks0), q.idesc0, 1u);
+    if (q.two) umma_f16_ss_pair(q.d1, a_desc, q.b1 + (uint64_t)(kk * q.ks1), q.idesc1, 1u);
+}
+
+template <bool BF16, bool PAIR = false>
 __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __grid_constant__ CUtensorMap tmap_x,
                                                                       const ResblockParams p) {
     using G = RBGeom;
@@ -222,12 +274,19 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     // (offset arithmetic on the __shared__ array, not an integer round trip: the compiler keeps the shared address space
     // and the epilogues' plain loads / stores become LDS / STS instead of generic accesses)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t* s_wA = smem + G::OFF_WA;
-    uint8_t* s_wB = smem + G::OFF_WB;
-    uint8_t* s_x = smem + G::OFF_X;
-    uint8_t* s_h = smem + G::OFF_H;
-    float* s_bias = reinterpret_cast<float*>(smem + G::OFF_BIAS);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
+    constexpr int XST = PAIR ? G::XSTAGES2 : G::XSTAGES;
+    uint8_t* s_wA = smem + (PAIR ? G::OFF2_WA : G::OFF_WA);
+    uint8_t* s_wB = smem + (PAIR ? G::OFF2_WB : G::OFF_WB);
+    uint8_t* s_x = smem + (PAIR ? G::OFF2_X : G::OFF_X);
+    uint8_t* s_h = smem + (PAIR ? G::OFF2_H : G::OFF_H);
+    float* s_bias = reinterpret_cast<float*>(smem + (PAIR ? G::OFF2_BIAS : G::OFF_BIAS));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (PAIR ? G::OFF2_BAR : G::OFF_BAR));
+    // CTA pair: rank 0 (the leader) issues every MMA for both CTAs; the consumer -> issuer barriers (haempty, hsfull, yaempty,
+    // and xfull for the TMA bytes) live in the LEADER and collect the arrivals of both CTAs, the issuer -> consumer barriers
+    // exist in both CTAs and are signalled by multicast commits
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0u;
+    const uint32_t bars_leader = PAIR ? mapa_u32(smem_u32(bars), 0u) : 0u;      // shared::cluster address of the leader's barrier array
     uint64_t* xfull = bars;            // [XSTAGES]  TMA -> MMA
     uint64_t* xempty = bars + 8;       // [XSTAGES]  MMA -> TMA
     uint64_t* hafull = bars + 16;      // [RH] hidden accumulator row complete        MMA -> hidden epilogue
@@ -271,18 +330,27 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         reinterpret_cast<uint4*>(s_h)[i] = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < G::CH + G::CB; i += G::THREADS) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
-        for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], G::KSPLIT); }
-        for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], G::KSPLIT); mbar_init(&haempty[i], 4); }
-        for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4); mbar_init(&hsempty[i], 1); }
-        for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
+        constexpr int NC = PAIR ? 2 : 1;     // CTAs whose warps arrive on the leader's consumer -> issuer barriers
+        for (int i = 0; i < XST; ++i) { mbar_init(&xfull[i], NC); mbar_init(&xempty[i], G::KSPLIT); }
+        for (int i = 0; i < G::RH; ++i) { mbar_init(&hafull[i], G::KSPLIT); mbar_init(&haempty[i], 4 * NC); }
+        for (int i = 0; i < G::HSLOTS; ++i) { mbar_init(&hsfull[i], 4 * NC); mbar_init(&hsempty[i], 1); }
+        for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8 * NC); }
         mbar_init(wbar, 1);
         fence_mbar_init();
         tma_prefetch_desc(&tmap_x);
+        if constexpr (PAIR) {                // this CTA's half of the filters (the leader's issuers need both halves in place
+            fence_proxy_async_smem();        // before their first MMA: waited for below, ahead of the cluster barrier)
+            mbar_arrive_expect_tx(wbar, 2 * G::W2_BYTES);
+            const uint8_t* ga = p.wA2 + (size_t)rank * G::W2_BYTES;
+            const uint8_t* gb = p.wB2 + (size_t)rank * G::W2_BYTES;
+            for (int off = 0; off < G::W2_BYTES; off += 12288) bulk_load_1d(s_wA + off, ga + off, 12288, wbar);
+            for (int off = 0; off < G::W2_BYTES; off += 12288) bulk_load_1d(s_wB + off, gb + off, 12288, wbar);
+        }
     }
     fence_proxy_async_smem();
-    if (warp == 0) { __syncwarp(); tmem_alloc(s_tmem, 512); }
+    if (warp == 0) { __syncwarp(); if constexpr (PAIR) tmem_alloc_pair(s_tmem, 512); else tmem_alloc(s_tmem, 512); }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
     if (warp >= 4 && warp < 8) {
@@ -299,21 +367,25 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         }
         tmem_st_wait();
     }
+    if constexpr (PAIR) { if (warp == 0) mbar_wait(wbar, 0, 32); }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
 
     if (SRB_DBG(p.dbg_trace != nullptr) && threadIdx.x == 0) p.dbg_trace[1024 + 8 * blockIdx.x + 2] = clock64();
     // Everything above touched only this launch's constants.  The next launch in the stream may now start its own
     // prologue on every SM this grid vacates; the warps below that touch activations first wait for the previous launch.
     pdl_launch_dependents();
-    const int g_begin = (int)((long long)blockIdx.x * p.total_rows / gridDim.x);
-    const int g_end = SRB_DBG(p.dbg_skip & 2048) ? g_begin : (int)((long long)(blockIdx.x + 1) * p.total_rows / gridDim.x);   // 2048: prologue-only probe
+    // (pair: total_rows counts rows of strip-set PAIRS; both CTAs of a cluster take the same run and march in lock-step)
+    const int n_units = PAIR ? (int)gridDim.x >> 1 : (int)gridDim.x, unit = PAIR ? (int)blockIdx.x >> 1 : (int)blockIdx.x;
+    const int g_begin = (int)((long long)unit * p.total_rows / n_units);
+    const int g_end = SRB_DBG(p.dbg_skip & 2048) ? g_begin : (int)((long long)(unit + 1) * p.total_rows / n_units);   // 2048: prologue-only probe
+    const int ss_mul = PAIR ? 2 : 1, ss_add = (int)rank;
     const size_t HW = (size_t)p.H * p.W;
 
     if (warp == 0) {
         // ===================== TMA producer: filters once, then one x row (16 group boxes) per stage =====================
-        if (elect_one()) {
+        if (!PAIR && elect_one()) {
             mbar_arrive_expect_tx(wbar, G::WA_BYTES + G::WB_BYTES);
             for (int off = 0; off < G::WA_BYTES; off += 12288) bulk_load_1d(s_wA + off, p.wA + off, 12288, wbar);
             for (int off = 0; off < G::WB_BYTES; off += 12288) bulk_load_1d(s_wB + off, p.wB + off, 12288, wbar);
@@ -322,14 +394,24 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         pdl_wait();                          // x is the previous launch's output
         int xc = 0, g = g_begin;
         RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
+        while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
             const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
             const int n = sl.n, gx = sl.gx;
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
-                const int st = xc % G::XSTAGES;
-                mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 31);
+                const int st = xc % XST;
+                mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / XST) & 1) ^ 1), 31);
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 19);         // x stage free
+                if constexpr (PAIR) {
+                    // both CTAs' rows of this step complete the LEADER's barrier (two arrivals, 2 x XROW bytes)
+                    const uint32_t xf = bars_leader + (uint32_t)(st * 8);
+                    if (lane == 0) mbar_arrive_expect_tx_cluster(xf, G::XROW);
+                    __syncwarp();
+                    if (lane < 16)
+                        tma_load_4d_pair(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, xf, (gx * 8 - 1) * 4, r, 0, n);
+                    __syncwarp();
+                    continue;
+                }
                 if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
@@ -339,7 +421,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 20);         // x row requested
             }
         }
-    } else if (warp == 1 || (G::KSPLIT == 2 && warp == 3)) {
+    } else if ((warp == 1 || (G::KSPLIT == 2 && warp == 3)) && leader) {
         // ===================== convA MMA issuer(s): one x row per step, N = 3 x 32 into the hidden accumulator ring =====================
         // K split: warp 1 owns input channels 0..31 (K-steps c2 = 0, 1 of every dx) and ring H0, warp 3 channels 32..63 and H1
         const int kh = warp == 3 ? 1 : 0;
@@ -348,14 +430,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         // fast enough, and the tensor pipe interleaves the two warps' independent accumulation chains by itself)
         const uint64_t adescA0 = umma_desc_nosw(0, 160, G::XBOX);           // x row: planes 160 B apart, groups XBOX apart
         const uint64_t bdescA0 = umma_desc_nosw(smem_u32(s_wA), 3 * G::CH * 16, 128);
-        mbar_wait(wbar, 0, 32);
+        if constexpr (!PAIR) mbar_wait(wbar, 0, 32);
+        const uint32_t wA_u32 = smem_u32(s_wA);
         // ring positions are tracked incrementally (no divisions on the issue path)
         int xst = 0; uint32_t xph = 0;                 // x stage / phase of the next x row
         int hslot0 = 0;                                // ring slot of the segment's first hidden row (hidden counter hbase)
         int acq_slot = 0; uint32_t acq_ph = 1;         // next hidden slot to acquire, parity to wait for (empty: phase ^ 1)
         int hbase = 0, h_acq = 0, g = g_begin, xc = 0;
         RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
+        while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 mbar_wait<RB_CTRL>(&xfull[xst], xph, 33);
@@ -371,6 +454,19 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && kh == 0) rb_trace(p, xc, 0);          // waits of this x row satisfied
                 if (elect_one()) {
                     const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
+                    if constexpr (PAIR) {
+                        const RBPlan2 q2 = rb_plan2<G::CH, G::RH, G::KA, BF16>(tm_ring_a, wA_u32, slot_lo, a_n, a_s0);
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx)
+#pragma unroll
+                            for (int cc = 0; cc < (G::KSPLIT == 2 ? 2 : 4); ++cc) {
+                                const int c2 = (G::KSPLIT == 2 ? 2 * kh : 0) + cc, kk = dx * 4 + c2;
+                                rb_issue2(q2, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), kk);
+                            }
+                        umma_commit_pair(&xempty[xst]);
+                        if (r - 1 >= sg.hlo) umma_commit_pair(&hafull[(hslot0 + (r - 1 - sg.hlo)) % G::RH]);
+                        if (r == sg.xhi && r <= sg.hhi) umma_commit_pair(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
+                    } else {
                     const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tm_ring_a, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
                     if (!SRB_DBG(p.dbg_skip & (2 | 16))) {
                         if constexpr (G::KSPLIT == 2) {
@@ -393,26 +489,28 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     // hidden row r-1 is complete (all three input rows seen); at the last x row also row r itself
                     if (r - 1 >= sg.hlo) umma_commit(&hafull[(hslot0 + (r - 1 - sg.hlo)) % G::RH]);
                     if (r == sg.xhi && r <= sg.hhi) umma_commit(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
+                    }
                 }
                 __syncwarp();
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && kh == 0) rb_trace(p, xc, 1);          // MMAs + commits issued
-                if (++xst == G::XSTAGES) { xst = 0; xph ^= 1; }
+                if (++xst == XST) { xst = 0; xph ^= 1; }
             }
             const int nh = sg.hhi - sg.hlo + 1;
             hbase += nh;
             hslot0 = (hslot0 + nh) % G::RH;
         }
-    } else if (warp == 2) {
+    } else if (warp == 2 && leader) {
         // ===================== convB MMA issuer: one hidden row per step, N = 3 x 64 into the output accumulator ring =====================
         const uint64_t adescB0 = umma_desc_nosw(0, 160, G::HBOX);
         const uint64_t bdescB0 = umma_desc_nosw(smem_u32(s_wB), 3 * G::CB * 16, 128);
-        mbar_wait(wbar, 0, 37);
+        if constexpr (!PAIR) mbar_wait(wbar, 0, 37);
+        const uint32_t wB_u32 = smem_u32(s_wB);
         int hs = 0; uint32_t hph = 0;                  // hidden smem slot / phase of the next hidden row
         int yslot0 = 0;                                // ring slot of the segment's first output row
         int acq_slot = 0; uint32_t acq_ph = 1;
         int ybase = 0, ybase_h = 0, y_acq = 0, g = g_begin;
         RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
+        while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int hc = ybase_h + h - sg.hlo;               // running hidden-row counter (trace only)
@@ -429,6 +527,17 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, hc, 17);         // output accumulator rows acquired
                 if (elect_one()) {
                     const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
+                    if constexpr (PAIR) {
+                        const RBPlan2 q2 = rb_plan2<G::CB, G::RY, G::KB, BF16>(tmem_base + G::TM_Y, wB_u32, slot_lo, b_n, b_s0);
+#pragma unroll
+                        for (int k = 0; k < G::KB; ++k) {
+                            const int dx = k >> 1, c2 = k & 1;
+                            rb_issue2(q2, adB + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), k);
+                        }
+                        umma_commit_pair(&hsempty[hs]);
+                        if (h - 1 >= sg.y0) umma_commit_pair(&yafull[(yslot0 + (h - 1 - sg.y0)) % G::RY]);
+                        if (h == sg.hhi && h <= sg.y1 - 1) umma_commit_pair(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
+                    } else {
                     const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
                     if (!SRB_DBG(p.dbg_skip & (2 | 32))) {
 #pragma unroll
@@ -440,6 +549,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     umma_commit(&hsempty[hs]);
                     if (h - 1 >= sg.y0) umma_commit(&yafull[(yslot0 + (h - 1 - sg.y0)) % G::RY]);
                     if (h == sg.hhi && h <= sg.y1 - 1) umma_commit(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
+                    }
                 }
                 __syncwarp();
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, hc, 18);         // convB MMAs + commits issued
@@ -464,7 +574,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         const bool tr = SRB_DBG(p.dbg_trace != nullptr) && lane == 0 && lg == 0;
         int hbase = 0, g = g_begin;
         RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
+        while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
             const RBSlot sl = rb_slot(p, sg.ss, grp);
             const bool valid = sl.in && sl.gx * 8 + i < p.W;
             // halo pixels go to the neighbouring slot when that is the neighbouring group of the same image row (an idle or
@@ -527,7 +637,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (tr) rb_trace(p, c, 14);
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) { mbar_arrive(&haempty[slot]); mbar_arrive(&hsfull[hs]); }
+                if (lane == 0) {
+                    if constexpr (PAIR) { mbar_arrive_cluster(bars_leader + (uint32_t)((24 + slot) * 8)); mbar_arrive_cluster(bars_leader + (uint32_t)((32 + hs) * 8)); }
+                    else { mbar_arrive(&haempty[slot]); mbar_arrive(&hsfull[hs]); }
+                }
                 if (tr) rb_trace(p, c, 4);        // hidden row published
             }
             hbase += sg.hhi - sg.hlo + 1;
@@ -551,7 +664,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int c = 0, g = g_begin;                    // c: running output-row counter
         int slot = 0; uint32_t yph = 0;            // accumulator ring slot / phase
         RBSeg sg;
-        while (rb_next_seg(p, g, g_end, sg)) {
+        while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
             const RBSlot sl = rb_slot(p, sg.ss, grp);
             const int n = sl.n, gx = sl.gx;
             const bool valid = sl.out && gx * 8 + i < p.W;
@@ -613,7 +726,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 tc_fence_before();
                 if (tr) rb_trace(p, c, 9);
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&yaempty[slot]);
+                if (lane == 0) {
+                    if constexpr (PAIR) mbar_arrive_cluster(bars_leader + (uint32_t)((48 + slot) * 8));
+                    else mbar_arrive(&yaempty[slot]);
+                }
                 if (tr) rb_trace(p, c, 7);      // output row done
                 if (++slot == G::RY) { slot = 0; yph ^= 1; }
             }
@@ -633,7 +749,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             atomicMax(&p.dbg_trace[2304 + 4 * launch + 3], gt);
         }
     }
-    if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
+    if constexpr (PAIR) {
+        cluster_sync_all();          // the peer's barriers / TMEM are targets of this CTA's commits and arrivals until both are done
+        if (warp == 0) { __syncwarp(); tmem_dealloc_pair(tmem_base, 512); }
+    } else if (warp == 0) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
 }
 
 }  // namespace srb

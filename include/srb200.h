@@ -69,6 +69,7 @@ int srb_num_sms(const srb_ctx* ctx);
 #define SRB_PATH_LARGE_TILING 65536       /* never pick the small-problem super-tile shapes                             */
 #define SRB_PATH_UNSORTED_UNITS 131072    /* batched weight gradient: units in job order                                */
 #define SRB_PATH_WS_LARGE_TILING 262144   /* large tiling for the weight-streaming convs only                           */
+#define SRB_PATH_NO_PAIR 1048576          /* fused residual block on single CTAs (cta_group::1) instead of CTA pairs          */
 int srb_set_option(srb_ctx* ctx, int key, int value);
 
 /* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for

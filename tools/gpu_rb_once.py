@@ -7,6 +7,8 @@ import torch
 from image_super_resolution_b200 import ops
 from image_super_resolution_b200._lib import Context
 dev = torch.device("cuda:0"); ctx = Context.get(0)
+if os.environ.get("SRB_NO_PAIR") == "1":
+    ctx.set_option(2, 1048576)          # SRB_PATH_NO_PAIR: single-CTA kernel
 g = torch.Generator().manual_seed(0)
 rb = ops.ResBlock(ctx, torch.randn(32, 64, 3, 3, generator=g) / 24, torch.zeros(32), torch.randn(64, 32, 3, 3, generator=g) / 17,
                   torch.zeros(64), "fp16")
