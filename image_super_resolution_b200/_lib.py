@@ -48,7 +48,11 @@ SIGNATURES = {
     "srb_conv2d_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _i, _vp]),
     "srb_bias_grad": (_i, [_vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_conv2d_ex": (_i, [_vp, _vp, _vp, _vp]),
+    "srb_conv_chain_create": (_i, [_vp, _i, C.POINTER(_vp), _vp, C.POINTER(_vp)]),
+    "srb_conv_chain_run": (_i, [_vp, _vp, _vp]),
+    "srb_conv_chain_destroy": (None, [_vp]),
     "srb_alloc_conv": (_i, [_vp, _i, _i, _i, _i, C.POINTER(_vp)]),
+    "srb_alloc_conv_ex": (_i, [_vp, _i, _i, _i, _i, _i, C.POINTER(_vp)]),
     "srb_pack_conv_device": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "srb_conv9_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_tanh_bwd_to_c8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),

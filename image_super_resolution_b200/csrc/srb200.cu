@@ -4,6 +4,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdarg.h>
+#include <stddef.h>
 #include <stdio.h>
 #include <string.h>
 #include <math.h>
@@ -87,6 +88,7 @@ struct srb_ctx {
 struct srb_weights {
     int cout = 0, cin = 0, k = 0, dtype = 0;
     int mode = 0, c8in = 0, nout = 0, ksteps = 0;
+    int nmma = 0;      // B rows per K granule = N of one MMA: nout, or 3 * nout for the dy-folded 3x3 operands (MODE_DYF)
     int kblocks = 0;   // > 0: weight-streaming layout, blocks of 4 planes (32 channels)
     uint8_t* d_pack = nullptr;
     float* d_bias = nullptr;
@@ -207,26 +209,36 @@ static uint16_t f2h(float f, int dtype) {
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 // kernel family + packed-operand geometry of a (cout, cin, k) conv
-static int conv_geometry(int cout, int cin, int k, int* mode, int* c8in, int* nout, int* ksteps, int* kblocks) {
+static int conv_geometry(int cout, int cin, int k, int* mode, int* c8in, int* nout, int* ksteps, int* kblocks, bool force_ws = false,
+                         bool fold = false) {
     if (k == 9 && cin == 3) { *mode = MODE_PAIRDX; *c8in = 1; *nout = round_up(cout, 32); *ksteps = 9 * 5; }
     else if (k == 9 && cout == 3 && cin % 16 == 0) { *mode = MODE_DXN; *c8in = cin / 8; *nout = 32; *ksteps = 9 * (*c8in / 2); }
     else if (k == 3 && cin % 16 == 0) { *mode = MODE_STD; *c8in = cin / 8; *nout = round_up(cout, 32); *ksteps = 9 * (*c8in / 2); }
     else return fail(SRB_ENOSUP, "srb_pack_conv: no kernel for cout=%d cin=%d k=%d", cout, cin, k);
     if (*nout > 256) return fail(SRB_ENOSUP, "srb_pack_conv: cout=%d > 256", cout);
-    *kblocks = (*mode == MODE_STD && *c8in > 8) ? *c8in / 4 : 0;
+    *kblocks = (*mode == MODE_STD && (*c8in > 8 || (force_ws && *c8in % 4 == 0))) ? *c8in / 4 : 0;
+    if (fold) {      // dy taps folded into N (MODE_DYF): weight-streaming 3x3 convs with 32 outputs
+        if (*mode != MODE_STD || !*kblocks || *nout != 32) return fail(SRB_ENOSUP, "srb_alloc_conv_ex: no dy-folded kernel for cout=%d cin=%d k=%d", cout, cin, k);
+        *mode = MODE_DYF; *ksteps = 3 * (*c8in / 2);
+    }
     if (*kblocks && (*c8in % 4)) return fail(SRB_ENOSUP, "srb_pack_conv: cin=%d must be a multiple of 32 above 64", cin);
     return SRB_OK;
 }
 
 extern "C" int srb_alloc_conv(srb_ctx* ctx, int cout, int cin, int k, int dtype, srb_weights** out) {
+    return srb_alloc_conv_ex(ctx, cout, cin, k, dtype, 0, out);
+}
+
+extern "C" int srb_alloc_conv_ex(srb_ctx* ctx, int cout, int cin, int k, int dtype, int weight_streaming, srb_weights** out) {
     if (!ctx || !out) return fail(SRB_EINVAL, "srb_alloc_conv: NULL argument");
     if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_alloc_conv: dtype %d", dtype);
     int mode, c8in, nout, ksteps, kblocks;
-    if (int rc = conv_geometry(cout, cin, k, &mode, &c8in, &nout, &ksteps, &kblocks)) return rc;
+    if (int rc = conv_geometry(cout, cin, k, &mode, &c8in, &nout, &ksteps, &kblocks, weight_streaming != 0, weight_streaming == 2)) return rc;
     srb_weights* sw = new srb_weights();
     sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
     sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
-    sw->pack_bytes = (size_t)ksteps * 2 * nout * 8 * 2;
+    sw->nmma = mode == MODE_DYF ? 3 * nout : nout;
+    sw->pack_bytes = (size_t)ksteps * 2 * sw->nmma * 8 * 2;
     DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
         srb_free_weights(sw);
@@ -247,7 +259,7 @@ extern "C" int srb_pack_conv_device(srb_ctx* ctx, srb_weights* w, const float* w
         return fail(SRB_EINVAL, "srb_pack_conv_device: slice (%d+%d, %d+%d) exceeds the source filter [%d][%d]", o_off, w->cout,
                     c_off, w->cin, src_o, src_i);
     PackParams pp;
-    pp.mode = w->mode; pp.c8in = w->c8in; pp.nout = w->nout; pp.kblocks = w->kblocks; pp.cout = w->cout; pp.cin = w->cin;
+    pp.mode = w->mode; pp.c8in = w->c8in; pp.nout = w->nout; pp.nmma = w->nmma; pp.kblocks = w->kblocks; pp.cout = w->cout; pp.cin = w->cin;
     pp.k = w->k; pp.src_i = src_i; pp.o_off = o_off; pp.c_off = c_off; pp.transpose = transpose;
     pp.c_lo = 0; pp.c_n = 0; pp.scale = 1.f;
     pp.total = w->pack_bytes / 2;
@@ -312,7 +324,7 @@ extern "C" int srb_pack_conv(srb_ctx* ctx, const float* w, const float* bias, co
 
     srb_weights* sw = new srb_weights();
     sw->cout = cout; sw->cin = cin; sw->k = k; sw->dtype = dtype;
-    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
+    sw->mode = mode; sw->c8in = c8in; sw->nout = nout; sw->nmma = nout; sw->ksteps = ksteps; sw->kblocks = kblocks;
     sw->pack_bytes = pack.size() * 2;
     DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
@@ -342,7 +354,7 @@ extern "C" int srb_pack_conv_pair4(srb_ctx* ctx, const float* w, const float* bi
         }
     srb_weights* sw = new srb_weights();
     sw->cout = cout; sw->cin = 3; sw->k = 9; sw->dtype = dtype;
-    sw->mode = MODE_PAIR4; sw->c8in = 1; sw->nout = nout; sw->ksteps = ksteps; sw->kblocks = 0;
+    sw->mode = MODE_PAIR4; sw->c8in = 1; sw->nout = nout; sw->nmma = nout; sw->ksteps = ksteps; sw->kblocks = 0;
     sw->pack_bytes = pack.size() * 2;
     DeviceGuard dev_guard(ctx->device);
     if (cudaMalloc(&sw->d_pack, sw->pack_bytes) != cudaSuccess || cudaMalloc(&sw->d_bias, nout * sizeof(float)) != cudaSuccess) {
@@ -476,7 +488,7 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
         if (!a->mask || ((uintptr_t)a->mask & 15)) return fail(SRB_EINVAL, "srb_conv2d: SRB_F_MASK needs a 16-byte aligned mask buffer");
         if (a->mask_p0 < 0 || a->mask_p1 < a->mask_p0 || a->mask_c8_off + a->mask_p1 > a->mask_c8_total)
             return fail(SRB_EINVAL, "srb_conv2d: mask plane range out of bounds");
-        if (w->mode != MODE_STD || (flags & SRB_F_PIXSHUF2)) return fail(SRB_ENOSUP, "srb_conv2d: SRB_F_MASK is a 3x3 / head-conv epilogue");
+        if ((w->mode != MODE_STD && w->mode != MODE_DYF) || (flags & SRB_F_PIXSHUF2)) return fail(SRB_ENOSUP, "srb_conv2d: SRB_F_MASK is a 3x3 conv epilogue");
     }
     const bool partial_res = a->res_nplanes > 0 && a->res_nplanes < (w->cout + 7) / 8;
     cudaStream_t st = (cudaStream_t)stream;
@@ -501,6 +513,15 @@ extern "C" int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_
     if (w->mode == MODE_PAIRDX) {
         if (w->nout == 64) return launch_conv<1, 64, 9, 9, MODE_PAIRDX, 4>(ctx, w, x, x_c8_total, p, st);
         return fail(SRB_ENOSUP, "srb_conv2d_fwd: head conv with cout=%d", w->cout);
+    }
+    if (w->mode == MODE_DYF) {      // dy-folded weight-streaming 3x3 conv with 32 outputs, launched on its own (normally a chain layer)
+        if ((flags & SRB_F_RESIDUAL) || (flags & SRB_F_PIXSHUF2)) return fail(SRB_ENOSUP, "srb_conv2d: dy-folded convs carry no residual / PixelShuffle");
+        const long long mt = (long long)((W + 7) / 8) * ((H + 13) / 14) * N;
+        const bool sm_ = mt < (long long)ctx->num_sms * 6 && !(ctx->path & SRB_PATH_LARGE_TILING);
+        const bool bw = (flags & SRB_F_MASK) != 0;
+        if (bw) return sm_ ? launch_conv<4, 32, 3, 3, MODE_DYF, 2, false, true, true>(ctx, w, x, x_c8_total, p, st)
+                           : launch_conv<4, 32, 3, 3, MODE_DYF, 2, false, true, true>(ctx, w, x, x_c8_total, p, st);
+        return launch_conv<4, 32, 3, 3, MODE_DYF, 2, false, true, false>(ctx, w, x, x_c8_total, p, st);
     }
     // the TMA residual ring needs the residual on every output plane of a full-width (cout == NOUT) conv
     // Small problems (a training batch: 16 x 64 x 64 px = 512 M-tiles for 148 SMs): with NT = 4 a CTA gets ONE super-tile and
@@ -1342,7 +1363,7 @@ extern "C" int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int
         const srb_pack_job& q = jobs[j];
         srb_weights* w = q.w;
         if (!w || !q.w_src) return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: NULL", j);
-        if (q.c_n < 0 || q.c_lo < 0 || (q.c_n > 0 && (q.c_lo + q.c_n > w->cin || w->mode != MODE_STD)))
+        if (q.c_n < 0 || q.c_lo < 0 || (q.c_n > 0 && (q.c_lo + q.c_n > w->cin || (w->mode != MODE_STD && w->mode != MODE_DYF))))
             return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: channel range [%d, +%d) of a %d-channel 3x3 operand", j, q.c_lo, q.c_n, w->cin);
         const int ncin = q.c_n > 0 ? q.c_n : w->cin;
         const int so_need = q.transpose ? q.c_off + ncin : q.o_off + w->cout;
@@ -1350,7 +1371,7 @@ extern "C" int srb_pack_batch_create(srb_ctx* ctx, const srb_pack_job* jobs, int
         if (q.o_off < 0 || q.c_off < 0 || so_need > q.src_o || si_need > q.src_i)
             return fail(SRB_EINVAL, "srb_pack_batch_create: job %d: slice exceeds the source filter", j);
         PackJob& pj = v[j];
-        pj.p.mode = w->mode; pj.p.c8in = w->c8in; pj.p.nout = w->nout; pj.p.kblocks = w->kblocks; pj.p.cout = w->cout;
+        pj.p.mode = w->mode; pj.p.c8in = w->c8in; pj.p.nout = w->nout; pj.p.nmma = w->nmma; pj.p.kblocks = w->kblocks; pj.p.cout = w->cout;
         pj.p.cin = w->cin; pj.p.k = w->k; pj.p.src_i = q.src_i; pj.p.o_off = q.o_off; pj.p.c_off = q.c_off;
         pj.p.transpose = q.transpose; pj.p.total = w->pack_bytes / 2;
         pj.p.c_lo = q.c_lo; pj.p.c_n = q.c_n; pj.p.scale = q.scale == 0.f ? 1.f : q.scale;
@@ -1879,4 +1900,123 @@ extern "C" int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_
                                    static_cast<const uint8_t*>(src) + (size_t)p * src_plane, src_pitch, width, height, k,
                                    (cudaStream_t)stream));
     return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv chains: the weight-streaming 3x3 convs (Cout = 32) of one dense block — RDB.forward conv1 .. conv3, the gathered
+// data-gradient stages of its backward — as ONE launch of persistent CTAs with tile-level dependencies (srb_conv.cuh: CHAIN)
+// ------------------------------------------------------------------------------------------
+struct srb_conv_chain {
+    int n = 0, dtype = 0, grid = 0, num_tiles = 0;
+    bool small = false, bwd = false, fold = false;
+    ConvParams* d_layers = nullptr;
+    CUtensorMap* d_tmaps = nullptr;
+    unsigned int* d_flags = nullptr;      // [n][num_tiles] + epoch + ticket
+};
+
+extern "C" void srb_conv_chain_destroy(srb_conv_chain* c) {
+    if (!c) return;
+    if (c->d_layers) cudaFree(c->d_layers);
+    if (c->d_tmaps) cudaFree(c->d_tmaps);
+    if (c->d_flags) cudaFree(c->d_flags);
+    delete c;
+}
+
+extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* const* ws, const srb_conv_args* args, srb_conv_chain** out) {
+    if (!ctx || !ws || !args || !out) return fail(SRB_EINVAL, "srb_conv_chain_create: NULL argument");
+    if (n < 1 || n > CHAIN_MAX_LAYERS) return fail(SRB_EINVAL, "srb_conv_chain_create: %d layers (1 .. %d)", n, CHAIN_MAX_LAYERS);
+    const int N = args[0].N, H = args[0].H, W = args[0].W;
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_conv_chain_create: empty shape");
+    const long long mtiles = (long long)((W + 7) / 8) * ((H + 15) / 16) * N;
+    const bool fold = ws[0] && ws[0]->mode == MODE_DYF;
+    const bool small = fold || (mtiles < (long long)ctx->num_sms * 6 && !(ctx->path & SRB_PATH_LARGE_TILING));   // (dy-folded: NT = 2 only)
+    const int NT = small ? 2 : 4, SUPER_W = 8 * NT, SUPER_H = fold ? 14 : 16, HALO_W = SUPER_W + 2, HALO_H = SUPER_H + 2;
+    std::vector<ConvParams> lay(n);
+    std::vector<CUtensorMap> tms(n);
+    bool bwd = false;
+    for (int l = 0; l < n; ++l) {
+        const srb_weights* w = ws[l];
+        const srb_conv_args& a = args[l];
+        if (!w || !a.x || !a.y) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: NULL", l);
+        if ((w->mode != MODE_STD && w->mode != MODE_DYF) || w->mode != ws[0]->mode || !w->kblocks || w->nout != 32 || w->dtype != ws[0]->dtype)
+            return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: chains hold weight-streaming 3x3 convs with 32 outputs (cin=%d cout=%d)", l, w->cin, w->cout);
+        if (a.N != N || a.H != H || a.W != W) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: all layers share one shape", l);
+        if (((uintptr_t)a.x & 15) || ((uintptr_t)a.y & 15) || ((uintptr_t)a.mask & 15)) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: alignment", l);
+        if (a.flags & ~(SRB_F_LRELU | SRB_F_MASK)) return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: flags 0x%x (LRELU / MASK only)", l, a.flags);
+        if (a.x_c8_off < 0 || a.x_c8_off + w->c8in > a.x_c8_total || a.y_c8_off < 0 || a.y_c8_off + 4 > a.y_c8_total)
+            return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: plane slice out of range", l);
+        if ((a.flags & SRB_F_MASK) && (!a.mask || a.mask_p0 < 0 || a.mask_p1 < a.mask_p0 || a.mask_c8_off + a.mask_p1 > a.mask_c8_total))
+            return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: mask", l);
+        bwd = bwd || (a.flags & SRB_F_MASK);
+        ConvParams& p = lay[l];
+        memset(&p, 0, sizeof(p));
+        p.N = N; p.H = H; p.W = W;
+        p.tiles_x = (W + SUPER_W - 1) / SUPER_W; p.tiles_y = (H + SUPER_H - 1) / SUPER_H;
+        const long long nt = (long long)p.tiles_x * p.tiles_y * N;
+        if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_conv_chain_create: %lld tiles", nt);
+        p.num_tiles = (int)nt;
+        p.x_c8_off = a.x_c8_off; p.wpack = w->d_pack; p.bias = w->d_bias;
+        p.y = a.y; p.y_c8_total = a.y_c8_total; p.y_c8_off = a.y_c8_off;
+        p.res_scale = a.res_scale; p.out_scale = a.out_scale; p.slope = a.lrelu_slope;
+        p.res_nplanes = 1 << 30;
+        p.mask = a.mask; p.mask_c8_total = a.mask_c8_total; p.mask_c8_off = a.mask_c8_off;
+        p.mask_p0 = a.mask_p0; p.mask_p1 = a.mask_p1; p.mask_slope = a.mask_slope;
+        p.kblocks = w->kblocks; p.flags = a.flags; p.cout = w->cout;
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, (cuuint64_t)a.x_c8_total, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * a.x_c8_total};
+        cuuint32_t box[4] = {(cuuint32_t)HALO_W * 4, (cuuint32_t)HALO_H, 4, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = ctx->encode(&tms[l], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(a.x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "srb_conv_chain_create: cuTensorMapEncodeTiled failed: %d", (int)r);
+    }
+    srb_conv_chain* c = new srb_conv_chain();
+    c->n = n; c->dtype = ws[0]->dtype; c->num_tiles = lay[0].num_tiles; c->small = small; c->bwd = bwd; c->fold = fold;
+    c->grid = c->num_tiles < ctx->num_sms ? c->num_tiles : ctx->num_sms;       // every CTA resident: the tile-level waits rely on it
+    DeviceGuard dev_guard(ctx->device);
+    const size_t fl = ((size_t)n * c->num_tiles + 2) * sizeof(unsigned int);
+    if (cudaMalloc(&c->d_layers, n * sizeof(ConvParams)) != cudaSuccess || cudaMalloc(&c->d_tmaps, n * sizeof(CUtensorMap)) != cudaSuccess ||
+        cudaMalloc(&c->d_flags, fl) != cudaSuccess) { srb_conv_chain_destroy(c); return fail(SRB_ENOMEM, "srb_conv_chain_create: cudaMalloc failed"); }
+    CUDA_TRY(cudaMemcpy(c->d_layers, lay.data(), n * sizeof(ConvParams), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(c->d_tmaps, tms.data(), n * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemset(c->d_flags, 0, fl));
+    *out = c;
+    return SRB_OK;
+}
+
+template <int MODE, int NT, bool BF16, bool BWD>
+static int launch_chain(srb_ctx* ctx, const srb_conv_chain* c, cudaStream_t st) {
+    constexpr int KACC = (MODE == MODE_STD && NT == 2) ? 2 : 1;      // small-problem super-tiles: two accumulators per M-tile
+    using G = ConvGeom<4, 32, 3, 3, MODE, NT, false, true, KACC>;
+    ChainCtl cc{};
+    cc.layers = c->d_layers; cc.tmaps = c->d_tmaps; cc.nlayers = c->n;
+    cc.flags = c->d_flags; cc.epoch = c->d_flags + (size_t)c->n * c->num_tiles; cc.ticket = cc.epoch + 1;
+    auto kern = conv_chain_kernel<4, 32, MODE, NT, BF16, BWD, KACC>;
+    const int smem = G::SMEM_BYTES + (MODE == MODE_DYF ? 0 : CHAIN_SMEM_EXTRA);      // (the dy-folded geometry already holds the chain area)
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(c->grid); cfg.blockDim = dim3(CONV_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->pdl || ctx->pdl_all) ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, cc));
+    return SRB_OK;
+}
+
+extern "C" int srb_conv_chain_run(srb_ctx* ctx, srb_conv_chain* c, srb_stream_t stream) {
+    if (!ctx || !c) return fail(SRB_EINVAL, "srb_conv_chain_run: NULL argument");
+    if (c->grid > ctx->num_sms) return fail(SRB_EINVAL, "srb_conv_chain_run: grid %d exceeds the device's %d SMs", c->grid, ctx->num_sms);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool bf = c->dtype == SRB_DT_BF16;
+#ifdef SRB_DEBUG
+    for (int l = 0; l < c->n; ++l)      // probe build: the clock trace of CTA 0 (srb_debug_trace) follows the chain through its layers
+        CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(c->d_layers + l) + offsetof(ConvParams, dbg_trace), &ctx->dbg_trace, sizeof(long long*),
+                                 cudaMemcpyHostToDevice, st));
+#endif
+#define SRB_CH(MD, NTV) { if (c->bwd) return bf ? launch_chain<MD, NTV, true, true>(ctx, c, st) : launch_chain<MD, NTV, false, true>(ctx, c, st); \
+                          return bf ? launch_chain<MD, NTV, true, false>(ctx, c, st) : launch_chain<MD, NTV, false, false>(ctx, c, st); }
+    if (c->fold) SRB_CH(MODE_DYF, 2) else if (c->small) SRB_CH(MODE_STD, 2) else SRB_CH(MODE_STD, 4)
+#undef SRB_CH
 }

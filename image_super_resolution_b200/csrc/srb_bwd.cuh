@@ -12,7 +12,7 @@ namespace srb {
 // packed UMMA B operand from fp32 OIHW weights on the device (same element order as srb_pack_conv)
 // ------------------------------------------------------------------------------------------
 struct PackParams {
-    int mode, c8in, nout, kblocks, cout, cin, k;
+    int mode, c8in, nout, nmma, kblocks, cout, cin, k;   // nmma: B rows per K granule (3 * nout for the dy-folded operands)
     int src_i, o_off, c_off, transpose;
     int c_lo, c_n;  // c_n > 0: this job fills only the packed input channels [c_lo, c_lo + c_n) (source channel = c - c_lo + c_off):
                     // an operand whose input channels are gathered from several source filters (one job per source)
@@ -25,15 +25,21 @@ __device__ __forceinline__ void pack_conv_element(const float* __restrict__ w, u
                                                   const float* __restrict__ bias_src, float* __restrict__ bias_dst, size_t e) {
     if (e < (size_t)p.nout) bias_dst[e] = (bias_src != nullptr && (int)e < p.cout) ? bias_src[p.o_off + e] : 0.f;
     if (e >= p.total) return;
-    const int step = 2 * p.nout * 8;
+    const int step = 2 * p.nmma * 8;
     const int ks = (int)(e / step);
     int rem = (int)(e - (size_t)ks * step);
-    const int g = rem / (p.nout * 8);
-    rem -= g * p.nout * 8;
+    const int g = rem / (p.nmma * 8);
+    rem -= g * p.nmma * 8;
     const int n = rem >> 3, j = rem & 7;
     int o = n, c = 0, dy = 0, dx = 0;
     bool valid = true;
-    if (p.mode == 0) {   // MODE_STD
+    if (p.mode == 4) {   // MODE_DYF (weight streaming): K-steps [K block of 32 channels][dx][channel pair], B row = dy * nout + co
+        const int c2 = ks & 1; const int t = ks >> 1;
+        dx = t % 3; const int kb = t / 3;
+        dy = n / p.nout; o = n - dy * p.nout;
+        c = (kb * 4 + 2 * c2 + g) * 8 + j;
+        valid = o < p.cout;
+    } else if (p.mode == 0) {   // MODE_STD
         if (p.kblocks) {   // [K block of 32 channels][dy][dx][2 K-steps]
             const int c2 = ks & 1; int t = ks >> 1;
             dx = t % 3; t /= 3; dy = t % 3; const int kb = t / 3;

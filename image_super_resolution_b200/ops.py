@@ -166,11 +166,13 @@ def bias_grad(dy: torch.Tensor, dy_planes: int, dy_off: int, cout: int, db: torc
 class DeviceConv:
     """Packed operand of a (cout, cin, k) conv that is (re)filled on the device from fp32 master weights."""
 
-    def __init__(self, ctx: Context, cout: int, cin: int, k: int, dtype):
+    def __init__(self, ctx: Context, cout: int, cin: int, k: int, dtype, ws: int = 0):
+        """ws = 1: weight-streaming layout also for cin = 64 (the conv can then be a layer of a ConvChain);
+        ws = 2: ... with the dy taps folded into N (MODE_DYF: one N = 96 MMA per three taps; 32 outputs)."""
         self.ctx, self.cout, self.cin, self.k = ctx, cout, cin, k
         self.dtype = dtype_code(dtype)
         h = C.c_void_p()
-        check(lib().srb_alloc_conv(ctx.handle, cout, cin, k, self.dtype, C.byref(h)), "srb_alloc_conv")
+        check(lib().srb_alloc_conv_ex(ctx.handle, cout, cin, k, self.dtype, int(ws), C.byref(h)), "srb_alloc_conv_ex")
         self.handle = h
 
     def fill(self, weight: torch.Tensor, bias: torch.Tensor | None = None, o_off: int = 0, c_off: int = 0,
@@ -207,6 +209,48 @@ def conv2d_ex(pc, x, x_planes, x_off, y, y_planes, y_off, N, H, W, residual=None
         a.mask_p0, a.mask_p1, a.mask_slope = mask_p0, mask_p1, mask_slope
     a.flags, a.N, a.H, a.W = flags, N, H, W
     check(lib().srb_conv2d_ex(pc.ctx.handle, pc.handle, C.byref(a), _stream_ptr(x.device)), "srb_conv2d_ex")
+
+
+def conv_args(x, x_planes, x_off, y, y_planes, y_off, N, H, W, slope=0.0, flags=0, out_scale=1.0,
+              mask=None, mask_planes=0, mask_off=0, mask_p0=0, mask_p1=0, mask_slope=0.0) -> "_lib.ConvArgs":
+    """srb_conv_args of a layer without residual (the layers of a ConvChain)."""
+    a = _lib.ConvArgs()
+    a.x, a.x_c8_total, a.x_c8_off = x.data_ptr(), x_planes, x_off
+    a.y, a.y_c8_total, a.y_c8_off = y.data_ptr(), y_planes, y_off
+    a.res_scale, a.out_scale, a.lrelu_slope = 1.0, out_scale, slope
+    if mask is not None:
+        flags |= _lib.F_MASK
+        a.mask, a.mask_c8_total, a.mask_c8_off = mask.data_ptr(), mask_planes, mask_off
+        a.mask_p0, a.mask_p1, a.mask_slope = mask_p0, mask_p1, mask_slope
+    a.flags, a.N, a.H, a.W = flags, N, H, W
+    return a
+
+
+class ConvChain:
+    """Up to four weight-streaming 3x3 convs (32 outputs each) of one dense block as ONE launch (srb_conv_chain_*):
+    layers = [(packed conv, ConvArgs)]; the tensors named by the arguments must outlive the chain."""
+
+    def __init__(self, ctx: Context, layers: list, keep=()):
+        self.ctx, self._keep = ctx, (layers, keep)
+        n = len(layers)
+        wp = (C.c_void_p * n)(*[pc.handle for pc, _ in layers])
+        arr = (_lib.ConvArgs * n)()
+        for i, (_, a) in enumerate(layers):
+            C.memmove(C.byref(arr[i]), C.byref(a), C.sizeof(_lib.ConvArgs))
+        h = C.c_void_p()
+        check(lib().srb_conv_chain_create(ctx.handle, n, wp, C.cast(arr, C.c_void_p), C.byref(h)), "srb_conv_chain_create")
+        self.handle = h
+
+    def run(self, device):
+        check(lib().srb_conv_chain_run(self.ctx.handle, self.handle, _stream_ptr(device)), "srb_conv_chain_run")
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_conv_chain_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
 
 
 def conv9_wgrad(x, x_planes, x_off, cin, dy, dy_planes, dy_off, cout, dw, N, H, W, scale=1.0):

@@ -57,15 +57,19 @@ class TrainPlan:
         self.ctx = Context.get(device.index)
         self.allreduce = allreduce
         mk = lambda co, ci, k: ops.DeviceConv(self.ctx, co, ci, k, self.dt)  # noqa: E731
+        # 1: nine-tap kernels (default: 8.73 ms per step at B = 16 x 64 x 64); 2: dy taps folded into N (csrc/srb_conv.cuh MODE_DYF: 9.12 ms —
+        # fewer, larger MMAs but 14-row tiles and a heavier epilogue; ahead only on large frames). profiles/chain_variants_r2.log
+        fold = int(getattr(net, "train_conv_fold", 1))
+        mkw = lambda co, ci, k: ops.DeviceConv(self.ctx, co, ci, k, self.dt, ws=fold)  # noqa: E731  (layers of a ConvChain)
         with torch.cuda.device(device):
             self.f_conv0 = mk(64, 3, 9)
             self.rdbs = []
             for rrdb in net.residual:
                 for rdb in rrdb.net:
-                    fwd = [mk(32, 64 + 32 * i, 3) for i in range(4)] + [mk(64, 192, 3)]
+                    fwd = [mkw(32, 64 + 32 * i, 3) for i in range(4)] + [mk(64, 192, 3)]
                     # data gradients, gathered: stage k = ONE conv over the concatenated output gradients of all later convs
                     # [dY4 (64) | dY3 | .. | dY_{k+1}] -> the 32 channels of o_k; fin = all five -> the 64 input channels
-                    stage = [mk(32, 64 + 32 * (3 - k), 3) for k in range(4)]
+                    stage = [mkw(32, 64 + 32 * (3 - k), 3) for k in range(4)]
                     fin = mk(64, 192, 3)
                     self.rdbs.append((rrdb, rdb, fwd, stage, fin))
             self.f_conv1, self.d_conv1 = mk(64, 64, 3), mk(64, 64, 3)
@@ -85,6 +89,11 @@ class TrainPlan:
         self.saved = None
         self.use_graphs = True
         self.use_pdl = True          # programmatic edges between the conv nodes of the captured graphs
+        # conv0 .. conv3 of an RDB (and the four gathered data-gradient stages of its backward) as ONE launch each: persistent
+        # CTAs with tile-level dependencies instead of four launches (ops.ConvChain; csrc/srb_conv.cuh CHAIN)
+        self.use_chains = True
+        self.fchains, self.bchains, self.chain_key = None, None, None
+        self.chain_nt4 = bool(getattr(net, "train_chain_nt4", False))    # super-tiles of four M-tiles in the chains even for small batches
         self.wgrad_splitk = 1
         # Internal gradient shift: the data-gradient chain runs on 16-bit tensors whose magnitudes span the tail conv (~1 with
         # GradScaler's 65536) down to the dense blocks of a x4 net at initialisation (~4e-5: fp16 subnormals).  The chain is
@@ -156,6 +165,15 @@ class TrainPlan:
         self.pack_batch.run(self.device)
         if track_versions:             # (eager mode re-packs only when a parameter changed; graph mode re-packs every forward)
             self.versions = self._versions()
+
+    def _mk_chain(self, layers, keep=()):
+        if self.chain_nt4:
+            self.ctx.set_option(_lib.OPT_PATH, _lib.PATH_LARGE_TILING)
+        try:
+            return ops.ConvChain(self.ctx, layers, keep=keep)
+        finally:
+            if self.chain_nt4:
+                self.ctx.set_option(_lib.OPT_PATH, 0)
 
     def _b(self, name, N, planes, H, W):
         key = (name, N, planes, H, W)
@@ -250,12 +268,22 @@ class TrainPlan:
         tr = self._b("tr", N, 8, H, W)
         s0 = _slope_of(n.conv0.act)
         cv(self.f_conv0, xin, 1, 0, dense[0], 24, 0, N, H, W, slope=s0, flags=ops.F_LRELU)     # x0 = planes 0..7 of dense[0]
+        if self.use_chains and self.chain_key != (N, H, W):
+            self.fchains, self.bchains, self.chain_key = [], None, (N, H, W)
+            for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
+                D = dense[r]
+                self.fchains.append(self._mk_chain([
+                    (fwd[i], ops.conv_args(D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=_slope_of(getattr(rdb, f"conv{i}").act),
+                                           flags=ops.F_LRELU)) for i in range(4)], keep=(D,)))
         for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
             D = dense[r]
             dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
-            for i in range(4):
-                si = _slope_of(getattr(rdb, f"conv{i}").act)
-                cv(fwd[i], D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=si, flags=ops.F_LRELU)
+            if self.use_chains:
+                self.fchains[r].run(self.device)
+            else:
+                for i in range(4):
+                    si = _slope_of(getattr(rdb, f"conv{i}").act)
+                    cv(fwd[i], D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=si, flags=ops.F_LRELU)
             a = float(rdb.add_rate)
             if r % 3 < 2:    # add_rate*conv + rdb_in  (utils/models.py:271)
                 cv(fwd[4], D, 24, 0, dst, dplanes, 0, N, H, W, residual=D, res_planes=24, res_off=0, res_scale=1.0, out_scale=a)
@@ -331,6 +359,15 @@ class TrainPlan:
         nr = len(self.rdbs)
         Gd = [self._b(f"G{j}", N, 24, H, W) for j in range(nr)]
         gxf = self._b("g_x0t", N, 8, H, W)                  # gradient of x0 through the trunk
+        if self.use_chains and self.bchains is None:
+            self.bchains = []
+            for r in range(nr):
+                rrdb, rdb, _, stage, _ = self.rdbs[r]
+                D, G = sv["dense"][r], Gd[r]
+                self.bchains.append(self._mk_chain([
+                    (stage[k], ops.conv_args(G, 24, 0, G, 24, 8 + 4 * (3 - k), N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k,
+                                             mask_p0=0, mask_p1=4, mask_slope=_slope_of(getattr(rdb, f"conv{k}").act)))
+                    for k in range(3, -1, -1)], keep=(D, G)))
         cv(self.d_conv1, g_t, 8, 0, Gd[nr - 1], 24, 0, N, H, W)
         for r in range(nr - 1, -1, -1):
             rrdb, rdb, _, stage, fin = self.rdbs[r]
@@ -340,10 +377,13 @@ class TrainPlan:
             s_out, s_res = (a * R, R) if d == 2 else (a, 1.0)          # utils/models.py:271 / :317
             sl = [_slope_of(getattr(rdb, f"conv{i}").act) for i in range(4)]
             self._wb(rdb.conv, D, 24, 0, 192, G, 24, 0, 64, N, H, W, scale=s_out)
+            if self.use_chains:
+                self.bchains[r].run(self.device)
             for k in range(3, -1, -1):
                 nin = 8 + 4 * (3 - k)                                   # gy + dY3 .. dY_{k+1}
-                cv(stage[k], G, 24, 0, G, 24, nin, N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k, mask_p0=0, mask_p1=4,
-                   mask_slope=sl[k])
+                if not self.use_chains:
+                    cv(stage[k], G, 24, 0, G, 24, nin, N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k, mask_p0=0, mask_p1=4,
+                       mask_slope=sl[k])
                 self._wb(getattr(rdb, f"conv{k}"), D, 24, 0, 64 + 32 * k, G, 24, nin, 32, N, H, W)
             dst, dplanes = (Gd[r - 1], 24) if r > 0 else (gxf, 8)
             kw = dict(residual=G, res_planes=24, res_off=0, res_scale=s_res)

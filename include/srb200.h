@@ -115,6 +115,19 @@ typedef struct srb_conv_args {
 } srb_conv_args;
 int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_args* args, srb_stream_t stream);
 
+/* Conv chain: up to 4 weight-streaming 3x3 convs with 32 outputs each that feed one another through one dense buffer — conv1 ..
+ * conv3 of RDB.forward (utils/models.py:267-270: o_k = act(conv_k(cat[x, o_0 .. o_{k-1}]))) or the gathered data-gradient
+ * stages of its backward (train.py:57) — as ONE launch: persistent CTAs run the layers back to back and a tile of layer l
+ * waits only for the 3 x 3 neighbourhood of tiles of layer l-1 (arrival counters in device memory owned by the chain).
+ * args[l]: the srb_conv2d_ex arguments of layer l (same N, H, W; flags SRB_F_LRELU and / or SRB_F_MASK; no residual).
+ * The buffers and packed weights named at creation must keep their addresses while the chain lives; the weights' CONTENTS
+ * may be re-packed between runs.  Same results as the layers launched one by one with srb_conv2d_ex (bit-identical). */
+typedef struct srb_conv_chain srb_conv_chain;
+struct srb_conv_args;
+int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* const* weights, const struct srb_conv_args* args, srb_conv_chain** out);
+int srb_conv_chain_run(srb_ctx* ctx, srb_conv_chain* chain, srb_stream_t stream);
+void srb_conv_chain_destroy(srb_conv_chain* chain);
+
 /* Training keeps fp32 master weights on the DEVICE (nn.Parameter storage); these re-derive the packed 16-bit
  * operand from them every step without a host round trip.  srb_alloc_conv creates an empty packed filter for a
  * (cout, cin, k) conv; srb_pack_conv_device fills it from w_src = fp32 [src_o][src_i][k][k] on the device:
@@ -122,6 +135,9 @@ int srb_conv2d_ex(srb_ctx* ctx, const srb_weights* w, const srb_conv_args* args,
  *   transpose = 1:  W'[o][c][dy][dx] = w_src[c_off + c][o_off + o][k-1-dy][k-1-dx]   (data-gradient operand)
  * bias_src (device, may be NULL -> zero bias) is read at [o_off + o] when transpose = 0 and ignored otherwise. */
 int srb_alloc_conv(srb_ctx* ctx, int cout, int cin, int k, int dtype, srb_weights** out);
+/* weight_streaming != 0: a 3x3 filter with cin = 64 is laid out in 32-channel K blocks like the wider ones (streamed with the
+ * halo tiles instead of resident in shared memory), which lets the conv join a srb_conv_chain. */
+int srb_alloc_conv_ex(srb_ctx* ctx, int cout, int cin, int k, int dtype, int weight_streaming, srb_weights** out);
 int srb_pack_conv_device(srb_ctx* ctx, srb_weights* w, const float* w_src, int src_o, int src_i, int o_off, int c_off,
                          int transpose, const float* bias_src, srb_stream_t stream);
 

@@ -300,3 +300,80 @@ def test_batched_gradients_match_single_launches(ctx, dev):
         for j, (rw, rb) in zip(jobs, refs):
             assert (j["dw"] - rw).abs().max().item() <= 1e-3 * rw.abs().max().item() + 1e-4
             assert (j["db"] - rb).abs().max().item() <= 1e-3 * rb.abs().max().item() + 1e-4
+
+
+@pytest.mark.parametrize("cin", [64, 96, 160])
+def test_dy_folded_conv_matches_nine_tap_conv(ctx, dev, cin):
+    """MODE_DYF (dy taps folded into N = 96, rows recombined in the epilogue) against fp32 conv of the same bf16-rounded
+    operands and against the nine-tap weight-streaming kernel, forward epilogue (LeakyReLU) and backward epilogue (mask), at a
+    ragged shape with several 14-row tiles per image."""
+    from image_super_resolution_b200 import ops
+    g = torch.Generator().manual_seed(cin)
+    N, H, W = 2, 45, 52
+    w = _q(torch.randn(32, cin, 3, 3, generator=g) / np.sqrt(cin * 9))
+    b = torch.randn(32, generator=g) * 0.1
+    x = _q(torch.randn(N, cin, H, W, generator=g))
+    act = _q(torch.randn(N, 32, H, W, generator=g))
+    ref = F.leaky_relu(F.conv2d(x, w, b, padding=1), 0.01)
+    ref_m = F.conv2d(x, w, None, padding=1) * torch.where(act > 0, 1.0, 0.01)
+    xc = ops.nchw_to_c8(x.to(dev), dtype="bf16")
+    A = ops.nchw_to_c8(act.to(dev), dtype="bf16")
+    outs = {}
+    for ws in (1, 2):
+        pk = ops.DeviceConv(ctx, 32, cin, 3, "bf16", ws=ws)
+        pk.fill(w.to(dev), b.to(dev))
+        y = torch.zeros(N, 4, H, W, 8, dtype=torch.bfloat16, device=dev)
+        ops.conv2d_ex(pk, xc, cin // 8, 0, y, 4, 0, N, H, W, slope=0.01, flags=ops.F_LRELU)
+        pk0 = ops.DeviceConv(ctx, 32, cin, 3, "bf16", ws=ws)
+        pk0.fill(w.to(dev))
+        ym = torch.zeros(N, 4, H, W, 8, dtype=torch.bfloat16, device=dev)
+        ops.conv2d_ex(pk0, xc, cin // 8, 0, ym, 4, 0, N, H, W, mask=A, mask_planes=4, mask_off=0, mask_p0=0, mask_p1=4, mask_slope=0.01)
+        outs[ws] = (ops.c8_to_nchw(y, 32).cpu(), ops.c8_to_nchw(ym, 32).cpu())
+    torch.cuda.synchronize()
+    for got, want in ((outs[2][0], ref), (outs[2][1], ref_m)):
+        err = (got - want).abs().max().item()
+        assert err <= 8e-3 * want.abs().max().item() + 1e-3, err
+    assert (outs[2][0] - outs[1][0]).abs().max().item() <= 2e-2 * ref.abs().max().item()      # same math, other summation order
+
+
+def test_conv_chains_equal_layer_by_layer_launches(dev):
+    """ops.ConvChain (conv0 .. conv3 of an RDB and the four data-gradient stages of its backward as ONE launch each, tiles of a
+    layer waiting only for their 3 x 3 neighbourhood in the previous layer) gives bit-identical outputs and data gradients to
+    the same layers launched one by one — at a shape with several super-tiles per image and ragged edges, twice in a row
+    (the arrival counters are never reset: the second launch runs on the next epoch)."""
+    from image_super_resolution_b200 import models
+    from image_super_resolution_b200.training import L1Loss, TrainPlan
+    from oracle import nets_oracle as no
+    hr, lr = no.make_lr_hr(21, 3, 2 * 44, 2)              # LR 44 x 44: 3 x 3 super-tiles of 16 x 16 per image, ragged
+    hr, lr = hr.to(dev), lr.to(dev)
+    loss_fn = L1Loss().to(dev)
+    res = []
+    for chains in (True, False):
+        torch.manual_seed(100)
+        net = models.EResNet(2, 0.2, 2).to(dev).train()
+        outs = []
+        for rep in range(2):
+            for p in net.parameters():
+                p.grad = None
+            out = net(lr)
+            plan = net._train_plans[dev]
+            if rep == 0 and not chains:
+                assert plan.use_chains
+                plan.use_chains = False
+                plan.graphs = {}                              # re-capture without the chains
+                out = net(lr)
+            (loss_fn(out, hr) * 65536.0).backward()
+            torch.cuda.synchronize()
+            outs.append((out.detach().clone(), {n_: p_.grad.detach().clone() for n_, p_ in net.named_parameters()}))
+        assert torch.equal(outs[0][0], outs[1][0])
+        res.append(outs[1])
+    from image_super_resolution_b200._lib import Context
+    Context.get(0).check_device()
+    assert torch.equal(res[0][0], res[1][0]), "forward differs between chained and layer-by-layer launches"
+    # (the 9x9 head / tail weight and bias gradients finish through fp32 atomics: those to rounding, everything else bit for bit)
+    atomics = {"conv0.conv.weight", "conv0.conv.bias", "conv2.conv.weight", "conv2.conv.bias"}
+    for name, g in res[1][1].items():
+        if name in atomics:
+            assert (res[0][1][name] - g).abs().max().item() <= 1e-5 * g.abs().max().item() + 1e-9, name
+        else:
+            assert torch.equal(res[0][1][name], g), name

@@ -1,13 +1,11 @@
 #!/bin/bash
-# Build libsrb200.so variants with different fused-block ring sizes into build/v_<RH>_<RY>_<HSLOTS>_<XSTAGES>/ (sweeps on the GPU box).
-set -e
-cd "$(dirname "$0")/.."
-for v in "$@"; do
-  IFS=_ read rh ry hs xs <<< "$v"
-  mkdir -p build/v_$v
-  nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared \
-    -DRB_RH=$rh -DRB_RY=$ry -DRB_HSLOTS=$hs -DRB_XSTAGES=$xs ${EXTRA_DEFS} \
-    -o build/v_$v/libsrb200.so image_super_resolution_b200/csrc/srb200.cu &
+# Build kernel-variant libraries (compile-time knobs) side by side: image_super_resolution_b200/variants/lib_<name>.so
+# usage: tools/build_variants.sh name1:"-DRB_KSPLIT=0 -DRB_RH=4 ..." name2:"..."     (SRB200_LIB=... selects one at run time)
+cd "$(dirname "$0")/../image_super_resolution_b200" || exit 1
+mkdir -p variants
+for spec in "$@"; do
+    name="${spec%%:*}"; flags="${spec#*:}"
+    ( nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 $flags -Xcompiler -fPIC -shared -o variants/lib_$name.so csrc/srb200.cu 2>&1 | grep -v "^$" | sed "s/^/[$name] /" ) &
 done
 wait
-ls -la build/v_*/libsrb200.so
+ls -la variants/

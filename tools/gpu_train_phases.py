@@ -12,6 +12,8 @@ dev = torch.device("cuda:0")
 B = 16
 torch.manual_seed(100)
 net = models.EResNet(16, 0.2, 2).to(dev)
+for kv in sys.argv[2:]:                      # e.g. train_conv_fold=1 train_chain_nt4=1
+    k, v = kv.split("="); setattr(net, k, int(v))
 g = torch.Generator().manual_seed(100)
 hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
 lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
