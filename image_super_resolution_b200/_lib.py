@@ -57,6 +57,7 @@ SIGNATURES = {
     "srb_conv9_wgrad": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_tanh_bwd_to_c8": (_i, [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp]),
     "srb_pixunshuffle_mask": (_i, [_vp, _vp, _vp, _vp, _i, _f, _i, _i, _i, _i, _vp]),
+    "srb_pixshuffle_lrelu": (_i, [_vp, _vp, _vp, _i, _f, _i, _i, _i, _i, _vp]),
     "srb_c8_axpby_mask": (_i, [_vp, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "srb_grad_batch_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "srb_grad_batch_units": (_i, [_vp]),

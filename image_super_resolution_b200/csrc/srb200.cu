@@ -1183,6 +1183,19 @@ extern "C" int srb_pixunshuffle_mask(srb_ctx* ctx, const void* g_u, const void* 
     return SRB_OK;
 }
 
+extern "C" int srb_pixshuffle_lrelu(srb_ctx* ctx, const void* s_c8, void* u_c8, int c8_u, float slope, int dtype, int N, int H, int W,
+                                    srb_stream_t stream) {
+    if (!ctx || !s_c8 || !u_c8) return fail(SRB_EINVAL, "srb_pixshuffle_lrelu: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0 || c8_u <= 0) return fail(SRB_EINVAL, "srb_pixshuffle_lrelu: empty shape");
+    const size_t total = (size_t)N * c8_u * 4 * H * W;
+    const int grid = ew_grid(ctx, total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SRB_DT_BF16) pixshuffle_lrelu_kernel<true><<<grid, 256, 0, st>>>(s_c8, (uint4*)u_c8, c8_u, H, W, slope, total);
+    else pixshuffle_lrelu_kernel<false><<<grid, 256, 0, st>>>(s_c8, (uint4*)u_c8, c8_u, H, W, slope, total);
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
 extern "C" int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off, float alpha, const void* b,
                                  int b_c8_total, int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off,
                                  float slope, void* out, int out_c8_total, int out_c8_off, int planes, int dtype, int N, int H,

@@ -151,6 +151,32 @@ __global__ void pixunshuffle_mask_kernel(const void* __restrict__ gu, const void
     }
 }
 
+// bare nn.PixelShuffle(2) + LeakyReLU of the current Denoise generator (utils/models.py:685: residual_conv1), not preceded by a conv
+// whose store could carry it (the conv before it adds a residual first): u[n, c, 2y+i, 2x+j] = lrelu(s[n, 4c+2i+j, y, x]).
+// s: [N][4P][H][W][8], u: [N][P][2H][2W][8]; one thread per output granule.
+template <bool BF16>
+__global__ void pixshuffle_lrelu_kernel(const void* __restrict__ sbuf, uint4* __restrict__ u, int P, int H, int W, float slope, size_t total) {
+    const size_t HW = (size_t)H * W;
+    const int W2 = 2 * W, H2 = 2 * H;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int X = (int)(i % W2); size_t t = i / W2;
+        const int Y = (int)(t % H2); t /= H2;
+        const int k = (int)(t % P); const size_t n = t / P;
+        const int ij = 2 * (Y & 1) + (X & 1);
+        const size_t px = (size_t)(Y >> 1) * W + (X >> 1);
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int sc = 32 * k + 4 * q + ij;                        // source channel
+            const float a = ld16f<BF16>(sbuf, ((n * (4 * (size_t)P) + (sc >> 3)) * HW + px) * 8 + (sc & 7));
+            v[q] = a > 0.f ? a : a * slope;
+        }
+        uint4 o;
+        o.x = pk2<BF16>(v[0], v[1]); o.y = pk2<BF16>(v[2], v[3]); o.z = pk2<BF16>(v[4], v[5]); o.w = pk2<BF16>(v[6], v[7]);
+        u[i] = o;
+    }
+}
+
 // out = (alpha*a + beta*b) [* LeakyReLU'(act)] over C8 plane slices (gradient fan-in at the long skip, utils/models.py:647)
 template <bool BF16>
 __global__ void c8_axpby_mask_kernel(const uint4* __restrict__ a, int a_tot, int a_off, const uint4* __restrict__ b, int b_tot,

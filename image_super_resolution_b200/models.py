@@ -63,11 +63,22 @@ class ConvWithoutBN(nn.Module):
 
     def __init__(self, c1, c2, k=1, s=1, p=None, g=1, d=1, act=True, dropout=0.0):
         super().__init__()
-        if s != 1 or g != 1 or d != 1 or dropout != 0.0:
-            raise NotImplementedError("hot-path convs are stride 1, groups 1, dilation 1, dropout 0 (SURVEY a8)")
+        # stride 2 only as Denoise's down-sampling 3x3 conv (utils/models.py:680), run as a stride-1 conv over the
+        # space-to-depth input (_DenoisePlan)
+        if s not in (1, 2) or (s == 2 and k != 3) or g != 1 or d != 1 or dropout != 0.0:
+            raise NotImplementedError("hot-path convs are stride 1 (3x3: or 2), groups 1, dilation 1, dropout 0 (SURVEY a8)")
         self.conv = nn.Conv2d(c1, c2, k, s, k // 2 if p is None else p, bias=True)
         self.drop = nn.Identity()
         self.act = _act(act)
+
+
+class ResidualBlock1(nn.Module):
+    """utils/models.py:202-209 — x + Conv(Conv(x)) (parameter container)."""
+
+    def __init__(self, in_channel, out_channel, hidden_channel, kernel, act):
+        super().__init__()
+        self.m = nn.Sequential(Conv(in_channel, hidden_channel, kernel, 1, None, act=act),
+                               Conv(hidden_channel, out_channel, kernel, 1, None, act=False))
 
 
 class RDB(nn.Module):
@@ -269,11 +280,14 @@ class _NetPlan:
 class _SRNet(nn.Module):
     """Common forward of ResNet / EResNet (utils/models.py:613-618, :645-650)."""
     operand_dtype = "fp16"
+    trainable = True
+
+    plan_class = _NetPlan
 
     def _plan(self, device) -> _NetPlan:
         plans = self.__dict__.setdefault("_plans", {})
         if device not in plans:
-            plans[device] = _NetPlan(self, device, self.operand_dtype)
+            plans[device] = self.plan_class(self, device, self.operand_dtype)
         return plans[device]
 
     def forward(self, inputs: torch.Tensor) -> torch.Tensor:
@@ -281,6 +295,9 @@ class _SRNet(nn.Module):
             raise RuntimeError("the B200 path has no CPU fallback: move the model and its inputs to a CUDA device")
         if inputs.dim() != 4 or inputs.shape[1] != 3:
             raise RuntimeError(f"expected [N,3,h,w], got {tuple(inputs.shape)}")
+        if torch.is_grad_enabled() and self._any_requires_grad() and not self.trainable:
+            raise NotImplementedError(f"{self.__class__.__name__}: only the inference forward is on the sm_100a path "
+                                      "(wrap the call in torch.no_grad() or .requires_grad_(False); SURVEY §8(f))")
         if torch.is_grad_enabled() and self._any_requires_grad():
             # train.py:55 — forward with saved activations; backward runs on the same kernels (training.py)
             from .training import train_forward
@@ -334,6 +351,126 @@ class EResNet(_SRNet):
         for x in self.modules():
             if isinstance(x, nn.Conv2d):
                 x.weight.data *= 0.2
+
+
+class _DenoisePlan(_NetPlan):
+    """Launch schedule of the current-revision `Denoise` generator (utils/models.py:672-706), inference (BatchNorm folded).
+
+      conv0 9x9 + LReLU                                      head kernel (as the SR nets)
+      residual_0 / residual_2: x + Conv(LReLU(Conv(x)))      two 3x3 64->64 launches per block, the skip in the second's epilogue
+      residual_conv0: 3x3 stride 2, 64->256, LReLU            space-to-depth (srb_pixunshuffle_mask, slope 1: channel 4c+2i+j of
+                                                             pixel (y,x) = channel c of pixel (2y+i, 2x+j)) + a STRIDE-1 3x3 conv
+                                                             256->256 at H/2 x W/2 whose filter holds the nine taps at
+                                                             (DY, i) = (0,1), (1,0), (1,1) for dy = 0, 1, 2 (same for dx), zeros
+                                                             elsewhere: exactly the reference's sums, zero padding included
+      residual_1: 256->256 blocks                            weight-streaming kernels, four 64-output launches per conv
+      residual_conv1: PixelShuffle(2) + LReLU                srb_pixshuffle_lrelu
+      conv1 + long skip, conv2 9x9 + tanh                    as the SR nets
+    """
+
+    def _pack_down(self, m, q):
+        w = m.conv.weight.detach().float().cpu().numpy()          # [256][64][3][3], stride 2, padding 1
+        co, ci = w.shape[:2]
+        import numpy as np
+        w2 = np.zeros((co, ci, 2, 2, 3, 3), dtype=np.float32)     # [o][c][i][j][DY][DX]
+        tap = ((0, 1), (1, 0), (1, 1))                            # d -> (D, parity): input row 2y + d - 1 = 2(y + D - 1) + parity
+        for dy, (DY, i) in enumerate(tap):
+            for dx, (DX, j) in enumerate(tap):
+                w2[:, :, i, j, DY, DX] = w[:, :, dy, dx]
+        w2 = w2.reshape(co, ci * 4, 3, 3)
+        sl = slice(64 * q, 64 * q + 64)
+        return ops.PackedConv(self.ctx, w2[sl], m.conv.bias.detach()[sl], dtype=self.dtype)
+
+    def repack(self):
+        n = self.net
+        if n.residual_conv0.conv.out_channels != 256 or n.residual_conv0.conv.in_channels != 64:
+            raise NotImplementedError("Denoise: the down-sampling conv is 64 -> 256 (utils/models.py:680)")
+        q4 = [slice(64 * q, 64 * q + 64) for q in range(4)]
+        with torch.cuda.device(self.device):
+            self.conv0 = self._pack(n.conv0[0])
+            self.res0 = [[self._pack(b.m[0]), self._pack(b.m[1])] for b in n.residual_0]
+            self.down = [self._pack_down(n.residual_conv0, q) for q in range(4)]
+            self.res1 = [[[self._pack(b.m[j], sl) for sl in q4] for j in range(2)] for b in n.residual_1]
+            self.res2 = [[self._pack(b.m[0]), self._pack(b.m[1])] for b in n.residual_2]
+            self.conv1 = self._pack(n.conv1)
+            self.conv2 = self._pack(n.conv2[0])
+        self.versions = self._param_versions()
+        self.graphs = {}
+
+    def _blocks64(self, blocks, packs, r, keep, N, H, W):
+        """x + Conv(LReLU(Conv(x))) chains on 8-plane buffers; `keep` is never written.  Returns the buffer holding the result."""
+        t = self._buf("t", N, 8, H, W)
+        pool = [self._buf(f"r{i}", N, 8, H, W) for i in range(2)]
+        for b, pk in zip(blocks, packs):
+            out = next(x for x in pool if x is not r and x is not keep)
+            s0, f0 = _slope(b.m[0].act)
+            ops.conv2d_fwd(pk[0], r, 8, 0, t, 8, 0, N, H, W, slope=s0, flags=f0)
+            ops.conv2d_fwd(pk[1], t, 8, 0, out, 8, 0, N, H, W, residual=r, res_planes=8, res_off=0)
+            r = out
+        return r
+
+    def _run_trunk(self, xin, N, H, W):
+        n = self.net
+        if H % 2 or W % 2:
+            raise NotImplementedError(f"Denoise: H and W must be even on the sm_100a path (got {H} x {W}): the stride-2 conv runs "
+                                      "over the space-to-depth input")
+        h, w = H // 2, W // 2
+        X0 = self._buf("x0", N, 8, H, W)                    # conv0's output: the long skip (utils/models.py:702)
+        s0, f0 = _slope(n.conv0[0].act)
+        ops.conv2d_fwd(self.conv0, xin, 1, 0, X0, 8, 0, N, H, W, slope=s0, flags=f0)
+        r = self._blocks64(n.residual_0, self.res0, X0, X0, N, H, W)
+        U = self._buf("s2d", N, 32, h, w)
+        ops.pixunshuffle_mask(r, r, U, 1.0)                 # space-to-depth (slope 1: no mask)
+        D = [self._buf(f"d{i}", N, 32, h, w) for i in range(3)]
+        sd, fd = _slope(n.residual_conv0.act)
+        for q in range(4):
+            ops.conv2d_fwd(self.down[q], U, 32, 0, D[0], 32, 8 * q, N, h, w, slope=sd, flags=fd)
+        d = D[0]
+        for b, pk in zip(n.residual_1, self.res1):
+            t = D[2]
+            out = D[1] if d is D[0] else D[0]
+            s1, f1 = _slope(b.m[0].act)
+            for q in range(4):
+                ops.conv2d_fwd(pk[0][q], d, 32, 0, t, 32, 8 * q, N, h, w, slope=s1, flags=f1)
+            for q in range(4):
+                ops.conv2d_fwd(pk[1][q], t, 32, 0, out, 32, 8 * q, N, h, w, residual=d, res_planes=32, res_off=8 * q)
+            d = out
+        up = self._buf("up", N, 8, H, W)
+        ops.pixshuffle_lrelu(d, up, float(n.residual_conv1[1].negative_slope))
+        r = self._blocks64(n.residual_2, self.res2, up, X0, N, H, W)
+        y = self._buf("y", N, 8, H, W)
+        ops.conv2d_fwd(self.conv1, r, 8, 0, y, 8, 0, N, H, W, residual=X0, res_planes=8, res_off=0)
+        return y, H, W
+
+    def _run_tail(self, cur, N, h, w, u8_out):
+        tanh = ops.F_TANH if isinstance(self.net.conv2[0].act, nn.Tanh) else 0
+        out = torch.empty((N, 3, h, w), dtype=torch.uint8 if u8_out else torch.float32, device=self.device)
+        ops.conv2d_fwd(self.conv2, cur, 8, 0, out, 0, 0, N, h, w, flags=tanh | (ops.F_U8OUT if u8_out else ops.F_F32OUT))
+        return out
+
+    def launches(self) -> int:
+        return 1 + 2 * len(self.res0) + 1 + 4 + 8 * len(self.res1) + 1 + 2 * len(self.res2) + 2
+
+
+class Denoise(_SRNet):
+    """utils/models.py:672-706 (current revision: 9x9 head, ResidualBlock1 stacks around a stride-2 / PixelShuffle pair).
+    Inference forward on the sm_100a kernels; its training loop (train_gan.py) is outside the hot path."""
+    plan_class = _DenoisePlan
+    trainable = False
+
+    def __init__(self, residual_blocks):
+        super().__init__()
+        self.conv0 = nn.Sequential(ConvWithoutBN(3, 64, 9, 1, act=nn.LeakyReLU(0.2)))
+        self.residual_0 = nn.Sequential(*[ResidualBlock1(64, 64, 64, 3, act=nn.LeakyReLU(0.2)) for _ in range(residual_blocks // 2)])
+        self.residual_conv0 = ConvWithoutBN(64, 256, 3, 2, act=nn.LeakyReLU(0.2))
+        self.residual_1 = nn.Sequential(*[ResidualBlock1(256, 256, 256, 3, nn.LeakyReLU(0.2)) for _ in range(2)])
+        self.residual_conv1 = nn.Sequential(*[nn.PixelShuffle(2), nn.LeakyReLU(0.2)])
+        self.residual_2 = nn.Sequential(*[ResidualBlock1(64, 64, 64, 3, act=nn.LeakyReLU(0.2)) for _ in range(residual_blocks // 2)])
+        self.conv1 = Conv(64, 64, 3, 1, None, act=False)
+        self.conv2 = nn.Sequential(ConvWithoutBN(64, 3, 9, 1, None, act=nn.Tanh()))
+        for x in self.modules():                                # utils/models.py:691-693
+            if hasattr(x, "inplace"):
+                x.inplace = True
 
 
 class SRGAN(nn.Module):

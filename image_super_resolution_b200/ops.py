@@ -284,6 +284,14 @@ def pixunshuffle_mask(g_u: torch.Tensor, u: torch.Tensor, g_s: torch.Tensor, slo
                                       dtype_code(g_u.dtype), N, H2 // 2, W2 // 2, _stream_ptr(g_u.device)), "srb_pixunshuffle_mask")
 
 
+def pixshuffle_lrelu(s: torch.Tensor, u: torch.Tensor, slope: float):
+    """s: [N][4p][H][W][8] -> u: [N][p][2H][2W][8] = LeakyReLU(PixelShuffle(2)(s))."""
+    N, p, H2, W2, _ = u.shape
+    ctx = Context.get(u.device.index or 0)
+    check(lib().srb_pixshuffle_lrelu(ctx.handle, s.data_ptr(), u.data_ptr(), p, float(slope), dtype_code(u.dtype), N, H2 // 2, W2 // 2,
+                                     _stream_ptr(u.device)), "srb_pixshuffle_lrelu")
+
+
 def c8_axpby_mask(a, a_planes, a_off, alpha, b, b_planes, b_off, beta, act, act_planes, act_off, slope, out, out_planes, out_off,
                   planes, N, H, W):
     ctx = Context.get(a.device.index or 0)

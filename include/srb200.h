@@ -267,6 +267,12 @@ int srb_tanh_bwd_to_c8(srb_ctx* ctx, const float* gout, const float* out, void* 
  * 2H x 2W; g_s: 4*c8_u planes at H x W. */
 int srb_pixunshuffle_mask(srb_ctx* ctx, const void* g_u, const void* u, void* g_s, int c8_u, float slope, int dtype, int N, int H,
                           int W, srb_stream_t stream);
+/* Bare nn.PixelShuffle(2) + LeakyReLU of the current-revision Denoise generator (utils/models.py:685 `residual_conv1`; the conv
+ * before it adds a residual first, so its store cannot carry the shuffle): u[n, c, 2y+i, 2x+j] = lrelu(s[n, 4c+2i+j, y, x]).
+ * s: 4*c8_u planes at H x W, u: c8_u planes at 2H x 2W.  With slope = 1 and the roles swapped, srb_pixunshuffle_mask (u = g_u,
+ * slope 1) is the inverse permutation: the space-to-depth step that turns the stride-2 conv (:680) into a stride-1 one. */
+int srb_pixshuffle_lrelu(srb_ctx* ctx, const void* s_c8, void* u_c8, int c8_u, float slope, int dtype, int N, int H, int W,
+                         srb_stream_t stream);
 /* out = (alpha*a + beta*b) * LeakyReLU'(act) over C8 plane slices; b and act may be NULL (gradient fan-in at the long skip). */
 int srb_c8_axpby_mask(srb_ctx* ctx, const void* a, int a_c8_total, int a_c8_off, float alpha, const void* b, int b_c8_total,
                       int b_c8_off, float beta, const void* act, int act_c8_total, int act_c8_off, float slope, void* out,

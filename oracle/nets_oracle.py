@@ -58,3 +58,26 @@ def make_lr_hr(seed: int, n: int, hr: int, scale: int = 2):
     mean = torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
     std = torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
     return hr_t, (lr01 - mean) / std
+
+
+def _res1(x, sd, prefix, slope=0.2):
+    """ResidualBlock1.forward (utils/models.py:208-209): x + m(x), m = Conv(act=LeakyReLU), Conv(act=False) — both with BatchNorm."""
+    h = F.leaky_relu(_conv(x, sd, f"{prefix}.m.0", 1), slope)
+    return x + _conv(h, sd, f"{prefix}.m.1", 1)
+
+
+@torch.no_grad()
+def denoise_forward(x, sd, residual_blocks):
+    """Current-revision Denoise.forward (utils/models.py:697-706; ctor :673-695), eval mode (BatchNorm running statistics)."""
+    x0 = F.leaky_relu(_conv(x, sd, "conv0.0", 4), 0.2)
+    r = x0
+    for i in range(residual_blocks // 2):
+        r = _res1(r, sd, f"residual_0.{i}")
+    r = F.leaky_relu(F.conv2d(r, sd["residual_conv0.conv.weight"], sd["residual_conv0.conv.bias"], stride=2, padding=1), 0.2)
+    for i in range(2):
+        r = _res1(r, sd, f"residual_1.{i}")
+    r = F.leaky_relu(F.pixel_shuffle(r, 2), 0.2)
+    for i in range(residual_blocks // 2):
+        r = _res1(r, sd, f"residual_2.{i}")
+    y = x0 + _conv(r, sd, "conv1", 1)
+    return torch.tanh(_conv(y, sd, "conv2.0", 4))

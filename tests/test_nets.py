@@ -172,3 +172,96 @@ def test_gpu_captured_forward_replays_correctly():
         w2 = eager(xs[0])
         assert not torch.equal(w2, want[0])
         assert torch.equal(net(xs[0]), w2)
+
+
+# --------------------------------------------------------------------------------------------------------------------------
+# the current-revision Denoise generator (utils/models.py:672-706), inference
+# --------------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gold_dn(golden_dir):
+    return np.load(os.path.join(golden_dir, "denoise_golden.npz"))
+
+
+def _build_denoise():
+    from image_super_resolution_b200 import models
+    torch.manual_seed(100)
+    net = models.Denoise(4).eval()
+    g = torch.Generator().manual_seed(109)       # tools/make_golden.py golden_denoise(): non-trivial BatchNorm statistics
+    with torch.no_grad():
+        for m in net.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+                m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.weight.copy_(torch.rand(m.num_features, generator=g) * 0.5 + 0.25)
+                m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    return net
+
+
+def test_denoise_dropin_and_oracle_match_reference(gold_dn):
+    """Same module tree / construction order as the reference class (keys in order, same seeded weights), and the oracle
+    restatement (stride-2 conv, 256-channel blocks, bare PixelShuffle + LeakyReLU) reproduces the reference's forward."""
+    net = _build_denoise()
+    sd = net.state_dict()
+    assert list(sd.keys()) == list(gold_dn["keys"])
+    sums = np.array([float(v.double().sum()) for v in sd.values()])
+    assert np.allclose(sums, gold_dn["sums"], rtol=0, atol=1e-9)
+    y = no.denoise_forward(torch.from_numpy(gold_dn["x"]), sd, 4)
+    assert np.abs(y.numpy() - gold_dn["out"]).max() <= 2e-6
+    assert all(m.inplace for m in net.modules() if hasattr(m, "inplace"))        # utils/models.py:691-693
+
+
+def test_denoise_refuses_what_is_not_on_the_path():
+    from image_super_resolution_b200 import models
+    net = models.Denoise(2)
+    with pytest.raises(RuntimeError):
+        net(torch.zeros(1, 3, 8, 8))                       # CPU tensor
+    with pytest.raises(NotImplementedError):
+        models.ConvWithoutBN(64, 64, 9, 2)                 # stride 2 only as the 3x3 down-sampling conv
+
+
+@pytest.mark.gpu
+def test_gpu_denoise_forward_matches_reference_golden(gold_dn):
+    """fp16 operands / fp32 accumulate through 1 + 4 + 1 + 4 + 4 + 1 + 1 convs vs the reference class (fp32 CPU).
+    Tolerance: max-abs <= 8e-3 on the tanh output; the relative bound keeps it from being vacuous."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    net = _build_denoise().to("cuda:0")
+    x = torch.from_numpy(gold_dn["x"]).to("cuda:0")
+    with torch.no_grad():
+        y = net(x).cpu().numpy()
+        y2 = net(x).cpu().numpy()                          # second call: the captured graph replays
+    ref = gold_dn["out"]
+    assert y.shape == ref.shape
+    err = np.abs(y - ref).max()
+    rel = err / np.abs(ref).max()
+    print(f"Denoise(4) forward [2,3,32,40]: max err {err:.3e} ({rel:.3%} of max|ref|)")
+    assert err <= 8e-3 and rel <= 2e-2, (err, rel)
+    assert np.array_equal(y, y2)
+    with pytest.raises(NotImplementedError):               # odd sizes / training are not on the sm_100a path
+        with torch.no_grad():
+            net(torch.zeros(1, 3, 31, 40, device="cuda:0"))
+    with pytest.raises(NotImplementedError):
+        net(x)                                             # grad enabled, parameters require grad
+
+
+@pytest.mark.gpu
+def test_gpu_denoise_model_wrapper_uint8_fuse_and_larger_frame(gold_dn):
+    """Model(Denoise).init_normalize().fuse(): uint8 in -> uint8 out against the oracle on a 96 x 136 frame (several M-tiles per
+    row at both resolutions)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from image_super_resolution_b200 import models
+    net = _build_denoise()
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    m = models.Model(net)
+    m.init_normalize([0.485, 0.456, 0.406], [0.229, 0.224, 0.225])
+    m.fuse()
+    m = m.to("cuda:0").eval()
+    g = torch.Generator().manual_seed(2)
+    x = torch.randint(0, 256, (3, 3, 96, 136), dtype=torch.uint8, generator=g)
+    y = m(x.to("cuda:0")).cpu()
+    xn = ((x.float() / 255.0) - torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)) / torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    ref = ((no.denoise_forward(xn, sd, 4) + 1) / 2 * 255).round().to(torch.uint8)
+    assert y.dtype == torch.uint8 and y.shape == ref.shape
+    d = (y.int() - ref.int()).abs()
+    assert int(d.max()) <= 2 and float((d == 0).float().mean()) >= 0.97, (int(d.max()), float((d == 0).float().mean()))

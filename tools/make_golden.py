@@ -214,6 +214,29 @@ def golden_eresnet16():
           "max|y|", float(y.abs().max()))
 
 
+@torch.no_grad()
+def golden_denoise():
+    """The CURRENT-revision Denoise generator (utils/models.py:672-706: stride-2 3x3 64->256, 256-channel ResidualBlock1s, bare
+    PixelShuffle(2) + LeakyReLU) in eval mode with non-trivial BatchNorm statistics, forward on a seeded [2,3,32,40] batch."""
+    from utils.models import Denoise
+    torch.manual_seed(SEED)
+    net = Denoise(4).eval()
+    g = torch.Generator().manual_seed(SEED + 9)
+    for m in net.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+            m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+            m.weight.copy_(torch.rand(m.num_features, generator=g) * 0.5 + 0.25)
+            m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    x = torch.randn(2, 3, 32, 40, generator=g)
+    y = net(x.clone())
+    sd = net.state_dict()
+    out = {"x": x.numpy(), "out": y.numpy(), "keys": np.array(list(sd.keys())),
+           "sums": np.array([float(v.double().sum()) for v in sd.values()])}
+    np.savez_compressed(os.path.join(OUT, "denoise_golden.npz"), **out)
+    print("denoise_golden.npz: params", sum(p.numel() for p in net.parameters()), "keys", len(sd), "out", tuple(y.shape), "mean|y|", float(y.abs().mean()))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 1)
     install_stubs()
@@ -224,3 +247,4 @@ if __name__ == "__main__":
     golden_l1()
     golden_nets()
     golden_eresnet16()
+    golden_denoise()
