@@ -1553,7 +1553,8 @@ extern "C" int srb_resblock_fwd(srb_ctx* ctx, const srb_resblock* rb, const void
         cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
         cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
         cuuint32_t estr[4] = {1, 1, 1, 1};
-        cuuint32_t box[4] = {40, 1, 8, 1};                              // convA operand: one group with its halo
+        // convA operand: one group with its halo; narrow rows (group-major tiles, RB_GM): the same group of the tile's TR images
+        cuuint32_t box[4] = {40, 1, 8, (cuuint32_t)(RB_GM && p.TS == 0 ? p.TR : 1)};
         CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -2000,7 +2001,9 @@ extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* con
 
 template <int MODE, int NT, bool BF16, bool BWD>
 static int launch_chain(srb_ctx* ctx, const srb_conv_chain* c, cudaStream_t st) {
-    constexpr int KACC = (MODE == MODE_STD && NT == 2) ? 2 : 1;      // small-problem super-tiles: two accumulators per M-tile
+    // (KACC = 2 — two accumulators per M-tile, K-steps alternating — is implemented in conv_body and measured equal in time; it changes
+    // the fp32 summation order, and chains are kept bit-identical to the same layers launched one by one)
+    constexpr int KACC = 1;
     using G = ConvGeom<4, 32, 3, 3, MODE, NT, false, true, KACC>;
     ChainCtl cc{};
     cc.layers = c->d_layers; cc.tmaps = c->d_tmaps; cc.nlayers = c->n;

@@ -247,6 +247,9 @@ __device__ __forceinline__ bool elect_one() {
 // ------------------------------------------------------------------------------------------
 namespace srb {
 
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));

@@ -193,6 +193,19 @@ __device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBS
 //   tail's dx exchange) the first / last slot of a strip only feeds its neighbour — its own result comes from the adjacent
 //   strip — unless it is the image's edge group.
 // `in`: the slot is a group of the image (else its operand rows are zero), `out`: this tile produces the group's result.
+#ifndef RB_PF
+#define RB_PF 0
+#endif
+// Narrow rows (TS == 0: TR image rows of GX groups side by side in a tile): slots in GROUP-major order (slot = gx * TR + image), so
+// that ONE TMA box [10 px][8 planes][TR images] fills the TR slots of a group column: GX TMA instructions per x row instead of 16.
+// Measured (profiles/rb_trace_tma_r2.log): the producer warp issues one TMA instruction per 70-90 clk, 16 per row put 1 400 clk between
+// "stage free" and "row requested" and made the x ring (3 stages in the CTA-pair kernel) the loop that set the row period.
+#ifndef RB_GM
+#define RB_GM 1
+#endif
+#ifndef RB_EARLY_REL
+#define RB_EARLY_REL 1
+#endif
 struct RBSlot { int n, gx; bool in, out; };
 template <class Params>
 __device__ __forceinline__ RBSlot rb_slot(const Params& p, int ss, int j) {
@@ -210,6 +223,19 @@ __device__ __forceinline__ RBSlot rb_slot(const Params& p, int ss, int j) {
         s.out = s.in && (p.OV == 0 || ((j > 0 || s.gx == 0) && (j < 15 || s.gx == p.GX - 1)));
     }
     if (!s.in) { s.n = p.N; s.gx = 0; }        // as TMA coordinates: outside the tensor, the box is zero-filled
+    return s;
+}
+
+// fused residual block: narrow tiles in group-major slot order (RB_GM above); wide tiles as rb_slot
+template <class Params>
+__device__ __forceinline__ RBSlot rb_slot_gm(const Params& p, int ss, int j) {
+    if (!RB_GM || p.TS != 0) return rb_slot(p, ss, j);
+    RBSlot s;
+    s.gx = j / p.TR;
+    s.n = ss * p.TR + (j - s.gx * p.TR);
+    s.in = s.gx < p.GX && s.n < p.N;
+    s.out = s.in;
+    if (!s.in) { s.n = p.N; s.gx = 0; }
     return s;
 }
 
@@ -328,6 +354,8 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
     // zero the hidden ring once: halo slots at image borders are never written and must read as zero padding
     for (int i = threadIdx.x; i < G::HSLOTS * G::HROW / 16; i += G::THREADS)
         reinterpret_cast<uint4*>(s_h)[i] = make_uint4(0, 0, 0, 0);
+    if (RB_GM && p.TS == 0 && p.GX * p.TR < 16)      // slots no TMA box ever fills: their operand rows read as zeros
+        for (int i = threadIdx.x; i < XST * G::XROW / 16; i += G::THREADS) reinterpret_cast<uint4*>(s_x)[i] = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < G::CH + G::CB; i += G::THREADS) s_bias[i] = p.bias[i];
     if (threadIdx.x == 0) {
         constexpr int NC = PAIR ? 2 : 1;     // CTAs whose warps arrive on the leader's consumer -> issuer barriers
@@ -392,30 +420,52 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         }
         __syncwarp();
         pdl_wait();                          // x is the previous launch's output
+        const bool gm = RB_GM && p.TS == 0;
+        const int gm_box = p.TR * G::XBOX;
+        const uint32_t xbytes = gm ? (uint32_t)(p.GX * gm_box) : (uint32_t)G::XROW;
         int xc = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
-            const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const RBSlot sl = rb_slot_gm(p, sg.ss, lane & 15);
             const int n = sl.n, gx = sl.gx;
+            // group-major tiles: lane gx loads the box of group column gx for the tile's TR images (images beyond N: zero-filled)
+            const int gm_n0 = sg.ss * p.TR < p.N ? sg.ss * p.TR : p.N;
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % XST;
+                if constexpr (RB_PF > 0) {
+                    // L2 prefetch of the x row RB_PF steps ahead (one 128-byte line per slot and plane): the TMA boxes of that row
+                    // then hit L2 instead of waiting on HBM with only XST stages of requests in flight
+                    const int rr = r + RB_PF;
+                    if (lane < 16 && sl.in && rr < p.H) {
+                        const char* a = (const char*)p.x + (((size_t)n * 8 * p.H + rr) * p.W + (size_t)gx * 8) * 16;
+#pragma unroll
+                        for (int pl = 0; pl < 8; ++pl) prefetch_l2(a + (size_t)pl * HW * 16);
+                    }
+                }
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / XST) & 1) ^ 1), 31);
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 19);         // x stage free
                 if constexpr (PAIR) {
                     // both CTAs' rows of this step complete the LEADER's barrier (two arrivals, 2 x XROW bytes)
                     const uint32_t xf = bars_leader + (uint32_t)(st * 8);
-                    if (lane == 0) mbar_arrive_expect_tx_cluster(xf, G::XROW);
+                    if (lane == 0) mbar_arrive_expect_tx_cluster(xf, xbytes);
                     __syncwarp();
-                    if (lane < 16)
+                    if (gm) {
+                        if (lane < p.GX)
+                            tma_load_4d_pair(s_x + st * G::XROW + lane * gm_box, &tmap_x, xf, (lane * 8 - 1) * 4, r, 0, gm_n0);
+                    } else if (lane < 16)
                         tma_load_4d_pair(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, xf, (gx * 8 - 1) * 4, r, 0, n);
                     __syncwarp();
+                    if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 20);         // x row requested
                     continue;
                 }
                 if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
-                if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
+                if (lane == 0) mbar_arrive_expect_tx(&xfull[st], xbytes);
                 __syncwarp();
-                if (lane < 16)
+                if (gm) {
+                    if (lane < p.GX)
+                        tma_load_4d(s_x + st * G::XROW + lane * gm_box, &tmap_x, &xfull[st], (lane * 8 - 1) * 4, r, 0, gm_n0);
+                } else if (lane < 16)
                     tma_load_4d(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, &xfull[st], (gx * 8 - 1) * 4, r, 0, n);
                 __syncwarp();
                 if (SRB_DBG(p.dbg_trace != nullptr) && lane == 0) rb_trace(p, xc, 20);         // x row requested
@@ -575,12 +625,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int hbase = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
-            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const RBSlot sl = rb_slot_gm(p, sg.ss, grp);
             const bool valid = sl.in && sl.gx * 8 + i < p.W;
             // halo pixels go to the neighbouring slot when that is the neighbouring group of the same image row (an idle or
             // out-of-image slot of a wide tile writes the zeros its neighbour needs as padding)
-            const bool left = i == 0 && grp > 0 && (p.TS > 0 || sl.gx > 0);
-            const bool right = i == 7 && grp < 15 && (p.TS > 0 || sl.gx < p.GX - 1);
+            // (group-major narrow tiles: the same image row's neighbouring groups are TR slots away; idle slots have no neighbours)
+            const bool gmt = RB_GM && p.TS == 0;
+            const int nb = gmt ? p.TR * G::HBOX : G::HBOX;
+            const bool left = i == 0 && (gmt ? sl.in && sl.gx > 0 : grp > 0 && (p.TS > 0 || sl.gx > 0));
+            const bool right = i == 7 && (gmt ? sl.in && sl.gx < p.GX - 1 : grp < 15 && (p.TS > 0 || sl.gx < p.GX - 1));
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int c = hbase + h - sg.hlo;
@@ -608,6 +661,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[k]);
                     tmem_st32(t_lane + slot * G::CH, bv);
                 }
+                if constexpr (RB_EARLY_REL) {      // hand the accumulator row back as soon as it is drained and re-armed (not after the
+                    tmem_st_wait();                // shared-memory stores below): the convA issuer two rows ahead is waiting for it
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if constexpr (PAIR) mbar_arrive_cluster(bars_leader + (uint32_t)((24 + slot) * 8));
+                        else mbar_arrive(&haempty[slot]);
+                    }
+                }
                 if (tr) rb_trace(p, c, 11);
                 uint4 o[4];
 #pragma unroll
@@ -628,18 +690,22 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll
                 for (int pl = 0; pl < 4; ++pl) {
                     sts_u4(box + pl * 160 + (i + 1) * 16, o[pl]);
-                    if (left) sts_u4(box - G::HBOX + pl * 160 + 9 * 16, o[pl]);      // right halo slot of the group to the left
-                    if (right) sts_u4(box + G::HBOX + pl * 160, o[pl]);              // left halo slot of the group to the right
+                    if (left) sts_u4(box - nb + pl * 160 + 9 * 16, o[pl]);           // right halo slot of the group to the left
+                    if (right) sts_u4(box + nb + pl * 160, o[pl]);                   // left halo slot of the group to the right
                 }
                 if (tr) rb_trace(p, c, 13);
-                tmem_st_wait();
-                tc_fence_before();
+                if constexpr (!RB_EARLY_REL) { tmem_st_wait(); tc_fence_before(); }
                 if (tr) rb_trace(p, c, 14);
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    if constexpr (PAIR) { mbar_arrive_cluster(bars_leader + (uint32_t)((24 + slot) * 8)); mbar_arrive_cluster(bars_leader + (uint32_t)((32 + hs) * 8)); }
-                    else { mbar_arrive(&haempty[slot]); mbar_arrive(&hsfull[hs]); }
+                    if constexpr (PAIR) {
+                        if constexpr (!RB_EARLY_REL) mbar_arrive_cluster(bars_leader + (uint32_t)((24 + slot) * 8));
+                        mbar_arrive_cluster(bars_leader + (uint32_t)((32 + hs) * 8));
+                    } else {
+                        if constexpr (!RB_EARLY_REL) mbar_arrive(&haempty[slot]);
+                        mbar_arrive(&hsfull[hs]);
+                    }
                 }
                 if (tr) rb_trace(p, c, 4);        // hidden row published
             }
@@ -665,7 +731,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
         int slot = 0; uint32_t yph = 0;            // accumulator ring slot / phase
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg, ss_mul, ss_add)) {
-            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const RBSlot sl = rb_slot_gm(p, sg.ss, grp);
             const int n = sl.n, gx = sl.gx;
             const bool valid = sl.out && gx * 8 + i < p.W;
             // granule index of (n, plane 4*half, row 0, this pixel)
@@ -696,6 +762,15 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                     for (int k = 0; k < 32; ++k) bv[k] = __float_as_uint(s_bias[G::CH + half * 32 + k]);
                     tmem_st32(t_lane + slot * G::CB, bv);
                 }
+                if constexpr (RB_EARLY_REL) {      // the accumulator row goes back to the convB issuer before the residual add / stores
+                    tmem_st_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if constexpr (PAIR) mbar_arrive_cluster(bars_leader + (uint32_t)((48 + slot) * 8));
+                        else mbar_arrive(&yaempty[slot]);
+                    }
+                }
                 if (tr) rb_trace(p, c, 10);
                 if (y + 1 < sg.y1 && valid && !no_ld) {
 #pragma unroll
@@ -722,13 +797,16 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (half == 0) finish(std::integral_constant<int, G::CH>{});
                 else finish(std::integral_constant<int, G::CH + 32>{});
                 if (tr) rb_trace(p, c, 15);
-                tmem_st_wait();
-                tc_fence_before();
-                if (tr) rb_trace(p, c, 9);
-                __syncwarp();
-                if (lane == 0) {
-                    if constexpr (PAIR) mbar_arrive_cluster(bars_leader + (uint32_t)((48 + slot) * 8));
-                    else mbar_arrive(&yaempty[slot]);
+                if (RB_EARLY_REL && tr) rb_trace(p, c, 9);
+                if constexpr (!RB_EARLY_REL) {
+                    tmem_st_wait();
+                    tc_fence_before();
+                    if (tr) rb_trace(p, c, 9);
+                    __syncwarp();
+                    if (lane == 0) {
+                        if constexpr (PAIR) mbar_arrive_cluster(bars_leader + (uint32_t)((48 + slot) * 8));
+                        else mbar_arrive(&yaempty[slot]);
+                    }
                 }
                 if (tr) rb_trace(p, c, 7);      // output row done
                 if (++slot == G::RY) { slot = 0; yph ^= 1; }

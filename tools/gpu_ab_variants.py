@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""A/B of kernel-variant libraries (tools/build_variants.sh) on the model.pt forward at the bench shape: every variant runs in its
+own process (SRB200_LIB), the variants alternate over several rounds on the same box, medians are compared.
+usage: python tools/gpu_ab_variants.py [--rounds R] [--single] name1 name2 ...      ("base" = the product library)
+child:  python tools/gpu_ab_variants.py --child [--single]"""
+import os, subprocess, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def child(single):
+    import torch
+    import image_super_resolution_b200 as srb
+    from image_super_resolution_b200 import ops, _lib
+    dev = torch.device("cuda:0")
+    model = srb.load(os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")).to(dev).eval()
+    ctx = model._ctx
+    if single:
+        ctx.set_option(_lib.OPT_PATH, _lib.PATH_NO_PAIR)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randint(0, 256, (256, 3, 64, 64), dtype=torch.uint8, device=dev); y = torch.empty_like(x)
+    # parity guard: a variant that changes results is reported as such
+    from oracle import modelpt_oracle as mo
+    xs = torch.randint(0, 256, (2, 3, 40, 64), dtype=torch.uint8, generator=g)
+    d = (model(xs.to(dev)).cpu().int() - mo.forward_u8(xs).int()).abs()
+    ok = int(d.max()) <= 2 and float((d == 0).float().mean()) >= 0.97
+
+    def timed(fn, n=20):
+        for _ in range(3): fn()
+        torch.cuda.synchronize(); a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n): fn()
+        b.record(); torch.cuda.synchronize()
+        return a.elapsed_time(b) / n * 1e3
+    rb = ops.ResBlock(ctx, torch.randn(32, 64, 3, 3, generator=g) / 24, torch.zeros(32), torch.randn(64, 32, 3, 3, generator=g) / 17, torch.zeros(64), "fp16")
+    xa = torch.randn(256, 8, 64, 64, 8, device=dev).half(); ya = torch.empty_like(xa)
+    f = sorted(timed(lambda: model(x, out=y)) for _ in range(5))
+    r = sorted(timed(lambda: rb.forward(xa, ya, 0.2)) for _ in range(5))
+    ctx.check_device()
+    print(f"RESULT {f[2]:.2f} {f[0]:.2f} {r[2]:.2f} {r[0]:.2f} {'ok' if ok else 'PARITY-FAIL'}")
+
+
+def main():
+    args = sys.argv[1:]
+    single = "--single" in args
+    if "--child" in args:
+        return child(single)
+    rounds = 3
+    if "--rounds" in args:
+        rounds = int(args[args.index("--rounds") + 1])
+    names = [a for a in args if not a.startswith("--") and not a.isdigit()]
+    res = {n: [] for n in names}
+    for rnd in range(rounds):
+        for n in names:
+            env = dict(os.environ)
+            if n != "base":
+                env["SRB200_LIB"] = os.path.join(ROOT, "image_super_resolution_b200", "variants", f"lib_{n}.so")
+            out = subprocess.run([sys.executable, __file__, "--child"] + (["--single"] if single else []), env=env, capture_output=True, text=True, timeout=300)
+            line = [l for l in out.stdout.splitlines() if l.startswith("RESULT")]
+            if not line:
+                print(f"{n}: FAILED\n{out.stdout[-400:]}\n{out.stderr[-800:]}", flush=True)
+                continue
+            v = line[0].split()
+            res[n].append((float(v[1]), float(v[2]), float(v[3]), float(v[4]), v[5]))
+            print(f"round {rnd} {n:14s} forward {v[1]:>8s} us (min {v[2]})  resblock {v[3]:>7s} us (min {v[4]})  {v[5]}", flush=True)
+    print("medians over rounds (forward us -> Mpix/s | resblock us):")
+    for n in names:
+        if res[n]:
+            f = sorted(t[0] for t in res[n]); r = sorted(t[2] for t in res[n])
+            print(f"  {n:14s} forward {f[len(f)//2]:8.1f} us = {256*64*64/f[len(f)//2]:6.0f} Mpix/s | resblock {r[len(r)//2]:6.1f} us (min {min(t[3] for t in res[n]):.1f})")
+
+
+if __name__ == "__main__":
+    main()

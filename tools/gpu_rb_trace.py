@@ -8,6 +8,8 @@ from image_super_resolution_b200 import ops
 from image_super_resolution_b200._lib import Context, lib, check
 dev = torch.device("cuda:0"); ctx = Context.get(0)
 N, H, W = 256, 64, 64
+if len(sys.argv) > 2: H = int(sys.argv[2])
+if len(sys.argv) > 3: N = int(sys.argv[3])
 g = torch.Generator().manual_seed(0)
 rb = ops.ResBlock(ctx, torch.randn(32, 64, 3, 3, generator=g) / 24, torch.zeros(32), torch.randn(64, 32, 3, 3, generator=g) / 17,
                   torch.zeros(64), "fp16")
