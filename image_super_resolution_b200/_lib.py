@@ -87,6 +87,12 @@ SIGNATURES = {
     "srb_l1_loss_fwd_noalloc": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp]),
     "srb_l1_loss_bwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp]),
     "srb_l1_loss_bwd_dev": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp, _vp]),
+    "srb_bn_stats": (_i, [_vp, _vp, _i, _vp]),
+    "srb_bn_apply": (_i, [_vp, _vp, _i, _vp]),
+    "srb_bn_bwd_reduce": (_i, [_vp, _vp, _i, _vp]),
+    "srb_bn_bwd_apply": (_i, [_vp, _vp, _i, _vp]),
+    "srb_mse_loss_fwd": (_i, [_vp, _vp, _i, _vp, _sz, _f, _vp, _vp, _vp]),
+    "srb_mse_loss_bwd_dev": (_i, [_vp, _vp, _i, _vp, _sz, _f, _f, _vp, _vp, _vp]),
 }
 
 # probe hooks of the -DSRB_DEBUG build (include/srb200_debug.h): present only when SRB200_LIB points at libsrb200_dbg.so (tools/)
@@ -181,6 +187,20 @@ class ConvArgs(C.Structure):
                 ("res2", _vp), ("res2_c8_total", _i), ("res2_c8_off", _i), ("res2_scale", _f),
                 ("out_scale", _f), ("lrelu_slope", _f), ("flags", _i),
                 ("mask", _vp), ("mask_c8_total", _i), ("mask_c8_off", _i), ("mask_p0", _i), ("mask_p1", _i), ("mask_slope", _f),
+                ("N", _i), ("H", _i), ("W", _i)]
+
+
+class BNArgs(C.Structure):
+    """srb_bn_args of include/srb200.h."""
+    _fields_ = [("y", _vp), ("y_c8_total", _i), ("y_c8_off", _i),
+                ("out", _vp), ("out_c8_total", _i), ("out_c8_off", _i),
+                ("planes", _i), ("gamma", _vp), ("beta", _vp), ("sums", _vp),
+                ("running_mean", _vp), ("running_var", _vp), ("num_batches_tracked", _vp),
+                ("momentum", _f), ("eps", _f), ("slope", _f), ("act", _i), ("out_scale", _f),
+                ("res", _vp), ("res_c8_total", _i), ("res_c8_off", _i), ("res_scale", _f),
+                ("res2", _vp), ("res2_c8_total", _i), ("res2_c8_off", _i), ("res2_scale", _f),
+                ("da", _vp), ("da_c8_total", _i), ("da_c8_off", _i), ("up_scale", _f),
+                ("bsums", _vp), ("dgamma", _vp), ("dbeta", _vp), ("grad_scale", _f),
                 ("N", _i), ("H", _i), ("W", _i)]
 
 

@@ -28,6 +28,7 @@
 #include "srb_rowconv.cuh"
 #include "srb_tail.cuh"
 #include "srb_optim.cuh"
+#include "srb_bn.cuh"
 
 using namespace srb;
 
@@ -712,48 +713,134 @@ extern "C" int srb_adam_ema_step(srb_ctx* ctx, float* params, const float* grads
 // ------------------------------------------------------------------------------------------
 extern "C" int srb_l1_partials_len(void) { return L1_MAX_BLOCKS; }
 
-extern "C" int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
-                               float* loss_out, float* partials, srb_stream_t stream) {
-    if (!ctx || !pred || !tgt || !loss_out || !partials) return fail(SRB_EINVAL, "srb_l1_loss_fwd: NULL argument");
-    if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_fwd: empty input (mean of nothing)");
-    if (((uintptr_t)pred & 15) || ((uintptr_t)tgt & 15)) return fail(SRB_EINVAL, "srb_l1_loss_fwd: buffers must be 16-byte aligned");
+static int loss_fwd_impl(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w, float* loss_out,
+                         float* partials, srb_stream_t stream, bool sq, const char* who) {
+    if (!ctx || !pred || !tgt || !loss_out || !partials) return fail(SRB_EINVAL, "%s: NULL argument", who);
+    if (n == 0) return fail(SRB_EINVAL, "%s: empty input (mean of nothing)", who);
+    if (((uintptr_t)pred & 15) || ((uintptr_t)tgt & 15)) return fail(SRB_EINVAL, "%s: buffers must be 16-byte aligned", who);
     size_t b = (n / 4 + 255) / 256;
     int grid = (int)(b < (size_t)L1_MAX_BLOCKS ? (b ? b : 1) : L1_MAX_BLOCKS);
     float scale = (float)((double)w / (double)n);
     cudaStream_t st = (cudaStream_t)stream;
+#define SRB_LOSS_FWD(DT) \
+    if (sq) l1_fwd_kernel<DT, true><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); \
+    else l1_fwd_kernel<DT, false><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials)
     switch (pred_dtype) {
-        case 0: l1_fwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
-        case 1: l1_fwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
-        case 2: l1_fwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, scale, loss_out, partials); break;
-        default: return fail(SRB_EINVAL, "srb_l1_loss_fwd: pred_dtype %d", pred_dtype);
+        case 0: SRB_LOSS_FWD(0); break;
+        case 1: SRB_LOSS_FWD(1); break;
+        case 2: SRB_LOSS_FWD(2); break;
+        default: return fail(SRB_EINVAL, "%s: pred_dtype %d", who, pred_dtype);
     }
+#undef SRB_LOSS_FWD
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
 
-extern "C" int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
-                               float grad_scale, void* dpred, srb_stream_t stream) {
-    return srb_l1_loss_bwd_dev(ctx, pred, pred_dtype, tgt, n, w, grad_scale, nullptr, dpred, stream);
-}
-
-extern "C" int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
-                                   float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream) {
-    if (!ctx || !pred || !tgt || !dpred) return fail(SRB_EINVAL, "srb_l1_loss_bwd: NULL argument");
-    if (n == 0) return fail(SRB_EINVAL, "srb_l1_loss_bwd: empty input");
+static int loss_bwd_impl(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w, float grad_scale,
+                         const float* grad_out_dev, void* dpred, srb_stream_t stream, bool sq, const char* who) {
+    if (!ctx || !pred || !tgt || !dpred) return fail(SRB_EINVAL, "%s: NULL argument", who);
+    if (n == 0) return fail(SRB_EINVAL, "%s: empty input", who);
     size_t b = (n + 255) / 256;
     size_t cap = (size_t)ctx->num_sms * 8;
     int grid = (int)(b < cap ? b : cap);
     float g = (float)((double)w * (double)grad_scale / (double)n);
     cudaStream_t st = (cudaStream_t)stream;
+#define SRB_LOSS_BWD(DT) \
+    if (sq) l1_bwd_kernel<DT, true><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); \
+    else l1_bwd_kernel<DT, false><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev)
     switch (pred_dtype) {
-        case 0: l1_bwd_kernel<0><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
-        case 1: l1_bwd_kernel<1><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
-        case 2: l1_bwd_kernel<2><<<grid, 256, 0, st>>>(pred, tgt, n, g, dpred, grad_out_dev); break;
-        default: return fail(SRB_EINVAL, "srb_l1_loss_bwd: pred_dtype %d", pred_dtype);
+        case 0: SRB_LOSS_BWD(0); break;
+        case 1: SRB_LOSS_BWD(1); break;
+        case 2: SRB_LOSS_BWD(2); break;
+        default: return fail(SRB_EINVAL, "%s: pred_dtype %d", who, pred_dtype);
+    }
+#undef SRB_LOSS_BWD
+    CUDA_TRY(cudaGetLastError());
+    return SRB_OK;
+}
+
+extern "C" int srb_l1_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                               float* loss_out, float* partials, srb_stream_t stream) {
+    return loss_fwd_impl(ctx, pred, pred_dtype, tgt, n, w, loss_out, partials, stream, false, "srb_l1_loss_fwd");
+}
+
+extern "C" int srb_l1_loss_bwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                               float grad_scale, void* dpred, srb_stream_t stream) {
+    return loss_bwd_impl(ctx, pred, pred_dtype, tgt, n, w, grad_scale, nullptr, dpred, stream, false, "srb_l1_loss_bwd");
+}
+
+extern "C" int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                                   float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream) {
+    return loss_bwd_impl(ctx, pred, pred_dtype, tgt, n, w, grad_scale, grad_out_dev, dpred, stream, false, "srb_l1_loss_bwd");
+}
+
+extern "C" int srb_mse_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                                float* loss_out, float* partials, srb_stream_t stream) {
+    return loss_fwd_impl(ctx, pred, pred_dtype, tgt, n, w, loss_out, partials, stream, true, "srb_mse_loss_fwd");
+}
+
+extern "C" int srb_mse_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                                    float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream) {
+    return loss_bwd_impl(ctx, pred, pred_dtype, tgt, n, w, grad_scale, grad_out_dev, dpred, stream, true, "srb_mse_loss_bwd_dev");
+}
+
+// ------------------------------------------------------------------------------------------
+// train-mode BatchNorm passes (utils/models.py:75-111 `Conv`; srb_bn.cuh)
+// ------------------------------------------------------------------------------------------
+static int bn_launch(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream, int which, const char* who) {
+    if (!ctx || !a) return fail(SRB_EINVAL, "%s: NULL argument", who);
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "%s: dtype %d", who, dtype);
+    if (a->N <= 0 || a->H <= 0 || a->W <= 0 || a->planes <= 0) return fail(SRB_EINVAL, "%s: empty shape", who);
+    if (!a->y || !a->gamma || !a->beta || !a->sums) return fail(SRB_EINVAL, "%s: y / gamma / beta / sums missing", who);
+    if (a->y_c8_off < 0 || a->y_c8_off + a->planes > a->y_c8_total) return fail(SRB_EINVAL, "%s: y plane slice out of range", who);
+    if (which != 0 && which != 2) {
+        if (!a->out) return fail(SRB_EINVAL, "%s: out missing", who);
+        if (a->out_c8_off < 0 || a->out_c8_off + a->planes > a->out_c8_total) return fail(SRB_EINVAL, "%s: out plane slice out of range", who);
+    }
+    if (which == 1) {
+        if (a->res && (a->res_c8_off < 0 || a->res_c8_off + a->planes > a->res_c8_total)) return fail(SRB_EINVAL, "%s: res plane slice out of range", who);
+        if (a->res2 && (a->res2_c8_off < 0 || a->res2_c8_off + a->planes > a->res2_c8_total)) return fail(SRB_EINVAL, "%s: res2 plane slice out of range", who);
+    }
+    if (which >= 2) {
+        if (!a->da || !a->bsums) return fail(SRB_EINVAL, "%s: da / bsums missing", who);
+        if (a->da_c8_off < 0 || a->da_c8_off + a->planes > a->da_c8_total) return fail(SRB_EINVAL, "%s: da plane slice out of range", who);
+    }
+    if (a->act != 0 && a->act != 1) return fail(SRB_EINVAL, "%s: act %d", who, a->act);
+    if ((long long)a->N > 65535) return fail(SRB_EINVAL, "%s: batch %d", who, a->N);
+    BNParams p{};
+    p.y = a->y; p.y_c8_total = a->y_c8_total; p.y_c8_off = a->y_c8_off;
+    p.out = a->out; p.out_c8_total = a->out_c8_total; p.out_c8_off = a->out_c8_off;
+    p.planes = a->planes; p.gamma = a->gamma; p.beta = a->beta; p.sums = a->sums;
+    p.running_mean = a->running_mean; p.running_var = a->running_var; p.nbt = a->num_batches_tracked;
+    if ((p.running_mean == nullptr) != (p.running_var == nullptr)) return fail(SRB_EINVAL, "%s: running_mean and running_var go together", who);
+    p.momentum = a->momentum; p.eps = a->eps; p.slope = a->slope; p.act = a->act; p.out_scale = a->out_scale;
+    p.res = a->res; p.res_c8_total = a->res_c8_total; p.res_c8_off = a->res_c8_off; p.res_scale = a->res_scale;
+    p.res2 = a->res2; p.res2_c8_total = a->res2_c8_total; p.res2_c8_off = a->res2_c8_off; p.res2_scale = a->res2_scale;
+    p.da = a->da; p.da_c8_total = a->da_c8_total; p.da_c8_off = a->da_c8_off; p.up_scale = a->up_scale;
+    p.bsums = a->bsums; p.dgamma = a->dgamma; p.dbeta = a->dbeta; p.grad_scale = a->grad_scale;
+    p.N = a->N; p.H = a->H; p.W = a->W;
+    // blocks per (image, plane): enough to fill the GPU a few times over, at least 256 pixels each
+    const long long HW = (long long)a->H * a->W;
+    long long chunks = (HW + 1023) / 1024;
+    const long long want = (long long)ctx->num_sms * 8 / ((long long)a->planes * a->N) + 1;
+    if (chunks > want) chunks = want;
+    if (chunks < 1) chunks = 1;
+    const dim3 grid((unsigned)chunks, (unsigned)a->planes, (unsigned)a->N);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool bf = dtype == SRB_DT_BF16;
+    switch (which) {
+        case 0: if (bf) bn_stats_kernel<true><<<grid, 256, 0, st>>>(p); else bn_stats_kernel<false><<<grid, 256, 0, st>>>(p); break;
+        case 1: if (bf) bn_apply_kernel<true><<<grid, 256, 0, st>>>(p); else bn_apply_kernel<false><<<grid, 256, 0, st>>>(p); break;
+        case 2: if (bf) bn_bwd_reduce_kernel<true><<<grid, 256, 0, st>>>(p); else bn_bwd_reduce_kernel<false><<<grid, 256, 0, st>>>(p); break;
+        default: if (bf) bn_bwd_apply_kernel<true><<<grid, 256, 0, st>>>(p); else bn_bwd_apply_kernel<false><<<grid, 256, 0, st>>>(p); break;
     }
     CUDA_TRY(cudaGetLastError());
     return SRB_OK;
 }
+extern "C" int srb_bn_stats(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream) { return bn_launch(ctx, a, dtype, stream, 0, "srb_bn_stats"); }
+extern "C" int srb_bn_apply(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream) { return bn_launch(ctx, a, dtype, stream, 1, "srb_bn_apply"); }
+extern "C" int srb_bn_bwd_reduce(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream) { return bn_launch(ctx, a, dtype, stream, 2, "srb_bn_bwd_reduce"); }
+extern "C" int srb_bn_bwd_apply(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream) { return bn_launch(ctx, a, dtype, stream, 3, "srb_bn_bwd_apply"); }
 
 // ------------------------------------------------------------------------------------------
 // model.pt graph

@@ -175,7 +175,11 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-template <int DT>
+// SQ: squared error (nn.MSELoss, train.py:264 without --enchant) instead of the absolute error
+template <bool SQ>
+__device__ __forceinline__ float loss_term(float d) { return SQ ? d * d : fabsf(d); }
+
+template <int DT, bool SQ = false>
 __global__ void __launch_bounds__(256) l1_fwd_kernel(const void* __restrict__ pred, const float* __restrict__ tgt,
                                                      size_t n, float scale /* w / n */, float* __restrict__ loss,
                                                      float* __restrict__ partials) {
@@ -198,10 +202,10 @@ __global__ void __launch_bounds__(256) l1_fwd_kernel(const void* __restrict__ pr
                 p0 = a.x; p1 = a.y; p2 = b.x; p3 = b.y;
             }
         }
-        acc += fabsf(p0 - t.x) + fabsf(p1 - t.y) + fabsf(p2 - t.z) + fabsf(p3 - t.w);
+        acc += loss_term<SQ>(p0 - t.x) + loss_term<SQ>(p1 - t.y) + loss_term<SQ>(p2 - t.z) + loss_term<SQ>(p3 - t.w);
     }
     for (size_t i = n4 * 4 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride)
-        acc += fabsf(ldp<DT>(pred, i) - tgt[i]);
+        acc += loss_term<SQ>(ldp<DT>(pred, i) - tgt[i]);
 
     __shared__ float s_part[8];
     __shared__ bool s_last;
@@ -232,7 +236,7 @@ __global__ void __launch_bounds__(256) l1_fwd_kernel(const void* __restrict__ pr
     }
 }
 
-template <int DT>
+template <int DT, bool SQ = false>
 __global__ void __launch_bounds__(256) l1_bwd_kernel(const void* __restrict__ pred, const float* __restrict__ tgt,
                                                      size_t n, float g /* w*scale/n */, void* __restrict__ dpred,
                                                      const float* __restrict__ g_dev /* optional device factor */) {
@@ -240,7 +244,7 @@ __global__ void __launch_bounds__(256) l1_bwd_kernel(const void* __restrict__ pr
     if (g_dev != nullptr) g *= *g_dev;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += stride) {
         float d = ldp<DT>(pred, i) - tgt[i];
-        float s = d > 0.f ? g : (d < 0.f ? -g : 0.f);
+        float s = SQ ? 2.f * d * g : (d > 0.f ? g : (d < 0.f ? -g : 0.f));
         if constexpr (DT == 0) reinterpret_cast<__half*>(dpred)[i] = __float2half_rn(s);
         else if constexpr (DT == 1) reinterpret_cast<__nv_bfloat16*>(dpred)[i] = __float2bfloat16_rn(s);
         else reinterpret_cast<float*>(dpred)[i] = s;

@@ -117,7 +117,8 @@ def _pred_code(t: torch.Tensor) -> int:
     return {torch.float16: SRB_DT_F16, torch.bfloat16: SRB_DT_BF16, torch.float32: SRB_DT_F32}[t.dtype]
 
 
-def l1_loss_fwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0) -> torch.Tensor:
+def l1_loss_fwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0, squared: bool = False) -> torch.Tensor:
+    """w * mean|pred - tgt| (squared: w * mean (pred - tgt)^2, nn.MSELoss)."""
     _require_cuda(pred, "pred")
     _require_cuda(tgt, "tgt")
     if tgt.dtype != torch.float32 or pred.shape != tgt.shape:
@@ -125,8 +126,9 @@ def l1_loss_fwd(pred: torch.Tensor, tgt: torch.Tensor, w: float = 1.0) -> torch.
     ctx = Context.get(pred.device.index or 0)
     out = torch.empty((), dtype=torch.float32, device=pred.device)
     partials = torch.empty(lib().srb_l1_partials_len(), dtype=torch.float32, device=pred.device)
-    check(lib().srb_l1_loss_fwd(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w),
-                                out.data_ptr(), partials.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_fwd")
+    fn = lib().srb_mse_loss_fwd if squared else lib().srb_l1_loss_fwd
+    check(fn(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w),
+             out.data_ptr(), partials.data_ptr(), _stream_ptr(pred.device)), "srb_mse_loss_fwd" if squared else "srb_l1_loss_fwd")
     return out
 
 
@@ -226,6 +228,58 @@ def conv_args(x, x_planes, x_off, y, y_planes, y_off, N, H, W, slope=0.0, flags=
     return a
 
 
+class BatchNormPass:
+    """The four train-mode BatchNorm passes of one `Conv` block (srb_bn_*; utils/models.py:75-111) over fixed buffers: the
+    argument block is built once, `stats / apply / bwd_reduce / bwd_apply` launch on the current stream."""
+
+    def __init__(self, ctx: Context, dtype, N, H, W, planes, y, y_planes, y_off, gamma, beta, sums, bsums, bn=None, slope=0.0,
+                 act=0, out=None, out_planes=0, out_off=0, out_scale=1.0, res=None, res_planes=0, res_off=0, res_scale=1.0,
+                 res2=None, res2_planes=0, res2_off=0, res2_scale=1.0):
+        self.ctx, self.dt = ctx, dtype_code(dtype)
+        a = self.a = _lib.BNArgs()
+        a.y, a.y_c8_total, a.y_c8_off = y.data_ptr(), y_planes, y_off
+        a.planes, a.gamma, a.beta = planes, gamma.data_ptr(), beta.data_ptr()
+        a.sums, a.bsums = sums.data_ptr(), bsums.data_ptr()
+        if bn is not None and bn.running_mean is not None:
+            a.running_mean, a.running_var = bn.running_mean.data_ptr(), bn.running_var.data_ptr()
+            a.num_batches_tracked = bn.num_batches_tracked.data_ptr()
+            a.momentum = 0.1 if bn.momentum is None else float(bn.momentum)
+        a.eps = 1e-5 if bn is None else float(bn.eps)
+        a.slope, a.act, a.out_scale = float(slope), int(act), float(out_scale)
+        if out is not None:
+            a.out, a.out_c8_total, a.out_c8_off = out.data_ptr(), out_planes, out_off
+        if res is not None:
+            a.res, a.res_c8_total, a.res_c8_off, a.res_scale = res.data_ptr(), res_planes, res_off, float(res_scale)
+        if res2 is not None:
+            a.res2, a.res2_c8_total, a.res2_c8_off, a.res2_scale = res2.data_ptr(), res2_planes, res2_off, float(res2_scale)
+        a.up_scale, a.grad_scale = 1.0, 1.0
+        a.N, a.H, a.W = N, H, W
+        self._keep = (y, gamma, beta, sums, bsums, bn, out, res, res2)
+        self._fwd = C.create_string_buffer(bytes(a), C.sizeof(a))       # the forward's argument block (backward re-targets `out`)
+
+    def _run(self, fn, name, args, device):
+        check(fn(self.ctx.handle, C.byref(args), self.dt, _stream_ptr(device)), name)
+
+    def stats(self, device):
+        self._run(lib().srb_bn_stats, "srb_bn_stats", self.a, device)
+
+    def apply(self, device):
+        self._run(lib().srb_bn_apply, "srb_bn_apply", self.a, device)
+
+    def set_backward(self, da, da_planes, da_off, out, out_planes, out_off, dgamma, dbeta, up_scale=1.0, grad_scale=1.0):
+        b = self.b = _lib.BNArgs.from_buffer_copy(self._fwd)
+        b.da, b.da_c8_total, b.da_c8_off, b.up_scale = da.data_ptr(), da_planes, da_off, float(up_scale)
+        b.out, b.out_c8_total, b.out_c8_off = out.data_ptr(), out_planes, out_off
+        b.dgamma, b.dbeta, b.grad_scale = dgamma.data_ptr(), dbeta.data_ptr(), float(grad_scale)
+        self._keep_b = (da, out, dgamma, dbeta)
+
+    def bwd_reduce(self, device):
+        self._run(lib().srb_bn_bwd_reduce, "srb_bn_bwd_reduce", self.b, device)
+
+    def bwd_apply(self, device):
+        self._run(lib().srb_bn_bwd_apply, "srb_bn_bwd_apply", self.b, device)
+
+
 class ConvChain:
     """Up to four weight-streaming 3x3 convs (32 outputs each) of one dense block as ONE launch (srb_conv_chain_*):
     layers = [(packed conv, ConvArgs)]; the tensors named by the arguments must outlive the chain."""
@@ -302,14 +356,15 @@ def c8_axpby_mask(a, a_planes, a_off, alpha, b, b_planes, b_off, beta, act, act_
                                   _stream_ptr(a.device)), "srb_c8_axpby_mask")
 
 
-def l1_loss_bwd_dev(pred: torch.Tensor, tgt: torch.Tensor, grad_out: torch.Tensor, w: float = 1.0) -> torch.Tensor:
-    """dpred = grad_out (device scalar) * w * sign(pred - tgt) / numel."""
+def l1_loss_bwd_dev(pred: torch.Tensor, tgt: torch.Tensor, grad_out: torch.Tensor, w: float = 1.0, squared: bool = False) -> torch.Tensor:
+    """dpred = grad_out (device scalar) * w * sign(pred - tgt) / numel  (squared: ... * 2 (pred - tgt) / numel)."""
     _require_cuda(pred, "pred"); _require_cuda(tgt, "tgt"); _require_cuda(grad_out, "grad_out")
     ctx = Context.get(pred.device.index or 0)
     g = torch.empty_like(pred)
     go = grad_out.detach().reshape(()).float().contiguous()
-    check(lib().srb_l1_loss_bwd_dev(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w), 1.0,
-                                    go.data_ptr(), g.data_ptr(), _stream_ptr(pred.device)), "srb_l1_loss_bwd_dev")
+    fn = lib().srb_mse_loss_bwd_dev if squared else lib().srb_l1_loss_bwd_dev
+    check(fn(ctx.handle, pred.data_ptr(), _pred_code(pred), tgt.data_ptr(), pred.numel(), float(w), 1.0,
+             go.data_ptr(), g.data_ptr(), _stream_ptr(pred.device)), "srb_mse_loss_bwd_dev" if squared else "srb_l1_loss_bwd_dev")
     return g
 
 

@@ -9,7 +9,7 @@ Schedule, all launches through the C ABI:
             Measured on EResNet(16) (tools/gpu_train_parity.py): with GradScaler's loss scale (65536) every one of the
             488 gradient tensors has cosine >= 0.9991 vs fp32 autograd; bf16 operands reach only 0.9958 (242 tensors
             below the 0.999 contract), fp16 WITHOUT loss scaling underflows.  `net.train_operand_dtype = "bf16"` selects bf16;
-  backward  per conv: weight gradient (tcgen05, srb_conv2d_wgrad; FP32-pipe srb_conv9_wgrad for the 9x9 head/tail),
+  backward  per conv: weight gradient (tcgen05: srb_grad_batch_run, one launch for all convs; the 9x9 head/tail in the same mapping, KS = 9),
             bias gradient, and the data gradient as a conv of dY with the transposed / rotated filter that
             ACCUMULATES in place into the dense block's gradient buffer and applies the LeakyReLU mask of the slice
             that becomes final with that launch (no separate elementwise kernels inside the trunk).
@@ -48,11 +48,11 @@ def _slope_of(act) -> float:
 class TrainPlan:
     """Device-packed operands, saved activations and the fwd/bwd launch schedule of one EResNet on one device."""
 
+    allow_bn = False           # BNTrainPlan (below) schedules the nets whose `Conv` blocks carry a BatchNorm2d
+
     def __init__(self, net, device: torch.device, dtype="fp16", allreduce: bool = True):
-        for m in net.modules():
-            if isinstance(m, nn.BatchNorm2d):
-                raise NotImplementedError("train-mode BatchNorm (ResNet) is not on the sm_100a path (SURVEY §8(f) rank 3); "
-                                          "train EResNet, or run ResNet in eval mode")
+        if not self.allow_bn and any(isinstance(m, nn.BatchNorm2d) for m in net.modules()):
+            raise RuntimeError("TrainPlan schedules the BatchNorm-free EResNet; nets with BatchNorm2d train through BNTrainPlan")
         self.net, self.device, self.dt = net, device, ops.dtype_code(dtype)
         self.ctx = Context.get(device.index)
         self.allreduce = allreduce
@@ -123,12 +123,13 @@ class TrainPlan:
 
     def _pack_jobs(self):
         n = self.net
+        bias = lambda m: None if m.conv.bias is None else m.conv.bias.data     # noqa: E731  (`Conv` blocks are bias-free)
         jobs = [(self.f_conv0, n.conv0.conv.weight.data, n.conv0.conv.bias.data, 0, 0, False)]
         for r, (rrdb, rdb, fwd, stage, fin) in enumerate(self.rdbs):
             Wt = []
             for i in range(5):
                 m = getattr(rdb, f"conv{i}") if i < 4 else rdb.conv
-                w, b = m.conv.weight.data, m.conv.bias.data
+                w, b = m.conv.weight.data, bias(m)
                 jobs.append((fwd[i], w, b, 0, 0, False))
                 Wt.append(w)
             # transposed / rotated filters of the gathered data-gradient convs: input channels [0,64) come from conv4 (times
@@ -142,7 +143,7 @@ class TrainPlan:
             jobs.append((fin, Wt[4], None, 0, 0, True, 0, 64, s_out))
             for j in range(3, -1, -1):
                 jobs.append((fin, Wt[j], None, 0, 0, True, 64 + 32 * (3 - j), 32, 1.0))
-        jobs.append((self.f_conv1, n.conv1.conv.weight.data, n.conv1.conv.bias.data, 0, 0, False))
+        jobs.append((self.f_conv1, n.conv1.conv.weight.data, bias(n.conv1), 0, 0, False))
         jobs.append((self.d_conv1, n.conv1.conv.weight.data, None, 0, 0, True))
         for s, fq, dq in zip(n.scaler, self.f_scaler, self.d_scaler):
             w, b = s.net[0].conv.weight.data, s.net[0].conv.bias.data
@@ -201,8 +202,10 @@ class TrainPlan:
         if st != key:                                        # new shape / re-allocated parameters: capture again
             self.graphs = {"key": key, "x": x.clone()}
             self.repack()
+            keep = self._warmup_state()
             self._forward_impl(self.graphs["x"])             # eager warm-up: allocates buffers, sets kernel attributes
             torch.cuda.synchronize(self.device)
+            self._warmup_restore(keep)
             # The operand re-pack stays outside the graph: inside it the packed weights are then constants, and the conv
             # nodes can be linked by programmatic edges (each conv's prologue overlaps its predecessor's tail).
             g = torch.cuda.CUDAGraph()
@@ -219,6 +222,13 @@ class TrainPlan:
         self.graphs["fwd"].replay()
         self.saved = self.graphs["saved"]
         return self.graphs["out"]
+
+    def _warmup_state(self):
+        """State the eager warm-up forward must not change (none here; BatchNorm running statistics in BNTrainPlan)."""
+        return None
+
+    def _warmup_restore(self, keep):
+        pass
 
     def backward(self, gout: torch.Tensor) -> list[torch.Tensor]:
         # The gradients handed to autograd are views of the flat arena this call rewrites.  A parameter that still holds
@@ -313,7 +323,8 @@ class TrainPlan:
         backward: weight gradients are off the critical path and every unit is then owned by one CTA)."""
         if self._gjobs is not None:
             self._gjobs.append(dict(x=x, x_planes=x_planes, x_off=x_off, cin=cin, dy=dy, dy_planes=dy_planes, dy_off=dy_off,
-                                    cout=cout, dw=self.grad_views[id(m.conv.weight)], db=self.grad_views[id(m.conv.bias)],
+                                    cout=cout, dw=self.grad_views[id(m.conv.weight)],
+                                    db=None if m.conv.bias is None else self.grad_views[id(m.conv.bias)],
                                     scale=scale / float(self.grad_shift), N=N, H=H, W=W))
 
     def _backward_impl(self, gout: torch.Tensor, run_batch: bool = True) -> list[torch.Tensor]:
@@ -464,6 +475,186 @@ def allreduce_mean_(flat: torch.Tensor, async_op: bool = False):
     return flat
 
 
+class BNTrainPlan(TrainPlan):
+    """Training step of `ResNet` (utils/models.py:592-618): every conv of the trunk is a `Conv` block, conv -> BatchNorm2d -> act
+    (:75-111), in training mode — batch statistics, running-statistics update, and the BatchNorm backward.
+
+    A train-mode BatchNorm needs the whole batch before its first output, so neither the activation (forward) nor the
+    LeakyReLU mask (backward) can ride in the conv's epilogue, and the tile-level conv chains do not apply: every `Conv` is
+        forward   conv (raw y, saved) -> srb_bn_stats -> srb_bn_apply (normalise, act, and the block's residual terms)
+        backward  gathered data-gradient conv (raw dL/da) -> srb_bn_bwd_reduce -> srb_bn_bwd_apply (dL/dy, d gamma, d beta)
+    on the same conv kernels, packed operands, dense activation / gradient buffers, deferred weight-gradient batch, flat
+    gradient arena and CUDA graphs as TrainPlan.  Per-rank statistics under data parallelism (what torch DDP does without
+    SyncBatchNorm; the reference has no multi-GPU training at all)."""
+    allow_bn = True
+
+    def __init__(self, net, device, dtype="fp16", allreduce: bool = True):
+        super().__init__(net, device, dtype, allreduce)
+        self.use_chains = False
+        self.bn_modules = [m for m in net.modules() if isinstance(m, nn.BatchNorm2d)]
+        for m in self.bn_modules:
+            if not m.affine or not m.track_running_stats:
+                raise NotImplementedError("BatchNorm2d without affine parameters / running statistics")
+        nbn = 5 * len(self.rdbs) + 1
+        self.bn_sums = torch.zeros((nbn, 2, 64), dtype=torch.float64, device=device)      # sum y, sum y^2 per `Conv`
+        self.bn_bsums = torch.zeros((nbn, 2, 64), dtype=torch.float64, device=device)     # sum dz, sum dz * x_hat
+        self.bn_pass, self.bn_key = None, None
+
+    def _warmup_state(self):
+        return [(m, m.running_mean.clone(), m.running_var.clone(), m.num_batches_tracked.clone()) for m in self.bn_modules]
+
+    def _warmup_restore(self, keep):
+        for m, rm, rv, nb in keep:
+            m.running_mean.copy_(rm); m.running_var.copy_(rv); m.num_batches_tracked.copy_(nb)
+
+    def _mk_bn(self, idx, m, N, H, W, planes, y, y_planes, y_off, **kw):
+        act = 1 if isinstance(m.act, nn.LeakyReLU) else 0
+        if not isinstance(m.act, (nn.LeakyReLU, nn.Identity)):
+            raise NotImplementedError(f"activation {m.act.__class__.__name__} after BatchNorm")
+        return ops.BatchNormPass(self.ctx, self.dt, N, H, W, planes, y, y_planes, y_off, m.bn.weight.data, m.bn.bias.data,
+                                 self.bn_sums[idx], self.bn_bsums[idx], bn=m.bn, slope=_slope_of(m.act) if act else 0.0, act=act, **kw)
+
+    def _forward_impl(self, x: torch.Tensor) -> torch.Tensor:
+        n = self.net
+        N, _, H, W = x.shape
+        cv = ops.conv2d_ex
+        PARAM_EPOCH[0] += 1            # the running statistics move: inference plans derived from them are stale
+        xin = self._b("xin", N, 1, H, W)
+        ops.nchw_to_c8(x, out=xin, planes=1, dtype=self.dt)
+        nr = len(self.rdbs)
+        dense = [self._b(f"dense{r}", N, 24, H, W) for r in range(nr)]
+        raw = [self._b(f"raw{r}", N, 24, H, W) for r in range(nr)]      # y of conv4 in planes 0..7, of conv_i in planes 8+4i..
+        tr, t, rawc1 = self._b("tr", N, 8, H, W), self._b("t", N, 8, H, W), self._b("rawc1", N, 8, H, W)
+        if self.bn_key != (N, H, W):
+            self.bn_pass, self.bn_key = [], (N, H, W)
+            for r, (rrdb, rdb, _, _, _) in enumerate(self.rdbs):
+                D, Y = dense[r], raw[r]
+                ps = [self._mk_bn(5 * r + i, getattr(rdb, f"conv{i}"), N, H, W, 4, Y, 24, 8 + 4 * i, out=D, out_planes=24,
+                                  out_off=8 + 4 * i) for i in range(4)]
+                dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
+                a, R = float(rdb.add_rate), float(rrdb.add_rate)
+                if r % 3 < 2:      # add_rate * Conv(...) + rdb_in  (utils/models.py:271)
+                    kw = dict(out_scale=a, res=D, res_planes=24, res_off=0, res_scale=1.0)
+                else:              # R * (add_rate * Conv(...) + rdb_in) + rrdb_in  (utils/models.py:317)
+                    kw = dict(out_scale=R * a, res=D, res_planes=24, res_off=0, res_scale=R, res2=dense[r - 2], res2_planes=24,
+                              res2_off=0, res2_scale=1.0)
+                ps.append(self._mk_bn(5 * r + 4, rdb.conv, N, H, W, 8, Y, 24, 0, out=dst, out_planes=dplanes, out_off=0, **kw))
+                self.bn_pass.append(ps)
+            # conv1 + long skip: t = x0 + BN(conv1(trunk))  (utils/models.py:616)
+            self.bn_c1 = self._mk_bn(5 * nr, n.conv1, N, H, W, 8, rawc1, 8, 0, out=t, out_planes=8, out_off=0, res=dense[0],
+                                     res_planes=24, res_off=0, res_scale=1.0)
+        self.bn_sums.zero_()
+        cv(self.f_conv0, xin, 1, 0, dense[0], 24, 0, N, H, W, slope=_slope_of(n.conv0.act), flags=ops.F_LRELU)
+        for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
+            D, Y, ps = dense[r], raw[r], self.bn_pass[r]
+            for i in range(4):
+                cv(fwd[i], D, 24, 0, Y, 24, 8 + 4 * i, N, H, W)
+                ps[i].stats(self.device); ps[i].apply(self.device)
+            cv(fwd[4], D, 24, 0, Y, 24, 0, N, H, W)
+            ps[4].stats(self.device); ps[4].apply(self.device)
+        cv(self.f_conv1, tr, 8, 0, rawc1, 8, 0, N, H, W)
+        self.bn_c1.stats(self.device); self.bn_c1.apply(self.device)
+        cur, h, w, ups = t, H, W, []
+        for k, (s, fq) in enumerate(zip(n.scaler, self.f_scaler)):
+            up = self._b(f"up{k}", N, 8, 2 * h, 2 * w)
+            sl = _slope_of(s.net[2])
+            for q in range(4):
+                cv(fq[q], cur, 8, 0, up, 8, 2 * q, N, h, w, slope=sl, flags=ops.F_LRELU | ops.F_PIXSHUF2)
+            ups.append((cur, up, h, w))
+            cur, h, w = up, 2 * h, 2 * w
+        out = torch.empty((N, 3, h, w), dtype=torch.float32, device=self.device)
+        tanh = ops.F_TANH if isinstance(n.conv2.act, nn.Tanh) else 0
+        cv(self.f_conv2, cur, 8, 0, out, 0, 0, N, h, w, flags=tanh | ops.F_F32OUT)
+        self.saved = dict(N=N, H=H, W=W, xin=xin, dense=dense, raw=raw, rawc1=rawc1, tr=tr, t=t, ups=ups, out=out, tanh=bool(tanh))
+        return out
+
+    def _backward_impl(self, gout: torch.Tensor, run_batch: bool = True) -> list[torch.Tensor]:
+        sv, n = self.saved, self.net
+        if sv is None:
+            raise RuntimeError("backward without a saved forward")
+        N, H, W = sv["N"], sv["H"], sv["W"]
+        cv = ops.conv2d_ex
+        gv = self.grad_views
+        self.flat_grad.zero_()
+        self.bn_bsums.zero_()
+        gkey = (N, H, W, tuple(sv["out"].shape))
+        first = self.grad_batch is None or self.grad_key != gkey
+        self._gjobs = [] if first else None
+        gout = gout.float().contiguous()
+        h2, w2 = sv["out"].shape[2], sv["out"].shape[3]
+        if not sv["tanh"]:
+            raise NotImplementedError("tail conv without tanh")
+        sh, ish = float(self.grad_shift), 1.0 / float(self.grad_shift)
+        # ---- tail conv and scalers: ConvWithoutBN, as TrainPlan
+        g2 = ops.tanh_bwd_to_c8(gout, sv["out"], self.dt, scale=sh, g8=self._b("g2", N, 1, h2, w2))
+        up_last = sv["ups"][-1][1] if sv["ups"] else sv["t"]
+        ops.conv9_wgrad(up_last, 8, 0, 64, g2, 1, 0, 3, gv[id(n.conv2.conv.weight)], N, h2, w2, scale=ish)
+        if self._gjobs is not None:
+            self._gjobs.append(dict(dy=g2, dy_planes=1, dy_off=0, cout=3, db=gv[id(n.conv2.conv.bias)], N=N, H=h2, W=w2, scale=ish))
+        g_cur = self._b("g_up_last", N, 8, h2, w2)
+        cv(self.d_conv2, g2, 1, 0, g_cur, 8, 0, N, h2, w2)
+        for k in range(len(sv["ups"]) - 1, -1, -1):
+            cur_in, up, h, w = sv["ups"][k]
+            s = n.scaler[k]
+            g_s = self._b(f"g_s{k}", N, 32, h, w)
+            ops.pixunshuffle_mask(g_cur, up, g_s, _slope_of(s.net[2]))
+            self._wb(s.net[0], cur_in, 8, 0, 64, g_s, 32, 0, 256, N, h, w)
+            g_in = self._b(f"g_in{k}", N, 8, h, w)
+            cv(self.d_scaler[k], g_s, 32, 0, g_in, 8, 0, N, h, w)
+            g_cur = g_in
+        g_t = g_cur                                         # gradient of t = x0 + BN(conv1(trunk))
+        nr = len(self.rdbs)
+        Gd = [self._b(f"G{j}", N, 24, H, W) for j in range(nr)]     # [dY4 | dY3 | dY2 | dY1 | dY0]: gradients of the convs' RAW outputs
+        GY = [self._b(f"GY{j}", N, 8, H, W) for j in range(nr)]     # gradient of the RDB's output (the residual term of the block in front)
+        T = self._b("g_da", N, 4, H, W)                             # dL/da_k before the BatchNorm backward
+        dyc1 = self._b("g_yc1", N, 8, H, W)
+        gxf = self._b("g_x0t", N, 8, H, W)
+        if first:
+            self.bn_c1.set_backward(g_t, 8, 0, dyc1, 8, 0, gv[id(n.conv1.bn.weight)], gv[id(n.conv1.bn.bias)], 1.0, ish)
+            for r, (rrdb, rdb, _, _, _) in enumerate(self.rdbs):
+                a, R = float(rdb.add_rate), float(rrdb.add_rate)
+                s_out = a * R if r % 3 == 2 else a
+                ps, G = self.bn_pass[r], Gd[r]
+                # the block's output scale stays folded into the transposed filters (TrainPlan._pack_jobs), so G[0..7] holds the
+                # BatchNorm backward of the UNSCALED gy and only the parameter gradients carry s_out
+                ps[4].set_backward(GY[r], 8, 0, G, 24, 0, gv[id(rdb.conv.bn.weight)], gv[id(rdb.conv.bn.bias)], 1.0, s_out * ish)
+                for k in range(4):
+                    m = getattr(rdb, f"conv{k}")
+                    ps[k].set_backward(T, 4, 0, G, 24, 8 + 4 * (3 - k), gv[id(m.bn.weight)], gv[id(m.bn.bias)], 1.0, ish)
+        # ---- conv1: BatchNorm backward, weight gradient, data gradient -> gy of the last RDB
+        self.bn_c1.bwd_reduce(self.device); self.bn_c1.bwd_apply(self.device)
+        self._wb(n.conv1, sv["tr"], 8, 0, 64, dyc1, 8, 0, 64, N, H, W)
+        cv(self.d_conv1, dyc1, 8, 0, GY[nr - 1], 8, 0, N, H, W)
+        for r in range(nr - 1, -1, -1):
+            rrdb, rdb, _, stage, fin = self.rdbs[r]
+            D, G, ps = sv["dense"][r], Gd[r], self.bn_pass[r]
+            d = r % 3
+            a, R = float(rdb.add_rate), float(rrdb.add_rate)
+            s_out, s_res = (a * R, R) if d == 2 else (a, 1.0)
+            ps[4].bwd_reduce(self.device); ps[4].bwd_apply(self.device)                  # GY[r] -> G[0..7]
+            self._wb(rdb.conv, D, 24, 0, 192, G, 24, 0, 64, N, H, W, scale=s_out)
+            for k in range(3, -1, -1):
+                nin = 8 + 4 * (3 - k)
+                cv(stage[k], G, 24, 0, T, 4, 0, N, H, W)                                 # dL/da_k from everything to its left
+                ps[k].bwd_reduce(self.device); ps[k].bwd_apply(self.device)              # -> dY_k = G[nin .. nin+4)
+                self._wb(getattr(rdb, f"conv{k}"), D, 24, 0, 64 + 32 * k, G, 24, nin, 32, N, H, W)
+            dst = GY[r - 1] if r > 0 else gxf
+            kw = dict(residual=GY[r], res_planes=8, res_off=0, res_scale=s_res)
+            if d == 0:                                                                    # + the RRDB skip
+                kw.update(res2=GY[r + 2], res2_planes=8, res2_off=0, res2_scale=1.0)
+            cv(fin, G, 24, 0, dst, 8, 0, N, H, W, **kw)
+        # ---- head conv
+        gx0 = self._b("gx0", N, 8, H, W)
+        ops.c8_axpby_mask(gxf, 8, 0, 1.0, g_t, 8, 0, 1.0, sv["dense"][0], 24, 0, _slope_of(n.conv0.act), gx0, 8, 0, 8, N, H, W)
+        ops.conv9_wgrad(sv["xin"], 1, 0, 3, gx0, 8, 0, 64, gv[id(n.conv0.conv.weight)], N, H, W, scale=ish)
+        if self._gjobs is not None:
+            self._gjobs.append(dict(dy=gx0, dy_planes=8, dy_off=0, cout=64, db=gv[id(n.conv0.conv.bias)], N=N, H=H, W=W, scale=ish))
+            self.grad_batch, self.grad_key = ops.GradBatch(self.ctx, self._gjobs, self.dt), gkey
+            self.grad_parts = None
+            self._gjobs = None
+        self.grad_batch.run(self.device, self.wgrad_splitk)
+        return [gv[id(p)] for p in self.params]
+
 class _NetFunction(torch.autograd.Function):
     """preds = net(lr) with the whole forward / backward on the sm_100a kernels (train.py:55,57)."""
 
@@ -485,21 +676,26 @@ def train_forward(net, x: torch.Tensor) -> torch.Tensor:
     plans = net.__dict__.setdefault("_train_plans", {})
     plan = plans.get(x.device)
     if plan is None:           # (also after deepcopy(model): see TrainPlan.__deepcopy__)
-        plan = plans[x.device] = TrainPlan(net, x.device, getattr(net, "train_operand_dtype", "fp16"))
+        bns = [m for m in net.modules() if isinstance(m, nn.BatchNorm2d)]
+        cls = BNTrainPlan if bns else TrainPlan
+        plan = plans[x.device] = cls(net, x.device, getattr(net, "train_operand_dtype", "fp16"))
+    if plan.allow_bn and not all(m.training for m in plan.bn_modules):
+        raise NotImplementedError("gradients through eval-mode BatchNorm (running statistics) are not on the sm_100a path: "
+                                  "net.train() for training, torch.no_grad() for inference")
     return _NetFunction.apply(x.float().contiguous(), plan, *plan.params)
 
 
 class _L1Function(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pred, tgt, w):
+    def forward(ctx, pred, tgt, w, squared=False):
         ctx.save_for_backward(pred, tgt)
-        ctx.w = w
-        return ops.l1_loss_fwd(pred, tgt, w)
+        ctx.w, ctx.squared = w, squared
+        return ops.l1_loss_fwd(pred, tgt, w, squared)
 
     @staticmethod
     def backward(ctx, g):
         pred, tgt = ctx.saved_tensors
-        return ops.l1_loss_bwd_dev(pred, tgt, g, ctx.w), None, None
+        return ops.l1_loss_bwd_dev(pred, tgt, g, ctx.w, ctx.squared), None, None, None
 
 
 class L1Loss(nn.Module):
@@ -524,3 +720,21 @@ class L1Loss(nn.Module):
         pred = inputs.contiguous()
         tgt = ground_truth.float().contiguous()
         return _L1Function.apply(pred, tgt, self._weight())
+
+
+class MSELoss(nn.Module):
+    """torch.nn.MSELoss() as train.py uses it (train.py:13, :233, :264: the loss of a run without --enchant; default mean reduction)
+    on the library's deterministic reduction kernels: loss = mean((pred - target)^2), d/dpred = 2 (pred - target) / numel."""
+
+    def __init__(self, size_average=None, reduce=None, reduction: str = "mean"):
+        super().__init__()
+        if size_average is not None or reduce is not None or reduction != "mean":
+            raise NotImplementedError("MSELoss: only the default mean reduction is on the sm_100a path (train.py:233)")
+        self.reduction = reduction
+
+    def forward(self, inputs: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if not inputs.is_cuda:
+            raise RuntimeError("the B200 path has no CPU fallback: move predictions and targets to a CUDA device")
+        if inputs.shape != target.shape:
+            raise RuntimeError(f"MSELoss: shapes differ: {tuple(inputs.shape)} vs {tuple(target.shape)}")
+        return _L1Function.apply(inputs.contiguous(), target.float().contiguous(), 1.0, True)

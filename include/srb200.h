@@ -353,6 +353,46 @@ int srb_l1_loss_fwd_noalloc(srb_ctx* ctx, const void* pred, int pred_dtype, cons
 int srb_l1_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
                         float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream);
 
+/* Train-mode nn.BatchNorm2d of the reference's `Conv` block (utils/models.py:75-111: conv -> BatchNorm2d -> act), for the `ResNet`
+ * generator trained by train.py:41-67.  The conv stores its raw output y (16-bit C8 planes, no bias, no
+ * activation); the four passes below work on a slice of `planes` planes (8 channels each) of the batch N x H x W:
+ *   srb_bn_stats        sums[c] += sum y, sums[C + c] += sum y^2           (the caller zeroes `sums`, 2 * C doubles, before the step)
+ *   srb_bn_apply        out = out_scale * act(gamma * (y - mean) / sqrt(var + eps) + beta) + res_scale * res + res2_scale * res2
+ *                       with the biased batch variance; moves running_mean / running_var (momentum, unbiased variance) and
+ *                       num_batches_tracked exactly as torch does in training mode (all three may be NULL)
+ *   srb_bn_bwd_reduce   dz = up_scale * da * act'(z);  bsums[c] += sum dz, bsums[C + c] += sum dz * x_hat   (caller zeroes `bsums`)
+ *   srb_bn_bwd_apply    out = dL/dy = gamma / sqrt(var + eps) * (dz - mean(dz) - x_hat * mean(dz * x_hat));
+ *                       dgamma += grad_scale * sum dz * x_hat, dbeta += grad_scale * sum dz   (fp32, either may be NULL)
+ * act: 0 identity, 1 LeakyReLU(slope).  Sums are accumulated in double with atomics: results are deterministic to fp32 rounding. */
+typedef struct srb_bn_args {
+    const void* y; int y_c8_total, y_c8_off;
+    void* out; int out_c8_total, out_c8_off;
+    int planes;
+    const float* gamma; const float* beta;
+    double* sums;
+    float* running_mean; float* running_var; long long* num_batches_tracked;
+    float momentum, eps;
+    float slope; int act;
+    float out_scale;
+    const void* res; int res_c8_total, res_c8_off; float res_scale;
+    const void* res2; int res2_c8_total, res2_c8_off; float res2_scale;
+    const void* da; int da_c8_total, da_c8_off; float up_scale;
+    double* bsums;
+    float* dgamma; float* dbeta; float grad_scale;
+    int N, H, W;
+} srb_bn_args;
+int srb_bn_stats(srb_ctx* ctx, const srb_bn_args* args, int dtype, srb_stream_t stream);
+int srb_bn_apply(srb_ctx* ctx, const srb_bn_args* args, int dtype, srb_stream_t stream);
+int srb_bn_bwd_reduce(srb_ctx* ctx, const srb_bn_args* args, int dtype, srb_stream_t stream);
+int srb_bn_bwd_apply(srb_ctx* ctx, const srb_bn_args* args, int dtype, srb_stream_t stream);
+
+/* nn.MSELoss() (train.py:13, :233, :264 — the loss of `train.py` without --enchant): loss = w * mean((pred - tgt)^2), and
+ * dpred = w * grad_scale * (*grad_out_dev) * 2 (pred - tgt) / n.  Same kernels, scratch and determinism as the L1 pair. */
+int srb_mse_loss_fwd(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                     float* loss_out, float* partials, srb_stream_t stream);
+int srb_mse_loss_bwd_dev(srb_ctx* ctx, const void* pred, int pred_dtype, const float* tgt, size_t n, float w,
+                         float grad_scale, const float* grad_out_dev, void* dpred, srb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,3 +18,15 @@ def l1_loss(pred: np.ndarray, tgt: np.ndarray, w: float = 1.0) -> np.float32:
 def l1_grad(pred: np.ndarray, tgt: np.ndarray, w: float = 1.0, grad_scale: float = 1.0) -> np.ndarray:
     d = pred.astype(np.float32) - tgt.astype(np.float32)
     return (np.sign(d) * np.float32(w * grad_scale / d.size)).astype(np.float32)
+
+
+# nn.MSELoss() — train.py:13, :233, :264 (the loss of a run without --enchant), default mean reduction:
+# mean((x - y)^2);  d/dx = 2 (x - y) / numel.  Pinned against torch.nn.MSELoss itself in tests/test_oracle.py.
+def mse_loss(pred: np.ndarray, tgt: np.ndarray, w: float = 1.0) -> np.float32:
+    d = pred.astype(np.float32) - tgt.astype(np.float32)
+    return np.float32(w * (d.astype(np.float64) ** 2).sum() / d.size)
+
+
+def mse_grad(pred: np.ndarray, tgt: np.ndarray, w: float = 1.0, grad_scale: float = 1.0) -> np.ndarray:
+    d = pred.astype(np.float32) - tgt.astype(np.float32)
+    return (np.float32(2.0) * d * np.float32(w * grad_scale / d.size)).astype(np.float32)

@@ -11,13 +11,19 @@ import torch
 import torch.nn.functional as F
 
 
+_BN_TRAIN = [False]     # resnet_forward_train: BatchNorm with batch statistics (nn.BatchNorm2d in training mode)
+
+
 def _conv(x, sd, prefix, pad):
     w = sd[prefix + ".conv.weight"]
     b = sd.get(prefix + ".conv.bias")
     y = F.conv2d(x, w, b, padding=pad)
-    if prefix + ".bn.weight" in sd:  # Conv with BatchNorm in eval mode (utils/models.py:97-98)
+    if prefix + ".bn.weight" in sd:  # Conv with BatchNorm (utils/models.py:97-98): eval mode = running statistics;
+        # training mode = batch statistics, and the running buffers move by momentum 0.1 (F.batch_norm updates them in place)
         y = F.batch_norm(y, sd[prefix + ".bn.running_mean"], sd[prefix + ".bn.running_var"], sd[prefix + ".bn.weight"],
-                         sd[prefix + ".bn.bias"], False, 0.0, 1e-5)
+                         sd[prefix + ".bn.bias"], _BN_TRAIN[0], 0.1 if _BN_TRAIN[0] else 0.0, 1e-5)
+        if _BN_TRAIN[0] and prefix + ".bn.num_batches_tracked" in sd:
+            sd[prefix + ".bn.num_batches_tracked"] += 1
     return y
 
 
@@ -48,6 +54,16 @@ def resnet_forward(x, sd, num_block, add_rate=0.2, scale=2, conv0_slope=0.01):
     for k in range(scale // 2):
         y = F.leaky_relu(F.pixel_shuffle(_conv(y, sd, f"scaler.{k}.net.0", 1), 2), 0.01)
     return torch.tanh(_conv(y, sd, "conv2", 4))
+
+
+def resnet_forward_train(x, sd, num_block, add_rate=0.2, scale=2, conv0_slope=0.2):
+    """ResNet.forward (utils/models.py:613-618) in TRAINING mode, differentiable (train.py:55-57): BatchNorm normalises with the
+    batch's own mean / biased variance and moves sd's running_mean / running_var / num_batches_tracked in place."""
+    _BN_TRAIN[0] = True
+    try:
+        return resnet_forward.__wrapped__(x, sd, num_block, add_rate, scale, conv0_slope)
+    finally:
+        _BN_TRAIN[0] = False
 
 
 def make_lr_hr(seed: int, n: int, hr: int, scale: int = 2):

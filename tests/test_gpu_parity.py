@@ -333,6 +333,35 @@ def test_l1_loss_kernels(dev, golden_dir):
     assert np.array_equal(gr, l1_oracle.l1_grad(p.numpy(), t.numpy(), 1.0, 1024.0))
 
 
+def test_mse_loss_module_matches_oracle_and_autograd(dev):
+    """srb.MSELoss (nn.MSELoss of train.py:264) on the library's kernels: value within 1e-6 rel of the oracle, gradient
+    2 (p - t) / n times the upstream factor (GradScaler's scale) to fp32 rounding; fp16 predictions get an fp16 gradient."""
+    import image_super_resolution_b200 as srb
+    from oracle import l1_oracle
+    g = torch.Generator().manual_seed(3)
+    p = (torch.rand(16, 3, 128, 128 + 1, generator=g) * 2 - 1)             # ragged tail: numel % 4 != 0
+    t = (torch.rand(16, 3, 128, 128 + 1, generator=g) * 2 - 1)
+    pd = p.to(dev).requires_grad_(True)
+    loss = srb.MSELoss()(pd, t.to(dev))
+    (loss * 65536.0).backward()
+    want = float(l1_oracle.mse_loss(p.numpy(), t.numpy()))
+    assert abs(loss.item() - want) <= 1e-6 * want
+    ref = l1_oracle.mse_grad(p.numpy(), t.numpy(), 1.0, 65536.0)
+    assert np.abs(pd.grad.cpu().numpy() - ref).max() <= 2e-7 * np.abs(ref).max()
+    ph = p.half().to(dev).requires_grad_(True)
+    lh = srb.MSELoss()(ph, t.to(dev))
+    (lh * 65536.0).backward()
+    want16 = float(l1_oracle.mse_loss(p.half().float().numpy(), t.numpy()))
+    assert abs(lh.item() - want16) <= 1e-6 * want16
+    ref16 = l1_oracle.mse_grad(p.half().float().numpy(), t.numpy(), 1.0, 65536.0)
+    assert ph.grad.dtype == torch.float16
+    assert np.abs(ph.grad.float().cpu().numpy() - ref16).max() <= 1e-3 * np.abs(ref16).max()
+    with pytest.raises(NotImplementedError):
+        srb.MSELoss(reduction="sum")
+    with pytest.raises(RuntimeError):
+        srb.MSELoss()(torch.zeros(2, 3), torch.zeros(2, 3))                 # CPU tensors
+
+
 def test_bad_arguments_raise(model, dev, ctx):
     from image_super_resolution_b200 import ops
     with pytest.raises(RuntimeError):

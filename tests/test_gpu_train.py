@@ -273,6 +273,38 @@ def test_reference_train_loop_runs_on_dropin(dev):
     assert losses[-1] < losses[0] * 0.95 and all(np.isfinite(losses)), losses
 
 
+def test_reference_default_run_resnet_bn_mse_trains(dev):
+    """The reference's DEFAULT training run (train.py:262-264 without --enchant): SRGAN(enchant=False) = `ResNet` with train-mode
+    BatchNorm, nn.MSELoss — the loop of train.py:41-67 call for call on the drop-ins (BNTrainPlan + MSELoss kernels): the loss
+    goes down on a fixed batch, the running statistics move, every step finite."""
+    import image_super_resolution_b200 as srb
+    from oracle import nets_oracle as no
+    torch.manual_seed(100)
+    net = srb.SRGAN(1, 0.2, enchant=False, scaleRate=2).to(dev).train()
+    hr, lr = no.make_lr_hr(11, 4, 32, 2)
+    hr, lr = hr.to(dev), lr.to(dev)
+    loss_fn = srb.MSELoss()
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3, betas=(0.9, 0.999))
+    scaler = torch.amp.GradScaler("cuda")
+    losses = []
+    for _ in range(20):
+        opt.zero_grad()
+        with torch.autocast(device_type="cuda"):
+            preds = net(lr)
+            loss = loss_fn(preds, hr)
+        scaler.scale(loss).backward()
+        scaler.unscale_(opt)
+        torch.nn.utils.clip_grad_norm_(net.parameters(), 10)
+        scaler.step(opt)
+        scaler.update()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0] * 0.9 and all(np.isfinite(losses)), losses
+    bn = net.res_net.conv1.bn
+    assert int(bn.num_batches_tracked.item()) == 20 and float(bn.running_var.sub(1).abs().max()) > 1e-3
+    from image_super_resolution_b200._lib import Context
+    Context.get(0).check_device()
+
+
 def test_batched_gradients_match_single_launches(ctx, dev):
     """srb_grad_batch (weight gradients with the bias gradient riding on the first input-channel block of every conv, with and
     without split-K) == srb_conv2d_wgrad / srb_bias_grad per conv."""

@@ -265,3 +265,108 @@ def test_gpu_denoise_model_wrapper_uint8_fuse_and_larger_frame(gold_dn):
     assert y.dtype == torch.uint8 and y.shape == ref.shape
     d = (y.int() - ref.int()).abs()
     assert int(d.max()) <= 2 and float((d == 0).float().mean()) >= 0.97, (int(d.max()), float((d == 0).float().mean()))
+
+
+# --------------------------------------------------------------------------------------------------------------------------
+# ResNet in training mode (BatchNorm batch statistics): utils/models.py:592-618 under train.py:55-57
+# --------------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gold_rt(golden_dir):
+    return np.load(os.path.join(golden_dir, "resnet_train_golden.npz"))
+
+
+def _build_resnet_train():
+    from image_super_resolution_b200 import models
+    torch.manual_seed(100)
+    net = models.ResNet(1, 0.2, 2).train()
+    g = torch.Generator().manual_seed(111)        # tools/make_golden.py golden_resnet_train()
+    with torch.no_grad():
+        for m in net.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.weight.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    return net
+
+
+def _grad_checks(named_grads, gold_rt, rtol):
+    names = list(gold_rt["grad.names"])
+    assert [n for n, _ in named_grads] == names
+    for i, (name, g) in enumerate(named_grads):
+        r = torch.randn(g.numel(), generator=torch.Generator().manual_seed(i), dtype=torch.float64)
+        scale = float(gold_rt["grad.abssums"][i]) + 1e-30
+        assert abs(float(g.double().sum()) - float(gold_rt["grad.sums"][i])) <= rtol * scale, name
+        assert abs(float(g.double().abs().sum()) - scale) <= rtol * scale, name
+        assert abs(float(g.double().flatten() @ r) - float(gold_rt["grad.proj"][i])) <= rtol * scale * 4, name
+
+
+def test_resnet_train_mode_oracle_matches_reference(gold_rt):
+    """The oracle's training-mode restatement (batch-statistics BatchNorm, autograd, running-buffer update) against the reference
+    class's own training step: output, loss, every gradient (checksums + a random projection) and every BatchNorm buffer."""
+    net = _build_resnet_train()
+    sd = {k: (v.detach().clone().requires_grad_(True) if v.dtype.is_floating_point and "running" not in k else v.detach().clone())
+          for k, v in net.state_dict().items()}
+    lr, hr = torch.from_numpy(gold_rt["lr"]), torch.from_numpy(gold_rt["hr"])
+    out = no.resnet_forward_train(lr, sd, 1, 0.2, 2, conv0_slope=0.2)
+    loss = (out - hr).abs().mean()
+    loss.backward()
+    assert np.abs(out.detach().numpy() - gold_rt["out"]).max() <= 2e-5
+    assert abs(loss.item() - float(gold_rt["loss"])) <= 1e-6
+    _grad_checks([(n, sd[n].grad) for n, _ in net.named_parameters()], gold_rt, 2e-4)
+    bn = np.concatenate([sd[k].detach().double().numpy().reshape(-1) for k in gold_rt["bn.keys"]])
+    assert np.abs(bn - gold_rt["bn.values"]).max() <= 1e-5
+
+
+@pytest.mark.gpu
+def test_gpu_resnet_train_step_matches_reference_and_fp32_autograd(gold_rt):
+    """The drop-in ResNet in train() mode on the sm_100a path (training.BNTrainPlan): output and loss against the reference's
+    training-mode golden, every gradient against fp32 autograd of the oracle (cosine >= 0.999), the BatchNorm
+    running statistics / num_batches_tracked against the reference's — after ONE step although the plan warms up, captures
+    and replays the forward — and eval() afterwards uses the moved statistics."""
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    import image_super_resolution_b200 as srb
+    dev = torch.device("cuda:0")
+    net = _build_resnet_train()
+    sd = {k: (v.detach().clone().requires_grad_(True) if v.dtype.is_floating_point and "running" not in k else v.detach().clone())
+          for k, v in net.state_dict().items()}
+    lr, hr = torch.from_numpy(gold_rt["lr"]), torch.from_numpy(gold_rt["hr"])
+    ref_out = no.resnet_forward_train(lr, sd, 1, 0.2, 2, conv0_slope=0.2)
+    (ref_out - hr).abs().mean().backward()
+    net = net.to(dev).train()
+    out = net(lr.to(dev))
+    loss = srb.L1Loss()(out, hr.to(dev))
+    (loss * 65536.0).backward()
+    torch.cuda.synchronize()
+    srb._lib.Context.get(0).check_device()
+    assert np.abs(out.detach().cpu().numpy() - gold_rt["out"]).max() <= 2e-2
+    assert abs(loss.item() - float(gold_rt["loss"])) <= 1e-2 * float(gold_rt["loss"])
+    rows = []
+    for name, p in net.named_parameters():
+        got, ref = p.grad.detach().cpu().double().flatten() / 65536.0, sd[name].grad.double().flatten()
+        cos = float(got @ ref / (got.norm() * ref.norm() + 1e-300))
+        rows.append((cos, abs(float(got.norm() / (ref.norm() + 1e-300)) - 1), name))
+    print(f"ResNet(1) train step: {len(rows)} tensors, gradient cosine min {min(r[0] for r in rows):.5f}, |norm ratio - 1| max "
+          f"{max(r[1] for r in rows):.4f}; worst: " + ", ".join(f"{n} {c:.5f}" for c, _, n in sorted(rows)[:4]))
+    # conv filters: the 0.999 of the EResNet contract.  BatchNorm gamma / beta gradients are 32- or 64-element vectors, each element
+    # a signed sum over all pixels of 16-bit data gradients: measured 0.9987 .. 0.99999 (fp16 operands, the reference's own
+    # autocast precision) -> 0.998 for those
+    bad = [(n, round(c, 5), round(d, 4)) for c, d, n in rows if c < (0.998 if ".bn." in n else 0.999) or d > 2e-2]
+    assert not bad, bad[:10]
+    got_sd = net.state_dict()
+    for k in gold_rt["bn.keys"]:
+        a, b = got_sd[str(k)].detach().cpu().double().reshape(-1), sd[str(k)].detach().double().reshape(-1)
+        assert (a - b).abs().max().item() <= 2e-3 * max(1.0, b.abs().max().item()), k
+    assert int(net.conv1.bn.num_batches_tracked.item()) == 1          # warm-up + capture + replay = ONE update
+    # a second step moves the statistics once more (graph replay), and eval() runs on them
+    for p in net.parameters():
+        p.grad = None
+    out2 = net(lr.to(dev))
+    (srb.L1Loss()(out2, hr.to(dev)) * 65536.0).backward()
+    assert int(net.conv1.bn.num_batches_tracked.item()) == 2
+    ref2 = no.resnet_forward_train(lr, {k: v.detach() for k, v in sd.items()}, 1, 0.2, 2, conv0_slope=0.2)
+    assert (out2.detach().cpu() - ref2).abs().max().item() <= 2e-2
+    net.eval()
+    with torch.no_grad():
+        ye = net(lr.to(dev)).cpu()
+    ref_e = no.resnet_forward(lr, {k: v.detach() for k, v in sd.items()}, 1, 0.2, 2, conv0_slope=0.2)
+    assert (ye - ref_e).abs().max().item() <= 2e-2

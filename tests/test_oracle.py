@@ -84,3 +84,17 @@ def test_l1_oracle_matches_reference(golden_dir):
         assert np.array_equal(l1_oracle.l1_grad(p, t), g[name + ".grad"])
     gb = l1_oracle.l1_grad(g["b.pred"], g["b.tgt"])
     assert np.all(gb[0, 0, 0, :3] == 0)  # sign(0) = 0 on exact ties
+
+
+def test_mse_oracle_matches_torch_mseloss():
+    """nn.MSELoss() is the reference's loss without --enchant (train.py:264): value and gradient of the restatement against torch."""
+    import torch
+    from oracle import l1_oracle
+    g = torch.Generator().manual_seed(100)
+    p = (torch.rand(4, 3, 32, 48, generator=g) * 2 - 1).requires_grad_(True)
+    t = torch.rand(4, 3, 32, 48, generator=g) * 2 - 1
+    loss = torch.nn.MSELoss()(p, t)
+    (loss * 1024.0).backward()
+    assert abs(float(l1_oracle.mse_loss(p.detach().numpy(), t.numpy())) - float(loss)) <= 1e-6 * float(loss)
+    got = l1_oracle.mse_grad(p.detach().numpy(), t.numpy(), 1.0, 1024.0)
+    assert np.abs(got - p.grad.numpy()).max() <= 1e-6 * np.abs(p.grad.numpy()).max()

@@ -11,13 +11,16 @@ from image_super_resolution_b200.training import L1Loss
 dev = torch.device("cuda:0")
 B = 16
 torch.manual_seed(100)
-net = models.EResNet(16, 0.2, 2).to(dev)
-for kv in sys.argv[2:]:                      # e.g. train_conv_fold=1 train_chain_nt4=1
-    k, v = kv.split("="); setattr(net, k, int(v))
+opts = dict(kv.split("=") for kv in sys.argv[2:])
+net = getattr(models, opts.pop("cls", "EResNet"))(16, 0.2, 2).to(dev)        # cls=ResNet: train-mode BatchNorm (BNTrainPlan)
+loss_name = opts.pop("loss", "l1")
+for k, v in opts.items():                    # e.g. train_conv_fold=1 train_chain_nt4=1
+    setattr(net, k, int(v))
 g = torch.Generator().manual_seed(100)
 hr = (torch.rand(B, 3, 128, 128, generator=g) * 2 - 1).to(dev)
 lr = torch.randn(B, 3, 64, 64, generator=g).to(dev)
-loss_fn = L1Loss().to(dev)
+from image_super_resolution_b200.training import MSELoss
+loss_fn = (MSELoss() if loss_name == "mse" else L1Loss()).to(dev)
 mode = sys.argv[1] if len(sys.argv) > 1 else "foreach"      # foreach | fused (torch Adam fused=True) | flat (optim.FlatAdam tail)
 fused = mode
 if mode == "flat":

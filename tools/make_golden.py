@@ -237,6 +237,40 @@ def golden_denoise():
     print("denoise_golden.npz: params", sum(p.numel() for p in net.parameters()), "keys", len(sd), "out", tuple(y.shape), "mean|y|", float(y.abs().mean()))
 
 
+def golden_resnet_train():
+    """One TRAINING step's forward + backward of the reference `ResNet(1, 0.2, 2)` (utils/models.py:592-618) in train mode —
+    BatchNorm batch statistics, running-statistics update, autograd through it — with nn.L1Loss on a seeded batch, CPU fp32.
+    Stored: the output, the loss, every updated BatchNorm buffer, and per-gradient checksums (sum, |sum|, a seeded random
+    projection): the drop-in re-creates the weights from the same seed."""
+    from utils.models import ResNet
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    from oracle.nets_oracle import make_lr_hr
+    torch.manual_seed(SEED)
+    net = ResNet(1, 0.2, 2).train()
+    g = torch.Generator().manual_seed(SEED + 11)
+    with torch.no_grad():
+        for m in net.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.weight.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    hr, lr = make_lr_hr(SEED + 13, 4, 48, 2)          # LR 24 x 24, B = 4
+    y = net(lr.clone())
+    loss = torch.nn.L1Loss()(y, hr)
+    loss.backward()
+    out = {"lr": lr.numpy(), "hr": hr.numpy(), "out": y.detach().numpy(), "loss": np.float32(loss.item())}
+    names, sums, abss, proj = [], [], [], []
+    for name, p in net.named_parameters():
+        r = torch.randn(p.numel(), generator=torch.Generator().manual_seed(len(names)), dtype=torch.float64)
+        names.append(name); sums.append(float(p.grad.double().sum())); abss.append(float(p.grad.double().abs().sum()))
+        proj.append(float(p.grad.double().flatten() @ r))
+    out["grad.names"], out["grad.sums"], out["grad.abssums"], out["grad.proj"] = np.array(names), np.array(sums), np.array(abss), np.array(proj)
+    bn = {k: v.numpy() for k, v in net.state_dict().items() if "running_" in k or "num_batches" in k}
+    out["bn.keys"] = np.array(list(bn.keys()))
+    out["bn.values"] = np.concatenate([np.asarray(v, dtype=np.float64).reshape(-1) for v in bn.values()])
+    np.savez_compressed(os.path.join(OUT, "resnet_train_golden.npz"), **out)
+    print("resnet_train_golden.npz: loss", float(loss), "tensors", len(names), "bn buffers", len(bn))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(os.cpu_count() or 1)
     install_stubs()
@@ -248,3 +282,4 @@ if __name__ == "__main__":
     golden_nets()
     golden_eresnet16()
     golden_denoise()
+    golden_resnet_train()
