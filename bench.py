@@ -408,6 +408,18 @@ def run_ours(args, rank, world, local):
         assert n == nl, (n, nl)
         for i in range(nl):
             acc[i] += buf[i]
+    # the trunk's eight fused blocks overlap through programmatic dependent launch (a block's prologue runs under its predecessor's
+    # tail): their AVERAGE duration inside the pipeline = the trunk's span / 8, events only around the trunk
+    trunk_ms = None
+    if nl == len(FUSED_NAMES):
+        check(lib().srb_profile_enable(ctxh, 2))
+        t_acc = 0.0
+        for _ in range(K):
+            model(x, out=y)
+            n = lib().srb_profile_read(ctxh, buf, 64)
+            assert n == 3, n
+            t_acc += buf[1]
+        trunk_ms = t_acc / K
     check(lib().srb_profile_enable(ctxh, 0))
     per_launch = [a / K for a in acc]
     groups = {}
@@ -418,9 +430,19 @@ def run_ours(args, rank, world, local):
     kernels = {k: {"launches": v[0], "ms_per_launch": v[1] / v[0], "tflops": (v[2] / v[0]) / (v[1] / v[0]) / 1e9,
                    "share": v[1] / sum(per_launch)} for k, v in groups.items()}
     top = max(groups, key=lambda k: groups[k][1])
-    achieved = kernels[top]["tflops"]
+    isolated = kernels[top]["tflops"]
+    achieved = isolated
+    pipe = None
+    if trunk_ms is not None and top == "resblock_64_32_64_fused":
+        # average launch duration of the dominant kernel as it runs in the timed region (overlapping launches)
+        ms_launch = trunk_ms / 8
+        achieved = (groups[top][2] / groups[top][0]) / ms_launch / 1e9
+        pipe = {"ms_per_launch": ms_launch, "tflops": achieved, "how": "CUDA events before the first and after the last of the eight "
+                "back-to-back launches, / 8", "isolated_ms_per_launch": kernels[top]["ms_per_launch"], "isolated_tflops": isolated,
+                "isolated_frac": isolated / pk["bf16_tflops"],
+                "isolated_how": "an event after every launch (ends the overlap between launches)"}
     roofline = {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                "frac": achieved / pk["bf16_tflops"],
+                "frac": achieved / pk["bf16_tflops"], "in_pipeline": pipe,
                 "traffic": NCU_TRAFFIC_BYTES.get(top) if (BATCH, HH, WW) == NCU_TRAFFIC_SHAPE else None,
                 "peak_source": f"{pk['source']} burst bf16 (MEASURED_PEAKS.json)",
                 "whole_step_tflops": px_step * FLOP_PER_PX / (sum(per_launch) / 1e3) / 1e12,

@@ -956,8 +956,11 @@ extern "C" int srb_profile_read(srb_ctx* ctx, float* ms, int max_n) {
     return n;
 }
 
-static void prof_mark(srb_ctx* ctx, cudaStream_t st, bool first = false) {
+// level 1: an event after every launch (serialises the programmatic overlap: per-kernel durations in isolation);
+// level 2: events only around the trunk's eight launches (coarse = true marks): their average duration in the pipeline
+static void prof_mark(srb_ctx* ctx, cudaStream_t st, bool first = false, bool coarse = false) {
     if (!ctx->prof) return;
+    if (ctx->prof == 2 && !coarse && !first) return;
     if (first) ctx->nev = 0;
     if ((int)ctx->ev.size() <= ctx->nev) {
         cudaEvent_t e;
@@ -1003,14 +1006,14 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
         prof_mark(ctx, pst);
         if ((rc = srb_conv2d_fwd(ctx, net->conv[0], in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
     }
-    prof_mark(ctx, pst);
+    prof_mark(ctx, pst, false, true);
     void* cur = x0;
     const bool fused = srb_resblock_supported(H, W) && !(ctx->path & SRB_PATH_UNFUSED_TRUNK);
     for (int i = 0; i < 8; ++i) {
         void* nxt = (i & 1) ? rb : ra;
         if (fused) {
             if ((rc = srb_resblock_fwd(ctx, net->rb[i], cur, nxt, s, N, H, W, stream))) return rc;
-            prof_mark(ctx, pst);
+            prof_mark(ctx, pst, false, i == 7);
             cur = nxt;
             continue;
         }
@@ -1028,7 +1031,7 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
     if (fused && !(ctx->path & SRB_PATH_TILED_TAIL)) {
         if ((rc = srb_tail9_fwd(ctx, net->tail, ra, out, oflags, N, H, W, stream))) return rc;
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[18], ra, 8, 0, out, 0, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, oflags, N, H, W, stream))) return rc;
-    prof_mark(ctx, pst);
+    prof_mark(ctx, pst, false, true);
     return SRB_OK;
 }
 

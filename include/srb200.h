@@ -197,6 +197,11 @@ int srb_poll_abort(srb_ctx* ctx);
  * and biases in the prologue: only enable this where those are not written by the immediately preceding launches of the
  * same stream.  srb_model_pt_forward / srb_resblock_fwd / srb_rowconv_fwd / srb_tail9_fwd always launch this way. */
 int srb_set_programmatic_launch(srb_ctx* ctx, int on);
+/* Timing of srb_model_pt_forward's launches with CUDA events on the launching stream.  on = 1: an event after every launch (an
+ * event between two launches ends their programmatic overlap: durations of the kernels in isolation); on = 2: events only before
+ * the first and after the last of the trunk's eight launches, which overlap through programmatic dependent launch (srb_profile_read
+ * then returns three intervals: input pack + head conv, the trunk, conv1 + tail) — the trunk interval / 8 is a fused block's average
+ * duration inside the pipeline; 0: off. */
 int srb_profile_enable(srb_ctx* ctx, int on);
 int srb_profile_read(srb_ctx* ctx, float* ms, int max_n);
 /* (probe hooks — in-kernel bottleneck probes, clock traces, the tcgen05.mma micro-benchmark — are not part of this library:
