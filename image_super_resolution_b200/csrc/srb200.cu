@@ -2012,7 +2012,7 @@ extern "C" int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_
 // ------------------------------------------------------------------------------------------
 struct srb_conv_chain {
     int n = 0, dtype = 0, grid = 0, num_tiles = 0;
-    bool small = false, bwd = false, fold = false;
+    bool small = false, bwd = false, fold = false, wide = false;      // wide: a 64-output layer (NOUT = 64 kernel)
     ConvParams* d_layers = nullptr;
     CUtensorMap* d_tmaps = nullptr;
     unsigned int* d_flags = nullptr;      // [n][num_tiles] + epoch + ticket
@@ -2037,18 +2037,28 @@ extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* con
     const int NT = small ? 2 : 4, SUPER_W = 8 * NT, SUPER_H = fold ? 14 : 16, HALO_W = SUPER_W + 2, HALO_H = SUPER_H + 2;
     std::vector<ConvParams> lay(n);
     std::vector<CUtensorMap> tms(n);
-    bool bwd = false;
+    bool bwd = false, wide = false;
     for (int l = 0; l < n; ++l) {
         const srb_weights* w = ws[l];
         const srb_conv_args& a = args[l];
         if (!w || !a.x || !a.y) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: NULL", l);
-        if ((w->mode != MODE_STD && w->mode != MODE_DYF) || w->mode != ws[0]->mode || !w->kblocks || w->nout != 32 || w->dtype != ws[0]->dtype)
-            return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: chains hold weight-streaming 3x3 convs with 32 outputs (cin=%d cout=%d)", l, w->cin, w->cout);
+        const bool n_ok = w->nout == 32 || (w->nout == 64 && w->mode == MODE_STD);
+        if ((w->mode != MODE_STD && w->mode != MODE_DYF) || w->mode != ws[0]->mode || !w->kblocks || !n_ok || w->dtype != ws[0]->dtype)
+            return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: chains hold weight-streaming 3x3 convs with 32 (nine-tap kernels: or 64) outputs (cin=%d cout=%d)", l, w->cin, w->cout);
+        wide = wide || w->nout == 64;
         if (a.N != N || a.H != H || a.W != W) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: all layers share one shape", l);
         if (((uintptr_t)a.x & 15) || ((uintptr_t)a.y & 15) || ((uintptr_t)a.mask & 15)) return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: alignment", l);
-        if (a.flags & ~(SRB_F_LRELU | SRB_F_MASK)) return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: flags 0x%x (LRELU / MASK only)", l, a.flags);
-        if (a.x_c8_off < 0 || a.x_c8_off + w->c8in > a.x_c8_total || a.y_c8_off < 0 || a.y_c8_off + 4 > a.y_c8_total)
+        if (a.flags & ~(SRB_F_LRELU | SRB_F_MASK | SRB_F_RESIDUAL)) return fail(SRB_ENOSUP, "srb_conv_chain_create: layer %d: flags 0x%x (LRELU / MASK / RESIDUAL only)", l, a.flags);
+        const int oplanes = (w->cout + 7) / 8;
+        if (a.x_c8_off < 0 || a.x_c8_off + w->c8in > a.x_c8_total || a.y_c8_off < 0 || a.y_c8_off + oplanes > a.y_c8_total)
             return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: plane slice out of range", l);
+        // residual terms (the block's last conv: add_rate * conv + x, the RRDB skip; its backward: + s_res * gy): plain loads in the epilogue
+        const bool has_res = a.residual != nullptr || (a.flags & SRB_F_RESIDUAL);
+        if (has_res && (!a.residual || ((uintptr_t)a.residual & 15) || a.res_c8_off < 0 ||
+                        a.res_c8_off + (a.res_nplanes > 0 ? a.res_nplanes : oplanes) > a.res_c8_total))
+            return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: residual", l);
+        if (a.res2 && (!has_res || ((uintptr_t)a.res2 & 15) || a.res2_c8_off < 0 || a.res2_c8_off + oplanes > a.res2_c8_total))
+            return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: second residual", l);
         if ((a.flags & SRB_F_MASK) && (!a.mask || a.mask_p0 < 0 || a.mask_p1 < a.mask_p0 || a.mask_c8_off + a.mask_p1 > a.mask_c8_total))
             return fail(SRB_EINVAL, "srb_conv_chain_create: layer %d: mask", l);
         bwd = bwd || (a.flags & SRB_F_MASK);
@@ -2062,10 +2072,13 @@ extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* con
         p.x_c8_off = a.x_c8_off; p.wpack = w->d_pack; p.bias = w->d_bias;
         p.y = a.y; p.y_c8_total = a.y_c8_total; p.y_c8_off = a.y_c8_off;
         p.res_scale = a.res_scale; p.out_scale = a.out_scale; p.slope = a.lrelu_slope;
-        p.res_nplanes = 1 << 30;
+        p.res_nplanes = a.res_nplanes > 0 ? a.res_nplanes : 1 << 30;
+        if (has_res) { p.res = a.residual; p.res_c8_total = a.res_c8_total; p.res_c8_off = a.res_c8_off; }
+        if (a.res2) { p.res2 = a.res2; p.res2_c8_total = a.res2_c8_total; p.res2_c8_off = a.res2_c8_off; p.res2_scale = a.res2_scale; }
+        p.nmma = w->nmma;
         p.mask = a.mask; p.mask_c8_total = a.mask_c8_total; p.mask_c8_off = a.mask_c8_off;
         p.mask_p0 = a.mask_p0; p.mask_p1 = a.mask_p1; p.mask_slope = a.mask_slope;
-        p.kblocks = w->kblocks; p.flags = a.flags; p.cout = w->cout;
+        p.kblocks = w->kblocks; p.flags = a.flags | (has_res ? SRB_F_RESIDUAL : 0); p.cout = w->cout;
         cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, (cuuint64_t)a.x_c8_total, (cuuint64_t)N};
         cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * a.x_c8_total};
         cuuint32_t box[4] = {(cuuint32_t)HALO_W * 4, (cuuint32_t)HALO_H, 4, 1};
@@ -2076,7 +2089,7 @@ extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* con
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "srb_conv_chain_create: cuTensorMapEncodeTiled failed: %d", (int)r);
     }
     srb_conv_chain* c = new srb_conv_chain();
-    c->n = n; c->dtype = ws[0]->dtype; c->num_tiles = lay[0].num_tiles; c->small = small; c->bwd = bwd; c->fold = fold;
+    c->n = n; c->dtype = ws[0]->dtype; c->num_tiles = lay[0].num_tiles; c->small = small; c->bwd = bwd; c->fold = fold; c->wide = wide;
     c->grid = c->num_tiles < ctx->num_sms ? c->num_tiles : ctx->num_sms;       // every CTA resident: the tile-level waits rely on it
     DeviceGuard dev_guard(ctx->device);
     const size_t fl = ((size_t)n * c->num_tiles + 2) * sizeof(unsigned int);
@@ -2089,16 +2102,16 @@ extern "C" int srb_conv_chain_create(srb_ctx* ctx, int n, const srb_weights* con
     return SRB_OK;
 }
 
-template <int MODE, int NT, bool BF16, bool BWD>
+template <int MODE, int NT, bool BF16, bool BWD, int NOUT = 32>
 static int launch_chain(srb_ctx* ctx, const srb_conv_chain* c, cudaStream_t st) {
     // (KACC = 2 — two accumulators per M-tile, K-steps alternating — is implemented in conv_body and measured equal in time; it changes
     // the fp32 summation order, and chains are kept bit-identical to the same layers launched one by one)
     constexpr int KACC = 1;
-    using G = ConvGeom<4, 32, 3, 3, MODE, NT, false, true, KACC>;
+    using G = ConvGeom<4, NOUT, 3, 3, MODE, NT, false, true, KACC>;
     ChainCtl cc{};
     cc.layers = c->d_layers; cc.tmaps = c->d_tmaps; cc.nlayers = c->n;
     cc.flags = c->d_flags; cc.epoch = c->d_flags + (size_t)c->n * c->num_tiles; cc.ticket = cc.epoch + 1;
-    auto kern = conv_chain_kernel<4, 32, MODE, NT, BF16, BWD, KACC>;
+    auto kern = conv_chain_kernel<4, NOUT, MODE, NT, BF16, BWD, KACC>;
     const int smem = G::SMEM_BYTES + (MODE == MODE_DYF ? 0 : CHAIN_SMEM_EXTRA);      // (the dy-folded geometry already holds the chain area)
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     cudaLaunchConfig_t cfg{};
@@ -2123,6 +2136,11 @@ extern "C" int srb_conv_chain_run(srb_ctx* ctx, srb_conv_chain* c, srb_stream_t 
 #endif
 #define SRB_CH(MD, NTV) { if (c->bwd) return bf ? launch_chain<MD, NTV, true, true>(ctx, c, st) : launch_chain<MD, NTV, false, true>(ctx, c, st); \
                           return bf ? launch_chain<MD, NTV, true, false>(ctx, c, st) : launch_chain<MD, NTV, false, false>(ctx, c, st); }
+    // a chain with a 64-output layer (the block's last conv) runs on the NOUT = 64 kernel; its 32-output layers issue N = 32 MMAs
+#define SRB_CHW(NTV) { if (c->bwd) return bf ? launch_chain<MODE_STD, NTV, true, true, 64>(ctx, c, st) : launch_chain<MODE_STD, NTV, false, true, 64>(ctx, c, st); \
+                       return bf ? launch_chain<MODE_STD, NTV, true, false, 64>(ctx, c, st) : launch_chain<MODE_STD, NTV, false, false, 64>(ctx, c, st); }
+    if (c->wide) { if (c->small) SRB_CHW(2) else SRB_CHW(4) }
+#undef SRB_CHW
     if (c->fold) SRB_CH(MODE_DYF, 2) else if (c->small) SRB_CH(MODE_STD, 2) else SRB_CH(MODE_STD, 4)
 #undef SRB_CH
 }

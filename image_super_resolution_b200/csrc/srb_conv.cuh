@@ -70,6 +70,7 @@ struct ConvParams {
     int mask_c8_total, mask_c8_off, mask_p0, mask_p1;
     float mask_slope;
     int kblocks;             // WS kernels: number of K blocks (C8IN planes each) streamed per super-tile
+    int nmma;                // chain layers: N of this layer's MMAs (a chain compiled for NOUT = 64 also runs 32-output layers); 0 = the kernel's
     int flags;
     int cout;                // real output channels (DXN: 3)
     int dbg_swap;            // debug: swap LBO/SBO of the descriptors (diagnostics only)
@@ -118,7 +119,7 @@ struct ConvGeom {
     // DYF: behind the barriers and the chain area, per epilogue set two buffers of [4 warps][2 directions][8 float4 groups][8 px]
     // for the rows exchanged across warps
     static constexpr int XCH_BUF = 4 * 2 * 8 * 8 * 16;            // 8 KB
-    static constexpr int XCH_BYTES = DYF ? 2048 + 2 * 2 * XCH_BUF : 0;      // (2048: the chain area, see CHAIN_SMEM_EXTRA)
+    static constexpr int XCH_BYTES = DYF ? 4096 + 2 * 2 * XCH_BUF : 0;      // (4096: the chain area, CHAIN_SMEM_EXTRA below)
     static constexpr int SMEM_FIXED = 1024 /*align slack*/ + (WBYTES + 1023) / 1024 * 1024 + NOUT * 4 + 256 /*barriers*/ + XCH_BYTES;
     static constexpr int max_stages() {
         int s = (227 * 1024 - SMEM_FIXED) / STAGE_STRIDE;
@@ -237,7 +238,8 @@ __device__ __forceinline__ uint4 lds_u4(uint32_t a) {
 // of layer l-1 has been stored (per-tile arrival counters in global memory; the neighbourhood's own inputs are then complete
 // as well), so neither a grid-wide barrier nor a launch boundary separates the layers.  All CTAs are resident (grid <= #SMs,
 // one CTA per SM) and every CTA visits (layer, tile) in the same order, so the waits cannot deadlock; they are bounded anyway.
-constexpr int CHAIN_MAX_LAYERS = 4;
+constexpr int CHAIN_MAX_LAYERS = 8;
+constexpr int CHAIN_SMEM_EXTRA = 4096;      // the layers' parameters and biases, behind the barriers
 struct ChainCtl {
     const ConvParams* layers;      // [nlayers] device
     const CUtensorMap* tmaps;      // [nlayers] device (64-byte aligned)
@@ -271,7 +273,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
     // CHAIN: the layers' parameters and biases live behind the barriers (the launch adds CHAIN_SMEM_EXTRA bytes)
     ConvParams* s_lay = reinterpret_cast<ConvParams*>(reinterpret_cast<uint8_t*>(bars) + 256);
     float* s_bias_l = reinterpret_cast<float*>(s_lay + CHAIN_MAX_LAYERS);          // [nlayers][NOUT]
-    uint8_t* s_xch = reinterpret_cast<uint8_t*>(bars) + 256 + 2048;                // DYF: rows exchanged between the epilogue warps
+    uint8_t* s_xch = reinterpret_cast<uint8_t*>(bars) + 256 + CHAIN_SMEM_EXTRA;                // DYF: rows exchanged between the epilogue warps
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -280,7 +282,10 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
     if constexpr (CHAIN) {
         for (int i = threadIdx.x; i < nl * (int)(sizeof(ConvParams) / 4); i += blockDim.x)
             reinterpret_cast<uint32_t*>(s_lay)[i] = reinterpret_cast<const uint32_t*>(cc.layers)[i];
-        for (int i = threadIdx.x; i < nl * NOUT; i += blockDim.x) s_bias_l[i] = cc.layers[i / NOUT].bias[i % NOUT];
+        for (int i = threadIdx.x; i < nl * NOUT; i += blockDim.x) {
+            const ConvParams& q = cc.layers[i / NOUT];              // (a 32-output layer of a NOUT = 64 chain has 32 bias entries)
+            s_bias_l[i] = (i % NOUT) < (q.nmma > 0 ? q.nmma : NOUT) ? q.bias[i % NOUT] : 0.f;
+        }
     } else {
         for (int i = threadIdx.x; i < NOUT; i += blockDim.x) s_bias[i] = p0.bias[i];
     }
@@ -329,6 +334,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
         const ConvParams& p = CHAIN ? s_lay[l] : p0;
         const CUtensorMap* tm = CHAIN ? cc.tmaps + l : tmap_p;
         const int kblocks = WS ? p.kblocks : 1;
+        const int wblk = (CHAIN && p.nmma > 0) ? G::WBLK_BYTES / G::NMMA * p.nmma : G::WBLK_BYTES;     // this layer's filter slice per K block
         for (int tile = chain_first_tile<CHAIN>(l, p.num_tiles); tile < p.num_tiles; tile += gridDim.x, ++pit) {
             int n = tile / tiles_per_img;
             int r = tile - n * tiles_per_img;
@@ -349,14 +355,14 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
                 if (elect_one()) {
                     if SRB_DBG(p.dbg_skip & 1) { mbar_arrive(&full[s]); }
                     else {
-                        mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES + (WS ? G::WBLK_BYTES : 0));
+                        mbar_arrive_expect_tx(&full[s], G::STAGE_BYTES + (WS ? wblk : 0));
                         tma_load_4d(s_a + s * G::STAGE_STRIDE, tm, &full[s], (tx * G::SUPER_W - G::PADX + (MODE == MODE_PAIR4 ? 1 : 0)) * 4,
                                     ty * G::SUPER_H - G::PADY, p.x_c8_off + kb * C8IN, n);
                         if constexpr (WS) {
                             uint8_t* wdst = s_a + s * G::STAGE_STRIDE + G::A_STRIDE;
-                            const uint8_t* wsrc = p.wpack + (size_t)kb * G::WBLK_BYTES;
-                            for (int off = 0; off < G::WBLK_BYTES; off += 16384) {
-                                int nb = G::WBLK_BYTES - off < 16384 ? G::WBLK_BYTES - off : 16384;
+                            const uint8_t* wsrc = p.wpack + (size_t)kb * wblk;
+                            for (int off = 0; off < wblk; off += 16384) {
+                                int nb = wblk - off < 16384 ? wblk - off : 16384;
                                 bulk_load_1d(wdst + off, wsrc + off, nb, &full[s]);
                             }
                         }
@@ -369,7 +375,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = umma_idesc_f16(128, G::NMMA, BF16 ? 1 : 0);
+        constexpr uint32_t idesc0 = umma_idesc_f16(128, G::NMMA, BF16 ? 1 : 0);
         uint32_t a_lbo = (MODE == MODE_PAIRDX) ? 16u : (MODE == MODE_PAIR4) ? 32u : (uint32_t)G::PLANE;
         uint32_t a_sbo = (MODE == MODE_DXN) ? 128u : (uint32_t)G::ROWP;
         uint32_t b_lbo = G::NMMA * 16, b_sbo = 128;
@@ -383,6 +389,11 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
         for (int l = 0; l < nl; ++l) {
         const ConvParams& p = CHAIN ? s_lay[l] : p0;
         const int kblocks = WS ? p.kblocks : 1;
+        // (chain: N of this layer's MMAs; the accumulators keep the kernel's column stride)
+        const bool own_n = CHAIN && p.nmma > 0 && p.nmma != G::NMMA;
+        const uint32_t idesc = own_n ? umma_idesc_f16(128, p.nmma, BF16 ? 1 : 0) : idesc0;
+        const uint32_t wstep = own_n ? (uint32_t)(2 * p.nmma * 16) : (uint32_t)G::WSTEP_BYTES;
+        if (own_n) b_lbo = (uint32_t)p.nmma * 16; else if (CHAIN) b_lbo = G::NMMA * 16;
         for (int tile = chain_first_tile<CHAIN>(l, p.num_tiles); tile < p.num_tiles; tile += gridDim.x, ++it) {
             const int b = it & 1;
             const uint32_t bph = (it >> 1) & 1;
@@ -406,7 +417,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                             for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
                                 const uint32_t ao = (2 * c2 * G::PLANE + dx * 16) >> 4;
-                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * wstep) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * G::NMMA, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, (ks | kb) != 0);
@@ -419,7 +430,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                                 for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
                                     const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP + dx * 16) >> 4;
-                                    const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                    const uint64_t bd = b_desc_s + (uint64_t)((ks * wstep) >> 4);
                                     if constexpr (KACC == 2) {      // K-steps alternate between the tile's two accumulators (c2 = 0 / 1)
 #pragma unroll
                                         for (int t = 0; t < NT; ++t)
@@ -436,7 +447,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                             for (int dxp = 0; dxp < (KW + 1) / 2; ++dxp, ++ks) {
                                 const uint32_t ao = (dy * G::ROWP + 2 * dxp * 16) >> 4;
-                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * wstep) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
@@ -447,7 +458,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                             for (int dxq = 0; dxq < (KW + 3) / 4; ++dxq, ++ks) {
                                 const uint32_t ao = (dy * G::ROWP + 4 * dxq * 16) >> 4;
-                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * wstep) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
@@ -458,7 +469,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                             for (int c2 = 0; c2 < C8IN / 2; ++c2, ++ks) {
                                 const uint32_t ao = (2 * c2 * G::PLANE + dy * G::ROWP) >> 4;
-                                const uint64_t bd = b_desc_s + (uint64_t)((ks * G::WSTEP_BYTES) >> 4);
+                                const uint64_t bd = b_desc_s + (uint64_t)((ks * wstep) >> 4);
 #pragma unroll
                                 for (int t = 0; t < NT; ++t)
                                     umma_f16_ss(d_tmem + t * NOUT, a_desc + ao + t * (G::TOFF >> 4), bd, idesc, ks > 0);
@@ -528,7 +539,7 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
             if (threadIdx.x == 128) trace(p, it, 4);   // epilogue starts waiting
             // backward of a 32-channel layer: the saved activation granules of this set's first M-tile are requested before
             // the wait for the accumulators (the mask read was an exposed DRAM / L2 round trip per tile)
-            constexpr bool MASK_PF = BWD && NOUT == 32 && G::XT;
+            constexpr bool MASK_PF = BWD && NOUT <= 64 && G::XT && (CHAIN || NOUT == 32);
             uint4 mpf[MASK_PF ? 4 : 1];
             bool mpf_ok = false;
             if constexpr (MASK_PF) {
@@ -646,10 +657,12 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
                                 const float4 b1 = lds_f4(s_bias_u32 + (c0 + 8 * j + 4) * 4);
                                 const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
+                                // (explicitly rounded steps: the same conv must give the same bits in every instantiation — tiled, chained,
+                                // with or without the TMA residual ring — and the compiler contracts a * b + c differently in each)
                                 for (int i = 0; i < 8; ++i) {
-                                    float tt = __uint_as_float(rr[8 * j + i]) + bb[i];
-                                    if (do_lrelu) tt = fmaxf(tt, tt * p.slope);   // LeakyReLU for 0 <= slope <= 1
-                                    v[i] = tt * p.out_scale;
+                                    float tt = __fadd_rn(__uint_as_float(rr[8 * j + i]), bb[i]);
+                                    if (do_lrelu) tt = fmaxf(tt, __fmul_rn(tt, p.slope));   // LeakyReLU for 0 <= slope <= 1
+                                    v[i] = __fmul_rn(tt, p.out_scale);
                                 }
                                 if (valid) {
                                     if ((RES || has_res) && (!BWD || gj < p.res_nplanes)) {
@@ -661,8 +674,8 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
                                             float2 f = unpack2<BF16>(qq[i]);
-                                            v[2 * i] += p.res_scale * f.x;
-                                            v[2 * i + 1] += p.res_scale * f.y;
+                                            v[2 * i] = __fmaf_rn(p.res_scale, f.x, v[2 * i]);
+                                            v[2 * i + 1] = __fmaf_rn(p.res_scale, f.y, v[2 * i + 1]);
                                         }
                                     }
                                     if (p.res2 != nullptr) {
@@ -672,8 +685,8 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
                                             float2 f = unpack2<BF16>(qq[i]);
-                                            v[2 * i] += p.res2_scale * f.x;
-                                            v[2 * i + 1] += p.res2_scale * f.y;
+                                            v[2 * i] = __fmaf_rn(p.res2_scale, f.x, v[2 * i]);
+                                            v[2 * i + 1] = __fmaf_rn(p.res2_scale, f.y, v[2 * i + 1]);
                                         }
                                     }
                                     if (BWD && (p.flags & F_MASK) && gj >= p.mask_p0 && gj < p.mask_p1) {
@@ -686,8 +699,8 @@ __device__ __forceinline__ void conv_body(const CUtensorMap* tmap_p, const CUten
 #pragma unroll
                                         for (int i = 0; i < 4; ++i) {
                                             float2 f = unpack2<BF16>(qq[i]);
-                                            if (!(f.x > 0.f)) v[2 * i] *= p.mask_slope;
-                                            if (!(f.y > 0.f)) v[2 * i + 1] *= p.mask_slope;
+                                            if (!(f.x > 0.f)) v[2 * i] = __fmul_rn(v[2 * i], p.mask_slope);
+                                            if (!(f.y > 0.f)) v[2 * i + 1] = __fmul_rn(v[2 * i + 1], p.mask_slope);
                                         }
                                     }
                                     uint4 o;
@@ -796,7 +809,6 @@ __global__ void __launch_bounds__(CONV_THREADS, 1) conv_tc_kernel(const __grid_c
 }
 
 // the weight-streaming 3x3 convs of a dense block as one launch (see CHAIN above)
-constexpr int CHAIN_SMEM_EXTRA = 2048;
 static_assert(CHAIN_MAX_LAYERS * ((int)sizeof(ConvParams) + 64 * 4) <= CHAIN_SMEM_EXTRA, "chain area");
 template <int C8IN, int NOUT, int MODE, int NT, bool BF16, bool BWD, int KACC>
 __global__ void __launch_bounds__(CONV_THREADS, 1) conv_chain_kernel(const ChainCtl cc) {

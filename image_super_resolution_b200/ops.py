@@ -214,12 +214,18 @@ def conv2d_ex(pc, x, x_planes, x_off, y, y_planes, y_off, N, H, W, residual=None
 
 
 def conv_args(x, x_planes, x_off, y, y_planes, y_off, N, H, W, slope=0.0, flags=0, out_scale=1.0,
-              mask=None, mask_planes=0, mask_off=0, mask_p0=0, mask_p1=0, mask_slope=0.0) -> "_lib.ConvArgs":
-    """srb_conv_args of a layer without residual (the layers of a ConvChain)."""
+              mask=None, mask_planes=0, mask_off=0, mask_p0=0, mask_p1=0, mask_slope=0.0,
+              residual=None, res_planes=0, res_off=0, res_scale=1.0, res2=None, res2_planes=0, res2_off=0, res2_scale=1.0) -> "_lib.ConvArgs":
+    """srb_conv_args of a layer of a ConvChain (residual terms: the block's last conv)."""
     a = _lib.ConvArgs()
     a.x, a.x_c8_total, a.x_c8_off = x.data_ptr(), x_planes, x_off
     a.y, a.y_c8_total, a.y_c8_off = y.data_ptr(), y_planes, y_off
-    a.res_scale, a.out_scale, a.lrelu_slope = 1.0, out_scale, slope
+    a.res_scale, a.out_scale, a.lrelu_slope = res_scale, out_scale, slope
+    if residual is not None:
+        flags |= _lib.F_RESIDUAL
+        a.residual, a.res_c8_total, a.res_c8_off = residual.data_ptr(), res_planes, res_off
+    if res2 is not None:
+        a.res2, a.res2_c8_total, a.res2_c8_off, a.res2_scale = res2.data_ptr(), res2_planes, res2_off, res2_scale
     if mask is not None:
         flags |= _lib.F_MASK
         a.mask, a.mask_c8_total, a.mask_c8_off = mask.data_ptr(), mask_planes, mask_off

@@ -93,6 +93,9 @@ class TrainPlan:
         # CTAs with tile-level dependencies instead of four launches (ops.ConvChain; csrc/srb_conv.cuh CHAIN)
         self.use_chains = True
         self.fchains, self.bchains, self.chain_key = None, None, None
+        # the block's LAST conv (192 -> 64 with its residual terms; in the backward the data gradient of the block's input) rides in the
+        # chain as a fifth layer on the 64-output chain kernel (nine-tap layout only)
+        self.chain5 = bool(getattr(net, "train_chain5", 1)) and fold == 1
         self.chain_nt4 = bool(getattr(net, "train_chain_nt4", False))    # super-tiles of four M-tiles in the chains even for small batches
         self.wgrad_splitk = 1
         # Internal gradient shift: the data-gradient chain runs on 16-bit tensors whose magnitudes span the tail conv (~1 with
@@ -278,18 +281,33 @@ class TrainPlan:
         tr = self._b("tr", N, 8, H, W)
         s0 = _slope_of(n.conv0.act)
         cv(self.f_conv0, xin, 1, 0, dense[0], 24, 0, N, H, W, slope=s0, flags=ops.F_LRELU)     # x0 = planes 0..7 of dense[0]
+        def last_conv_kw(r):
+            """residual terms of an RDB's last conv: add_rate*conv + rdb_in (utils/models.py:271), for the third RDB of an RRDB
+            R*(add_rate*conv + rdb_in) + rrdb_in (:317)"""
+            rrdb, rdb = self.rdbs[r][0], self.rdbs[r][1]
+            a = float(rdb.add_rate)
+            if r % 3 < 2:
+                return dict(residual=dense[r], res_planes=24, res_off=0, res_scale=1.0, out_scale=a)
+            R = float(rrdb.add_rate)
+            return dict(residual=dense[r], res_planes=24, res_off=0, res_scale=R, out_scale=R * a, res2=dense[r - 2], res2_planes=24,
+                        res2_off=0, res2_scale=1.0)
         if self.use_chains and self.chain_key != (N, H, W):
             self.fchains, self.bchains, self.chain_key = [], None, (N, H, W)
             for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
                 D = dense[r]
-                self.fchains.append(self._mk_chain([
-                    (fwd[i], ops.conv_args(D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=_slope_of(getattr(rdb, f"conv{i}").act),
-                                           flags=ops.F_LRELU)) for i in range(4)], keep=(D,)))
+                dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
+                layers = [(fwd[i], ops.conv_args(D, 24, 0, D, 24, 8 + 4 * i, N, H, W, slope=_slope_of(getattr(rdb, f"conv{i}").act),
+                                                 flags=ops.F_LRELU)) for i in range(4)]
+                if self.chain5:     # ... and the block's last conv (64 outputs, residual terms) as the chain's fifth layer
+                    layers.append((fwd[4], ops.conv_args(D, 24, 0, dst, dplanes, 0, N, H, W, **last_conv_kw(r))))
+                self.fchains.append(self._mk_chain(layers, keep=(D, dst, dense[r - 2] if r % 3 == 2 else None)))
         for r, (rrdb, rdb, fwd, _, _) in enumerate(self.rdbs):
             D = dense[r]
             dst, dplanes = (dense[r + 1], 24) if r + 1 < nr else (tr, 8)
             if self.use_chains:
                 self.fchains[r].run(self.device)
+                if self.chain5:
+                    continue
             else:
                 for i in range(4):
                     si = _slope_of(getattr(rdb, f"conv{i}").act)
@@ -375,10 +393,18 @@ class TrainPlan:
             for r in range(nr):
                 rrdb, rdb, _, stage, _ = self.rdbs[r]
                 D, G = sv["dense"][r], Gd[r]
-                self.bchains.append(self._mk_chain([
-                    (stage[k], ops.conv_args(G, 24, 0, G, 24, 8 + 4 * (3 - k), N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k,
-                                             mask_p0=0, mask_p1=4, mask_slope=_slope_of(getattr(rdb, f"conv{k}").act)))
-                    for k in range(3, -1, -1)], keep=(D, G)))
+                layers = [(stage[k], ops.conv_args(G, 24, 0, G, 24, 8 + 4 * (3 - k), N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k,
+                                                   mask_p0=0, mask_p1=4, mask_slope=_slope_of(getattr(rdb, f"conv{k}").act)))
+                          for k in range(3, -1, -1)]
+                if self.chain5:     # ... and the data gradient of the block's input (all five sources -> 64 channels, + s_res * gy [+ RRDB skip])
+                    fin = self.rdbs[r][4]
+                    dstb, dpl = (Gd[r - 1], 24) if r > 0 else (gxf, 8)
+                    s_res = float(rrdb.add_rate) if r % 3 == 2 else 1.0
+                    kwb = dict(residual=G, res_planes=24, res_off=0, res_scale=s_res)
+                    if r % 3 == 0:
+                        kwb.update(res2=Gd[r + 2], res2_planes=24, res2_off=0, res2_scale=1.0)
+                    layers.append((fin, ops.conv_args(G, 24, 0, dstb, dpl, 0, N, H, W, **kwb)))
+                self.bchains.append(self._mk_chain(layers, keep=(D, G, Gd[r - 1] if r > 0 else gxf, Gd[r + 2] if r % 3 == 0 else None)))
         cv(self.d_conv1, g_t, 8, 0, Gd[nr - 1], 24, 0, N, H, W)
         for r in range(nr - 1, -1, -1):
             rrdb, rdb, _, stage, fin = self.rdbs[r]
@@ -396,6 +422,8 @@ class TrainPlan:
                     cv(stage[k], G, 24, 0, G, 24, nin, N, H, W, mask=D, mask_planes=24, mask_off=8 + 4 * k, mask_p0=0, mask_p1=4,
                        mask_slope=sl[k])
                 self._wb(getattr(rdb, f"conv{k}"), D, 24, 0, 64 + 32 * k, G, 24, nin, 32, N, H, W)
+            if self.use_chains and self.chain5:
+                continue                                                # (fin is the chain's fifth layer)
             dst, dplanes = (Gd[r - 1], 24) if r > 0 else (gxf, 8)
             kw = dict(residual=G, res_planes=24, res_off=0, res_scale=s_res)
             if d == 0:                                                  # + the RRDB skip (utils/models.py:317)
