@@ -29,14 +29,13 @@ if ROOT not in sys.path:
 WEIGHTS = os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")
 BATCH, HH, WW = 256, 64, 64
 FLOP_PER_PX = 725760  # algorithmic FLOP (2*MAC) per pixel of the model.pt graph
-# algorithmic FLOP/px of each launch of one forward, in launch order (pack, conv0, 8x(A,B), conv1, conv2)
-LAUNCH_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
-LAUNCH_NAMES = ["u8nchw_to_pair4_x4", "conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64",
-                                                                                                 "conv9x9_tail_64_3"]
+# algorithmic FLOP/px of each launch of one forward, in launch order (conv0 with the uint8 ingest folded in, 8x(A,B), conv1, conv2)
+LAUNCH_FLOP_PX = [2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
+LAUNCH_NAMES = ["ingest_conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
 assert sum(LAUNCH_FLOP_PX) == FLOP_PER_PX
-# with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 12 launches
-FUSED_FLOP_PX = [0, 2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
-FUSED_NAMES = ["u8nchw_to_pair4_x4", "conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
+# with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 11 launches
+FUSED_FLOP_PX = [2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
+FUSED_NAMES = ["ingest_conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
 assert sum(FUSED_FLOP_PX) == FLOP_PER_PX
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the dominant kernel at the bench shape, from the
 # one `ncu --set full` capture of a whole forward summarised in profiles/ncu_fwd_r1_full.txt (mean of the 8 launches:

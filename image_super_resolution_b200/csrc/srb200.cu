@@ -26,6 +26,7 @@
 #include "srb_bwd.cuh"
 #include "srb_resblock.cuh"
 #include "srb_rowconv.cuh"
+#include "srb_head.cuh"
 #include "srb_tail.cuh"
 #include "srb_optim.cuh"
 #include "srb_bn.cuh"
@@ -99,12 +100,14 @@ struct srb_weights {
 struct srb_resblock;
 struct srb_rowconv;
 struct srb_tail9;
+struct srb_head;
 struct srb_net {
     srb_weights* conv[19];
     srb_resblock* rb[8];     // fused ResidualBlock1 operands (used when the shape qualifies)
     srb_rowconv* rc1 = nullptr;   // conv1 (+ long skip) on the row-fold kernel
     srb_tail9* tail = nullptr;    // conv2 + tanh -> uint8 on the row-fold kernel
     srb_weights* head4 = nullptr; // conv0 packed for pixel-pair input granules (MODE_PAIR4)
+    srb_head* head = nullptr;     // Normalize + conv0 straight from the uint8 frame (srb_head.cuh)
     float mean[3], std_[3], maxv, slope;
     int dtype;
 };
@@ -843,6 +846,88 @@ extern "C" int srb_bn_bwd_reduce(srb_ctx* ctx, const srb_bn_args* a, int dtype, 
 extern "C" int srb_bn_bwd_apply(srb_ctx* ctx, const srb_bn_args* a, int dtype, srb_stream_t stream) { return bn_launch(ctx, a, dtype, stream, 3, "srb_bn_bwd_apply"); }
 
 // ------------------------------------------------------------------------------------------
+// Normalize + conv0 9x9 3 -> 64 + LeakyReLU straight from uint8 frames (srb_head.cuh)
+// ------------------------------------------------------------------------------------------
+struct srb_head {
+    int dtype = 0;
+    uint8_t* d_w = nullptr;
+    float h_bias[64] = {};
+    mutable bool attr_set = false;
+};
+
+extern "C" void srb_head_destroy(srb_head* h) {
+    if (!h) return;
+    if (h->d_w) cudaFree(h->d_w);
+    delete h;
+}
+
+extern "C" int srb_head_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_head** out) {
+    if (!ctx || !w || !bias || !out) return fail(SRB_EINVAL, "srb_head_create: NULL argument");
+    if (dtype != SRB_DT_F16 && dtype != SRB_DT_BF16) return fail(SRB_EINVAL, "srb_head_create: dtype %d", dtype);
+    using G = HDGeom;
+    // K-step (dy, kk): K slot k < 15 is pixel offset k / 3, channel k % 3 of the five pixels starting at tap dx = 5 * kk; slot 15 = 0
+    std::vector<uint16_t> pk((size_t)G::W_BYTES / 2, 0);
+    for (int dy = 0; dy < 9; ++dy) for (int kk = 0; kk < 2; ++kk) for (int k = 0; k < 15; ++k) {
+        const int dx = 5 * kk + k / 3, c = k % 3;
+        if (dx > 8) continue;
+        for (int n = 0; n < 64; ++n)
+            pk[(((size_t)(dy * 2 + kk) * 2 + (k >> 3)) * 64 + n) * 8 + (k & 7)] = f2h(w[(((size_t)n * 3 + c) * 9 + dy) * 9 + dx], dtype);
+    }
+    srb_head* h = new srb_head();
+    h->dtype = dtype;
+    DeviceGuard dev_guard(ctx->device);
+    if (cudaMalloc(&h->d_w, G::W_BYTES) != cudaSuccess) {
+        srb_head_destroy(h);
+        return fail(SRB_ENOMEM, "srb_head_create: cudaMalloc failed");
+    }
+    CUDA_TRY(cudaMemcpy(h->d_w, pk.data(), G::W_BYTES, cudaMemcpyHostToDevice));
+    memcpy(h->h_bias, bias, 64 * 4);
+    *out = h;
+    return SRB_OK;
+}
+
+extern "C" int srb_head_fwd(srb_ctx* ctx, const srb_head* h, const uint8_t* in, int in_layout, const float mean[3], const float std_[3],
+                            float maxv, void* y, float slope, int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !h || !in || !mean || !std_ || !y) return fail(SRB_EINVAL, "srb_head_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_head_fwd: empty shape");
+    if ((uintptr_t)y & 15) return fail(SRB_EINVAL, "srb_head_fwd: y must be 16-byte aligned");
+    if (in_layout != SRB_LAYOUT_NCHW_RGB && in_layout != SRB_LAYOUT_NHWC_BGR && in_layout != SRB_LAYOUT_NHWC_RGB)
+        return fail(SRB_EINVAL, "srb_head_fwd: in_layout %d", in_layout);
+    using G = HDGeom;
+    HeadParams p{};
+    p.N = N; p.H = H; p.W = W;
+    p.tiles_x = (W + G::TW - 1) / G::TW; p.tiles_y = (H + G::SUPER_H - 1) / G::SUPER_H;
+    const long long nt = (long long)N * p.tiles_x * p.tiles_y;
+    if (nt > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_head_fwd: too many tiles");
+    p.num_tiles = (int)nt;
+    p.in = in;
+    p.layout = in_layout == SRB_LAYOUT_NCHW_RGB ? HEAD_NCHW_RGB : in_layout == SRB_LAYOUT_NHWC_RGB ? HEAD_NHWC_RGB : HEAD_NHWC_BGR;
+    p.fast = (W % 4) == 0 && ((uintptr_t)in & 3) == 0;
+    p.wpack = h->d_w;
+    memcpy(p.bias, h->h_bias, sizeof(p.bias));
+    p.slope = slope;
+    for (int i = 0; i < 3; ++i) { p.mean[i] = mean[i]; p.stdv[i] = std_[i]; }
+    p.maxv = maxv; p.y = y;
+    int grid = p.num_tiles < ctx->num_sms ? p.num_tiles : ctx->num_sms;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
+    if (!h->attr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(head_ingest_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(head_ingest_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        h->attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (h->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, head_ingest_kernel<true>, p));
+    else CUDA_TRY(cudaLaunchKernelEx(&cfg, head_ingest_kernel<false>, p));
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // model.pt graph
 // ------------------------------------------------------------------------------------------
 extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const float* const* b, const float mean[3],
@@ -869,6 +954,7 @@ extern "C" int srb_model_pt_create(srb_ctx* ctx, const float* const* w, const fl
     if (rc == SRB_OK) rc = srb_rowconv_create(ctx, w[17], b[17], dtype, &net->rc1);
     if (rc == SRB_OK) rc = srb_tail9_create(ctx, w[18], b[18], dtype, &net->tail);
     if (rc == SRB_OK) rc = srb_pack_conv_pair4(ctx, w[0], b[0], 64, dtype, &net->head4);
+    if (rc == SRB_OK) rc = srb_head_create(ctx, w[0], b[0], dtype, &net->head);
     if (rc != SRB_OK) { srb_model_pt_destroy(net); return rc; }
     *out = net;
     return SRB_OK;
@@ -881,6 +967,7 @@ extern "C" void srb_model_pt_destroy(srb_net* net) {
     srb_rowconv_destroy(net->rc1);
     srb_tail9_destroy(net->tail);
     srb_free_weights(net->head4);
+    srb_head_destroy(net->head);
     delete net;
 }
 
@@ -892,8 +979,8 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
     return align256((size_t)N * H * (W + 1) * 16) + 3 * align256(P * 128) + align256(P * 64);
 }
 
-// kernels one forward enqueues: pack, head, 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
-extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? 12 : 20; }
+// kernels one forward enqueues: head (ingest + conv0), 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
+extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? 11 : 19; }
 
 #ifdef SRB_DEBUG
 // measurement only: per-step clock trace of CTA 0 of the next conv launches (512 int64 device buffer, or NULL)
@@ -977,7 +1064,16 @@ extern "C" int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* i
 
 extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uint8_t* in, uint8_t* out, int out_layout, int N, int H, int W,
                                     void* ws, size_t ws_bytes, srb_stream_t stream) {
+    return srb_model_pt_forward_io(ctx, net, in, SRB_LAYOUT_NCHW_RGB, out, out_layout, N, H, W, ws, ws_bytes, stream);
+}
+
+extern "C" int srb_model_pt_forward_io(srb_ctx* ctx, srb_net* net, const uint8_t* in, int in_layout, uint8_t* out, int out_layout, int N, int H,
+                                       int W, void* ws, size_t ws_bytes, srb_stream_t stream) {
     if (!ctx || !net || !in || !out || !ws) return fail(SRB_EINVAL, "srb_model_pt_forward: NULL argument");
+    if (in_layout != SRB_LAYOUT_NCHW_RGB && in_layout != SRB_LAYOUT_NHWC_BGR && in_layout != SRB_LAYOUT_NHWC_RGB)
+        return fail(SRB_EINVAL, "srb_model_pt_forward_io: in_layout %d", in_layout);
+    if (in_layout != SRB_LAYOUT_NCHW_RGB && (ctx->path & (SRB_PATH_C8_HEAD | SRB_PATH_PAIR4_HEAD)))
+        return fail(SRB_ENOSUP, "srb_model_pt_forward_io: HWC frames are read by the ingest head only (SRB_PATH_C8_HEAD / SRB_PATH_PAIR4_HEAD take NCHW)");
     if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_model_pt_forward: empty shape %dx%dx%d", N, H, W);
     size_t need = srb_model_pt_workspace_bytes(N, H, W);
     if (ws_bytes < need) return fail(SRB_EINVAL, "srb_model_pt_forward: workspace %zu < %zu bytes", ws_bytes, need);
@@ -997,7 +1093,10 @@ extern "C" int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uin
     struct PdlScope { srb_ctx* c; ~PdlScope() { c->pdl = false; } } pdl_scope{ctx};
     ctx->pdl = !(ctx->path & SRB_PATH_NO_PDL);
     prof_mark(ctx, pst, true);
-    if (!(ctx->path & SRB_PATH_C8_HEAD)) {      // head conv on pixel-pair granules: 27 MMAs per M-tile instead of 45
+    if (!(ctx->path & (SRB_PATH_C8_HEAD | SRB_PATH_PAIR4_HEAD))) {
+        // Normalize + conv0 in one launch, reading the uint8 frame itself (18 MMAs per M-tile, no normalised plane in HBM)
+        if ((rc = srb_head_fwd(ctx, net->head, in, in_layout, net->mean, net->std_, net->maxv, x0, s, N, H, W, stream))) return rc;
+    } else if (!(ctx->path & SRB_PATH_C8_HEAD)) {      // head conv on pixel-pair granules: 27 MMAs per M-tile instead of 45
         if ((rc = srb_u8nchw_to_pair4(ctx, in, in8, net->mean, net->std_, net->maxv, net->dtype, N, H, W, stream))) return rc;
         prof_mark(ctx, pst);
         if ((rc = srb_conv2d_fwd(ctx, net->head4, in8, 1, 0, x0, 8, 0, nullptr, 0, 0, 0.f, 1.f, s, SRB_F_LRELU, N, H, W, stream))) return rc;
@@ -1508,7 +1607,7 @@ extern "C" int srb_pack_batch_run(srb_ctx* ctx, srb_pack_batch* b, srb_stream_t 
 // ------------------------------------------------------------------------------------------
 // fused residual block (srb_resblock.cuh)
 // ------------------------------------------------------------------------------------------
-struct RBMaps { const void* x = nullptr; int N = 0, H = 0, W = 0; CUtensorMap tm; };
+struct RBMaps { const void* x = nullptr; int N = 0, H = 0, W = 0; int kind = 0; CUtensorMap tm; };   // kind 1: 5-D whole-row boxes (tail)
 struct srb_resblock {
     int dtype = 0;
     uint8_t* d_wA = nullptr; uint8_t* d_wB = nullptr;
@@ -1757,13 +1856,16 @@ extern "C" int srb_rowconv_fwd(srb_ctx* ctx, const srb_rowconv* rc, const void* 
         cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
         cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
         cuuint32_t estr[4] = {1, 1, 1, 1};
-        cuuint32_t box[4] = {40, 1, 8, 1};
+        // narrow rows (group-major tiles): the same group of the tile's TR images in one box
+        m->kind = (p.TS == 0 && !(ctx->path & SRB_PATH_GROUP_BOXES)) ? 1 : 0;
+        cuuint32_t box[4] = {40, 1, 8, (cuuint32_t)(m->kind ? p.TR : 1)};
         CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
+    p.gm = m->kind;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_rowconv_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.w = rc->d_w;
@@ -1850,16 +1952,33 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
         m = &t->maps[t->next_map];
         t->next_map ^= 1;
         m->x = nullptr;
-        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
-        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
-        cuuint32_t estr[4] = {1, 1, 1, 1};
-        cuuint32_t box[4] = {32, 1, 8, 1};                              // one group of 8 px, no halo
-        CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
-                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        m->kind = 0;
+        CUresult r = CUDA_ERROR_INVALID_VALUE;
+        if ((W % 8) == 0 && !(ctx->path & SRB_PATH_GROUP_BOXES)) {
+            // whole-row boxes: the groups of a row as a tensor dimension of their own (stride 128 B), so that ONE box
+            // [8 px][8 planes][groups][1 row][images] fills all 16 slots of a stage in the slot order of rb_slot
+            cuuint64_t gdim[5] = {32, 8, (cuuint64_t)(W / 8), (cuuint64_t)H, (cuuint64_t)N};
+            cuuint64_t gstr[4] = {(cuuint64_t)W * H * 16, 128, (cuuint64_t)W * 16, (cuuint64_t)W * H * 16 * 8};
+            cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+            cuuint32_t box[5] = {32, 8, (cuuint32_t)(p.TS == 0 ? p.GX : 16), 1, (cuuint32_t)(p.TS == 0 ? p.TR : 1)};
+            r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 5, const_cast<void*>(x), gdim, gstr, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r == CUDA_SUCCESS) m->kind = 1;
+        }
+        if (r != CUDA_SUCCESS) {
+            cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+            cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+            cuuint32_t estr[4] = {1, 1, 1, 1};
+            cuuint32_t box[4] = {32, 1, 8, 1};                              // one group of 8 px, no halo
+            r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        }
         if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
         m->x = x; m->N = N; m->H = H; m->W = W;
     }
+    p.row5d = m->kind;
     if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_tail9_fwd: too many rows");
     p.total_rows = (int)(sets * H);
     p.w = t->d_w;

@@ -23,8 +23,20 @@ struct RowconvParams {
     void* y;
     float slope;              // LeakyReLU slope applied before the residual add when lrelu != 0
     int lrelu;
+    int gm;                   // narrow rows in group-major slot order: one TMA box [10 px][8 planes][TR images] per group column
     int dbg_skip;
 };
+template <class Params>
+__device__ __forceinline__ RBSlot rc_slot(const Params& p, int ss, int j) {
+    if (!p.gm) return rb_slot(p, ss, j);
+    RBSlot s;
+    s.gx = j / p.TR;
+    s.n = ss * p.TR + (j - s.gx * p.TR);
+    s.in = s.gx < p.GX && s.n < p.N;
+    s.out = s.in;
+    if (!s.in) { s.n = p.N; s.gx = 0; }
+    return s;
+}
 
 struct RCGeom {
     static constexpr int C = 64;
@@ -56,6 +68,8 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 25);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (p.gm && p.GX * p.TR < 16)      // slots no TMA box ever fills: their operand rows read as zeros
+        for (int i = threadIdx.x; i < G::XSTAGES * G::XROW / 16; i += G::THREADS) reinterpret_cast<uint4*>(s_x)[i] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x == 0) {
         for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 8); }
@@ -95,18 +109,24 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
         __syncwarp();
         pdl_wait();
         int xc = 0, g = g_begin;
+        const int gm_box = p.TR * G::XBOX;
+        const uint32_t xbytes = p.gm ? (uint32_t)(p.GX * gm_box) : (uint32_t)G::XROW;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const RBSlot sl = rc_slot(p, sg.ss, lane & 15);
             const int n = sl.n, gx = sl.gx;
+            const int gm_n0 = sg.ss * p.TR < p.N ? sg.ss * p.TR : p.N;
 #pragma unroll 1
             for (int r = sg.hlo; r <= sg.hhi; ++r, ++xc) {          // x rows y0-1 .. y1 (clipped): RBSeg's hidden-row range
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 51);
                 if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
-                if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
+                if (lane == 0) mbar_arrive_expect_tx(&xfull[st], xbytes);
                 __syncwarp();
-                if (lane < 16)
+                if (p.gm) {         // lane gx: the box of group column gx for the tile's TR images (images beyond N: zero-filled)
+                    if (lane < p.GX)
+                        tma_load_4d(s_x + st * G::XROW + lane * gm_box, &tmap_x, &xfull[st], (lane * 8 - 1) * 4, r, 0, gm_n0);
+                } else if (lane < 16)
                     tma_load_4d(s_x + st * G::XROW + lane * G::XBOX, &tmap_x, &xfull[st], (gx * 8 - 1) * 4, r, 0, n);
                 __syncwarp();
             }
@@ -170,7 +190,7 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
         int c = 0, g = g_begin;
         RBSeg sg;
         while (rb_next_seg(p, g, g_end, sg)) {
-            const RBSlot sl = rb_slot(p, sg.ss, grp);
+            const RBSlot sl = rc_slot(p, sg.ss, grp);
             const int n = sl.n, gx = sl.gx;
             const bool valid = sl.out && gx * 8 + i < p.W;
             const size_t px0 = valid ? ((size_t)n * 8 + 4 * half) * HW + (size_t)(gx * 8 + i) : 0;

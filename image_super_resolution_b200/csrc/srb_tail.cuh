@@ -23,6 +23,7 @@ struct TailParams {
     float bias[3];
     void* y;                  // NCHW uint8 (F_U8OUT) or fp32 (F_F32OUT)
     int flags;                // F_TANH, F_U8OUT (+ F_HWC_BGR), F_F32OUT
+    int row5d;                // the tensor map is 5-D [32 words][8 planes][groups][rows][images]: ONE box per input row (W % 8 == 0)
     int dbg_skip;
 };
 
@@ -74,6 +75,8 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < 2 * G::PCOLS * G::PLEN; i += G::THREADS) s_p[i] = 0.f;   // pads between image rows stay zero
+    if (p.row5d && p.TS == 0 && p.GX * p.TR < 16)      // slots the row box never fills: their operand rows read as zeros
+        for (int i = threadIdx.x; i < G::XSTAGES * G::XROW / 16; i += G::THREADS) reinterpret_cast<uint4*>(s_x)[i] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x == 0) {
         for (int i = 0; i < G::XSTAGES; ++i) { mbar_init(&xfull[i], 1); mbar_init(&xempty[i], 1); }
         for (int i = 0; i < G::RY; ++i) { mbar_init(&yafull[i], 1); mbar_init(&yaempty[i], 4); }
@@ -111,15 +114,28 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
         __syncwarp();
         pdl_wait();
         int xc = 0, g = g_begin;
+        const uint32_t xbytes5 = p.TS == 0 ? (uint32_t)(p.TR * p.GX * G::XBOX) : (uint32_t)G::XROW;
         TLSeg sg;
         while (tl_next_seg(p, g, g_end, sg)) {
             const RBSlot sl = rb_slot(p, sg.ss, lane & 15);
+            const RBSlot sl0 = rb_slot(p, sg.ss, 0);
             const int n = sl.n, gx = sl.gx;
 #pragma unroll 1
             for (int r = sg.xlo; r <= sg.xhi; ++r, ++xc) {
                 const int st = xc % G::XSTAGES;
                 mbar_wait<RB_CTRL>(&xempty[st], (uint32_t)(((xc / G::XSTAGES) & 1) ^ 1), 61);
                 if SRB_DBG(p.dbg_skip & 1) { if (lane == 0) mbar_arrive(&xfull[st]); __syncwarp(); continue; }
+                if (p.row5d) {
+                    // the tile's slots are consecutive groups of TR image rows (narrow) or of one strip (wide): one 5-D box
+                    // [8 px][8 planes][groups][1 row][images] lands as [slot][plane][px] — 1 TMA instruction per row instead of 16
+                    // (the producer warp pays ~60-90 clk per instruction: 16 of them set the row period of this kernel)
+                    if (lane == 0) {
+                        mbar_arrive_expect_tx(&xfull[st], xbytes5);
+                        tma_load_5d(s_x + st * G::XROW, &tmap_x, &xfull[st], 0, 0, sl0.gx, r, sl0.n);
+                    }
+                    __syncwarp();
+                    continue;
+                }
                 if (lane == 0) mbar_arrive_expect_tx(&xfull[st], G::XROW);
                 __syncwarp();
                 if (lane < 16)

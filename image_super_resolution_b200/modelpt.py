@@ -116,17 +116,24 @@ class ModelPT:
     def workspace_bytes(self, N: int, H: int, W: int) -> int:
         return int(lib().srb_model_pt_workspace_bytes(N, H, W))
 
+    _IN_LAYOUTS = {"nchw": 0, "hwc_bgr": 1, "hwc_rgb": 2}
+
     @torch.no_grad()
-    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None, layout: str = "nchw") -> torch.Tensor:
+    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None, layout: str = "nchw", in_layout: str = "nchw") -> torch.Tensor:
         """uint8 [N,3,H,W] -> uint8 [N,3,H,W] (rs.py:64 / :94).  layout="hwc_bgr" (device inputs): the result is written as
         [N,H,W,3] with the channels reversed — the frame the video writer takes (rs.py:65-74: RGB2BGR + permute), produced
-        by the tail conv's store instead of two elementwise kernels."""
+        by the tail conv's store instead of two elementwise kernels.  in_layout="hwc_rgb" / "hwc_bgr" (device inputs): x is
+        [N,H,W,3] uint8 as a decoder hands frames over; the head conv's loader reads it directly (no permute, no `.float()`,
+        no Normalize pass — rs.py:60-63)."""
         if layout not in ("nchw", "hwc_bgr"):
             raise ValueError(f"layout {layout!r}")
+        if in_layout not in self._IN_LAYOUTS:
+            raise ValueError(f"in_layout {in_layout!r}")
         if self._net is None:
             raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
-        if x.dim() != 4 or x.shape[1] != 3:
-            raise RuntimeError(f"expected [N,3,H,W], got {tuple(x.shape)}")
+        hwc_in = in_layout != "nchw"
+        if x.dim() != 4 or x.shape[3 if hwc_in else 1] != 3:
+            raise RuntimeError(f"expected {'[N,H,W,3]' if hwc_in else '[N,3,H,W]'}, got {tuple(x.shape)}")
         if x.dtype != torch.uint8:
             # The trace baked the uint8 branch of Normalize (SURVEY F5): a float input is divided by 255
             # too.  Only integral values in [0,255] are representable on the uint8 kernel path.
@@ -135,11 +142,15 @@ class ModelPT:
                 raise RuntimeError("float input with non-integral / out-of-range pixels is not supported by the "
                                    "uint8 kernel path (model.pt divides by 255 internally)")
             x = xr.to(torch.uint8)
-        N, _, H, W = x.shape
+        if hwc_in:
+            N, H, W, _ = x.shape
+        else:
+            N, _, H, W = x.shape
+        oshape = (N, 3, H, W) if layout == "nchw" else (N, H, W, 3)
         if N == 0 or H == 0 or W == 0:
-            return torch.empty_like(x) if layout == "nchw" else x.new_empty((N, H, W, 3))
-        if not x.is_cuda and layout != "nchw":
-            raise RuntimeError("layout='hwc_bgr' takes device inputs (use stream(..., layout='hwc_bgr') for host batches)")
+            return x.new_empty(oshape)
+        if not x.is_cuda and (layout != "nchw" or hwc_in):
+            raise RuntimeError("HWC layouts take device inputs (use stream(..., layout=, in_layout=) for host batches)")
         if not x.is_cuda:  # host tensors: the C ABI's host entry does H2D / D2H itself
             x = x.contiguous()
             y = torch.empty_like(x)
@@ -150,35 +161,39 @@ class ModelPT:
         if x.device != self._device:
             raise RuntimeError(f"input on {x.device}, model on {self._device}")
         x = x.contiguous()
-        y = out if out is not None else (torch.empty_like(x) if layout == "nchw" else x.new_empty((N, H, W, 3)))
+        y = out if out is not None else x.new_empty(oshape)
         if y.numel() != x.numel() or y.dtype != torch.uint8 or not y.is_contiguous() or y.device != x.device:
             raise RuntimeError("out must be a contiguous uint8 tensor of the input's size on the input's device")
         nbytes = self.workspace_bytes(N, H, W)
         ws = self._workspace(nbytes)
         stream = C.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
         with torch.cuda.device(self._device):
-            check(lib().srb_model_pt_forward_frames(self._ctx.handle, self._net, x.data_ptr(), y.data_ptr(),
-                                                    1 if layout == "hwc_bgr" else 0, N, H, W, ws.data_ptr(), ws.numel(), stream),
-                  "srb_model_pt_forward_frames")
+            check(lib().srb_model_pt_forward_io(self._ctx.handle, self._net, x.data_ptr(), self._IN_LAYOUTS[in_layout], y.data_ptr(),
+                                                1 if layout == "hwc_bgr" else 0, N, H, W, ws.data_ptr(), ws.numel(), stream),
+                  "srb_model_pt_forward_io")
         return y
 
     __call__ = forward
 
     @torch.no_grad()
-    def stream(self, batches, depth: int = 2, layout: str = "nchw", graphs: bool = True):
+    def stream(self, batches, depth: int = 2, layout: str = "nchw", graphs: bool = True, in_layout: str = "nchw"):
         """Pipelined host-to-host inference over a sequence of uint8 host batches — the shape of rs.py's video loop
         (rs.py:58-76: frames from the reader -> model -> writer).  Yields one pinned uint8 host tensor per input batch, in
         order.  H2D of batch i+1 and D2H of batch i-1 run on copy streams while the kernels of batch i run on the compute
         stream; `depth` batches are in flight.  A yielded tensor stays valid until `depth` more items have been taken from the
         generator (the ring holds 2 * depth + 1 slots; the slot is then reused): write it out or copy it before that, as a
         frame writer does.  `list(model.stream(...))` of more than depth + 1 batches therefore needs a .clone() per item.
-        The ring of device / pinned buffers is kept on the model between calls, and (graphs=True) the 12 launches of a slot's
+        The ring of device / pinned buffers is kept on the model between calls, and (graphs=True) the 11 launches of a slot's
         forward are captured once per (slot, shape) as a CUDA graph: a step costs the host three enqueues, which is what
-        keeps eight ranks sharing one host at the single-GPU rate."""
+        keeps eight ranks sharing one host at the single-GPU rate.  in_layout="hwc_rgb" / "hwc_bgr": the host batches are
+        [N,H,W,3] frames (a decoder's layout); they are uploaded as they are and read by the head conv's loader."""
         if self._net is None:
             raise RuntimeError("call .to('cuda') first (as rs.py:49 does)")
         if layout not in ("nchw", "hwc_bgr"):
             raise ValueError(f"layout {layout!r}")
+        if in_layout not in self._IN_LAYOUTS:
+            raise ValueError(f"in_layout {in_layout!r}")
+        hwc_in = in_layout != "nchw"
         depth = max(1, int(depth))
         dev = self._device
         st = self.__dict__.get("_stream_state")
@@ -191,28 +206,29 @@ class ModelPT:
         i = 0
 
         def make_slot(shape):
-            oshape = shape if layout == "nchw" else (shape[0], shape[2], shape[3], 3)
+            n_, h_, w_ = (shape[0], shape[1], shape[2]) if hwc_in else (shape[0], shape[2], shape[3])
+            oshape = (n_, 3, h_, w_) if layout == "nchw" else (n_, h_, w_, 3)
             x_dev = torch.empty(shape, dtype=torch.uint8, device=dev)
             y_dev = torch.empty(oshape, dtype=torch.uint8, device=dev)
             y_host = torch.empty(oshape, dtype=torch.uint8).pin_memory()
             g = None
             if graphs:
                 with torch.cuda.stream(s_c):               # eager once: workspace, tensor-map caches, kernel attributes
-                    self.forward(x_dev, out=y_dev, layout=layout)
+                    self.forward(x_dev, out=y_dev, layout=layout, in_layout=in_layout)
                 torch.cuda.synchronize(dev)
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=s_c, capture_error_mode="thread_local"):   # (NCCL watchdog / sampler threads may call CUDA)
-                    self.forward(x_dev, out=y_dev, layout=layout)
+                    self.forward(x_dev, out=y_dev, layout=layout, in_layout=in_layout)
             # (the captured launches hold the address of the workspace they were recorded with: the slot keeps it alive)
             return (x_dev, y_dev, y_host, torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event(), g, self._ws)
 
         for xb in batches:
-            if xb.dtype != torch.uint8 or xb.dim() != 4 or xb.shape[1] != 3 or xb.is_cuda:
-                raise RuntimeError("stream() takes uint8 host tensors [N,3,H,W]")
+            if xb.dtype != torch.uint8 or xb.dim() != 4 or xb.shape[3 if hwc_in else 1] != 3 or xb.is_cuda:
+                raise RuntimeError("stream() takes uint8 host tensors [N,3,H,W] ([N,H,W,3] with in_layout='hwc_*')")
             xb = xb.contiguous()
             if len(pending) > depth:                       # (never: a batch is yielded as soon as depth + 1 are pending)
                 raise RuntimeError("internal: ring overrun")
-            key = (i % nbuf, nbuf, layout, tuple(xb.shape), bool(graphs))
+            key = (i % nbuf, nbuf, layout, in_layout, tuple(xb.shape), bool(graphs))
             sl = st["slots"].get(key)
             if sl is None:
                 for j in pending:                          # (capturing synchronises: nothing may be in flight on a slot)
@@ -227,7 +243,7 @@ class ModelPT:
                 if g is not None:
                     g.replay()
                 else:
-                    self.forward(x_dev, out=y_dev, layout=layout)
+                    self.forward(x_dev, out=y_dev, layout=layout, in_layout=in_layout)
                 ev_c.record(s_c)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_c)

@@ -474,6 +474,47 @@ class RowConv:
             pass
 
 
+class Head:
+    """Normalize + conv0 9x9 3 -> 64 (+ bias, LeakyReLU) in one launch straight from uint8 frames (srb_head_*): `norm_(frames)`
+    (rs.py:62-63, utils/datasets.py:65-71) fused into the first conv of the model.pt graph (utils/models.py:687, :97-98)."""
+    LAYOUTS = {"nchw": 0, "hwc_bgr": 1, "hwc_rgb": 2}
+
+    def __init__(self, ctx: Context, w, b, dtype=SRB_DT_F16):
+        arrs = [np.ascontiguousarray(t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t, dtype=np.float32)
+                for t in (w, b)]
+        if arrs[0].shape != (64, 3, 9, 9) or arrs[1].shape != (64,):
+            raise ValueError("Head: weight must be [64][3][9][9], bias [64]")
+        self.ctx, self.dtype = ctx, dtype_code(dtype)
+        h = C.c_void_p()
+        check(lib().srb_head_create(ctx.handle, *[_lib.f32_ptr(a) for a in arrs], self.dtype, C.byref(h)), "srb_head_create")
+        self.handle = h
+
+    def forward(self, x: torch.Tensor, mean, std, slope: float, layout: str = "nchw", max_pixel_value: float = 255.0,
+                out: torch.Tensor | None = None) -> torch.Tensor:
+        _require_cuda(x, "x")
+        if x.dtype != torch.uint8 or x.dim() != 4 or not x.is_contiguous():
+            raise RuntimeError("Head: x must be a contiguous uint8 tensor [N,3,H,W] (nchw) or [N,H,W,3] (hwc_*)")
+        if layout == "nchw":
+            N, ch, H, W = x.shape
+        else:
+            N, H, W, ch = x.shape
+        if ch != 3:
+            raise RuntimeError("Head: three channels")
+        y = out if out is not None else c8_empty(N, 8, H, W, torch.bfloat16 if self.dtype == SRB_DT_BF16 else torch.float16, x.device)
+        check(lib().srb_head_fwd(self.ctx.handle, self.handle, x.data_ptr(), self.LAYOUTS[layout], (C.c_float * 3)(*mean),
+                                 (C.c_float * 3)(*std), float(max_pixel_value), y.data_ptr(), float(slope), N, H, W,
+                                 _stream_ptr(x.device)), "srb_head_fwd")
+        return y
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                lib().srb_head_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
 class Tail9:
     """Row-fold 9x9 conv 64 -> 3 + bias (+ tanh) -> NCHW uint8 / fp32 in one launch (srb_tail9_*): conv2 + TanhToArrayImage
     of the model.pt graph (utils/models.py:691, :448-451)."""

@@ -248,7 +248,7 @@ class ByteSink:
 
 @torch.no_grad()
 def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor], sink, bgr: bool = True,
-                   threads: bool | None = None) -> int:
+                   threads: bool | None = None, in_layout: str = "nchw") -> int:
     """rs.py:60-74 with the model call replaced: each uint8 [B,3,H,W] batch is one unit, dealt round-robin over the
     devices; results leave in frame order as HWC (BGR like RGB2BGR, utils/datasets.py:113-124) into sink.writeFrame.
 
@@ -256,7 +256,9 @@ def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor
     overlap the kernels; the forward is a captured graph); batch i goes to device i mod G and the results are taken in frame
     order, so the writer gets each pinned result while the following batches compute.  threads (default: G > 1): one feeder
     thread per device drives its replica's stream — the CUDA calls release the GIL, so the enqueue work of G devices and the
-    writer's memcpy overlap instead of queueing behind one Python thread — and the calling thread only writes frames."""
+    writer's memcpy overlap instead of queueing behind one Python thread — and the calling thread only writes frames.
+    in_layout="hwc_rgb" / "hwc_bgr": the batches are [B,H,W,3] frames as a decoder delivers them; they are uploaded as they
+    are and conv0's loader reads them (no permute, `.float()` or Normalize pass: rs.py:60-63 disappears into the head kernel)."""
     import threading
     import queue as _queue
     sm = model if isinstance(model, ShardedModel) else None
@@ -296,7 +298,7 @@ def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor
             yield item
 
     if not threads:
-        gens = [m.stream(feeder(d), depth=2, layout=layout) for d, m in enumerate(reps)]
+        gens = [m.stream(feeder(d), depth=2, layout=layout, in_layout=in_layout) for d, m in enumerate(reps)]
         i = 0
         while True:
             m = reps[i % G]
@@ -316,7 +318,7 @@ def upscale_frames(model: ModelPT | ShardedModel, batches: Iterable[torch.Tensor
     def worker(d):
         try:
             with torch.cuda.device(reps[d]._device):
-                for y in reps[d].stream(feeder(d), depth=2, layout=layout):
+                for y in reps[d].stream(feeder(d), depth=2, layout=layout, in_layout=in_layout):
                     while not stop.is_set():
                         try:
                             outq[d].put(y, timeout=0.1)

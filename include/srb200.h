@@ -70,6 +70,8 @@ int srb_num_sms(const srb_ctx* ctx);
 #define SRB_PATH_UNSORTED_UNITS 131072    /* batched weight gradient: units in job order                                */
 #define SRB_PATH_WS_LARGE_TILING 262144   /* large tiling for the weight-streaming convs only                           */
 #define SRB_PATH_NO_PAIR 1048576          /* fused residual block on single CTAs (cta_group::1) instead of CTA pairs          */
+#define SRB_PATH_GROUP_BOXES 2097152      /* row-fold conv1 / tail: one TMA box per 8-px group instead of whole-row boxes       */
+#define SRB_PATH_PAIR4_HEAD 4194304       /* Normalize as its own pass into pixel-pair granules + conv0 on the tiled kernel    */
 int srb_set_option(srb_ctx* ctx, int key, int value);
 
 /* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for
@@ -167,8 +169,23 @@ int srb_model_pt_forward(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uin
  * (utils/datasets.py:113-124) + permute + contiguous before FFMPEG_recorder.writeFrame (utils/ffmpeg.py:69-76). */
 #define SRB_LAYOUT_NCHW_RGB 0
 #define SRB_LAYOUT_NHWC_BGR 1
+#define SRB_LAYOUT_NHWC_RGB 2      /* input only */
 int srb_model_pt_forward_frames(srb_ctx* ctx, srb_net* net, const uint8_t* in_nchw, uint8_t* out, int out_layout, int N, int H,
                                 int W, void* workspace, size_t ws_bytes, srb_stream_t stream);
+/* The ingest half of the same glue: the frames may arrive as uint8 NCHW RGB (what the reference's
+ * reader yields, utils/datasets.py:431-463, and rs.py:60-63 turns into `norm_(frames.to(device).float())`) or as uint8 HWC
+ * frames in RGB or BGR order (what a decoder hands over); Normalize (utils/datasets.py:65-71) is part of conv0's loader
+ * either way, so `frames.float()`, `norm_` and any permute never run as passes of their own. */
+int srb_model_pt_forward_io(srb_ctx* ctx, srb_net* net, const uint8_t* in, int in_layout, uint8_t* out, int out_layout, int N,
+                            int H, int W, void* workspace, size_t ws_bytes, srb_stream_t stream);
+/* Normalize + conv0 (9x9, 3 -> 64, BN folded) + LeakyReLU in one launch, uint8 frames in (in_layout as above), C8 planes
+ * [N][8][H][W][8] out: Normalize.forward (utils/datasets.py:65-71) fused into Conv._forward_impl of conv0
+ * (utils/models.py:97-98, :687) — rs.py:62-64's `norm_(frames)` + the first layer of `model(frames)`. */
+typedef struct srb_head srb_head;
+int srb_head_create(srb_ctx* ctx, const float* w_64x3x9x9, const float* bias64, int dtype, srb_head** out);
+void srb_head_destroy(srb_head* h);
+int srb_head_fwd(srb_ctx* ctx, const srb_head* h, const uint8_t* in, int in_layout, const float mean[3], const float std_[3],
+                 float max_pixel_value, void* y_c8, float lrelu_slope, int N, int H, int W, srb_stream_t stream);
 /* host uint8 NCHW -> host uint8 NCHW (H2D, forward, D2H, sync) — the call a non-torch host would make */
 int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host, uint8_t* out_host, int N,
                               int H, int W);
@@ -180,8 +197,8 @@ int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host
 #define SRB_COPY_D2D 2
 int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_t dst_plane, const void* src, size_t src_pitch,
                      size_t src_plane, int planes, size_t width, size_t height, int kind, srb_stream_t stream);
-/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (12: normalise, head, 8 fused
- * residual blocks, conv1, tail) */
+/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (11: head with the ingest folded
+ * in, 8 fused residual blocks, conv1, tail) */
 int srb_model_pt_launches(int H, int W);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */

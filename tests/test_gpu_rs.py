@@ -60,6 +60,10 @@ def test_sharded_model_and_frame_path(model, ndev, nb):
     sink_rgb = rs.ByteSink(keep=True)
     rs.upscale_frames(sm, batches[:2], sink_rgb, bgr=False)
     assert np.array_equal(sink_rgb.kept[3], model(batches[1].cuda())[1].permute(1, 2, 0).cpu().numpy())
+    # HWC BGR frames in (a decoder's layout), HWC BGR frames out: the same bytes
+    sink_hwc = rs.ByteSink(keep=True)
+    rs.upscale_frames(sm, [b.permute(0, 2, 3, 1).flip(-1).contiguous() for b in batches], sink_hwc, in_layout="hwc_bgr")
+    assert len(sink_hwc.kept) == 2 * nb and all(np.array_equal(a, b) for a, b in zip(sink_hwc.kept, sink.kept))
 
 
 def test_stream_pipelined_host_batches_match_forward(model):
