@@ -37,6 +37,9 @@ struct HeadParams {
     void* y;                  // C8 planes [N][8][H][W][8]
 };
 
+#ifndef HD_STAGES
+#define HD_STAGES 4
+#endif
 struct HDGeom {
     static constexpr int TW = 8, TH = 16, NT = 4, SUPER_H = TH * NT;       // 8 x 64 output pixels per pipeline step
     static constexpr int HALO_H = SUPER_H + 8;                             // 72 rows
@@ -45,7 +48,7 @@ struct HDGeom {
     static constexpr int PLANE = HALO_H * ROWP;                            // 14 976 B between plane A and plane B
     static constexpr int STAGE_BYTES = 2 * PLANE;
     static constexpr int STAGE_STRIDE = (STAGE_BYTES + 1023) / 1024 * 1024;
-    static constexpr int STAGES = 4;
+    static constexpr int STAGES = HD_STAGES;
     static constexpr int KSTEPS = 18;                                      // 9 dy x 2
     static constexpr int WSTEP = 2 * 64 * 16;                              // 2 KB per K-step
     static constexpr int W_BYTES = KSTEPS * WSTEP;                         // 36 864
@@ -54,7 +57,7 @@ struct HDGeom {
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 256;
     static constexpr int THREADS = 384;
     static constexpr int PRODUCERS = 3;                                    // warps 0, 2, 3
-    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+    static_assert(SMEM_BYTES <= 227 * 1024 && STAGES <= 8, "shared memory budget / barrier layout");
     static_assert(HALO_H <= 32 * PRODUCERS, "one halo row per producer thread");
 };
 
@@ -74,11 +77,11 @@ __global__ void __launch_bounds__(HDGeom::THREADS, 1) head_ingest_kernel(const H
     uint16_t* s_lut = reinterpret_cast<uint16_t*>(smem + G::OFF_LUT);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
     uint64_t* full = bars;              // [STAGES] producers -> MMA
-    uint64_t* empty = bars + 4;         // [STAGES] MMA -> producers
-    uint64_t* tfull = bars + 8;         // [2] accumulator set complete      MMA -> epilogue
-    uint64_t* tempty = bars + 10;       // [2] drained                       epilogue -> MMA
-    uint64_t* wbar = bars + 12;
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 14);
+    uint64_t* empty = bars + 8;         // [STAGES] MMA -> producers
+    uint64_t* tfull = bars + 16;        // [2] accumulator set complete      MMA -> epilogue
+    uint64_t* tempty = bars + 18;       // [2] drained                       epilogue -> MMA
+    uint64_t* wbar = bars + 20;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 22);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // look-up tables: [c][v] = 16-bit operand of ((v / maxv) - mean[c]) / std[c] (three rounded fp32 steps like the reference's

@@ -38,15 +38,19 @@ __device__ __forceinline__ RBSlot rc_slot(const Params& p, int ss, int j) {
     return s;
 }
 
+#ifndef RC_XSTAGES
+#define RC_XSTAGES 4
+#endif
 struct RCGeom {
     static constexpr int C = 64;
-    static constexpr int XBOX = 8 * 10 * 16, XROW = 16 * XBOX, XSTAGES = 4;
+    static constexpr int XBOX = 8 * 10 * 16, XROW = 16 * XBOX, XSTAGES = RC_XSTAGES;
     static constexpr int KS = 3 * (C / 16);                   // 12 K-steps per row
     static constexpr int W_STEP = 2 * 3 * C * 16;              // 6144
     static constexpr int W_BYTES = KS * W_STEP;                // 73728
     static constexpr int RY = 8;                               // accumulator ring: 8 x 64 = 512 TMEM columns
     static constexpr int OFF_W = 0, OFF_X = W_BYTES, OFF_BIAS = OFF_X + XSTAGES * XROW, OFF_BAR = OFF_BIAS + C * 4;
-    static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 256;
+    static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
+    static_assert(XSTAGES <= 8, "barrier layout");
     static constexpr int THREADS = 640;                        // 4 control warps + two epilogue sets of 8 warps
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
@@ -61,11 +65,11 @@ __global__ void __launch_bounds__(RCGeom::THREADS, 1) rowconv_kernel(const __gri
     uint8_t* s_x = smem + G::OFF_X;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
     uint64_t* xfull = bars;            // [XSTAGES] TMA -> MMA
-    uint64_t* xempty = bars + 4;       // [XSTAGES] MMA -> TMA
-    uint64_t* yafull = bars + 8;       // [RY] accumulator row complete      MMA -> epilogue
-    uint64_t* yaempty = bars + 16;     // [RY] drained and re-armed          epilogue -> MMA
-    uint64_t* wbar = bars + 24;
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 25);
+    uint64_t* xempty = bars + 8;       // [XSTAGES] MMA -> TMA
+    uint64_t* yafull = bars + 16;      // [RY] accumulator row complete      MMA -> epilogue
+    uint64_t* yaempty = bars + 24;     // [RY] drained and re-armed          epilogue -> MMA
+    uint64_t* wbar = bars + 32;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 33);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (p.gm && p.GX * p.TR < 16)      // slots no TMA box ever fills: their operand rows read as zeros

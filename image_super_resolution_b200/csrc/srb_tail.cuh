@@ -27,9 +27,12 @@ struct TailParams {
     int dbg_skip;
 };
 
+#ifndef TL_XSTAGES
+#define TL_XSTAGES 6
+#endif
 struct TLGeom {
     static constexpr int C = 64, NS = 32, TAPS = 9;            // input channels, columns per row accumulator, dy taps
-    static constexpr int XBOX = 8 * 8 * 16, XROW = 16 * XBOX, XSTAGES = 6;       // 1 KB boxes, 16 KB per row
+    static constexpr int XBOX = 8 * 8 * 16, XROW = 16 * XBOX, XSTAGES = TL_XSTAGES;       // 1 KB boxes, 16 KB per row
     static constexpr int KS = C / 16;                          // 4 K-steps per row
     static constexpr int BROWS = TAPS * NS;                    // 288 B rows per granule
     static constexpr int W_STEP = 2 * BROWS * 16;              // 9216

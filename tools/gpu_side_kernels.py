@@ -38,6 +38,8 @@ def make(path):
 def main():
     torch.manual_seed(3)
     shapes = [(4, 64, 64), (3, 40, 56), (5, 33, 40), (2, 24, 200), (1, 50, 136), (2, 17, 128), (1, 20, 264), (3, 9, 16), (1, 30, 1000)]
+    if "--quick" in sys.argv:
+        shapes = shapes[:2]
     g.manual_seed(11); ca, ra, ta = make(0)
     g.manual_seed(11); cb, rb, tb = make(_lib.PATH_GROUP_BOXES)
     ok = True
@@ -54,6 +56,20 @@ def main():
     ca.check_device(); cb.check_device()
     print("PATHS", "BIT-EQUAL" if ok else "DIFFER", flush=True)
     if "--shapes-only" in sys.argv:
+        return
+    if "--quick" in sys.argv:
+        x = torch.randn(256, 8, 64, 64, 8, device=dev).half(); res = torch.randn_like(x); y = torch.empty_like(x)
+        out = torch.empty(256, 3, 64, 64, dtype=torch.uint8, device=dev)
+        g.manual_seed(4)
+        hd = ops.Head(ca, torch.randn(64, 3, 9, 9, generator=g) / 15.6, torch.randn(64, generator=g) * 0.1, "fp16")
+        xi = torch.randint(0, 256, (256, 3, 64, 64), dtype=torch.uint8, device=dev); yo = torch.empty_like(xi)
+        mean, std = [0.485, 0.456, 0.406], [0.229, 0.224, 0.225]
+        m1 = cold(lambda: ra.forward(x, y, res)); m2 = cold(lambda: ta.forward(x, out=out)); m3 = cold(lambda: hd.forward(xi, mean, std, 0.2, out=y))
+        model = srb.load(os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")).to(dev).eval()
+        for _ in range(3): model(xi, out=yo)
+        f = cold(lambda: model(xi, out=yo), 12)
+        print(f"QUICK {os.environ.get('SRB200_LIB', 'product')[-16:]:16s} rowconv {m1[0]:6.1f}  tail {m2[0]:6.1f}  head {m3[0]:6.1f}  forward {f[0]:6.1f} us = {256 * 64 * 64 / f[0]:.0f} Mpix/s", flush=True)
+        ca.check_device()
         return
     x = torch.randn(256, 8, 64, 64, 8, device=dev).half(); res = torch.randn_like(x); y = torch.empty_like(x)
     out = torch.empty(256, 3, 64, 64, dtype=torch.uint8, device=dev)
