@@ -30,6 +30,9 @@ struct TailParams {
 #ifndef TL_XSTAGES
 #define TL_XSTAGES 6
 #endif
+#ifndef TL_SETS
+#define TL_SETS 2
+#endif
 struct TLGeom {
     static constexpr int C = 64, NS = 32, TAPS = 9;            // input channels, columns per row accumulator, dy taps
     static constexpr int XBOX = 8 * 8 * 16, XROW = 16 * XBOX, XSTAGES = TL_XSTAGES;       // 1 KB boxes, 16 KB per row
@@ -40,9 +43,10 @@ struct TLGeom {
     static constexpr int RY = 16;                              // accumulator ring: 16 x 32 = 512 TMEM columns
     static constexpr int PLEN = 256, PCOLS = 27;               // exchange buffer [27 columns][256 padded pixels] fp32 per set
     static constexpr int P_BYTES = PCOLS * PLEN * 4;           // 27 648
-    static constexpr int OFF_W = 0, OFF_X = W_BYTES, OFF_P = OFF_X + XSTAGES * XROW, OFF_BAR = OFF_P + 2 * P_BYTES;
+    static constexpr int SETS = TL_SETS;                        // epilogue sets of 4 warps alternating output rows
+    static constexpr int OFF_W = 0, OFF_X = W_BYTES, OFF_P = OFF_X + XSTAGES * XROW, OFF_BAR = OFF_P + SETS * P_BYTES;
     static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 512;
-    static constexpr int THREADS = 384;                        // 4 control warps + two epilogue sets of 4 warps
+    static constexpr int THREADS = 128 + 128 * SETS;            // 4 control warps + SETS epilogue sets of 4 warps
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -77,7 +81,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 49);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < 2 * G::PCOLS * G::PLEN; i += G::THREADS) s_p[i] = 0.f;   // pads between image rows stay zero
+    for (int i = threadIdx.x; i < G::SETS * G::PCOLS * G::PLEN; i += G::THREADS) s_p[i] = 0.f;   // pads between image rows stay zero
     if (p.row5d && p.TS == 0 && p.GX * p.TR < 16)      // slots the row box never fills: their operand rows read as zeros
         for (int i = threadIdx.x; i < G::XSTAGES * G::XROW / 16; i += G::THREADS) reinterpret_cast<uint4*>(s_x)[i] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x == 0) {
@@ -222,7 +226,7 @@ __global__ void __launch_bounds__(TLGeom::THREADS, 1) tail9_kernel(const __grid_
             const bool inside = sl.in && x < p.W, valid = sl.out && x < p.W;
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
-                if ((c & 1) != set) continue;
+                if ((c % G::SETS) != set) continue;
                 const int slot = c % G::RY;
                 mbar_wait<RB_SLEEP>(&yafull[slot], (uint32_t)((c / G::RY) & 1), 65);
                 tc_fence_after();
