@@ -163,6 +163,20 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+__device__ __forceinline__ uint4 rb_ld_res(const uint4* p) {
+#if RB_IO_NOALLOC >= 1
+    return ldg_nc16(p);
+#else
+    return __ldg(p);
+#endif
+}
+__device__ __forceinline__ void rb_st_out(uint4* p, uint4 v) {
+#if RB_IO_NOALLOC >= 2
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+#else
+    *p = v;
+#endif
+}
 __device__ __forceinline__ void rb_trace(const ResblockParams& p, int row, int k) {
     if (SRB_DBG(p.dbg_trace != nullptr) && blockIdx.x == 0 && row < 32) p.dbg_trace[row * 32 + k] = clock64();
 }
@@ -205,6 +219,12 @@ __device__ __forceinline__ bool rb_next_seg(const Params& p, int& g, int g1, RBS
 #endif
 #ifndef RB_EARLY_REL
 #define RB_EARLY_REL 1
+#endif
+#ifndef RB_HALO_MERGED
+#define RB_HALO_MERGED 1
+#endif
+#ifndef RB_IO_NOALLOC
+#define RB_IO_NOALLOC 2      // 1: residual loads with L1::no_allocate; 2: the result's stores as well (forward 835.6 -> 833.5 us, profiles/ab_halo_io_r2.log)
 #endif
 struct RBSlot { int n, gx; bool in, out; };
 template <class Params>
@@ -634,6 +654,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             const int nb = gmt ? p.TR * G::HBOX : G::HBOX;
             const bool left = i == 0 && (gmt ? sl.in && sl.gx > 0 : grp > 0 && (p.TS > 0 || sl.gx > 0));
             const bool right = i == 7 && (gmt ? sl.in && sl.gx < p.GX - 1 : grp < 15 && (p.TS > 0 || sl.gx < p.GX - 1));
+            const int halo_off = left ? 9 * 16 - nb : nb;
 #pragma unroll 1
             for (int h = sg.hlo; h <= sg.hhi; ++h) {
                 const int c = hbase + h - sg.hlo;
@@ -690,8 +711,16 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
 #pragma unroll
                 for (int pl = 0; pl < 4; ++pl) {
                     sts_u4(box + pl * 160 + (i + 1) * 16, o[pl]);
+#if RB_HALO_MERGED
+                    // the edge pixels' copies into the neighbouring groups' halo slots — pixel 0 into the right halo slot of the group
+                    // to the left, pixel 7 into the left halo slot of the group to the right — as ONE store: a 16-byte store is issued
+                    // per quarter-warp, so two predicated stores with one active lane per quarter each cost 4 + 4 wavefronts of the L1
+                    // data pipe (ncu source page: 3.5 per instruction), the merged one 4 (the two lanes of a quarter hit different banks)
+                    if (left || right) sts_u4(box + halo_off + pl * 160, o[pl]);
+#else
                     if (left) sts_u4(box - nb + pl * 160 + 9 * 16, o[pl]);           // right halo slot of the group to the left
                     if (right) sts_u4(box + nb + pl * 160, o[pl]);                   // left halo slot of the group to the right
+#endif
                 }
                 if (tr) rb_trace(p, c, 13);
                 if constexpr (!RB_EARLY_REL) { tmem_st_wait(); tc_fence_before(); }
@@ -741,7 +770,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
             uint4 nxt[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-                nxt[j] = valid && !no_ld ? __ldg(xg + j * plane + (size_t)sg.y0 * p.W) : make_uint4(0, 0, 0, 0);
+                nxt[j] = valid && !no_ld ? rb_ld_res(xg + j * plane + (size_t)sg.y0 * p.W) : make_uint4(0, 0, 0, 0);
 #pragma unroll 1
             for (int y = sg.y0; y < sg.y1; ++y, ++c) {
                 uint4 rq[4];
@@ -774,7 +803,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (tr) rb_trace(p, c, 10);
                 if (y + 1 < sg.y1 && valid && !no_ld) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) nxt[j] = __ldg(xg + j * plane + (size_t)(y + 1) * p.W);
+                    for (int j = 0; j < 4; ++j) nxt[j] = rb_ld_res(xg + j * plane + (size_t)(y + 1) * p.W);
                 }
                 if (tr) rb_trace(p, c, 8);
                 // (the bias index must be a compile-time constant to become a constant-bank operand: one copy per channel half)
@@ -791,7 +820,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                             if (RB_BIAS_MODE == 1) { a += p.bias[OFF + 8 * j + 2 * k]; b += p.bias[OFF + 8 * j + 2 * k + 1]; }
                             ov[k] = pack2<BF16>(a + f.x, b + f.y);
                         }
-                        if (valid && !no_st) yg[j * plane + (size_t)y * p.W] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
+                        if (valid && !no_st) rb_st_out(yg + j * plane + (size_t)y * p.W, make_uint4(ov[0], ov[1], ov[2], ov[3]));
                     }
                 };
                 if (half == 0) finish(std::integral_constant<int, G::CH>{});
