@@ -33,9 +33,13 @@ FLOP_PER_PX = 725760  # algorithmic FLOP (2*MAC) per pixel of the
 LAUNCH_FLOP_PX = [2 * 243 * 64] + [2 * 576 * 32, 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
 LAUNCH_NAMES = ["ingest_conv9x9_head_3_64"] + ["conv3x3_64_32", "conv3x3_32_64"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
 assert sum(LAUNCH_FLOP_PX) == FLOP_PER_PX
-# with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 11 launches
+# with the fused residual-block kernel (widths that qualify, srb_resblock_supported): 11 launches, 10 when conv1 and the tail
+# run as one launch (rows of at least 57 pixels, srb_c1tail_supported)
 FUSED_FLOP_PX = [2 * 243 * 64] + [2 * 576 * 32 + 2 * 288 * 64] * 8 + [2 * 576 * 64, 2 * 5184 * 3]
 FUSED_NAMES = ["ingest_conv9x9_head_3_64"] + ["resblock_64_32_64_fused"] * 8 + ["conv3x3_64_64", "conv9x9_tail_64_3"]
+FUSED10_FLOP_PX = FUSED_FLOP_PX[:9] + [2 * 576 * 64 + 2 * 5184 * 3]
+FUSED10_NAMES = FUSED_NAMES[:9] + ["conv3x3_64_64_skip_conv9x9_tail_64_3_fused"]
+assert sum(FUSED10_FLOP_PX) == FLOP_PER_PX
 assert sum(FUSED_FLOP_PX) == FLOP_PER_PX
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the dominant kernel at the bench shape, from the
 # one `ncu --set full` capture of a whole forward summarised in profiles/ncu_fwd_r1_full.txt (mean of the 8 launches:
@@ -397,7 +401,8 @@ def run_ours(args, rank, world, local):
     # ---- per-launch durations (CUDA events recorded by the library on the launching stream) ----
     ctxh = model._ctx.handle
     nl = model.launches_per_forward(HH, WW)
-    names, flops = (FUSED_NAMES, FUSED_FLOP_PX) if nl == len(FUSED_NAMES) else (LAUNCH_NAMES, LAUNCH_FLOP_PX)
+    names, flops = ((FUSED10_NAMES, FUSED10_FLOP_PX) if nl == len(FUSED10_NAMES) else (FUSED_NAMES, FUSED_FLOP_PX) if nl == len(FUSED_NAMES)
+                    else (LAUNCH_NAMES, LAUNCH_FLOP_PX))
     acc = [0.0] * nl
     buf = (C.c_float * 64)()
     check(lib().srb_profile_enable(ctxh, 1))
@@ -410,7 +415,7 @@ def run_ours(args, rank, world, local):
     # the trunk's eight fused blocks overlap through programmatic dependent launch (a block's prologue runs under its predecessor's
     # tail): their AVERAGE duration inside the pipeline = the trunk's span / 8, events only around the trunk
     trunk_ms = None
-    if nl == len(FUSED_NAMES):
+    if nl in (len(FUSED_NAMES), len(FUSED10_NAMES)):
         check(lib().srb_profile_enable(ctxh, 2))
         t_acc = 0.0
         for _ in range(K):

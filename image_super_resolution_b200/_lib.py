@@ -39,6 +39,8 @@ SIGNATURES = {
     "srb_model_pt_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_frames": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),
     "srb_model_pt_forward_io": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "srb_c1tail_supported": (_i, [_i, _i]),
+    "srb_c1tail_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "srb_head_create": (_i, [_vp, _vp, _vp, _i, C.POINTER(_vp)]),
     "srb_head_destroy": (None, [_vp]),
     "srb_head_fwd": (_i, [_vp, _vp, _vp, _i, _fp, _fp, C.c_float, _vp, C.c_float, _i, _i, _i, _vp]),
@@ -109,7 +111,7 @@ DEBUG_SIGNATURES = {
 OPT_MAX_GRID, OPT_PATH = 1, 2
 PATH_UNFUSED_TRUNK, PATH_NO_PDL, PATH_TILED_CONV1, PATH_TILED_TAIL, PATH_C8_HEAD = 8, 1024, 8192, 16384, 32768
 PATH_LARGE_TILING, PATH_UNSORTED_UNITS, PATH_WS_LARGE_TILING, PATH_NO_PAIR = 65536, 131072, 262144, 1048576
-PATH_GROUP_BOXES, PATH_PAIR4_HEAD = 2097152, 4194304
+PATH_GROUP_BOXES, PATH_PAIR4_HEAD, PATH_SPLIT_C1TAIL = 2097152, 4194304, 8388608
 
 _lib = None
 _lock = threading.Lock()

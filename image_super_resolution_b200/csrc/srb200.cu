@@ -27,6 +27,7 @@
 #include "srb_resblock.cuh"
 #include "srb_rowconv.cuh"
 #include "srb_head.cuh"
+#include "srb_c1tail.cuh"
 #include "srb_tail.cuh"
 #include "srb_optim.cuh"
 #include "srb_bn.cuh"
@@ -980,7 +981,7 @@ extern "C" size_t srb_model_pt_workspace_bytes(int N, int H, int W) {
 }
 
 // kernels one forward enqueues: head (ingest + conv0), 8 fused blocks (or 16 convs when the width does not qualify), conv1, tail
-extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? 11 : 19; }
+extern "C" int srb_model_pt_launches(int H, int W) { return srb_resblock_supported(H, W) ? (srb_c1tail_supported(H, W) ? 10 : 11) : 19; }
 
 #ifdef SRB_DEBUG
 // measurement only: per-step clock trace of CTA 0 of the next conv launches (512 int64 device buffer, or NULL)
@@ -1123,6 +1124,12 @@ extern "C" int srb_model_pt_forward_io(srb_ctx* ctx, srb_net* net, const uint8_t
         cur = nxt;
     }
     // cur == rb after 8 blocks; long skip adds conv0's (post-activation) output
+    if (fused && !(ctx->path & (SRB_PATH_TILED_CONV1 | SRB_PATH_TILED_TAIL | SRB_PATH_SPLIT_C1TAIL)) && srb_c1tail_supported(H, W)) {
+        // conv1 + skip + conv2 + tanh -> uint8 as one launch: conv1's result never leaves the SM
+        if ((rc = srb_c1tail_fwd(ctx, net->rc1, net->tail, cur, x0, out, oflags, N, H, W, stream))) return rc;
+        prof_mark(ctx, pst, false, true);
+        return SRB_OK;
+    }
     if (fused && !(ctx->path & SRB_PATH_TILED_CONV1)) {
         if ((rc = srb_rowconv_fwd(ctx, net->rc1, cur, x0, ra, 0.f, 0, N, H, W, stream))) return rc;
     } else if ((rc = srb_conv2d_fwd(ctx, net->conv[17], cur, 8, 0, ra, 8, 0, x0, 8, 0, 1.f, 1.f, 0.f, SRB_F_RESIDUAL, N, H, W, stream))) return rc;
@@ -1902,6 +1909,9 @@ struct srb_tail9 {
     mutable RBMaps maps[2];
     mutable int next_map = 0;
     mutable bool attr_set = false;
+    mutable RBMaps fmaps[2];         // srb_c1tail_fwd: tensor maps of conv1's input
+    mutable int next_fmap = 0;
+    mutable bool fattr_set = false;
 };
 
 extern "C" void srb_tail9_destroy(srb_tail9* t) {
@@ -2002,6 +2012,69 @@ extern "C" int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, vo
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (t->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<true>, m->tm, p));
     else CUDA_TRY(cudaLaunchKernelEx(&cfg, tail9_kernel<false>, m->tm, p));
+    return SRB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv1 + long skip + conv2 9x9 + tanh -> uint8 in one launch (srb_c1tail.cuh): conv1's result stays on chip
+// ------------------------------------------------------------------------------------------
+extern "C" int srb_c1tail_supported(int H, int W) { return H > 0 && W >= 57; }     // (the exchange buffer holds rows of >= 8 groups)
+
+extern "C" int srb_c1tail_fwd(srb_ctx* ctx, const srb_rowconv* rc, const srb_tail9* t, const void* x, const void* res, void* y, int flags,
+                              int N, int H, int W, srb_stream_t stream) {
+    if (!ctx || !rc || !t || !x || !res || !y) return fail(SRB_EINVAL, "srb_c1tail_fwd: NULL argument");
+    if (N <= 0 || H <= 0 || W <= 0) return fail(SRB_EINVAL, "srb_c1tail_fwd: empty shape");
+    if (!srb_c1tail_supported(H, W)) return fail(SRB_ENOSUP, "srb_c1tail_fwd: W=%d (rows of at least 57 pixels; use srb_rowconv_fwd + srb_tail9_fwd)", W);
+    if (rc->dtype != t->dtype) return fail(SRB_EINVAL, "srb_c1tail_fwd: conv1 and conv2 were packed for different operand types");
+    if (((uintptr_t)x & 15) || ((uintptr_t)res & 15)) return fail(SRB_EINVAL, "srb_c1tail_fwd: buffers must be 16-byte aligned");
+    const int fmt = flags & (SRB_F_U8OUT | SRB_F_F32OUT);
+    if ((flags & ~(SRB_F_TANH | SRB_F_U8OUT | SRB_F_F32OUT | SRB_F_HWC_BGR)) || (fmt != SRB_F_U8OUT && fmt != SRB_F_F32OUT) ||
+        ((flags & SRB_F_HWC_BGR) && fmt != SRB_F_U8OUT))
+        return fail(SRB_ENOSUP, "srb_c1tail_fwd: flags 0x%x (SRB_F_TANH, exactly one of SRB_F_U8OUT / SRB_F_F32OUT, SRB_F_HWC_BGR only with U8OUT)", flags);
+    using G = CTGeom;
+    C1TailParams p{};
+    const long long sets = set_tile_geom(p, N, H, W, 1);
+    RBMaps* m = nullptr;
+    for (RBMaps& c : t->fmaps)
+        if (c.x == x && c.N == N && c.H == H && c.W == W) m = &c;
+    if (!m) {
+        m = &t->fmaps[t->next_fmap];
+        t->next_fmap ^= 1;
+        m->x = nullptr;
+        cuuint64_t gdim[4] = {(cuuint64_t)W * 4, (cuuint64_t)H, 8, (cuuint64_t)N};
+        cuuint64_t gstr[3] = {(cuuint64_t)W * 16, (cuuint64_t)W * H * 16, (cuuint64_t)W * H * 16 * 8};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        cuuint32_t box[4] = {40, 1, 8, 1};                              // one group with its halo
+        CUresult r = ctx->encode(&m->tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<void*>(x), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(SRB_ECUDA, "cuTensorMapEncodeTiled failed: %d", (int)r);
+        m->x = x; m->N = N; m->H = H; m->W = W;
+    }
+    if (sets * H > 0x7fffffffLL) return fail(SRB_EINVAL, "srb_c1tail_fwd: too many rows");
+    p.total_rows = (int)(sets * H);
+    p.w1 = rc->d_w; p.w2 = t->d_w;
+    memcpy(p.bias1, rc->h_bias, sizeof(p.bias1));
+    memcpy(p.bias2, t->h_bias, sizeof(p.bias2));
+    p.res = res; p.y = y; p.flags = flags;
+    int grid = p.total_rows / 8;
+    if (grid < 1) grid = 1;
+    if (grid > ctx->num_sms) grid = ctx->num_sms;
+    if (ctx->max_grid > 0 && grid > ctx->max_grid) grid = ctx->max_grid;
+    if (!t->fattr_set) {
+        CUDA_TRY(cudaFuncSetAttribute(c1tail_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(c1tail_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES));
+        t->fattr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(G::THREADS); cfg.dynamicSmemBytes = G::SMEM_BYTES;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (ctx->path & SRB_PATH_NO_PDL) ? 0 : 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (t->dtype == SRB_DT_BF16) CUDA_TRY(cudaLaunchKernelEx(&cfg, c1tail_kernel<true>, m->tm, p));
+    else CUDA_TRY(cudaLaunchKernelEx(&cfg, c1tail_kernel<false>, m->tm, p));
     return SRB_OK;
 }
 

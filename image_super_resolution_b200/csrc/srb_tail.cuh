@@ -52,7 +52,8 @@ struct TLGeom {
 
 // output rows [y0, y1) of strip-set ss and the input rows they need
 struct TLSeg { int ss, y0, y1, xlo, xhi; };
-__device__ __forceinline__ bool tl_next_seg(const TailParams& p, int& g, int g1, TLSeg& s) {
+template <class Params>
+__device__ __forceinline__ bool tl_next_seg(const Params& p, int& g, int g1, TLSeg& s) {
     if (g >= g1) return false;
     s.ss = g / p.H;
     s.y0 = g - s.ss * p.H;

@@ -554,6 +554,30 @@ class Tail9:
             pass
 
 
+def c1tail_supported(H: int, W: int) -> bool:
+    return bool(lib().srb_c1tail_supported(H, W))
+
+
+def c1tail_forward(rc: "RowConv", t: "Tail9", x: torch.Tensor, skip: torch.Tensor, tanh: bool = True, u8: bool = True,
+                   out: torch.Tensor | None = None, hwc_bgr: bool = False) -> torch.Tensor:
+    """conv1 + long skip + conv2 9x9 (+ tanh) -> uint8 / fp32 in ONE launch (srb_c1tail_fwd): `rc.forward(x, tmp, skip)` followed
+    by `t.forward(tmp)` with tmp kept in shared memory (utils/models.py:690, :704, :691, :448-451); bit-identical to the two calls."""
+    _require_cuda(x, "x"); _require_cuda(skip, "skip")
+    N, planes, H, W, _ = x.shape
+    if planes != 8 or skip.shape != x.shape:
+        raise RuntimeError("c1tail_forward: x and skip must be [N][8][H][W][8]")
+    dt = torch.uint8 if u8 else torch.float32
+    oshape = (N, H, W, 3) if hwc_bgr else (N, 3, H, W)
+    if out is None:
+        out = torch.empty(oshape, dtype=dt, device=x.device)
+    elif out.dtype != dt or out.numel() != N * 3 * H * W or not out.is_contiguous() or out.device != x.device:
+        raise RuntimeError("c1tail_forward: out must be a contiguous tensor of the output type and size on x's device")
+    flags = (F_TANH if tanh else 0) | (F_U8OUT if u8 else F_F32OUT) | (128 if hwc_bgr else 0)
+    check(lib().srb_c1tail_fwd(rc.ctx.handle, rc.handle, t.handle, x.data_ptr(), skip.data_ptr(), out.data_ptr(), flags, N, H, W,
+                               _stream_ptr(x.device)), "srb_c1tail_fwd")
+    return out
+
+
 class ResBlock:
     """Fused ResidualBlock1 (utils/models.py:208-209): y = x + convB(LeakyReLU(convA(x))) in one kernel (srb_resblock_*)."""
 

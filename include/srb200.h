@@ -72,6 +72,7 @@ int srb_num_sms(const srb_ctx* ctx);
 #define SRB_PATH_NO_PAIR 1048576          /* fused residual block on single CTAs (cta_group::1) instead of CTA pairs          */
 #define SRB_PATH_GROUP_BOXES 2097152      /* row-fold conv1 / tail: one TMA box per 8-px group instead of whole-row boxes       */
 #define SRB_PATH_PAIR4_HEAD 4194304       /* Normalize as its own pass into pixel-pair granules + conv0 on the tiled kernel    */
+#define SRB_PATH_SPLIT_C1TAIL 8388608     /* conv1 + skip and conv2 9x9 + tanh as two launches instead of the fused kernel          */
 int srb_set_option(srb_ctx* ctx, int key, int value);
 
 /* Fold BN (fuse_conv_and_bn, utils/models.py:366-406: bn4 = gamma,beta,mean,var each [cout]; NULL for
@@ -197,8 +198,8 @@ int srb_model_pt_forward_host(srb_ctx* ctx, srb_net* net, const uint8_t* in_host
 #define SRB_COPY_D2D 2
 int srb_copy_rect_u8(srb_ctx* ctx, void* dst, size_t dst_pitch, size_t dst_plane, const void* src, size_t src_pitch,
                      size_t src_plane, int planes, size_t width, size_t height, int kind, srb_stream_t stream);
-/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (11: head with the ingest folded
- * in, 8 fused residual blocks, conv1, tail) */
+/* number of kernels of this library one srb_model_pt_forward enqueues for H x W images (10: head with the ingest folded
+ * in, 8 fused residual blocks, conv1 + tail; 11 for rows under 57 pixels: conv1 and tail as two launches) */
 int srb_model_pt_launches(int H, int W);
 /* measurement only: record a CUDA event before/after every launch of srb_model_pt_forward on its stream;
  * srb_profile_read returns the per-launch milliseconds of the last forward (count written, <0 on error) */
@@ -264,6 +265,13 @@ typedef struct srb_tail9 srb_tail9;
 int srb_tail9_create(srb_ctx* ctx, const float* w, const float* bias, int dtype, srb_tail9** out);
 void srb_tail9_destroy(srb_tail9* t);
 int srb_tail9_fwd(srb_ctx* ctx, const srb_tail9* t, const void* x, void* y, int flags, int N, int H, int W, srb_stream_t stream);
+/* conv1 + long skip + conv2 + tanh + TanhToArrayImage as ONE launch (utils/models.py:690, :704, :691, :448-451): srb_rowconv_fwd
+ * followed by srb_tail9_fwd with conv1's 64-channel result kept in shared memory instead of HBM (bit-identical to the two calls).
+ * Takes the packed filters of an srb_rowconv and an srb_tail9 of the same operand type; rows of at least 57 pixels
+ * (srb_c1tail_supported), otherwise make the two calls.  flags as srb_tail9_fwd. */
+int srb_c1tail_supported(int H, int W);
+int srb_c1tail_fwd(srb_ctx* ctx, const srb_rowconv* rc, const srb_tail9* t, const void* x, const void* skip, void* y, int flags,
+                   int N, int H, int W, srb_stream_t stream);
 
 /* Weight gradient of a 3x3 conv (autograd of aten::_convolution, train.py:57):
  * dw[co][ci][dy][dx] += scale * sum_p dY[p][co] * X[p+(dy-1,dx-1)][ci].  x, dy: C8-plane slices (device);

@@ -65,6 +65,8 @@ def main():
         xi = torch.randint(0, 256, (256, 3, 64, 64), dtype=torch.uint8, device=dev); yo = torch.empty_like(xi)
         mean, std = [0.485, 0.456, 0.406], [0.229, 0.224, 0.225]
         m1 = cold(lambda: ra.forward(x, y, res)); m2 = cold(lambda: ta.forward(x, out=out)); m3 = cold(lambda: hd.forward(xi, mean, std, 0.2, out=y))
+        m4 = cold(lambda: ops.c1tail_forward(ra, ta, x, res, out=out))
+        print(f"QUICK conv1 + tail fused {m4[0]:6.1f} us (min {m4[1]:.1f})   two launches {m1[0] + m2[0]:6.1f} us", flush=True)
         model = srb.load(os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz")).to(dev).eval()
         for _ in range(3): model(xi, out=yo)
         f = cold(lambda: model(xi, out=yo), 12)
