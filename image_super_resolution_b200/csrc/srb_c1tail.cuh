@@ -33,6 +33,9 @@ struct C1TailParams {
     int flags;                // F_TANH, F_U8OUT (+ F_HWC_BGR), F_F32OUT
 };
 
+#ifndef CT_MID_WAIT
+#define CT_MID_WAIT RB_SLEEP_NS      // the mid epilogue's wait for a conv1 row: ns between polls (< 0: parked by the hardware)
+#endif
 struct CTGeom {
     static constexpr int C = 64;
     static constexpr int XBOX = 8 * 10 * 16, XROW = 16 * XBOX, XSTAGES = 3;      // x rows with their halo: 20 KB each
@@ -258,7 +261,7 @@ __global__ void __launch_bounds__(CTGeom::THREADS, 1) c1tail_kernel(const __grid
                 uint4 rq[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) rq[j] = nxt[j];
-                mbar_wait<RB_SLEEP>(&y1full[slot], (uint32_t)((c / G::RY1) & 1), 88);
+                mbar_wait<CT_MID_WAIT>(&y1full[slot], (uint32_t)((c / G::RY1) & 1), 88);
                 tc_fence_after();
                 uint32_t rr[32];
                 tmem_ld32(t_lane + slot * G::C, rr);
