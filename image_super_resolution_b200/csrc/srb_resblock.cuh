@@ -163,15 +163,30 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// L2 eviction priorities as cache-policy operands (the encodings createpolicy.fractional.L2::evict_{first,last} produce for a
+// fraction of 1.0).  RB_L2_HINTS: a block's result is the next block's input — kept in L2 with evict_last when it is stored and
+// released with evict_first on its last read (the residual add), so that the next launch finds most of its 134 MB input in the
+// 126 MB L2 instead of reading rows that were written a whole launch (268 MB of traffic) earlier.
+#ifndef RB_L2_HINTS
+#define RB_L2_HINTS 3      // bit 0: evict_first on the residual load, bit 1: evict_last on the result store (forward 803.9 -> 800.7 us, profiles/ab_l2hints_r2.log)
+#endif
+constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull, L2_EVICT_LAST = 0x14F0000000000000ull;
 __device__ __forceinline__ uint4 rb_ld_res(const uint4* p) {
-#if RB_IO_NOALLOC >= 1
+#if RB_L2_HINTS & 1
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(L2_EVICT_FIRST));
+    return r;
+#elif RB_IO_NOALLOC >= 1
     return ldg_nc16(p);
 #else
     return __ldg(p);
 #endif
 }
 __device__ __forceinline__ void rb_st_out(uint4* p, uint4 v) {
-#if RB_IO_NOALLOC >= 2
+#if RB_L2_HINTS & 2
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(L2_EVICT_LAST) : "memory");
+#elif RB_IO_NOALLOC >= 2
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 #else
     *p = v;
