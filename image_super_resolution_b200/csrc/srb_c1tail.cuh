@@ -251,7 +251,8 @@ __global__ void __launch_bounds__(CTGeom::THREADS, 1) c1tail_kernel(const __grid
             const size_t px0 = valid ? ((size_t)sl.n * 8 + 4 * half) * HW + (size_t)(sl.gx * 8 + i) : 0;
             const uint4* rg = reinterpret_cast<const uint4*>(p.res) + px0;
             // (one set of warps takes every row: the skip of row m + 1 is requested while row m is finished, or its DRAM round
-            // trip would sit between the drain and the shared-memory stores of every row)
+            // trip would sit between the drain and the shared-memory stores of every row; two rows of lead measured slower:
+            // 108.2 against 104.0 us)
             uint4 nxt[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) nxt[j] = valid ? ldg_nc16(rg + j * HW + (size_t)sg.xlo * p.W) : make_uint4(0, 0, 0, 0);

@@ -61,8 +61,14 @@ struct ResblockParams {
 #endif
 #endif
 #ifndef RB_HSLOTS
-#define RB_HSLOTS 3
+#define RB_HSLOTS 2            // hidden rows in shared memory: 2 vs 3 slots measure equal (profiles/ab_hslots_r2.log); the third paid for an x stage
+#endif
+#ifndef RB_XSTAGES
 #define RB_XSTAGES 4
+#endif
+#ifndef RB_XSTAGES2
+#define RB_XSTAGES2 4          // x ring of the CTA-pair kernel (its filters take 120 KB): 3 -> 4 stages = forward 798.2 -> 787.8 us;
+                               // ncu's samples had the convA issuers waiting 24 % of their time for an x row with three stages
 #endif
 #ifndef RB_BIAS_MODE
 #define RB_BIAS_MODE 1       // 0: accumulator rows armed with the bias (re-armed from shared memory); 1: rows armed with zero,
@@ -102,7 +108,7 @@ struct RBGeom {
     //   arrangement 2: pieces (0,2) then (2,1)      ... split after its second row / a bottom edge
     //   arrangement 3: piece (1,1)                  one-row segments
     // rows per CTA and arrangement: 3*CO/2 (arrangement 3: CO/2); bytes: K-steps x 2 granules x rows x 16.
-    static constexpr int XSTAGES2 = 3;
+    static constexpr int XSTAGES2 = RB_XSTAGES2;
     static constexpr int W2_ARR = KA * 2 * (3 * CH / 2) * 16;                        // 18432 (convB: KB * 2 * (3*CB/2) * 16 = the same)
     static constexpr int W2_P3 = KA * 2 * (CH / 2) * 16;                             // 6144
     static constexpr int W2_BYTES = 3 * W2_ARR + W2_P3;                              // 61440 per conv and CTA
