@@ -333,6 +333,51 @@ __device__ __forceinline__ void rb_issue2(const RBPlan2& q, uint64_t a_desc, int
     if (q.two) umma_f16_ss_pair(q.d1, a_desc, q.b1 + (uint64_t)(kk * q.ks1), q.idesc1, 1u);
 }
 
+// ---- Steady-state issue path of the CTA-pair kernel -------------------------------------------------------------------------
+// ncu's samples (profiles/ncu_fwd_r2_ingest_full.txt, source page) have the MMA-issuing threads busy three quarters of the time
+// with their own instruction stream — about 270 SASS instructions per row and issuer, most of them the per-row plan (which
+// arrangement, which piece, 64-bit descriptor arithmetic) — while the UTCHMMAs themselves almost never stall.  For a window of
+// three rows with no clipping (every row but a segment's first and last) the plan depends only on the ring slot of the window's
+// first row, so it is compiled four times with everything folded: a descriptor is {low word = a run-time base + an immediate,
+// high word = a constant}, one add per operand and MMA.  Same MMAs in the same order as rb_plan2 / rb_issue2.
+#ifndef RB_STEADY
+#define RB_STEADY 1
+#endif
+template <int CO, int KST, int S0, int N, bool BF16>
+struct RBPieceC {          // rb_piece2 at compile time
+    static constexpr int ROWS = 3 * CO / 2, ARR = KST * 2 * ROWS * 16;
+    static constexpr int arr = N == 3 ? 0 : N == 2 ? (S0 == 1 ? 1 : 2) : (S0 == 0 ? 1 : (S0 == 2 ? 2 : 3));
+    static constexpr int off = N == 3 ? 0 : N == 2 ? (S0 == 1 ? CO / 2 : 0) : (S0 == 2 ? CO : 0);
+    static constexpr int rows = arr == 3 ? CO / 2 : ROWS;
+    static constexpr uint32_t lo = (uint32_t)((arr * ARR + off * 16) >> 4) + ((uint32_t)rows << 16);    // + (w_addr >> 4): address and LBO fields
+    static constexpr uint32_t ks = (uint32_t)((2 * rows * 16) >> 4);
+    static constexpr uint32_t idesc = umma_idesc_f16(256, N * CO, BF16 ? 1 : 0);
+};
+__device__ __forceinline__ void umma_pair_lohi(uint32_t d, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\tsetp.eq.u32 p, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}"
+        ::"r"(d), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc) : "memory");
+}
+// NK K-steps i: the A operand of step i starts (i & 1) * 20 + (i >> 1) granules into the row (channel pair, dx), its filters are
+// K-step (CONVA ? (i >> 1) * 4 + (i & 1) : i) of the pack; a K-split issuer's channel offset is part of alo / wlo
+template <int CO, int R, int KST, int SLOT, int NK, bool CONVA, bool BF16>
+__device__ __forceinline__ void rb_steady2(uint32_t tm_ring, uint32_t wlo, uint32_t alo, uint32_t ahi) {
+    constexpr int N1 = (R - SLOT < 3) ? R - SLOT : 3;
+    constexpr bool TWO = N1 < 3;
+    using Q0 = RBPieceC<CO, KST, 0, N1, BF16>;
+    using Q1 = RBPieceC<CO, KST, TWO ? N1 : 0, TWO ? 3 - N1 : 3, BF16>;
+    constexpr uint32_t BHI = (128u >> 4) | (1u << 14);
+#pragma unroll
+    for (int i = 0; i < NK; ++i) {
+        const uint32_t aimm = (uint32_t)((i & 1) * 20 + (i >> 1));
+        const uint32_t kimm = (uint32_t)(CONVA ? (i >> 1) * 4 + (i & 1) : i);
+        umma_pair_lohi(tm_ring + SLOT * CO, alo + aimm, ahi, wlo + Q0::lo + kimm * Q0::ks, BHI, Q0::idesc);
+        if constexpr (TWO) umma_pair_lohi(tm_ring, alo + aimm, ahi, wlo + Q1::lo + kimm * Q1::ks, BHI, Q1::idesc);
+    }
+}
+
 template <bool BF16, bool PAIR = false>
 __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __grid_constant__ CUtensorMap tmap_x,
                                                                       const ResblockParams p) {
@@ -546,6 +591,18 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (elect_one()) {
                     const uint64_t adA = adescA0 + (uint64_t)(smem_u32(s_x + xst * G::XROW) >> 4);
                     if constexpr (PAIR) {
+                        if (RB_STEADY && G::KSPLIT == 2 && G::RH == 4 && a_n == 3 && a_s0 == 0) {
+                            // (K-split: this issuer's channel pairs c2 = 2 * kh + cc start kh * 40 granules into the row, its K-steps at 2 * kh)
+                            const uint32_t alo = (10u << 16) + (smem_u32(s_x + xst * G::XROW) >> 4) + (uint32_t)kh * 40u;
+                            const uint32_t wlo = (wA_u32 >> 4) + (uint32_t)kh * 2u * RBPieceC<G::CH, G::KA, 0, 3, BF16>::ks;
+                            constexpr uint32_t AHI = (uint32_t)(G::XBOX >> 4) | (1u << 14);
+                            switch (slot_lo) {
+                                case 0: rb_steady2<G::CH, 4, G::KA, 0, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
+                                case 1: rb_steady2<G::CH, 4, G::KA, 1, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
+                                case 2: rb_steady2<G::CH, 4, G::KA, 2, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
+                                default: rb_steady2<G::CH, 4, G::KA, 3, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
+                            }
+                        } else {
                         const RBPlan2 q2 = rb_plan2<G::CH, G::RH, G::KA, BF16>(tm_ring_a, wA_u32, slot_lo, a_n, a_s0);
 #pragma unroll
                         for (int dx = 0; dx < 3; ++dx)
@@ -554,6 +611,7 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                                 const int c2 = (G::KSPLIT == 2 ? 2 * kh : 0) + cc, kk = dx * 4 + c2;
                                 rb_issue2(q2, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), kk);
                             }
+                        }
                         umma_commit_pair(&xempty[xst]);
                         if (r - 1 >= sg.hlo) umma_commit_pair(&hafull[(hslot0 + (r - 1 - sg.hlo)) % G::RH]);
                         if (r == sg.xhi && r <= sg.hhi) umma_commit_pair(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
@@ -619,11 +677,24 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                 if (elect_one()) {
                     const uint64_t adB = adescB0 + (uint64_t)(smem_u32(s_h + hs * G::HROW) >> 4);
                     if constexpr (PAIR) {
+                        if (RB_STEADY && G::RY == 4 && b_n == 3 && b_s0 == 0) {
+                            const uint32_t alo = (10u << 16) + (smem_u32(s_h + hs * G::HROW) >> 4);
+                            const uint32_t wlo = wB_u32 >> 4;
+                            constexpr uint32_t AHI = (uint32_t)(G::HBOX >> 4) | (1u << 14);
+                            const uint32_t tm_y = tmem_base + G::TM_Y;
+                            switch (slot_lo) {
+                                case 0: rb_steady2<G::CB, 4, G::KB, 0, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
+                                case 1: rb_steady2<G::CB, 4, G::KB, 1, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
+                                case 2: rb_steady2<G::CB, 4, G::KB, 2, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
+                                default: rb_steady2<G::CB, 4, G::KB, 3, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
+                            }
+                        } else {
                         const RBPlan2 q2 = rb_plan2<G::CB, G::RY, G::KB, BF16>(tmem_base + G::TM_Y, wB_u32, slot_lo, b_n, b_s0);
 #pragma unroll
                         for (int k = 0; k < G::KB; ++k) {
                             const int dx = k >> 1, c2 = k & 1;
                             rb_issue2(q2, adB + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), k);
+                        }
                         }
                         umma_commit_pair(&hsempty[hs]);
                         if (h - 1 >= sg.y0) umma_commit_pair(&yafull[(yslot0 + (h - 1 - sg.y0)) % G::RY]);
