@@ -596,12 +596,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                             const uint32_t alo = (10u << 16) + (smem_u32(s_x + xst * G::XROW) >> 4) + (uint32_t)kh * 40u;
                             const uint32_t wlo = (wA_u32 >> 4) + (uint32_t)kh * 2u * RBPieceC<G::CH, G::KA, 0, 3, BF16>::ks;
                             constexpr uint32_t AHI = (uint32_t)(G::XBOX >> 4) | (1u << 14);
-                            switch (slot_lo) {
-                                case 0: rb_steady2<G::CH, 4, G::KA, 0, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
-                                case 1: rb_steady2<G::CH, 4, G::KA, 1, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
-                                case 2: rb_steady2<G::CH, 4, G::KA, 2, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
-                                default: rb_steady2<G::CH, 4, G::KA, 3, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); break;
-                            }
+                            // (a full window: hidden row r - 1 sits in ring slot slot_lo and is now complete; row r is not the segment's last)
+#define RB_CASE_A(S) case S: rb_steady2<G::CH, 4, G::KA, S, 6, true, BF16>(tm_ring_a, wlo, alo, AHI); umma_commit_pair(&xempty[xst]); umma_commit_pair(&hafull[S]); break;
+                            switch (slot_lo) { RB_CASE_A(0) RB_CASE_A(1) RB_CASE_A(2) default: RB_CASE_A(3) }
+#undef RB_CASE_A
                         } else {
                         const RBPlan2 q2 = rb_plan2<G::CH, G::RH, G::KA, BF16>(tm_ring_a, wA_u32, slot_lo, a_n, a_s0);
 #pragma unroll
@@ -611,10 +609,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                                 const int c2 = (G::KSPLIT == 2 ? 2 * kh : 0) + cc, kk = dx * 4 + c2;
                                 rb_issue2(q2, adA + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), kk);
                             }
-                        }
                         umma_commit_pair(&xempty[xst]);
                         if (r - 1 >= sg.hlo) umma_commit_pair(&hafull[(hslot0 + (r - 1 - sg.hlo)) % G::RH]);
                         if (r == sg.xhi && r <= sg.hhi) umma_commit_pair(&hafull[(hslot0 + (r - sg.hlo)) % G::RH]);
+                        }
                     } else {
                     const RBPlan q = rb_plan<G::CH, G::RH, BF16>(tm_ring_a, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RH - 3 ? G::RH - 3 : slot_lo, a_n, a_s0);
                     if (!SRB_DBG(p.dbg_skip & (2 | 16))) {
@@ -682,12 +680,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                             const uint32_t wlo = wB_u32 >> 4;
                             constexpr uint32_t AHI = (uint32_t)(G::HBOX >> 4) | (1u << 14);
                             const uint32_t tm_y = tmem_base + G::TM_Y;
-                            switch (slot_lo) {
-                                case 0: rb_steady2<G::CB, 4, G::KB, 0, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
-                                case 1: rb_steady2<G::CB, 4, G::KB, 1, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
-                                case 2: rb_steady2<G::CB, 4, G::KB, 2, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
-                                default: rb_steady2<G::CB, 4, G::KB, 3, G::KB, false, BF16>(tm_y, wlo, alo, AHI); break;
-                            }
+                            // (a full window: output row h - 1 sits in ring slot slot_lo and is now complete; row h is not the segment's last)
+#define RB_CASE_B(S) case S: rb_steady2<G::CB, 4, G::KB, S, G::KB, false, BF16>(tm_y, wlo, alo, AHI); umma_commit_pair(&hsempty[hs]); umma_commit_pair(&yafull[S]); break;
+                            switch (slot_lo) { RB_CASE_B(0) RB_CASE_B(1) RB_CASE_B(2) default: RB_CASE_B(3) }
+#undef RB_CASE_B
                         } else {
                         const RBPlan2 q2 = rb_plan2<G::CB, G::RY, G::KB, BF16>(tmem_base + G::TM_Y, wB_u32, slot_lo, b_n, b_s0);
 #pragma unroll
@@ -695,10 +691,10 @@ __global__ void __launch_bounds__(RBGeom::THREADS, 1) resblock_kernel(const __gr
                             const int dx = k >> 1, c2 = k & 1;
                             rb_issue2(q2, adB + (uint64_t)((2 * c2 * 160 + dx * 16) >> 4), k);
                         }
-                        }
                         umma_commit_pair(&hsempty[hs]);
                         if (h - 1 >= sg.y0) umma_commit_pair(&yafull[(yslot0 + (h - 1 - sg.y0)) % G::RY]);
                         if (h == sg.hhi && h <= sg.y1 - 1) umma_commit_pair(&yafull[(yslot0 + (h - sg.y0)) % G::RY]);
+                        }
                     } else {
                     const RBPlan q = rb_plan<G::CB, G::RY, BF16>(tmem_base + G::TM_Y, SRB_DBG(p.dbg_skip & 512) && slot_lo > G::RY - 3 ? G::RY - 3 : slot_lo, b_n, b_s0);
                     if (!SRB_DBG(p.dbg_skip & (2 | 32))) {
