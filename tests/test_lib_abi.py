@@ -73,3 +73,17 @@ def test_product_has_no_oracle_or_cpu_fallback():
     m = srb.load(os.path.join(ROOT, "tests", "golden", "model_pt_weights.npz"))
     with pytest.raises(RuntimeError):
         m.to("cpu")
+
+
+def test_python_constants_mirror_the_header():
+    """The option / path / layout constants of the ctypes binding are the header's #defines (a drifted bit would silently select
+    another kernel family)."""
+    from image_super_resolution_b200 import _lib
+    src = open(os.path.join(ROOT, "include", "srb200.h")).read()
+    defs = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define\s+(SRB_[A-Z0-9_]+)\s+(\d+)\b", src)}
+    for name, val in vars(_lib).items():
+        if name.startswith(("PATH_", "OPT_")) and isinstance(val, int):
+            assert defs.get("SRB_" + name) == val, (name, val, defs.get("SRB_" + name))
+    assert defs["SRB_LAYOUT_NCHW_RGB"] == 0 and defs["SRB_LAYOUT_NHWC_BGR"] == 1 and defs["SRB_LAYOUT_NHWC_RGB"] == 2
+    from image_super_resolution_b200.modelpt import ModelPT
+    assert ModelPT._IN_LAYOUTS == {"nchw": 0, "hwc_bgr": 1, "hwc_rgb": 2}
